@@ -1,0 +1,147 @@
+"""Pin the CPU oracle (oracle/md_oracle.c) before anything is compared with it.
+
+Anchors, in order of authority:
+  1. the notebook known-answer vector of the reference (V_Calculations/Test-1/tutorial.ipynb:231-271);
+  2. outputs of the reference's unmodified TorchMD_Fix/forces.py in fp64 / fp32 (tests/golden/*.npz,
+     produced by tools/make_golden.py);
+  3. the colvar known answers (smd_out.colvars.traj) for the SMD end-to-end distance;
+  4. the restated upstream velocity-Verlet loop driving the reference forces.py (unpinned upstream).
+"""
+import numpy as np
+import pytest
+
+import oracle
+from conftest import MODES, SYSTEMS, load_golden
+from molecular_dynamics_b200 import _cabi
+
+TIMEFACTOR = 48.88821
+
+
+def test_known_answer_vector_energies_and_forces():
+    g = load_golden("bb40")
+    f, e = oracle.forces(g.packed, g["pos"], **MODES["rf"])
+    kat_e, kat_f = g["kat_energies"], g["kat_forces"]
+    # stored at full fp32 precision: the fp64 oracle must agree to fp32 rounding of the reference path
+    np.testing.assert_allclose(e[0], kat_e, rtol=2e-6, atol=1e-9)
+    assert kat_f.shape == (40, 3)
+    # forces are printed to 5 significant figures
+    np.testing.assert_allclose(f[0], kat_f, rtol=2e-4, atol=2e-4 * np.abs(kat_f).max() * 1e-1)
+    # the reference itself, rerun here in fp32, reproduced the notebook bit-for-bit
+    np.testing.assert_array_equal(g["ref_rf_f32_energies"][0].astype(np.float32), kat_e.astype(np.float32))
+
+
+@pytest.mark.parametrize("system", SYSTEMS)
+@pytest.mark.parametrize("mode", list(MODES))
+def test_oracle_matches_reference_fp64(system, mode):
+    g = load_golden(system)
+    f, e = oracle.forces(g.packed, g["pos"], **MODES[mode])
+    ref_f, ref_e = g[f"ref_{mode}_f64_forces"], g[f"ref_{mode}_f64_energies"]
+    np.testing.assert_allclose(e, ref_e, rtol=1e-11, atol=1e-10)
+    assert np.abs(f - ref_f).max() <= 1e-11 * np.abs(ref_f).max()
+    # and sits within fp32 rounding of the reference's fp32 run
+    ref32 = g[f"ref_{mode}_f32_forces"]
+    assert np.abs(f - ref32).max() <= 2e-5 * np.abs(ref_f).max()
+
+
+def test_oracle_batched_frames_bb40():
+    g = load_golden("bb40")
+    for mode in MODES:
+        f, e = oracle.forces(g.packed, g["frames"], **MODES[mode])
+        np.testing.assert_allclose(e, g[f"frames_ref_{mode}_f64_energies"], rtol=1e-11, atol=1e-10)
+        assert np.abs(f - g[f"frames_ref_{mode}_f64_forces"]).max() < 1e-9
+
+
+def test_pair_index_is_bit_exact():
+    """Forces._make_indeces (forces.py:346-355) restated in _cabi.make_pair_index."""
+    for system in SYSTEMS:
+        g = load_golden(system)
+        mine = _cabi.make_pair_index(g.par.natoms, g.par.get_exclusions(("bonds", "angles", "1-4")))
+        assert mine.dtype == np.int64
+        np.testing.assert_array_equal(mine, g.ava_idx)
+
+
+def test_smd_bias_energy_and_force():
+    g = load_golden("ala10")
+    a1, a2, fk, c = g["smd"]
+    smd = dict(atom1=int(a1), atom2=int(a2), fk=fk, center0=c)
+    f, e = oracle.forces(g.packed, g["pos"], smd=smd)
+    np.testing.assert_allclose(e, g["ref_smd_plain_f64_energies"], rtol=1e-11, atol=1e-10)
+    assert np.abs(f - g["ref_smd_plain_f64_forces"]).max() < 1e-9
+    g = load_golden("bb40_improper")
+    a1, a2, fk, c = g["smd"]
+    smd = dict(atom1=int(a1), atom2=int(a2), fk=fk, center0=c)
+    f, e = oracle.forces(g.packed, g["pos"], smd=smd, **MODES["rf"])
+    np.testing.assert_allclose(e, g["ref_smd_rf_f64_energies"], rtol=1e-11, atol=1e-10)
+    assert np.abs(f - g["ref_smd_rf_f64_forces"]).max() < 1e-9
+
+
+def test_colvar_known_answers():
+    """|r98 - r3| of each run's final frame equals the End2EndDist NAMD logged (50 runs)."""
+    g = load_golden("ala10")
+    base, kat = g["base_frames"], g["kat_colvar"]
+    for r in range(50):
+        final = base[1 + 2 * r]
+        d = np.linalg.norm(final[98] - final[3])
+        assert abs(d - kat[r, 0]) < 5e-7 * kat[r, 0]
+        assert kat[r, 1] == 34.0  # moving centre reached 12 + 22 * step/500000
+
+
+def test_per_replica_smd_centres():
+    g = load_golden("ala10")
+    pos = g["pos"]
+    cen = np.linspace(12, 34, len(pos)).astype(np.float32)
+    smd = dict(atom1=3, atom2=98, fk=1.0, center0=0.0)
+    _, e = oracle.forces(g.packed, pos, smd=smd, smd_centers=cen)
+    d = np.linalg.norm(pos[:, 98].astype(np.float64) - pos[:, 3], axis=1)
+    np.testing.assert_allclose(e[:, 7], 0.5 * (cen - d) ** 2, rtol=1e-12)
+
+
+def test_nan_guard():
+    g = load_golden("diala")
+    pos = g["pos"].copy()
+    pos[1, 3, 2] = np.nan
+    with pytest.raises(RuntimeError, match="Found NaN coordinates."):
+        oracle.forces(g.packed, pos)
+
+
+@pytest.mark.parametrize("system", ["bb40", "ala10"])
+def test_oracle_integrator_matches_restated_upstream_loop(system):
+    g = load_golden(system)
+    n = len(g["vv_vel0"])
+    pos0 = (g["frames"] if system == "bb40" else g["pos"])[:n]
+    f0, _ = oracle.forces(g.packed, pos0)
+    assert np.abs(f0 - g["vv_forces0"]).max() < 1e-9
+    nsteps, dt = int(g["vv_nsteps"]), float(g["vv_dt_fs"]) / TIMEFACTOR
+    out = oracle.integrate(g.packed, pos0, g["vv_vel0"], f0, nsteps=nsteps, dt=np.float32(dt), energy_every=1)
+    # dt is rounded to fp32 at the C-ABI (as the GPU path sees it): 6e-8 relative on dt
+    np.testing.assert_allclose(out["pos"], g["vv_pos"], atol=2e-6)
+    np.testing.assert_allclose(out["vel"], g["vv_vel"], rtol=0, atol=2e-6 * np.abs(g["vv_vel"]).max() * 10)
+    epot = out["observables"][:, :, :8].sum(-1)
+    np.testing.assert_allclose(epot, g["vv_epot"], rtol=1e-6, atol=1e-5)
+    np.testing.assert_allclose(out["observables"][:, :, _cabi.OBS_EKIN], g["vv_ekin"], rtol=1e-5)
+    # NVE: total energy conserved over the short run
+    etot = epot + out["observables"][:, :, _cabi.OBS_EKIN]
+    assert np.abs(etot - etot[0]).max() < 0.3  # 1 fs VV fluctuation, no drift
+
+
+def test_philox_known_answer_and_normals():
+    # Random123 known-answer test for philox4x32-10, zero counter and key
+    np.testing.assert_array_equal(oracle.philox(0, 0, 0, 0, 0),
+                                  np.array([0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8], dtype=np.uint32))
+    # Random123 kat: counter/key all ones
+    np.testing.assert_array_equal(oracle.philox(0xFFFFFFFFFFFFFFFF, 0xFFFFFFFF, 0xFFFFFFFF, 0xFFFFFFFF, 0xFFFFFFFF),
+                                  np.array([0x408F276D, 0x41C83B0E, 0xA20BC7C6, 0x6D5451FD], dtype=np.uint32))
+    xs = np.array([oracle.normal3(7, r, a, s) for r in range(8) for a in range(20) for s in range(20)])
+    assert abs(xs.mean()) < 0.03 and abs(xs.std() - 1.0) < 0.03
+
+
+def test_langevin_thermostat_reaches_temperature():
+    g = load_golden("diala")
+    pos0 = np.repeat(g["pos"][:1], 16, axis=0)
+    f0, _ = oracle.forces(g.packed, pos0)
+    dt, gamma = 1.0 / TIMEFACTOR, 10.0 / (1000.0 / TIMEFACTOR)
+    out = oracle.integrate(g.packed, pos0, np.zeros_like(pos0), f0, nsteps=4000, dt=dt, gamma=gamma,
+                           temperature=300.0, seed=3, energy_every=100)
+    ekin = out["observables"][10:, :, _cabi.OBS_EKIN]
+    T = 2.0 / (3 * 22 * 0.001987191) * ekin.mean()
+    assert 255 < T < 345
