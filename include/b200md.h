@@ -61,6 +61,7 @@ enum b200md_status {
 
 /* per-replica status flags written by the kernels (uint32 per replica) */
 #define B200MD_FLAG_NAN_POS 1u
+#define B200MD_FLAG_PBC_UNSUPPORTED 2u /* non-zero box diagonal: minimum-image path not built yet */
 
 /*
  * Host-side description of one molecule's parameters: the flattened content of the `parameters`

@@ -1,1 +1,15 @@
-"""B200-native drop-in for the TorchMD force-field + integrator hot path of johncava/Molecular_Dynamics."""
+"""B200-native drop-in for the TorchMD force-field + integrator hot path of johncava/Molecular_Dynamics.
+
+    from molecular_dynamics_b200 import Forces, System, Integrator, maxwell_boltzmann, Parameters
+
+mirrors ``torchmd.forces.Forces`` / ``torchmd.systems.System`` (the reference's TorchMD_Fix copies) and
+upstream ``torchmd.integrator``.  The compute path is libb200md.so (hand-written sm_100a CUDA behind the
+C-ABI of include/b200md.h); importing this package never imports the CPU oracle.
+"""
+from .forces import Forces, SMDBias
+from .integrator import BOLTZMAN, TIMEFACTOR, Integrator, kinetic_energy, kinetic_to_temp, maxwell_boltzmann
+from .parameters import Parameters, parameters_from_prmtop, parameters_from_psf_yaml
+from .systems import System
+
+__all__ = ["Forces", "SMDBias", "System", "Integrator", "maxwell_boltzmann", "kinetic_energy", "kinetic_to_temp",
+           "Parameters", "parameters_from_prmtop", "parameters_from_psf_yaml", "TIMEFACTOR", "BOLTZMAN"]

@@ -1,0 +1,82 @@
+"""Differentiable energies for the ML callers.
+
+The reference's TorchMD_Fix patches exist so that per-term energies stay differentiable w.r.t. the
+positions (systems.py:54, forces.py:341-344; consumed at cGAN/cGAN_D_pos-2.3.2/cgan.py:351-360).  Here
+the energies come from a kernel, so the graph edge is provided by an autograd.Function whose backward is
+
+    d(sum_k g_k E_k)/d pos = - sum_k g_k F_k
+
+When every enabled term of a replica receives the same upstream weight the total force of the forward
+launch is reused; otherwise the per-term forces F_k are recomputed with one extra launch per term group.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _cabi
+
+_B = _cabi.TERM_BITS
+# energy column -> term bits whose forces belong to that column (1-4 energies are booked under lj /
+# electrostatics, forces.py:202-226)
+_COLUMN_TERMS = {
+    0: lambda m: (m & _B["electrostatics"]) | (m & _B["1-4"]),
+    1: lambda m: (m & _B["lj"]) | (m & _B["1-4"]),
+    2: lambda m: m & _B["bonds"],
+    3: lambda m: m & _B["angles"],
+    4: lambda m: m & _B["dihedrals"],
+    6: lambda m: m & _B["impropers"],
+}
+
+
+class _EnergyFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pos, fobj, box, forces):
+        ene = fobj.compute_batch(pos, box, forces)
+        ctx.fobj = fobj
+        ctx.save_for_backward(pos.detach().contiguous(), box.detach(), forces.detach().clone())
+        ctx.in_dtype = pos.dtype
+        return ene.to(pos.dtype)
+
+    @staticmethod
+    def backward(ctx, g):
+        pos, box, ftot = ctx.saved_tensors
+        fobj = ctx.fobj
+        from .forces import SMDBias
+
+        mask = fobj._terms_mask
+        cols = [c for c, fn in _COLUMN_TERMS.items() if fn(mask)]
+        smd = isinstance(fobj.external, SMDBias)
+        if smd:
+            cols.append(7)
+        if not cols:
+            return torch.zeros_like(pos), None, None, None
+        gsel = g[:, cols]
+        if bool((gsel == gsel[:, :1]).all()):  # uniform weight per replica: reuse the forward launch
+            grad = -gsel[:, :1, None] * ftot
+            return grad.to(ctx.in_dtype), None, None, None
+        b = box.to(device=pos.device, dtype=torch.float32).contiguous()
+        grad = torch.zeros_like(pos)
+        tmp = torch.empty_like(pos)
+        for c in cols:
+            if c == 7:
+                fobj._launch(pos, b, tmp, terms_mask=0, with_smd=True)
+            else:
+                fobj._launch(pos, b, tmp, terms_mask=_COLUMN_TERMS[c](mask), with_smd=False)
+            grad -= g[:, c:c + 1, None] * tmp
+        return grad.to(ctx.in_dtype), None, None, None
+
+
+def energies_with_grad(fobj, pos, box, forces):
+    """(R, 8) energies in pos.dtype, differentiable w.r.t. ``pos``; fills ``forces`` like compute()."""
+    from .forces import SMDBias
+
+    ene = _EnergyFunction.apply(pos, fobj, box, forces)
+    ext = fobj.external
+    if ext is not None and not isinstance(ext, SMDBias):
+        # generic external object: its own torch ops carry the graph (forces.py:318-323); the forward above
+        # already added its detached energy/force, so only the graph edge is added here
+        ext_ene, _ = ext.calculate(pos, box)
+        col = torch.zeros_like(ene)
+        col[:, 7] = ext_ene.reshape(-1).to(ene.dtype) - ext_ene.detach().reshape(-1).to(ene.dtype)
+        ene = ene + col
+    return ene

@@ -1,0 +1,164 @@
+// b200md_kernels.cuh -- device code of the B200-native TorchMD force-field + integrator path.
+//
+// Mapping: one CTA of 128 threads (4 warps) per replica.  Positions (+ charge) live in
+// shared memory as float4[128]; the non-bonded half matrix is cut into "j-chunks" of 8 atoms; a warp
+// that owns a chunk sweeps the 32-lane i-blocks below it, every lane keeping its own i-atom force in
+// registers and 8 x 3 j-force partials that are butterfly-reduced with warp shuffles once per chunk.
+// Bonded terms are type-uniform chunks of 32 items whose force vectors go to private shared-memory
+// slots and are gathered per atom in a fixed order, so every reduction is deterministic and there is
+// not a single atomic on the force path.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/b200md.h"
+
+namespace b200md {
+
+constexpr int kThreads = 128;
+constexpr int kWarps = 4;
+constexpr int kMaxAtoms = B200MD_MAX_ATOMS;  // 128
+constexpr int kChunk = 8;                    // atoms per j-chunk
+constexpr int kMaxChunks = kMaxAtoms / kChunk;
+constexpr int kAbStride = kMaxAtoms + 1;     // float2 per LJ-table row: (2t + 2j) mod 32 is conflict-free
+constexpr int kMaxTasks = 64;                // per warp
+constexpr float kElecFactor = 332.06371307417066f;  // forces.py:373-376
+constexpr float kBoltzman = 0.001987191f;           // upstream torchmd.integrator
+
+// task kinds (one task = one warp-wide unit of work, scheduled statically on the host)
+enum TaskKind : uint32_t { TASK_TILE = 0, TASK_BOND = 1, TASK_ANGLE = 2, TASK_DIHEDRAL = 3, TASK_IMPROPER = 4, TASK_P14 = 5 };
+__host__ __device__ inline uint32_t make_task(uint32_t kind, uint32_t chunk, uint32_t passes) {
+  return kind | (chunk << 8) | (passes << 24);
+}
+
+// Device view of a packed topology.  All pointers point into one device allocation.
+struct DevTopo {
+  int natoms, ntypes, nchunks;
+  const float2* ab;         // [ntypes][kAbStride]  (A, B) of (type t, atom j)
+  const float* charge;      // [128]
+  const float* mass;        // [128]
+  const int* ab_row_off;    // [128] byte offset of atom's LJ-table row
+  const uint8_t* mask8;     // [kMaxChunks][128] bit s: pair (i, 8*chunk+s) is NOT evaluated
+  int nbonds, nangles, ndih, nimp, n14;
+  const uint32_t* bond_idx;  const float2* bond_prm;
+  const uint32_t* angle_idx; const float2* angle_prm;
+  const uint32_t* dih_idx;   const uint2* dih_terms;  const float4* dih_term_prm;
+  const uint32_t* imp_idx;   const uint2* imp_terms;  const float4* imp_term_prm;
+  const uint32_t* p14_idx;   const float4* p14_prm;   // A/scnb, B/scnb, K qi qj/scee, 0
+  // bonded force slots: slot(type, pos, item) = base[type] + pos * pad[type] + item
+  int slot_base[6], slot_pad[6], nslots;
+  const uint16_t* gather_start;  // [129]
+  const uint16_t* gather_list;   // [gather_total] slot ids, per atom, fixed order
+  int gather_total;
+  const uint32_t* tasks;  // [kWarps][kMaxTasks]
+  int ntasks[kWarps];
+  int smem_bytes;
+};
+
+struct ForceParams {
+  uint32_t terms;
+  int has_cutoff;
+  float rc, rc2, rs, inv_sw;  // cutoff, cutoff^2, switch_dist (or +inf), 1/(rc-rs)
+  float krf, crf;             // reaction-field constants (0 when rfa is off)
+  float lj_on, el_on;
+  int smd_on, smd_a1, smd_a2;
+  float smd_fk, smd_c0, smd_rate;
+  const float* smd_centers;
+};
+
+struct StepParams {
+  float dt, gamma, temperature;
+  unsigned long long seed, step0;
+  long long replica0;
+  int nsteps, energy_every, snapshot_every;
+};
+
+// ---- shared-memory carve-up -----------------------------------------------------------------
+struct Smem {
+  float4* pos;        // [128]
+  float2* ab;         // [ntypes*kAbStride]
+  int* ab_row_off;    // [128]
+  uint8_t* mask8;     // [kMaxChunks*128]
+  float* fi;          // [kWarps][3][128]
+  float* fj;          // [3][128]
+  float* fb;          // [3][nslots]
+  uint16_t* gstart;   // [130]
+  uint16_t* glist;    // [gather_total]
+  uint32_t* tasks;    // [kWarps*kMaxTasks]
+  double* ered;       // [kWarps][10]
+  float* smd;         // [8]: force on atom2 (xyz), energy, distance
+};
+
+__host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
+
+__host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, int nslots, int gather_total) {
+  size_t o = 0;
+  auto take = [&](size_t bytes) { size_t r = o; o = align16(o + bytes); return base + r; };
+  char* p;
+  p = take(sizeof(float4) * kMaxAtoms);                 if (s) s->pos = (float4*)p;
+  p = take(sizeof(float2) * (size_t)ntypes * kAbStride); if (s) s->ab = (float2*)p;
+  p = take(sizeof(int) * kMaxAtoms);                    if (s) s->ab_row_off = (int*)p;
+  p = take(kMaxChunks * kMaxAtoms);                     if (s) s->mask8 = (uint8_t*)p;
+  p = take(sizeof(float) * kWarps * 3 * kMaxAtoms);     if (s) s->fi = (float*)p;
+  p = take(sizeof(float) * 3 * kMaxAtoms);              if (s) s->fj = (float*)p;
+  p = take(sizeof(float) * 3 * (size_t)(nslots > 0 ? nslots : 1)); if (s) s->fb = (float*)p;
+  p = take(sizeof(uint16_t) * (kMaxAtoms + 2));         if (s) s->gstart = (uint16_t*)p;
+  p = take(sizeof(uint16_t) * (size_t)(gather_total > 0 ? gather_total : 1)); if (s) s->glist = (uint16_t*)p;
+  p = take(sizeof(uint32_t) * kWarps * kMaxTasks);      if (s) s->tasks = (uint32_t*)p;
+  p = take(sizeof(double) * kWarps * 10);               if (s) s->ered = (double*)p;
+  p = take(sizeof(float) * 8);                          if (s) s->smd = (float*)p;
+  return o;
+}
+
+// ---- small math helpers ---------------------------------------------------------------------
+__device__ __forceinline__ float fast_rsqrt(float x) {
+  float y;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float fast_rcp(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// rsqrt with one Newton step: relative error ~1 ulp (used where the value is raised to high powers)
+__device__ __forceinline__ float rsqrt_nr(float x) {
+  float y = fast_rsqrt(x);
+  float t = x * y;
+  float u = fmaf(-0.5f * t, y, 1.5f);
+  return y * u;
+}
+struct f3 { float x, y, z; };
+__device__ __forceinline__ f3 sub3(float4 a, float4 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ f3 cross3(f3 a, f3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+__device__ __forceinline__ float dot3(f3 a, f3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
+
+// ---- Philox4x32-10 + Box-Muller (same stream as oracle_normal3) ---------------------------------
+__device__ __forceinline__ void philox4x32_10(unsigned long long seed, uint32_t c0, uint32_t c1, uint32_t c2,
+                                              uint32_t c3, uint32_t out[4]) {
+  uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+__device__ __forceinline__ void normal3(unsigned long long seed, unsigned long long replica, uint32_t atom,
+                                        unsigned long long step, float n[3]) {
+  uint32_t u[4];
+  philox4x32_10(seed, atom, (uint32_t)replica, (uint32_t)step, (uint32_t)(step >> 32), u);
+  const float s = 1.0f / 16777216.0f;
+  float u0 = ((float)(u[0] >> 8) + 0.5f) * s, u1 = ((float)(u[1] >> 8) + 0.5f) * s;
+  float u2 = ((float)(u[2] >> 8) + 0.5f) * s, u3 = ((float)(u[3] >> 8) + 0.5f) * s;
+  float r0 = sqrtf(-2.0f * logf(u0)), r1 = sqrtf(-2.0f * logf(u2));
+  float s1, c1, c3, s3;
+  sincospif(2.0f * u1, &s1, &c1);
+  sincospif(2.0f * u3, &s3, &c3);
+  n[0] = r0 * c1; n[1] = r0 * s1; n[2] = r1 * c3;
+}
+
+}  // namespace b200md

@@ -1,0 +1,262 @@
+"""Drop-in ``Forces`` for the reference's TorchMD_Fix/forces.py, backed by the sm_100a kernels.
+
+Same constructor, attributes and ``compute`` contract as the reference class (forces.py:28-73,
+:82-344; behaviours Q1-Q15 of SURVEY.md 7.4).  The arithmetic runs in ``libb200md.so`` through the
+PyTorch custom ops ``b200md::forces_compute`` / ``b200md::integrate``; there is no CPU fallback: CPU
+tensors, a missing library or an unsupported option raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _cabi
+
+__all__ = ["Forces", "SMDBias"]
+
+
+# ----------------------------------------------------------------------------------------------
+# custom ops: thin shims over the C-ABI (pointers + sizes only)
+# ----------------------------------------------------------------------------------------------
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream_ptr(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _check(rc):
+    if rc != _cabi.OK:
+        msg = _cabi.last_error()
+        if rc == _cabi.ERR_NAN_COORDINATES:
+            raise RuntimeError("Found NaN coordinates.")
+        if rc == _cabi.ERR_UNSUPPORTED:
+            raise NotImplementedError(msg)
+        if rc in (_cabi.ERR_INVALID_ARGUMENT, _cabi.ERR_TOO_MANY_ATOMS):
+            raise ValueError(msg)
+        raise RuntimeError(f"b200md error {rc}: {msg}")
+
+
+@torch.library.custom_op("b200md::forces_compute", mutates_args=("forces", "energies", "status"))
+def _forces_compute_op(pos: torch.Tensor, box: torch.Tensor, forces: torch.Tensor, energies: torch.Tensor,
+                       status: torch.Tensor, handle: int, terms: int, cutoff: float, rfa: bool, eps: float,
+                       switch_dist: float, smd_on: bool, smd_a1: int, smd_a2: int, smd_fk: float, smd_c0: float,
+                       smd_centers: torch.Tensor) -> None:
+    lib = _cabi.load_library()
+    fo = _cabi.ForceOpts(terms, cutoff, int(rfa), eps, switch_dist)
+    cen = smd_centers.data_ptr() if smd_centers.numel() else None
+    so = _cabi.SmdOpts(int(smd_on), smd_a1, smd_a2, smd_fk, smd_c0, 0.0, cen)
+    _check(lib.b200md_forces_compute(C.c_void_p(handle), C.byref(fo), C.byref(so), pos.shape[0], _ptr(pos),
+                                     _ptr(box), _ptr(forces), _ptr(energies), _ptr(status), _stream_ptr(pos.device)))
+
+
+@torch.library.custom_op("b200md::integrate", mutates_args=("pos", "vel", "forces", "observables", "snapshots", "status"))
+def _integrate_op(pos: torch.Tensor, vel: torch.Tensor, forces: torch.Tensor, box: torch.Tensor,
+                  observables: torch.Tensor, snapshots: torch.Tensor, status: torch.Tensor, handle: int, terms: int,
+                  cutoff: float, rfa: bool, eps: float, switch_dist: float, smd_on: bool, smd_a1: int, smd_a2: int,
+                  smd_fk: float, smd_c0: float, smd_rate: float, dt: float, gamma: float, temperature: float,
+                  seed: int, step0: int, replica0: int, nsteps: int, energy_every: int, snapshot_every: int) -> None:
+    lib = _cabi.load_library()
+    fo = _cabi.ForceOpts(terms, cutoff, int(rfa), eps, switch_dist)
+    so = _cabi.SmdOpts(int(smd_on), smd_a1, smd_a2, smd_fk, smd_c0, smd_rate, None)
+    io = _cabi.IntegrateOpts(dt, gamma, temperature, seed, step0, replica0, nsteps, energy_every, snapshot_every)
+    snaps = _ptr(snapshots) if snapshots.numel() else None
+    _check(lib.b200md_integrate(C.c_void_p(handle), C.byref(fo), C.byref(so), C.byref(io), pos.shape[0], _ptr(pos),
+                                _ptr(vel), _ptr(forces), _ptr(box), _ptr(observables), snaps, _ptr(status),
+                                _stream_ptr(pos.device)))
+
+
+class SMDBias:
+    """Steered-MD end-to-end harmonic restraint, the bias the reference's ``Energy`` adapter adds on
+    the caller side (V_Calculations/Test-6_full_system/potcalc.py:75-89; cGAN/.../cgan.py:209-217):
+
+        c(t) = cent_0 + (cent_1 - cent_0) * t / T ;  E = 0.5 * fk * (c - |r[group2[0]] - r[group1[0]]|)^2
+
+    Pass it as ``Forces(..., external=SMDBias(...))``: the kernels evaluate it fused (energy slot
+    "external", force = -dE/dr).  ``center`` may be a float or a per-replica tensor; in the integrator the
+    centre moves by ``rate_per_step`` each step.
+    """
+
+    def __init__(self, group1, group2, fk=1.0, cent_0=12.0, cent_1=34.0, T=1.0, rate_per_step=0.0):
+        self.atom1 = int(group1[0] if hasattr(group1, "__len__") else group1)
+        self.atom2 = int(group2[0] if hasattr(group2, "__len__") else group2)
+        self.fk, self.cent_0, self.cent_1, self.T = float(fk), float(cent_0), float(cent_1), float(T)
+        self.rate_per_step = float(rate_per_step)
+        self.center = self.cent_0
+
+    @classmethod
+    def from_colvar(cls, colvar):
+        """From the reference's ``colvar`` dict (potcalc.py:99-107)."""
+        return cls(colvar["group1"], colvar["group2"], colvar["fk"], colvar["cent_0"], colvar["cent_1"], colvar["T"])
+
+    def set_time(self, t):
+        """Frame-index form of Q19: centre = cent_0 + (cent_1 - cent_0) * t / T (t: float or (R,) tensor)."""
+        self.center = self.cent_0 + (self.cent_1 - self.cent_0) * t / self.T
+        return self
+
+
+class Forces:
+    """Same interface as the reference class; see module docstring."""
+
+    bonded = ["bonds", "angles", "dihedrals", "impropers", "1-4"]
+    nonbonded = ["electrostatics", "lj", "repulsion", "repulsioncg"]
+    terms = bonded + nonbonded
+
+    def __init__(self, parameters, terms=None, external=None, cutoff=None, rfa=False, solventDielectric=78.5,
+                 switch_dist=None, exclusions=("bonds", "angles", "1-4")):
+        self.par = parameters
+        if terms is None:
+            terms = ("electrostatics", "lj", "bonds", "angles", "dihedrals", "1-4", "impropers")
+        self.energies = [ene.lower() for ene in terms]
+        for et in self.energies:
+            if et not in Forces.terms:
+                raise ValueError(f"Force term {et} is not implemented.")
+        if "1-4" in self.energies and "dihedrals" not in self.energies:
+            raise RuntimeError("You cannot enable 1-4 interactions without enabling dihedrals")
+        for et in ("repulsion", "repulsioncg"):
+            if et in self.energies:
+                raise NotImplementedError(f"term {et!r} (forces.py:416-448) has no CUDA path in this build")
+        self.natoms = len(parameters.masses)
+        self.require_distances = any(f in self.nonbonded for f in self.energies)
+        self._pair_idx = (_cabi.make_pair_index(self.natoms, parameters.get_exclusions(exclusions))
+                          if self.require_distances else None)
+        self.ava_idx = (torch.tensor(self._pair_idx).to(parameters.device) if self.require_distances else None)
+        self.external = external
+        self.cutoff = cutoff
+        self.rfa = rfa
+        self.solventDielectric = solventDielectric
+        self.switch_dist = switch_dist
+        self.check_nan = True  # forces.py:91-92 costs one device->host flag read per call
+        if rfa and cutoff is None:
+            raise ValueError("rfa=True needs a cutoff (forces.py:467 divides by cutoff**3)")
+        self._terms_mask = 0
+        for et in self.energies:
+            self._terms_mask |= _cabi.TERM_BITS[et]
+        self._packed = _cabi.PackedTopology(parameters, self._pair_idx)
+        self._handles = {}  # device index -> native handle
+        self.last_energies = None  # (R, 8) float64 tensor of the last compute, FP64-accumulated
+
+    # -- native handle management ----------------------------------------------------------------
+    def _handle(self, device):
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        if idx not in self._handles:
+            lib = _cabi.load_library()
+            h = lib.b200md_topology_create(C.byref(self._packed.desc), idx)
+            if not h:
+                msg = _cabi.last_error()
+                if "natoms" in msg:
+                    raise ValueError(msg)
+                raise RuntimeError(f"b200md_topology_create failed: {msg}")
+            self._handles[idx] = h
+        return self._handles[idx]
+
+    def __del__(self):
+        try:
+            lib = _cabi.load_library()
+            for h in self._handles.values():
+                lib.b200md_topology_destroy(C.c_void_p(h))
+        except Exception:
+            pass
+
+    def exclusion_mask(self, device="cuda"):
+        """(natoms, 4) uint32 bitmask the kernels use (bit j of row i set <=> pair not evaluated)."""
+        h = self._handle(torch.device(device))
+        out = np.zeros((self.natoms, 4), dtype=np.uint32)
+        _check(_cabi.load_library().b200md_topology_exclusion_mask(C.c_void_p(h), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def _opts(self):
+        return (self._terms_mask, float(self.cutoff) if self.cutoff is not None else 0.0, bool(self.rfa),
+                float(self.solventDielectric), float(self.switch_dist) if self.switch_dist is not None else 0.0)
+
+    def _smd_args(self, R, device):
+        ext = self.external
+        empty = torch.empty(0, dtype=torch.float32, device=device)
+        if not isinstance(ext, SMDBias):
+            return (False, 0, 0, 0.0, 0.0), empty
+        c = ext.center
+        if isinstance(c, torch.Tensor) and c.numel() > 1:
+            cen = c.to(device=device, dtype=torch.float32).contiguous()
+            if cen.numel() != R:
+                raise ValueError("per-replica SMD centres must have one entry per replica")
+            return (True, ext.atom1, ext.atom2, ext.fk, 0.0), cen
+        return (True, ext.atom1, ext.atom2, ext.fk, float(c)), empty
+
+    @staticmethod
+    def _require_cuda(t, what):
+        if not t.is_cuda:
+            raise RuntimeError(f"{what} must be a CUDA tensor: the B200 path has no CPU fallback")
+
+    # -- low-level launch ------------------------------------------------------------------------
+    def _launch(self, pos, box, forces, terms_mask=None, with_smd=True):
+        """One b200md::forces_compute launch; ``forces`` must be a contiguous float32 CUDA tensor."""
+        R = pos.shape[0]
+        dev = pos.device
+        ene = torch.empty((R, _cabi.NUM_ENERGIES), dtype=torch.float64, device=dev)
+        status = torch.empty(R, dtype=torch.int32, device=dev)
+        opts = list(self._opts())
+        if terms_mask is not None:
+            opts[0] = terms_mask
+        (smd_on, a1, a2, fk, c0), cen = self._smd_args(R, dev)
+        if not with_smd:
+            smd_on, cen = False, torch.empty(0, dtype=torch.float32, device=dev)
+        torch.ops.b200md.forces_compute(pos, box, forces, ene, status, self._handle(dev), *opts, smd_on, a1, a2, fk,
+                                        c0, cen)
+        return ene, status
+
+    # -- batched fast path -----------------------------------------------------------------------
+    def compute_batch(self, pos, box, forces):
+        """Evaluate all replicas; fills ``forces`` in place and returns the (R, 8) float64 energy tensor
+        (columns in ``_cabi.ENERGY_SLOTS`` order).  No Python work per replica."""
+        self._require_cuda(pos, "pos")
+        self._require_cuda(forces, "forces")
+        if pos.dtype != torch.float32:
+            raise TypeError("the CUDA path computes in float32: pass precision=torch.float tensors")
+        R, N, _ = pos.shape
+        if N != self.natoms:
+            raise ValueError(f"pos has {N} atoms, parameters have {self.natoms}")
+        dev = pos.device
+        p = pos.detach().contiguous()  # System.set_positions hands over a permuted view (Q17)
+        direct = forces.is_contiguous() and forces.dtype == torch.float32 and forces.device == dev
+        f = forces if direct else torch.empty((R, N, 3), dtype=torch.float32, device=dev)
+        b = box.detach().to(device=dev, dtype=torch.float32).contiguous()
+        ene, status = self._launch(p, b, f)
+        if self.check_nan:
+            flags = int(status.max().item()) if R else 0
+            if flags & _cabi.FLAG_NAN_POS:
+                raise RuntimeError("Found NaN coordinates.")
+            if flags & 2:
+                raise NotImplementedError("non-zero box: periodic wrapping (forces.py:358-363) has no CUDA path yet")
+        if not direct:
+            forces.copy_(f)
+        if self.external is not None and not isinstance(self.external, SMDBias):  # forces.py:318-323
+            ext_ene, ext_force = self.external.calculate(pos.detach(), box)
+            ene[:, 7] += ext_ene.detach().to(ene.dtype).reshape(-1)
+            forces += ext_force.detach()
+        self.last_energies = ene
+        return ene
+
+    # -- reference-shaped entry point --------------------------------------------------------------
+    def compute(self, pos, box, forces, returnDetails=False, explicit_forces=True):
+        """Forces.compute of the reference (forces.py:82-344): zeroes and fills ``forces`` in place and
+        returns per-replica energies (list of dicts of 1-element tensors when ``returnDetails``)."""
+        if pos.requires_grad or not explicit_forces:
+            from .autograd import energies_with_grad
+
+            ene = energies_with_grad(self, pos, box, forces)  # (R, 8), differentiable w.r.t. pos
+        else:
+            ene = self.compute_batch(pos, box, forces).to(pos.dtype)
+        keys = list(self.energies) + ["external"]
+        cols = [_cabi.ENERGY_SLOTS.index(k) for k in keys]
+        if not explicit_forces:  # Q13: return the summed tensor
+            return ene[:, cols].sum().reshape(1)
+        pot = []
+        for i in range(ene.shape[0]):
+            row = ene[i]
+            pot.append({k: row[c:c + 1] for k, c in zip(keys, cols)})
+        if returnDetails:
+            return pot
+        return [sum(pp.values()) for pp in pot]

@@ -1,0 +1,113 @@
+"""Drop-in for upstream ``torchmd.integrator`` (not vendored by the reference; used at
+V_Calculations/Test-1/tutorial.ipynb:212,313,374): ``Integrator(systems, forces, timestep, device,
+gamma, T).step(niter) -> (Ekin, pot, T)`` and ``maxwell_boltzmann(masses, T, replicas)``.
+
+``step(niter)`` is ONE kernel launch: velocity Verlet (+ Langevin kick) fused with the force evaluation,
+the replica's positions / velocities / forces staying on chip for all ``niter`` steps
+(b200md_integrate, include/b200md.h).  Semantics restated from upstream:
+
+    for _ in range(niter):
+        pos += vel*dt + 0.5*(F/m)*dt^2 ; vel += 0.5*dt*F/m          # _first_VV
+        pot = forces.compute(pos, box, forces)
+        if T: vel += -gamma*vel*dt + sqrt(2*gamma/m*kB*T*dt) * N(0,1)  # langevin
+        vel += 0.5*dt*F/m                                            # _second_VV
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _cabi
+from .forces import SMDBias
+
+TIMEFACTOR = 48.88821  # fs per internal time unit
+BOLTZMAN = 0.001987191  # kcal/mol/K
+PICOSEC2TIMEU = 1000.0 / TIMEFACTOR
+
+
+def kinetic_energy(masses, vel):
+    return torch.sum(0.5 * torch.sum(vel * vel, dim=2, keepdim=True) * masses, dim=1)
+
+
+def kinetic_to_temp(Ekin, natoms):
+    return 2.0 / (3.0 * natoms * BOLTZMAN) * Ekin
+
+
+def maxwell_boltzmann(masses, T, replicas=1, generator=None):
+    """vel = sqrt(T*kB/m) * N(0,1), shape (replicas, natoms, 3), dtype/device of ``masses``."""
+    natoms = len(masses)
+    noise = torch.randn((replicas, natoms, 3), generator=generator,
+                        device=masses.device if generator is None else generator.device).to(masses)
+    return torch.sqrt(T * BOLTZMAN / masses).unsqueeze(0) * noise
+
+
+class Integrator:
+    def __init__(self, systems, forces, timestep, device=None, gamma=None, T=None, seed=0):
+        self.dt = timestep / TIMEFACTOR
+        self.systems = systems
+        self.forces = forces
+        self.device = device
+        self.gamma = (gamma if gamma is not None else 0.0) / PICOSEC2TIMEU
+        self.T = T
+        if T:
+            M = self.forces.par.masses
+            self.vcoeff = torch.sqrt(2.0 * self.gamma / M * BOLTZMAN * T * self.dt).to(device)
+        # counter-based RNG state: (seed, global step, global replica) -> reproducible under any sharding
+        self.seed = int(seed)
+        self.step_count = 0
+        self.replica0 = 0
+        self.energy_every = 0  # 0: record observables after the last step of each step() call only
+        self.snapshot_every = 0
+        self.observables = None  # (nreports, R, 10) float64 after step(): 8 energy slots, Ekin, |r_a2 - r_a1|
+        self.snapshots = None  # (nsnap, R, natoms, 3) float32 when snapshot_every > 0
+        self.check_nan = True
+
+    def step(self, niter=1):
+        s, f = self.systems, self.forces
+        for name in ("pos", "vel", "forces"):
+            t = getattr(s, name)
+            if not t.is_cuda:
+                raise RuntimeError(f"System.{name} must be a CUDA tensor: the B200 path has no CPU fallback")
+            if t.dtype != torch.float32:
+                raise TypeError("the CUDA path integrates in float32")
+            if not t.is_contiguous():  # set_positions rebinding (Q17) may have left a permuted view
+                setattr(s, name, t.detach().contiguous())
+        pos, vel, frc = s.pos, s.vel, s.forces
+        R, N, _ = pos.shape
+        dev = pos.device
+        box = s.box.to(device=dev, dtype=torch.float32).contiguous()
+        nrep = niter // self.energy_every if self.energy_every > 0 else 1
+        nsnap = niter // self.snapshot_every if self.snapshot_every > 0 else 0
+        obs = torch.zeros((nrep, R, _cabi.NUM_OBSERVABLES), dtype=torch.float64, device=dev)
+        snaps = torch.empty((nsnap, R, N, 3), dtype=torch.float32, device=dev)
+        status = torch.empty(R, dtype=torch.int32, device=dev)
+        ext = f.external
+        if ext is not None and not isinstance(ext, SMDBias):
+            raise NotImplementedError("the fused integrator supports only the SMDBias external term")
+        if isinstance(ext, SMDBias):  # centre of the restraint after global step g: center + rate * g
+            c = ext.center
+            if isinstance(c, torch.Tensor):
+                c = float(c.reshape(-1)[0])
+            smd = (True, ext.atom1, ext.atom2, ext.fk, float(c), ext.rate_per_step)
+        else:
+            smd = (False, 0, 0, 0.0, 0.0, 0.0)
+        smd_c0 = smd[4]
+        torch.ops.b200md.integrate(pos, vel, frc, box, obs, snaps, status, f._handle(dev), *f._opts(), smd[0], smd[1],
+                                   smd[2], smd[3], smd_c0, smd[5], float(self.dt), float(self.gamma),
+                                   float(self.T) if self.T else 0.0, self.seed, self.step_count, self.replica0,
+                                   int(niter), int(self.energy_every), int(self.snapshot_every))
+        self.step_count += int(niter)
+        if self.check_nan:
+            flags = int(status.max().item()) if R else 0
+            if flags & _cabi.FLAG_NAN_POS:
+                raise RuntimeError("Found NaN coordinates.")
+            if flags & 2:
+                raise NotImplementedError("non-zero box: periodic wrapping has no CUDA path yet")
+        self.observables, self.snapshots = obs, snaps
+        last = obs[-1]
+        Ekin = last[:, _cabi.OBS_EKIN].cpu().numpy()
+        T = kinetic_to_temp(Ekin, N)
+        keys = list(f.energies) + ["external"]
+        cols = [_cabi.ENERGY_SLOTS.index(k) for k in keys]
+        pot = last[:, cols].sum(dim=1).to(pos.dtype)
+        return Ekin, [pot[i] for i in range(R)], T

@@ -1,0 +1,305 @@
+"""Parity of the CUDA path (through the drop-in classes -> custom op -> C-ABI) against the oracle and the
+golden fixtures produced by the reference's own forces.py.
+
+Tolerances (BASELINE.json north_star, calibrated in SURVEY.md 8c):
+  * integer artefacts (pair list, exclusion mask)             bit-exact
+  * forces   max|dF| / max|F| per replica                     <= 1e-5
+  * energies per term vs fp64 reference                       <= 1e-6 relative, except plain-Coulomb sums
+    that cancel ~1000:1 (sum|terms| >> |total|): there the bound is 1e-6 of sum|pair terms|, the accuracy
+    fp32 pair arithmetic can deliver (the reference's own fp32 run is at 3.5e-6 of the total).
+"""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from conftest import MODES, SYSTEMS, load_golden
+from molecular_dynamics_b200 import Forces, Integrator, SMDBias, System, _cabi
+from molecular_dynamics_b200.parameters import Parameters
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+TIMEFACTOR = 48.88821
+F_TOL = 1e-5
+E_TOL = 1e-6
+
+
+def gpu_par(g):
+    return Parameters.from_arrays(g.par.to_arrays(), device=DEV)
+
+
+def run_gpu(g, pos, smd=None, centers=None, **kw):
+    par = gpu_par(g)
+    ext = None
+    if smd is not None:
+        ext = SMDBias([smd["atom1"]], [smd["atom2"]], fk=smd["fk"], cent_0=smd["center0"])
+        if centers is not None:
+            ext.center = torch.tensor(centers, device=DEV)
+    F = Forces(par, external=ext, **kw)
+    p = torch.tensor(np.asarray(pos, dtype=np.float32), device=DEV)
+    R, N, _ = p.shape
+    s = System(N, R, torch.float, DEV)
+    ene = F.compute_batch(p, s.box, s.forces)
+    torch.cuda.synchronize()
+    return s.forces.cpu().numpy().astype(np.float64), ene.cpu().numpy(), F
+
+
+def coulomb_scale(g, pos):
+    """sum over evaluated pairs of |K qi qj / r| per replica: the magnitude the fp32 pair terms carry."""
+    q = g.par.charges.numpy().astype(np.float64)
+    idx = np.concatenate([g.ava_idx, g.par.idx14.numpy()]) if g.par.idx14 is not None else g.ava_idx
+    d = np.linalg.norm(pos[:, idx[:, 0]].astype(np.float64) - pos[:, idx[:, 1]], axis=-1)
+    return (332.06371307417066 * np.abs(q[idx[:, 0]] * q[idx[:, 1]]) / d).sum(1)
+
+
+def check(g, pos, f, e, f_ref, e_ref, mode):
+    ferr = np.abs(f - f_ref).reshape(len(f), -1).max(1) / np.abs(f_ref).reshape(len(f), -1).max(1)
+    assert ferr.max() <= F_TOL, f"force error {ferr.max():.3e}"
+    for k, name in enumerate(_cabi.ENERGY_SLOTS):
+        err = np.abs(e[:, k] - e_ref[:, k])
+        scale = np.abs(e_ref[:, k])
+        if name == "electrostatics":
+            scale = np.maximum(scale, coulomb_scale(g, pos))
+        assert (err <= E_TOL * scale + 1e-9).all(), f"{name}: {(err / (scale + 1e-30)).max():.3e} ({mode})"
+    return ferr.max()
+
+
+@pytest.mark.parametrize("system", SYSTEMS)
+@pytest.mark.parametrize("mode", list(MODES))
+def test_forces_and_energies_vs_reference_fp64(system, mode):
+    g = load_golden(system)
+    f, e, F = run_gpu(g, g["pos"], **MODES[mode])
+    check(g, g["pos"], f, e, g[f"ref_{mode}_f64_forces"], g[f"ref_{mode}_f64_energies"], mode)
+    # integer artefacts: Forces.ava_idx equals the reference's (forces.py:346-355)
+    np.testing.assert_array_equal(F.ava_idx.cpu().numpy(), g.ava_idx)
+
+
+def test_known_answer_vector_on_gpu():
+    g = load_golden("bb40")
+    f, e, _ = run_gpu(g, g["pos"], **MODES["rf"])
+    np.testing.assert_allclose(e[0], g["kat_energies"], rtol=3e-6, atol=1e-9)
+    np.testing.assert_allclose(f[0], g["kat_forces"], rtol=2e-4, atol=2e-3)
+
+
+def test_exclusion_mask_bit_exact():
+    for system in SYSTEMS:
+        g = load_golden(system)
+        F = Forces(gpu_par(g))
+        mask = F.exclusion_mask(DEV)
+        N = g.par.natoms
+        allowed = np.zeros((N, 128), dtype=bool)
+        allowed[g.ava_idx[:, 0], g.ava_idx[:, 1]] = True
+        allowed[g.ava_idx[:, 1], g.ava_idx[:, 0]] = True
+        bits = ((mask[:, :, None] >> np.arange(32, dtype=np.uint32)) & 1).reshape(N, 128).astype(bool)
+        np.testing.assert_array_equal(bits, ~allowed)
+
+
+def test_batched_frames_bb40_both_modes():
+    g = load_golden("bb40")
+    for mode in MODES:
+        f, e, _ = run_gpu(g, g["frames"], **MODES[mode])
+        check(g, g["frames"], f, e, g[f"frames_ref_{mode}_f64_forces"], g[f"frames_ref_{mode}_f64_energies"], mode)
+
+
+def test_large_batch_vs_oracle_ala10():
+    """4 096 perturbed ALA10 conformers (bench recipe: base frame r mod 101 + 0.05 A noise)."""
+    g = load_golden("ala10")
+    rng = np.random.default_rng(1234)
+    base = g["base_frames"]
+    R = 4096
+    pos = (base[np.arange(R) % len(base)] + 0.05 * rng.standard_normal((R, 104, 3))).astype(np.float32)
+    for mode in MODES:
+        f, e, _ = run_gpu(g, pos, **MODES[mode])
+        f_ref, e_ref = oracle.forces(g.packed, pos, **MODES[mode])
+        check(g, pos, f, e, f_ref, e_ref, mode)
+
+
+def test_smd_bias_fused():
+    g = load_golden("ala10")
+    a1, a2, fk, c = g["smd"]
+    smd = dict(atom1=int(a1), atom2=int(a2), fk=float(fk), center0=float(c))
+    f, e, _ = run_gpu(g, g["pos"], smd=smd)
+    check(g, g["pos"], f, e, g["ref_smd_plain_f64_forces"], g["ref_smd_plain_f64_energies"], "plain+smd")
+    cen = np.linspace(12, 34, len(g["pos"])).astype(np.float32)
+    f, e, _ = run_gpu(g, g["pos"], smd=smd, centers=cen)
+    f_ref, e_ref = oracle.forces(g.packed, g["pos"], smd=smd, smd_centers=cen)
+    check(g, g["pos"], f, e, f_ref, e_ref, "plain+smd centres")
+
+
+def test_term_subsets():
+    g = load_golden("ala10_ff14sb")
+    for terms in (("bonds",), ("angles", "bonds"), ("dihedrals", "1-4", "lj"), ("electrostatics",),
+                  ("lj", "impropers"), ("dihedrals", "1-4", "electrostatics", "lj")):
+        f, e, _ = run_gpu(g, g["pos"], terms=terms)
+        f_ref, e_ref = oracle.forces(g.packed, g["pos"], terms=terms)
+        check(g, g["pos"], f, e, f_ref, e_ref, str(terms))
+
+
+def test_reference_shaped_compute_api():
+    g = load_golden("bb40")
+    par = gpu_par(g)
+    s = System(40, 1, torch.float, DEV)
+    s.set_positions(torch.tensor(g["pos"][0].reshape(40, 3, 1), device=DEV))  # permuted view (Q17)
+    F = Forces(par, cutoff=9, rfa=True, switch_dist=7.5)
+    pot = F.compute(s.pos, s.box, s.forces, returnDetails=True)
+    assert list(pot[0].keys()) == ["electrostatics", "lj", "bonds", "angles", "dihedrals", "1-4", "impropers", "external"]
+    assert pot[0]["1-4"].item() == 0.0 and pot[0]["bonds"].shape == (1,)
+    np.testing.assert_allclose([v.item() for v in pot[0].values()], g["kat_energies"], rtol=3e-6, atol=1e-9)
+    tot = F.compute(s.pos, s.box, s.forces)
+    assert abs(float(tot[0]) - g["kat_energies"].sum()) < 1e-3
+
+
+def test_errors_match_reference():
+    g = load_golden("diala")
+    par = gpu_par(g)
+    with pytest.raises(ValueError, match="not implemented"):
+        Forces(par, terms=("bonds", "magic"))
+    with pytest.raises(RuntimeError, match="1-4"):
+        Forces(par, terms=("1-4", "lj"))
+    F = Forces(par)
+    pos = torch.tensor(g["pos"], device=DEV)
+    pos[2, 5, 1] = float("nan")
+    s = System(22, len(pos), torch.float, DEV)
+    with pytest.raises(RuntimeError, match="Found NaN coordinates."):
+        F.compute(pos, s.box, s.forces)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        F.compute_batch(pos.cpu(), s.box.cpu(), s.forces.cpu())
+
+
+def test_determinism_bitwise():
+    g = load_golden("ala10")
+    pos = np.repeat(g["pos"], 64, axis=0)
+    f1, e1, _ = run_gpu(g, pos)
+    f2, e2, _ = run_gpu(g, pos)
+    np.testing.assert_array_equal(f1, f2)
+    np.testing.assert_array_equal(e1, e2)
+    # identical replicas give identical results wherever they sit in the batch
+    np.testing.assert_array_equal(f1[:8], f1[8:16])
+
+
+def test_autograd_matches_forces():
+    g = load_golden("ala10")
+    par = gpu_par(g)
+    F = Forces(par)
+    pos = torch.tensor(g["pos"][:2], device=DEV, requires_grad=True)
+    s = System(104, 2, torch.float, DEV)
+    pot = F.compute(pos, s.box, s.forces, returnDetails=True)
+    loss = sum(sum(p.values()) for p in pot).sum()
+    loss.backward()
+    np.testing.assert_allclose(pos.grad.cpu().numpy(), -s.forces.cpu().numpy(), rtol=1e-6, atol=1e-5)
+    # non-uniform term weights -> per-term force launches
+    pos2 = torch.tensor(g["pos"][:2], device=DEV, requires_grad=True)
+    pot = F.compute(pos2, s.box, s.forces, returnDetails=True)
+    loss = sum(2.0 * p["bonds"] + 0.5 * p["lj"] + p["electrostatics"] for p in pot).sum()
+    loss.backward()
+    fb, _ = oracle.forces(g.packed, g["pos"][:2], terms=("bonds",))
+    fl, _ = oracle.forces(g.packed, g["pos"][:2], terms=("lj", "dihedrals", "1-4"))
+    fd, _ = oracle.forces(g.packed, g["pos"][:2], terms=("dihedrals",))
+    fe, _ = oracle.forces(g.packed, g["pos"][:2], terms=("electrostatics", "dihedrals", "1-4"))
+    want = -(2.0 * fb + 0.5 * (fl - fd) + (fe - fd))
+    got = pos2.grad.cpu().numpy()
+    assert np.abs(got - want).max() <= 2e-5 * np.abs(want).max()
+
+
+# ---------------------------------------------------------------------------------------------------
+# fused integrator
+# ---------------------------------------------------------------------------------------------------
+def make_system(g, pos, vel):
+    par = gpu_par(g)
+    R, N, _ = pos.shape
+    s = System(N, R, torch.float, DEV)
+    s.pos[:] = torch.tensor(pos, device=DEV)
+    s.vel[:] = torch.tensor(vel, device=DEV)
+    return par, s
+
+
+@pytest.mark.parametrize("system", ["bb40", "ala10"])
+def test_nve_short_horizon_vs_oracle_and_upstream_loop(system):
+    g = load_golden(system)
+    n = len(g["vv_vel0"])
+    pos0 = (g["frames"] if system == "bb40" else g["pos"])[:n]
+    par, s = make_system(g, pos0, g["vv_vel0"])
+    F = Forces(par)
+    F.compute_batch(s.pos, s.box, s.forces)
+    integ = Integrator(s, F, timestep=float(g["vv_dt_fs"]), device=DEV)
+    integ.energy_every = 1
+    nsteps = int(g["vv_nsteps"])
+    ekin, pot, T = integ.step(niter=nsteps)
+    # vs the restated upstream loop driving the reference forces.py in fp64 (golden)
+    assert np.abs(s.pos.cpu().numpy() - g["vv_pos"]).max() < 2e-4
+    assert np.abs(s.vel.cpu().numpy() - g["vv_vel"]).max() < 2e-4 * np.abs(g["vv_vel"]).max() * 50
+    obs = integ.observables.cpu().numpy()
+    epot = obs[:, :, :8].sum(-1)
+    np.testing.assert_allclose(epot, g["vv_epot"], rtol=2e-5, atol=2e-3)
+    np.testing.assert_allclose(obs[:, :, _cabi.OBS_EKIN], g["vv_ekin"], rtol=2e-4)
+    np.testing.assert_allclose(ekin, g["vv_ekin"][-1], rtol=2e-4)
+    assert abs(float(pot[0]) - g["vv_epot"][-1, 0]) < 5e-3
+
+
+def test_langevin_smd_short_horizon_vs_oracle():
+    g = load_golden("ala10")
+    pos0 = g["pos"][:4]
+    vel0 = (0.1 * np.random.default_rng(5).standard_normal(pos0.shape)).astype(np.float32)
+    par, s = make_system(g, pos0, vel0)
+    rate = 22.0 / 5000
+    ext = SMDBias([3], [98], fk=1.0, cent_0=14.0, rate_per_step=rate)
+    F = Forces(par, external=ext)
+    F.compute_batch(s.pos, s.box, s.forces)
+    f0 = s.forces.cpu().numpy().astype(np.float64)
+    integ = Integrator(s, F, timestep=1.0, device=DEV, gamma=1.0, T=300.0, seed=42)
+    integ.energy_every = 5
+    integ.replica0 = 1000
+    integ.step(niter=30)
+    out = oracle.integrate(g.packed, pos0, vel0, f0, nsteps=30, dt=np.float32(integ.dt), gamma=np.float32(integ.gamma),
+                           temperature=300.0, seed=42, replica0=1000, energy_every=5,
+                           smd=dict(atom1=3, atom2=98, fk=1.0, center0=14.0, center_rate=np.float32(rate)))
+    assert np.abs(s.pos.cpu().numpy() - out["pos"]).max() < 3e-4
+    obs = integ.observables.cpu().numpy()
+    np.testing.assert_allclose(obs[:, :, _cabi.OBS_E2E_DIST], out["observables"][:, :, _cabi.OBS_E2E_DIST], rtol=1e-5)
+    np.testing.assert_allclose(obs[:, :, 7], out["observables"][:, :, 7], rtol=2e-3, atol=1e-4)
+    np.testing.assert_allclose(obs[:, :, _cabi.OBS_EKIN], out["observables"][:, :, _cabi.OBS_EKIN], rtol=1e-3)
+
+
+def test_integrator_chunking_and_sharding_are_bitwise_invariant():
+    """step(20) == step(10)+step(10); replicas [0,8) in one call == two shards with replica0 offsets."""
+    g = load_golden("ala10")
+    pos0 = g["pos"]
+    vel0 = np.zeros_like(pos0)
+
+    def run(chunks, shards):
+        outs = []
+        for lo, hi in shards:
+            par, s = make_system(g, pos0[lo:hi], vel0[lo:hi])
+            F = Forces(par)
+            F.compute_batch(s.pos, s.box, s.forces)
+            integ = Integrator(s, F, timestep=1.0, device=DEV, gamma=1.0, T=300.0, seed=7)
+            integ.replica0 = lo
+            for c in chunks:
+                integ.step(niter=c)
+            outs.append(s.pos.cpu().numpy())
+        return np.concatenate(outs)
+
+    a = run([20], [(0, 8)])
+    b = run([10, 10], [(0, 8)])
+    c = run([20], [(0, 3), (3, 8)])
+    np.testing.assert_array_equal(a, b)
+    np.testing.assert_array_equal(a, c)
+
+
+def test_snapshots_and_reports_layout():
+    g = load_golden("diala")
+    pos0 = g["pos"]
+    par, s = make_system(g, pos0, np.zeros_like(pos0))
+    F = Forces(par)
+    F.compute_batch(s.pos, s.box, s.forces)
+    integ = Integrator(s, F, timestep=0.5, device=DEV)
+    integ.energy_every, integ.snapshot_every = 4, 8
+    integ.step(niter=16)
+    assert integ.observables.shape == (4, 4, 10) and integ.snapshots.shape == (2, 4, 22, 3)
+    np.testing.assert_array_equal(integ.snapshots[-1].cpu().numpy(), s.pos.cpu().numpy())
+    f0, _ = oracle.forces(g.packed, pos0)
+    out = oracle.integrate(g.packed, pos0, np.zeros_like(pos0), f0, nsteps=16, dt=np.float32(integ.dt), energy_every=4,
+                           snapshot_every=8)
+    assert np.abs(integ.snapshots.cpu().numpy() - out["snapshots"]).max() < 1e-4
+    np.testing.assert_allclose(integ.observables.cpu().numpy()[:, :, :8].sum(-1), out["observables"][:, :, :8].sum(-1),
+                               rtol=1e-5, atol=1e-3)
