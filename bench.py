@@ -1,0 +1,387 @@
+#!/usr/bin/env python
+"""bench.py -- ALA10 replica-steps/s of the fused force + velocity-Verlet kernel (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--replicas R] [--inner S]
+
+Workload (BASELINE.json configs[2]): ALA10 (104 atoms, CHAMBER prmtop parameters from
+tests/golden/ala10.npz), NVE velocity Verlet, dt = 1 fs, plain all-pairs LJ + Coulomb, R = 8 192 replicas
+PER GPU (weak scaling; replicas never interact), synthetic perturbed conformers: base frame r mod 101 +
+0.05 A Gaussian noise (seed 1234), Maxwell-Boltzmann velocities at 300 K (seed 5678).  One bench "step"
+= one Integrator.step(niter=S) call = one kernel launch advancing every replica S MD steps (default
+S = 1000, energies recorded every 100).  value = replica-steps/s over all GPUs with state resident in HBM;
+e2e = the same through the public API with pinned HOST buffers (H2D of pos/vel/forces and D2H of
+pos/vel/observables inside the timed region).
+
+--impl reference times the reference's CPU implementation of the same path (oracle/torchmd_port.py, the
+torch-op restatement with the reference's per-replica Python loop: /root/reference is not on the GPU box)
+on all host cores, each step being a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+FLOP_PER_REPLICA_STEP = 240824  # SURVEY.md 8d, ALA10 plain NVE (force-only evaluation: 236144)
+FLOP_PER_REPLICA_EVAL = 236144
+NOMINAL_FP32_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.5
+TIMEFACTOR = 48.88821
+BOLTZMAN = 0.001987191
+
+
+def load_ala10():
+    with np.load(os.path.join(ROOT, "tests", "golden", "ala10.npz")) as z:
+        return {k: z[k] for k in z.files}
+
+
+def synth_inputs(g, R, replica0=0):
+    """Deterministic per global replica id: independent of how replicas are sharded over GPUs."""
+    base = g["base_frames"]
+    mass = g["par_masses"].reshape(-1).astype(np.float64)
+    pos = np.empty((R, 104, 3), dtype=np.float32)
+    vel = np.empty((R, 104, 3), dtype=np.float32)
+    for k in range(R):
+        r = replica0 + k
+        rng = np.random.default_rng([1234, r])
+        pos[k] = (base[r % len(base)] + 0.05 * rng.standard_normal((104, 3))).astype(np.float32)
+        rngv = np.random.default_rng([5678, r])
+        vel[k] = (np.sqrt(300.0 * BOLTZMAN / mass)[:, None] * rngv.standard_normal((104, 3))).astype(np.float32)
+    return pos, vel
+
+
+class ClockSampler:
+    """Samples SM clock + throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+                 "hw_power_brake": 0x80, "sync_boost": 0x10}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                for n, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+        return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU legs: the oracle is executed here only as the *reported baseline* (never on the product path)
+# ---------------------------------------------------------------------------------------------------
+_WORKER_CACHE = {}
+
+
+def _port_worker(args):
+    """One host core: `nrep` replicas x `nsteps` MD steps with the torch port (1 torch thread)."""
+    import torch
+
+    torch.set_num_threads(1)
+    from molecular_dynamics_b200 import _cabi
+    from molecular_dynamics_b200.parameters import Parameters
+    from oracle import torchmd_port as port
+
+    replica0, nrep, nsteps, dt = args
+    if "top" not in _WORKER_CACHE:
+        g = load_ala10()
+        par = Parameters.from_arrays({k[4:]: v for k, v in g.items() if k.startswith("par_")})
+        packed = _cabi.PackedTopology(par, g["ava_idx"])
+        _WORKER_CACHE["g"], _WORKER_CACHE["top"] = g, port.PortTopology(packed, torch.float32)
+    g, top = _WORKER_CACHE["g"], _WORKER_CACHE["top"]
+    pos, vel = synth_inputs(g, nrep, replica0)
+    pos, vel = torch.tensor(pos), torch.tensor(vel)
+    frc = torch.zeros_like(pos)
+    port.compute(top, pos, frc)
+    t0 = time.perf_counter()
+    port.integrate(top, pos, vel, frc, nsteps, dt)
+    return time.perf_counter() - t0
+
+
+def cpu_port_rate(cores, nrep_per_core, nsteps, pool=None):
+    """replica-steps/s of the torch port over `cores` worker processes (max over workers' wall time)."""
+    import multiprocessing as mp
+
+    dt = 1.0 / TIMEFACTOR
+    jobs = [(c * nrep_per_core, nrep_per_core, nsteps, dt) for c in range(cores)]
+    own = pool is None
+    if own:
+        pool = mp.get_context("spawn").Pool(cores)
+    try:
+        t0 = time.perf_counter()
+        times = pool.map(_port_worker, jobs)
+        wall = time.perf_counter() - t0
+    finally:
+        if own:
+            pool.close()
+            pool.join()
+    return cores * nrep_per_core * nsteps / max(times), max(times), wall
+
+
+def cpu_c_oracle_rate(nrep, nsteps):
+    """replica-steps/s of the FP64 C oracle (OpenMP over replicas, all host cores)."""
+    import oracle
+    from molecular_dynamics_b200 import _cabi
+    from molecular_dynamics_b200.parameters import Parameters
+
+    g = load_ala10()
+    par = Parameters.from_arrays({k[4:]: v for k, v in g.items() if k.startswith("par_")})
+    packed = _cabi.PackedTopology(par, g["ava_idx"])
+    pos, vel = synth_inputs(g, nrep)
+    f0, _ = oracle.forces(packed, pos)
+    t0 = time.perf_counter()
+    oracle.integrate(packed, pos, vel, f0, nsteps=nsteps, dt=1.0 / TIMEFACTOR)
+    return nrep * nsteps / (time.perf_counter() - t0)
+
+
+def run_reference(args):
+    """--impl reference: the CPU path on all host cores, same metric/config, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+
+    cores = os.cpu_count() or 1
+    nrep, nsteps = 2, 25  # per core and per bench step: 50 replica-steps x ~4 ms
+    pool = mp.get_context("spawn").Pool(cores)
+    try:
+        for _ in range(max(1, min(args.warmup, 1))):
+            cpu_port_rate(cores, nrep, nsteps, pool)
+        units, wall = 0, 0.0
+        for _ in range(args.steps):
+            _, slowest, _ = cpu_port_rate(cores, nrep, nsteps, pool)
+            wall += slowest  # slowest worker's compute time: the step ends when the last core finishes
+            units += cores * nrep * nsteps
+    finally:
+        pool.close()
+        pool.join()
+    value = units / wall
+    sample = f"{cores} procs x {nrep} replicas x {nsteps} MD steps per bench step (torch port of TorchMD_Fix/forces.py + upstream VV loop, fp32, 1 thread each)"
+    print(json.dumps({
+        "impl": "reference", "metric": "ALA10 replica-steps/s", "value": value, "unit": "replica-steps/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD_NAME, "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "replica-steps/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "replica-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+WORKLOAD_NAME = ("configs[2]: ALA10 NVE velocity-Verlet, 8192 replicas per GPU, fused persistent kernel, "
+                 "dt=1fs, plain all-pairs LJ+Coulomb")
+
+
+# ---------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    import __graft_entry__ as entry
+
+    if not os.path.exists(entry.LIB):
+        entry.build()
+    from molecular_dynamics_b200 import Forces, Integrator, Parameters, System, _cabi
+
+    lib = _cabi.load_library()
+    g = load_ala10()
+    par = Parameters.from_arrays({k[4:]: v for k, v in g.items() if k.startswith("par_")}, device=dev)
+    R, S = args.replicas, args.inner
+    replica0 = rank * R
+    pos_h, vel_h = synth_inputs(g, R, replica0)
+    forces = Forces(par)
+    forces.check_nan = False
+    system = System(104, R, torch.float, dev)
+    system.pos[:] = torch.tensor(pos_h, device=dev)
+    system.vel[:] = torch.tensor(vel_h, device=dev)
+    forces.compute_batch(system.pos, system.box, system.forces)
+    frc_h = system.forces.cpu().numpy()
+    integ = Integrator(system, forces, timestep=1.0, device=dev)
+    integ.energy_every = args.energy_every
+    integ.replica0 = replica0
+    integ.check_nan = False
+
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    gathered = torch.empty((world, R, _cabi.NUM_OBSERVABLES), dtype=torch.float64, device=dev) if world > 1 else None
+
+    def one_step():
+        integ.step(niter=S)
+        if world > 1:  # reporting interval: all-gather the per-replica observables (the only collective)
+            dist.all_gather_into_tensor(gathered, integ.observables[-1].contiguous())
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        one_step()
+    barrier()
+
+    # ---- device-timed region: K steps, each bracketed by CUDA events, L2 flushed in between ----------
+    launches0 = lib.b200md_launch_count()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    with ClockSampler(local) as clocks:
+        barrier()
+        for a, b in ev:
+            flush.fill_(1)
+            a.record()
+            one_step()
+            b.record()
+        barrier()
+    launches = lib.b200md_launch_count() - launches0
+    ms = sum(a.elapsed_time(b) for a, b in ev)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    units = world * R * S * args.steps
+    value = units / (ms * 1e-3)
+    nan_count = int(torch.isnan(system.pos).any(dim=2).any(dim=1).sum().item())
+
+    # ---- end-to-end through the public API with pinned host buffers ----------------------------------
+    hp = torch.tensor(pos_h).pin_memory()
+    hv = torch.tensor(vel_h).pin_memory()
+    hf = torch.tensor(frc_h).pin_memory()
+    out_p, out_v = torch.empty_like(hp).pin_memory(), torch.empty_like(hv).pin_memory()
+    out_o = torch.empty((max(1, S // args.energy_every) if args.energy_every else 1, R, _cabi.NUM_OBSERVABLES),
+                        dtype=torch.float64).pin_memory()
+    h2d = hp.numel() * 4 * 3
+    d2h = out_p.numel() * 4 * 2 + out_o.numel() * 8
+
+    def e2e_step():
+        system.pos.copy_(hp, non_blocking=True)
+        system.vel.copy_(hv, non_blocking=True)
+        system.forces.copy_(hf, non_blocking=True)
+        ekin, pot, temp = integ.step(niter=S)  # returns host Ekin/T (device->host read inside)
+        out_p.copy_(system.pos, non_blocking=True)
+        out_v.copy_(system.vel, non_blocking=True)
+        out_o.copy_(integ.observables, non_blocking=True)
+        torch.cuda.synchronize()
+        return float(ekin[0])
+
+    e2e_steps = max(2, min(args.steps, 5))
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * R * S * e2e_steps / float(t.item())
+
+    if rank == 0:
+        peak = lib.b200md_fp32_peak_tflops(local, 4096)
+        achieved = value / world * FLOP_PER_REPLICA_STEP / 1e12  # per GPU
+        line = {
+            "metric": "ALA10 replica-steps/s", "value": value, "unit": "replica-steps/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD_NAME, "replicas_per_gpu": R, "md_steps_per_launch": S,
+                       "energy_every": args.energy_every, "dt_fs": 1.0, "natoms": 104,
+                       "l2": "flushed between timed steps (256 MiB fill, outside the event pair)",
+                       "ns_per_day_aggregate": value * 1.0 * 86400 * 1e-6,
+                       "replicas_with_nan_after_run": nan_count},
+            "clocks": clocks.summary(),
+            "e2e": {"value": e2e_value, "unit": "replica-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "steps": e2e_steps},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                         "frac": achieved / peak if peak > 0 else None, "traffic": None,
+                         "peak_source": "measured live: b200md_fp32_peak_tflops (dependent-FMA kernel, all SMs)",
+                         "nominal_peak": NOMINAL_FP32_TFLOPS, "frac_of_nominal": achieved / NOMINAL_FP32_TFLOPS,
+                         "flop_per_replica_step": FLOP_PER_REPLICA_STEP, "kernel": "integrate_kernel<0>",
+                         "kernel_ms_per_launch": ms / args.steps},
+        }
+        if world == 1 and not args.no_cpu:
+            cores = os.cpu_count() or 1
+            rate, slowest, _ = cpu_port_rate(cores, 2, 25)
+            line["cpu_baseline"] = {
+                "value": rate, "unit": "replica-steps/s", "cores": cores, "kind": "port",
+                "sample": f"{cores} procs x 2 replicas x 25 MD steps, torch port (oracle/torchmd_port.py), fp32, "
+                          f"1 thread each; slowest worker {slowest:.2f} s"}
+            try:
+                line["cpu_baseline_c_oracle"] = {
+                    "value": cpu_c_oracle_rate(64 * cores, 20), "unit": "replica-steps/s", "cores": cores,
+                    "kind": "port", "sample": f"{64 * cores} replicas x 20 MD steps, oracle/md_oracle.c FP64, OpenMP"}
+            except Exception as exc:  # the C oracle is optional here
+                line["cpu_baseline_c_oracle"] = {"error": str(exc)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--replicas", type=int, default=8192, help="replicas per GPU")
+    ap.add_argument("--inner", type=int, default=1000, help="MD steps per launch (Integrator.step niter)")
+    ap.add_argument("--energy-every", type=int, default=100)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

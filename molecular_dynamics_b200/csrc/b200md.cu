@@ -39,6 +39,8 @@ __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, co
   if (tid < 8) S.smd[tid] = 0.0f;
   // slots of disabled / dropped terms are never written: keep them at zero for the gather
   for (int k = tid; k < 3 * T.nslots; k += kThreads) S.fb[k] = 0.0f;
+  // chunks without a tile task (no non-bonded term enabled) must read as zero in the gather
+  for (int k = tid; k < 3 * kMaxAtoms; k += kThreads) S.fj[k] = 0.0f;
 }
 
 // Forces.compute (forces.py:82-344) for a batch of replicas: one CTA per replica (grid-stride).
@@ -323,7 +325,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   std::vector<float2> ab((size_t)NT * kAbStride, make_float2(0.f, 0.f));
   for (int t = 0; t < NT; ++t)
     for (int j = 0; j < N; ++j)
-      ab[(size_t)t * kAbStride + j] = make_float2(d->lj_a[t * NT + d->atom_type[j]], d->lj_b[t * NT + d->atom_type[j]]);
+      ab[(size_t)t * kAbStride + j] = make_float2(12.0f * d->lj_a[t * NT + d->atom_type[j]], 6.0f * d->lj_b[t * NT + d->atom_type[j]]);
   std::vector<float> charge(kMaxAtoms, 0.f), mass(kMaxAtoms, 1.f);
   std::vector<int> rowoff(kMaxAtoms, 0);
   for (int a = 0; a < N; ++a) {

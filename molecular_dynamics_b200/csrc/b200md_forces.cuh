@@ -16,39 +16,52 @@ struct Energies {
 
 // ---- one non-bonded pair (forces.py:258-316 with evaluate_LJ :379-413, evaluate_electrostatics
 // :451-489).  MODE 0: no cutoff, plain Coulomb.  MODE 1: cutoff with optional reaction field and
-// LJ switching.  Returns s = -(dE/dr)/r so that F_i += s * d, F_j -= s * d with d = r_i - r_j. ----
+// LJ switching.  Returns s = -(dE/dr)/r so that F_i += s * d, F_j -= s * d with d = r_i - r_j.
+//
+// The force path is written with explicit round-to-nearest intrinsics so that the ENERGY and the
+// force-only instantiations produce bit-identical forces (no compiler-chosen FMA contraction): a
+// trajectory does not depend on how often energies are reported.  `ab` holds (12 A, 6 B).
+// Energies (report steps only) use one Newton step on rsqrt: the MUFU error (2^-22) would otherwise be
+// amplified 12x in r^-12 and miss the 1e-6 energy tolerance.
 template <int MODE, bool ENERGY>
 __device__ __forceinline__ float pair_eval(float dx, float dy, float dz, float kqi, float qj, float2 ab, bool excl,
                                            const ForceParams& P, float& pel, float& plj) {
-  const float r2 = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+  const float r2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
   float rinv = fast_rsqrt(r2);
   if (MODE == 1) excl = excl || !(r2 <= P.rc2);
   rinv = excl ? 0.0f : rinv;
-  const float r2inv = rinv * rinv;
-  const float r6 = r2inv * r2inv * r2inv;
-  const float u = ab.x * r6;   // A r^-6
-  const float t1 = u - ab.y;   // A r^-6 - B
-  float elj = t1 * r6;         // A r^-12 - B r^-6
-  float glj = 6.0f * ((u + t1) * r6);  // 12 A r^-12 - 6 B r^-6 = -r dE/dr
-  float ec, gc;
+  const float r2inv = __fmul_rn(rinv, rinv);
+  const float r6 = __fmul_rn(__fmul_rn(r2inv, r2inv), r2inv);
+  const float qq = (MODE == 1 && excl) ? 0.0f : __fmul_rn(kqi, qj);
+  float glj = __fmul_rn(__fmaf_rn(ab.x, r6, -ab.y), r6);  // 12 A r^-12 - 6 B r^-6 = -r dE/dr
+  float gc;
+  float corr = 1.0f, elj = 0.0f;
+  if (ENERGY || MODE == 1) {
+    // Newton correction factor for rinv: rinv_exact ~= rinv * corr
+    corr = __fmaf_rn(__fmul_rn(r2, r2inv), -0.5f, 1.5f);
+    const float c2 = corr * corr;
+    const float r6e = r6 * (c2 * c2 * c2);
+    elj = (ab.x * r6e * (1.0f / 12.0f) - ab.y * (1.0f / 6.0f)) * r6e;  // A r^-12 - B r^-6
+  }
   if (MODE == 0) {
-    ec = (kqi * qj) * rinv;  // K qi qj / r
-    gc = ec;
+    gc = __fmul_rn(qq, rinv);  // K qi qj / r = -r dE/dr
+    if (ENERGY) pel += gc * corr;
   } else {
-    const float qq = excl ? 0.0f : kqi * qj;
-    ec = qq * (rinv + fmaf(P.krf, r2, -P.crf));   // forces.py:476
-    gc = qq * fmaf(-2.0f * P.krf, r2, rinv);      // -r * forces.py:478
-    const float r = r2 * rinv;
-    if (r > P.rs) {                                // forces.py:401-411 (note pot*deriv/dist as written)
-      const float t = (r - P.rs) * P.inv_sw;
-      const float sv = fmaf(t * t * t, fmaf(t, fmaf(t, -6.0f, 15.0f), -10.0f), 1.0f);
-      const float sd = t * t * fmaf(t, fmaf(t, -30.0f, 60.0f), -30.0f) * P.inv_sw;
-      glj = fmaf(sv, glj, -elj * sd);
+    gc = __fmul_rn(qq, __fmaf_rn(-2.0f * P.krf, r2, rinv));  // -r * forces.py:478
+    const float rinv_e = rinv * corr;
+    const float r = __fmul_rn(r2, rinv_e);
+    if (r > P.rs) {  // forces.py:401-411 (note pot*deriv/dist as written)
+      const float t = __fmul_rn(r - P.rs, P.inv_sw);
+      const float t2 = __fmul_rn(t, t);
+      const float sv = __fmaf_rn(__fmul_rn(t2, t), __fmaf_rn(t, __fmaf_rn(t, -6.0f, 15.0f), -10.0f), 1.0f);
+      const float sd = __fmul_rn(__fmul_rn(t2, __fmaf_rn(t, __fmaf_rn(t, -30.0f, 60.0f), -30.0f)), P.inv_sw);
+      glj = __fmaf_rn(sv, glj, -__fmul_rn(elj, sd));
       elj *= sv;
     }
+    if (ENERGY) pel += qq * (rinv_e + fmaf(P.krf, r2, -P.crf));  // forces.py:476
   }
-  if (ENERGY) { pel += ec; plj += elj; }
-  return (glj + gc) * r2inv;
+  if (ENERGY) plj += elj;
+  return __fmul_rn(__fadd_rn(glj, gc), r2inv);
 }
 
 // ---- TASK_TILE: j-chunk `chunk` (8 atoms) against i-blocks 0..passes-1 (32 lanes each) ----------
@@ -64,19 +77,19 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
     if (p < passes) {
       const int i = p * 32 + lane;
       const float4 pi = S.pos[i];
-      const float kqi = pi.w * kElecFactor;
+      const float kqi = __fmul_rn(pi.w, kElecFactor);
       const float2* row = (const float2*)((const char*)S.ab + S.ab_row_off[i]) + chunk * kChunk;
       const uint32_t m8 = S.mask8[chunk * kMaxAtoms + i];
       float pel = 0.0f, plj = 0.0f, ax = 0.0f, ay = 0.0f, az = 0.0f;
 #pragma unroll
       for (int s = 0; s < kChunk; ++s) {
         const float4 q = pj[s];
-        const float dx = pi.x - q.x, dy = pi.y - q.y, dz = pi.z - q.z;
+        const float dx = __fsub_rn(pi.x, q.x), dy = __fsub_rn(pi.y, q.y), dz = __fsub_rn(pi.z, q.z);
         const float sc = pair_eval<MODE, ENERGY>(dx, dy, dz, kqi, q.w, row[s], (m8 >> s) & 1u, P, pel, plj);
-        ax = fmaf(sc, dx, ax); ay = fmaf(sc, dy, ay); az = fmaf(sc, dz, az);
-        fj[s][0] = fmaf(sc, dx, fj[s][0]); fj[s][1] = fmaf(sc, dy, fj[s][1]); fj[s][2] = fmaf(sc, dz, fj[s][2]);
+        ax = __fmaf_rn(sc, dx, ax); ay = __fmaf_rn(sc, dy, ay); az = __fmaf_rn(sc, dz, az);
+        fj[s][0] = __fmaf_rn(sc, dx, fj[s][0]); fj[s][1] = __fmaf_rn(sc, dy, fj[s][1]); fj[s][2] = __fmaf_rn(sc, dz, fj[s][2]);
       }
-      fi[p][0] += ax; fi[p][1] += ay; fi[p][2] += az;
+      fi[p][0] = __fadd_rn(fi[p][0], ax); fi[p][1] = __fadd_rn(fi[p][1], ay); fi[p][2] = __fadd_rn(fi[p][2], az);
       if (ENERGY) { E.e[B200MD_E_ELECTROSTATICS] += (double)pel; E.e[B200MD_E_LJ] += (double)plj; }
     }
   }

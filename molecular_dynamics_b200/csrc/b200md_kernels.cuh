@@ -34,7 +34,7 @@ __host__ __device__ inline uint32_t make_task(uint32_t kind, uint32_t chunk, uin
 // Device view of a packed topology.  All pointers point into one device allocation.
 struct DevTopo {
   int natoms, ntypes, nchunks;
-  const float2* ab;         // [ntypes][kAbStride]  (A, B) of (type t, atom j)
+  const float2* ab;         // [ntypes][kAbStride]  (12 A, 6 B) of (type t, atom j)
   const float* charge;      // [128]
   const float* mass;        // [128]
   const int* ab_row_off;    // [128] byte offset of atom's LJ-table row
@@ -130,7 +130,9 @@ __device__ __forceinline__ float rsqrt_nr(float x) {
 }
 struct f3 { float x, y, z; };
 __device__ __forceinline__ f3 sub3(float4 a, float4 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
-__device__ __forceinline__ f3 cross3(f3 a, f3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+__device__ __forceinline__ f3 cross3(f3 a, f3 b) {
+  return {fmaf(a.y, b.z, -(a.z * b.y)), fmaf(a.z, b.x, -(a.x * b.z)), fmaf(a.x, b.y, -(a.y * b.x))};
+}
 __device__ __forceinline__ float dot3(f3 a, f3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
 
 // ---- Philox4x32-10 + Box-Muller (same stream as oracle_normal3) ---------------------------------

@@ -76,7 +76,8 @@ class Integrator:
         R, N, _ = pos.shape
         dev = pos.device
         box = s.box.to(device=dev, dtype=torch.float32).contiguous()
-        nrep = niter // self.energy_every if self.energy_every > 0 else 1
+        energy_every = self.energy_every if 0 < self.energy_every <= niter else 0  # shorter call: report at its end
+        nrep = niter // energy_every if energy_every > 0 else 1
         nsnap = niter // self.snapshot_every if self.snapshot_every > 0 else 0
         obs = torch.zeros((nrep, R, _cabi.NUM_OBSERVABLES), dtype=torch.float64, device=dev)
         snaps = torch.empty((nsnap, R, N, 3), dtype=torch.float32, device=dev)
@@ -95,7 +96,7 @@ class Integrator:
         torch.ops.b200md.integrate(pos, vel, frc, box, obs, snaps, status, f._handle(dev), *f._opts(), smd[0], smd[1],
                                    smd[2], smd[3], smd_c0, smd[5], float(self.dt), float(self.gamma),
                                    float(self.T) if self.T else 0.0, self.seed, self.step_count, self.replica0,
-                                   int(niter), int(self.energy_every), int(self.snapshot_every))
+                                   int(niter), int(energy_every), int(self.snapshot_every))
         self.step_count += int(niter)
         if self.check_nan:
             flags = int(status.max().item()) if R else 0

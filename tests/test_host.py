@@ -1,0 +1,103 @@
+"""Host-side logic and the C-ABI surface (no GPU needed)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import ROOT, SYSTEMS, load_golden
+from molecular_dynamics_b200 import Forces, System, _cabi
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    import __graft_entry__ as entry
+
+    entry.build()
+    header = open(os.path.join(ROOT, "include", "b200md.h")).read()
+    declared = set(re.findall(r"\b(b200md_[a-z0-9_]+)\s*\(", header))
+    declared -= {"b200md_topology_desc", "b200md_force_opts", "b200md_smd_opts", "b200md_integrate_opts"}
+    assert declared == set(_cabi.EXPORTED_SYMBOLS)
+    lib = ctypes.CDLL(_cabi.LIB_PATH)
+    for sym in declared:
+        assert hasattr(lib, sym), sym
+    assert b"sm_100a" in _cabi.load_library().b200md_version()
+
+
+def test_struct_layouts_match_header_sizes(tmp_path):
+    """sizeof of every struct as gcc sees include/b200md.h equals the ctypes mirror."""
+    import subprocess
+
+    src = tmp_path / "sz.c"
+    src.write_text('#include <stdio.h>\n#include "b200md.h"\nint main(){printf("%zu %zu %zu %zu\\n",'
+                   "sizeof(b200md_topology_desc),sizeof(b200md_force_opts),sizeof(b200md_smd_opts),"
+                   "sizeof(b200md_integrate_opts));return 0;}\n")
+    exe = tmp_path / "sz"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    sizes = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    mirror = [ctypes.sizeof(c) for c in (_cabi.TopologyDesc, _cabi.ForceOpts, _cabi.SmdOpts, _cabi.IntegrateOpts)]
+    assert sizes == mirror
+
+
+def test_product_path_has_no_cpu_fallback():
+    g = load_golden("diala")
+    F = Forces(g.par)
+    s = System(22, 1, torch.float, "cpu")
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        F.compute(s.pos, s.box, s.forces)
+    # nothing under molecular_dynamics_b200/ imports the oracle
+    pkg = os.path.join(ROOT, "molecular_dynamics_b200")
+    for fn in os.listdir(pkg):
+        if fn.endswith(".py"):
+            src = open(os.path.join(pkg, fn)).read()
+            assert not re.search(r"^\s*(import|from)\s+oracle", src, re.M), fn
+
+
+def test_forces_constructor_contract():
+    g = load_golden("bb40")
+    F = Forces(g.par, cutoff=9, rfa=True, switch_dist=7.5)
+    assert F.natoms == 40 and F.require_distances and F.cutoff == 9 and F.rfa and F.switch_dist == 7.5
+    assert F.energies == ["electrostatics", "lj", "bonds", "angles", "dihedrals", "1-4", "impropers"]
+    assert F.ava_idx.dtype == torch.int64 and tuple(F.ava_idx.shape) == (648, 2)
+    np.testing.assert_array_equal(F.ava_idx.numpy(), g.ava_idx)
+    assert Forces(g.par, terms=("bonds",)).ava_idx is None
+    with pytest.raises(ValueError):
+        Forces(g.par, terms=("bonds", "nope"))
+    with pytest.raises(RuntimeError):
+        Forces(g.par, terms=("1-4", "lj"))
+
+
+def test_torsion_slice_flattening_keeps_reference_branch_rule():
+    """forces.py:565: a slice is AMBER iff ALL its periodicities are > 0, else every term is harmonic."""
+    sl = [{"idx": torch.tensor([0, 1]), "params": torch.tensor([[1.0, 0.0, 2.0], [2.0, 0.1, 0.0]])},
+          {"idx": torch.tensor([1]), "params": torch.tensor([[0.5, 3.14, 3.0]])}]
+    owner, prm, harm = _cabi._flatten_torsion_slices(sl)
+    np.testing.assert_array_equal(owner, [0, 1, 1])
+    np.testing.assert_array_equal(harm, [1, 1, 0])
+    assert prm.shape == (3, 3)
+
+
+def test_system_setters_follow_reference():
+    s = System(5, 2, torch.float, "cpu")
+    assert s.natoms == 5 and s.nreplicas == 2 and s.box.shape == (2, 3, 3)
+    src = torch.arange(30, dtype=torch.float32).reshape(5, 3, 2).requires_grad_(True)
+    s.set_positions(src)
+    assert s.pos.shape == (2, 5, 3) and s.pos.requires_grad and not s.pos.is_contiguous()
+    with pytest.raises(RuntimeError):
+        s.set_positions(torch.zeros(5, 4, 2))
+    s.set_box(np.array([10.0, 11.0, 12.0]))
+    np.testing.assert_array_equal(s.box[1].numpy(), np.diag([10.0, 11.0, 12.0]))
+    with pytest.raises(RuntimeError):
+        s.set_velocities(torch.zeros(1, 5, 3))
+    s.set_velocities(torch.ones(2, 5, 3, dtype=torch.float64))
+    assert s.vel.dtype == torch.float32 and float(s.vel.sum()) == 30.0
+    s.set_forces(np.ones((2, 5, 3)))
+    assert float(s.forces.sum()) == 30.0
+
+
+def test_packed_topology_counts():
+    want = {"ala10": (104, 12, 103, 183, 250, 260, 250, 4820), "bb40": (40, 4, 39, 47, 46, 46, 46, 648)}
+    for name, w in want.items():
+        d = load_golden(name).packed.desc
+        assert (d.natoms, d.ntypes, d.nbonds, d.nangles, d.ndihedrals, d.ndihedral_terms, d.n14, d.npairs) == w

@@ -145,3 +145,45 @@ def test_langevin_thermostat_reaches_temperature():
     ekin = out["observables"][10:, :, _cabi.OBS_EKIN]
     T = 2.0 / (3 * 22 * 0.001987191) * ekin.mean()
     assert 255 < T < 345
+
+
+@pytest.mark.parametrize("system", SYSTEMS)
+def test_torch_port_matches_reference(system):
+    """oracle/torchmd_port.py (the timed CPU baseline) against the reference's own outputs."""
+    import torch
+
+    from oracle import torchmd_port as port
+
+    g = load_golden(system)
+    for mode, kw in MODES.items():
+        top = port.PortTopology(g.packed, torch.float64)
+        pos = torch.tensor(g["pos"]).double()
+        frc = torch.zeros_like(pos)
+        ene = port.compute(top, pos, frc, **kw).numpy()
+        np.testing.assert_allclose(ene, g[f"ref_{mode}_f64_energies"], rtol=1e-10, atol=1e-9)
+        assert np.abs(frc.numpy() - g[f"ref_{mode}_f64_forces"]).max() < 1e-9
+        top32 = port.PortTopology(g.packed, torch.float32)
+        pos32 = torch.tensor(g["pos"])
+        frc32 = torch.zeros_like(pos32)
+        ene32 = port.compute(top32, pos32, frc32, **kw).numpy()
+        ref32 = g[f"ref_{mode}_f32_forces"]
+        assert np.abs(frc32.numpy() - ref32).max() <= 2e-5 * np.abs(ref32).max()
+        np.testing.assert_allclose(ene32, g[f"ref_{mode}_f32_energies"], rtol=2e-5, atol=1e-4)
+
+
+def test_torch_port_integrator_matches_c_oracle():
+    import torch
+
+    from oracle import torchmd_port as port
+
+    g = load_golden("diala")
+    pos0 = g["pos"]
+    vel0 = (0.05 * np.random.default_rng(0).standard_normal(pos0.shape)).astype(np.float32)
+    f0, _ = oracle.forces(g.packed, pos0)
+    dt = float(np.float32(1.0 / TIMEFACTOR))
+    out = oracle.integrate(g.packed, pos0, vel0, f0, nsteps=25, dt=dt)
+    top = port.PortTopology(g.packed, torch.float64)
+    p, v, f = torch.tensor(pos0).double(), torch.tensor(vel0).double(), torch.tensor(f0)
+    ekin, ene = port.integrate(top, p, v, f, 25, dt)
+    np.testing.assert_allclose(p.numpy(), out["pos"], atol=1e-9)
+    np.testing.assert_allclose(ekin.numpy(), out["observables"][0, :, _cabi.OBS_EKIN], rtol=1e-9)
