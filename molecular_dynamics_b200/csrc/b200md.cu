@@ -34,11 +34,10 @@ __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, co
   for (int k = tid; k < kMaxChunks * kMaxAtoms / 4; k += kThreads)
     ((uint32_t*)S.mask8)[k] = __ldg((const uint32_t*)T.mask8 + k);
   for (int k = tid; k <= kMaxAtoms; k += kThreads) S.gstart[k] = __ldg(T.gather_start + k);
-  for (int k = tid; k < T.gather_total; k += kThreads) S.glist[k] = __ldg(T.gather_list + k);
   for (int k = tid; k < kWarps * kMaxTasks; k += kThreads) S.tasks[k] = __ldg(T.tasks + k);
   if (tid < 8) S.smd[tid] = 0.0f;
   // slots of disabled / dropped terms are never written: keep them at zero for the gather
-  for (int k = tid; k < 3 * T.nslots; k += kThreads) S.fb[k] = 0.0f;
+  for (int k = tid; k < T.nslots; k += kThreads) S.fb[k] = make_float4(0.f, 0.f, 0.f, 0.f);
   // chunks without a tile task (no non-bonded term enabled) must read as zero in the gather
   for (int k = tid; k < 3 * kMaxAtoms; k += kThreads) S.fj[k] = 0.0f;
 }
@@ -51,7 +50,7 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
               uint32_t* __restrict__ status) {
   extern __shared__ __align__(16) char smem_raw[];
   Smem S;
-  smem_layout(&S, smem_raw, T.ntypes, T.nslots, T.gather_total);
+  smem_layout(&S, smem_raw, T.ntypes, T.nslots);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int N = T.natoms;
   stage_tables(S, T, P, tid);
@@ -78,11 +77,11 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
     __syncthreads();
     if (tid < N) {
       float fx, fy, fz;
-      gather_forces(S, T, P, tid, fx, fy, fz);
+      gather_forces(S, P, tid, fx, fy, fz);
       float* f = forces + (r * N + tid) * 3;
       f[0] = fx; f[1] = fy; f[2] = fz;
     }
-    if (P.smd_on && tid == 0) E.e[B200MD_E_EXTERNAL] += (double)S.smd[3];
+    if (P.smd_on && tid == 0) E.e[B200MD_E_EXTERNAL] += S.smd_energy[0];
     reduce_energies(S, E, warp, lane);
     if (tid == 0) {
 #pragma unroll
@@ -101,7 +100,7 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
                  double* __restrict__ observables, float* __restrict__ snapshots, uint32_t* __restrict__ status) {
   extern __shared__ __align__(16) char smem_raw[];
   Smem S;
-  smem_layout(&S, smem_raw, T.ntypes, T.nslots, T.gather_total);
+  smem_layout(&S, smem_raw, T.ntypes, T.nslots);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int N = T.natoms;
   stage_tables(S, T, P, tid);
@@ -143,7 +142,7 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       }
       if (P.smd_on && tid == kThreads - 1) smd_task(S, P, (float)((double)P.smd_c0 + (double)P.smd_rate * (double)(gstep + 1)));
       __syncthreads();
-      if (live) gather_forces(S, T, P, tid, fx, fy, fz);
+      if (live) gather_forces(S, P, tid, fx, fy, fz);
       if (langevin) {  // vel += -gamma vel dt + vcoeff N(0,1)
         float n[3];
         normal3(I.seed, (unsigned long long)(I.replica0 + r), (uint32_t)tid, gstep, n);
@@ -153,7 +152,7 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       vx = fmaf(hdt_m, fx, vx); vy = fmaf(hdt_m, fy, vy); vz = fmaf(hdt_m, fz, vz);
       if (report) {
         if (live) E.e[B200MD_OBS_EKIN] = 0.5 * (double)mass * ((double)vx * vx + (double)vy * vy + (double)vz * vz);
-        if (P.smd_on && tid == 0) { E.e[B200MD_E_EXTERNAL] += (double)S.smd[3]; E.e[B200MD_OBS_E2E_DIST] = (double)S.smd[4]; }
+        if (P.smd_on && tid == 0) { E.e[B200MD_E_EXTERNAL] += S.smd_energy[0]; E.e[B200MD_OBS_E2E_DIST] = (double)S.smd[4]; }
         reduce_energies(S, E, warp, lane);
         if (tid == 0 && observables != nullptr) {
           const long long slot = I.energy_every > 0 ? (s + 1) / I.energy_every - 1 : 0;
@@ -246,15 +245,26 @@ uint32_t pack4(const int32_t* a, int n) {
   return q;
 }
 
-// flatten par.dihedral_params slices into per-dihedral [first, count] ranges (slice order kept)
+// flatten par.dihedral_params slices into per-dihedral [first, count] ranges (slice order kept).
+// term = (k0, per | marker, c0, s0): integer periodicity 1..8 -> (cos phi0, sin phi0) so the kernel never
+// forms phi; harmonic slices (forces.py:565 failed) and non-integer periodicities keep phi0.
 void build_terms(int nitems, int nterms, const int32_t* owner, const float* prm, const int32_t* harmonic,
                  std::vector<uint2>& ranges, std::vector<float4>& out) {
   ranges.assign(std::max(nitems, 1), make_uint2(0, 0));
   out.clear();
   for (int d = 0; d < nitems; ++d) {
     uint32_t first = (uint32_t)out.size();
-    for (int t = 0; t < nterms; ++t)
-      if (owner[t] == d) out.push_back(make_float4(prm[3 * t], prm[3 * t + 1], prm[3 * t + 2], harmonic[t] ? 1.0f : 0.0f));
+    for (int t = 0; t < nterms; ++t) {
+      if (owner[t] != d) continue;
+      const float k0 = prm[3 * t], phi0 = prm[3 * t + 1], per = prm[3 * t + 2];
+      if (harmonic[t]) {
+        out.push_back(make_float4(k0, kTermHarmonic, phi0, 0.0f));
+      } else if (per >= 1.0f && per <= 8.0f && per == floorf(per)) {
+        out.push_back(make_float4(k0, per, (float)cos((double)phi0), (float)sin((double)phi0)));
+      } else {
+        out.push_back(make_float4(k0, kTermGeneral, phi0, per));
+      }
+    }
     ranges[d] = make_uint2(first, (uint32_t)out.size() - first);
   }
 }
@@ -335,10 +345,8 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   }
 
   // ---- bonded items ------------------------------------------------------------------------------
-  std::vector<uint32_t> bond_idx(d->nbonds), angle_idx(d->nangles), dih_idx(d->ndihedrals), imp_idx(d->nimpropers),
-      p14_idx(d->n14);
+  std::vector<uint32_t> bond_idx(d->nbonds), angle_idx(d->nangles), dih_idx(d->ndihedrals), imp_idx(d->nimpropers);
   std::vector<float2> bond_prm(d->nbonds), angle_prm(d->nangles);
-  std::vector<float4> p14_prm(d->n14);
   for (int k = 0; k < d->nbonds; ++k) {
     bond_idx[k] = pack4(d->bond_idx + 2 * k, 2);
     bond_prm[k] = make_float2(d->bond_prm[2 * k], d->bond_prm[2 * k + 1]);
@@ -349,13 +357,33 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   }
   for (int k = 0; k < d->ndihedrals; ++k) dih_idx[k] = pack4(d->dihedral_idx + 4 * k, 4);
   for (int k = 0; k < d->nimpropers; ++k) imp_idx[k] = pack4(d->improper_idx + 4 * k, 4);
+  // 1-4 pairs (forces.py:176-226): fused into the first dihedral item whose end atoms they are; pairs
+  // without such a dihedral stay in their own ("orphan") list.  Stored as (12 A/scnb, 6 B/scnb, K qi qj/scee).
+  std::vector<float4> dih_p14(std::max(d->ndihedrals, 1), make_float4(0.f, 0.f, 0.f, 0.f)), p14_prm;
+  std::vector<uint32_t> p14_idx;
+  std::vector<int> orphan_src;
   for (int k = 0; k < d->n14; ++k) {
-    p14_idx[k] = pack4(d->idx14 + 2 * k, 2);
+    const int i = d->idx14[2 * k], j = d->idx14[2 * k + 1];
     const float* p = d->prm14 + 4 * k;  // A, B, scnb, scee (forces.py:197-200)
-    const double qi = d->charge ? d->charge[d->idx14[2 * k]] : 0.0, qj = d->charge ? d->charge[d->idx14[2 * k + 1]] : 0.0;
-    p14_prm[k] = make_float4((float)((double)p[0] / p[2]), (float)((double)p[1] / p[2]),
-                             (float)(332.06371307417066 * qi * qj / p[3]), 0.f);
+    const double qi = d->charge ? d->charge[i] : 0.0, qj = d->charge ? d->charge[j] : 0.0;
+    float4 prm = make_float4((float)(12.0 * (double)p[0] / p[2]), (float)(6.0 * (double)p[1] / p[2]),
+                             (float)(332.06371307417066 * qi * qj / p[3]), 1.0f);
+    int owner = -1;
+    for (int q = 0; q < d->ndihedrals && owner < 0; ++q) {
+      const int32_t* a = d->dihedral_idx + 4 * q;
+      if (dih_p14[q].w == 0.0f && ((a[0] == i && a[3] == j) || (a[0] == j && a[3] == i))) owner = q;
+    }
+    if (owner >= 0) {
+      dih_p14[owner] = prm;
+    } else {
+      p14_idx.push_back(pack4(d->idx14 + 2 * k, 2));
+      p14_prm.push_back(prm);
+      orphan_src.push_back(k);
+    }
   }
+  T.n14 = (int)p14_idx.size();
+  T.dih_on = 1;
+  T.p14_on = 1;
   std::vector<uint2> dih_terms, imp_terms;
   std::vector<float4> dih_tp, imp_tp;
   build_terms(d->ndihedrals, d->ndihedral_terms, d->dihedral_term_owner, d->dihedral_term_prm,
@@ -363,30 +391,42 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   build_terms(d->nimpropers, d->nimproper_terms, d->improper_term_owner, d->improper_term_prm,
               d->improper_term_harmonic, imp_terms, imp_tp);
 
-  // ---- bonded force slots + per-atom gather lists (fixed order => deterministic sums) ------------
-  const int counts[6] = {0, d->nbonds, d->nangles, d->ndihedrals, d->nimpropers, d->n14};
+  // ---- atom-major force slots: contribution (item, position) of atom a gets the next slot of a -----
+  // (fixed order bonds, angles, dihedrals, impropers, orphan 1-4 => deterministic sums in the gather)
+  std::vector<int> orphan_atoms(2 * p14_idx.size());
+  for (size_t k = 0; k < p14_idx.size(); ++k) {
+    orphan_atoms[2 * k] = d->idx14[2 * orphan_src[k]];
+    orphan_atoms[2 * k + 1] = d->idx14[2 * orphan_src[k] + 1];
+  }
+  const int counts[6] = {0, d->nbonds, d->nangles, d->ndihedrals, d->nimpropers, (int)p14_idx.size()};
   const int arity[6] = {0, 2, 3, 4, 4, 2};
-  const int32_t* idxs[6] = {nullptr, d->bond_idx, d->angle_idx, d->dihedral_idx, d->improper_idx, d->idx14};
-  int nslots = 0;
-  for (int ty = 1; ty < 6; ++ty) {
-    T.slot_base[ty] = nslots;
-    T.slot_pad[ty] = (counts[ty] + 31) / 32 * 32;
-    nslots += arity[ty] * T.slot_pad[ty];
-  }
-  T.slot_base[0] = T.slot_pad[0] = 0;
-  T.nslots = nslots;
-  std::vector<std::vector<uint16_t>> per_atom(kMaxAtoms);
+  const int32_t* idxs[6] = {nullptr, d->bond_idx, d->angle_idx, d->dihedral_idx, d->improper_idx, orphan_atoms.data()};
+  std::vector<int> per_atom_count(kMaxAtoms, 0);
   for (int ty = 1; ty < 6; ++ty)
-    for (int it = 0; it < counts[ty]; ++it)
-      for (int p = 0; p < arity[ty]; ++p)
-        per_atom[idxs[ty][it * arity[ty] + p]].push_back((uint16_t)(T.slot_base[ty] + p * T.slot_pad[ty] + it));
-  std::vector<uint16_t> gstart(kMaxAtoms + 2, 0), glist;
-  for (int a = 0; a < kMaxAtoms; ++a) {
-    gstart[a] = (uint16_t)glist.size();
-    glist.insert(glist.end(), per_atom[a].begin(), per_atom[a].end());
+    for (int it = 0; it < counts[ty] * arity[ty]; ++it) per_atom_count[idxs[ty][it]]++;
+  std::vector<uint16_t> gstart(kMaxAtoms + 2, 0);
+  int nslots = 0;
+  for (int a = 0; a < kMaxAtoms; ++a) { gstart[a] = (uint16_t)nslots; nslots += per_atom_count[a]; }
+  gstart[kMaxAtoms] = gstart[kMaxAtoms + 1] = (uint16_t)nslots;
+  if (nslots > 65535) { delete topo; fail(B200MD_ERR_UNSUPPORTED, "too many bonded force contributions"); return nullptr; }
+  T.nslots = nslots;
+  std::vector<int> cursor(gstart.begin(), gstart.begin() + kMaxAtoms);
+  std::vector<std::vector<uint16_t>> slot_of(6);
+  for (int ty = 1; ty < 6; ++ty) {
+    slot_of[ty].resize((size_t)counts[ty] * arity[ty]);
+    for (int it = 0; it < counts[ty] * arity[ty]; ++it) slot_of[ty][it] = (uint16_t)cursor[idxs[ty][it]]++;
   }
-  gstart[kMaxAtoms] = gstart[kMaxAtoms + 1] = (uint16_t)glist.size();
-  T.gather_total = (int)glist.size();
+  auto pair16 = [](uint16_t lo, uint16_t hi) { return (uint32_t)lo | ((uint32_t)hi << 16); };
+  std::vector<uint32_t> bond_slot(d->nbonds), p14_slot(p14_idx.size());
+  std::vector<uint2> angle_slot(d->nangles), dih_slot(std::max(d->ndihedrals, 1)), imp_slot(std::max(d->nimpropers, 1));
+  for (int k = 0; k < d->nbonds; ++k) bond_slot[k] = pair16(slot_of[1][2 * k], slot_of[1][2 * k + 1]);
+  for (int k = 0; k < d->nangles; ++k)
+    angle_slot[k] = make_uint2(pair16(slot_of[2][3 * k], slot_of[2][3 * k + 1]), slot_of[2][3 * k + 2]);
+  for (int k = 0; k < d->ndihedrals; ++k)
+    dih_slot[k] = make_uint2(pair16(slot_of[3][4 * k], slot_of[3][4 * k + 1]), pair16(slot_of[3][4 * k + 2], slot_of[3][4 * k + 3]));
+  for (int k = 0; k < d->nimpropers; ++k)
+    imp_slot[k] = make_uint2(pair16(slot_of[4][4 * k], slot_of[4][4 * k + 1]), pair16(slot_of[4][4 * k + 2], slot_of[4][4 * k + 3]));
+  for (size_t k = 0; k < p14_idx.size(); ++k) p14_slot[k] = pair16(slot_of[5][2 * k], slot_of[5][2 * k + 1]);
 
   // ---- static task schedule: longest-processing-time-first over the 4 warps ----------------------
   struct Task { uint32_t word; int cost; };
@@ -395,9 +435,9 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   if (d->npairs > 0)
     for (int c = 0; c < T.nchunks; ++c) {
       const int passes = std::min(nblocks, (c * kChunk + kChunk - 1) / 32 + 1);
-      all.push_back({make_task(TASK_TILE, c, passes), passes * kChunk * 28 + 110});
+      all.push_back({make_task(TASK_TILE, c, passes), passes * kChunk * 24 + 110});
     }
-  const int chunk_cost[6] = {0, 50, 120, 280, 280, 45};
+  const int chunk_cost[6] = {0, 50, 110, 230, 200, 45};
   for (int ty = 1; ty < 6; ++ty)
     for (int c = 0; c < (counts[ty] + 31) / 32; ++c) all.push_back({make_task(ty, c, 0), chunk_cost[ty]});
   std::stable_sort(all.begin(), all.end(), [](const Task& a, const Task& b) { return a.cost > b.cost; });
@@ -415,11 +455,12 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   // ---- upload --------------------------------------------------------------------------------------
   BlobBuilder B;
   const size_t o_ab = B.add(ab), o_q = B.add(charge), o_m = B.add(mass), o_ro = B.add(rowoff), o_mask = B.add(mask8);
-  const size_t o_bi = B.add(bond_idx), o_bp = B.add(bond_prm), o_ai = B.add(angle_idx), o_ap = B.add(angle_prm);
-  const size_t o_di = B.add(dih_idx), o_dt = B.add(dih_terms), o_dp = B.add(dih_tp);
-  const size_t o_ii = B.add(imp_idx), o_it = B.add(imp_terms), o_ip = B.add(imp_tp);
-  const size_t o_pi = B.add(p14_idx), o_pp = B.add(p14_prm);
-  const size_t o_gs = B.add(gstart), o_gl = B.add(glist), o_tk = B.add(tasks);
+  const size_t o_bi = B.add(bond_idx), o_bp = B.add(bond_prm), o_bs = B.add(bond_slot);
+  const size_t o_ai = B.add(angle_idx), o_ap = B.add(angle_prm), o_as = B.add(angle_slot);
+  const size_t o_di = B.add(dih_idx), o_dt = B.add(dih_terms), o_dp = B.add(dih_tp), o_ds = B.add(dih_slot), o_d14 = B.add(dih_p14);
+  const size_t o_ii = B.add(imp_idx), o_it = B.add(imp_terms), o_ip = B.add(imp_tp), o_is = B.add(imp_slot);
+  const size_t o_pi = B.add(p14_idx), o_pp = B.add(p14_prm), o_ps = B.add(p14_slot);
+  const size_t o_gs = B.add(gstart), o_tk = B.add(tasks);
   auto cleanup = [&](const std::string& msg) { fail(B200MD_ERR_CUDA, msg); if (topo->blob) cudaFree(topo->blob); delete topo; };
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) { cleanup(std::string("cudaSetDevice: ") + cudaGetErrorString(e)); return nullptr; }
@@ -430,14 +471,16 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   char* base = (char*)topo->blob;
   T.ab = (const float2*)(base + o_ab); T.charge = (const float*)(base + o_q); T.mass = (const float*)(base + o_m);
   T.ab_row_off = (const int*)(base + o_ro); T.mask8 = (const uint8_t*)(base + o_mask);
-  T.bond_idx = (const uint32_t*)(base + o_bi); T.bond_prm = (const float2*)(base + o_bp);
-  T.angle_idx = (const uint32_t*)(base + o_ai); T.angle_prm = (const float2*)(base + o_ap);
+  T.bond_idx = (const uint32_t*)(base + o_bi); T.bond_prm = (const float2*)(base + o_bp); T.bond_slot = (const uint32_t*)(base + o_bs);
+  T.angle_idx = (const uint32_t*)(base + o_ai); T.angle_prm = (const float2*)(base + o_ap); T.angle_slot = (const uint2*)(base + o_as);
   T.dih_idx = (const uint32_t*)(base + o_di); T.dih_terms = (const uint2*)(base + o_dt); T.dih_term_prm = (const float4*)(base + o_dp);
+  T.dih_slot = (const uint2*)(base + o_ds); T.dih_p14 = (const float4*)(base + o_d14);
   T.imp_idx = (const uint32_t*)(base + o_ii); T.imp_terms = (const uint2*)(base + o_it); T.imp_term_prm = (const float4*)(base + o_ip);
-  T.p14_idx = (const uint32_t*)(base + o_pi); T.p14_prm = (const float4*)(base + o_pp);
-  T.gather_start = (const uint16_t*)(base + o_gs); T.gather_list = (const uint16_t*)(base + o_gl);
+  T.imp_slot = (const uint2*)(base + o_is);
+  T.p14_idx = (const uint32_t*)(base + o_pi); T.p14_prm = (const float4*)(base + o_pp); T.p14_slot = (const uint32_t*)(base + o_ps);
+  T.gather_start = (const uint16_t*)(base + o_gs);
   T.tasks = (const uint32_t*)(base + o_tk);
-  T.smem_bytes = (int)smem_layout(nullptr, nullptr, NT, nslots, T.gather_total);
+  T.smem_bytes = (int)smem_layout(nullptr, nullptr, NT, nslots);
   if (T.smem_bytes > 227 * 1024) { cleanup("topology needs more than 227 KB of shared memory per CTA"); g_last_error = "too much shared memory"; return nullptr; }
   cudaDeviceProp prop;
   cudaGetDeviceProperties(&prop, device);
@@ -499,17 +542,18 @@ static int make_force_params(const b200md_topology* topo, const b200md_force_opt
   return B200MD_OK;
 }
 
-// DevTopo copy with the per-call term switches applied: a disabled bonded term gets a zero count, so
-// its chunks return immediately and its slots are never written nor gathered (slots of disabled terms
-// would hold stale data, hence the gather lists are filtered by zeroing those slots once at staging).
-static DevTopo apply_terms(const DevTopo& in, uint32_t terms, bool* needs_slot_clear) {
+// DevTopo copy with the per-call term switches applied: a disabled bonded term gets a zero count, so its
+// chunks return immediately; its slots are zeroed once at staging and never written, so the gather adds 0.
+static DevTopo apply_terms(const DevTopo& in, uint32_t terms) {
   DevTopo T = in;
-  *needs_slot_clear = false;
-  if (!(terms & B200MD_T_BONDS)) { T.nbonds = 0; *needs_slot_clear = true; }
-  if (!(terms & B200MD_T_ANGLES)) { T.nangles = 0; *needs_slot_clear = true; }
-  if (!(terms & B200MD_T_DIHEDRALS)) { T.ndih = 0; *needs_slot_clear = true; }
-  if (!(terms & B200MD_T_IMPROPERS)) { T.nimp = 0; *needs_slot_clear = true; }
-  if (!(terms & B200MD_T_14) || !(terms & (B200MD_T_LJ | B200MD_T_ELECTROSTATICS))) { T.n14 = 0; *needs_slot_clear = true; }
+  const bool p14 = (terms & B200MD_T_14) && (terms & (B200MD_T_LJ | B200MD_T_ELECTROSTATICS));
+  if (!(terms & B200MD_T_BONDS)) T.nbonds = 0;
+  if (!(terms & B200MD_T_ANGLES)) T.nangles = 0;
+  if (!(terms & B200MD_T_IMPROPERS)) T.nimp = 0;
+  T.dih_on = (terms & B200MD_T_DIHEDRALS) ? 1 : 0;
+  T.p14_on = p14 ? 1 : 0;
+  if (!T.dih_on && !T.p14_on) T.ndih = 0;
+  if (!p14) T.n14 = 0;
   return T;
 }
 
@@ -522,8 +566,7 @@ extern "C" int b200md_forces_compute(const b200md_topology* topo, const b200md_f
   ForceParams P;
   int rc = make_force_params(topo, opts, smd, false, &P);
   if (rc) return rc;
-  bool clear;
-  DevTopo T = apply_terms(topo->dev, opts->terms, &clear);
+  DevTopo T = apply_terms(topo->dev, opts->terms);
   CUDA_TRY(cudaSetDevice(topo->device));
   const int mode = P.has_cutoff ? 1 : 0;
   const long long cap = (long long)topo->num_sms * topo->occ_forces[mode];
@@ -548,8 +591,7 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
   ForceParams P;
   int rc = make_force_params(topo, fopts, smd, true, &P);
   if (rc) return rc;
-  bool clear;
-  DevTopo T = apply_terms(topo->dev, fopts->terms, &clear);
+  DevTopo T = apply_terms(topo->dev, fopts->terms);
   StepParams I;
   I.dt = io->dt; I.gamma = io->gamma; I.temperature = io->temperature;
   I.seed = io->seed; I.step0 = io->step0; I.replica0 = io->replica0;

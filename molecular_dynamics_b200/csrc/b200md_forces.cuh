@@ -65,6 +65,8 @@ __device__ __forceinline__ float pair_eval(float dx, float dy, float dz, float k
 }
 
 // ---- TASK_TILE: j-chunk `chunk` (8 atoms) against i-blocks 0..passes-1 (32 lanes each) ----------
+// The pass loop is rolled (one 8-step body in the instruction cache); the i-side force of pass p goes
+// to the register accumulator fi[p] through a predicated add chain.
 template <int MODE, bool ENERGY>
 __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, int chunk, int passes, int lane,
                                           float (&fi)[4][3], Energies& E) {
@@ -72,26 +74,26 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
 #pragma unroll
   for (int s = 0; s < kChunk; ++s) fj[s][0] = fj[s][1] = fj[s][2] = 0.0f;
   const float4* pj = S.pos + chunk * kChunk;
+#pragma unroll 1
+  for (int p = 0; p < passes; ++p) {
+    const int i = p * 32 + lane;
+    const float4 pi = S.pos[i];
+    const float kqi = __fmul_rn(pi.w, kElecFactor);
+    const float2* row = (const float2*)((const char*)S.ab + S.ab_row_off[i]) + chunk * kChunk;
+    const uint32_t m8 = S.mask8[chunk * kMaxAtoms + i];
+    float pel = 0.0f, plj = 0.0f, ax = 0.0f, ay = 0.0f, az = 0.0f;
 #pragma unroll
-  for (int p = 0; p < 4; ++p) {
-    if (p < passes) {
-      const int i = p * 32 + lane;
-      const float4 pi = S.pos[i];
-      const float kqi = __fmul_rn(pi.w, kElecFactor);
-      const float2* row = (const float2*)((const char*)S.ab + S.ab_row_off[i]) + chunk * kChunk;
-      const uint32_t m8 = S.mask8[chunk * kMaxAtoms + i];
-      float pel = 0.0f, plj = 0.0f, ax = 0.0f, ay = 0.0f, az = 0.0f;
-#pragma unroll
-      for (int s = 0; s < kChunk; ++s) {
-        const float4 q = pj[s];
-        const float dx = __fsub_rn(pi.x, q.x), dy = __fsub_rn(pi.y, q.y), dz = __fsub_rn(pi.z, q.z);
-        const float sc = pair_eval<MODE, ENERGY>(dx, dy, dz, kqi, q.w, row[s], (m8 >> s) & 1u, P, pel, plj);
-        ax = __fmaf_rn(sc, dx, ax); ay = __fmaf_rn(sc, dy, ay); az = __fmaf_rn(sc, dz, az);
-        fj[s][0] = __fmaf_rn(sc, dx, fj[s][0]); fj[s][1] = __fmaf_rn(sc, dy, fj[s][1]); fj[s][2] = __fmaf_rn(sc, dz, fj[s][2]);
-      }
-      fi[p][0] = __fadd_rn(fi[p][0], ax); fi[p][1] = __fadd_rn(fi[p][1], ay); fi[p][2] = __fadd_rn(fi[p][2], az);
-      if (ENERGY) { E.e[B200MD_E_ELECTROSTATICS] += (double)pel; E.e[B200MD_E_LJ] += (double)plj; }
+    for (int s = 0; s < kChunk; ++s) {
+      const float4 q = pj[s];
+      const float dx = __fsub_rn(pi.x, q.x), dy = __fsub_rn(pi.y, q.y), dz = __fsub_rn(pi.z, q.z);
+      const float sc = pair_eval<MODE, ENERGY>(dx, dy, dz, kqi, q.w, row[s], (m8 >> s) & 1u, P, pel, plj);
+      ax = __fmaf_rn(sc, dx, ax); ay = __fmaf_rn(sc, dy, ay); az = __fmaf_rn(sc, dz, az);
+      fj[s][0] = __fmaf_rn(sc, dx, fj[s][0]); fj[s][1] = __fmaf_rn(sc, dy, fj[s][1]); fj[s][2] = __fmaf_rn(sc, dz, fj[s][2]);
     }
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (p == k) { fi[k][0] = __fadd_rn(fi[k][0], ax); fi[k][1] = __fadd_rn(fi[k][1], ay); fi[k][2] = __fadd_rn(fi[k][2], az); }
+    if (ENERGY) { E.e[B200MD_E_ELECTROSTATICS] += (double)pel; E.e[B200MD_E_LJ] += (double)plj; }
   }
   // Transposing butterfly: 24 per-lane partials -> per-atom sums.  After the xor-16/8/4 stages lane l
   // holds atom (l >> 2) & 7 of the chunk; xor-2/1 finish the sum.  Fixed order => deterministic.
@@ -103,7 +105,7 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
     for (int c = 0; c < 3; ++c) {
       const float send = b4 ? fj[k][c] : fj[k + 4][c];
       const float keep = b4 ? fj[k + 4][c] : fj[k][c];
-      v4[k][c] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+      v4[k][c] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 16));
     }
 #pragma unroll
   for (int k = 0; k < 2; ++k)
@@ -111,15 +113,15 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
     for (int c = 0; c < 3; ++c) {
       const float send = b3 ? v4[k][c] : v4[k + 2][c];
       const float keep = b3 ? v4[k + 2][c] : v4[k][c];
-      v2[k][c] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+      v2[k][c] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 8));
     }
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
     const float send = b2 ? v2[0][c] : v2[1][c];
     const float keep = b2 ? v2[1][c] : v2[0][c];
-    float v = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-    v += __shfl_xor_sync(0xffffffffu, v, 2);
-    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    float v = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 4));
+    v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, 2));
+    v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, 1));
     v1[c] = v;
   }
   if ((lane & 3) == 0) {
@@ -130,30 +132,26 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
   }
 }
 
-// ---- bonded slots -----------------------------------------------------------------------------
-__device__ __forceinline__ void put_slot(const Smem& S, const DevTopo& T, int type, int pos, int item, float x,
-                                         float y, float z) {
-  const int k = T.slot_base[type] + pos * T.slot_pad[type] + item;
-  S.fb[k] = x;
-  S.fb[T.nslots + k] = y;
-  S.fb[2 * T.nslots + k] = z;
+// ---- bonded items: force vectors go to private atom-major float4 slots ------------------------------
+__device__ __forceinline__ void put(const Smem& S, uint32_t slot, float x, float y, float z) {
+  S.fb[slot] = make_float4(x, y, z, 0.0f);
 }
 
 // evaluate_bonds, forces.py:111-132, 492-501
 template <bool ENERGY>
 __device__ __forceinline__ void bond_task(const Smem& S, const DevTopo& T, const ForceParams& P, int item, Energies& E) {
   if (item >= T.nbonds) return;
-  const uint32_t q = __ldg(T.bond_idx + item);
+  const uint32_t q = __ldg(T.bond_idx + item), sl = __ldg(T.bond_slot + item);
   const float2 prm = __ldg(T.bond_prm + item);
   const float4 pa = S.pos[q & 0xff], pb = S.pos[(q >> 8) & 0xff];
   const f3 d = sub3(pa, pb);
   const float r2 = dot3(d, d);
   const float rinv = rsqrtf(r2), dist = r2 * rinv;
-  const bool keep = !P.has_cutoff || dist <= P.rc;
+  const bool keep = !P.has_cutoff || dist <= P.rc;  // forces.py:117-125
   const float x = dist - prm.y;
   const float c = keep ? 2.0f * prm.x * x * rinv : 0.0f;  // dE/dr / r
-  put_slot(S, T, TASK_BOND, 0, item, -c * d.x, -c * d.y, -c * d.z);
-  put_slot(S, T, TASK_BOND, 1, item, c * d.x, c * d.y, c * d.z);
+  put(S, sl & 0xffff, -c * d.x, -c * d.y, -c * d.z);
+  put(S, sl >> 16, c * d.x, c * d.y, c * d.z);
   if (ENERGY && keep) {
     // k (r - r0)^2 cancels ~40:1 in (r - r0): the energy (report steps only) takes r in FP64
     const double ddx = (double)pa.x - (double)pb.x, ddy = (double)pa.y - (double)pb.y, ddz = (double)pa.z - (double)pb.z;
@@ -167,6 +165,7 @@ template <bool ENERGY>
 __device__ __forceinline__ void angle_task(const Smem& S, const DevTopo& T, int item, Energies& E) {
   if (item >= T.nangles) return;
   const uint32_t q = __ldg(T.angle_idx + item);
+  const uint2 sl = __ldg(T.angle_slot + item);
   const float2 prm = __ldg(T.angle_prm + item);
   const float4 p0 = S.pos[q & 0xff], p1 = S.pos[(q >> 8) & 0xff], p2 = S.pos[(q >> 16) & 0xff];
   const f3 r21 = sub3(p0, p1), r23 = sub3(p2, p1);
@@ -175,79 +174,127 @@ __device__ __forceinline__ void angle_task(const Smem& S, const DevTopo& T, int 
   ct = fminf(fmaxf(ct, -1.0f), 1.0f);
   const float th = acosf(ct), dth = th - prm.y;
   if (ENERGY) E.e[B200MD_E_ANGLES] += (double)(prm.x * dth * dth);
-  const float st = sqrtf(fmaf(-ct, ct, 1.0f));
-  const float coef = (st != 0.0f) ? -2.0f * prm.x * dth / st : 0.0f;
+  const float st2 = fmaf(-ct, ct, 1.0f);
+  const float coef = (st2 > 0.0f) ? -2.0f * prm.x * dth * rsqrtf(st2) : 0.0f;  // 0 where sin(theta) == 0
   const float a0 = coef * n21i, a2 = coef * n23i;
   const float c21 = ct * n21i, c23 = ct * n23i;
-  const float f0x = a0 * (c21 * r21.x - r23.x * n23i), f0y = a0 * (c21 * r21.y - r23.y * n23i),
-              f0z = a0 * (c21 * r21.z - r23.z * n23i);
-  const float f2x = a2 * (c23 * r23.x - r21.x * n21i), f2y = a2 * (c23 * r23.y - r21.y * n21i),
-              f2z = a2 * (c23 * r23.z - r21.z * n21i);
-  put_slot(S, T, TASK_ANGLE, 0, item, f0x, f0y, f0z);
-  put_slot(S, T, TASK_ANGLE, 1, item, -(f0x + f2x), -(f0y + f2y), -(f0z + f2z));
-  put_slot(S, T, TASK_ANGLE, 2, item, f2x, f2y, f2z);
+  const float f0x = a0 * fmaf(c21, r21.x, -r23.x * n23i), f0y = a0 * fmaf(c21, r21.y, -r23.y * n23i),
+              f0z = a0 * fmaf(c21, r21.z, -r23.z * n23i);
+  const float f2x = a2 * fmaf(c23, r23.x, -r21.x * n21i), f2y = a2 * fmaf(c23, r23.y, -r21.y * n21i),
+              f2z = a2 * fmaf(c23, r23.z, -r21.z * n21i);
+  put(S, sl.x & 0xffff, f0x, f0y, f0z);
+  put(S, sl.x >> 16, -(f0x + f2x), -(f0y + f2y), -(f0z + f2z));
+  put(S, sl.y & 0xffff, f2x, f2y, f2z);
 }
 
-// evaluate_torsion, forces.py:147-174 / 228-255, 540-602 (dihedrals and impropers share it)
+// One LJ + Coulomb pair with its own (12 A', 6 B', K qi qj') parameters: forces.py:176-226 (1-4 pairs are
+// never cut, switched or reaction-field corrected).  Returns s with F_a += s d, F_b -= s d, d = r_a - r_b.
 template <bool ENERGY>
-__device__ __forceinline__ void torsion_task(const Smem& S, const DevTopo& T, int type, int item, int count,
-                                             const uint32_t* idx, const uint2* terms, const float4* term_prm,
-                                             double& Eacc) {
+__device__ __forceinline__ float pair14(f3 d, float4 prm, const ForceParams& P, Energies& E) {
+  const float rinv = rsqrt_nr(dot3(d, d));
+  const float r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
+  const float a12 = prm.x * P.lj_on, b6 = prm.y * P.lj_on, qq = prm.z * P.el_on;
+  const float ec = qq * rinv;
+  const float glj = fmaf(a12, r6, -b6) * r6;
+  if (ENERGY) {
+    E.e[B200MD_E_LJ] += (double)(fmaf(a12 * (1.0f / 12.0f), r6, -b6 * (1.0f / 6.0f)) * r6);
+    E.e[B200MD_E_ELECTROSTATICS] += (double)ec;
+  }
+  return (glj + ec) * r2inv;
+}
+
+// evaluate_torsion, forces.py:147-174 / 228-255, 540-602 (dihedrals and impropers share it), with the
+// 1-4 pair on the end atoms (forces.py:176-226) fused into the dihedral item that owns it.
+// phi = -atan2(sinPhi, cosPhi) is never formed for AMBER terms with integer periodicity: cos/sin(n phi)
+// come from (cos phi + i sin phi)^n and the phase enters through its precomputed cosine / sine.
+template <bool ENERGY>
+__device__ __forceinline__ void torsion_task(const Smem& S, const ForceParams& P, bool torsion_on, bool fuse14,
+                                             int item, int count, const uint32_t* idx, const uint2* terms,
+                                             const float4* term_prm, const uint2* slots, const float4* p14,
+                                             double& Eacc, Energies& E) {
   if (item >= count) return;
   const uint32_t q = __ldg(idx + item);
+  const uint2 sl = __ldg(slots + item);
   const float4 p0 = S.pos[q & 0xff], p1 = S.pos[(q >> 8) & 0xff], p2 = S.pos[(q >> 16) & 0xff], p3 = S.pos[q >> 24];
-  const f3 r12 = sub3(p0, p1), r23 = sub3(p1, p2), r34 = sub3(p2, p3);
-  const f3 cA = cross3(r12, r23), cB = cross3(r23, r34), cC = cross3(r23, cA);
-  const float nA2 = dot3(cA, cA), nB2 = dot3(cB, cB), nC2 = dot3(cC, cC);
-  const float rnA = rsqrtf(nA2), rnB = rsqrtf(nB2), rnC = rsqrtf(nC2);
-  const float cosPhi = dot3(cA, cB) * rnB * rnA, sinPhi = dot3(cC, cB) * rnB * rnC;
-  const float phi = -atan2f(sinPhi, cosPhi);
-  const uint2 tr = __ldg(terms + item);
-  float pot = 0.0f, coeff = 0.0f;
-  for (uint32_t t = tr.x; t < tr.x + tr.y; ++t) {
-    const float4 tp = __ldg(term_prm + t);  // k0, phi0, per, harmonic
-    if (tp.w == 0.0f) {                     // AMBER, forces.py:565-569
-      float sn, cs;
-      sincosf(fmaf(tp.z, phi, -tp.y), &sn, &cs);
-      pot += tp.x * (1.0f + cs);
-      coeff -= tp.z * tp.x * sn;
-    } else {                                // CHARMM harmonic, forces.py:570-576
-      float ad = phi - tp.y;
-      const float pi_f = 3.14159265358979323846f;
-      if (ad < -pi_f) ad += 2.0f * pi_f; else if (ad > pi_f) ad -= 2.0f * pi_f;
-      pot += tp.x * ad * ad;
-      coeff += 2.0f * tp.x * ad;
+  float f0x = 0.f, f0y = 0.f, f0z = 0.f, f1x = 0.f, f1y = 0.f, f1z = 0.f, f2x = 0.f, f2y = 0.f, f2z = 0.f,
+        f3x = 0.f, f3y = 0.f, f3z = 0.f;
+  if (torsion_on) {
+    const f3 r12 = sub3(p0, p1), r23 = sub3(p1, p2), r34 = sub3(p2, p3);
+    const f3 cA = cross3(r12, r23), cB = cross3(r23, r34);
+    const float nA2 = dot3(cA, cA), nB2 = dot3(cB, cB), n23sq = dot3(r23, r23);
+    const float rnA = rsqrtf(nA2), rnB = rsqrtf(nB2), rn23 = rsqrtf(n23sq), n23 = n23sq * rn23;
+    // cosPhi = A.B / (|A||B|);  sinPhi = (C.B)/(|C||B|) with C = r23 x A  =>  |r23| (r12.B) / (|A||B|)
+    const float rab = rnA * rnB;
+    const float cosPhi = dot3(cA, cB) * rab, sinPhi = n23 * dot3(r12, cB) * rab;
+    const float hinv = rsqrtf(fmaf(cosPhi, cosPhi, sinPhi * sinPhi));
+    const float c = cosPhi * hinv, s = -sinPhi * hinv;  // cos / sin of phi = -atan2(sinPhi, cosPhi)
+    const uint2 tr = __ldg(terms + item);
+    float pot = 0.0f, coeff = 0.0f;
+    for (uint32_t t = tr.x; t < tr.x + tr.y; ++t) {
+      const float4 tp = __ldg(term_prm + t);  // k0, per | marker, c0, s0
+      if (tp.y > 0.0f) {                      // AMBER, integer periodicity (forces.py:565-569)
+        float cn = c, sn = s;
+        for (float k = 1.5f; k < tp.y; k += 1.0f) {
+          const float t0 = fmaf(cn, c, -sn * s);
+          sn = fmaf(cn, s, sn * c);
+          cn = t0;
+        }
+        pot += tp.x * (1.0f + fmaf(cn, tp.z, sn * tp.w));      // k (1 + cos(n phi - phi0))
+        coeff -= tp.y * tp.x * fmaf(sn, tp.z, -cn * tp.w);     // -n k sin(n phi - phi0)
+      } else {
+        const float phi = atan2f(s, c);
+        if (tp.y == kTermHarmonic) {          // CHARMM harmonic (forces.py:570-576)
+          float ad = phi - tp.z;
+          const float pi_f = 3.14159265358979323846f;
+          if (ad < -pi_f) ad += 2.0f * pi_f; else if (ad > pi_f) ad -= 2.0f * pi_f;
+          pot += tp.x * ad * ad;
+          coeff += 2.0f * tp.x * ad;
+        } else {                              // AMBER with a non-integer periodicity: general path
+          float sn, cs;
+          sincosf(fmaf(tp.w, phi, -tp.z), &sn, &cs);
+          pot += tp.x * (1.0f + cs);
+          coeff -= tp.w * tp.x * sn;
+        }
+      }
+    }
+    if (ENERGY) Eacc += (double)pot;
+    // OpenMM-style projection (forces.py:582-600)
+    const float ff0 = -coeff * n23 * (rnA * rnA), ff3 = coeff * n23 * (rnB * rnB);
+    const float rn23sq = rn23 * rn23;
+    const float ff1 = dot3(r12, r23) * rn23sq, ff2 = dot3(r34, r23) * rn23sq;
+    const float ax = ff0 * cA.x, ay = ff0 * cA.y, az = ff0 * cA.z;
+    const float bx = ff3 * cB.x, by = ff3 * cB.y, bz = ff3 * cB.z;
+    const float sx = fmaf(ff1, ax, -ff2 * bx), sy = fmaf(ff1, ay, -ff2 * by), sz = fmaf(ff1, az, -ff2 * bz);
+    f0x = -ax; f0y = -ay; f0z = -az;
+    f1x = ax + sx; f1y = ay + sy; f1z = az + sz;
+    f2x = bx - sx; f2y = by - sy; f2z = bz - sz;
+    f3x = -bx; f3y = -by; f3z = -bz;
+  }
+  if (fuse14) {
+    const float4 prm = __ldg(p14 + item);
+    if (prm.w != 0.0f) {
+      const f3 d = sub3(p0, p3);
+      const float sc = pair14<ENERGY>(d, prm, P, E);
+      f0x = fmaf(sc, d.x, f0x); f0y = fmaf(sc, d.y, f0y); f0z = fmaf(sc, d.z, f0z);
+      f3x = fmaf(-sc, d.x, f3x); f3y = fmaf(-sc, d.y, f3y); f3z = fmaf(-sc, d.z, f3z);
     }
   }
-  if (ENERGY) Eacc += (double)pot;
-  const float nd2sq = dot3(r23, r23), nd2 = sqrtf(nd2sq), inv_nd2sq = 1.0f / nd2sq;
-  const float ff0 = -coeff * nd2 / nA2, ff3 = coeff * nd2 / nB2;
-  const float ff1 = dot3(r12, r23) * inv_nd2sq, ff2 = dot3(r34, r23) * inv_nd2sq;
-  const f3 f0 = {ff0 * cA.x, ff0 * cA.y, ff0 * cA.z}, f3v = {ff3 * cB.x, ff3 * cB.y, ff3 * cB.z};
-  const f3 s = {ff1 * f0.x - ff2 * f3v.x, ff1 * f0.y - ff2 * f3v.y, ff1 * f0.z - ff2 * f3v.z};
-  put_slot(S, T, type, 0, item, -f0.x, -f0.y, -f0.z);
-  put_slot(S, T, type, 1, item, f0.x + s.x, f0.y + s.y, f0.z + s.z);
-  put_slot(S, T, type, 2, item, f3v.x - s.x, f3v.y - s.y, f3v.z - s.z);
-  put_slot(S, T, type, 3, item, -f3v.x, -f3v.y, -f3v.z);
+  put(S, sl.x & 0xffff, f0x, f0y, f0z);
+  put(S, sl.x >> 16, f1x, f1y, f1z);
+  put(S, sl.y & 0xffff, f2x, f2y, f2z);
+  put(S, sl.y >> 16, f3x, f3y, f3z);
 }
 
-// 1-4 pairs, forces.py:176-226: own A/B scaled by scnb, Coulomb scaled by scee; never cut/switched.
+// 1-4 pairs that no dihedral item owns (only possible with hand-made parameter objects)
 template <bool ENERGY>
 __device__ __forceinline__ void p14_task(const Smem& S, const DevTopo& T, const ForceParams& P, int item, Energies& E) {
   if (item >= T.n14) return;
-  const uint32_t q = __ldg(T.p14_idx + item);
+  const uint32_t q = __ldg(T.p14_idx + item), sl = __ldg(T.p14_slot + item);
   const float4 prm = __ldg(T.p14_prm + item);
-  const float4 pa = S.pos[q & 0xff], pb = S.pos[(q >> 8) & 0xff];
-  const f3 d = sub3(pa, pb);
-  const float rinv = rsqrt_nr(dot3(d, d));
-  const float r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
-  const float a = prm.x * P.lj_on, b = prm.y * P.lj_on, qq = prm.z * P.el_on;
-  const float u = a * r6, t1 = u - b;
-  const float elj = t1 * r6, ec = qq * rinv;
-  const float sc = (6.0f * ((u + t1) * r6) + ec) * r2inv;
-  put_slot(S, T, TASK_P14, 0, item, sc * d.x, sc * d.y, sc * d.z);
-  put_slot(S, T, TASK_P14, 1, item, -sc * d.x, -sc * d.y, -sc * d.z);
-  if (ENERGY) { E.e[B200MD_E_LJ] += (double)elj; E.e[B200MD_E_ELECTROSTATICS] += (double)ec; }
+  const f3 d = sub3(S.pos[q & 0xff], S.pos[(q >> 8) & 0xff]);
+  const float sc = pair14<ENERGY>(d, prm, P, E);
+  put(S, sl & 0xffff, sc * d.x, sc * d.y, sc * d.z);
+  put(S, sl >> 16, -sc * d.x, -sc * d.y, -sc * d.z);
 }
 
 // ---- all tasks of this warp for one force evaluation; positions must be in S.pos ------------------
@@ -258,6 +305,7 @@ __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const
 #pragma unroll
   for (int p = 0; p < 4; ++p) fi[p][0] = fi[p][1] = fi[p][2] = 0.0f;
   const int nt = T.ntasks[warp];
+#pragma unroll 1
   for (int t = 0; t < nt; ++t) {
     const uint32_t task = S.tasks[warp * kMaxTasks + t];
     const uint32_t kind = task & 0xff, chunk = (task >> 8) & 0xffff, passes = task >> 24;
@@ -267,10 +315,12 @@ __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const
       case TASK_BOND: bond_task<ENERGY>(S, T, P, item, E); break;
       case TASK_ANGLE: angle_task<ENERGY>(S, T, item, E); break;
       case TASK_DIHEDRAL:
-        torsion_task<ENERGY>(S, T, TASK_DIHEDRAL, item, T.ndih, T.dih_idx, T.dih_terms, T.dih_term_prm, E.e[B200MD_E_DIHEDRALS]);
+        torsion_task<ENERGY>(S, P, T.dih_on != 0, T.p14_on != 0, item, T.ndih, T.dih_idx, T.dih_terms, T.dih_term_prm,
+                             T.dih_slot, T.dih_p14, E.e[B200MD_E_DIHEDRALS], E);
         break;
       case TASK_IMPROPER:
-        torsion_task<ENERGY>(S, T, TASK_IMPROPER, item, T.nimp, T.imp_idx, T.imp_terms, T.imp_term_prm, E.e[B200MD_E_IMPROPERS]);
+        torsion_task<ENERGY>(S, P, true, false, item, T.nimp, T.imp_idx, T.imp_terms, T.imp_term_prm, T.imp_slot,
+                             nullptr, E.e[B200MD_E_IMPROPERS], E);
         break;
       case TASK_P14: p14_task<ENERGY>(S, T, P, item, E); break;
       default: break;
@@ -284,19 +334,20 @@ __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const
 
 // ---- SMD end-to-end bias (potcalc.py:75-89; force = -dE/dr): one lane, during the task phase -------
 __device__ __forceinline__ void smd_task(const Smem& S, const ForceParams& P, float center) {
+  // one lane per replica: FP64 throughout, (c - d)^2 cancels when the restraint is nearly satisfied
   const float4 p1 = S.pos[P.smd_a1], p2 = S.pos[P.smd_a2];
-  const f3 d = sub3(p2, p1);
-  const float r2 = dot3(d, d), rinv = rsqrt_nr(r2), dist = r2 * rinv;
-  const float dev = center - dist;
-  const float c = P.smd_fk * dev * rinv;  // force on atom2 = +fk (c - d) unit(r2 - r1)
-  S.smd[0] = c * d.x; S.smd[1] = c * d.y; S.smd[2] = c * d.z;
-  S.smd[3] = 0.5f * P.smd_fk * dev * dev;
-  S.smd[4] = dist;
+  const double dx = (double)p2.x - (double)p1.x, dy = (double)p2.y - (double)p1.y, dz = (double)p2.z - (double)p1.z;
+  const double dist = sqrt(dx * dx + dy * dy + dz * dz);
+  const double dev = (double)center - dist;
+  const double c = (double)P.smd_fk * dev / dist;  // force on atom2 = +fk (c - d) unit(r2 - r1)
+  S.smd[0] = (float)(c * dx); S.smd[1] = (float)(c * dy); S.smd[2] = (float)(c * dz);
+  S.smd[4] = (float)dist;
+  S.smd_energy[0] = 0.5 * (double)P.smd_fk * dev * dev;
 }
 
-// ---- per-atom gather in a fixed order: 4 i-side partials, the j-side slot, bonded slots, SMD --------
-__device__ __forceinline__ void gather_forces(const Smem& S, const DevTopo& T, const ForceParams& P, int a,
-                                              float& fx, float& fy, float& fz) {
+// ---- per-atom gather in a fixed order: j-side slot, 4 i-side partials, bonded slots, SMD ------------
+__device__ __forceinline__ void gather_forces(const Smem& S, const ForceParams& P, int a, float& fx, float& fy,
+                                              float& fz) {
   fx = S.fj[a]; fy = S.fj[kMaxAtoms + a]; fz = S.fj[2 * kMaxAtoms + a];
 #pragma unroll
   for (int w = 0; w < kWarps; ++w) {
@@ -304,10 +355,11 @@ __device__ __forceinline__ void gather_forces(const Smem& S, const DevTopo& T, c
     fy += S.fi[(w * 3 + 1) * kMaxAtoms + a];
     fz += S.fi[(w * 3 + 2) * kMaxAtoms + a];
   }
-  const int g0 = S.gstart[a], g1 = S.gstart[a + 1];
-  for (int g = g0; g < g1; ++g) {
-    const int k = S.glist[g];
-    fx += S.fb[k]; fy += S.fb[T.nslots + k]; fz += S.fb[2 * T.nslots + k];
+  const int g1 = S.gstart[a + 1];
+#pragma unroll 4
+  for (int g = S.gstart[a]; g < g1; ++g) {
+    const float4 v = S.fb[g];
+    fx += v.x; fy += v.y; fz += v.z;
   }
   if (P.smd_on) {
     if (a == P.smd_a2) { fx += S.smd[0]; fy += S.smd[1]; fz += S.smd[2]; }

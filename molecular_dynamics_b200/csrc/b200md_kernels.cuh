@@ -31,6 +31,10 @@ __host__ __device__ inline uint32_t make_task(uint32_t kind, uint32_t chunk, uin
   return kind | (chunk << 8) | (passes << 24);
 }
 
+// torsion term modes (float4 term = k, per | marker, c0, s0)
+constexpr float kTermHarmonic = -1.0f;  // CHARMM harmonic branch (forces.py:570-576): c0 = phi0
+constexpr float kTermGeneral = -2.0f;   // AMBER branch with a non-integer periodicity: c0 = phi0, s0 = per
+
 // Device view of a packed topology.  All pointers point into one device allocation.
 struct DevTopo {
   int natoms, ntypes, nchunks;
@@ -39,17 +43,17 @@ struct DevTopo {
   const float* mass;        // [128]
   const int* ab_row_off;    // [128] byte offset of atom's LJ-table row
   const uint8_t* mask8;     // [kMaxChunks][128] bit s: pair (i, 8*chunk+s) is NOT evaluated
-  int nbonds, nangles, ndih, nimp, n14;
-  const uint32_t* bond_idx;  const float2* bond_prm;
-  const uint32_t* angle_idx; const float2* angle_prm;
-  const uint32_t* dih_idx;   const uint2* dih_terms;  const float4* dih_term_prm;
-  const uint32_t* imp_idx;   const uint2* imp_terms;  const float4* imp_term_prm;
-  const uint32_t* p14_idx;   const float4* p14_prm;   // A/scnb, B/scnb, K qi qj/scee, 0
-  // bonded force slots: slot(type, pos, item) = base[type] + pos * pad[type] + item
-  int slot_base[6], slot_pad[6], nslots;
-  const uint16_t* gather_start;  // [129]
-  const uint16_t* gather_list;   // [gather_total] slot ids, per atom, fixed order
-  int gather_total;
+  int nbonds, nangles, ndih, nimp, n14;   // n14: 1-4 pairs NOT fused into a dihedral item ("orphans")
+  int dih_on, p14_on;                     // proper-torsion part / fused 1-4 part of the dihedral items
+  // every bonded item carries the slot ids (atom-major float4 slots) its force vectors go to
+  const uint32_t* bond_idx;  const float2* bond_prm;  const uint32_t* bond_slot;   // s0 | s1 << 16
+  const uint32_t* angle_idx; const float2* angle_prm; const uint2* angle_slot;     // s0 | s1 << 16, s2
+  const uint32_t* dih_idx;   const uint2* dih_terms;  const float4* dih_term_prm;  const uint2* dih_slot;
+  const float4* dih_p14;     // [ndih] A/scnb*12, B/scnb*6, K qi qj/scee, has14 (0/1): 1-4 pair on atoms 0,3
+  const uint32_t* imp_idx;   const uint2* imp_terms;  const float4* imp_term_prm;  const uint2* imp_slot;
+  const uint32_t* p14_idx;   const float4* p14_prm;   const uint32_t* p14_slot;    // orphans only
+  int nslots;
+  const uint16_t* gather_start;  // [129]: slots of atom a are [gather_start[a], gather_start[a+1])
   const uint32_t* tasks;  // [kWarps][kMaxTasks]
   int ntasks[kWarps];
   int smem_bytes;
@@ -81,17 +85,17 @@ struct Smem {
   uint8_t* mask8;     // [kMaxChunks*128]
   float* fi;          // [kWarps][3][128]
   float* fj;          // [3][128]
-  float* fb;          // [3][nslots]
+  float4* fb;         // [nslots] atom-major bonded force slots
   uint16_t* gstart;   // [130]
-  uint16_t* glist;    // [gather_total]
   uint32_t* tasks;    // [kWarps*kMaxTasks]
   double* ered;       // [kWarps][10]
-  float* smd;         // [8]: force on atom2 (xyz), energy, distance
+  float* smd;         // [8]: force on atom2 (xyz), -, distance
+  double* smd_energy; // [1]
 };
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
-__host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, int nslots, int gather_total) {
+__host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, int nslots) {
   size_t o = 0;
   auto take = [&](size_t bytes) { size_t r = o; o = align16(o + bytes); return base + r; };
   char* p;
@@ -101,12 +105,12 @@ __host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, i
   p = take(kMaxChunks * kMaxAtoms);                     if (s) s->mask8 = (uint8_t*)p;
   p = take(sizeof(float) * kWarps * 3 * kMaxAtoms);     if (s) s->fi = (float*)p;
   p = take(sizeof(float) * 3 * kMaxAtoms);              if (s) s->fj = (float*)p;
-  p = take(sizeof(float) * 3 * (size_t)(nslots > 0 ? nslots : 1)); if (s) s->fb = (float*)p;
+  p = take(sizeof(float4) * (size_t)(nslots > 0 ? nslots : 1)); if (s) s->fb = (float4*)p;
   p = take(sizeof(uint16_t) * (kMaxAtoms + 2));         if (s) s->gstart = (uint16_t*)p;
-  p = take(sizeof(uint16_t) * (size_t)(gather_total > 0 ? gather_total : 1)); if (s) s->glist = (uint16_t*)p;
   p = take(sizeof(uint32_t) * kWarps * kMaxTasks);      if (s) s->tasks = (uint32_t*)p;
   p = take(sizeof(double) * kWarps * 10);               if (s) s->ered = (double*)p;
   p = take(sizeof(float) * 8);                          if (s) s->smd = (float*)p;
+  p = take(sizeof(double) * 2);                         if (s) s->smd_energy = (double*)p;
   return o;
 }
 
