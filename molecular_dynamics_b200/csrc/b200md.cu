@@ -29,6 +29,7 @@ __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, co
   }
   for (int k = tid; k < kMaxAtoms; k += kThreads) {
     S.ab_row_off[k] = __ldg(T.ab_row_off + k);
+    S.rotmask[k] = __ldg(T.rotmask + k);
     S.pos[k] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   for (int k = tid; k < kMaxChunks * kMaxAtoms / 4; k += kThreads)
@@ -37,7 +38,7 @@ __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, co
   for (int k = tid; k < kWarps * kMaxTasks; k += kThreads) S.tasks[k] = __ldg(T.tasks + k);
   if (tid < 8) S.smd[tid] = 0.0f;
   // slots of disabled / dropped terms are never written: keep them at zero for the gather
-  for (int k = tid; k < T.nslots; k += kThreads) S.fb[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int k = tid; k < 3 * T.nslots; k += kThreads) S.fb[k] = 0.0f;
   // chunks without a tile task (no non-bonded term enabled) must read as zero in the gather
   for (int k = tid; k < 3 * kMaxAtoms; k += kThreads) S.fj[k] = 0.0f;
 }
@@ -331,6 +332,21 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
       mask8[(size_t)c * kMaxAtoms + i] = m;
     }
 
+  // rotation masks of the diagonal blocks (tile_diag_task): block b holds n_b atoms, steps t = 1..n_b/2
+  std::vector<uint32_t> rotmask(kMaxAtoms, 0xffffffffu);
+  for (int b = 0; b * 32 < N; ++b) {
+    const int n = std::min(32, N - 32 * b), nsteps = n / 2;
+    for (int l = 0; l < n; ++l) {
+      uint32_t m = 0xffffffffu;
+      for (int t = 1; t <= nsteps; ++t) {
+        if (2 * t == n && l >= n / 2) continue;  // second visit of the same pair
+        const int i = 32 * b + l, j = 32 * b + (l + t) % n;
+        if (allowed[(size_t)std::min(i, j) * kMaxAtoms + std::max(i, j)]) m &= ~(1u << (t - 1));
+      }
+      rotmask[32 * b + l] = m;
+    }
+  }
+
   // ---- per-atom tables ---------------------------------------------------------------------------
   std::vector<float2> ab((size_t)NT * kAbStride, make_float2(0.f, 0.f));
   for (int t = 0; t < NT; ++t)
@@ -432,11 +448,16 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   struct Task { uint32_t word; int cost; };
   std::vector<Task> all;
   const int nblocks = (N + 31) / 32;
-  if (d->npairs > 0)
-    for (int c = 0; c < T.nchunks; ++c) {
-      const int passes = std::min(nblocks, (c * kChunk + kChunk - 1) / 32 + 1);
-      all.push_back({make_task(TASK_TILE, c, passes), passes * kChunk * 24 + 110});
+  if (d->npairs > 0) {
+    for (int c = 4; c < T.nchunks; ++c) {  // off-diagonal: chunk of block J against the full blocks 0..J-1
+      const int passes = c / 4;
+      all.push_back({make_task(TASK_TILE, c, passes), passes * (kChunk * 24 + 30) + 110});
     }
+    for (int b = 0; b < nblocks; ++b) {  // diagonal blocks by rotation
+      const int n = std::min(32, N - 32 * b), nsteps = n / 2;
+      if (nsteps > 0) all.push_back({make_task(TASK_DIAG, (uint32_t)b | ((uint32_t)n << 8), nsteps), nsteps * 36 + 40});
+    }
+  }
   const int chunk_cost[6] = {0, 50, 110, 230, 200, 45};
   for (int ty = 1; ty < 6; ++ty)
     for (int c = 0; c < (counts[ty] + 31) / 32; ++c) all.push_back({make_task(ty, c, 0), chunk_cost[ty]});
@@ -454,7 +475,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
 
   // ---- upload --------------------------------------------------------------------------------------
   BlobBuilder B;
-  const size_t o_ab = B.add(ab), o_q = B.add(charge), o_m = B.add(mass), o_ro = B.add(rowoff), o_mask = B.add(mask8);
+  const size_t o_ab = B.add(ab), o_q = B.add(charge), o_m = B.add(mass), o_ro = B.add(rowoff), o_mask = B.add(mask8), o_rot = B.add(rotmask);
   const size_t o_bi = B.add(bond_idx), o_bp = B.add(bond_prm), o_bs = B.add(bond_slot);
   const size_t o_ai = B.add(angle_idx), o_ap = B.add(angle_prm), o_as = B.add(angle_slot);
   const size_t o_di = B.add(dih_idx), o_dt = B.add(dih_terms), o_dp = B.add(dih_tp), o_ds = B.add(dih_slot), o_d14 = B.add(dih_p14);
@@ -470,7 +491,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   if (e != cudaSuccess) { cleanup(std::string("cudaMemcpy: ") + cudaGetErrorString(e)); return nullptr; }
   char* base = (char*)topo->blob;
   T.ab = (const float2*)(base + o_ab); T.charge = (const float*)(base + o_q); T.mass = (const float*)(base + o_m);
-  T.ab_row_off = (const int*)(base + o_ro); T.mask8 = (const uint8_t*)(base + o_mask);
+  T.ab_row_off = (const int*)(base + o_ro); T.mask8 = (const uint8_t*)(base + o_mask); T.rotmask = (const uint32_t*)(base + o_rot);
   T.bond_idx = (const uint32_t*)(base + o_bi); T.bond_prm = (const float2*)(base + o_bp); T.bond_slot = (const uint32_t*)(base + o_bs);
   T.angle_idx = (const uint32_t*)(base + o_ai); T.angle_prm = (const float2*)(base + o_ap); T.angle_slot = (const uint2*)(base + o_as);
   T.dih_idx = (const uint32_t*)(base + o_di); T.dih_terms = (const uint2*)(base + o_dt); T.dih_term_prm = (const float4*)(base + o_dp);

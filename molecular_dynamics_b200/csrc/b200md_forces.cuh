@@ -132,9 +132,52 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
   }
 }
 
-// ---- bonded items: force vectors go to private atom-major float4 slots ------------------------------
+// ---- TASK_DIAG: all pairs inside one 32-atom block by rotation --------------------------------------
+// Lane l owns atom 32*block + l.  At step t = 1..floor(n/2) it evaluates the pair with partner
+// (l + t) mod n, keeps its own side in registers and hands the partner's side back with one shuffle per
+// component (the partner of lane l is served by lane (l - t) mod n).  Every unordered pair is visited
+// once: n(n-1)/2 pairs in ~n/2 steps, against 4 x 8 steps at < 50 % lane use for the staircase of
+// broadcast chunks.  rotmask bit (t-1) set <=> lane skips step t (exclusion, padding, or the duplicate
+// half of step n/2).
+template <int MODE, bool ENERGY>
+__device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams& P, int block, int n, int nsteps,
+                                               int lane, float (&fi)[4][3], Energies& E) {
+  const int i0 = block * 32;
+  const float4 pi = S.pos[i0 + lane];
+  const float kqi = __fmul_rn(pi.w, kElecFactor);
+  const char* row = (const char*)S.ab + S.ab_row_off[i0 + lane] + i0 * (int)sizeof(float2);
+  const uint32_t rot = S.rotmask[i0 + lane];
+  float pel = 0.0f, plj = 0.0f, ax = 0.0f, ay = 0.0f, az = 0.0f;
+#pragma unroll 1
+  for (int g = 0; g < nsteps; g += 4) {
+    const uint32_t m4 = rot >> g;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int t = g + u + 1;
+      int jl = lane + t, sl = lane - t;
+      jl = jl >= n ? jl - n : jl;
+      sl = sl < 0 ? sl + n : sl;
+      const float4 q = S.pos[i0 + jl];
+      const float2 ab = *(const float2*)(row + jl * (int)sizeof(float2));
+      const float dx = __fsub_rn(pi.x, q.x), dy = __fsub_rn(pi.y, q.y), dz = __fsub_rn(pi.z, q.z);
+      const float sc = pair_eval<MODE, ENERGY>(dx, dy, dz, kqi, q.w, ab, (m4 >> u) & 1u, P, pel, plj);
+      const float gx = __fmul_rn(sc, dx), gy = __fmul_rn(sc, dy), gz = __fmul_rn(sc, dz);
+      ax = __fadd_rn(ax, gx); ay = __fadd_rn(ay, gy); az = __fadd_rn(az, gz);
+      ax = __fsub_rn(ax, __shfl_sync(0xffffffffu, gx, sl));
+      ay = __fsub_rn(ay, __shfl_sync(0xffffffffu, gy, sl));
+      az = __fsub_rn(az, __shfl_sync(0xffffffffu, gz, sl));
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    if (block == k) { fi[k][0] = __fadd_rn(fi[k][0], ax); fi[k][1] = __fadd_rn(fi[k][1], ay); fi[k][2] = __fadd_rn(fi[k][2], az); }
+  if (ENERGY) { E.e[B200MD_E_ELECTROSTATICS] += (double)pel; E.e[B200MD_E_LJ] += (double)plj; }
+}
+
+// ---- bonded items: force vectors go to private atom-major 12-byte slots -----------------------------
 __device__ __forceinline__ void put(const Smem& S, uint32_t slot, float x, float y, float z) {
-  S.fb[slot] = make_float4(x, y, z, 0.0f);
+  float* p = S.fb + 3 * slot;
+  p[0] = x; p[1] = y; p[2] = z;
 }
 
 // evaluate_bonds, forces.py:111-132, 492-501
@@ -146,7 +189,7 @@ __device__ __forceinline__ void bond_task(const Smem& S, const DevTopo& T, const
   const float4 pa = S.pos[q & 0xff], pb = S.pos[(q >> 8) & 0xff];
   const f3 d = sub3(pa, pb);
   const float r2 = dot3(d, d);
-  const float rinv = rsqrtf(r2), dist = r2 * rinv;
+  const float rinv = fast_rsqrt(r2), dist = r2 * rinv;
   const bool keep = !P.has_cutoff || dist <= P.rc;  // forces.py:117-125
   const float x = dist - prm.y;
   const float c = keep ? 2.0f * prm.x * x * rinv : 0.0f;  // dE/dr / r
@@ -169,13 +212,13 @@ __device__ __forceinline__ void angle_task(const Smem& S, const DevTopo& T, int 
   const float2 prm = __ldg(T.angle_prm + item);
   const float4 p0 = S.pos[q & 0xff], p1 = S.pos[(q >> 8) & 0xff], p2 = S.pos[(q >> 16) & 0xff];
   const f3 r21 = sub3(p0, p1), r23 = sub3(p2, p1);
-  const float n21i = rsqrtf(dot3(r21, r21)), n23i = rsqrtf(dot3(r23, r23));
+  const float n21i = fast_rsqrt(dot3(r21, r21)), n23i = fast_rsqrt(dot3(r23, r23));
   float ct = dot3(r23, r21) * n21i * n23i;
   ct = fminf(fmaxf(ct, -1.0f), 1.0f);
   const float th = acosf(ct), dth = th - prm.y;
   if (ENERGY) E.e[B200MD_E_ANGLES] += (double)(prm.x * dth * dth);
   const float st2 = fmaf(-ct, ct, 1.0f);
-  const float coef = (st2 > 0.0f) ? -2.0f * prm.x * dth * rsqrtf(st2) : 0.0f;  // 0 where sin(theta) == 0
+  const float coef = (st2 > 0.0f) ? -2.0f * prm.x * dth * fast_rsqrt(st2) : 0.0f;  // 0 where sin(theta) == 0
   const float a0 = coef * n21i, a2 = coef * n23i;
   const float c21 = ct * n21i, c23 = ct * n23i;
   const float f0x = a0 * fmaf(c21, r21.x, -r23.x * n23i), f0y = a0 * fmaf(c21, r21.y, -r23.y * n23i),
@@ -222,11 +265,11 @@ __device__ __forceinline__ void torsion_task(const Smem& S, const ForceParams& P
     const f3 r12 = sub3(p0, p1), r23 = sub3(p1, p2), r34 = sub3(p2, p3);
     const f3 cA = cross3(r12, r23), cB = cross3(r23, r34);
     const float nA2 = dot3(cA, cA), nB2 = dot3(cB, cB), n23sq = dot3(r23, r23);
-    const float rnA = rsqrtf(nA2), rnB = rsqrtf(nB2), rn23 = rsqrtf(n23sq), n23 = n23sq * rn23;
+    const float rnA = fast_rsqrt(nA2), rnB = fast_rsqrt(nB2), rn23 = fast_rsqrt(n23sq), n23 = n23sq * rn23;
     // cosPhi = A.B / (|A||B|);  sinPhi = (C.B)/(|C||B|) with C = r23 x A  =>  |r23| (r12.B) / (|A||B|)
     const float rab = rnA * rnB;
     const float cosPhi = dot3(cA, cB) * rab, sinPhi = n23 * dot3(r12, cB) * rab;
-    const float hinv = rsqrtf(fmaf(cosPhi, cosPhi, sinPhi * sinPhi));
+    const float hinv = fast_rsqrt(fmaf(cosPhi, cosPhi, sinPhi * sinPhi));
     const float c = cosPhi * hinv, s = -sinPhi * hinv;  // cos / sin of phi = -atan2(sinPhi, cosPhi)
     const uint2 tr = __ldg(terms + item);
     float pot = 0.0f, coeff = 0.0f;
@@ -312,6 +355,7 @@ __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const
     const int item = chunk * 32 + lane;
     switch (kind) {
       case TASK_TILE: tile_task<MODE, ENERGY>(S, P, chunk, passes, lane, fi, E); break;
+      case TASK_DIAG: tile_diag_task<MODE, ENERGY>(S, P, chunk & 0xff, (chunk >> 8) & 0xff, passes, lane, fi, E); break;
       case TASK_BOND: bond_task<ENERGY>(S, T, P, item, E); break;
       case TASK_ANGLE: angle_task<ENERGY>(S, T, item, E); break;
       case TASK_DIHEDRAL:
@@ -358,8 +402,8 @@ __device__ __forceinline__ void gather_forces(const Smem& S, const ForceParams& 
   const int g1 = S.gstart[a + 1];
 #pragma unroll 4
   for (int g = S.gstart[a]; g < g1; ++g) {
-    const float4 v = S.fb[g];
-    fx += v.x; fy += v.y; fz += v.z;
+    const float* v = S.fb + 3 * g;
+    fx += v[0]; fy += v[1]; fz += v[2];
   }
   if (P.smd_on) {
     if (a == P.smd_a2) { fx += S.smd[0]; fy += S.smd[1]; fz += S.smd[2]; }

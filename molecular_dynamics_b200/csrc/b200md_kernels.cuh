@@ -26,7 +26,7 @@ constexpr float kElecFactor = 332.06371307417066f;  // forces.py:373-376
 constexpr float kBoltzman = 0.001987191f;           // upstream torchmd.integrator
 
 // task kinds (one task = one warp-wide unit of work, scheduled statically on the host)
-enum TaskKind : uint32_t { TASK_TILE = 0, TASK_BOND = 1, TASK_ANGLE = 2, TASK_DIHEDRAL = 3, TASK_IMPROPER = 4, TASK_P14 = 5 };
+enum TaskKind : uint32_t { TASK_TILE = 0, TASK_BOND = 1, TASK_ANGLE = 2, TASK_DIHEDRAL = 3, TASK_IMPROPER = 4, TASK_P14 = 5, TASK_DIAG = 6 };
 __host__ __device__ inline uint32_t make_task(uint32_t kind, uint32_t chunk, uint32_t passes) {
   return kind | (chunk << 8) | (passes << 24);
 }
@@ -43,6 +43,7 @@ struct DevTopo {
   const float* mass;        // [128]
   const int* ab_row_off;    // [128] byte offset of atom's LJ-table row
   const uint8_t* mask8;     // [kMaxChunks][128] bit s: pair (i, 8*chunk+s) is NOT evaluated
+  const uint32_t* rotmask;  // [128] bit t-1: lane skips rotation step t of its diagonal block
   int nbonds, nangles, ndih, nimp, n14;   // n14: 1-4 pairs NOT fused into a dihedral item ("orphans")
   int dih_on, p14_on;                     // proper-torsion part / fused 1-4 part of the dihedral items
   // every bonded item carries the slot ids (atom-major float4 slots) its force vectors go to
@@ -83,9 +84,10 @@ struct Smem {
   float2* ab;         // [ntypes*kAbStride]
   int* ab_row_off;    // [128]
   uint8_t* mask8;     // [kMaxChunks*128]
+  uint32_t* rotmask;  // [128]
   float* fi;          // [kWarps][3][128]
   float* fj;          // [3][128]
-  float4* fb;         // [nslots] atom-major bonded force slots
+  float* fb;          // [nslots][3] atom-major bonded force slots
   uint16_t* gstart;   // [130]
   uint32_t* tasks;    // [kWarps*kMaxTasks]
   double* ered;       // [kWarps][10]
@@ -103,9 +105,10 @@ __host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, i
   p = take(sizeof(float2) * (size_t)ntypes * kAbStride); if (s) s->ab = (float2*)p;
   p = take(sizeof(int) * kMaxAtoms);                    if (s) s->ab_row_off = (int*)p;
   p = take(kMaxChunks * kMaxAtoms);                     if (s) s->mask8 = (uint8_t*)p;
+  p = take(sizeof(uint32_t) * kMaxAtoms);               if (s) s->rotmask = (uint32_t*)p;
   p = take(sizeof(float) * kWarps * 3 * kMaxAtoms);     if (s) s->fi = (float*)p;
   p = take(sizeof(float) * 3 * kMaxAtoms);              if (s) s->fj = (float*)p;
-  p = take(sizeof(float4) * (size_t)(nslots > 0 ? nslots : 1)); if (s) s->fb = (float4*)p;
+  p = take(sizeof(float) * 3 * (size_t)(nslots > 0 ? nslots : 1)); if (s) s->fb = (float*)p;
   p = take(sizeof(uint16_t) * (kMaxAtoms + 2));         if (s) s->gstart = (uint16_t*)p;
   p = take(sizeof(uint32_t) * kWarps * kMaxTasks);      if (s) s->tasks = (uint32_t*)p;
   p = take(sizeof(double) * kWarps * 10);               if (s) s->ered = (double*)p;
