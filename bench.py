@@ -253,12 +253,12 @@ def run_ours(args):
     integ.check_nan = False
 
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
-    gathered = torch.empty((world, R, _cabi.NUM_OBSERVABLES), dtype=torch.float64, device=dev) if world > 1 else None
+    from molecular_dynamics_b200.sharding import gather_observables
 
     def one_step():
         integ.step(niter=S)
         if world > 1:  # reporting interval: all-gather the per-replica observables (the only collective)
-            dist.all_gather_into_tensor(gathered, integ.observables[-1].contiguous())
+            gather_observables(integ.observables[-1], world * R)
 
     def barrier():
         torch.cuda.synchronize()
