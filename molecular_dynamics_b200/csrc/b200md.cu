@@ -21,6 +21,7 @@ namespace b200md {
 
 // Stage the replica-independent tables into shared memory once per CTA (the CTA then loops over
 // replicas).  Term switches (forces.py:40-50) are applied here: "lj" off -> A = B = 0.
+template <bool FIXED>
 __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, const ForceParams& P, int tid) {
   const int nab = T.ntypes * kAbStride;
   for (int k = tid; k < nab; k += kThreads) {
@@ -38,7 +39,11 @@ __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, co
   for (int k = tid; k < kWarps * kMaxTasks; k += kThreads) S.tasks[k] = __ldg(T.tasks + k);
   if (tid < 8) S.smd[tid] = 0.0f;
   // slots of disabled / dropped terms are never written: keep them at zero for the gather
-  for (int k = tid; k < 3 * T.nslots; k += kThreads) S.fb[k] = 0.0f;
+  if (FIXED) {
+    for (int k = tid; k < 3 * kMaxAtoms; k += kThreads) S.fbi[k] = 0;
+  } else {
+    for (int k = tid; k < 3 * T.nslots; k += kThreads) S.fb[k] = 0.0f;
+  }
   // chunks without a tile task (no non-bonded term enabled) must read as zero in the gather
   for (int k = tid; k < 3 * kMaxAtoms; k += kThreads) S.fj[k] = 0.0f;
 }
@@ -51,10 +56,10 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
               uint32_t* __restrict__ status) {
   extern __shared__ __align__(16) char smem_raw[];
   Smem S;
-  smem_layout(&S, smem_raw, T.ntypes, T.nslots);
+  smem_layout(&S, smem_raw, T.ntypes, T.nslots, false);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int N = T.natoms;
-  stage_tables(S, T, P, tid);
+  stage_tables<false>(S, T, P, tid);
   const float q = tid < N ? __ldg(T.charge + tid) * P.el_on : 0.0f;
   for (long long r = blockIdx.x; r < R; r += gridDim.x) {
     __syncthreads();  // previous replica fully consumed (and tables staged)
@@ -73,12 +78,12 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
     if (flag && status != nullptr) atomicOr(status + r, flag);
     Energies E;
     E.clear();
-    run_tasks<MODE, true>(S, T, P, warp, lane, E);
+    run_tasks<MODE, true, false>(S, T, P, warp, lane, E, flag);
     if (P.smd_on && tid == kThreads - 1) smd_task(S, P, P.smd_centers ? __ldg(P.smd_centers + r) : P.smd_c0);
     __syncthreads();
     if (tid < N) {
       float fx, fy, fz;
-      gather_forces(S, P, tid, fx, fy, fz);
+      gather_forces<false>(S, P, tid, fx, fy, fz);
       float* f = forces + (r * N + tid) * 3;
       f[0] = fx; f[1] = fy; f[2] = fz;
     }
@@ -101,10 +106,10 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
                  double* __restrict__ observables, float* __restrict__ snapshots, uint32_t* __restrict__ status) {
   extern __shared__ __align__(16) char smem_raw[];
   Smem S;
-  smem_layout(&S, smem_raw, T.ntypes, T.nslots);
+  smem_layout(&S, smem_raw, T.ntypes, T.nslots, true);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int N = T.natoms;
-  stage_tables(S, T, P, tid);
+  stage_tables<true>(S, T, P, tid);
   const bool live = tid < N;
   const float q = live ? __ldg(T.charge + tid) * P.el_on : 0.0f;
   const float mass = live ? __ldg(T.mass + tid) : 1.0f;
@@ -137,13 +142,13 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       Energies E;
       if (report) {
         E.clear();
-        run_tasks<MODE, true>(S, T, P, warp, lane, E);
+        run_tasks<MODE, true, true>(S, T, P, warp, lane, E, flag);
       } else {
-        run_tasks<MODE, false>(S, T, P, warp, lane, E);
+        run_tasks<MODE, false, true>(S, T, P, warp, lane, E, flag);
       }
       if (P.smd_on && tid == kThreads - 1) smd_task(S, P, (float)((double)P.smd_c0 + (double)P.smd_rate * (double)(gstep + 1)));
       __syncthreads();
-      if (live) gather_forces(S, P, tid, fx, fy, fz);
+      if (live) gather_forces<true>(S, P, tid, fx, fy, fz);
       if (langevin) {  // vel += -gamma vel dt + vcoeff N(0,1)
         float n[3];
         normal3(I.seed, (unsigned long long)(I.replica0 + r), (uint32_t)tid, gstep, n);
@@ -501,15 +506,16 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   T.p14_idx = (const uint32_t*)(base + o_pi); T.p14_prm = (const float4*)(base + o_pp); T.p14_slot = (const uint32_t*)(base + o_ps);
   T.gather_start = (const uint16_t*)(base + o_gs);
   T.tasks = (const uint32_t*)(base + o_tk);
-  T.smem_bytes = (int)smem_layout(nullptr, nullptr, NT, nslots);
+  T.smem_bytes = (int)smem_layout(nullptr, nullptr, NT, nslots, false);
+  T.smem_bytes_fixed = (int)smem_layout(nullptr, nullptr, NT, nslots, true);
   if (T.smem_bytes > 227 * 1024) { cleanup("topology needs more than 227 KB of shared memory per CTA"); g_last_error = "too much shared memory"; return nullptr; }
   cudaDeviceProp prop;
   cudaGetDeviceProperties(&prop, device);
   topo->num_sms = prop.multiProcessorCount;
   topo->occ_forces[0] = query_occupancy(forces_kernel<0>, T.smem_bytes);
   topo->occ_forces[1] = query_occupancy(forces_kernel<1>, T.smem_bytes);
-  topo->occ_integrate[0] = query_occupancy(integrate_kernel<0>, T.smem_bytes);
-  topo->occ_integrate[1] = query_occupancy(integrate_kernel<1>, T.smem_bytes);
+  topo->occ_integrate[0] = query_occupancy(integrate_kernel<0>, T.smem_bytes_fixed);
+  topo->occ_integrate[1] = query_occupancy(integrate_kernel<1>, T.smem_bytes_fixed);
   if (topo->occ_forces[0] < 1 || topo->occ_integrate[0] < 1) { cleanup("kernel does not fit on an SM"); return nullptr; }
   g_last_error.clear();
   return topo;
@@ -623,9 +629,9 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
   const int grid = (int)std::min<long long>(R, cap);
   cudaStream_t st = (cudaStream_t)stream;
   if (mode == 0)
-    integrate_kernel<0><<<grid, kThreads, T.smem_bytes, st>>>(T, P, I, R, pos, vel, forces, box, observables, snapshots, status);
+    integrate_kernel<0><<<grid, kThreads, T.smem_bytes_fixed, st>>>(T, P, I, R, pos, vel, forces, box, observables, snapshots, status);
   else
-    integrate_kernel<1><<<grid, kThreads, T.smem_bytes, st>>>(T, P, I, R, pos, vel, forces, box, observables, snapshots, status);
+    integrate_kernel<1><<<grid, kThreads, T.smem_bytes_fixed, st>>>(T, P, I, R, pos, vel, forces, box, observables, snapshots, status);
   g_launches.fetch_add(1);
   CUDA_TRY(cudaGetLastError());
   return B200MD_OK;

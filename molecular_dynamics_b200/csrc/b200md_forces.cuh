@@ -174,17 +174,35 @@ __device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams&
   if (ENERGY) { E.e[B200MD_E_ELECTROSTATICS] += (double)pel; E.e[B200MD_E_LJ] += (double)plj; }
 }
 
-// ---- bonded items: force vectors go to private atom-major 12-byte slots -----------------------------
-__device__ __forceinline__ void put(const Smem& S, uint32_t slot, float x, float y, float z) {
-  float* p = S.fb + 3 * slot;
-  p[0] = x; p[1] = y; p[2] = z;
+// ---- bonded items: where a force vector goes ---------------------------------------------------------
+// FIXED = false (single-shot Forces.compute): private atom-major 12-byte slots, summed per atom in a fixed
+//   order after the barrier -- exact fp32 sums for arbitrarily large forces (generated / clashing frames).
+// FIXED = true (fused integrator): 2^-17 kcal/mol/A fixed point, one shared-memory integer atomic per
+//   component.  Integer addition is associative, so the sum is still order-independent and bit-reproducible,
+//   and the slot buffer, its stores and the gather loop disappear.  A contribution above kFixedLimit raises the
+//   per-replica range flag (the run has exploded long before 16 384 kcal/mol/A are reached on one atom).
+constexpr float kFixedScale = 131072.0f, kFixedInv = 1.0f / 131072.0f, kFixedLimit = 2048.0f;
+
+template <bool FIXED>
+__device__ __forceinline__ void emit(const Smem& S, uint32_t slot, uint32_t atom, float x, float y, float z,
+                                     uint32_t& flag) {
+  if (FIXED) {
+    if (fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z))) > kFixedLimit) flag |= B200MD_FLAG_FORCE_RANGE;
+    atomicAdd(S.fbi + atom, __float2int_rn(x * kFixedScale));
+    atomicAdd(S.fbi + kMaxAtoms + atom, __float2int_rn(y * kFixedScale));
+    atomicAdd(S.fbi + 2 * kMaxAtoms + atom, __float2int_rn(z * kFixedScale));
+  } else {
+    float* p = S.fb + 3 * slot;
+    p[0] = x; p[1] = y; p[2] = z;
+  }
 }
 
 // evaluate_bonds, forces.py:111-132, 492-501
-template <bool ENERGY>
-__device__ __forceinline__ void bond_task(const Smem& S, const DevTopo& T, const ForceParams& P, int item, Energies& E) {
+template <bool ENERGY, bool FIXED>
+__device__ __forceinline__ void bond_task(const Smem& S, const DevTopo& T, const ForceParams& P, int item, Energies& E,
+                                          uint32_t& flag) {
   if (item >= T.nbonds) return;
-  const uint32_t q = __ldg(T.bond_idx + item), sl = __ldg(T.bond_slot + item);
+  const uint32_t q = __ldg(T.bond_idx + item), sl = FIXED ? 0u : __ldg(T.bond_slot + item);
   const float2 prm = __ldg(T.bond_prm + item);
   const float4 pa = S.pos[q & 0xff], pb = S.pos[(q >> 8) & 0xff];
   const f3 d = sub3(pa, pb);
@@ -193,8 +211,8 @@ __device__ __forceinline__ void bond_task(const Smem& S, const DevTopo& T, const
   const bool keep = !P.has_cutoff || dist <= P.rc;  // forces.py:117-125
   const float x = dist - prm.y;
   const float c = keep ? 2.0f * prm.x * x * rinv : 0.0f;  // dE/dr / r
-  put(S, sl & 0xffff, -c * d.x, -c * d.y, -c * d.z);
-  put(S, sl >> 16, c * d.x, c * d.y, c * d.z);
+  emit<FIXED>(S, sl & 0xffff, q & 0xff, -c * d.x, -c * d.y, -c * d.z, flag);
+  emit<FIXED>(S, sl >> 16, (q >> 8) & 0xff, c * d.x, c * d.y, c * d.z, flag);
   if (ENERGY && keep) {
     // k (r - r0)^2 cancels ~40:1 in (r - r0): the energy (report steps only) takes r in FP64
     const double ddx = (double)pa.x - (double)pb.x, ddy = (double)pa.y - (double)pb.y, ddz = (double)pa.z - (double)pb.z;
@@ -204,11 +222,11 @@ __device__ __forceinline__ void bond_task(const Smem& S, const DevTopo& T, const
 }
 
 // evaluate_angles, forces.py:134-145, 504-537
-template <bool ENERGY>
-__device__ __forceinline__ void angle_task(const Smem& S, const DevTopo& T, int item, Energies& E) {
+template <bool ENERGY, bool FIXED>
+__device__ __forceinline__ void angle_task(const Smem& S, const DevTopo& T, int item, Energies& E, uint32_t& flag) {
   if (item >= T.nangles) return;
   const uint32_t q = __ldg(T.angle_idx + item);
-  const uint2 sl = __ldg(T.angle_slot + item);
+  const uint2 sl = FIXED ? make_uint2(0u, 0u) : __ldg(T.angle_slot + item);
   const float2 prm = __ldg(T.angle_prm + item);
   const float4 p0 = S.pos[q & 0xff], p1 = S.pos[(q >> 8) & 0xff], p2 = S.pos[(q >> 16) & 0xff];
   const f3 r21 = sub3(p0, p1), r23 = sub3(p2, p1);
@@ -225,9 +243,9 @@ __device__ __forceinline__ void angle_task(const Smem& S, const DevTopo& T, int 
               f0z = a0 * fmaf(c21, r21.z, -r23.z * n23i);
   const float f2x = a2 * fmaf(c23, r23.x, -r21.x * n21i), f2y = a2 * fmaf(c23, r23.y, -r21.y * n21i),
               f2z = a2 * fmaf(c23, r23.z, -r21.z * n21i);
-  put(S, sl.x & 0xffff, f0x, f0y, f0z);
-  put(S, sl.x >> 16, -(f0x + f2x), -(f0y + f2y), -(f0z + f2z));
-  put(S, sl.y & 0xffff, f2x, f2y, f2z);
+  emit<FIXED>(S, sl.x & 0xffff, q & 0xff, f0x, f0y, f0z, flag);
+  emit<FIXED>(S, sl.x >> 16, (q >> 8) & 0xff, -(f0x + f2x), -(f0y + f2y), -(f0z + f2z), flag);
+  emit<FIXED>(S, sl.y & 0xffff, (q >> 16) & 0xff, f2x, f2y, f2z, flag);
 }
 
 // One LJ + Coulomb pair with its own (12 A', 6 B', K qi qj') parameters: forces.py:176-226 (1-4 pairs are
@@ -250,14 +268,14 @@ __device__ __forceinline__ float pair14(f3 d, float4 prm, const ForceParams& P, 
 // 1-4 pair on the end atoms (forces.py:176-226) fused into the dihedral item that owns it.
 // phi = -atan2(sinPhi, cosPhi) is never formed for AMBER terms with integer periodicity: cos/sin(n phi)
 // come from (cos phi + i sin phi)^n and the phase enters through its precomputed cosine / sine.
-template <bool ENERGY>
+template <bool ENERGY, bool FIXED>
 __device__ __forceinline__ void torsion_task(const Smem& S, const ForceParams& P, bool torsion_on, bool fuse14,
                                              int item, int count, const uint32_t* idx, const uint2* terms,
                                              const float4* term_prm, const uint2* slots, const float4* p14,
-                                             double& Eacc, Energies& E) {
+                                             double& Eacc, Energies& E, uint32_t& flag) {
   if (item >= count) return;
   const uint32_t q = __ldg(idx + item);
-  const uint2 sl = __ldg(slots + item);
+  const uint2 sl = FIXED ? make_uint2(0u, 0u) : __ldg(slots + item);
   const float4 p0 = S.pos[q & 0xff], p1 = S.pos[(q >> 8) & 0xff], p2 = S.pos[(q >> 16) & 0xff], p3 = S.pos[q >> 24];
   float f0x = 0.f, f0y = 0.f, f0z = 0.f, f1x = 0.f, f1y = 0.f, f1z = 0.f, f2x = 0.f, f2y = 0.f, f2z = 0.f,
         f3x = 0.f, f3y = 0.f, f3z = 0.f;
@@ -322,28 +340,29 @@ __device__ __forceinline__ void torsion_task(const Smem& S, const ForceParams& P
       f3x = fmaf(-sc, d.x, f3x); f3y = fmaf(-sc, d.y, f3y); f3z = fmaf(-sc, d.z, f3z);
     }
   }
-  put(S, sl.x & 0xffff, f0x, f0y, f0z);
-  put(S, sl.x >> 16, f1x, f1y, f1z);
-  put(S, sl.y & 0xffff, f2x, f2y, f2z);
-  put(S, sl.y >> 16, f3x, f3y, f3z);
+  emit<FIXED>(S, sl.x & 0xffff, q & 0xff, f0x, f0y, f0z, flag);
+  emit<FIXED>(S, sl.x >> 16, (q >> 8) & 0xff, f1x, f1y, f1z, flag);
+  emit<FIXED>(S, sl.y & 0xffff, (q >> 16) & 0xff, f2x, f2y, f2z, flag);
+  emit<FIXED>(S, sl.y >> 16, q >> 24, f3x, f3y, f3z, flag);
 }
 
 // 1-4 pairs that no dihedral item owns (only possible with hand-made parameter objects)
-template <bool ENERGY>
-__device__ __forceinline__ void p14_task(const Smem& S, const DevTopo& T, const ForceParams& P, int item, Energies& E) {
+template <bool ENERGY, bool FIXED>
+__device__ __forceinline__ void p14_task(const Smem& S, const DevTopo& T, const ForceParams& P, int item, Energies& E,
+                                         uint32_t& flag) {
   if (item >= T.n14) return;
   const uint32_t q = __ldg(T.p14_idx + item), sl = __ldg(T.p14_slot + item);
   const float4 prm = __ldg(T.p14_prm + item);
   const f3 d = sub3(S.pos[q & 0xff], S.pos[(q >> 8) & 0xff]);
   const float sc = pair14<ENERGY>(d, prm, P, E);
-  put(S, sl & 0xffff, sc * d.x, sc * d.y, sc * d.z);
-  put(S, sl >> 16, -sc * d.x, -sc * d.y, -sc * d.z);
+  emit<FIXED>(S, sl & 0xffff, q & 0xff, sc * d.x, sc * d.y, sc * d.z, flag);
+  emit<FIXED>(S, sl >> 16, (q >> 8) & 0xff, -sc * d.x, -sc * d.y, -sc * d.z, flag);
 }
 
 // ---- all tasks of this warp for one force evaluation; positions must be in S.pos ------------------
-template <int MODE, bool ENERGY>
+template <int MODE, bool ENERGY, bool FIXED>
 __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const ForceParams& P, int warp, int lane,
-                                          Energies& E) {
+                                          Energies& E, uint32_t& flag) {
   float fi[4][3];
 #pragma unroll
   for (int p = 0; p < 4; ++p) fi[p][0] = fi[p][1] = fi[p][2] = 0.0f;
@@ -356,17 +375,17 @@ __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const
     switch (kind) {
       case TASK_TILE: tile_task<MODE, ENERGY>(S, P, chunk, passes, lane, fi, E); break;
       case TASK_DIAG: tile_diag_task<MODE, ENERGY>(S, P, chunk & 0xff, (chunk >> 8) & 0xff, passes, lane, fi, E); break;
-      case TASK_BOND: bond_task<ENERGY>(S, T, P, item, E); break;
-      case TASK_ANGLE: angle_task<ENERGY>(S, T, item, E); break;
+      case TASK_BOND: bond_task<ENERGY, FIXED>(S, T, P, item, E, flag); break;
+      case TASK_ANGLE: angle_task<ENERGY, FIXED>(S, T, item, E, flag); break;
       case TASK_DIHEDRAL:
-        torsion_task<ENERGY>(S, P, T.dih_on != 0, T.p14_on != 0, item, T.ndih, T.dih_idx, T.dih_terms, T.dih_term_prm,
-                             T.dih_slot, T.dih_p14, E.e[B200MD_E_DIHEDRALS], E);
+        torsion_task<ENERGY, FIXED>(S, P, T.dih_on != 0, T.p14_on != 0, item, T.ndih, T.dih_idx, T.dih_terms, T.dih_term_prm,
+                             T.dih_slot, T.dih_p14, E.e[B200MD_E_DIHEDRALS], E, flag);
         break;
       case TASK_IMPROPER:
-        torsion_task<ENERGY>(S, P, true, false, item, T.nimp, T.imp_idx, T.imp_terms, T.imp_term_prm, T.imp_slot,
-                             nullptr, E.e[B200MD_E_IMPROPERS], E);
+        torsion_task<ENERGY, FIXED>(S, P, true, false, item, T.nimp, T.imp_idx, T.imp_terms, T.imp_term_prm, T.imp_slot,
+                             nullptr, E.e[B200MD_E_IMPROPERS], E, flag);
         break;
-      case TASK_P14: p14_task<ENERGY>(S, T, P, item, E); break;
+      case TASK_P14: p14_task<ENERGY, FIXED>(S, T, P, item, E, flag); break;
       default: break;
     }
   }
@@ -390,6 +409,7 @@ __device__ __forceinline__ void smd_task(const Smem& S, const ForceParams& P, fl
 }
 
 // ---- per-atom gather in a fixed order: j-side slot, 4 i-side partials, bonded slots, SMD ------------
+template <bool FIXED>
 __device__ __forceinline__ void gather_forces(const Smem& S, const ForceParams& P, int a, float& fx, float& fy,
                                               float& fz) {
   fx = S.fj[a]; fy = S.fj[kMaxAtoms + a]; fz = S.fj[2 * kMaxAtoms + a];
@@ -399,11 +419,16 @@ __device__ __forceinline__ void gather_forces(const Smem& S, const ForceParams& 
     fy += S.fi[(w * 3 + 1) * kMaxAtoms + a];
     fz += S.fi[(w * 3 + 2) * kMaxAtoms + a];
   }
-  const int g1 = S.gstart[a + 1];
+  if (FIXED) {  // bonded forces arrived as fixed-point atomics; read and re-arm the accumulators
+    fx += (float)S.fbi[a] * kFixedInv; fy += (float)S.fbi[kMaxAtoms + a] * kFixedInv; fz += (float)S.fbi[2 * kMaxAtoms + a] * kFixedInv;
+    S.fbi[a] = 0; S.fbi[kMaxAtoms + a] = 0; S.fbi[2 * kMaxAtoms + a] = 0;
+  } else {
+    const int g1 = S.gstart[a + 1];
 #pragma unroll 4
-  for (int g = S.gstart[a]; g < g1; ++g) {
-    const float* v = S.fb + 3 * g;
-    fx += v[0]; fy += v[1]; fz += v[2];
+    for (int g = S.gstart[a]; g < g1; ++g) {
+      const float* v = S.fb + 3 * g;
+      fx += v[0]; fy += v[1]; fz += v[2];
+    }
   }
   if (P.smd_on) {
     if (a == P.smd_a2) { fx += S.smd[0]; fy += S.smd[1]; fz += S.smd[2]; }

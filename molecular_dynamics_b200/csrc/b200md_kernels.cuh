@@ -57,7 +57,7 @@ struct DevTopo {
   const uint16_t* gather_start;  // [129]: slots of atom a are [gather_start[a], gather_start[a+1])
   const uint32_t* tasks;  // [kWarps][kMaxTasks]
   int ntasks[kWarps];
-  int smem_bytes;
+  int smem_bytes, smem_bytes_fixed;
 };
 
 struct ForceParams {
@@ -87,7 +87,8 @@ struct Smem {
   uint32_t* rotmask;  // [128]
   float* fi;          // [kWarps][3][128]
   float* fj;          // [3][128]
-  float* fb;          // [nslots][3] atom-major bonded force slots
+  float* fb;          // [nslots][3] atom-major bonded force slots (slot mode)
+  int* fbi;           // [3][128] fixed-point bonded force accumulators (fixed mode)
   uint16_t* gstart;   // [130]
   uint32_t* tasks;    // [kWarps*kMaxTasks]
   double* ered;       // [kWarps][10]
@@ -97,7 +98,7 @@ struct Smem {
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
-__host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, int nslots) {
+__host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, int nslots, bool fixed) {
   size_t o = 0;
   auto take = [&](size_t bytes) { size_t r = o; o = align16(o + bytes); return base + r; };
   char* p;
@@ -108,7 +109,8 @@ __host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, i
   p = take(sizeof(uint32_t) * kMaxAtoms);               if (s) s->rotmask = (uint32_t*)p;
   p = take(sizeof(float) * kWarps * 3 * kMaxAtoms);     if (s) s->fi = (float*)p;
   p = take(sizeof(float) * 3 * kMaxAtoms);              if (s) s->fj = (float*)p;
-  p = take(sizeof(float) * 3 * (size_t)(nslots > 0 ? nslots : 1)); if (s) s->fb = (float*)p;
+  p = take(fixed ? sizeof(int) * 3 * kMaxAtoms : sizeof(float) * 3 * (size_t)(nslots > 0 ? nslots : 1));
+  if (s) { s->fb = (float*)p; s->fbi = (int*)p; }
   p = take(sizeof(uint16_t) * (kMaxAtoms + 2));         if (s) s->gstart = (uint16_t*)p;
   p = take(sizeof(uint32_t) * kWarps * kMaxTasks);      if (s) s->tasks = (uint32_t*)p;
   p = take(sizeof(double) * kWarps * 10);               if (s) s->ered = (double*)p;
