@@ -98,25 +98,43 @@ struct Smem {
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
+// Every array except the two whose size depends on the topology sits at a compile-time offset, so shared
+// addresses fold into LDS/STS immediates (a run-time layout cost 11 % of all executed instructions in
+// address re-materialisation, profiles/r01_v4).  Order: fixed arrays, LJ table (ntypes rows), slot buffer.
+constexpr size_t kOffPos = 0;
+constexpr size_t kOffRowOff = kOffPos + sizeof(float4) * kMaxAtoms;
+constexpr size_t kOffMask8 = kOffRowOff + sizeof(int) * kMaxAtoms;
+constexpr size_t kOffRotMask = kOffMask8 + kMaxChunks * kMaxAtoms;
+constexpr size_t kOffFi = kOffRotMask + sizeof(uint32_t) * kMaxAtoms;
+constexpr size_t kOffFj = kOffFi + sizeof(float) * kWarps * 3 * kMaxAtoms;
+constexpr size_t kOffGstart = kOffFj + sizeof(float) * 3 * kMaxAtoms;
+constexpr size_t kOffTasks = kOffGstart + 272;
+constexpr size_t kOffEred = kOffTasks + sizeof(uint32_t) * kWarps * kMaxTasks;
+constexpr size_t kOffSmd = kOffEred + sizeof(double) * kWarps * 10;
+constexpr size_t kOffSmdEnergy = kOffSmd + 32;
+constexpr size_t kOffFbi = kOffSmdEnergy + 16;
+constexpr size_t kOffAb = kOffFbi + sizeof(int) * 3 * kMaxAtoms;
+static_assert(kOffAb % 16 == 0 && kOffFi % 16 == 0 && kOffEred % 16 == 0, "shared-memory layout must stay 16-byte aligned");
+
 __host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, int nslots, bool fixed) {
-  size_t o = 0;
-  auto take = [&](size_t bytes) { size_t r = o; o = align16(o + bytes); return base + r; };
-  char* p;
-  p = take(sizeof(float4) * kMaxAtoms);                 if (s) s->pos = (float4*)p;
-  p = take(sizeof(float2) * (size_t)ntypes * kAbStride); if (s) s->ab = (float2*)p;
-  p = take(sizeof(int) * kMaxAtoms);                    if (s) s->ab_row_off = (int*)p;
-  p = take(kMaxChunks * kMaxAtoms);                     if (s) s->mask8 = (uint8_t*)p;
-  p = take(sizeof(uint32_t) * kMaxAtoms);               if (s) s->rotmask = (uint32_t*)p;
-  p = take(sizeof(float) * kWarps * 3 * kMaxAtoms);     if (s) s->fi = (float*)p;
-  p = take(sizeof(float) * 3 * kMaxAtoms);              if (s) s->fj = (float*)p;
-  p = take(fixed ? sizeof(int) * 3 * kMaxAtoms : sizeof(float) * 3 * (size_t)(nslots > 0 ? nslots : 1));
-  if (s) { s->fb = (float*)p; s->fbi = (int*)p; }
-  p = take(sizeof(uint16_t) * (kMaxAtoms + 2));         if (s) s->gstart = (uint16_t*)p;
-  p = take(sizeof(uint32_t) * kWarps * kMaxTasks);      if (s) s->tasks = (uint32_t*)p;
-  p = take(sizeof(double) * kWarps * 10);               if (s) s->ered = (double*)p;
-  p = take(sizeof(float) * 8);                          if (s) s->smd = (float*)p;
-  p = take(sizeof(double) * 2);                         if (s) s->smd_energy = (double*)p;
-  return o;
+  const size_t off_fb = kOffAb + align16(sizeof(float2) * (size_t)ntypes * kAbStride);
+  if (s) {
+    s->pos = (float4*)(base + kOffPos);
+    s->ab_row_off = (int*)(base + kOffRowOff);
+    s->mask8 = (uint8_t*)(base + kOffMask8);
+    s->rotmask = (uint32_t*)(base + kOffRotMask);
+    s->fi = (float*)(base + kOffFi);
+    s->fj = (float*)(base + kOffFj);
+    s->gstart = (uint16_t*)(base + kOffGstart);
+    s->tasks = (uint32_t*)(base + kOffTasks);
+    s->ered = (double*)(base + kOffEred);
+    s->smd = (float*)(base + kOffSmd);
+    s->smd_energy = (double*)(base + kOffSmdEnergy);
+    s->fbi = (int*)(base + kOffFbi);
+    s->ab = (float2*)(base + kOffAb);
+    s->fb = (float*)(base + off_fb);
+  }
+  return fixed ? off_fb : off_fb + align16(sizeof(float) * 3 * (size_t)(nslots > 0 ? nslots : 1));
 }
 
 // ---- small math helpers ---------------------------------------------------------------------
