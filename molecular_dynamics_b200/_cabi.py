@@ -158,7 +158,8 @@ class PackedTopology:
 # library loading
 # ----------------------------------------------------------------------------------------------
 _LIB = None
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libb200md.so")
+# B200MD_LIB selects another build of the same library (kernel experiments); default: the in-tree build
+LIB_PATH = os.environ.get("B200MD_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libb200md.so")
 
 
 def declare_signatures(lib):

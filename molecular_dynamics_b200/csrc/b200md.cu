@@ -100,7 +100,7 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
 // forces of a replica stay in registers / shared memory for all nsteps; HBM sees only the initial
 // load, the final store, the observable records and the optional snapshots.
 template <int MODE>
-__global__ void __launch_bounds__(kThreads, 4)
+__global__ void __launch_bounds__(kThreads, 5)
 integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const long long R, float* __restrict__ pos,
                  float* __restrict__ vel, float* __restrict__ forces, const float* __restrict__ box,
                  double* __restrict__ observables, float* __restrict__ snapshots, uint32_t* __restrict__ status) {
@@ -137,6 +137,7 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       vx = fmaf(hdt_m, fx, vx); vy = fmaf(hdt_m, fy, vy); vz = fmaf(hdt_m, fz, vz);
       x = fmaf(dt, vx, x); y = fmaf(dt, vy, y); z = fmaf(dt, vz, z);
       if (live) S.pos[tid] = make_float4(x, y, z, q);
+      S.vel[tid] = make_float4(vx, vy, vz, 0.0f);  // parked: frees 6 registers across the task phase
       __syncthreads();
       const bool report = I.energy_every > 0 ? ((s + 1) % I.energy_every == 0) : (s == I.nsteps - 1);
       Energies E;
@@ -148,6 +149,10 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       }
       if (P.smd_on && tid == kThreads - 1) smd_task(S, P, (float)((double)P.smd_c0 + (double)P.smd_rate * (double)(gstep + 1)));
       __syncthreads();
+      {
+        const float4 pp = S.pos[tid], vv = S.vel[tid];
+        x = pp.x; y = pp.y; z = pp.z; vx = vv.x; vy = vv.y; vz = vv.z;
+      }
       if (live) gather_forces<true>(S, P, tid, fx, fy, fz);
       if (langevin) {  // vel += -gamma vel dt + vcoeff N(0,1)
         float n[3];

@@ -76,6 +76,7 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
   const float4* pj = S.pos + chunk * kChunk;
 #pragma unroll 1
   for (int p = 0; p < passes; ++p) {
+    asm volatile("" ::: "memory");  // re-read the 8 broadcast j atoms every pass instead of pinning 32 registers
     const int i = p * 32 + lane;
     const float4 pi = S.pos[i];
     const float kqi = __fmul_rn(pi.w, kElecFactor);

@@ -89,6 +89,7 @@ struct Smem {
   float* fj;          // [3][128]
   float* fb;          // [nslots][3] atom-major bonded force slots (slot mode)
   int* fbi;           // [3][128] fixed-point bonded force accumulators (fixed mode)
+  float4* vel;        // [128] velocities parked during the task phase of the integrator
   uint16_t* gstart;   // [130]
   uint32_t* tasks;    // [kWarps*kMaxTasks]
   double* ered;       // [kWarps][10]
@@ -113,7 +114,8 @@ constexpr size_t kOffEred = kOffTasks + sizeof(uint32_t) * kWarps * kMaxTasks;
 constexpr size_t kOffSmd = kOffEred + sizeof(double) * kWarps * 10;
 constexpr size_t kOffSmdEnergy = kOffSmd + 32;
 constexpr size_t kOffFbi = kOffSmdEnergy + 16;
-constexpr size_t kOffAb = kOffFbi + sizeof(int) * 3 * kMaxAtoms;
+constexpr size_t kOffVel = kOffFbi + sizeof(int) * 3 * kMaxAtoms;
+constexpr size_t kOffAb = kOffVel + sizeof(float4) * kMaxAtoms;
 static_assert(kOffAb % 16 == 0 && kOffFi % 16 == 0 && kOffEred % 16 == 0, "shared-memory layout must stay 16-byte aligned");
 
 __host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, int nslots, bool fixed) {
@@ -131,6 +133,7 @@ __host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, i
     s->smd = (float*)(base + kOffSmd);
     s->smd_energy = (double*)(base + kOffSmdEnergy);
     s->fbi = (int*)(base + kOffFbi);
+    s->vel = (float4*)(base + kOffVel);
     s->ab = (float2*)(base + kOffAb);
     s->fb = (float*)(base + off_fb);
   }
