@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -457,18 +458,22 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   // ---- static task schedule: longest-processing-time-first over the 4 warps ----------------------
   struct Task { uint32_t word; int cost; };
   std::vector<Task> all;
+  // cost model of the schedule (issue slots per warp); B200MD_COSTS="pass,chunk,diagstep,diag,bond,angle,dih,imp,p14"
+  // overrides it for tuning runs
+  int cm[9] = {214, 160, 48, 40, 60, 140, 360, 300, 50};
+  if (const char* env = getenv("B200MD_COSTS")) sscanf(env, "%d,%d,%d,%d,%d,%d,%d,%d,%d", cm, cm + 1, cm + 2, cm + 3, cm + 4, cm + 5, cm + 6, cm + 7, cm + 8);
   const int nblocks = (N + 31) / 32;
   if (d->npairs > 0) {
     for (int c = 4; c < T.nchunks; ++c) {  // off-diagonal: chunk of block J against the full blocks 0..J-1
       const int passes = c / 4;
-      all.push_back({make_task(TASK_TILE, c, passes), passes * (kChunk * 24 + 30) + 110});
+      all.push_back({make_task(TASK_TILE, c, passes), passes * cm[0] + cm[1]});
     }
     for (int b = 0; b < nblocks; ++b) {  // diagonal blocks by rotation
       const int n = std::min(32, N - 32 * b), nsteps = n / 2;
-      if (nsteps > 0) all.push_back({make_task(TASK_DIAG, (uint32_t)b | ((uint32_t)n << 8), nsteps), nsteps * 36 + 40});
+      if (nsteps > 0) all.push_back({make_task(TASK_DIAG, (uint32_t)b | ((uint32_t)n << 8), nsteps), nsteps * cm[2] + cm[3]});
     }
   }
-  const int chunk_cost[6] = {0, 50, 110, 230, 200, 45};
+  const int chunk_cost[6] = {0, cm[4], cm[5], cm[6], cm[7], cm[8]};
   for (int ty = 1; ty < 6; ++ty)
     for (int c = 0; c < (counts[ty] + 31) / 32; ++c) all.push_back({make_task(ty, c, 0), chunk_cost[ty]});
   std::stable_sort(all.begin(), all.end(), [](const Task& a, const Task& b) { return a.cost > b.cost; });
@@ -630,8 +635,11 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
   I.nsteps = io->nsteps; I.energy_every = io->energy_every; I.snapshot_every = io->snapshot_every;
   CUDA_TRY(cudaSetDevice(topo->device));
   const int mode = P.has_cutoff ? 1 : 0;
+  // long launches: one CTA per replica, so the hardware block scheduler hands a finished SM its next replica
+  // (a static grid-stride split of 8 192 replicas over 740 resident CTAs ends with a 12th round on 52 CTAs);
+  // short launches keep the grid-stride loop to stage the tables once per resident CTA
   const long long cap = (long long)topo->num_sms * topo->occ_integrate[mode];
-  const int grid = (int)std::min<long long>(R, cap);
+  const int grid = (int)((io->nsteps >= 32 && R < (1ll << 30)) ? R : std::min<long long>(R, cap));
   cudaStream_t st = (cudaStream_t)stream;
   if (mode == 0)
     integrate_kernel<0><<<grid, kThreads, T.smem_bytes_fixed, st>>>(T, P, I, R, pos, vel, forces, box, observables, snapshots, status);
