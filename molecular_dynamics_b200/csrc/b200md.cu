@@ -372,6 +372,29 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   }
 
   // ---- bonded items ------------------------------------------------------------------------------
+  // Dihedral items are processed in an internal order sorted by (number of terms, branch kind, largest
+  // periodicity), so the 32 lanes of a chunk run the same term loop; par.dihedrals itself is untouched.
+  std::vector<int> dperm(d->ndihedrals), dinv(d->ndihedrals);
+  {
+    std::vector<long long> key(d->ndihedrals, 0);
+    std::vector<int> nterm(d->ndihedrals, 0), maxper(d->ndihedrals, 0), special(d->ndihedrals, 0);
+    for (int t = 0; t < d->ndihedral_terms; ++t) {
+      const int o = d->dihedral_term_owner[t];
+      if (o < 0 || o >= d->ndihedrals) { delete topo; fail(B200MD_ERR_INVALID_ARGUMENT, "dihedral term owner out of range"); return nullptr; }
+      const float per = d->dihedral_term_prm[3 * t + 2];
+      nterm[o]++;
+      const bool fast = !d->dihedral_term_harmonic[t] && per >= 1.0f && per <= 8.0f && per == floorf(per);
+      if (!fast) special[o] = 1; else maxper[o] = std::max(maxper[o], (int)per);
+    }
+    for (int k = 0; k < d->ndihedrals; ++k) key[k] = ((long long)special[k] << 40) | ((long long)nterm[k] << 20) | maxper[k];
+    for (int k = 0; k < d->ndihedrals; ++k) dperm[k] = k;
+    std::stable_sort(dperm.begin(), dperm.end(), [&](int a, int b) { return key[a] < key[b]; });
+    for (int k = 0; k < d->ndihedrals; ++k) dinv[dperm[k]] = k;
+  }
+  std::vector<int32_t> dihedral_idx_s((size_t)4 * std::max(d->ndihedrals, 1)), dihedral_owner_s(std::max(d->ndihedral_terms, 1));
+  for (int k = 0; k < d->ndihedrals; ++k)
+    for (int c = 0; c < 4; ++c) dihedral_idx_s[4 * k + c] = d->dihedral_idx[4 * dperm[k] + c];
+  for (int t = 0; t < d->ndihedral_terms; ++t) dihedral_owner_s[t] = dinv[d->dihedral_term_owner[t]];
   std::vector<uint32_t> bond_idx(d->nbonds), angle_idx(d->nangles), dih_idx(d->ndihedrals), imp_idx(d->nimpropers);
   std::vector<float2> bond_prm(d->nbonds), angle_prm(d->nangles);
   for (int k = 0; k < d->nbonds; ++k) {
@@ -382,7 +405,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
     angle_idx[k] = pack4(d->angle_idx + 3 * k, 3);
     angle_prm[k] = make_float2(d->angle_prm[2 * k], d->angle_prm[2 * k + 1]);
   }
-  for (int k = 0; k < d->ndihedrals; ++k) dih_idx[k] = pack4(d->dihedral_idx + 4 * k, 4);
+  for (int k = 0; k < d->ndihedrals; ++k) dih_idx[k] = pack4(dihedral_idx_s.data() + 4 * k, 4);
   for (int k = 0; k < d->nimpropers; ++k) imp_idx[k] = pack4(d->improper_idx + 4 * k, 4);
   // 1-4 pairs (forces.py:176-226): fused into the first dihedral item whose end atoms they are; pairs
   // without such a dihedral stay in their own ("orphan") list.  Stored as (12 A/scnb, 6 B/scnb, K qi qj/scee).
@@ -397,7 +420,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
                              (float)(332.06371307417066 * qi * qj / p[3]), 1.0f);
     int owner = -1;
     for (int q = 0; q < d->ndihedrals && owner < 0; ++q) {
-      const int32_t* a = d->dihedral_idx + 4 * q;
+      const int32_t* a = dihedral_idx_s.data() + 4 * q;
       if (dih_p14[q].w == 0.0f && ((a[0] == i && a[3] == j) || (a[0] == j && a[3] == i))) owner = q;
     }
     if (owner >= 0) {
@@ -413,7 +436,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   T.p14_on = 1;
   std::vector<uint2> dih_terms, imp_terms;
   std::vector<float4> dih_tp, imp_tp;
-  build_terms(d->ndihedrals, d->ndihedral_terms, d->dihedral_term_owner, d->dihedral_term_prm,
+  build_terms(d->ndihedrals, d->ndihedral_terms, dihedral_owner_s.data(), d->dihedral_term_prm,
               d->dihedral_term_harmonic, dih_terms, dih_tp);
   build_terms(d->nimpropers, d->nimproper_terms, d->improper_term_owner, d->improper_term_prm,
               d->improper_term_harmonic, imp_terms, imp_tp);
@@ -427,7 +450,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   }
   const int counts[6] = {0, d->nbonds, d->nangles, d->ndihedrals, d->nimpropers, (int)p14_idx.size()};
   const int arity[6] = {0, 2, 3, 4, 4, 2};
-  const int32_t* idxs[6] = {nullptr, d->bond_idx, d->angle_idx, d->dihedral_idx, d->improper_idx, orphan_atoms.data()};
+  const int32_t* idxs[6] = {nullptr, d->bond_idx, d->angle_idx, dihedral_idx_s.data(), d->improper_idx, orphan_atoms.data()};
   std::vector<int> per_atom_count(kMaxAtoms, 0);
   for (int ty = 1; ty < 6; ++ty)
     for (int it = 0; it < counts[ty] * arity[ty]; ++it) per_atom_count[idxs[ty][it]]++;

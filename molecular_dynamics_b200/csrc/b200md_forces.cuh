@@ -21,8 +21,8 @@ struct Energies {
 // The force path is written with explicit round-to-nearest intrinsics so that the ENERGY and the
 // force-only instantiations produce bit-identical forces (no compiler-chosen FMA contraction): a
 // trajectory does not depend on how often energies are reported.  `ab` holds (12 A, 6 B).
-// Energies (report steps only) use one Newton step on rsqrt: the MUFU error (2^-22) would otherwise be
-// amplified 12x in r^-12 and miss the 1e-6 energy tolerance.
+// Energies come from the same r^-1, r^-6 (a Newton step on rsqrt was tried and changed nothing measurable:
+// the energy error is set by the fp32 rounding of dx, dy, dz, not by MUFU.RSQ).
 template <int MODE, bool ENERGY>
 __device__ __forceinline__ float pair_eval(float dx, float dy, float dz, float kqi, float qj, float2 ab, bool excl,
                                            const ForceParams& P, float& pel, float& plj) {
@@ -33,35 +33,35 @@ __device__ __forceinline__ float pair_eval(float dx, float dy, float dz, float k
   const float r2inv = __fmul_rn(rinv, rinv);
   const float r6 = __fmul_rn(__fmul_rn(r2inv, r2inv), r2inv);
   const float qq = (MODE == 1 && excl) ? 0.0f : __fmul_rn(kqi, qj);
-  float glj = __fmul_rn(__fmaf_rn(ab.x, r6, -ab.y), r6);  // 12 A r^-12 - 6 B r^-6 = -r dE/dr
-  float gc;
-  float corr = 1.0f, elj = 0.0f;
-  if (ENERGY || MODE == 1) {
-    // Newton correction factor for rinv: rinv_exact ~= rinv * corr
-    corr = __fmaf_rn(__fmul_rn(r2, r2inv), -0.5f, 1.5f);
-    const float c2 = corr * corr;
-    const float r6e = r6 * (c2 * c2 * c2);
-    elj = (ab.x * r6e * (1.0f / 12.0f) - ab.y * (1.0f / 6.0f)) * r6e;  // A r^-12 - B r^-6
-  }
+  const float glj1 = __fmaf_rn(ab.x, r6, -ab.y);  // 12 A r^-6 - 6 B;  glj1 * r6 = -r dE_lj/dr
   if (MODE == 0) {
-    gc = __fmul_rn(qq, rinv);  // K qi qj / r = -r dE/dr
-    if (ENERGY) pel += gc * corr;
+    const float gc = __fmul_rn(qq, rinv);  // K qi qj / r = -r dE_c/dr
+    if (ENERGY) {
+      pel += gc;
+      plj += __fmul_rn(__fmaf_rn(__fmul_rn(ab.x, 1.0f / 12.0f), r6, -__fmul_rn(ab.y, 1.0f / 6.0f)), r6);
+    }
+    return __fmul_rn(__fmaf_rn(glj1, r6, gc), r2inv);
   } else {
-    gc = __fmul_rn(qq, __fmaf_rn(-2.0f * P.krf, r2, rinv));  // -r * forces.py:478
-    const float rinv_e = rinv * corr;
-    const float r = __fmul_rn(r2, rinv_e);
-    if (r > P.rs) {  // forces.py:401-411 (note pot*deriv/dist as written)
+    const float gc = __fmul_rn(qq, __fmaf_rn(-2.0f * P.krf, r2, rinv));  // -r * forces.py:478
+    float glj = __fmul_rn(glj1, r6);
+    const float r = __fmul_rn(r2, rinv);
+    const bool sw = r > P.rs;
+    float elj = 0.0f;
+    if (ENERGY || sw) elj = __fmul_rn(__fmaf_rn(__fmul_rn(ab.x, 1.0f / 12.0f), r6, -__fmul_rn(ab.y, 1.0f / 6.0f)), r6);
+    if (sw) {  // forces.py:401-411 (note pot*deriv/dist as written)
       const float t = __fmul_rn(r - P.rs, P.inv_sw);
       const float t2 = __fmul_rn(t, t);
       const float sv = __fmaf_rn(__fmul_rn(t2, t), __fmaf_rn(t, __fmaf_rn(t, -6.0f, 15.0f), -10.0f), 1.0f);
       const float sd = __fmul_rn(__fmul_rn(t2, __fmaf_rn(t, __fmaf_rn(t, -30.0f, 60.0f), -30.0f)), P.inv_sw);
       glj = __fmaf_rn(sv, glj, -__fmul_rn(elj, sd));
-      elj *= sv;
+      elj = __fmul_rn(elj, sv);
     }
-    if (ENERGY) pel += qq * (rinv_e + fmaf(P.krf, r2, -P.crf));  // forces.py:476
+    if (ENERGY) {
+      pel += __fmul_rn(qq, __fadd_rn(rinv, __fmaf_rn(P.krf, r2, -P.crf)));  // forces.py:476
+      plj += elj;
+    }
+    return __fmul_rn(__fadd_rn(glj, gc), r2inv);
   }
-  if (ENERGY) plj += elj;
-  return __fmul_rn(__fadd_rn(glj, gc), r2inv);
 }
 
 // ---- TASK_TILE: j-chunk `chunk` (8 atoms) against i-blocks 0..passes-1 (32 lanes each) ----------
