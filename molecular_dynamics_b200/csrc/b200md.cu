@@ -58,7 +58,10 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
   extern __shared__ __align__(16) char smem_raw[];
   Smem S;
   smem_layout(&S, smem_raw, T.ntypes, T.nslots, false);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // pinned in registers: under register pressure the compiler otherwise re-reads SR_TID.X (a ~25-cycle S2R)
+  // at the top of every task
+  int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  asm volatile("" : "+r"(tid), "+r"(warp), "+r"(lane));
   const int N = T.natoms;
   stage_tables<false>(S, T, P, tid);
   const float q = tid < N ? __ldg(T.charge + tid) * P.el_on : 0.0f;
@@ -108,7 +111,10 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
   extern __shared__ __align__(16) char smem_raw[];
   Smem S;
   smem_layout(&S, smem_raw, T.ntypes, T.nslots, true);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // pinned in registers: under register pressure the compiler otherwise re-reads SR_TID.X (a ~25-cycle S2R)
+  // at the top of every task
+  int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  asm volatile("" : "+r"(tid), "+r"(warp), "+r"(lane));
   const int N = T.natoms;
   stage_tables<true>(S, T, P, tid);
   const bool live = tid < N;

@@ -74,14 +74,24 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
 #pragma unroll
   for (int s = 0; s < kChunk; ++s) fj[s][0] = fj[s][1] = fj[s][2] = 0.0f;
   const float4* pj = S.pos + chunk * kChunk;
+  // software-pipelined pass prologue: the i atom, its LJ row offset and its 8 mask bits of pass p+1 are loaded
+  // while pass p computes (their shared-memory latency was exposed at the top of every pass)
+  float4 pi_n = S.pos[lane];
+  int roff_n = S.ab_row_off[lane];
+  uint32_t m8_n = S.mask8[chunk * kMaxAtoms + lane];
 #pragma unroll 1
   for (int p = 0; p < passes; ++p) {
     asm volatile("" ::: "memory");  // re-read the 8 broadcast j atoms every pass instead of pinning 32 registers
-    const int i = p * 32 + lane;
-    const float4 pi = S.pos[i];
+    const float4 pi = pi_n;
     const float kqi = __fmul_rn(pi.w, kElecFactor);
-    const float2* row = (const float2*)((const char*)S.ab + S.ab_row_off[i]) + chunk * kChunk;
-    const uint32_t m8 = S.mask8[chunk * kMaxAtoms + i];
+    const float2* row = (const float2*)((const char*)S.ab + roff_n) + chunk * kChunk;
+    const uint32_t m8 = m8_n;
+    {
+      const int in = (p + 1 < passes ? p + 1 : p) * 32 + lane;
+      pi_n = S.pos[in];
+      roff_n = S.ab_row_off[in];
+      m8_n = S.mask8[chunk * kMaxAtoms + in];
+    }
     float pel = 0.0f, plj = 0.0f, ax = 0.0f, ay = 0.0f, az = 0.0f;
 #pragma unroll
     for (int s = 0; s < kChunk; ++s) {
