@@ -24,15 +24,17 @@ namespace b200md {
 // replicas).  Term switches (forces.py:40-50) are applied here: "lj" off -> A = B = 0.
 template <bool FIXED>
 __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, const ForceParams& P, int tid) {
-  const int nab = T.ntypes * kAbStride;
-  for (int k = tid; k < nab; k += kThreads) {
-    const float2 v = __ldg(T.ab + k);
-    S.ab[k] = make_float2(v.x * P.lj_on, v.y * P.lj_on);
-  }
+  for (int t = 0; t < T.ntypes; ++t)
+    for (int j = tid; j < kTabStride; j += kThreads) {
+      const float2 v = j < kMaxAtoms ? __ldg(T.ab + t * kAbStride + j) : make_float2(0.f, 0.f);
+      S.ta[t * kTabStride + j] = v.x * P.lj_on;
+      S.tb[t * kTabStride + j] = -(v.y * P.lj_on);
+    }
   for (int k = tid; k < kMaxAtoms; k += kThreads) {
     S.ab_row_off[k] = __ldg(T.ab_row_off + k);
     S.rotmask[k] = __ldg(T.rotmask + k);
     S.pos[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    S.sx[k] = S.sx[kMaxAtoms + k] = S.sx[2 * kMaxAtoms + k] = S.sx[3 * kMaxAtoms + k] = 0.0f;
   }
   for (int k = tid; k < kMaxChunks * kMaxAtoms / 4; k += kThreads)
     ((uint32_t*)S.mask8)[k] = __ldg((const uint32_t*)T.mask8 + k);
@@ -47,6 +49,7 @@ __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, co
   }
   // chunks without a tile task (no non-bonded term enabled) must read as zero in the gather
   for (int k = tid; k < 3 * kMaxAtoms; k += kThreads) S.fj[k] = 0.0f;
+  for (int k = tid; k < kWarps * 3 * kMaxAtoms; k += kThreads) S.fi[k] = 0.0f;  // i-side partials: armed here, re-armed by the gather
 }
 
 // Forces.compute (forces.py:82-344) for a batch of replicas: one CTA per replica (grid-stride).
@@ -73,6 +76,7 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
       const float x = __ldg(p), y = __ldg(p + 1), z = __ldg(p + 2);
       if (x != x || y != y || z != z) flag |= B200MD_FLAG_NAN_POS;
       S.pos[tid] = make_float4(x, y, z, q);
+      S.sx[tid] = x; S.sx[kMaxAtoms + tid] = y; S.sx[2 * kMaxAtoms + tid] = z; S.sx[3 * kMaxAtoms + tid] = q;
     }
     if (box != nullptr && tid < 3 && __ldg(box + r * 9 + tid * 4) != 0.0f) flag |= B200MD_FLAG_PBC_UNSUPPORTED;
     if (status != nullptr) {
@@ -143,7 +147,10 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       // _first_VV: pos += vel dt + 0.5 a dt^2 ; vel += 0.5 dt a
       vx = fmaf(hdt_m, fx, vx); vy = fmaf(hdt_m, fy, vy); vz = fmaf(hdt_m, fz, vz);
       x = fmaf(dt, vx, x); y = fmaf(dt, vy, y); z = fmaf(dt, vz, z);
-      if (live) S.pos[tid] = make_float4(x, y, z, q);
+      if (live) {
+        S.pos[tid] = make_float4(x, y, z, q);
+        S.sx[tid] = x; S.sx[kMaxAtoms + tid] = y; S.sx[2 * kMaxAtoms + tid] = z; S.sx[3 * kMaxAtoms + tid] = q;
+      }
       S.vel[tid] = make_float4(vx, vy, vz, 0.0f);  // parked: frees 6 registers across the task phase
       __syncthreads();
       const bool report = I.energy_every > 0 ? ((s + 1) % I.energy_every == 0) : (s == I.nsteps - 1);
@@ -374,7 +381,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   for (int a = 0; a < N; ++a) {
     charge[a] = d->charge ? d->charge[a] : 0.f;
     mass[a] = d->mass[a];
-    rowoff[a] = d->atom_type[a] * kAbStride * (int)sizeof(float2);
+    rowoff[a] = d->atom_type[a] * kTabStride * (int)sizeof(float);
   }
 
   // ---- bonded items ------------------------------------------------------------------------------

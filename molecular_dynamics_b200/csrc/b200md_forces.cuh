@@ -20,42 +20,40 @@ struct Energies {
 //
 // The force path is written with explicit round-to-nearest intrinsics so that the ENERGY and the
 // force-only instantiations produce bit-identical forces (no compiler-chosen FMA contraction): a
-// trajectory does not depend on how often energies are reported.  `ab` holds (12 A, 6 B).
+// trajectory does not depend on how often energies are reported.  (a12, nb6) = (12 A, -6 B).
 // Energies come from the same r^-1, r^-6 (a Newton step on rsqrt was tried and changed nothing measurable:
 // the energy error is set by the fp32 rounding of dx, dy, dz, not by MUFU.RSQ).
 template <int MODE, bool ENERGY>
-__device__ __forceinline__ float pair_eval(float dx, float dy, float dz, float kqi, float qj, float2 ab, bool excl,
-                                           const ForceParams& P, float& pel, float& plj) {
+__device__ __forceinline__ float pair_eval(float dx, float dy, float dz, float kqi, float qj, float a12, float nb6,
+                                           bool excl, const ForceParams& P, float& pel, float& plj) {
   const float r2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
   float rinv = fast_rsqrt(r2);
   if (MODE == 1) excl = excl || !(r2 <= P.rc2);
   rinv = excl ? 0.0f : rinv;
   const float r2inv = __fmul_rn(rinv, rinv);
   const float r6 = __fmul_rn(__fmul_rn(r2inv, r2inv), r2inv);
-  const float qq = (MODE == 1 && excl) ? 0.0f : __fmul_rn(kqi, qj);
-  const float glj1 = __fmaf_rn(ab.x, r6, -ab.y);  // 12 A r^-6 - 6 B;  glj1 * r6 = -r dE_lj/dr
+  const float qq = __fmul_rn((MODE == 1 && excl) ? 0.0f : kqi, qj);
+  const float glj1 = __fmaf_rn(a12, r6, nb6);  // 12 A r^-6 - 6 B;  glj1 * r6 = -r dE_lj/dr
   if (MODE == 0) {
     const float gc = __fmul_rn(qq, rinv);  // K qi qj / r = -r dE_c/dr
     if (ENERGY) {
       pel += gc;
-      plj += __fmul_rn(__fmaf_rn(__fmul_rn(ab.x, 1.0f / 12.0f), r6, -__fmul_rn(ab.y, 1.0f / 6.0f)), r6);
+      plj += __fmul_rn(__fmaf_rn(__fmul_rn(a12, 1.0f / 12.0f), r6, __fmul_rn(nb6, 1.0f / 6.0f)), r6);
     }
     return __fmul_rn(__fmaf_rn(glj1, r6, gc), r2inv);
   } else {
     const float gc = __fmul_rn(qq, __fmaf_rn(-2.0f * P.krf, r2, rinv));  // -r * forces.py:478
     float glj = __fmul_rn(glj1, r6);
     const float r = __fmul_rn(r2, rinv);
-    const bool sw = r > P.rs;
-    float elj = 0.0f;
-    if (ENERGY || sw) elj = __fmul_rn(__fmaf_rn(__fmul_rn(ab.x, 1.0f / 12.0f), r6, -__fmul_rn(ab.y, 1.0f / 6.0f)), r6);
-    if (sw) {  // forces.py:401-411 (note pot*deriv/dist as written)
-      const float t = __fmul_rn(r - P.rs, P.inv_sw);
-      const float t2 = __fmul_rn(t, t);
-      const float sv = __fmaf_rn(__fmul_rn(t2, t), __fmaf_rn(t, __fmaf_rn(t, -6.0f, 15.0f), -10.0f), 1.0f);
-      const float sd = __fmul_rn(__fmul_rn(t2, __fmaf_rn(t, __fmaf_rn(t, -30.0f, 60.0f), -30.0f)), P.inv_sw);
-      glj = __fmaf_rn(sv, glj, -__fmul_rn(elj, sd));
-      elj = __fmul_rn(elj, sv);
-    }
+    // forces.py:401-411 (pot*deriv/dist as written).  t is clamped at 0 below the switch distance (and for
+    // switch_dist = None, where rs = +inf makes it NaN): sv = 1, sd = 0 there, which leaves glj and elj untouched.
+    const float t = fmaxf(__fmul_rn(r - P.rs, P.inv_sw), 0.0f);
+    const float t2 = __fmul_rn(t, t);
+    const float sv = __fmaf_rn(__fmul_rn(t2, t), __fmaf_rn(t, __fmaf_rn(t, -6.0f, 15.0f), -10.0f), 1.0f);
+    const float nsd = __fmul_rn(__fmul_rn(t2, __fmaf_rn(t, __fmaf_rn(t, 30.0f, -60.0f), 30.0f)), P.inv_sw);
+    float elj = __fmul_rn(__fmaf_rn(__fmul_rn(a12, 1.0f / 12.0f), r6, __fmul_rn(nb6, 1.0f / 6.0f)), r6);
+    glj = __fmaf_rn(sv, glj, __fmul_rn(elj, nsd));
+    elj = __fmul_rn(elj, sv);
     if (ENERGY) {
       pel += __fmul_rn(qq, __fadd_rn(rinv, __fmaf_rn(P.krf, r2, -P.crf)));  // forces.py:476
       plj += elj;
@@ -64,16 +62,76 @@ __device__ __forceinline__ float pair_eval(float dx, float dy, float dz, float k
   }
 }
 
-// ---- TASK_TILE: j-chunk `chunk` (8 atoms) against i-blocks 0..passes-1 (32 lanes each) ----------
-// The pass loop is rolled (one 8-step body in the instruction cache); the i-side force of pass p goes
-// to the register accumulator fi[p] through a predicated add chain.
+// Two pairs of one i atom (j, j+1) in packed f32x2: the same operations in the same order as pair_eval, one issue
+// slot per two fp32 results.  Only rsqrt and the exclusion selects are per half.
+struct PairConst {  // loop-invariant packed constants
+  u64 c12, c6, m2krf, krf, ncrf, rs, inv_sw, cm6, c15, cm10, one, c30, cm60;
+};
+template <int MODE>
+__device__ __forceinline__ PairConst make_pair_const(const ForceParams& P) {
+  PairConst C;
+  C.c12 = dup2(1.0f / 12.0f); C.c6 = dup2(1.0f / 6.0f);
+  if (MODE == 1) {
+    C.m2krf = dup2(-2.0f * P.krf); C.krf = dup2(P.krf); C.ncrf = dup2(-P.crf); C.rs = dup2(P.rs); C.inv_sw = dup2(P.inv_sw);
+    C.cm6 = dup2(-6.0f); C.c15 = dup2(15.0f); C.cm10 = dup2(-10.0f); C.one = dup2(1.0f); C.c30 = dup2(30.0f); C.cm60 = dup2(-60.0f);
+  }
+  return C;
+}
 template <int MODE, bool ENERGY>
-__device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, int chunk, int passes, int lane,
-                                          float (&fi)[4][3], Energies& E) {
-  float fj[kChunk][3];
+__device__ __forceinline__ u64 pair_eval2(u64 dx, u64 dy, u64 dz, float kqi, u64 kq2, u64 qj, u64 a12, u64 nb6, bool e0,
+                                          bool e1, const ForceParams& P, const PairConst& C, u64& pel, u64& plj) {
+  const u64 r2 = fma2(dz, dz, fma2(dy, dy, mul2(dx, dx)));
+  float r2a, r2b;
+  upk(r2, r2a, r2b);
+  float ia = fast_rsqrt(r2a), ib = fast_rsqrt(r2b);
+  if (MODE == 1) { e0 = e0 || !(r2a <= P.rc2); e1 = e1 || !(r2b <= P.rc2); }
+  ia = e0 ? 0.0f : ia; ib = e1 ? 0.0f : ib;
+  const u64 rinv = pk(ia, ib);
+  const u64 r2inv = mul2(rinv, rinv);
+  const u64 r6 = mul2(mul2(r2inv, r2inv), r2inv);
+  const u64 qq = mul2(MODE == 1 ? pk(e0 ? 0.0f : kqi, e1 ? 0.0f : kqi) : kq2, qj);
+  const u64 glj1 = fma2(a12, r6, nb6);
+  if (MODE == 0) {
+    const u64 gc = mul2(qq, rinv);
+    if (ENERGY) {
+      pel = add2(pel, gc);
+      plj = add2(plj, mul2(fma2(mul2(a12, C.c12), r6, mul2(nb6, C.c6)), r6));
+    }
+    return mul2(fma2(glj1, r6, gc), r2inv);
+  } else {
+    const u64 gc = mul2(qq, fma2(C.m2krf, r2, rinv));
+    u64 glj = mul2(glj1, r6);
+    const u64 r = mul2(r2, rinv);
+    float ta, tb;
+    upk(mul2(sub2(r, C.rs), C.inv_sw), ta, tb);
+    const u64 t = pk(fmaxf(ta, 0.0f), fmaxf(tb, 0.0f));
+    const u64 t2 = mul2(t, t);
+    const u64 sv = fma2(mul2(t2, t), fma2(t, fma2(t, C.cm6, C.c15), C.cm10), C.one);
+    const u64 nsd = mul2(mul2(t2, fma2(t, fma2(t, C.c30, C.cm60), C.c30)), C.inv_sw);
+    u64 elj = mul2(fma2(mul2(a12, C.c12), r6, mul2(nb6, C.c6)), r6);
+    glj = fma2(sv, glj, mul2(elj, nsd));
+    elj = mul2(elj, sv);
+    if (ENERGY) {
+      pel = add2(pel, mul2(qq, add2(rinv, fma2(C.krf, r2, C.ncrf))));
+      plj = add2(plj, elj);
+    }
+    return mul2(add2(glj, gc), r2inv);
+  }
+}
+
+// ---- TASK_TILE: j-chunk `chunk` (8 atoms) against i-blocks 0..passes-1 (32 lanes each) ----------
+// Lane = i atom; the 8 j atoms arrive as 4 packed pairs (x[], y[], z[], q[] and the 12A / -6B rows are
+// structure-of-arrays, so one LDS.128 delivers two f32x2 operands).  The pass loop is rolled (one body in the
+// instruction cache); the i-side force of a pass is added to this warp's shared-memory partial.
+template <int MODE, bool ENERGY>
+__device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, int chunk, int passes, int warp,
+                                          int lane, Energies& E) {
+  u64 fjx[kChunk / 2], fjy[kChunk / 2], fjz[kChunk / 2];
 #pragma unroll
-  for (int s = 0; s < kChunk; ++s) fj[s][0] = fj[s][1] = fj[s][2] = 0.0f;
-  const float4* pj = S.pos + chunk * kChunk;
+  for (int s = 0; s < kChunk / 2; ++s) fjx[s] = fjy[s] = fjz[s] = 0ull;
+  const PairConst C = make_pair_const<MODE>(P);
+  const float* sj = S.sx + chunk * kChunk;
+  float* fiw = S.fi + warp * 3 * kMaxAtoms + lane;
   // software-pipelined pass prologue: the i atom, its LJ row offset and its 8 mask bits of pass p+1 are loaded
   // while pass p computes (their shared-memory latency was exposed at the top of every pass)
   float4 pi_n = S.pos[lane];
@@ -84,7 +142,9 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
     asm volatile("" ::: "memory");  // re-read the 8 broadcast j atoms every pass instead of pinning 32 registers
     const float4 pi = pi_n;
     const float kqi = __fmul_rn(pi.w, kElecFactor);
-    const float2* row = (const float2*)((const char*)S.ab + roff_n) + chunk * kChunk;
+    const u64 xi = dup2(pi.x), yi = dup2(pi.y), zi = dup2(pi.z), kq2 = dup2(kqi);
+    const char* rowa = (const char*)S.ta + roff_n + chunk * kChunk * (int)sizeof(float);
+    const char* rowb = (const char*)S.tb + roff_n + chunk * kChunk * (int)sizeof(float);
     const uint32_t m8 = m8_n;
     {
       const int in = (p + 1 < passes ? p + 1 : p) * 32 + lane;
@@ -92,19 +152,36 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
       roff_n = S.ab_row_off[in];
       m8_n = S.mask8[chunk * kMaxAtoms + in];
     }
-    float pel = 0.0f, plj = 0.0f, ax = 0.0f, ay = 0.0f, az = 0.0f;
+    u64 pel = 0ull, plj = 0ull, ax = 0ull, ay = 0ull, az = 0ull;
 #pragma unroll
-    for (int s = 0; s < kChunk; ++s) {
-      const float4 q = pj[s];
-      const float dx = __fsub_rn(pi.x, q.x), dy = __fsub_rn(pi.y, q.y), dz = __fsub_rn(pi.z, q.z);
-      const float sc = pair_eval<MODE, ENERGY>(dx, dy, dz, kqi, q.w, row[s], (m8 >> s) & 1u, P, pel, plj);
-      ax = __fmaf_rn(sc, dx, ax); ay = __fmaf_rn(sc, dy, ay); az = __fmaf_rn(sc, dz, az);
-      fj[s][0] = __fmaf_rn(sc, dx, fj[s][0]); fj[s][1] = __fmaf_rn(sc, dy, fj[s][1]); fj[s][2] = __fmaf_rn(sc, dz, fj[s][2]);
+    for (int h = 0; h < kChunk / 4; ++h) {
+      const ulonglong2 xj = *(const ulonglong2*)(sj + 4 * h), yj = *(const ulonglong2*)(sj + kMaxAtoms + 4 * h),
+                       zj = *(const ulonglong2*)(sj + 2 * kMaxAtoms + 4 * h), qj = *(const ulonglong2*)(sj + 3 * kMaxAtoms + 4 * h);
+      const ulonglong2 aj = *(const ulonglong2*)(rowa + 16 * h), bj = *(const ulonglong2*)(rowb + 16 * h);
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int s = 2 * h + k;
+        const u64 dx = sub2(xi, k ? xj.y : xj.x), dy = sub2(yi, k ? yj.y : yj.x), dz = sub2(zi, k ? zj.y : zj.x);
+        const u64 sc = pair_eval2<MODE, ENERGY>(dx, dy, dz, kqi, kq2, k ? qj.y : qj.x, k ? aj.y : aj.x, k ? bj.y : bj.x,
+                                                (m8 >> (2 * s)) & 1u, (m8 >> (2 * s + 1)) & 1u, P, C, pel, plj);
+        ax = fma2(sc, dx, ax); ay = fma2(sc, dy, ay); az = fma2(sc, dz, az);
+        fjx[s] = fma2(sc, dx, fjx[s]); fjy[s] = fma2(sc, dy, fjy[s]); fjz[s] = fma2(sc, dz, fjz[s]);
+      }
     }
+    float* f = fiw + p * 32;
+    f[0] = __fadd_rn(f[0], hsum2(ax)); f[kMaxAtoms] = __fadd_rn(f[kMaxAtoms], hsum2(ay)); f[2 * kMaxAtoms] = __fadd_rn(f[2 * kMaxAtoms], hsum2(az));
+    if (ENERGY) {
+      float a, b;
+      upk(pel, a, b); E.e[B200MD_E_ELECTROSTATICS] += (double)a + (double)b;
+      upk(plj, a, b); E.e[B200MD_E_LJ] += (double)a + (double)b;
+    }
+  }
+  float fj[kChunk][3];
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
-      if (p == k) { fi[k][0] = __fadd_rn(fi[k][0], ax); fi[k][1] = __fadd_rn(fi[k][1], ay); fi[k][2] = __fadd_rn(fi[k][2], az); }
-    if (ENERGY) { E.e[B200MD_E_ELECTROSTATICS] += (double)pel; E.e[B200MD_E_LJ] += (double)plj; }
+  for (int s = 0; s < kChunk / 2; ++s) {
+    upk(fjx[s], fj[2 * s][0], fj[2 * s + 1][0]);
+    upk(fjy[s], fj[2 * s][1], fj[2 * s + 1][1]);
+    upk(fjz[s], fj[2 * s][2], fj[2 * s + 1][2]);
   }
   // Transposing butterfly: 24 per-lane partials -> per-atom sums.  After the xor-16/8/4 stages lane l
   // holds atom (l >> 2) & 7 of the chunk; xor-2/1 finish the sum.  Fixed order => deterministic.
@@ -152,11 +229,13 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
 // half of step n/2).
 template <int MODE, bool ENERGY>
 __device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams& P, int block, int n, int nsteps,
-                                               int lane, float (&fi)[4][3], Energies& E) {
+                                               int warp, int lane, Energies& E) {
   const int i0 = block * 32;
   const float4 pi = S.pos[i0 + lane];
   const float kqi = __fmul_rn(pi.w, kElecFactor);
-  const char* row = (const char*)S.ab + S.ab_row_off[i0 + lane] + i0 * (int)sizeof(float2);
+  const int roff = S.ab_row_off[i0 + lane] + i0 * (int)sizeof(float);
+  const char* rowa = (const char*)S.ta + roff;
+  const char* rowb = (const char*)S.tb + roff;
   const uint32_t rot = S.rotmask[i0 + lane];
   float pel = 0.0f, plj = 0.0f, ax = 0.0f, ay = 0.0f, az = 0.0f;
 #pragma unroll 1
@@ -169,9 +248,9 @@ __device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams&
       jl = jl >= n ? jl - n : jl;
       sl = sl < 0 ? sl + n : sl;
       const float4 q = S.pos[i0 + jl];
-      const float2 ab = *(const float2*)(row + jl * (int)sizeof(float2));
+      const float a12 = *(const float*)(rowa + jl * (int)sizeof(float)), nb6 = *(const float*)(rowb + jl * (int)sizeof(float));
       const float dx = __fsub_rn(pi.x, q.x), dy = __fsub_rn(pi.y, q.y), dz = __fsub_rn(pi.z, q.z);
-      const float sc = pair_eval<MODE, ENERGY>(dx, dy, dz, kqi, q.w, ab, (m4 >> u) & 1u, P, pel, plj);
+      const float sc = pair_eval<MODE, ENERGY>(dx, dy, dz, kqi, q.w, a12, nb6, (m4 >> u) & 1u, P, pel, plj);
       const float gx = __fmul_rn(sc, dx), gy = __fmul_rn(sc, dy), gz = __fmul_rn(sc, dz);
       ax = __fadd_rn(ax, gx); ay = __fadd_rn(ay, gy); az = __fadd_rn(az, gz);
       ax = __fsub_rn(ax, __shfl_sync(0xffffffffu, gx, sl));
@@ -179,9 +258,8 @@ __device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams&
       az = __fsub_rn(az, __shfl_sync(0xffffffffu, gz, sl));
     }
   }
-#pragma unroll
-  for (int k = 0; k < 4; ++k)
-    if (block == k) { fi[k][0] = __fadd_rn(fi[k][0], ax); fi[k][1] = __fadd_rn(fi[k][1], ay); fi[k][2] = __fadd_rn(fi[k][2], az); }
+  float* f = S.fi + warp * 3 * kMaxAtoms + i0 + lane;
+  f[0] = __fadd_rn(f[0], ax); f[kMaxAtoms] = __fadd_rn(f[kMaxAtoms], ay); f[2 * kMaxAtoms] = __fadd_rn(f[2 * kMaxAtoms], az);
   if (ENERGY) { E.e[B200MD_E_ELECTROSTATICS] += (double)pel; E.e[B200MD_E_LJ] += (double)plj; }
 }
 
@@ -374,9 +452,6 @@ __device__ __forceinline__ void p14_task(const Smem& S, const DevTopo& T, const 
 template <int MODE, bool ENERGY, bool FIXED>
 __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const ForceParams& P, int warp, int lane,
                                           Energies& E, uint32_t& flag) {
-  float fi[4][3];
-#pragma unroll
-  for (int p = 0; p < 4; ++p) fi[p][0] = fi[p][1] = fi[p][2] = 0.0f;
   const int nt = T.ntasks[warp];
 #pragma unroll 1
   for (int t = 0; t < nt; ++t) {
@@ -384,8 +459,8 @@ __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const
     const uint32_t kind = task & 0xff, chunk = (task >> 8) & 0xffff, passes = task >> 24;
     const int item = chunk * 32 + lane;
     switch (kind) {
-      case TASK_TILE: tile_task<MODE, ENERGY>(S, P, chunk, passes, lane, fi, E); break;
-      case TASK_DIAG: tile_diag_task<MODE, ENERGY>(S, P, chunk & 0xff, (chunk >> 8) & 0xff, passes, lane, fi, E); break;
+      case TASK_TILE: tile_task<MODE, ENERGY>(S, P, chunk, passes, warp, lane, E); break;
+      case TASK_DIAG: tile_diag_task<MODE, ENERGY>(S, P, chunk & 0xff, (chunk >> 8) & 0xff, passes, warp, lane, E); break;
       case TASK_BOND: bond_task<ENERGY, FIXED>(S, T, P, item, E, flag); break;
       case TASK_ANGLE: angle_task<ENERGY, FIXED>(S, T, item, E, flag); break;
       case TASK_DIHEDRAL:
@@ -400,10 +475,6 @@ __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const
       default: break;
     }
   }
-#pragma unroll
-  for (int p = 0; p < 4; ++p)
-#pragma unroll
-    for (int c = 0; c < 3; ++c) S.fi[(warp * 3 + c) * kMaxAtoms + p * 32 + lane] = fi[p][c];
 }
 
 // ---- SMD end-to-end bias (potcalc.py:75-89; force = -dE/dr): one lane, during the task phase -------
@@ -429,6 +500,7 @@ __device__ __forceinline__ void gather_forces(const Smem& S, const ForceParams& 
     fx += S.fi[(w * 3 + 0) * kMaxAtoms + a];
     fy += S.fi[(w * 3 + 1) * kMaxAtoms + a];
     fz += S.fi[(w * 3 + 2) * kMaxAtoms + a];
+    S.fi[(w * 3 + 0) * kMaxAtoms + a] = 0.0f; S.fi[(w * 3 + 1) * kMaxAtoms + a] = 0.0f; S.fi[(w * 3 + 2) * kMaxAtoms + a] = 0.0f;  // re-arm
   }
   if (FIXED) {  // bonded forces arrived as fixed-point atomics; read and re-arm the accumulators
     fx += (float)S.fbi[a] * kFixedInv; fy += (float)S.fbi[kMaxAtoms + a] * kFixedInv; fz += (float)S.fbi[2 * kMaxAtoms + a] * kFixedInv;

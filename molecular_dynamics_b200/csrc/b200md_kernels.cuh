@@ -20,7 +20,10 @@ constexpr int kWarps = 4;
 constexpr int kMaxAtoms = B200MD_MAX_ATOMS;  // 128
 constexpr int kChunk = 8;                    // atoms per j-chunk
 constexpr int kMaxChunks = kMaxAtoms / kChunk;
-constexpr int kAbStride = kMaxAtoms + 1;     // float2 per LJ-table row: (2t + 2j) mod 32 is conflict-free
+constexpr int kAbStride = kMaxAtoms + 1;     // float2 per LJ-table row of the global (HBM) table
+constexpr int kTabStride = kMaxAtoms + 4;    // floats per row of the shared-memory 12A / -6B tables: rows of
+                                             // different types start 4 banks apart, so the per-lane LDS.128 of a
+                                             // quarter warp (<= 8 types) is conflict-free
 constexpr int kMaxTasks = 64;                // per warp
 constexpr float kElecFactor = 332.06371307417066f;  // forces.py:373-376
 constexpr float kBoltzman = 0.001987191f;           // upstream torchmd.integrator
@@ -41,7 +44,7 @@ struct DevTopo {
   const float2* ab;         // [ntypes][kAbStride]  (12 A, 6 B) of (type t, atom j)
   const float* charge;      // [128]
   const float* mass;        // [128]
-  const int* ab_row_off;    // [128] byte offset of atom's LJ-table row
+  const int* ab_row_off;    // [128] byte offset of atom's row in the shared-memory 12A / -6B tables
   const uint8_t* mask8;     // [kMaxChunks][128] bit s: pair (i, 8*chunk+s) is NOT evaluated
   const uint32_t* rotmask;  // [128] bit t-1: lane skips rotation step t of its diagonal block
   int nbonds, nangles, ndih, nimp, n14;   // n14: 1-4 pairs NOT fused into a dihedral item ("orphans")
@@ -80,8 +83,10 @@ struct StepParams {
 
 // ---- shared-memory carve-up -----------------------------------------------------------------
 struct Smem {
-  float4* pos;        // [128]
-  float2* ab;         // [ntypes*kAbStride]
+  float4* pos;        // [128] (x, y, z, q) per atom: bonded items and the i side of the pair tiles
+  float* sx;          // [4][128] the same as x[], y[], z[], q[]: two j atoms arrive as one packed f32x2 operand
+  float* ta;          // [ntypes][kTabStride] 12 A of (type t, atom j)
+  float* tb;          // [ntypes][kTabStride] -6 B of (type t, atom j)
   int* ab_row_off;    // [128]
   uint8_t* mask8;     // [kMaxChunks*128]
   uint32_t* rotmask;  // [128]
@@ -115,11 +120,13 @@ constexpr size_t kOffSmd = kOffEred + sizeof(double) * kWarps * 10;
 constexpr size_t kOffSmdEnergy = kOffSmd + 32;
 constexpr size_t kOffFbi = kOffSmdEnergy + 16;
 constexpr size_t kOffVel = kOffFbi + sizeof(int) * 3 * kMaxAtoms;
-constexpr size_t kOffAb = kOffVel + sizeof(float4) * kMaxAtoms;
+constexpr size_t kOffSx = kOffVel + sizeof(float4) * kMaxAtoms;
+constexpr size_t kOffAb = kOffSx + sizeof(float) * 4 * kMaxAtoms;
 static_assert(kOffAb % 16 == 0 && kOffFi % 16 == 0 && kOffEred % 16 == 0, "shared-memory layout must stay 16-byte aligned");
 
 __host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, int nslots, bool fixed) {
-  const size_t off_fb = kOffAb + align16(sizeof(float2) * (size_t)ntypes * kAbStride);
+  const size_t tab = align16(sizeof(float) * (size_t)ntypes * kTabStride);
+  const size_t off_fb = kOffAb + 2 * tab;
   if (s) {
     s->pos = (float4*)(base + kOffPos);
     s->ab_row_off = (int*)(base + kOffRowOff);
@@ -134,7 +141,9 @@ __host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, i
     s->smd_energy = (double*)(base + kOffSmdEnergy);
     s->fbi = (int*)(base + kOffFbi);
     s->vel = (float4*)(base + kOffVel);
-    s->ab = (float2*)(base + kOffAb);
+    s->sx = (float*)(base + kOffSx);
+    s->ta = (float*)(base + kOffAb);
+    s->tb = (float*)(base + kOffAb + tab);
     s->fb = (float*)(base + off_fb);
   }
   return fixed ? off_fb : off_fb + align16(sizeof(float) * 3 * (size_t)(nslots > 0 ? nslots : 1));
@@ -158,6 +167,20 @@ __device__ __forceinline__ float rsqrt_nr(float x) {
   float u = fmaf(-0.5f * t, y, 1.5f);
   return y * u;
 }
+// ---- packed FP32 (sm_100a FFMA2 / FADD2 / FMUL2): two lanes of work per issue slot ---------------------
+// One instruction does two IEEE fp32 operations on a 64-bit register pair.  The FP32 pipe takes two cycles for
+// it (same flops as two scalar instructions) but only ONE issue slot, which leaves room for the loads,
+// predicates and MUFU of the pair loop (profiles/r01_microbench_ffma2.txt).
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pk(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void upk(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ u64 add2(u64 a, u64 b) { u64 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ u64 sub2(u64 a, u64 b) { u64 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) { u64 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) { u64 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ u64 dup2(float v) { return pk(v, v); }
+__device__ __forceinline__ float hsum2(u64 v) { float a, b; upk(v, a, b); return __fadd_rn(a, b); }
+
 struct f3 { float x, y, z; };
 __device__ __forceinline__ f3 sub3(float4 a, float4 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
 __device__ __forceinline__ f3 cross3(f3 a, f3 b) {
