@@ -32,7 +32,7 @@ __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, co
     }
   for (int k = tid; k < kMaxAtoms; k += kThreads) {
     S.ab_row_off[k] = __ldg(T.ab_row_off + k);
-    S.rotmask[k] = __ldg(T.rotmask + k);
+    S.diagmask[k] = __ldg(T.diagmask + k);
     S.pos[k] = make_float4(0.f, 0.f, 0.f, 0.f);
     S.sx[k] = S.sx[kMaxAtoms + k] = S.sx[2 * kMaxAtoms + k] = S.sx[3 * kMaxAtoms + k] = 0.0f;
   }
@@ -356,20 +356,9 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
       mask8[(size_t)c * kMaxAtoms + i] = m;
     }
 
-  // rotation masks of the diagonal blocks (tile_diag_task): block b holds n_b atoms, steps t = 1..n_b/2
-  std::vector<uint32_t> rotmask(kMaxAtoms, 0xffffffffu);
-  for (int b = 0; b * 32 < N; ++b) {
-    const int n = std::min(32, N - 32 * b), nsteps = n / 2;
-    for (int l = 0; l < n; ++l) {
-      uint32_t m = 0xffffffffu;
-      for (int t = 1; t <= nsteps; ++t) {
-        if (2 * t == n && l >= n / 2) continue;  // second visit of the same pair
-        const int i = 32 * b + l, j = 32 * b + (l + t) % n;
-        if (allowed[(size_t)std::min(i, j) * kMaxAtoms + std::max(i, j)]) m &= ~(1u << (t - 1));
-      }
-      rotmask[32 * b + l] = m;
-    }
-  }
+  // diagonal-block masks (tile_diag_task): bit j of atom i = pair (i, 32*block(i) + j) is not evaluated
+  std::vector<uint32_t> diagmask(kMaxAtoms, 0xffffffffu);
+  for (int i = 0; i < N; ++i) diagmask[i] = topo->mask_rows[(size_t)i * 4 + i / 32];
 
   // ---- per-atom tables ---------------------------------------------------------------------------
   std::vector<float2> ab((size_t)NT * kAbStride, make_float2(0.f, 0.f));
@@ -496,7 +485,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   std::vector<Task> all;
   // cost model of the schedule (issue slots per warp); B200MD_COSTS="pass,chunk,diagstep,diag,bond,angle,dih,imp,p14"
   // overrides it for tuning runs
-  int cm[9] = {214, 160, 48, 40, 60, 140, 360, 300, 50};
+  int cm[9] = {150, 120, 52, 30, 60, 140, 330, 300, 50};
   if (const char* env = getenv("B200MD_COSTS")) sscanf(env, "%d,%d,%d,%d,%d,%d,%d,%d,%d", cm, cm + 1, cm + 2, cm + 3, cm + 4, cm + 5, cm + 6, cm + 7, cm + 8);
   const int nblocks = (N + 31) / 32;
   if (d->npairs > 0) {
@@ -504,9 +493,12 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
       const int passes = c / 4;
       all.push_back({make_task(TASK_TILE, c, passes), passes * cm[0] + cm[1]});
     }
-    for (int b = 0; b < nblocks; ++b) {  // diagonal blocks by rotation
-      const int n = std::min(32, N - 32 * b), nsteps = n / 2;
-      if (nsteps > 0) all.push_back({make_task(TASK_DIAG, (uint32_t)b | ((uint32_t)n << 8), nsteps), nsteps * cm[2] + cm[3]});
+    for (int b = 0; b < nblocks; ++b) {  // diagonal blocks, full shell: tasks of up to 4 groups of 4 j atoms
+      const int n = std::min(32, N - 32 * b), groups = (n + 3) / 4;
+      for (int g0 = 0; g0 < groups; g0 += 4) {
+        const int ng = std::min(4, groups - g0);
+        all.push_back({make_task(TASK_DIAG, (uint32_t)b | ((uint32_t)g0 << 8), ng), ng * cm[2] + cm[3]});
+      }
     }
   }
   const int chunk_cost[6] = {0, cm[4], cm[5], cm[6], cm[7], cm[8]};
@@ -526,7 +518,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
 
   // ---- upload --------------------------------------------------------------------------------------
   BlobBuilder B;
-  const size_t o_ab = B.add(ab), o_q = B.add(charge), o_m = B.add(mass), o_ro = B.add(rowoff), o_mask = B.add(mask8), o_rot = B.add(rotmask);
+  const size_t o_ab = B.add(ab), o_q = B.add(charge), o_m = B.add(mass), o_ro = B.add(rowoff), o_mask = B.add(mask8), o_rot = B.add(diagmask);
   const size_t o_bi = B.add(bond_idx), o_bp = B.add(bond_prm), o_bs = B.add(bond_slot);
   const size_t o_ai = B.add(angle_idx), o_ap = B.add(angle_prm), o_as = B.add(angle_slot);
   const size_t o_di = B.add(dih_idx), o_dt = B.add(dih_terms), o_dp = B.add(dih_tp), o_ds = B.add(dih_slot), o_d14 = B.add(dih_p14);
@@ -542,7 +534,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   if (e != cudaSuccess) { cleanup(std::string("cudaMemcpy: ") + cudaGetErrorString(e)); return nullptr; }
   char* base = (char*)topo->blob;
   T.ab = (const float2*)(base + o_ab); T.charge = (const float*)(base + o_q); T.mass = (const float*)(base + o_m);
-  T.ab_row_off = (const int*)(base + o_ro); T.mask8 = (const uint8_t*)(base + o_mask); T.rotmask = (const uint32_t*)(base + o_rot);
+  T.ab_row_off = (const int*)(base + o_ro); T.mask8 = (const uint8_t*)(base + o_mask); T.diagmask = (const uint32_t*)(base + o_rot);
   T.bond_idx = (const uint32_t*)(base + o_bi); T.bond_prm = (const float2*)(base + o_bp); T.bond_slot = (const uint32_t*)(base + o_bs);
   T.angle_idx = (const uint32_t*)(base + o_ai); T.angle_prm = (const float2*)(base + o_ap); T.angle_slot = (const uint2*)(base + o_as);
   T.dih_idx = (const uint32_t*)(base + o_di); T.dih_terms = (const uint2*)(base + o_dt); T.dih_term_prm = (const float4*)(base + o_dp);

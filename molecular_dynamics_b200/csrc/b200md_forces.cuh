@@ -220,47 +220,48 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
   }
 }
 
-// ---- TASK_DIAG: all pairs inside one 32-atom block by rotation --------------------------------------
-// Lane l owns atom 32*block + l.  At step t = 1..floor(n/2) it evaluates the pair with partner
-// (l + t) mod n, keeps its own side in registers and hands the partner's side back with one shuffle per
-// component (the partner of lane l is served by lane (l - t) mod n).  Every unordered pair is visited
-// once: n(n-1)/2 pairs in ~n/2 steps, against 4 x 8 steps at < 50 % lane use for the staircase of
-// broadcast chunks.  rotmask bit (t-1) set <=> lane skips step t (exclusion, padding, or the duplicate
-// half of step n/2).
+// ---- TASK_DIAG: pairs inside one 32-atom block, full shell -----------------------------------------------
+// Lane l owns atom 32*block + l and meets `ng` groups of 4 atoms of its own block as broadcast j atoms, exactly
+// like a tile pass but WITHOUT a j side: every unordered pair is evaluated by both of its lanes (identical
+// r^2, hence identical s and identical energy terms), so there is no partner force to hand back, no shuffle and
+// no butterfly, and the whole step stays in packed FP32.  17 packed instructions per two pair evaluations against
+// 26 scalar ones + 3 shuffles per pair of the rotation scheme it replaces (profiles/r01_v10: 46 issue slots per
+// rotation step).  Energies are halved.  diagmask bit j: pair (lane, j) is not evaluated (self, exclusion, padding).
 template <int MODE, bool ENERGY>
-__device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams& P, int block, int n, int nsteps,
-                                               int warp, int lane, Energies& E) {
+__device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams& P, int block, int g0, int ng, int warp,
+                                               int lane, Energies& E) {
   const int i0 = block * 32;
+  const PairConst C = make_pair_const<MODE>(P);
   const float4 pi = S.pos[i0 + lane];
   const float kqi = __fmul_rn(pi.w, kElecFactor);
-  const int roff = S.ab_row_off[i0 + lane] + i0 * (int)sizeof(float);
+  const u64 xi = dup2(pi.x), yi = dup2(pi.y), zi = dup2(pi.z), kq2 = dup2(kqi);
+  const int roff = S.ab_row_off[i0 + lane] + (i0 + 4 * g0) * (int)sizeof(float);
   const char* rowa = (const char*)S.ta + roff;
   const char* rowb = (const char*)S.tb + roff;
-  const uint32_t rot = S.rotmask[i0 + lane];
-  float pel = 0.0f, plj = 0.0f, ax = 0.0f, ay = 0.0f, az = 0.0f;
+  const float* sj = S.sx + i0 + 4 * g0;
+  uint32_t dm = S.diagmask[i0 + lane] >> (4 * g0);
+  u64 pel = 0ull, plj = 0ull, ax = 0ull, ay = 0ull, az = 0ull;
 #pragma unroll 1
-  for (int g = 0; g < nsteps; g += 4) {
-    const uint32_t m4 = rot >> g;
+  for (int g = 0; g < ng; ++g) {
+    const ulonglong2 xj = *(const ulonglong2*)(sj + 4 * g), yj = *(const ulonglong2*)(sj + kMaxAtoms + 4 * g),
+                     zj = *(const ulonglong2*)(sj + 2 * kMaxAtoms + 4 * g), qj = *(const ulonglong2*)(sj + 3 * kMaxAtoms + 4 * g);
+    const ulonglong2 aj = *(const ulonglong2*)(rowa + 16 * g), bj = *(const ulonglong2*)(rowb + 16 * g);
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int t = g + u + 1;
-      int jl = lane + t, sl = lane - t;
-      jl = jl >= n ? jl - n : jl;
-      sl = sl < 0 ? sl + n : sl;
-      const float4 q = S.pos[i0 + jl];
-      const float a12 = *(const float*)(rowa + jl * (int)sizeof(float)), nb6 = *(const float*)(rowb + jl * (int)sizeof(float));
-      const float dx = __fsub_rn(pi.x, q.x), dy = __fsub_rn(pi.y, q.y), dz = __fsub_rn(pi.z, q.z);
-      const float sc = pair_eval<MODE, ENERGY>(dx, dy, dz, kqi, q.w, a12, nb6, (m4 >> u) & 1u, P, pel, plj);
-      const float gx = __fmul_rn(sc, dx), gy = __fmul_rn(sc, dy), gz = __fmul_rn(sc, dz);
-      ax = __fadd_rn(ax, gx); ay = __fadd_rn(ay, gy); az = __fadd_rn(az, gz);
-      ax = __fsub_rn(ax, __shfl_sync(0xffffffffu, gx, sl));
-      ay = __fsub_rn(ay, __shfl_sync(0xffffffffu, gy, sl));
-      az = __fsub_rn(az, __shfl_sync(0xffffffffu, gz, sl));
+    for (int k = 0; k < 2; ++k) {
+      const u64 dx = sub2(xi, k ? xj.y : xj.x), dy = sub2(yi, k ? yj.y : yj.x), dz = sub2(zi, k ? zj.y : zj.x);
+      const u64 sc = pair_eval2<MODE, ENERGY>(dx, dy, dz, kqi, kq2, k ? qj.y : qj.x, k ? aj.y : aj.x, k ? bj.y : bj.x,
+                                              (dm >> (2 * k)) & 1u, (dm >> (2 * k + 1)) & 1u, P, C, pel, plj);
+      ax = fma2(sc, dx, ax); ay = fma2(sc, dy, ay); az = fma2(sc, dz, az);
     }
+    dm >>= 4;
   }
   float* f = S.fi + warp * 3 * kMaxAtoms + i0 + lane;
-  f[0] = __fadd_rn(f[0], ax); f[kMaxAtoms] = __fadd_rn(f[kMaxAtoms], ay); f[2 * kMaxAtoms] = __fadd_rn(f[2 * kMaxAtoms], az);
-  if (ENERGY) { E.e[B200MD_E_ELECTROSTATICS] += (double)pel; E.e[B200MD_E_LJ] += (double)plj; }
+  f[0] = __fadd_rn(f[0], hsum2(ax)); f[kMaxAtoms] = __fadd_rn(f[kMaxAtoms], hsum2(ay)); f[2 * kMaxAtoms] = __fadd_rn(f[2 * kMaxAtoms], hsum2(az));
+  if (ENERGY) {
+    float a, b;
+    upk(pel, a, b); E.e[B200MD_E_ELECTROSTATICS] += 0.5 * ((double)a + (double)b);
+    upk(plj, a, b); E.e[B200MD_E_LJ] += 0.5 * ((double)a + (double)b);
+  }
 }
 
 // ---- bonded items: where a force vector goes ---------------------------------------------------------

@@ -46,7 +46,7 @@ struct DevTopo {
   const float* mass;        // [128]
   const int* ab_row_off;    // [128] byte offset of atom's row in the shared-memory 12A / -6B tables
   const uint8_t* mask8;     // [kMaxChunks][128] bit s: pair (i, 8*chunk+s) is NOT evaluated
-  const uint32_t* rotmask;  // [128] bit t-1: lane skips rotation step t of its diagonal block
+  const uint32_t* diagmask;  // [128] bit j: pair (i, 32*block(i) + j) is not evaluated in the diagonal block
   int nbonds, nangles, ndih, nimp, n14;   // n14: 1-4 pairs NOT fused into a dihedral item ("orphans")
   int dih_on, p14_on;                     // proper-torsion part / fused 1-4 part of the dihedral items
   // every bonded item carries the slot ids (atom-major float4 slots) its force vectors go to
@@ -89,7 +89,7 @@ struct Smem {
   float* tb;          // [ntypes][kTabStride] -6 B of (type t, atom j)
   int* ab_row_off;    // [128]
   uint8_t* mask8;     // [kMaxChunks*128]
-  uint32_t* rotmask;  // [128]
+  uint32_t* diagmask;  // [128]
   float* fi;          // [kWarps][3][128]
   float* fj;          // [3][128]
   float* fb;          // [nslots][3] atom-major bonded force slots (slot mode)
@@ -110,8 +110,8 @@ __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(
 constexpr size_t kOffPos = 0;
 constexpr size_t kOffRowOff = kOffPos + sizeof(float4) * kMaxAtoms;
 constexpr size_t kOffMask8 = kOffRowOff + sizeof(int) * kMaxAtoms;
-constexpr size_t kOffRotMask = kOffMask8 + kMaxChunks * kMaxAtoms;
-constexpr size_t kOffFi = kOffRotMask + sizeof(uint32_t) * kMaxAtoms;
+constexpr size_t kOffDiagMask = kOffMask8 + kMaxChunks * kMaxAtoms;
+constexpr size_t kOffFi = kOffDiagMask + sizeof(uint32_t) * kMaxAtoms;
 constexpr size_t kOffFj = kOffFi + sizeof(float) * kWarps * 3 * kMaxAtoms;
 constexpr size_t kOffGstart = kOffFj + sizeof(float) * 3 * kMaxAtoms;
 constexpr size_t kOffTasks = kOffGstart + 272;
@@ -131,7 +131,7 @@ __host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, i
     s->pos = (float4*)(base + kOffPos);
     s->ab_row_off = (int*)(base + kOffRowOff);
     s->mask8 = (uint8_t*)(base + kOffMask8);
-    s->rotmask = (uint32_t*)(base + kOffRotMask);
+    s->diagmask = (uint32_t*)(base + kOffDiagMask);
     s->fi = (float*)(base + kOffFi);
     s->fj = (float*)(base + kOffFj);
     s->gstart = (uint16_t*)(base + kOffGstart);
