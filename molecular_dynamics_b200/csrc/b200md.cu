@@ -294,6 +294,48 @@ void build_terms(int nitems, int nterms, const int32_t* owner, const float* prm,
   }
 }
 
+// Orders the items of one bonded kind so that the 32 lanes of a chunk touch distinct shared-memory banks at every
+// atom position: the fused integrator accumulates bonded forces with shared-memory atomics (bank = atom mod 32),
+// which serialise on bank and on address collisions (4.6 wavefronts per ATOMS in topology order, profiles/r01_v11),
+// and the LDS.128 position gathers want the 8 lanes of a quarter warp on distinct atoms mod 8.  `order` must
+// already be grouped by `key` (items of equal key stay contiguous, so chunks keep running uniform term loops).
+std::vector<int> spread_banks(const std::vector<int>& order, const int32_t* idx, int arity, const std::vector<long long>& key) {
+  std::vector<int> out;
+  std::vector<char> used(order.size(), 0);
+  uint32_t busy[4] = {0, 0, 0, 0}, busy8[4] = {0, 0, 0, 0};
+  int fill = 0;
+  size_t g0 = 0;
+  while (g0 < order.size()) {
+    size_t g1 = g0;
+    while (g1 < order.size() && key[order[g1]] == key[order[g0]]) ++g1;
+    for (size_t left = g1 - g0; left > 0; --left) {
+      if (fill == 32) { fill = 0; for (int k = 0; k < 4; ++k) busy[k] = 0; }
+      if (fill % 8 == 0) for (int k = 0; k < 4; ++k) busy8[k] = 0;
+      long best = -1;
+      int bestc = 1 << 30;
+      for (size_t m = g0; m < g1 && bestc > 0; ++m) {
+        if (used[m]) continue;
+        int c = 0;
+        for (int k = 0; k < arity; ++k) {
+          const int a = idx[arity * order[m] + k];
+          c += 3 * ((busy[k] >> (a & 31)) & 1u) + ((busy8[k] >> (a & 7)) & 1u);
+        }
+        if (c < bestc) { bestc = c; best = (long)m; }
+      }
+      used[best] = 1;
+      out.push_back(order[best]);
+      for (int k = 0; k < arity; ++k) {
+        const int a = idx[arity * order[best] + k];
+        busy[k] |= 1u << (a & 31);
+        busy8[k] |= 1u << (a & 7);
+      }
+      ++fill;
+    }
+    g0 = g1;
+  }
+  return out;
+}
+
 template <typename K>
 int query_occupancy(K kernel, int smem) {
   if (smem > 48 * 1024) cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -391,21 +433,39 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
     for (int k = 0; k < d->ndihedrals; ++k) key[k] = ((long long)special[k] << 40) | ((long long)nterm[k] << 20) | maxper[k];
     for (int k = 0; k < d->ndihedrals; ++k) dperm[k] = k;
     std::stable_sort(dperm.begin(), dperm.end(), [&](int a, int b) { return key[a] < key[b]; });
+    dperm = spread_banks(dperm, d->dihedral_idx, 4, key);
     for (int k = 0; k < d->ndihedrals; ++k) dinv[dperm[k]] = k;
   }
   std::vector<int32_t> dihedral_idx_s((size_t)4 * std::max(d->ndihedrals, 1)), dihedral_owner_s(std::max(d->ndihedral_terms, 1));
   for (int k = 0; k < d->ndihedrals; ++k)
     for (int c = 0; c < 4; ++c) dihedral_idx_s[4 * k + c] = d->dihedral_idx[4 * dperm[k] + c];
   for (int t = 0; t < d->ndihedral_terms; ++t) dihedral_owner_s[t] = dinv[d->dihedral_term_owner[t]];
+  // bonds and angles in bank-spread order too (energies are sums, the slot order stays fixed: results are deterministic)
+  std::vector<int32_t> bond_idx_p((size_t)2 * std::max(d->nbonds, 1)), angle_idx_p((size_t)3 * std::max(d->nangles, 1));
+  std::vector<float> bond_prm_p((size_t)2 * std::max(d->nbonds, 1)), angle_prm_p((size_t)2 * std::max(d->nangles, 1));
+  {
+    std::vector<int> ob(d->nbonds), oa(d->nangles);
+    for (int k = 0; k < d->nbonds; ++k) ob[k] = k;
+    for (int k = 0; k < d->nangles; ++k) oa[k] = k;
+    ob = spread_banks(ob, d->bond_idx, 2, std::vector<long long>(d->nbonds, 0));
+    oa = spread_banks(oa, d->angle_idx, 3, std::vector<long long>(d->nangles, 0));
+    for (int k = 0; k < d->nbonds; ++k) {
+      for (int c = 0; c < 2; ++c) { bond_idx_p[2 * k + c] = d->bond_idx[2 * ob[k] + c]; bond_prm_p[2 * k + c] = d->bond_prm[2 * ob[k] + c]; }
+    }
+    for (int k = 0; k < d->nangles; ++k) {
+      for (int c = 0; c < 3; ++c) angle_idx_p[3 * k + c] = d->angle_idx[3 * oa[k] + c];
+      for (int c = 0; c < 2; ++c) angle_prm_p[2 * k + c] = d->angle_prm[2 * oa[k] + c];
+    }
+  }
   std::vector<uint32_t> bond_idx(d->nbonds), angle_idx(d->nangles), dih_idx(d->ndihedrals), imp_idx(d->nimpropers);
   std::vector<float2> bond_prm(d->nbonds), angle_prm(d->nangles);
   for (int k = 0; k < d->nbonds; ++k) {
-    bond_idx[k] = pack4(d->bond_idx + 2 * k, 2);
-    bond_prm[k] = make_float2(d->bond_prm[2 * k], d->bond_prm[2 * k + 1]);
+    bond_idx[k] = pack4(bond_idx_p.data() + 2 * k, 2);
+    bond_prm[k] = make_float2(bond_prm_p[2 * k], bond_prm_p[2 * k + 1]);
   }
   for (int k = 0; k < d->nangles; ++k) {
-    angle_idx[k] = pack4(d->angle_idx + 3 * k, 3);
-    angle_prm[k] = make_float2(d->angle_prm[2 * k], d->angle_prm[2 * k + 1]);
+    angle_idx[k] = pack4(angle_idx_p.data() + 3 * k, 3);
+    angle_prm[k] = make_float2(angle_prm_p[2 * k], angle_prm_p[2 * k + 1]);
   }
   for (int k = 0; k < d->ndihedrals; ++k) dih_idx[k] = pack4(dihedral_idx_s.data() + 4 * k, 4);
   for (int k = 0; k < d->nimpropers; ++k) imp_idx[k] = pack4(d->improper_idx + 4 * k, 4);
@@ -452,7 +512,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   }
   const int counts[6] = {0, d->nbonds, d->nangles, d->ndihedrals, d->nimpropers, (int)p14_idx.size()};
   const int arity[6] = {0, 2, 3, 4, 4, 2};
-  const int32_t* idxs[6] = {nullptr, d->bond_idx, d->angle_idx, dihedral_idx_s.data(), d->improper_idx, orphan_atoms.data()};
+  const int32_t* idxs[6] = {nullptr, bond_idx_p.data(), angle_idx_p.data(), dihedral_idx_s.data(), d->improper_idx, orphan_atoms.data()};
   std::vector<int> per_atom_count(kMaxAtoms, 0);
   for (int ty = 1; ty < 6; ++ty)
     for (int it = 0; it < counts[ty] * arity[ty]; ++it) per_atom_count[idxs[ty][it]]++;
@@ -507,13 +567,23 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   std::stable_sort(all.begin(), all.end(), [](const Task& a, const Task& b) { return a.cost > b.cost; });
   std::vector<uint32_t> tasks((size_t)kWarps * kMaxTasks, 0);
   int load[kWarps] = {0, 0, 0, 0};
-  for (int w = 0; w < kWarps; ++w) T.ntasks[w] = 0;
+  std::vector<std::vector<uint32_t>> mine(kWarps);
   for (const Task& t : all) {
     int w = 0;
     for (int k = 1; k < kWarps; ++k) if (load[k] < load[w]) w = k;
-    if (T.ntasks[w] >= kMaxTasks) { delete topo; fail(B200MD_ERR_UNSUPPORTED, "too many tasks per warp"); return nullptr; }
-    tasks[(size_t)w * kMaxTasks + T.ntasks[w]++] = t.word;
+    if ((int)mine[w].size() >= kMaxTasks - 1) { delete topo; fail(B200MD_ERR_UNSUPPORTED, "too many tasks per warp"); return nullptr; }
+    mine[w].push_back(t.word);
     load[w] += t.cost;
+  }
+  // each warp runs its tasks kind by kind (run_tasks): tiles, diagonal blocks, dihedrals, impropers, angles, bonds, 1-4
+  const uint32_t kind_order[kNumKinds] = {TASK_TILE, TASK_DIAG, TASK_DIHEDRAL, TASK_IMPROPER, TASK_ANGLE, TASK_BOND, TASK_P14};
+  for (int w = 0; w < kWarps; ++w) {
+    int n = 0;
+    for (int k = 0; k < kNumKinds; ++k) {
+      for (uint32_t word : mine[w]) if ((word & 0xff) == kind_order[k]) tasks[(size_t)w * kMaxTasks + n++] = word;
+      T.kend[w][k] = n;
+    }
+    T.kend[w][kNumKinds] = n;
   }
 
   // ---- upload --------------------------------------------------------------------------------------

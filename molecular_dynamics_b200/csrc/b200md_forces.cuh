@@ -450,32 +450,38 @@ __device__ __forceinline__ void p14_task(const Smem& S, const DevTopo& T, const 
 }
 
 // ---- all tasks of this warp for one force evaluation; positions must be in S.pos ------------------
+// The warp's static task list is sorted by kind on the host (T.kend[warp][k] = end of the k-th run), so every kind
+// is a tight loop around its own body: no switch, and the next task word is fetched while the current task runs
+// (the fetch -> decode -> branch chain of a switch-per-task loop cost 33 issue slots and ~150 cycles of exposed
+// latency per task, profiles/r01_v11).
 template <int MODE, bool ENERGY, bool FIXED>
 __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const ForceParams& P, int warp, int lane,
                                           Energies& E, uint32_t& flag) {
-  const int nt = T.ntasks[warp];
-#pragma unroll 1
-  for (int t = 0; t < nt; ++t) {
-    const uint32_t task = S.tasks[warp * kMaxTasks + t];
-    const uint32_t kind = task & 0xff, chunk = (task >> 8) & 0xffff, passes = task >> 24;
-    const int item = chunk * 32 + lane;
-    switch (kind) {
-      case TASK_TILE: tile_task<MODE, ENERGY>(S, P, chunk, passes, warp, lane, E); break;
-      case TASK_DIAG: tile_diag_task<MODE, ENERGY>(S, P, chunk & 0xff, (chunk >> 8) & 0xff, passes, warp, lane, E); break;
-      case TASK_BOND: bond_task<ENERGY, FIXED>(S, T, P, item, E, flag); break;
-      case TASK_ANGLE: angle_task<ENERGY, FIXED>(S, T, item, E, flag); break;
-      case TASK_DIHEDRAL:
-        torsion_task<ENERGY, FIXED>(S, P, T.dih_on != 0, T.p14_on != 0, item, T.ndih, T.dih_idx, T.dih_terms, T.dih_term_prm,
-                             T.dih_slot, T.dih_p14, E.e[B200MD_E_DIHEDRALS], E, flag);
-        break;
-      case TASK_IMPROPER:
-        torsion_task<ENERGY, FIXED>(S, P, true, false, item, T.nimp, T.imp_idx, T.imp_terms, T.imp_term_prm, T.imp_slot,
-                             nullptr, E.e[B200MD_E_IMPROPERS], E, flag);
-        break;
-      case TASK_P14: p14_task<ENERGY, FIXED>(S, T, P, item, E, flag); break;
-      default: break;
-    }
+  const uint32_t* tk = S.tasks + warp * kMaxTasks;
+  int t = 0;
+  uint32_t next = tk[0];
+#define B200MD_TASK_LOOP(K, BODY)                                                     \
+  {                                                                                   \
+    const int end = T.kend[warp][K];                                                  \
+    _Pragma("unroll 1") for (; t < end;) {                                            \
+      const uint32_t task = next;                                                     \
+      next = tk[++t];                                                                 \
+      const uint32_t chunk = (task >> 8) & 0xffff, passes = task >> 24;               \
+      const int item = chunk * 32 + lane;                                             \
+      (void)passes; (void)item;                                                       \
+      BODY;                                                                           \
+    }                                                                                 \
   }
+  B200MD_TASK_LOOP(0, (tile_task<MODE, ENERGY>(S, P, chunk, passes, warp, lane, E)))
+  B200MD_TASK_LOOP(1, (tile_diag_task<MODE, ENERGY>(S, P, chunk & 0xff, (chunk >> 8) & 0xff, passes, warp, lane, E)))
+  B200MD_TASK_LOOP(2, (torsion_task<ENERGY, FIXED>(S, P, T.dih_on != 0, T.p14_on != 0, item, T.ndih, T.dih_idx, T.dih_terms,
+                                                   T.dih_term_prm, T.dih_slot, T.dih_p14, E.e[B200MD_E_DIHEDRALS], E, flag)))
+  B200MD_TASK_LOOP(3, (torsion_task<ENERGY, FIXED>(S, P, true, false, item, T.nimp, T.imp_idx, T.imp_terms, T.imp_term_prm,
+                                                   T.imp_slot, nullptr, E.e[B200MD_E_IMPROPERS], E, flag)))
+  B200MD_TASK_LOOP(4, (angle_task<ENERGY, FIXED>(S, T, item, E, flag)))
+  B200MD_TASK_LOOP(5, (bond_task<ENERGY, FIXED>(S, T, P, item, E, flag)))
+  B200MD_TASK_LOOP(6, (p14_task<ENERGY, FIXED>(S, T, P, item, E, flag)))
+#undef B200MD_TASK_LOOP
 }
 
 // ---- SMD end-to-end bias (potcalc.py:75-89; force = -dE/dr): one lane, during the task phase -------

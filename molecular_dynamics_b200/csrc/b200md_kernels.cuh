@@ -30,6 +30,8 @@ constexpr float kBoltzman = 0.001987191f;           // upstream torchmd.integrat
 
 // task kinds (one task = one warp-wide unit of work, scheduled statically on the host)
 enum TaskKind : uint32_t { TASK_TILE = 0, TASK_BOND = 1, TASK_ANGLE = 2, TASK_DIHEDRAL = 3, TASK_IMPROPER = 4, TASK_P14 = 5, TASK_DIAG = 6 };
+// execution order of the kinds inside a warp's task list
+constexpr int kNumKinds = 7;
 __host__ __device__ inline uint32_t make_task(uint32_t kind, uint32_t chunk, uint32_t passes) {
   return kind | (chunk << 8) | (passes << 24);
 }
@@ -59,7 +61,7 @@ struct DevTopo {
   int nslots;
   const uint16_t* gather_start;  // [129]: slots of atom a are [gather_start[a], gather_start[a+1])
   const uint32_t* tasks;  // [kWarps][kMaxTasks]
-  int ntasks[kWarps];
+  int kend[kWarps][8];    // per warp: end index of the k-th run of its kind-sorted task list (kTaskOrder)
   int smem_bytes, smem_bytes_fixed;
 };
 
