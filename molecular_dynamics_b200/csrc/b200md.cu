@@ -86,12 +86,12 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
     if (flag && status != nullptr) atomicOr(status + r, flag);
     Energies E;
     E.clear();
-    run_tasks<MODE, true, false>(S, T, P, warp, lane, E, flag);
+    run_tasks<MODE, true, false>(S, T, P, warp, lane, E);
     if (P.smd_on && tid == kThreads - 1) smd_task(S, P, P.smd_centers ? __ldg(P.smd_centers + r) : P.smd_c0);
     __syncthreads();
     if (tid < N) {
       float fx, fy, fz;
-      gather_forces<false>(S, P, tid, fx, fy, fz);
+      gather_forces<false>(S, P, tid, fx, fy, fz, flag);
       float* f = forces + (r * N + tid) * 3;
       f[0] = fx; f[1] = fy; f[2] = fz;
     }
@@ -157,9 +157,9 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       Energies E;
       if (report) {
         E.clear();
-        run_tasks<MODE, true, true>(S, T, P, warp, lane, E, flag);
+        run_tasks<MODE, true, true>(S, T, P, warp, lane, E);
       } else {
-        run_tasks<MODE, false, true>(S, T, P, warp, lane, E, flag);
+        run_tasks<MODE, false, true>(S, T, P, warp, lane, E);
       }
       if (P.smd_on && tid == kThreads - 1) smd_task(S, P, (float)((double)P.smd_c0 + (double)P.smd_rate * (double)(gstep + 1)));
       __syncthreads();
@@ -167,7 +167,7 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
         const float4 pp = S.pos[tid], vv = S.vel[tid];
         x = pp.x; y = pp.y; z = pp.z; vx = vv.x; vy = vv.y; vz = vv.z;
       }
-      if (live) gather_forces<true>(S, P, tid, fx, fy, fz);
+      if (live) gather_forces<true>(S, P, tid, fx, fy, fz, flag);
       if (langevin) {  // vel += -gamma vel dt + vcoeff N(0,1)
         float n[3];
         normal3(I.seed, (unsigned long long)(I.replica0 + r), (uint32_t)tid, gstep, n);
@@ -294,27 +294,30 @@ void build_terms(int nitems, int nterms, const int32_t* owner, const float* prm,
   }
 }
 
-// Orders the items of one bonded kind so that the 32 lanes of a chunk touch distinct shared-memory banks at every
-// atom position: the fused integrator accumulates bonded forces with shared-memory atomics (bank = atom mod 32),
-// which serialise on bank and on address collisions (4.6 wavefronts per ATOMS in topology order, profiles/r01_v11),
-// and the LDS.128 position gathers want the 8 lanes of a quarter warp on distinct atoms mod 8.  `order` must
-// already be grouped by `key` (items of equal key stay contiguous, so chunks keep running uniform term loops).
-std::vector<int> spread_banks(const std::vector<int>& order, const int32_t* idx, int arity, const std::vector<long long>& key) {
+// Orders the items of one bonded kind into consecutive lane sets (`sets`: sizes, <= 32 each) whose members touch
+// distinct shared-memory banks at every atom position: the fused integrator accumulates bonded forces with
+// shared-memory atomics (bank = atom mod 32), which serialise on bank and on address collisions (4.6 wavefronts per
+// ATOMS in topology order, profiles/r01_v11), and the position gathers want the 8 lanes of a quarter warp on
+// distinct atoms mod 8.  `order` must be sorted by `key`; a set draws from the lowest keys still available (a window
+// of its own size), so chunks keep near-uniform periodicity bounds.
+std::vector<int> spread_banks(const std::vector<int>& order, const int32_t* idx, int arity, const std::vector<long long>& key,
+                              const std::vector<int>& sets) {
+  (void)key;
   std::vector<int> out;
   std::vector<char> used(order.size(), 0);
-  uint32_t busy[4] = {0, 0, 0, 0}, busy8[4] = {0, 0, 0, 0};
-  int fill = 0;
-  size_t g0 = 0;
-  while (g0 < order.size()) {
-    size_t g1 = g0;
-    while (g1 < order.size() && key[order[g1]] == key[order[g0]]) ++g1;
-    for (size_t left = g1 - g0; left > 0; --left) {
-      if (fill == 32) { fill = 0; for (int k = 0; k < 4; ++k) busy[k] = 0; }
+  size_t first = 0;  // first unused position
+  for (int size : sets) {
+    uint32_t busy[4] = {0, 0, 0, 0}, busy8[4] = {0, 0, 0, 0};
+    for (int fill = 0; fill < size; ++fill) {
       if (fill % 8 == 0) for (int k = 0; k < 4; ++k) busy8[k] = 0;
+      while (first < order.size() && used[first]) ++first;
+      // candidates: the next 2 * (remaining lanes of this set) unused items in key order
+      const int window = 2 * (size - fill) + 8;
       long best = -1;
-      int bestc = 1 << 30;
-      for (size_t m = g0; m < g1 && bestc > 0; ++m) {
+      int bestc = 1 << 30, seen = 0;
+      for (size_t m = first; m < order.size() && seen < window && bestc > 0; ++m) {
         if (used[m]) continue;
+        ++seen;
         int c = 0;
         for (int k = 0; k < arity; ++k) {
           const int a = idx[arity * order[m] + k];
@@ -322,6 +325,7 @@ std::vector<int> spread_banks(const std::vector<int>& order, const int32_t* idx,
         }
         if (c < bestc) { bestc = c; best = (long)m; }
       }
+      if (best < 0) break;
       used[best] = 1;
       out.push_back(order[best]);
       for (int k = 0; k < arity; ++k) {
@@ -329,9 +333,7 @@ std::vector<int> spread_banks(const std::vector<int>& order, const int32_t* idx,
         busy[k] |= 1u << (a & 31);
         busy8[k] |= 1u << (a & 7);
       }
-      ++fill;
     }
-    g0 = g1;
   }
   return out;
 }
@@ -371,7 +373,6 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   topo->natoms = N;
   DevTopo& T = topo->dev;
   T.natoms = N; T.ntypes = NT; T.nchunks = (N + kChunk - 1) / kChunk;
-  T.nbonds = d->nbonds; T.nangles = d->nangles; T.ndih = d->ndihedrals; T.nimp = d->nimpropers; T.n14 = d->n14;
 
   // ---- exclusion mask from the pair list (= Forces.ava_idx) ----------------------------------
   std::vector<uint8_t> allowed((size_t)kMaxAtoms * kMaxAtoms, 0);
@@ -416,136 +417,227 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   }
 
   // ---- bonded items ------------------------------------------------------------------------------
-  // Dihedral items are processed in an internal order sorted by (number of terms, branch kind, largest
-  // periodicity), so the 32 lanes of a chunk run the same term loop; par.dihedrals itself is untouched.
-  std::vector<int> dperm(d->ndihedrals), dinv(d->ndihedrals);
-  {
-    std::vector<long long> key(d->ndihedrals, 0);
-    std::vector<int> nterm(d->ndihedrals, 0), maxper(d->ndihedrals, 0), special(d->ndihedrals, 0);
-    for (int t = 0; t < d->ndihedral_terms; ++t) {
-      const int o = d->dihedral_term_owner[t];
-      if (o < 0 || o >= d->ndihedrals) { delete topo; fail(B200MD_ERR_INVALID_ARGUMENT, "dihedral term owner out of range"); return nullptr; }
-      const float per = d->dihedral_term_prm[3 * t + 2];
-      nterm[o]++;
-      const bool fast = !d->dihedral_term_harmonic[t] && per >= 1.0f && per <= 8.0f && per == floorf(per);
-      if (!fast) special[o] = 1; else maxper[o] = std::max(maxper[o], (int)per);
+  // Bonds, angles, proper torsions with integer periodicity and 1-4 pairs are evaluated TWO ITEMS PER LANE in
+  // packed FP32 (b200md_forces.cuh): lane l of chunk c holds items A = seq[64c + l] and B = seq[64c + 32 + l].
+  // The 32 A items (and the 32 B items) of a chunk are chosen so that they touch distinct shared-memory banks
+  // (spread_banks).  Torsions the packed path cannot express (CHARMM harmonic slices, non-integer or > 6
+  // periodicities) and all impropers go to the "general" list, evaluated one item per lane by torsion_task.
+  const int ND = d->ndihedrals;
+  std::vector<std::vector<int>> dterms(ND);
+  for (int t = 0; t < d->ndihedral_terms; ++t) {
+    const int o = d->dihedral_term_owner[t];
+    if (o < 0 || o >= ND) { delete topo; fail(B200MD_ERR_INVALID_ARGUMENT, "dihedral term owner out of range"); return nullptr; }
+    dterms[o].push_back(t);
+  }
+  for (int t = 0; t < d->nimproper_terms; ++t)
+    if (d->improper_term_owner[t] < 0 || d->improper_term_owner[t] >= d->nimpropers) {
+      delete topo; fail(B200MD_ERR_INVALID_ARGUMENT, "improper term owner out of range"); return nullptr;
     }
-    for (int k = 0; k < d->ndihedrals; ++k) key[k] = ((long long)special[k] << 40) | ((long long)nterm[k] << 20) | maxper[k];
-    for (int k = 0; k < d->ndihedrals; ++k) dperm[k] = k;
-    std::stable_sort(dperm.begin(), dperm.end(), [&](int a, int b) { return key[a] < key[b]; });
-    dperm = spread_banks(dperm, d->dihedral_idx, 4, key);
-    for (int k = 0; k < d->ndihedrals; ++k) dinv[dperm[k]] = k;
-  }
-  std::vector<int32_t> dihedral_idx_s((size_t)4 * std::max(d->ndihedrals, 1)), dihedral_owner_s(std::max(d->ndihedral_terms, 1));
-  for (int k = 0; k < d->ndihedrals; ++k)
-    for (int c = 0; c < 4; ++c) dihedral_idx_s[4 * k + c] = d->dihedral_idx[4 * dperm[k] + c];
-  for (int t = 0; t < d->ndihedral_terms; ++t) dihedral_owner_s[t] = dinv[d->dihedral_term_owner[t]];
-  // bonds and angles in bank-spread order too (energies are sums, the slot order stays fixed: results are deterministic)
-  std::vector<int32_t> bond_idx_p((size_t)2 * std::max(d->nbonds, 1)), angle_idx_p((size_t)3 * std::max(d->nangles, 1));
-  std::vector<float> bond_prm_p((size_t)2 * std::max(d->nbonds, 1)), angle_prm_p((size_t)2 * std::max(d->nangles, 1));
-  {
-    std::vector<int> ob(d->nbonds), oa(d->nangles);
-    for (int k = 0; k < d->nbonds; ++k) ob[k] = k;
-    for (int k = 0; k < d->nangles; ++k) oa[k] = k;
-    ob = spread_banks(ob, d->bond_idx, 2, std::vector<long long>(d->nbonds, 0));
-    oa = spread_banks(oa, d->angle_idx, 3, std::vector<long long>(d->nangles, 0));
-    for (int k = 0; k < d->nbonds; ++k) {
-      for (int c = 0; c < 2; ++c) { bond_idx_p[2 * k + c] = d->bond_idx[2 * ob[k] + c]; bond_prm_p[2 * k + c] = d->bond_prm[2 * ob[k] + c]; }
+  std::vector<int> dclass(ND, 0), dmaxper(ND, 1);  // 0: packed series, 1: general, 2: every k is 0 (only its 1-4 pair survives)
+  for (int q = 0; q < ND; ++q) {
+    bool fast = true, zero = true;
+    for (int t : dterms[q]) {
+      const float k0 = d->dihedral_term_prm[3 * t], per = d->dihedral_term_prm[3 * t + 2];
+      if (k0 != 0.0f) zero = false;
+      if (d->dihedral_term_harmonic[t] || !(per >= 1.0f && per <= (float)kMaxPer && per == floorf(per))) fast = false;
+      else dmaxper[q] = std::max(dmaxper[q], (int)per);
     }
-    for (int k = 0; k < d->nangles; ++k) {
-      for (int c = 0; c < 3; ++c) angle_idx_p[3 * k + c] = d->angle_idx[3 * oa[k] + c];
-      for (int c = 0; c < 2; ++c) angle_prm_p[2 * k + c] = d->angle_prm[2 * oa[k] + c];
-    }
+    dclass[q] = zero ? 2 : (fast ? 0 : 1);
   }
-  std::vector<uint32_t> bond_idx(d->nbonds), angle_idx(d->nangles), dih_idx(d->ndihedrals), imp_idx(d->nimpropers);
-  std::vector<float2> bond_prm(d->nbonds), angle_prm(d->nangles);
-  for (int k = 0; k < d->nbonds; ++k) {
-    bond_idx[k] = pack4(bond_idx_p.data() + 2 * k, 2);
-    bond_prm[k] = make_float2(bond_prm_p[2 * k], bond_prm_p[2 * k + 1]);
-  }
-  for (int k = 0; k < d->nangles; ++k) {
-    angle_idx[k] = pack4(angle_idx_p.data() + 3 * k, 3);
-    angle_prm[k] = make_float2(angle_prm_p[2 * k], angle_prm_p[2 * k + 1]);
-  }
-  for (int k = 0; k < d->ndihedrals; ++k) dih_idx[k] = pack4(dihedral_idx_s.data() + 4 * k, 4);
-  for (int k = 0; k < d->nimpropers; ++k) imp_idx[k] = pack4(d->improper_idx + 4 * k, 4);
-  // 1-4 pairs (forces.py:176-226): fused into the first dihedral item whose end atoms they are; pairs
-  // without such a dihedral stay in their own ("orphan") list.  Stored as (12 A/scnb, 6 B/scnb, K qi qj/scee).
-  std::vector<float4> dih_p14(std::max(d->ndihedrals, 1), make_float4(0.f, 0.f, 0.f, 0.f)), p14_prm;
-  std::vector<uint32_t> p14_idx;
-  std::vector<int> orphan_src;
+  std::vector<int> fastd, gend;
+  for (int q = 0; q < ND; ++q) (dclass[q] == 0 ? fastd : gend).push_back(q);
+  gend.erase(std::remove_if(gend.begin(), gend.end(), [&](int q) { return dclass[q] == 2; }), gend.end());
+  const int nspec = (int)gend.size();
+
+  // 1-4 pairs (forces.py:176-226): fused into the first packed dihedral whose end atoms they are, else own list
+  std::vector<int> own14(ND, -1), list14;
   for (int k = 0; k < d->n14; ++k) {
     const int i = d->idx14[2 * k], j = d->idx14[2 * k + 1];
-    const float* p = d->prm14 + 4 * k;  // A, B, scnb, scee (forces.py:197-200)
-    const double qi = d->charge ? d->charge[i] : 0.0, qj = d->charge ? d->charge[j] : 0.0;
-    float4 prm = make_float4((float)(12.0 * (double)p[0] / p[2]), (float)(6.0 * (double)p[1] / p[2]),
-                             (float)(332.06371307417066 * qi * qj / p[3]), 1.0f);
     int owner = -1;
-    for (int q = 0; q < d->ndihedrals && owner < 0; ++q) {
-      const int32_t* a = dihedral_idx_s.data() + 4 * q;
-      if (dih_p14[q].w == 0.0f && ((a[0] == i && a[3] == j) || (a[0] == j && a[3] == i))) owner = q;
+    for (int q : fastd) {
+      const int32_t* a4 = d->dihedral_idx + 4 * q;
+      if (own14[q] < 0 && ((a4[0] == i && a4[3] == j) || (a4[0] == j && a4[3] == i))) { owner = q; break; }
     }
-    if (owner >= 0) {
-      dih_p14[owner] = prm;
-    } else {
-      p14_idx.push_back(pack4(d->idx14 + 2 * k, 2));
-      p14_prm.push_back(prm);
-      orphan_src.push_back(k);
-    }
+    if (owner >= 0) own14[owner] = k; else list14.push_back(k);
   }
-  T.n14 = (int)p14_idx.size();
-  T.dih_on = 1;
-  T.p14_on = 1;
-  std::vector<uint2> dih_terms, imp_terms;
-  std::vector<float4> dih_tp, imp_tp;
-  build_terms(d->ndihedrals, d->ndihedral_terms, dihedral_owner_s.data(), d->dihedral_term_prm,
-              d->dihedral_term_harmonic, dih_terms, dih_tp);
-  build_terms(d->nimpropers, d->nimproper_terms, d->improper_term_owner, d->improper_term_prm,
-              d->improper_term_harmonic, imp_terms, imp_tp);
+  auto prm14 = [&](int k, float out[3]) {  // 12 A / scnb, -6 B / scnb, K qi qj / scee  (forces.py:197-226)
+    const float* p4 = d->prm14 + 4 * k;
+    const double qi = d->charge ? d->charge[d->idx14[2 * k]] : 0.0, qj = d->charge ? d->charge[d->idx14[2 * k + 1]] : 0.0;
+    out[0] = (float)(12.0 * (double)p4[0] / p4[2]);
+    out[1] = (float)(-6.0 * (double)p4[1] / p4[2]);
+    out[2] = (float)(332.06371307417066 * qi * qj / p4[3]);
+  };
 
-  // ---- atom-major force slots: contribution (item, position) of atom a gets the next slot of a -----
-  // (fixed order bonds, angles, dihedrals, impropers, orphan 1-4 => deterministic sums in the gather)
-  std::vector<int> orphan_atoms(2 * p14_idx.size());
-  for (size_t k = 0; k < p14_idx.size(); ++k) {
-    orphan_atoms[2 * k] = d->idx14[2 * orphan_src[k]];
-    orphan_atoms[2 * k + 1] = d->idx14[2 * orphan_src[k] + 1];
+  // item sequences (A / B sets of 32) per packed kind
+  struct Packing { std::vector<int> seq; std::vector<int> lane_a, lane_b; int nchunks = 0, npairs = 0; std::vector<int> chunk_key; };
+  auto pack_kind = [&](std::vector<int> items, const int32_t* idx, int arity, const std::vector<long long>& key) {
+    Packing K;
+    std::stable_sort(items.begin(), items.end(), [&](int x, int y) { return key[x] < key[y]; });
+    const int M = (int)items.size();
+    K.nchunks = (M + 63) / 64;
+    std::vector<int> sets;
+    for (int c = 0; c < K.nchunks; ++c) {
+      const int r = std::min(64, M - 64 * c);
+      const int na = r == 64 ? 32 : (r + 1) / 2;
+      sets.push_back(na);
+      sets.push_back(r - na);
+    }
+    K.seq = spread_banks(items, idx, arity, key, sets);
+    K.lane_a.assign((size_t)K.nchunks * 32, -1);
+    K.lane_b.assign((size_t)K.nchunks * 32, -1);
+    K.chunk_key.assign(K.nchunks, 0);
+    int pos = 0;
+    for (int c = 0; c < K.nchunks; ++c) {
+      for (int l = 0; l < sets[2 * c]; ++l) K.lane_a[(size_t)c * 32 + l] = K.seq[pos++];
+      for (int l = 0; l < sets[2 * c + 1]; ++l) K.lane_b[(size_t)c * 32 + l] = K.seq[pos++];
+      K.npairs = c * 32 + sets[2 * c];
+    }
+    return K;
+  };
+  std::vector<int> allb(d->nbonds), alla(d->nangles);
+  for (int k = 0; k < d->nbonds; ++k) allb[k] = k;
+  for (int k = 0; k < d->nangles; ++k) alla[k] = k;
+  std::vector<long long> dkey(ND, 0);
+  for (int q = 0; q < ND; ++q) dkey[q] = dmaxper[q];
+  // the 1-4 list works on its own index space
+  std::vector<int32_t> idx14l((size_t)2 * std::max<size_t>(list14.size(), 1));
+  std::vector<int> all14(list14.size());
+  for (size_t k = 0; k < list14.size(); ++k) { all14[k] = (int)k; idx14l[2 * k] = d->idx14[2 * list14[k]]; idx14l[2 * k + 1] = d->idx14[2 * list14[k] + 1]; }
+  const Packing PB = pack_kind(allb, d->bond_idx, 2, std::vector<long long>(std::max(d->nbonds, 1), 0));
+  const Packing PA = pack_kind(alla, d->angle_idx, 3, std::vector<long long>(std::max(d->nangles, 1), 0));
+  const Packing PD = pack_kind(fastd, d->dihedral_idx, 4, dkey);
+  const Packing PP = pack_kind(all14, idx14l.data(), 2, std::vector<long long>(std::max<size_t>(list14.size(), 1), 0));
+  T.nbond2 = PB.npairs; T.nangle2 = PA.npairs; T.ndih2 = PD.npairs; T.n14_2 = PP.npairs;
+
+  // general list: special dihedrals first, then the impropers
+  const int NG = nspec + d->nimpropers;
+  T.ngen = NG; T.nspec = nspec; T.gen_begin = 0; T.gen_end = NG;
+  std::vector<int32_t> gen_idx4((size_t)4 * std::max(NG, 1));
+  std::vector<int32_t> gen_owner;
+  std::vector<float> gen_prm;
+  std::vector<int32_t> gen_harm;
+  for (int g = 0; g < nspec; ++g) {
+    for (int c = 0; c < 4; ++c) gen_idx4[4 * g + c] = d->dihedral_idx[4 * gend[g] + c];
+    for (int t : dterms[gend[g]]) {
+      gen_owner.push_back(g); gen_harm.push_back(d->dihedral_term_harmonic[t]);
+      for (int c = 0; c < 3; ++c) gen_prm.push_back(d->dihedral_term_prm[3 * t + c]);
+    }
   }
-  const int counts[6] = {0, d->nbonds, d->nangles, d->ndihedrals, d->nimpropers, (int)p14_idx.size()};
-  const int arity[6] = {0, 2, 3, 4, 4, 2};
-  const int32_t* idxs[6] = {nullptr, bond_idx_p.data(), angle_idx_p.data(), dihedral_idx_s.data(), d->improper_idx, orphan_atoms.data()};
+  for (int k = 0; k < d->nimpropers; ++k)
+    for (int c = 0; c < 4; ++c) gen_idx4[4 * (nspec + k) + c] = d->improper_idx[4 * k + c];
+  for (int t = 0; t < d->nimproper_terms; ++t) {
+    gen_owner.push_back(nspec + d->improper_term_owner[t]); gen_harm.push_back(d->improper_term_harmonic[t]);
+    for (int c = 0; c < 3; ++c) gen_prm.push_back(d->improper_term_prm[3 * t + c]);
+  }
+  std::vector<uint2> gen_terms;
+  std::vector<float4> gen_tp;
+  build_terms(NG, (int)gen_owner.size(), gen_owner.data(), gen_prm.data(), gen_harm.data(), gen_terms, gen_tp);
+  std::vector<uint32_t> gen_idx(std::max(NG, 1), 0);
+  for (int g = 0; g < NG; ++g) gen_idx[g] = pack4(gen_idx4.data() + 4 * g, 4);
+
+  // ---- atom-major force slots (slot mode, Forces.compute): contribution (item, position) of atom a gets the
+  // next slot of a, in the fixed order bonds, angles, packed dihedrals, general torsions, 1-4 list => the per-atom
+  // gather adds them in a fixed order.  Lanes without an item write to the trash slot `nslots`.
+  struct KindRef { const std::vector<int>* seq; const int32_t* idx; int arity; };
+  std::vector<int> genseq(NG);
+  for (int g = 0; g < NG; ++g) genseq[g] = g;
+  const KindRef kinds[5] = {{&PB.seq, d->bond_idx, 2}, {&PA.seq, d->angle_idx, 3}, {&PD.seq, d->dihedral_idx, 4},
+                            {&genseq, gen_idx4.data(), 4}, {&PP.seq, idx14l.data(), 2}};
   std::vector<int> per_atom_count(kMaxAtoms, 0);
-  for (int ty = 1; ty < 6; ++ty)
-    for (int it = 0; it < counts[ty] * arity[ty]; ++it) per_atom_count[idxs[ty][it]]++;
+  for (const KindRef& K : kinds)
+    for (int it : *K.seq) for (int c = 0; c < K.arity; ++c) per_atom_count[K.idx[K.arity * it + c]]++;
   std::vector<uint16_t> gstart(kMaxAtoms + 2, 0);
   int nslots = 0;
   for (int a = 0; a < kMaxAtoms; ++a) { gstart[a] = (uint16_t)nslots; nslots += per_atom_count[a]; }
   gstart[kMaxAtoms] = gstart[kMaxAtoms + 1] = (uint16_t)nslots;
-  if (nslots > 65535) { delete topo; fail(B200MD_ERR_UNSUPPORTED, "too many bonded force contributions"); return nullptr; }
-  T.nslots = nslots;
+  if (nslots > 65534) { delete topo; fail(B200MD_ERR_UNSUPPORTED, "too many bonded force contributions"); return nullptr; }
+  T.nslots = nslots + 1;  // + the trash slot
   std::vector<int> cursor(gstart.begin(), gstart.begin() + kMaxAtoms);
-  std::vector<std::vector<uint16_t>> slot_of(6);
-  for (int ty = 1; ty < 6; ++ty) {
-    slot_of[ty].resize((size_t)counts[ty] * arity[ty]);
-    for (int it = 0; it < counts[ty] * arity[ty]; ++it) slot_of[ty][it] = (uint16_t)cursor[idxs[ty][it]]++;
+  std::vector<std::vector<uint16_t>> slot_of(5);  // [kind][item * arity + c], indexed by ORIGINAL item id
+  for (int ty = 0; ty < 5; ++ty) {
+    const KindRef& K = kinds[ty];
+    int maxid = -1;
+    for (int it : *K.seq) maxid = std::max(maxid, it);
+    slot_of[ty].assign((size_t)(maxid + 1) * K.arity, (uint16_t)nslots);
+    for (int it : *K.seq) for (int c = 0; c < K.arity; ++c) slot_of[ty][(size_t)it * K.arity + c] = (uint16_t)cursor[K.idx[K.arity * it + c]]++;
   }
   auto pair16 = [](uint16_t lo, uint16_t hi) { return (uint32_t)lo | ((uint32_t)hi << 16); };
-  std::vector<uint32_t> bond_slot(d->nbonds), p14_slot(p14_idx.size());
-  std::vector<uint2> angle_slot(d->nangles), dih_slot(std::max(d->ndihedrals, 1)), imp_slot(std::max(d->nimpropers, 1));
-  for (int k = 0; k < d->nbonds; ++k) bond_slot[k] = pair16(slot_of[1][2 * k], slot_of[1][2 * k + 1]);
-  for (int k = 0; k < d->nangles; ++k)
-    angle_slot[k] = make_uint2(pair16(slot_of[2][3 * k], slot_of[2][3 * k + 1]), slot_of[2][3 * k + 2]);
-  for (int k = 0; k < d->ndihedrals; ++k)
-    dih_slot[k] = make_uint2(pair16(slot_of[3][4 * k], slot_of[3][4 * k + 1]), pair16(slot_of[3][4 * k + 2], slot_of[3][4 * k + 3]));
-  for (int k = 0; k < d->nimpropers; ++k)
-    imp_slot[k] = make_uint2(pair16(slot_of[4][4 * k], slot_of[4][4 * k + 1]), pair16(slot_of[4][4 * k + 2], slot_of[4][4 * k + 3]));
-  for (size_t k = 0; k < p14_idx.size(); ++k) p14_slot[k] = pair16(slot_of[5][2 * k], slot_of[5][2 * k + 1]);
+  const uint16_t trash = (uint16_t)nslots;
+  auto slots4 = [&](int ty, int it, int arity) {  // (s0 | s1 << 16, s2 | s3 << 16) of one item, trash for a missing item
+    uint16_t sl[4] = {trash, trash, trash, trash};
+    if (it >= 0) for (int c = 0; c < arity; ++c) sl[c] = slot_of[ty][(size_t)it * arity + c];
+    return make_uint2(pair16(sl[0], sl[1]), pair16(sl[2], sl[3]));
+  };
+  // a lane half without an item repeats the atoms of the lane's A item (finite geometry) with zero parameters
+  auto atoms_of = [&](const int32_t* idx, int arity, int it, int fallback) { return pack4(idx + (size_t)arity * (it >= 0 ? it : fallback), arity); };
+
+  std::vector<uint2> bond2_idx(std::max(PB.npairs, 1)), angle2_idx(std::max(PA.npairs, 1)), dih2_idx(std::max(PD.npairs, 1)), p142_idx(std::max(PP.npairs, 1));
+  std::vector<uint4> bond2_slot(bond2_idx.size()), angle2_slot(angle2_idx.size()), dih2_slot(dih2_idx.size()), p142_slot(p142_idx.size());
+  std::vector<float4> bond2_prm(bond2_idx.size()), angle2_prm(angle2_idx.size()), dih2_p14ab(dih2_idx.size()), p142_ab(p142_idx.size());
+  std::vector<float2> dih2_k0(dih2_idx.size()), dih2_p14q(dih2_idx.size()), p142_q(p142_idx.size());
+  const size_t dstride = dih2_idx.size();
+  std::vector<float4> dih2_coef((size_t)kMaxPer * dstride, make_float4(0.f, 0.f, 0.f, 0.f));  // [n-1][pair]: n a_n (A,B), n b_n (A,B)
+  auto u4 = [](uint2 a2, uint2 b2) { return make_uint4(a2.x, a2.y, b2.x, b2.y); };
+  for (int p2 = 0; p2 < PB.npairs; ++p2) {
+    const int A = PB.lane_a[p2], Bi = PB.lane_b[p2];
+    bond2_idx[p2] = make_uint2(atoms_of(d->bond_idx, 2, A, A), atoms_of(d->bond_idx, 2, Bi, A));
+    bond2_slot[p2] = u4(slots4(0, A, 2), slots4(0, Bi, 2));
+    bond2_prm[p2] = make_float4(d->bond_prm[2 * A], Bi >= 0 ? d->bond_prm[2 * Bi] : 0.f, d->bond_prm[2 * A + 1], Bi >= 0 ? d->bond_prm[2 * Bi + 1] : 1.f);
+  }
+  for (int p2 = 0; p2 < PA.npairs; ++p2) {
+    const int A = PA.lane_a[p2], Bi = PA.lane_b[p2];
+    angle2_idx[p2] = make_uint2(atoms_of(d->angle_idx, 3, A, A), atoms_of(d->angle_idx, 3, Bi, A));
+    angle2_slot[p2] = u4(slots4(1, A, 3), slots4(1, Bi, 3));
+    angle2_prm[p2] = make_float4(d->angle_prm[2 * A], Bi >= 0 ? d->angle_prm[2 * Bi] : 0.f, d->angle_prm[2 * A + 1], Bi >= 0 ? d->angle_prm[2 * Bi + 1] : 1.f);
+  }
+  std::vector<int> dih_chunk_nmax(std::max(PD.nchunks, 1), 1);
+  for (int p2 = 0; p2 < PD.npairs; ++p2) {
+    const int it[2] = {PD.lane_a[p2], PD.lane_b[p2]};
+    dih2_idx[p2] = make_uint2(atoms_of(d->dihedral_idx, 4, it[0], it[0]), atoms_of(d->dihedral_idx, 4, it[1], it[0]));
+    dih2_slot[p2] = u4(slots4(2, it[0], 4), slots4(2, it[1], 4));
+    float k0s[2] = {0.f, 0.f}, ab[2][2] = {{0.f, 0.f}, {0.f, 0.f}}, qq[2] = {0.f, 0.f};
+    for (int h = 0; h < 2; ++h) {
+      if (it[h] < 0) continue;
+      dih_chunk_nmax[p2 / 32] = std::max(dih_chunk_nmax[p2 / 32], dmaxper[it[h]]);
+      double K0 = 0.0, ca[kMaxPer] = {0}, cb[kMaxPer] = {0};
+      for (int t : dterms[it[h]]) {  // k (1 + cos(n phi - phi0)) = k + k cos(phi0) cos(n phi) + k sin(phi0) sin(n phi)
+        const double k0 = d->dihedral_term_prm[3 * t], phi0 = d->dihedral_term_prm[3 * t + 1];
+        const int n = (int)d->dihedral_term_prm[3 * t + 2];
+        K0 += k0; ca[n - 1] += n * k0 * cos(phi0); cb[n - 1] += n * k0 * sin(phi0);
+      }
+      k0s[h] = (float)K0;
+      for (int n = 0; n < kMaxPer; ++n) {
+        float4& cf = dih2_coef[(size_t)n * dstride + p2];
+        (h ? cf.y : cf.x) = (float)ca[n];
+        (h ? cf.w : cf.z) = (float)cb[n];
+      }
+      if (own14[it[h]] >= 0) { float o3[3]; prm14(own14[it[h]], o3); ab[h][0] = o3[0]; ab[h][1] = o3[1]; qq[h] = o3[2]; }
+    }
+    dih2_k0[p2] = make_float2(k0s[0], k0s[1]);
+    dih2_p14ab[p2] = make_float4(ab[0][0], ab[1][0], ab[0][1], ab[1][1]);
+    dih2_p14q[p2] = make_float2(qq[0], qq[1]);
+  }
+  for (int p2 = 0; p2 < PP.npairs; ++p2) {
+    const int it[2] = {PP.lane_a[p2], PP.lane_b[p2]};
+    p142_idx[p2] = make_uint2(atoms_of(idx14l.data(), 2, it[0], it[0]), atoms_of(idx14l.data(), 2, it[1], it[0]));
+    p142_slot[p2] = u4(slots4(4, it[0], 2), slots4(4, it[1], 2));
+    float o3[2][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}};
+    for (int h = 0; h < 2; ++h) if (it[h] >= 0) prm14(list14[it[h]], o3[h]);
+    p142_ab[p2] = make_float4(o3[0][0], o3[1][0], o3[0][1], o3[1][1]);
+    p142_q[p2] = make_float2(o3[0][2], o3[1][2]);
+  }
+  std::vector<uint2> gen_slot(std::max(NG, 1));
+  for (int g = 0; g < NG; ++g) gen_slot[g] = slots4(3, g, 4);
+  T.dih_on = 1;
+  T.p14_on = 1;
+  T.dih2_stride = (int)dstride;
 
   // ---- static task schedule: longest-processing-time-first over the 4 warps ----------------------
   struct Task { uint32_t word; int cost; };
   std::vector<Task> all;
   // cost model of the schedule (issue slots per warp); B200MD_COSTS="pass,chunk,diagstep,diag,bond,angle,dih,imp,p14"
   // overrides it for tuning runs
-  int cm[9] = {150, 120, 52, 30, 60, 140, 330, 300, 50};
+  int cm[9] = {150, 120, 52, 30, 110, 230, 380, 400, 100};
   if (const char* env = getenv("B200MD_COSTS")) sscanf(env, "%d,%d,%d,%d,%d,%d,%d,%d,%d", cm, cm + 1, cm + 2, cm + 3, cm + 4, cm + 5, cm + 6, cm + 7, cm + 8);
   const int nblocks = (N + 31) / 32;
   if (d->npairs > 0) {
@@ -561,9 +653,12 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
       }
     }
   }
-  const int chunk_cost[6] = {0, cm[4], cm[5], cm[6], cm[7], cm[8]};
-  for (int ty = 1; ty < 6; ++ty)
-    for (int c = 0; c < (counts[ty] + 31) / 32; ++c) all.push_back({make_task(ty, c, 0), chunk_cost[ty]});
+  // bonded chunks: 32 lanes x 2 items (packed kinds) or 32 items (general torsions)
+  for (int c = 0; c < PB.nchunks; ++c) all.push_back({make_task(TASK_BOND, c, 0), cm[4]});
+  for (int c = 0; c < PA.nchunks; ++c) all.push_back({make_task(TASK_ANGLE, c, 0), cm[5]});
+  for (int c = 0; c < PD.nchunks; ++c) all.push_back({make_task(TASK_DIHEDRAL, c, dih_chunk_nmax[c]), cm[6] + 12 * dih_chunk_nmax[c]});
+  for (int c = 0; c < (NG + 31) / 32; ++c) all.push_back({make_task(TASK_IMPROPER, c, 0), cm[7]});
+  for (int c = 0; c < PP.nchunks; ++c) all.push_back({make_task(TASK_P14, c, 0), cm[8]});
   std::stable_sort(all.begin(), all.end(), [](const Task& a, const Task& b) { return a.cost > b.cost; });
   std::vector<uint32_t> tasks((size_t)kWarps * kMaxTasks, 0);
   int load[kWarps] = {0, 0, 0, 0};
@@ -589,11 +684,11 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   // ---- upload --------------------------------------------------------------------------------------
   BlobBuilder B;
   const size_t o_ab = B.add(ab), o_q = B.add(charge), o_m = B.add(mass), o_ro = B.add(rowoff), o_mask = B.add(mask8), o_rot = B.add(diagmask);
-  const size_t o_bi = B.add(bond_idx), o_bp = B.add(bond_prm), o_bs = B.add(bond_slot);
-  const size_t o_ai = B.add(angle_idx), o_ap = B.add(angle_prm), o_as = B.add(angle_slot);
-  const size_t o_di = B.add(dih_idx), o_dt = B.add(dih_terms), o_dp = B.add(dih_tp), o_ds = B.add(dih_slot), o_d14 = B.add(dih_p14);
-  const size_t o_ii = B.add(imp_idx), o_it = B.add(imp_terms), o_ip = B.add(imp_tp), o_is = B.add(imp_slot);
-  const size_t o_pi = B.add(p14_idx), o_pp = B.add(p14_prm), o_ps = B.add(p14_slot);
+  const size_t o_bi = B.add(bond2_idx), o_bp = B.add(bond2_prm), o_bs = B.add(bond2_slot);
+  const size_t o_ai = B.add(angle2_idx), o_ap = B.add(angle2_prm), o_as = B.add(angle2_slot);
+  const size_t o_di = B.add(dih2_idx), o_dc = B.add(dih2_coef), o_dk = B.add(dih2_k0), o_ds = B.add(dih2_slot), o_d14 = B.add(dih2_p14ab), o_dq = B.add(dih2_p14q);
+  const size_t o_gi = B.add(gen_idx), o_gt = B.add(gen_terms), o_gp = B.add(gen_tp), o_gsl = B.add(gen_slot);
+  const size_t o_pi = B.add(p142_idx), o_pp = B.add(p142_ab), o_pq = B.add(p142_q), o_ps = B.add(p142_slot);
   const size_t o_gs = B.add(gstart), o_tk = B.add(tasks);
   auto cleanup = [&](const std::string& msg) { fail(B200MD_ERR_CUDA, msg); if (topo->blob) cudaFree(topo->blob); delete topo; };
   cudaError_t e = cudaSetDevice(device);
@@ -605,17 +700,18 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   char* base = (char*)topo->blob;
   T.ab = (const float2*)(base + o_ab); T.charge = (const float*)(base + o_q); T.mass = (const float*)(base + o_m);
   T.ab_row_off = (const int*)(base + o_ro); T.mask8 = (const uint8_t*)(base + o_mask); T.diagmask = (const uint32_t*)(base + o_rot);
-  T.bond_idx = (const uint32_t*)(base + o_bi); T.bond_prm = (const float2*)(base + o_bp); T.bond_slot = (const uint32_t*)(base + o_bs);
-  T.angle_idx = (const uint32_t*)(base + o_ai); T.angle_prm = (const float2*)(base + o_ap); T.angle_slot = (const uint2*)(base + o_as);
-  T.dih_idx = (const uint32_t*)(base + o_di); T.dih_terms = (const uint2*)(base + o_dt); T.dih_term_prm = (const float4*)(base + o_dp);
-  T.dih_slot = (const uint2*)(base + o_ds); T.dih_p14 = (const float4*)(base + o_d14);
-  T.imp_idx = (const uint32_t*)(base + o_ii); T.imp_terms = (const uint2*)(base + o_it); T.imp_term_prm = (const float4*)(base + o_ip);
-  T.imp_slot = (const uint2*)(base + o_is);
-  T.p14_idx = (const uint32_t*)(base + o_pi); T.p14_prm = (const float4*)(base + o_pp); T.p14_slot = (const uint32_t*)(base + o_ps);
+  T.bond2_idx = (const uint2*)(base + o_bi); T.bond2_prm = (const float4*)(base + o_bp); T.bond2_slot = (const uint4*)(base + o_bs);
+  T.angle2_idx = (const uint2*)(base + o_ai); T.angle2_prm = (const float4*)(base + o_ap); T.angle2_slot = (const uint4*)(base + o_as);
+  T.dih2_idx = (const uint2*)(base + o_di); T.dih2_coef = (const float4*)(base + o_dc); T.dih2_k0 = (const float2*)(base + o_dk);
+  T.dih2_slot = (const uint4*)(base + o_ds); T.dih2_p14ab = (const float4*)(base + o_d14); T.dih2_p14q = (const float2*)(base + o_dq);
+  T.gen_idx = (const uint32_t*)(base + o_gi); T.gen_terms = (const uint2*)(base + o_gt); T.gen_term_prm = (const float4*)(base + o_gp);
+  T.gen_slot = (const uint2*)(base + o_gsl);
+  T.p142_idx = (const uint2*)(base + o_pi); T.p142_ab = (const float4*)(base + o_pp); T.p142_q = (const float2*)(base + o_pq);
+  T.p142_slot = (const uint4*)(base + o_ps);
   T.gather_start = (const uint16_t*)(base + o_gs);
   T.tasks = (const uint32_t*)(base + o_tk);
-  T.smem_bytes = (int)smem_layout(nullptr, nullptr, NT, nslots, false);
-  T.smem_bytes_fixed = (int)smem_layout(nullptr, nullptr, NT, nslots, true);
+  T.smem_bytes = (int)smem_layout(nullptr, nullptr, NT, T.nslots, false);
+  T.smem_bytes_fixed = (int)smem_layout(nullptr, nullptr, NT, T.nslots, true);
   if (T.smem_bytes > 227 * 1024) { cleanup("topology needs more than 227 KB of shared memory per CTA"); g_last_error = "too much shared memory"; return nullptr; }
   cudaDeviceProp prop;
   cudaGetDeviceProperties(&prop, device);
@@ -682,13 +778,15 @@ static int make_force_params(const b200md_topology* topo, const b200md_force_opt
 static DevTopo apply_terms(const DevTopo& in, uint32_t terms) {
   DevTopo T = in;
   const bool p14 = (terms & B200MD_T_14) && (terms & (B200MD_T_LJ | B200MD_T_ELECTROSTATICS));
-  if (!(terms & B200MD_T_BONDS)) T.nbonds = 0;
-  if (!(terms & B200MD_T_ANGLES)) T.nangles = 0;
-  if (!(terms & B200MD_T_IMPROPERS)) T.nimp = 0;
+  if (!(terms & B200MD_T_BONDS)) T.nbond2 = 0;
+  if (!(terms & B200MD_T_ANGLES)) T.nangle2 = 0;
   T.dih_on = (terms & B200MD_T_DIHEDRALS) ? 1 : 0;
   T.p14_on = p14 ? 1 : 0;
-  if (!T.dih_on && !T.p14_on) T.ndih = 0;
-  if (!p14) T.n14 = 0;
+  if (!T.dih_on && !T.p14_on) T.ndih2 = 0;
+  if (!p14) T.n14_2 = 0;
+  // general list = [special dihedrals | impropers]
+  T.gen_begin = T.dih_on ? 0 : T.nspec;
+  T.gen_end = (terms & B200MD_T_IMPROPERS) ? T.ngen : T.nspec;
   return T;
 }
 

@@ -269,184 +269,326 @@ __device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams&
 //   order after the barrier -- exact fp32 sums for arbitrarily large forces (generated / clashing frames).
 // FIXED = true (fused integrator): 2^-17 kcal/mol/A fixed point, one shared-memory integer atomic per
 //   component.  Integer addition is associative, so the sum is still order-independent and bit-reproducible,
-//   and the slot buffer, its stores and the gather loop disappear.  A contribution above kFixedLimit raises the
-//   per-replica range flag (the run has exploded long before 16 384 kcal/mol/A are reached on one atom).
-constexpr float kFixedScale = 131072.0f, kFixedInv = 1.0f / 131072.0f, kFixedLimit = 2048.0f;
+//   and the slot buffer, its stores and the gather loop disappear.  The items scale their force coefficient by
+//   kFixedScale themselves (one multiply per item instead of one per component); the per-atom gather raises the
+//   range flag when an accumulator passes 2^29 (4 096 kcal/mol/A: the run has exploded long before).
+constexpr float kFixedScale = 131072.0f, kFixedInv = 1.0f / 131072.0f;
+constexpr int kFixedLimit = 1 << 29;
 
 template <bool FIXED>
-__device__ __forceinline__ void emit(const Smem& S, uint32_t slot, uint32_t atom, float x, float y, float z,
-                                     uint32_t& flag) {
+__device__ __forceinline__ void emit(const Smem& S, uint32_t slot, uint32_t atom, float x, float y, float z) {
   if (FIXED) {
-    if (fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z))) > kFixedLimit) flag |= B200MD_FLAG_FORCE_RANGE;
-    atomicAdd(S.fbi + atom, __float2int_rn(x * kFixedScale));
-    atomicAdd(S.fbi + kMaxAtoms + atom, __float2int_rn(y * kFixedScale));
-    atomicAdd(S.fbi + 2 * kMaxAtoms + atom, __float2int_rn(z * kFixedScale));
+    atomicAdd(S.fbi + atom, __float2int_rn(x));
+    atomicAdd(S.fbi + kMaxAtoms + atom, __float2int_rn(y));
+    atomicAdd(S.fbi + 2 * kMaxAtoms + atom, __float2int_rn(z));
   } else {
     float* p = S.fb + 3 * slot;
     p[0] = x; p[1] = y; p[2] = z;
   }
 }
-
-// evaluate_bonds, forces.py:111-132, 492-501
-template <bool ENERGY, bool FIXED>
-__device__ __forceinline__ void bond_task(const Smem& S, const DevTopo& T, const ForceParams& P, int item, Energies& E,
-                                          uint32_t& flag) {
-  if (item >= T.nbonds) return;
-  const uint32_t q = __ldg(T.bond_idx + item), sl = FIXED ? 0u : __ldg(T.bond_slot + item);
-  const float2 prm = __ldg(T.bond_prm + item);
-  const float4 pa = S.pos[q & 0xff], pb = S.pos[(q >> 8) & 0xff];
-  const f3 d = sub3(pa, pb);
-  const float r2 = dot3(d, d);
-  const float rinv = fast_rsqrt(r2), dist = r2 * rinv;
-  const bool keep = !P.has_cutoff || dist <= P.rc;  // forces.py:117-125
-  const float x = dist - prm.y;
-  const float c = keep ? 2.0f * prm.x * x * rinv : 0.0f;  // dE/dr / r
-  emit<FIXED>(S, sl & 0xffff, q & 0xff, -c * d.x, -c * d.y, -c * d.z, flag);
-  emit<FIXED>(S, sl >> 16, (q >> 8) & 0xff, c * d.x, c * d.y, c * d.z, flag);
-  if (ENERGY && keep) {
-    // k (r - r0)^2 cancels ~40:1 in (r - r0): the energy (report steps only) takes r in FP64
-    const double ddx = (double)pa.x - (double)pb.x, ddy = (double)pa.y - (double)pb.y, ddz = (double)pa.z - (double)pb.z;
-    const double xd = sqrt(ddx * ddx + ddy * ddy + ddz * ddz) - (double)prm.y;
-    E.e[B200MD_E_BONDS] += (double)prm.x * xd * xd;
+// +v to (slot0, atom0) and -v to (slot1, atom1) from one conversion
+template <bool FIXED>
+__device__ __forceinline__ void emit_pm(const Smem& S, uint32_t slot0, uint32_t atom0, uint32_t slot1, uint32_t atom1,
+                                        float x, float y, float z) {
+  if (FIXED) {
+    const int ix = __float2int_rn(x), iy = __float2int_rn(y), iz = __float2int_rn(z);
+    atomicAdd(S.fbi + atom0, ix); atomicAdd(S.fbi + kMaxAtoms + atom0, iy); atomicAdd(S.fbi + 2 * kMaxAtoms + atom0, iz);
+    atomicAdd(S.fbi + atom1, -ix); atomicAdd(S.fbi + kMaxAtoms + atom1, -iy); atomicAdd(S.fbi + 2 * kMaxAtoms + atom1, -iz);
+  } else {
+    float* p = S.fb + 3 * slot0;
+    p[0] = x; p[1] = y; p[2] = z;
+    float* q = S.fb + 3 * slot1;
+    q[0] = -x; q[1] = -y; q[2] = -z;
   }
 }
 
-// evaluate_angles, forces.py:134-145, 504-537
-template <bool ENERGY, bool FIXED>
-__device__ __forceinline__ void angle_task(const Smem& S, const DevTopo& T, int item, Energies& E, uint32_t& flag) {
-  if (item >= T.nangles) return;
-  const uint32_t q = __ldg(T.angle_idx + item);
-  const uint2 sl = FIXED ? make_uint2(0u, 0u) : __ldg(T.angle_slot + item);
-  const float2 prm = __ldg(T.angle_prm + item);
-  const float4 p0 = S.pos[q & 0xff], p1 = S.pos[(q >> 8) & 0xff], p2 = S.pos[(q >> 16) & 0xff];
-  const f3 r21 = sub3(p0, p1), r23 = sub3(p2, p1);
-  const float n21i = fast_rsqrt(dot3(r21, r21)), n23i = fast_rsqrt(dot3(r23, r23));
-  float ct = dot3(r23, r21) * n21i * n23i;
-  ct = fminf(fmaxf(ct, -1.0f), 1.0f);
-  const float th = acosf(ct), dth = th - prm.y;
-  if (ENERGY) E.e[B200MD_E_ANGLES] += (double)(prm.x * dth * dth);
-  const float st2 = fmaf(-ct, ct, 1.0f);
-  const float coef = (st2 > 0.0f) ? -2.0f * prm.x * dth * fast_rsqrt(st2) : 0.0f;  // 0 where sin(theta) == 0
-  const float a0 = coef * n21i, a2 = coef * n23i;
-  const float c21 = ct * n21i, c23 = ct * n23i;
-  const float f0x = a0 * fmaf(c21, r21.x, -r23.x * n23i), f0y = a0 * fmaf(c21, r21.y, -r23.y * n23i),
-              f0z = a0 * fmaf(c21, r21.z, -r23.z * n23i);
-  const float f2x = a2 * fmaf(c23, r23.x, -r21.x * n21i), f2y = a2 * fmaf(c23, r23.y, -r21.y * n21i),
-              f2z = a2 * fmaf(c23, r23.z, -r21.z * n21i);
-  emit<FIXED>(S, sl.x & 0xffff, q & 0xff, f0x, f0y, f0z, flag);
-  emit<FIXED>(S, sl.x >> 16, (q >> 8) & 0xff, -(f0x + f2x), -(f0y + f2y), -(f0z + f2z), flag);
-  emit<FIXED>(S, sl.y & 0xffff, (q >> 16) & 0xff, f2x, f2y, f2z, flag);
+// ---- packed three-vectors: component pairs (item A, item B) ------------------------------------------
+struct v3p { u64 x, y, z; };
+__device__ __forceinline__ v3p sub3p(v3p a, v3p b) { return {sub2(a.x, b.x), sub2(a.y, b.y), sub2(a.z, b.z)}; }
+__device__ __forceinline__ u64 dot3p(v3p a, v3p b) { return fma2(a.z, b.z, fma2(a.y, b.y, mul2(a.x, b.x))); }
+__device__ __forceinline__ u64 neg2(u64 a) { return a ^ 0x8000000080000000ull; }
+__device__ __forceinline__ v3p cross3p(v3p a, v3p b) {
+  return {fma2(a.y, b.z, neg2(mul2(a.z, b.y))), fma2(a.z, b.x, neg2(mul2(a.x, b.z))), fma2(a.x, b.y, neg2(mul2(a.y, b.x)))};
+}
+__device__ __forceinline__ v3p scale3p(u64 s, v3p a) { return {mul2(s, a.x), mul2(s, a.y), mul2(s, a.z)}; }
+__device__ __forceinline__ u64 rsqrt2(u64 v) { float a, b; upk(v, a, b); return pk(fast_rsqrt(a), fast_rsqrt(b)); }
+// positions of atom `ia` (item A) and `ib` (item B) from the structure-of-arrays copy
+__device__ __forceinline__ v3p load3p(const Smem& S, uint32_t ia, uint32_t ib) {
+  return {pk(S.sx[ia], S.sx[ib]), pk(S.sx[kMaxAtoms + ia], S.sx[kMaxAtoms + ib]), pk(S.sx[2 * kMaxAtoms + ia], S.sx[2 * kMaxAtoms + ib])};
+}
+template <bool FIXED>
+__device__ __forceinline__ void emit2(const Smem& S, uint32_t slot_a, uint32_t slot_b, uint32_t atom_a, uint32_t atom_b, v3p f) {
+  float xa, xb, ya, yb, za, zb;
+  upk(f.x, xa, xb); upk(f.y, ya, yb); upk(f.z, za, zb);
+  emit<FIXED>(S, slot_a, atom_a, xa, ya, za);
+  emit<FIXED>(S, slot_b, atom_b, xb, yb, zb);
+}
+template <bool FIXED>
+__device__ __forceinline__ void emit2_pm(const Smem& S, uint32_t sa0, uint32_t sa1, uint32_t sb0, uint32_t sb1, uint32_t a0,
+                                         uint32_t a1, uint32_t b0, uint32_t b1, v3p f) {
+  float xa, xb, ya, yb, za, zb;
+  upk(f.x, xa, xb); upk(f.y, ya, yb); upk(f.z, za, zb);
+  emit_pm<FIXED>(S, sa0, a0, sa1, a1, xa, ya, za);
+  emit_pm<FIXED>(S, sb0, b0, sb1, b1, xb, yb, zb);
 }
 
-// One LJ + Coulomb pair with its own (12 A', 6 B', K qi qj') parameters: forces.py:176-226 (1-4 pairs are
+// evaluate_bonds, forces.py:111-132, 492-501 -- two bonds per lane
+template <bool ENERGY, bool FIXED>
+__device__ __forceinline__ void bond_task(const Smem& S, const DevTopo& T, const ForceParams& P, int pair, Energies& E) {
+  if (pair >= T.nbond2) return;
+  const uint2 q = __ldg(T.bond2_idx + pair);
+  const float4 prm = __ldg(T.bond2_prm + pair);  // kA, kB, r0A, r0B
+  const uint4 sl = FIXED ? make_uint4(0u, 0u, 0u, 0u) : __ldg(T.bond2_slot + pair);
+  const uint32_t a0 = q.x & 0xff, a1 = (q.x >> 8) & 0xff, b0 = q.y & 0xff, b1 = (q.y >> 8) & 0xff;
+  const v3p d = sub3p(load3p(S, a0, b0), load3p(S, a1, b1));
+  const u64 r2 = dot3p(d, d);
+  const u64 rinv = rsqrt2(r2), dist = mul2(r2, rinv);
+  float da, db;
+  upk(dist, da, db);
+  const bool keep_a = !P.has_cutoff || da <= P.rc, keep_b = !P.has_cutoff || db <= P.rc;  // forces.py:117-125
+  const float fs = FIXED ? -2.0f * kFixedScale : -2.0f;
+  const u64 k2 = pk(keep_a ? fs * prm.x : 0.0f, keep_b ? fs * prm.y : 0.0f);
+  const u64 c = mul2(mul2(k2, sub2(dist, pk(prm.z, prm.w))), rinv);  // -(dE/dr) / r (scaled)
+  emit2_pm<FIXED>(S, sl.x & 0xffff, sl.x >> 16, sl.z & 0xffff, sl.z >> 16, a0, a1, b0, b1, scale3p(c, d));
+  if (ENERGY) {
+    // k (r - r0)^2 cancels ~40:1 in (r - r0): the energy (report steps only) takes r in FP64
+    const float4 pa0 = S.pos[a0], pa1 = S.pos[a1], pb0 = S.pos[b0], pb1 = S.pos[b1];
+    if (keep_a) {
+      const double ddx = (double)pa0.x - (double)pa1.x, ddy = (double)pa0.y - (double)pa1.y, ddz = (double)pa0.z - (double)pa1.z;
+      const double xd = sqrt(ddx * ddx + ddy * ddy + ddz * ddz) - (double)prm.z;
+      E.e[B200MD_E_BONDS] += (double)prm.x * xd * xd;
+    }
+    if (keep_b) {
+      const double ddx = (double)pb0.x - (double)pb1.x, ddy = (double)pb0.y - (double)pb1.y, ddz = (double)pb0.z - (double)pb1.z;
+      const double xd = sqrt(ddx * ddx + ddy * ddy + ddz * ddz) - (double)prm.w;
+      E.e[B200MD_E_BONDS] += (double)prm.y * xd * xd;
+    }
+  }
+}
+
+// acos on [-1, 1] without branches: sqrt(1 - |x|) * P7(|x|) (Abramowitz & Stegun 4.4.46, |error| <= 2e-8 + fp32
+// rounding), reflected for x < 0.  Used for the FORCE of the angle term; energies take acosf.
+__device__ __forceinline__ u64 acos2(u64 x) {
+  float xa, xb;
+  upk(x, xa, xb);
+  const u64 t = pk(fabsf(xa), fabsf(xb));
+  u64 p = dup2(-0.0012624911f);
+  p = fma2(p, t, dup2(0.0066700901f)); p = fma2(p, t, dup2(-0.0170881256f)); p = fma2(p, t, dup2(0.0308918810f));
+  p = fma2(p, t, dup2(-0.0501743046f)); p = fma2(p, t, dup2(0.0889789874f)); p = fma2(p, t, dup2(-0.2145988016f));
+  p = fma2(p, t, dup2(1.5707963050f));
+  float ua, ub;
+  upk(sub2(dup2(1.0f), t), ua, ub);
+  const u64 r = mul2(pk(fast_sqrt(ua), fast_sqrt(ub)), p);
+  // x < 0: pi - r (pi split in two floats)
+  const u64 sg = pk(xa < 0.0f ? -1.0f : 1.0f, xb < 0.0f ? -1.0f : 1.0f);
+  const u64 hi = pk(xa < 0.0f ? 3.14159274101257324f : 0.0f, xb < 0.0f ? 3.14159274101257324f : 0.0f);
+  const u64 lo = pk(xa < 0.0f ? -8.74227766e-8f : 0.0f, xb < 0.0f ? -8.74227766e-8f : 0.0f);
+  return add2(fma2(sg, r, hi), lo);
+}
+
+// evaluate_angles, forces.py:134-145, 504-537 -- two angles per lane
+template <bool ENERGY, bool FIXED>
+__device__ __forceinline__ void angle_task(const Smem& S, const DevTopo& T, int pair, Energies& E) {
+  if (pair >= T.nangle2) return;
+  const uint2 q = __ldg(T.angle2_idx + pair);
+  const float4 prm = __ldg(T.angle2_prm + pair);  // kA, kB, theta0A, theta0B
+  const uint4 sl = FIXED ? make_uint4(0u, 0u, 0u, 0u) : __ldg(T.angle2_slot + pair);
+  const uint32_t a0 = q.x & 0xff, a1 = (q.x >> 8) & 0xff, a2 = (q.x >> 16) & 0xff;
+  const uint32_t b0 = q.y & 0xff, b1 = (q.y >> 8) & 0xff, b2 = (q.y >> 16) & 0xff;
+  const v3p p1 = load3p(S, a1, b1);
+  const v3p r21 = sub3p(load3p(S, a0, b0), p1), r23 = sub3p(load3p(S, a2, b2), p1);
+  const u64 n21i = rsqrt2(dot3p(r21, r21)), n23i = rsqrt2(dot3p(r23, r23));
+  float cta, ctb;
+  upk(mul2(mul2(dot3p(r23, r21), n21i), n23i), cta, ctb);
+  cta = fminf(fmaxf(cta, -1.0f), 1.0f); ctb = fminf(fmaxf(ctb, -1.0f), 1.0f);
+  const u64 ct = pk(cta, ctb);
+  const u64 dth = sub2(acos2(ct), pk(prm.z, prm.w));
+  if (ENERGY) {
+    const float da = acosf(cta) - prm.z, db = acosf(ctb) - prm.w;
+    E.e[B200MD_E_ANGLES] += (double)(prm.x * da * da) + (double)(prm.y * db * db);
+  }
+  float sa, sb;
+  upk(fma2(neg2(ct), ct, dup2(1.0f)), sa, sb);
+  const float fs = FIXED ? -2.0f * kFixedScale : -2.0f;
+  const u64 rs = pk(sa > 0.0f ? fs * fast_rsqrt(sa) : 0.0f, sb > 0.0f ? fs * fast_rsqrt(sb) : 0.0f);  // 0 where sin(theta) == 0
+  const u64 coef = mul2(mul2(pk(prm.x, prm.y), dth), rs);
+  const u64 c0 = mul2(coef, n21i), c2 = mul2(coef, n23i), c21 = mul2(ct, n21i), c23 = mul2(ct, n23i);
+  const v3p u23 = scale3p(n23i, r23), u21 = scale3p(n21i, r21);
+  const v3p f0 = {mul2(c0, fma2(c21, r21.x, neg2(u23.x))), mul2(c0, fma2(c21, r21.y, neg2(u23.y))), mul2(c0, fma2(c21, r21.z, neg2(u23.z)))};
+  const v3p f2 = {mul2(c2, fma2(c23, r23.x, neg2(u21.x))), mul2(c2, fma2(c23, r23.y, neg2(u21.y))), mul2(c2, fma2(c23, r23.z, neg2(u21.z)))};
+  const v3p f1 = {neg2(add2(f0.x, f2.x)), neg2(add2(f0.y, f2.y)), neg2(add2(f0.z, f2.z))};
+  emit2<FIXED>(S, sl.x & 0xffff, sl.z & 0xffff, a0, b0, f0);
+  emit2<FIXED>(S, sl.x >> 16, sl.z >> 16, a1, b1, f1);
+  emit2<FIXED>(S, sl.y & 0xffff, sl.w & 0xffff, a2, b2, f2);
+}
+
+// Two LJ + Coulomb pairs with their own (12 A', -6 B', K qi qj') parameters: forces.py:176-226 (1-4 pairs are
 // never cut, switched or reaction-field corrected).  Returns s with F_a += s d, F_b -= s d, d = r_a - r_b.
 template <bool ENERGY>
-__device__ __forceinline__ float pair14(f3 d, float4 prm, const ForceParams& P, Energies& E) {
-  const float rinv = rsqrt_nr(dot3(d, d));
-  const float r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
-  const float a12 = prm.x * P.lj_on, b6 = prm.y * P.lj_on, qq = prm.z * P.el_on;
-  const float ec = qq * rinv;
-  const float glj = fmaf(a12, r6, -b6) * r6;
+__device__ __forceinline__ u64 pair14_2(v3p d, u64 a12, u64 nb6, u64 qq, const ForceParams& P, Energies& E) {
+  const u64 r2 = dot3p(d, d);
+  u64 rinv = rsqrt2(r2);
+  rinv = mul2(rinv, fma2(mul2(mul2(r2, rinv), dup2(-0.5f)), rinv, dup2(1.5f)));  // Newton step: the value is raised to r^-12
+  const u64 r2inv = mul2(rinv, rinv), r6 = mul2(mul2(r2inv, r2inv), r2inv);
+  a12 = mul2(a12, dup2(P.lj_on)); nb6 = mul2(nb6, dup2(P.lj_on)); qq = mul2(qq, dup2(P.el_on));
+  const u64 ec = mul2(qq, rinv);
+  const u64 glj = mul2(fma2(a12, r6, nb6), r6);
   if (ENERGY) {
-    E.e[B200MD_E_LJ] += (double)(fmaf(a12 * (1.0f / 12.0f), r6, -b6 * (1.0f / 6.0f)) * r6);
-    E.e[B200MD_E_ELECTROSTATICS] += (double)ec;
+    float a, b;
+    upk(mul2(fma2(mul2(a12, dup2(1.0f / 12.0f)), r6, mul2(nb6, dup2(1.0f / 6.0f))), r6), a, b);
+    E.e[B200MD_E_LJ] += (double)a + (double)b;
+    upk(ec, a, b);
+    E.e[B200MD_E_ELECTROSTATICS] += (double)a + (double)b;
   }
-  return (glj + ec) * r2inv;
+  return mul2(add2(glj, ec), r2inv);
 }
 
-// evaluate_torsion, forces.py:147-174 / 228-255, 540-602 (dihedrals and impropers share it), with the
-// 1-4 pair on the end atoms (forces.py:176-226) fused into the dihedral item that owns it.
-// phi = -atan2(sinPhi, cosPhi) is never formed for AMBER terms with integer periodicity: cos/sin(n phi)
-// come from (cos phi + i sin phi)^n and the phase enters through its precomputed cosine / sine.
+// Proper torsions with integer periodicity, two per lane, as a Fourier series in phi (forces.py:147-174, 540-602):
+//   E = K0 + sum_n a_n cos(n phi) + b_n sin(n phi),  a_n = sum k cos(phi0), b_n = sum k sin(phi0) over the terms of
+// periodicity n, so any number of terms costs the same and there is no branch: cos / sin(n phi) come from
+// (cos phi + i sin phi)^n, phi = -atan2(sinPhi, cosPhi) is never formed.  `nmax` (largest periodicity of the chunk)
+// is warp-uniform.  The 1-4 pair on the end atoms (forces.py:176-226) is fused in (zero parameters if there is none).
 template <bool ENERGY, bool FIXED>
-__device__ __forceinline__ void torsion_task(const Smem& S, const ForceParams& P, bool torsion_on, bool fuse14,
-                                             int item, int count, const uint32_t* idx, const uint2* terms,
-                                             const float4* term_prm, const uint2* slots, const float4* p14,
-                                             double& Eacc, Energies& E, uint32_t& flag) {
-  if (item >= count) return;
-  const uint32_t q = __ldg(idx + item);
-  const uint2 sl = FIXED ? make_uint2(0u, 0u) : __ldg(slots + item);
-  const float4 p0 = S.pos[q & 0xff], p1 = S.pos[(q >> 8) & 0xff], p2 = S.pos[(q >> 16) & 0xff], p3 = S.pos[q >> 24];
-  float f0x = 0.f, f0y = 0.f, f0z = 0.f, f1x = 0.f, f1y = 0.f, f1z = 0.f, f2x = 0.f, f2y = 0.f, f2z = 0.f,
-        f3x = 0.f, f3y = 0.f, f3z = 0.f;
-  if (torsion_on) {
-    const f3 r12 = sub3(p0, p1), r23 = sub3(p1, p2), r34 = sub3(p2, p3);
-    const f3 cA = cross3(r12, r23), cB = cross3(r23, r34);
-    const float nA2 = dot3(cA, cA), nB2 = dot3(cB, cB), n23sq = dot3(r23, r23);
-    const float rnA = fast_rsqrt(nA2), rnB = fast_rsqrt(nB2), rn23 = fast_rsqrt(n23sq), n23 = n23sq * rn23;
+__device__ __forceinline__ void dihedral_task(const Smem& S, const DevTopo& T, const ForceParams& P, int pair, int nmax,
+                                              Energies& E) {
+  if (pair >= T.ndih2) return;
+  const uint2 q = __ldg(T.dih2_idx + pair);
+  const uint4 sl = FIXED ? make_uint4(0u, 0u, 0u, 0u) : __ldg(T.dih2_slot + pair);
+  const uint32_t a0 = q.x & 0xff, a1 = (q.x >> 8) & 0xff, a2 = (q.x >> 16) & 0xff, a3 = q.x >> 24;
+  const uint32_t b0 = q.y & 0xff, b1 = (q.y >> 8) & 0xff, b2 = (q.y >> 16) & 0xff, b3 = q.y >> 24;
+  const v3p p0 = load3p(S, a0, b0), p1 = load3p(S, a1, b1), p2 = load3p(S, a2, b2), p3 = load3p(S, a3, b3);
+  const u64 fs = dup2(FIXED ? kFixedScale : 1.0f);
+  v3p f0 = {0ull, 0ull, 0ull}, f1 = f0, f2 = f0, f3 = f0;
+  if (T.dih_on) {
+    const v3p r12 = sub3p(p0, p1), r23 = sub3p(p1, p2), r34 = sub3p(p2, p3);
+    const v3p cA = cross3p(r12, r23), cB = cross3p(r23, r34);
+    const u64 n23sq = dot3p(r23, r23);
+    const u64 rnA = rsqrt2(dot3p(cA, cA)), rnB = rsqrt2(dot3p(cB, cB)), rn23 = rsqrt2(n23sq), n23 = mul2(n23sq, rn23);
     // cosPhi = A.B / (|A||B|);  sinPhi = (C.B)/(|C||B|) with C = r23 x A  =>  |r23| (r12.B) / (|A||B|)
-    const float rab = rnA * rnB;
-    const float cosPhi = dot3(cA, cB) * rab, sinPhi = n23 * dot3(r12, cB) * rab;
-    const float hinv = fast_rsqrt(fmaf(cosPhi, cosPhi, sinPhi * sinPhi));
-    const float c = cosPhi * hinv, s = -sinPhi * hinv;  // cos / sin of phi = -atan2(sinPhi, cosPhi)
-    const uint2 tr = __ldg(terms + item);
-    float pot = 0.0f, coeff = 0.0f;
-    for (uint32_t t = tr.x; t < tr.x + tr.y; ++t) {
-      const float4 tp = __ldg(term_prm + t);  // k0, per | marker, c0, s0
-      if (tp.y > 0.0f) {                      // AMBER, integer periodicity (forces.py:565-569)
-        float cn = c, sn = s;
-        for (float k = 1.5f; k < tp.y; k += 1.0f) {
-          const float t0 = fmaf(cn, c, -sn * s);
-          sn = fmaf(cn, s, sn * c);
-          cn = t0;
-        }
-        pot += tp.x * (1.0f + fmaf(cn, tp.z, sn * tp.w));      // k (1 + cos(n phi - phi0))
-        coeff -= tp.y * tp.x * fmaf(sn, tp.z, -cn * tp.w);     // -n k sin(n phi - phi0)
-      } else {
-        const float phi = atan2f(s, c);
-        if (tp.y == kTermHarmonic) {          // CHARMM harmonic (forces.py:570-576)
-          float ad = phi - tp.z;
-          const float pi_f = 3.14159265358979323846f;
-          if (ad < -pi_f) ad += 2.0f * pi_f; else if (ad > pi_f) ad -= 2.0f * pi_f;
-          pot += tp.x * ad * ad;
-          coeff += 2.0f * tp.x * ad;
-        } else {                              // AMBER with a non-integer periodicity: general path
-          float sn, cs;
-          sincosf(fmaf(tp.w, phi, -tp.z), &sn, &cs);
-          pot += tp.x * (1.0f + cs);
-          coeff -= tp.w * tp.x * sn;
-        }
+    const u64 rab = mul2(rnA, rnB);
+    const u64 cosPhi = mul2(dot3p(cA, cB), rab), sinPhi = mul2(mul2(n23, dot3p(r12, cB)), rab);
+    const u64 hinv = rsqrt2(fma2(cosPhi, cosPhi, mul2(sinPhi, sinPhi)));
+    const u64 c = mul2(cosPhi, hinv), s = neg2(mul2(sinPhi, hinv));  // cos / sin of phi = -atan2(sinPhi, cosPhi)
+    u64 cn = c, sn = s, coeff = 0ull, pot = 0ull;
+    const float4* cf = T.dih2_coef + pair;
+#pragma unroll 1
+    for (int n = 1; n <= nmax; ++n) {
+      const float4 k4 = __ldg(cf);  // n a_n (A, B), n b_n (A, B)
+      cf += T.dih2_stride;
+      const u64 ca = pk(k4.x, k4.y), cb = pk(k4.z, k4.w);
+      coeff = fma2(cb, cn, fma2(neg2(ca), sn, coeff));  // dE/dphi += n (b_n cos(n phi) - a_n sin(n phi))
+      if (ENERGY) pot = fma2(fma2(ca, cn, mul2(cb, sn)), dup2(1.0f / (float)n), pot);
+      const u64 t0 = fma2(cn, c, neg2(mul2(sn, s)));
+      sn = fma2(cn, s, mul2(sn, c));
+      cn = t0;
+    }
+    if (ENERGY) {
+      const float2 k0 = __ldg(T.dih2_k0 + pair);
+      float a, b;
+      upk(pot, a, b);
+      E.e[B200MD_E_DIHEDRALS] += ((double)k0.x + (double)a) + ((double)k0.y + (double)b);
+    }
+    // OpenMM-style projection (forces.py:582-600), coefficient pre-scaled for the fixed-point accumulators
+    coeff = mul2(mul2(coeff, fs), n23);
+    const u64 g0 = mul2(coeff, mul2(rnA, rnA)), g3 = mul2(coeff, mul2(rnB, rnB));  // f0 = g0 cA, f3 = -g3 cB
+    const u64 rn23sq = mul2(rn23, rn23);
+    const u64 ff1 = mul2(dot3p(r12, r23), rn23sq), ff2 = mul2(dot3p(r34, r23), rn23sq);
+    f0 = scale3p(g0, cA);
+    const v3p b = scale3p(g3, cB);  // = -f3
+    // s = ff1 a - ff2 b with a = -f0:  f1 = a + s, f2 = b - s
+    const v3p sv = {neg2(fma2(ff1, f0.x, mul2(ff2, b.x))), neg2(fma2(ff1, f0.y, mul2(ff2, b.y))), neg2(fma2(ff1, f0.z, mul2(ff2, b.z)))};
+    f1 = {sub2(sv.x, f0.x), sub2(sv.y, f0.y), sub2(sv.z, f0.z)};
+    f2 = {sub2(b.x, sv.x), sub2(b.y, sv.y), sub2(b.z, sv.z)};
+    f3 = {neg2(b.x), neg2(b.y), neg2(b.z)};
+  }
+  if (T.p14_on) {
+    const float4 ab = __ldg(T.dih2_p14ab + pair);
+    const float2 qq = __ldg(T.dih2_p14q + pair);
+    const v3p d = sub3p(p0, p3);
+    const u64 sc = mul2(pair14_2<ENERGY>(d, pk(ab.x, ab.y), pk(ab.z, ab.w), pk(qq.x, qq.y), P, E), fs);
+    f0 = {fma2(sc, d.x, f0.x), fma2(sc, d.y, f0.y), fma2(sc, d.z, f0.z)};
+    f3 = {fma2(neg2(sc), d.x, f3.x), fma2(neg2(sc), d.y, f3.y), fma2(neg2(sc), d.z, f3.z)};
+  }
+  emit2<FIXED>(S, sl.x & 0xffff, sl.z & 0xffff, a0, b0, f0);
+  emit2<FIXED>(S, sl.x >> 16, sl.z >> 16, a1, b1, f1);
+  emit2<FIXED>(S, sl.y & 0xffff, sl.w & 0xffff, a2, b2, f2);
+  emit2<FIXED>(S, sl.y >> 16, sl.w >> 16, a3, b3, f3);
+}
+
+// 1-4 pairs that no packed dihedral owns (their dihedral has k = 0 everywhere, or is a general torsion)
+template <bool ENERGY, bool FIXED>
+__device__ __forceinline__ void p14_task(const Smem& S, const DevTopo& T, const ForceParams& P, int pair, Energies& E) {
+  if (pair >= T.n14_2) return;
+  const uint2 q = __ldg(T.p142_idx + pair);
+  const uint4 sl = FIXED ? make_uint4(0u, 0u, 0u, 0u) : __ldg(T.p142_slot + pair);
+  const float4 ab = __ldg(T.p142_ab + pair);
+  const float2 qq = __ldg(T.p142_q + pair);
+  const uint32_t a0 = q.x & 0xff, a1 = (q.x >> 8) & 0xff, b0 = q.y & 0xff, b1 = (q.y >> 8) & 0xff;
+  const v3p d = sub3p(load3p(S, a0, b0), load3p(S, a1, b1));
+  const u64 sc = mul2(pair14_2<ENERGY>(d, pk(ab.x, ab.y), pk(ab.z, ab.w), pk(qq.x, qq.y), P, E), dup2(FIXED ? kFixedScale : 1.0f));
+  emit2_pm<FIXED>(S, sl.x & 0xffff, sl.x >> 16, sl.z & 0xffff, sl.z >> 16, a0, a1, b0, b1, scale3p(sc, d));
+}
+
+// General torsion, one item per lane: evaluate_torsion, forces.py:147-174 / 228-255, 540-602, for what the packed
+// series cannot express -- impropers (either branch), CHARMM harmonic slices, non-integer or > 6 periodicities.
+// Items [0, nspec) are special dihedrals (energy slot "dihedrals"), the rest impropers.
+template <bool ENERGY, bool FIXED>
+__device__ __forceinline__ void torsion_task(const Smem& S, const DevTopo& T, int item, Energies& E) {
+  if (item < T.gen_begin || item >= T.gen_end) return;
+  const uint32_t q = __ldg(T.gen_idx + item);
+  const uint2 sl = FIXED ? make_uint2(0u, 0u) : __ldg(T.gen_slot + item);
+  const float4 p0 = S.pos[q & 0xff], p1 = S.pos[(q >> 8) & 0xff], p2 = S.pos[(q >> 16) & 0xff], p3 = S.pos[q >> 24];
+  const f3 r12 = sub3(p0, p1), r23 = sub3(p1, p2), r34 = sub3(p2, p3);
+  const f3 cA = cross3(r12, r23), cB = cross3(r23, r34);
+  const float nA2 = dot3(cA, cA), nB2 = dot3(cB, cB), n23sq = dot3(r23, r23);
+  const float rnA = fast_rsqrt(nA2), rnB = fast_rsqrt(nB2), rn23 = fast_rsqrt(n23sq), n23 = n23sq * rn23;
+  // cosPhi = A.B / (|A||B|);  sinPhi = (C.B)/(|C||B|) with C = r23 x A  =>  |r23| (r12.B) / (|A||B|)
+  const float rab = rnA * rnB;
+  const float cosPhi = dot3(cA, cB) * rab, sinPhi = n23 * dot3(r12, cB) * rab;
+  const float hinv = fast_rsqrt(fmaf(cosPhi, cosPhi, sinPhi * sinPhi));
+  const float c = cosPhi * hinv, s = -sinPhi * hinv;  // cos / sin of phi = -atan2(sinPhi, cosPhi)
+  const uint2 tr = __ldg(T.gen_terms + item);
+  float pot = 0.0f, coeff = 0.0f;
+  for (uint32_t t = tr.x; t < tr.x + tr.y; ++t) {
+    const float4 tp = __ldg(T.gen_term_prm + t);  // k0, per | marker, c0, s0
+    if (tp.y > 0.0f) {                            // AMBER, integer periodicity (forces.py:565-569)
+      float cn = c, sn = s;
+      for (float k = 1.5f; k < tp.y; k += 1.0f) {
+        const float t0 = fmaf(cn, c, -sn * s);
+        sn = fmaf(cn, s, sn * c);
+        cn = t0;
+      }
+      pot += tp.x * (1.0f + fmaf(cn, tp.z, sn * tp.w));      // k (1 + cos(n phi - phi0))
+      coeff -= tp.y * tp.x * fmaf(sn, tp.z, -cn * tp.w);     // -n k sin(n phi - phi0)
+    } else {
+      const float phi = atan2f(s, c);
+      if (tp.y == kTermHarmonic) {          // CHARMM harmonic (forces.py:570-576)
+        float ad = phi - tp.z;
+        const float pi_f = 3.14159265358979323846f;
+        if (ad < -pi_f) ad += 2.0f * pi_f; else if (ad > pi_f) ad -= 2.0f * pi_f;
+        pot += tp.x * ad * ad;
+        coeff += 2.0f * tp.x * ad;
+      } else {                              // AMBER with a non-integer periodicity: general path
+        float sn, cs;
+        sincosf(fmaf(tp.w, phi, -tp.z), &sn, &cs);
+        pot += tp.x * (1.0f + cs);
+        coeff -= tp.w * tp.x * sn;
       }
     }
-    if (ENERGY) Eacc += (double)pot;
-    // OpenMM-style projection (forces.py:582-600)
-    const float ff0 = -coeff * n23 * (rnA * rnA), ff3 = coeff * n23 * (rnB * rnB);
-    const float rn23sq = rn23 * rn23;
-    const float ff1 = dot3(r12, r23) * rn23sq, ff2 = dot3(r34, r23) * rn23sq;
-    const float ax = ff0 * cA.x, ay = ff0 * cA.y, az = ff0 * cA.z;
-    const float bx = ff3 * cB.x, by = ff3 * cB.y, bz = ff3 * cB.z;
-    const float sx = fmaf(ff1, ax, -ff2 * bx), sy = fmaf(ff1, ay, -ff2 * by), sz = fmaf(ff1, az, -ff2 * bz);
-    f0x = -ax; f0y = -ay; f0z = -az;
-    f1x = ax + sx; f1y = ay + sy; f1z = az + sz;
-    f2x = bx - sx; f2y = by - sy; f2z = bz - sz;
-    f3x = -bx; f3y = -by; f3z = -bz;
   }
-  if (fuse14) {
-    const float4 prm = __ldg(p14 + item);
-    if (prm.w != 0.0f) {
-      const f3 d = sub3(p0, p3);
-      const float sc = pair14<ENERGY>(d, prm, P, E);
-      f0x = fmaf(sc, d.x, f0x); f0y = fmaf(sc, d.y, f0y); f0z = fmaf(sc, d.z, f0z);
-      f3x = fmaf(-sc, d.x, f3x); f3y = fmaf(-sc, d.y, f3y); f3z = fmaf(-sc, d.z, f3z);
-    }
-  }
-  emit<FIXED>(S, sl.x & 0xffff, q & 0xff, f0x, f0y, f0z, flag);
-  emit<FIXED>(S, sl.x >> 16, (q >> 8) & 0xff, f1x, f1y, f1z, flag);
-  emit<FIXED>(S, sl.y & 0xffff, (q >> 16) & 0xff, f2x, f2y, f2z, flag);
-  emit<FIXED>(S, sl.y >> 16, q >> 24, f3x, f3y, f3z, flag);
-}
-
-// 1-4 pairs that no dihedral item owns (only possible with hand-made parameter objects)
-template <bool ENERGY, bool FIXED>
-__device__ __forceinline__ void p14_task(const Smem& S, const DevTopo& T, const ForceParams& P, int item, Energies& E,
-                                         uint32_t& flag) {
-  if (item >= T.n14) return;
-  const uint32_t q = __ldg(T.p14_idx + item), sl = __ldg(T.p14_slot + item);
-  const float4 prm = __ldg(T.p14_prm + item);
-  const f3 d = sub3(S.pos[q & 0xff], S.pos[(q >> 8) & 0xff]);
-  const float sc = pair14<ENERGY>(d, prm, P, E);
-  emit<FIXED>(S, sl & 0xffff, q & 0xff, sc * d.x, sc * d.y, sc * d.z, flag);
-  emit<FIXED>(S, sl >> 16, (q >> 8) & 0xff, -sc * d.x, -sc * d.y, -sc * d.z, flag);
+  if (ENERGY) E.e[item < T.nspec ? B200MD_E_DIHEDRALS : B200MD_E_IMPROPERS] += (double)pot;
+  if (FIXED) coeff *= kFixedScale;
+  // OpenMM-style projection (forces.py:582-600)
+  const float ff0 = -coeff * n23 * (rnA * rnA), ff3 = coeff * n23 * (rnB * rnB);
+  const float rn23sq = rn23 * rn23;
+  const float ff1 = dot3(r12, r23) * rn23sq, ff2 = dot3(r34, r23) * rn23sq;
+  const float ax = ff0 * cA.x, ay = ff0 * cA.y, az = ff0 * cA.z;
+  const float bx = ff3 * cB.x, by = ff3 * cB.y, bz = ff3 * cB.z;
+  const float sx = fmaf(ff1, ax, -ff2 * bx), sy = fmaf(ff1, ay, -ff2 * by), sz = fmaf(ff1, az, -ff2 * bz);
+  emit<FIXED>(S, sl.x & 0xffff, q & 0xff, -ax, -ay, -az);
+  emit<FIXED>(S, sl.x >> 16, (q >> 8) & 0xff, ax + sx, ay + sy, az + sz);
+  emit<FIXED>(S, sl.y & 0xffff, (q >> 16) & 0xff, bx - sx, by - sy, bz - sz);
+  emit<FIXED>(S, sl.y >> 16, q >> 24, -bx, -by, -bz);
 }
 
 // ---- all tasks of this warp for one force evaluation; positions must be in S.pos ------------------
@@ -456,7 +598,7 @@ __device__ __forceinline__ void p14_task(const Smem& S, const DevTopo& T, const 
 // latency per task, profiles/r01_v11).
 template <int MODE, bool ENERGY, bool FIXED>
 __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const ForceParams& P, int warp, int lane,
-                                          Energies& E, uint32_t& flag) {
+                                          Energies& E) {
   const uint32_t* tk = S.tasks + warp * kMaxTasks;
   int t = 0;
   uint32_t next = tk[0];
@@ -474,13 +616,11 @@ __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const
   }
   B200MD_TASK_LOOP(0, (tile_task<MODE, ENERGY>(S, P, chunk, passes, warp, lane, E)))
   B200MD_TASK_LOOP(1, (tile_diag_task<MODE, ENERGY>(S, P, chunk & 0xff, (chunk >> 8) & 0xff, passes, warp, lane, E)))
-  B200MD_TASK_LOOP(2, (torsion_task<ENERGY, FIXED>(S, P, T.dih_on != 0, T.p14_on != 0, item, T.ndih, T.dih_idx, T.dih_terms,
-                                                   T.dih_term_prm, T.dih_slot, T.dih_p14, E.e[B200MD_E_DIHEDRALS], E, flag)))
-  B200MD_TASK_LOOP(3, (torsion_task<ENERGY, FIXED>(S, P, true, false, item, T.nimp, T.imp_idx, T.imp_terms, T.imp_term_prm,
-                                                   T.imp_slot, nullptr, E.e[B200MD_E_IMPROPERS], E, flag)))
-  B200MD_TASK_LOOP(4, (angle_task<ENERGY, FIXED>(S, T, item, E, flag)))
-  B200MD_TASK_LOOP(5, (bond_task<ENERGY, FIXED>(S, T, P, item, E, flag)))
-  B200MD_TASK_LOOP(6, (p14_task<ENERGY, FIXED>(S, T, P, item, E, flag)))
+  B200MD_TASK_LOOP(2, (dihedral_task<ENERGY, FIXED>(S, T, P, item, (int)passes, E)))
+  B200MD_TASK_LOOP(3, (torsion_task<ENERGY, FIXED>(S, T, item, E)))
+  B200MD_TASK_LOOP(4, (angle_task<ENERGY, FIXED>(S, T, item, E)))
+  B200MD_TASK_LOOP(5, (bond_task<ENERGY, FIXED>(S, T, P, item, E)))
+  B200MD_TASK_LOOP(6, (p14_task<ENERGY, FIXED>(S, T, P, item, E)))
 #undef B200MD_TASK_LOOP
 }
 
@@ -500,7 +640,7 @@ __device__ __forceinline__ void smd_task(const Smem& S, const ForceParams& P, fl
 // ---- per-atom gather in a fixed order: j-side slot, 4 i-side partials, bonded slots, SMD ------------
 template <bool FIXED>
 __device__ __forceinline__ void gather_forces(const Smem& S, const ForceParams& P, int a, float& fx, float& fy,
-                                              float& fz) {
+                                              float& fz, uint32_t& flag) {
   fx = S.fj[a]; fy = S.fj[kMaxAtoms + a]; fz = S.fj[2 * kMaxAtoms + a];
 #pragma unroll
   for (int w = 0; w < kWarps; ++w) {
@@ -510,7 +650,9 @@ __device__ __forceinline__ void gather_forces(const Smem& S, const ForceParams& 
     S.fi[(w * 3 + 0) * kMaxAtoms + a] = 0.0f; S.fi[(w * 3 + 1) * kMaxAtoms + a] = 0.0f; S.fi[(w * 3 + 2) * kMaxAtoms + a] = 0.0f;  // re-arm
   }
   if (FIXED) {  // bonded forces arrived as fixed-point atomics; read and re-arm the accumulators
-    fx += (float)S.fbi[a] * kFixedInv; fy += (float)S.fbi[kMaxAtoms + a] * kFixedInv; fz += (float)S.fbi[2 * kMaxAtoms + a] * kFixedInv;
+    const int ix = S.fbi[a], iy = S.fbi[kMaxAtoms + a], iz = S.fbi[2 * kMaxAtoms + a];
+    if (max(max(abs(ix), abs(iy)), abs(iz)) > kFixedLimit) flag |= B200MD_FLAG_FORCE_RANGE;
+    fx += (float)ix * kFixedInv; fy += (float)iy * kFixedInv; fz += (float)iz * kFixedInv;
     S.fbi[a] = 0; S.fbi[kMaxAtoms + a] = 0; S.fbi[2 * kMaxAtoms + a] = 0;
   } else {
     const int g1 = S.gstart[a + 1];

@@ -32,6 +32,7 @@ constexpr float kBoltzman = 0.001987191f;           // upstream torchmd.integrat
 enum TaskKind : uint32_t { TASK_TILE = 0, TASK_BOND = 1, TASK_ANGLE = 2, TASK_DIHEDRAL = 3, TASK_IMPROPER = 4, TASK_P14 = 5, TASK_DIAG = 6 };
 // execution order of the kinds inside a warp's task list
 constexpr int kNumKinds = 7;
+constexpr int kMaxPer = 6;  // largest periodicity of the packed torsion series
 __host__ __device__ inline uint32_t make_task(uint32_t kind, uint32_t chunk, uint32_t passes) {
   return kind | (chunk << 8) | (passes << 24);
 }
@@ -49,15 +50,18 @@ struct DevTopo {
   const int* ab_row_off;    // [128] byte offset of atom's row in the shared-memory 12A / -6B tables
   const uint8_t* mask8;     // [kMaxChunks][128] bit s: pair (i, 8*chunk+s) is NOT evaluated
   const uint32_t* diagmask;  // [128] bit j: pair (i, 32*block(i) + j) is not evaluated in the diagonal block
-  int nbonds, nangles, ndih, nimp, n14;   // n14: 1-4 pairs NOT fused into a dihedral item ("orphans")
-  int dih_on, p14_on;                     // proper-torsion part / fused 1-4 part of the dihedral items
-  // every bonded item carries the slot ids (atom-major float4 slots) its force vectors go to
-  const uint32_t* bond_idx;  const float2* bond_prm;  const uint32_t* bond_slot;   // s0 | s1 << 16
-  const uint32_t* angle_idx; const float2* angle_prm; const uint2* angle_slot;     // s0 | s1 << 16, s2
-  const uint32_t* dih_idx;   const uint2* dih_terms;  const float4* dih_term_prm;  const uint2* dih_slot;
-  const float4* dih_p14;     // [ndih] A/scnb*12, B/scnb*6, K qi qj/scee, has14 (0/1): 1-4 pair on atoms 0,3
-  const uint32_t* imp_idx;   const uint2* imp_terms;  const float4* imp_term_prm;  const uint2* imp_slot;
-  const uint32_t* p14_idx;   const float4* p14_prm;   const uint32_t* p14_slot;    // orphans only
+  // packed bonded kinds: lane p of chunk c (pair index 32c + p) evaluates two items (A, B) in f32x2
+  int nbond2, nangle2, ndih2, n14_2;      // lane pairs in use per kind
+  int dih_on, p14_on;                     // proper-torsion part / fused 1-4 part of the packed dihedral items
+  const uint2* bond2_idx;  const float4* bond2_prm;  const uint4* bond2_slot;    // atoms 4 x u8 (A, B); (kA, kB, r0A, r0B)
+  const uint2* angle2_idx; const float4* angle2_prm; const uint4* angle2_slot;   // (kA, kB, theta0A, theta0B)
+  const uint2* dih2_idx;   const float4* dih2_coef;  const float2* dih2_k0;      // coef[n-1][pair] = n a_n (A, B), n b_n (A, B)
+  const uint4* dih2_slot;  const float4* dih2_p14ab; const float2* dih2_p14q;    // fused 1-4: 12A' (A, B), -6B' (A, B); K qi qj'
+  int dih2_stride;
+  const uint2* p142_idx;   const float4* p142_ab;    const float2* p142_q;   const uint4* p142_slot;
+  // general torsions (one item per lane): special dihedrals [0, nspec) then impropers [nspec, ngen)
+  int ngen, nspec, gen_begin, gen_end;
+  const uint32_t* gen_idx;   const uint2* gen_terms;  const float4* gen_term_prm;  const uint2* gen_slot;
   int nslots;
   const uint16_t* gather_start;  // [129]: slots of atom a are [gather_start[a], gather_start[a+1])
   const uint32_t* tasks;  // [kWarps][kMaxTasks]
@@ -155,6 +159,11 @@ __host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, i
 __device__ __forceinline__ float fast_rsqrt(float x) {
   float y;
   asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float fast_sqrt(float x) {
+  float y;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
 __device__ __forceinline__ float fast_rcp(float x) {
