@@ -295,45 +295,60 @@ void build_terms(int nitems, int nterms, const int32_t* owner, const float* prm,
 }
 
 // Orders the items of one bonded kind into consecutive lane sets (`sets`: sizes, <= 32 each) whose members touch
-// distinct shared-memory banks at every atom position: the fused integrator accumulates bonded forces with
-// shared-memory atomics (bank = atom mod 32), which serialise on bank and on address collisions (4.6 wavefronts per
-// ATOMS in topology order, profiles/r01_v11), and the position gathers want the 8 lanes of a quarter warp on
-// distinct atoms mod 8.  `order` must be sorted by `key`; a set draws from the lowest keys still available (a window
-// of its own size), so chunks keep near-uniform periodicity bounds.
-std::vector<int> spread_banks(const std::vector<int>& order, const int32_t* idx, int arity, const std::vector<long long>& key,
-                              const std::vector<int>& sets) {
-  (void)key;
+// distinct shared-memory banks (atom mod 32) at every atom position: the packed bonded tasks gather positions with
+// LDS.32 and accumulate forces with shared-memory integer atomics, and both serialise on bank collisions (2-6
+// wavefronts per instruction in topology order, profiles/r01_v14).  Greedy fill, then pairwise swaps between sets
+// while they lower the collision count (deterministic: fixed LCG seed).
+int bank_cost(const std::vector<int>& seq, size_t begin, int size, const int32_t* idx, int arity) {
+  int cost = 0;
+  for (int k = 0; k < arity; ++k) {
+    int cnt[32] = {0};
+    for (int l = 0; l < size; ++l) cnt[idx[arity * seq[begin + l] + k] & 31]++;
+    for (int b = 0; b < 32; ++b) cost += cnt[b] > 1 ? (cnt[b] - 1) * (cnt[b] - 1) : 0;
+  }
+  return cost;
+}
+std::vector<int> spread_banks(const std::vector<int>& order, const int32_t* idx, int arity, const std::vector<int>& sets) {
   std::vector<int> out;
   std::vector<char> used(order.size(), 0);
-  size_t first = 0;  // first unused position
   for (int size : sets) {
-    uint32_t busy[4] = {0, 0, 0, 0}, busy8[4] = {0, 0, 0, 0};
+    uint32_t busy[4] = {0, 0, 0, 0};
     for (int fill = 0; fill < size; ++fill) {
-      if (fill % 8 == 0) for (int k = 0; k < 4; ++k) busy8[k] = 0;
-      while (first < order.size() && used[first]) ++first;
-      // candidates: the next 2 * (remaining lanes of this set) unused items in key order
-      const int window = 2 * (size - fill) + 8;
       long best = -1;
-      int bestc = 1 << 30, seen = 0;
-      for (size_t m = first; m < order.size() && seen < window && bestc > 0; ++m) {
+      int bestc = 1 << 30;
+      for (size_t m = 0; m < order.size() && bestc > 0; ++m) {
         if (used[m]) continue;
-        ++seen;
         int c = 0;
-        for (int k = 0; k < arity; ++k) {
-          const int a = idx[arity * order[m] + k];
-          c += 3 * ((busy[k] >> (a & 31)) & 1u) + ((busy8[k] >> (a & 7)) & 1u);
-        }
+        for (int k = 0; k < arity; ++k) c += (busy[k] >> (idx[arity * order[m] + k] & 31)) & 1u;
         if (c < bestc) { bestc = c; best = (long)m; }
       }
       if (best < 0) break;
       used[best] = 1;
       out.push_back(order[best]);
-      for (int k = 0; k < arity; ++k) {
-        const int a = idx[arity * order[best] + k];
-        busy[k] |= 1u << (a & 31);
-        busy8[k] |= 1u << (a & 7);
-      }
+      for (int k = 0; k < arity; ++k) busy[k] |= 1u << (idx[arity * order[best] + k] & 31);
     }
+  }
+  std::vector<size_t> begin;
+  size_t pos = 0;
+  for (int size : sets) { begin.push_back(pos); pos += size; }
+  if (out.size() != pos || sets.size() < 2) return out;
+  auto set_of = [&](size_t m) { size_t s2 = 0; while (s2 + 1 < begin.size() && begin[s2 + 1] <= m) ++s2; return s2; };
+  uint32_t rng = 12345u;
+  auto next = [&]() { rng = rng * 1664525u + 1013904223u; return rng >> 8; };
+  for (int it = 0; it < 40000; ++it) {
+    const size_t m1 = next() % out.size(), m2 = next() % out.size();
+    const size_t s1 = set_of(m1), s2 = set_of(m2);
+    if (s1 == s2) continue;
+    const int before = bank_cost(out, begin[s1], sets[s1], idx, arity) + bank_cost(out, begin[s2], sets[s2], idx, arity);
+    if (before == 0) continue;
+    std::swap(out[m1], out[m2]);
+    const int after = bank_cost(out, begin[s1], sets[s1], idx, arity) + bank_cost(out, begin[s2], sets[s2], idx, arity);
+    if (after >= before) std::swap(out[m1], out[m2]);
+  }
+  if (getenv("B200MD_DEBUG")) {
+    int total = 0;
+    for (size_t s2 = 0; s2 < sets.size(); ++s2) total += bank_cost(out, begin[s2], sets[s2], idx, arity);
+    fprintf(stderr, "b200md: spread_banks arity %d items %zu sets %zu residual collision cost %d\n", arity, out.size(), sets.size(), total);
   }
   return out;
 }
@@ -482,7 +497,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
       sets.push_back(na);
       sets.push_back(r - na);
     }
-    K.seq = spread_banks(items, idx, arity, key, sets);
+    K.seq = spread_banks(items, idx, arity, sets);
     K.lane_a.assign((size_t)K.nchunks * 32, -1);
     K.lane_b.assign((size_t)K.nchunks * 32, -1);
     K.chunk_key.assign(K.nchunks, 0);
