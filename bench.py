@@ -34,6 +34,7 @@ FLOP_PER_REPLICA_STEP = 240824  # SURVEY.md 8d, ALA10 plain NVE (force-only eval
 FLOP_PER_REPLICA_EVAL = 236144
 NOMINAL_FP32_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.5
 TIMEFACTOR = 48.88821
+NCU_DRAM_BYTES_PER_LAUNCH = 31.1e6  # profiles/r01_v14_integrate_kernel.md: 31.08 MB read + 0.04 MB written
 BOLTZMAN = 0.001987191
 
 
@@ -181,7 +182,7 @@ def run_reference(args):
     import multiprocessing as mp
 
     cores = os.cpu_count() or 1
-    nrep, nsteps = 2, 25  # per core and per bench step: 50 replica-steps x ~4 ms
+    nrep, nsteps = 4, 400  # per core and per bench step: 1 600 replica-steps x ~1.3 ms = ~2 s of CPU work
     pool = mp.get_context("spawn").Pool(cores)
     try:
         for _ in range(max(1, min(args.warmup, 1))):
@@ -325,6 +326,49 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = world * R * S * e2e_steps / float(t.item())
 
+    # ---- secondary workloads (BASELINE.json configs[1] and configs[3]); reported under "extra", N = 1 only -----
+    extra = {}
+    if world == 1 and not args.no_extra:
+        def timed(fn, reps):
+            fn()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(reps):
+                fn()
+            b.record()
+            torch.cuda.synchronize()
+            return a.elapsed_time(b) * 1e-3 / reps
+
+        # configs[1]: batched energy + force evaluation over 65 536 conformers (Forces.compute, one launch)
+        R2 = 65536
+        reps2 = -(-R2 // R)
+        big = torch.tensor(pos_h, device=dev).repeat(reps2, 1, 1)[:R2].contiguous()
+        big += 0.01 * torch.randn(big.shape, device=dev, generator=torch.Generator(device=dev).manual_seed(7))
+        sys2 = System(104, R2, torch.float, dev)
+        sys2.pos[:] = big
+        for label, kw in (("plain", {}), ("cutoff9_rfa_switch7.5", {"cutoff": 9.0, "rfa": True, "switch_dist": 7.5})):
+            f2 = Forces(par, **kw)
+            f2.check_nan = False
+            t2 = timed(lambda: f2.compute_batch(sys2.pos, sys2.box, sys2.forces), 5)
+            flop = FLOP_PER_REPLICA_EVAL + (8 * 4820 if kw else 0)
+            extra[f"forces_compute_65536_{label}"] = {"value": R2 / t2, "unit": "replica-evaluations/s", "ms_per_launch": 1e3 * t2,
+                                                      "tflops": R2 / t2 * flop / 1e12}
+        del sys2, big
+        # configs[3]: Langevin 300 K, gamma = 1/ps, steered-MD end-to-end restraint moving 12 -> 34 A
+        from molecular_dynamics_b200 import SMDBias
+        nst = min(S, 500)
+        f3 = Forces(par, external=SMDBias([3], [98], fk=1.0, cent_0=12.0, cent_1=34.0, rate_per_step=22.0 / 500000))
+        f3.check_nan = False
+        sys3 = System(104, R, torch.float, dev)
+        sys3.pos[:] = torch.tensor(pos_h, device=dev)
+        sys3.vel[:] = torch.tensor(vel_h, device=dev)
+        f3.compute_batch(sys3.pos, sys3.box, sys3.forces)
+        integ3 = Integrator(sys3, f3, timestep=1.0, device=dev, gamma=1.0, T=300.0, seed=42)
+        integ3.energy_every, integ3.check_nan = args.energy_every, False
+        t3 = timed(lambda: integ3.step(niter=nst), 2)
+        extra["langevin_smd"] = {"value": R * nst / t3, "unit": "replica-steps/s", "replicas": R, "md_steps_per_launch": nst}
+
     if rank == 0:
         peak = lib.b200md_fp32_peak_tflops(local, 4096)
         achieved = value / world * FLOP_PER_REPLICA_STEP / 1e12  # per GPU
@@ -342,19 +386,23 @@ def run_ours(args):
                     "steps": e2e_steps},
             "gpu_launches": int(launches),
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                         "frac": achieved / peak if peak > 0 else None, "traffic": None,
+                         "frac": achieved / peak if peak > 0 else None, "traffic": NCU_DRAM_BYTES_PER_LAUNCH,
+                         "traffic_source": "ncu --set full of one 50-step launch, profiles/ (dram read + write; the state is read once per launch whatever its length)",
                          "peak_source": "measured live: b200md_fp32_peak_tflops (dependent-FMA kernel, all SMs)",
                          "nominal_peak": NOMINAL_FP32_TFLOPS, "frac_of_nominal": achieved / NOMINAL_FP32_TFLOPS,
                          "flop_per_replica_step": FLOP_PER_REPLICA_STEP, "kernel": "integrate_kernel<0>",
                          "kernel_ms_per_launch": ms / args.steps},
         }
+        if extra:
+            line["extra"] = extra
         if world == 1 and not args.no_cpu:
             cores = os.cpu_count() or 1
-            rate, slowest, _ = cpu_port_rate(cores, 2, 25)
+            rate, slowest, _ = cpu_port_rate(cores, 4, 3000)
             line["cpu_baseline"] = {
                 "value": rate, "unit": "replica-steps/s", "cores": cores, "kind": "port",
-                "sample": f"{cores} procs x 2 replicas x 25 MD steps, torch port (oracle/torchmd_port.py), fp32, "
-                          f"1 thread each; slowest worker {slowest:.2f} s"}
+                "sample": f"{cores} procs x 4 replicas x 3000 MD steps of the same workload, torch port of "
+                          f"TorchMD_Fix/forces.py + upstream VV loop (oracle/torchmd_port.py), fp32, 1 thread each; "
+                          f"slowest worker {slowest:.1f} s"}
             try:
                 line["cpu_baseline_c_oracle"] = {
                     "value": cpu_c_oracle_rate(64 * cores, 20), "unit": "replica-steps/s", "cores": cores,
@@ -376,6 +424,7 @@ def main():
     ap.add_argument("--inner", type=int, default=1000, help="MD steps per launch (Integrator.step niter)")
     ap.add_argument("--energy-every", type=int, default=100)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extra", action="store_true", help="skip the secondary workloads (configs[1], configs[3])")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -62,7 +62,7 @@ enum b200md_status {
 /* per-replica status flags written by the kernels (uint32 per replica) */
 #define B200MD_FLAG_NAN_POS 1u
 #define B200MD_FLAG_PBC_UNSUPPORTED 2u /* non-zero box diagonal: minimum-image path not built yet */
-#define B200MD_FLAG_FORCE_RANGE 4u     /* integrator: a bonded force vector exceeded 2048 kcal/mol/A (fixed-point range) */
+#define B200MD_FLAG_FORCE_RANGE 4u     /* integrator: the bonded force on an atom exceeded 4096 kcal/mol/A (fixed-point range) */
 
 /*
  * Host-side description of one molecule's parameters: the flattened content of the `parameters`

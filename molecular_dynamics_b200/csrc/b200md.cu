@@ -652,7 +652,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   std::vector<Task> all;
   // cost model of the schedule (issue slots per warp); B200MD_COSTS="pass,chunk,diagstep,diag,bond,angle,dih,imp,p14"
   // overrides it for tuning runs
-  int cm[9] = {150, 120, 52, 30, 110, 230, 380, 400, 100};
+  int cm[9] = {105, 120, 52, 30, 77, 230, 380, 400, 100};
   if (const char* env = getenv("B200MD_COSTS")) sscanf(env, "%d,%d,%d,%d,%d,%d,%d,%d,%d", cm, cm + 1, cm + 2, cm + 3, cm + 4, cm + 5, cm + 6, cm + 7, cm + 8);
   const int nblocks = (N + 31) / 32;
   if (d->npairs > 0) {

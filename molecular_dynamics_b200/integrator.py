@@ -105,9 +105,9 @@ class Integrator:
             if flags & _cabi.FLAG_PBC_UNSUPPORTED:
                 raise NotImplementedError("non-zero box: periodic wrapping has no CUDA path yet")
             if flags & _cabi.FLAG_FORCE_RANGE:
-                raise RuntimeError("a bonded force exceeded 2048 kcal/mol/A: the fused integrator accumulates bonded "
-                                   "forces in 2^-17 fixed point and the system has blown up (reduce the timestep or "
-                                   "relax the start structure)")
+                raise RuntimeError("the bonded force on an atom exceeded 4096 kcal/mol/A: the fused integrator accumulates "
+                                   "bonded forces in 2^-17 fixed point and the system has blown up (reduce the timestep "
+                                   "or relax the start structure)")
         self.observables, self.snapshots = obs, snaps
         last = obs[-1]
         Ekin = last[:, _cabi.OBS_EKIN].cpu().numpy()

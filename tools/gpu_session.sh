@@ -13,7 +13,7 @@ timeout 600 python bench.py > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err; e
 cat $OUT/${TAG}_bench.json
 kill $SMI
 if [ "${SKIP_NCU:-0}" != "1" ]; then
-CMD="python bench.py --steps 3 --warmup 3 --inner 50 --no-cpu"
+CMD="python bench.py --steps 3 --warmup 3 --inner 50 --no-cpu --no-extra"
 timeout 300 $CMD > $OUT/${TAG}_plain.log 2>&1 &&
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu_l.log 2>&1
 timeout 300 $CMD > $OUT/${TAG}_plain2.log 2>&1 &&
