@@ -108,7 +108,7 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
 // forces of a replica stay in registers / shared memory for all nsteps; HBM sees only the initial
 // load, the final store, the observable records and the optional snapshots.
 template <int MODE>
-__global__ void __launch_bounds__(kThreads, 5)
+__global__ void __launch_bounds__(kThreads, 4)
 integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const long long R, float* __restrict__ pos,
                  float* __restrict__ vel, float* __restrict__ forces, const float* __restrict__ box,
                  double* __restrict__ observables, float* __restrict__ snapshots, uint32_t* __restrict__ status) {
