@@ -241,19 +241,25 @@ __device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams&
   const float* sj = S.sx + i0 + 4 * g0;
   uint32_t dm = S.diagmask[i0 + lane] >> (4 * g0);
   u64 pel = 0ull, plj = 0ull, ax = 0ull, ay = 0ull, az = 0ull;
+  // two groups (4 packed pair steps) per iteration: four independent dependency chains to interleave.  An odd `ng`
+  // only occurs at the ragged end of a block, where the extra group is padding (all of its mask bits are set).
 #pragma unroll 1
-  for (int g = 0; g < ng; ++g) {
-    const ulonglong2 xj = *(const ulonglong2*)(sj + 4 * g), yj = *(const ulonglong2*)(sj + kMaxAtoms + 4 * g),
-                     zj = *(const ulonglong2*)(sj + 2 * kMaxAtoms + 4 * g), qj = *(const ulonglong2*)(sj + 3 * kMaxAtoms + 4 * g);
-    const ulonglong2 aj = *(const ulonglong2*)(rowa + 16 * g), bj = *(const ulonglong2*)(rowb + 16 * g);
+  for (int g2 = 0; g2 < ng; g2 += 2) {
 #pragma unroll
-    for (int k = 0; k < 2; ++k) {
-      const u64 dx = sub2(xi, k ? xj.y : xj.x), dy = sub2(yi, k ? yj.y : yj.x), dz = sub2(zi, k ? zj.y : zj.x);
-      const u64 sc = pair_eval2<MODE, ENERGY>(dx, dy, dz, kqi, kq2, k ? qj.y : qj.x, k ? aj.y : aj.x, k ? bj.y : bj.x,
-                                              (dm >> (2 * k)) & 1u, (dm >> (2 * k + 1)) & 1u, P, C, pel, plj);
-      ax = fma2(sc, dx, ax); ay = fma2(sc, dy, ay); az = fma2(sc, dz, az);
+    for (int u = 0; u < 2; ++u) {
+      const int g = g2 + u;
+      const ulonglong2 xj = *(const ulonglong2*)(sj + 4 * g), yj = *(const ulonglong2*)(sj + kMaxAtoms + 4 * g),
+                       zj = *(const ulonglong2*)(sj + 2 * kMaxAtoms + 4 * g), qj = *(const ulonglong2*)(sj + 3 * kMaxAtoms + 4 * g);
+      const ulonglong2 aj = *(const ulonglong2*)(rowa + 16 * g), bj = *(const ulonglong2*)(rowb + 16 * g);
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const u64 dx = sub2(xi, k ? xj.y : xj.x), dy = sub2(yi, k ? yj.y : yj.x), dz = sub2(zi, k ? zj.y : zj.x);
+        const u64 sc = pair_eval2<MODE, ENERGY>(dx, dy, dz, kqi, kq2, k ? qj.y : qj.x, k ? aj.y : aj.x, k ? bj.y : bj.x,
+                                                (dm >> (4 * u + 2 * k)) & 1u, (dm >> (4 * u + 2 * k + 1)) & 1u, P, C, pel, plj);
+        ax = fma2(sc, dx, ax); ay = fma2(sc, dy, ay); az = fma2(sc, dz, az);
+      }
     }
-    dm >>= 4;
+    dm >>= 8;
   }
   float* f = S.fi + warp * 3 * kMaxAtoms + i0 + lane;
   f[0] = __fadd_rn(f[0], hsum2(ax)); f[kMaxAtoms] = __fadd_rn(f[kMaxAtoms], hsum2(ay)); f[2 * kMaxAtoms] = __fadd_rn(f[2 * kMaxAtoms], hsum2(az));
