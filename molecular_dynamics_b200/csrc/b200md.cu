@@ -689,11 +689,11 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   const uint32_t kind_order[kNumKinds] = {TASK_TILE, TASK_DIAG, TASK_DIHEDRAL, TASK_IMPROPER, TASK_ANGLE, TASK_BOND, TASK_P14};
   for (int w = 0; w < kWarps; ++w) {
     int n = 0;
+    T.kend8[w] = make_uint2(0u, 0u);
     for (int k = 0; k < kNumKinds; ++k) {
       for (uint32_t word : mine[w]) if ((word & 0xff) == kind_order[k]) tasks[(size_t)w * kMaxTasks + n++] = word;
-      T.kend[w][k] = n;
+      (k < 4 ? T.kend8[w].x : T.kend8[w].y) |= (uint32_t)n << (8 * (k & 3));
     }
-    T.kend[w][kNumKinds] = n;
   }
 
   // ---- upload --------------------------------------------------------------------------------------

@@ -606,11 +606,12 @@ template <int MODE, bool ENERGY, bool FIXED>
 __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const ForceParams& P, int warp, int lane,
                                           Energies& E) {
   const uint32_t* tk = S.tasks + warp * kMaxTasks;
+  const uint2 kends = T.kend8[warp];  // the 7 run ends as bytes: one constant load instead of one per kind
   int t = 0;
   uint32_t next = tk[0];
 #define B200MD_TASK_LOOP(K, BODY)                                                     \
   {                                                                                   \
-    const int end = T.kend[warp][K];                                                  \
+    const int end = (int)(((K) < 4 ? kends.x >> (8 * ((K) & 3)) : kends.y >> (8 * ((K) & 3))) & 0xffu);  \
     _Pragma("unroll 1") for (; t < end;) {                                            \
       const uint32_t task = next;                                                     \
       next = tk[++t];                                                                 \

@@ -65,7 +65,7 @@ struct DevTopo {
   int nslots;
   const uint16_t* gather_start;  // [129]: slots of atom a are [gather_start[a], gather_start[a+1])
   const uint32_t* tasks;  // [kWarps][kMaxTasks]
-  int kend[kWarps][8];    // per warp: end index of the k-th run of its kind-sorted task list (kTaskOrder)
+  uint2 kend8[kWarps];    // per warp: end index of the k-th run of its kind-sorted task list, one byte per kind
   int smem_bytes, smem_bytes_fixed;
 };
 
