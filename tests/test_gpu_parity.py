@@ -9,6 +9,8 @@ Tolerances (BASELINE.json north_star, calibrated in SURVEY.md 8c):
     the total would need fp64 pair arithmetic; the reference's own fp32 run is at 1e-6 / 3.5e-6 of the
     totals); harmonic impropers <= 5e-6.  Achieved values: profiles/*parity_report.md.
 """
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -340,3 +342,41 @@ def test_snapshots_and_reports_layout():
     assert np.abs(integ.snapshots.cpu().numpy() - out["snapshots"]).max() < 1e-4
     np.testing.assert_allclose(integ.observables.cpu().numpy()[:, :, :8].sum(-1), out["observables"][:, :, :8].sum(-1),
                                rtol=1e-5, atol=1e-3)
+
+
+def test_nve_energy_drift_100k_steps_matches_fp64_oracle():
+    """BASELINE.json configs[2] check: NVE drift of E_pot + E_kin over 100 000 fused steps (dt = 1 fs, bench conformers),
+    and the same statistic against the FP64 oracle over the horizon the oracle finishes in seconds.  Trajectories
+    diverge chaotically, so the comparison is statistical (tools/nve_drift.py, profiles/r01_nve_drift.jsonl:
+    GPU 0.20 +- 0.22 kcal/mol per 100 ps at E_tot = 552, RMS fluctuation 0.49; oracle and GPU agree over 10 ps)."""
+    import bench
+    import sys as _sys
+    _sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    from nve_drift import drift_stats
+
+    g = load_golden("ala10")
+    R, RO, NO = 16, 8, 5000
+    pos, vel = bench.synth_inputs(bench.load_ala10(), R)
+    par, s = make_system(g, pos, vel)
+    F = Forces(par)
+    F.compute_batch(s.pos, s.box, s.forces)
+    f0 = s.forces.cpu().numpy().astype(np.float64)
+    integ = Integrator(s, F, timestep=1.0, device=DEV)
+    integ.energy_every = 100
+    chunks = []
+    for _ in range(5):
+        integ.step(niter=20000)
+        chunks.append(integ.observables.cpu().numpy())
+    obs = np.concatenate(chunks, 0)
+    etot = obs[:, :, :8].sum(-1) + obs[:, :, _cabi.OBS_EKIN]
+    assert np.isfinite(etot).all()
+    drift, rms = drift_stats(etot)
+    assert np.abs(drift).max() < 1.5 and abs(drift.mean()) < 0.6, drift  # kcal/mol per 100 ps at E_tot ~ 550
+    assert rms.max() < 1.0, rms
+    out = oracle.integrate(g.packed, pos[:RO], vel[:RO], f0[:RO], nsteps=NO, dt=np.float32(integ.dt), energy_every=100)
+    eo = out["observables"][:, :, :8].sum(-1) + out["observables"][:, :, _cabi.OBS_EKIN]
+    do, ro = drift_stats(eo)
+    dg, rg = drift_stats(etot[:NO // 100, :RO])
+    assert np.abs(etot[0, :RO] - eo[0]).max() < 0.05          # still the same trajectory after 100 steps
+    assert abs(dg.mean() - do.mean()) < 0.25, (dg, do)        # same transient drift over the common horizon
+    assert abs(rg.mean() / ro.mean() - 1.0) < 0.3, (rg, ro)   # same fluctuation amplitude

@@ -1,0 +1,87 @@
+#!/usr/bin/env python
+"""NVE energy-drift statistics of the fused integrator (BASELINE.json configs[2] check) next to the FP64 oracle.
+
+    python tools/nve_drift.py [--replicas 64] [--steps 100000] [--oracle-steps 10000] [--dt 1.0]
+
+Prints one JSON line: per-replica drift of E_tot = E_pot + E_kin (least-squares slope x run length, kcal/mol),
+RMS fluctuation about the fit, for the CUDA path over the full run and for both paths over the oracle's horizon.
+"""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def drift_stats(etot):
+    """etot (reports, R) -> (drift per replica over the run, rms about the linear fit)."""
+    n = etot.shape[0]
+    t = np.arange(n, dtype=np.float64)
+    t -= t.mean()
+    slope = (t[:, None] * (etot - etot.mean(0))).sum(0) / (t * t).sum()
+    fit = etot.mean(0) + slope * t[:, None]
+    return slope * (n - 1), np.sqrt(((etot - fit) ** 2).mean(0))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--replicas", type=int, default=64)
+    ap.add_argument("--steps", type=int, default=100000)
+    ap.add_argument("--oracle-steps", type=int, default=10000)
+    ap.add_argument("--oracle-replicas", type=int, default=8)
+    ap.add_argument("--dt", type=float, default=1.0)
+    ap.add_argument("--every", type=int, default=100)
+    a = ap.parse_args()
+    import torch
+
+    import bench
+    import oracle
+    from molecular_dynamics_b200 import Forces, Integrator, Parameters, System, _cabi
+
+    g = bench.load_ala10()
+    dev = torch.device("cuda", 0)
+    par = Parameters.from_arrays({k[4:]: v for k, v in g.items() if k.startswith("par_")}, device=dev)
+    pos, vel = bench.synth_inputs(g, a.replicas)
+    s = System(104, a.replicas, torch.float, dev)
+    s.pos[:] = torch.tensor(pos, device=dev)
+    s.vel[:] = torch.tensor(vel, device=dev)
+    F = Forces(par)
+    F.compute_batch(s.pos, s.box, s.forces)
+    f0 = s.forces.cpu().numpy().astype(np.float64)
+    integ = Integrator(s, F, timestep=a.dt, device=dev)
+    integ.energy_every = a.every
+    chunks = []
+    done = 0
+    while done < a.steps:  # launches of <= 20 000 steps (observable buffer stays small)
+        n = min(20000, a.steps - done)
+        integ.step(niter=n)
+        chunks.append(integ.observables.cpu().numpy())
+        done += n
+    obs = np.concatenate(chunks, 0)
+    etot = obs[:, :, :8].sum(-1) + obs[:, :, _cabi.OBS_EKIN]
+    d, r = drift_stats(etot)
+    out = {"dt_fs": a.dt, "steps": a.steps, "replicas": a.replicas, "energy_every": a.every,
+           "gpu": {"etot0_mean": float(etot[0].mean()), "ekin_mean": float(obs[:, :, _cabi.OBS_EKIN].mean()),
+                   "drift_mean": float(d.mean()), "drift_abs_max": float(np.abs(d).max()), "drift_std": float(d.std()),
+                   "rms_fluct_mean": float(r.mean()), "rms_fluct_max": float(r.max())}}
+    if a.oracle_steps > 0:
+        packed = _cabi.PackedTopology(Parameters.from_arrays({k[4:]: v for k, v in g.items() if k.startswith("par_")}), g["ava_idx"])
+        ro = a.oracle_replicas
+        o = oracle.integrate(packed, pos[:ro], vel[:ro], f0[:ro], nsteps=a.oracle_steps, dt=np.float32(integ.dt), energy_every=a.every)
+        eo = o["observables"][:, :, :8].sum(-1) + o["observables"][:, :, _cabi.OBS_EKIN]
+        do, ro_ = drift_stats(eo)
+        nrep = a.oracle_steps // a.every
+        dg, rg = drift_stats(etot[:nrep, :ro])
+        out["oracle_fp64"] = {"steps": a.oracle_steps, "replicas": ro, "drift_mean": float(do.mean()), "drift_abs_max": float(np.abs(do).max()),
+                              "rms_fluct_mean": float(ro_.mean())}
+        out["gpu_same_horizon"] = {"drift_mean": float(dg.mean()), "drift_abs_max": float(np.abs(dg).max()), "rms_fluct_mean": float(rg.mean()),
+                                   "etot_first_report_max_abs_diff": float(np.abs(etot[0, :ro] - eo[0]).max())}
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
