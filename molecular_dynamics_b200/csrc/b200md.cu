@@ -45,7 +45,7 @@ __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, co
   if (FIXED) {
     for (int k = tid; k < 3 * kMaxAtoms; k += kThreads) S.fbi[k] = 0;
   } else {
-    for (int k = tid; k < 3 * T.nslots; k += kThreads) S.fb[k] = 0.0f;
+    for (int k = tid; k < 4 * T.nslots; k += kThreads) S.fb[k] = 0.0f;
   }
   // chunks without a tile task (no non-bonded term enabled) must read as zero in the gather
   for (int k = tid; k < 3 * kMaxAtoms; k += kThreads) S.fj[k] = 0.0f;
@@ -68,15 +68,24 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
   const int N = T.natoms;
   stage_tables<false>(S, T, P, tid);
   const float q = tid < N ? __ldg(T.charge + tid) * P.el_on : 0.0f;
+  // the positions of the CTA's next replica are fetched while the current one is evaluated
+  float nx = 0.f, ny = 0.f, nz = 0.f;
+  if (tid < N && (long long)blockIdx.x < R) {
+    const float* p = pos + ((long long)blockIdx.x * N + tid) * 3;
+    nx = __ldg(p); ny = __ldg(p + 1); nz = __ldg(p + 2);
+  }
   for (long long r = blockIdx.x; r < R; r += gridDim.x) {
     __syncthreads();  // previous replica fully consumed (and tables staged)
     uint32_t flag = 0;
     if (tid < N) {
-      const float* p = pos + (r * N + tid) * 3;
-      const float x = __ldg(p), y = __ldg(p + 1), z = __ldg(p + 2);
+      const float x = nx, y = ny, z = nz;
       if (x != x || y != y || z != z) flag |= B200MD_FLAG_NAN_POS;
       S.pos[tid] = make_float4(x, y, z, q);
       S.sx[tid] = x; S.sx[kMaxAtoms + tid] = y; S.sx[2 * kMaxAtoms + tid] = z; S.sx[3 * kMaxAtoms + tid] = q;
+      if (r + gridDim.x < R) {
+        const float* p = pos + ((r + gridDim.x) * N + tid) * 3;
+        nx = __ldg(p); ny = __ldg(p + 1); nz = __ldg(p + 2);
+      }
     }
     if (box != nullptr && tid < 3 && __ldg(box + r * 9 + tid * 4) != 0.0f) flag |= B200MD_FLAG_PBC_UNSUPPORTED;
     if (status != nullptr) {
@@ -96,7 +105,7 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
       f[0] = fx; f[1] = fy; f[2] = fz;
     }
     if (P.smd_on && tid == 0) E.e[B200MD_E_EXTERNAL] += S.smd_energy[0];
-    reduce_energies(S, E, warp, lane);
+    reduce_energies<B200MD_NUM_ENERGIES>(S, E, warp, lane);
     if (tid == 0) {
 #pragma unroll
       for (int k = 0; k < B200MD_NUM_ENERGIES; ++k) energies[r * B200MD_NUM_ENERGIES + k] = E.e[k];
@@ -178,7 +187,7 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       if (report) {
         if (live) E.e[B200MD_OBS_EKIN] = 0.5 * (double)mass * ((double)vx * vx + (double)vy * vy + (double)vz * vz);
         if (P.smd_on && tid == 0) { E.e[B200MD_E_EXTERNAL] += S.smd_energy[0]; E.e[B200MD_OBS_E2E_DIST] = (double)S.smd[4]; }
-        reduce_energies(S, E, warp, lane);
+        reduce_energies<B200MD_NUM_OBSERVABLES>(S, E, warp, lane);
         if (tid == 0 && observables != nullptr) {
           const long long slot = I.energy_every > 0 ? (s + 1) / I.energy_every - 1 : 0;
           double* o = observables + (slot * R + r) * B200MD_NUM_OBSERVABLES;

@@ -271,7 +271,7 @@ __device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams&
 }
 
 // ---- bonded items: where a force vector goes ---------------------------------------------------------
-// FIXED = false (single-shot Forces.compute): private atom-major 12-byte slots, summed per atom in a fixed
+// FIXED = false (single-shot Forces.compute): private atom-major 16-byte slots, summed per atom in a fixed
 //   order after the barrier -- exact fp32 sums for arbitrarily large forces (generated / clashing frames).
 // FIXED = true (fused integrator): 2^-17 kcal/mol/A fixed point, one shared-memory integer atomic per
 //   component.  Integer addition is associative, so the sum is still order-independent and bit-reproducible,
@@ -288,8 +288,7 @@ __device__ __forceinline__ void emit(const Smem& S, uint32_t slot, uint32_t atom
     atomicAdd(S.fbi + kMaxAtoms + atom, __float2int_rn(y));
     atomicAdd(S.fbi + 2 * kMaxAtoms + atom, __float2int_rn(z));
   } else {
-    float* p = S.fb + 3 * slot;
-    p[0] = x; p[1] = y; p[2] = z;
+    ((float4*)S.fb)[slot] = make_float4(x, y, z, 0.0f);
   }
 }
 // +v to (slot0, atom0) and -v to (slot1, atom1) from one conversion
@@ -301,10 +300,8 @@ __device__ __forceinline__ void emit_pm(const Smem& S, uint32_t slot0, uint32_t 
     atomicAdd(S.fbi + atom0, ix); atomicAdd(S.fbi + kMaxAtoms + atom0, iy); atomicAdd(S.fbi + 2 * kMaxAtoms + atom0, iz);
     atomicAdd(S.fbi + atom1, -ix); atomicAdd(S.fbi + kMaxAtoms + atom1, -iy); atomicAdd(S.fbi + 2 * kMaxAtoms + atom1, -iz);
   } else {
-    float* p = S.fb + 3 * slot0;
-    p[0] = x; p[1] = y; p[2] = z;
-    float* q = S.fb + 3 * slot1;
-    q[0] = -x; q[1] = -y; q[2] = -z;
+    ((float4*)S.fb)[slot0] = make_float4(x, y, z, 0.0f);
+    ((float4*)S.fb)[slot1] = make_float4(-x, -y, -z, 0.0f);
   }
 }
 
@@ -665,8 +662,8 @@ __device__ __forceinline__ void gather_forces(const Smem& S, const ForceParams& 
     const int g1 = S.gstart[a + 1];
 #pragma unroll 4
     for (int g = S.gstart[a]; g < g1; ++g) {
-      const float* v = S.fb + 3 * g;
-      fx += v[0]; fy += v[1]; fz += v[2];
+      const float4 v = ((const float4*)S.fb)[g];
+      fx += v.x; fy += v.y; fz += v.z;
     }
   }
   if (P.smd_on) {
@@ -675,10 +672,11 @@ __device__ __forceinline__ void gather_forces(const Smem& S, const ForceParams& 
   }
 }
 
-// ---- block reduction of the FP64 accumulators (fixed order); thread 0 ends with the totals ---------
+// ---- block reduction of the first NOBS FP64 accumulators (fixed order); thread 0 ends with the totals -------
+template <int NOBS>
 __device__ __forceinline__ void reduce_energies(const Smem& S, Energies& E, int warp, int lane) {
 #pragma unroll
-  for (int k = 0; k < B200MD_NUM_OBSERVABLES; ++k) {
+  for (int k = 0; k < NOBS; ++k) {
     double v = E.e[k];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -687,7 +685,7 @@ __device__ __forceinline__ void reduce_energies(const Smem& S, Energies& E, int 
   __syncthreads();
   if (warp == 0 && lane == 0) {
 #pragma unroll
-    for (int k = 0; k < B200MD_NUM_OBSERVABLES; ++k)
+    for (int k = 0; k < NOBS; ++k)
       E.e[k] = (S.ered[k] + S.ered[B200MD_NUM_OBSERVABLES + k]) +
                (S.ered[2 * B200MD_NUM_OBSERVABLES + k] + S.ered[3 * B200MD_NUM_OBSERVABLES + k]);
   }

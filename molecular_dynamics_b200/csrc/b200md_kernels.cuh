@@ -98,7 +98,7 @@ struct Smem {
   uint32_t* diagmask;  // [128]
   float* fi;          // [kWarps][3][128]
   float* fj;          // [3][128]
-  float* fb;          // [nslots][3] atom-major bonded force slots (slot mode)
+  float* fb;          // [nslots] float4: atom-major bonded force slots (slot mode)
   int* fbi;           // [3][128] fixed-point bonded force accumulators (fixed mode)
   float4* vel;        // [128] velocities parked during the task phase of the integrator
   uint16_t* gstart;   // [130]
@@ -152,7 +152,7 @@ __host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, i
     s->tb = (float*)(base + kOffAb + tab);
     s->fb = (float*)(base + off_fb);
   }
-  return fixed ? off_fb : off_fb + align16(sizeof(float) * 3 * (size_t)(nslots > 0 ? nslots : 1));
+  return fixed ? off_fb : off_fb + sizeof(float4) * (size_t)(nslots > 0 ? nslots : 1);
 }
 
 // ---- small math helpers ---------------------------------------------------------------------
