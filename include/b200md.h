@@ -45,7 +45,8 @@ enum b200md_term_bit {
   B200MD_T_DIHEDRALS = 1u << 4,
   B200MD_T_14 = 1u << 5,
   B200MD_T_IMPROPERS = 1u << 6,
-  B200MD_T_REPULSION = 1u << 7,   /* forces.py:416-431 (A r^-12 only)  */
+  B200MD_T_REPULSION = 1u << 7,   /* forces.py:416-431 (A r^-12 only): energy reported in slot B200MD_E_LJ; */
+                                  /* at most one of LJ / REPULSION / REPULSIONCG per call                   */
   B200MD_T_REPULSIONCG = 1u << 8  /* forces.py:434-448 (B r^-6 only)   */
 };
 

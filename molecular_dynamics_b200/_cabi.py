@@ -20,6 +20,12 @@ MAX_ATOMS = 128
 
 # dict order of the reference's result (forces.py:40-50, :100)
 ENERGY_SLOTS = ("electrostatics", "lj", "bonds", "angles", "dihedrals", "1-4", "impropers", "external")
+
+
+def energy_slot(term):
+    """Column of the (R, 8) energy block a term is reported in: the one enabled pair term of the lj family
+    (lj / repulsion / repulsioncg, forces.py:258-316) uses the "lj" column (include/b200md.h)."""
+    return ENERGY_SLOTS.index("lj" if term in ("repulsion", "repulsioncg") else term)
 TERM_BITS = {"electrostatics": 1 << 0, "lj": 1 << 1, "bonds": 1 << 2, "angles": 1 << 3, "dihedrals": 1 << 4,
              "1-4": 1 << 5, "impropers": 1 << 6, "repulsion": 1 << 7, "repulsioncg": 1 << 8}
 

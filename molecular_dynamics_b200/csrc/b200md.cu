@@ -27,8 +27,8 @@ __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, co
   for (int t = 0; t < T.ntypes; ++t)
     for (int j = tid; j < kTabStride; j += kThreads) {
       const float2 v = j < kMaxAtoms ? __ldg(T.ab + t * kAbStride + j) : make_float2(0.f, 0.f);
-      S.ta[t * kTabStride + j] = v.x * P.lj_on;
-      S.tb[t * kTabStride + j] = -(v.y * P.lj_on);
+      S.ta[t * kTabStride + j] = v.x * P.tab_a;
+      S.tb[t * kTabStride + j] = v.y * P.tab_b;
     }
   for (int k = tid; k < kMaxAtoms; k += kThreads) {
     S.ab_row_off[k] = __ldg(T.ab_row_off + k);
@@ -768,14 +768,18 @@ extern "C" int b200md_topology_natoms(const b200md_topology* topo) { return topo
 static int make_force_params(const b200md_topology* topo, const b200md_force_opts* o, const b200md_smd_opts* smd,
                              bool integrator, ForceParams* P) {
   if (!o) return fail(B200MD_ERR_INVALID_ARGUMENT, "force options are required");
-  if (o->terms & (B200MD_T_REPULSION | B200MD_T_REPULSIONCG))
-    return fail(B200MD_ERR_UNSUPPORTED, "repulsion / repulsioncg terms are not implemented");
+  // forces.py:258-316 evaluates "lj", "repulsion" (A r^-12, :416-431) and "repulsioncg" (B r^-6, :434-448) over the
+  // same pair list; this ABI has ONE pair-table slot and reports its energy in B200MD_E_LJ, so at most one of the
+  // three may be enabled per call
+  const int nfamily = !!(o->terms & B200MD_T_LJ) + !!(o->terms & B200MD_T_REPULSION) + !!(o->terms & B200MD_T_REPULSIONCG);
+  if (nfamily > 1)
+    return fail(B200MD_ERR_UNSUPPORTED, "at most one of lj / repulsion / repulsioncg per call (they share the pair-table slot)");
   memset(P, 0, sizeof(*P));
   P->terms = o->terms;
   P->has_cutoff = o->cutoff > 0.0f;
   P->rc = o->cutoff;
   P->rc2 = o->cutoff * o->cutoff;
-  const bool sw = P->has_cutoff && o->switch_dist > 0.0f;  // forces.py:402
+  const bool sw = P->has_cutoff && o->switch_dist > 0.0f && (o->terms & B200MD_T_LJ);  // forces.py:402 (evaluate_LJ only)
   P->rs = sw ? o->switch_dist : INFINITY;
   P->inv_sw = sw ? 1.0f / (o->cutoff - o->switch_dist) : 0.0f;
   if (o->rfa) {
@@ -785,6 +789,8 @@ static int make_force_params(const b200md_topology* topo, const b200md_force_opt
     P->crf = (float)((1.0 / rc) * (3.0 * eps) / denom);
   }
   P->lj_on = (o->terms & B200MD_T_LJ) ? 1.0f : 0.0f;
+  P->tab_a = (o->terms & (B200MD_T_LJ | B200MD_T_REPULSION)) ? 1.0f : 0.0f;
+  P->tab_b = (o->terms & B200MD_T_LJ) ? -1.0f : ((o->terms & B200MD_T_REPULSIONCG) ? 1.0f : 0.0f);
   P->el_on = (o->terms & B200MD_T_ELECTROSTATICS) ? 1.0f : 0.0f;
   if (smd && smd->enabled) {
     if (smd->atom1 < 0 || smd->atom1 >= topo->natoms || smd->atom2 < 0 || smd->atom2 >= topo->natoms ||

@@ -74,7 +74,8 @@ struct ForceParams {
   int has_cutoff;
   float rc, rc2, rs, inv_sw;  // cutoff, cutoff^2, switch_dist (or +inf), 1/(rc-rs)
   float krf, crf;             // reaction-field constants (0 when rfa is off)
-  float lj_on, el_on;
+  float lj_on, el_on;         // 1-4 block switches (forces.py:176-226 tests "lj" / "electrostatics")
+  float tab_a, tab_b;         // pair tables = (tab_a * 12A, tab_b * 6B): lj (1, -1), repulsion (1, 0), repulsioncg (0, +1)
   int smd_on, smd_a1, smd_a2;
   float smd_fk, smd_c0, smd_rate;
   const float* smd_centers;

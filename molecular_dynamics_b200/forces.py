@@ -116,9 +116,9 @@ class Forces:
                 raise ValueError(f"Force term {et} is not implemented.")
         if "1-4" in self.energies and "dihedrals" not in self.energies:
             raise RuntimeError("You cannot enable 1-4 interactions without enabling dihedrals")
-        for et in ("repulsion", "repulsioncg"):
-            if et in self.energies:
-                raise NotImplementedError(f"term {et!r} (forces.py:416-448) has no CUDA path in this build")
+        if sum(et in self.energies for et in ("lj", "repulsion", "repulsioncg")) > 1:
+            raise NotImplementedError("at most one of 'lj', 'repulsion', 'repulsioncg' per Forces object: the CUDA path "
+                                      "has one pair-table slot (forces.py:281-311 would evaluate them one after another)")
         self.natoms = len(parameters.masses)
         self.require_distances = any(f in self.nonbonded for f in self.energies)
         self._pair_idx = (_cabi.make_pair_index(self.natoms, parameters.get_exclusions(exclusions))
@@ -250,7 +250,7 @@ class Forces:
         else:
             ene = self.compute_batch(pos, box, forces).to(pos.dtype)
         keys = list(self.energies) + ["external"]
-        cols = [_cabi.ENERGY_SLOTS.index(k) for k in keys]
+        cols = [_cabi.energy_slot(k) for k in keys]
         if not explicit_forces:  # Q13: return the summed tensor
             return ene[:, cols].sum().reshape(1)
         pot = []

@@ -113,6 +113,6 @@ class Integrator:
         Ekin = last[:, _cabi.OBS_EKIN].cpu().numpy()
         T = kinetic_to_temp(Ekin, N)
         keys = list(f.energies) + ["external"]
-        cols = [_cabi.ENERGY_SLOTS.index(k) for k in keys]
+        cols = [_cabi.energy_slot(k) for k in keys]
         pot = last[:, cols].sum(dim=1).to(pos.dtype)
         return Ekin, [pot[i] for i in range(R)], T

@@ -255,8 +255,18 @@ static void forces_one(const b200md_topology_desc* T, const b200md_force_opts* O
         e[B200MD_E_LJ] += E;
         c += dE;
       }
-      /* repulsion / repulsioncg (forces.py:416-448) have no energy slot among the 8 reported ones
-       * in this ABI; they are not exercised by any reference caller and are left out of the oracle. */
+      /* evaluate_repulsion (forces.py:416-431): A r^-12; evaluate_repulsion_CG (:434-448): B r^-6.  Never switched.
+       * The ABI reports the one enabled term of the lj family in the B200MD_E_LJ slot. */
+      if (terms & B200MD_T_REPULSION) {
+        double r6 = pow(1.0 / dist, 6), aa = T->lj_a[ti * T->ntypes + tj];
+        e[B200MD_E_LJ] += aa * r6 * r6;
+        c += -12.0 * aa * r6 * r6 / dist;
+      }
+      if (terms & B200MD_T_REPULSIONCG) {
+        double r6 = pow(1.0 / dist, 6), bb = T->lj_b[ti * T->ntypes + tj];
+        e[B200MD_E_LJ] += bb * r6;
+        c += -6.0 * bb * r6 / dist;
+      }
       addf(f, i, d, -c / dist);
       addf(f, j, d, c / dist);
     }

@@ -380,3 +380,29 @@ def test_nve_energy_drift_100k_steps_matches_fp64_oracle():
     assert np.abs(etot[0, :RO] - eo[0]).max() < 0.05          # still the same trajectory after 100 steps
     assert abs(dg.mean() - do.mean()) < 0.25, (dg, do)        # same transient drift over the common horizon
     assert abs(rg.mean() / ro.mean() - 1.0) < 0.3, (rg, ro)   # same fluctuation amplitude
+
+
+@pytest.mark.parametrize("system", ["bb40", "ala10"])
+@pytest.mark.parametrize("case", ["rep_plain", "rep_cut", "cg_plain", "cg_rf"])
+def test_repulsion_terms_vs_reference_fp64(system, case):
+    """SURVEY 8 row a12 (forces.py:416-448): CUDA path against the unmodified reference run in fp64
+    (tests/golden/repulsion.npz, tools/make_golden_repulsion.py)."""
+    from test_oracle import REPULSION_CASES
+
+    g = load_golden(system)
+    with np.load(os.path.join(os.path.dirname(__file__), "golden", "repulsion.npz")) as z:
+        r = {k: z[k] for k in z.files if k.startswith(system)}
+    terms, kw = REPULSION_CASES[case]
+    F = Forces(gpu_par(g), terms=terms, **kw)
+    pos = torch.tensor(r[f"{system}_pos"], device=DEV)
+    s = System(pos.shape[1], pos.shape[0], torch.float, DEV)
+    pot = F.compute(pos, s.box, s.forces, returnDetails=True)
+    fr = r[f"{system}_{case}_f64_forces"]
+    f = s.forces.cpu().numpy()
+    assert (np.abs(f - fr).reshape(len(f), -1).max(1) / np.abs(fr).reshape(len(f), -1).max(1)).max() <= 1e-5
+    assert set(pot[0]) == set(terms) | {"external"}
+    for t in terms:
+        got = np.array([float(p[t]) for p in pot])
+        np.testing.assert_allclose(got, r[f"{system}_{case}_f64_E_{t}"], rtol=2e-6)
+    with pytest.raises(NotImplementedError):
+        Forces(gpu_par(g), terms=("lj", "repulsion"))

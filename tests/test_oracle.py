@@ -7,6 +7,8 @@ Anchors, in order of authority:
   3. the colvar known answers (smd_out.colvars.traj) for the SMD end-to-end distance;
   4. the restated upstream velocity-Verlet loop driving the reference forces.py (unpinned upstream).
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -187,3 +189,27 @@ def test_torch_port_integrator_matches_c_oracle():
     ekin, ene = port.integrate(top, p, v, f, 25, dt)
     np.testing.assert_allclose(p.numpy(), out["pos"], atol=1e-9)
     np.testing.assert_allclose(ekin.numpy(), out["observables"][0, :, _cabi.OBS_EKIN], rtol=1e-9)
+
+
+REPULSION_CASES = {  # tools/make_golden_repulsion.py
+    "rep_plain": (("repulsion",), {}),
+    "rep_cut": (("repulsion", "bonds"), {"cutoff": 9.0, "switch_dist": 7.5}),
+    "cg_plain": (("repulsioncg", "electrostatics", "bonds"), {}),
+    "cg_rf": (("repulsioncg", "electrostatics", "angles"), {"cutoff": 9.0, "rfa": True, "switch_dist": 7.5}),
+}
+
+
+@pytest.mark.parametrize("system", ["bb40", "ala10"])
+@pytest.mark.parametrize("case", sorted(REPULSION_CASES))
+def test_oracle_repulsion_terms_vs_reference(system, case):
+    """evaluate_repulsion / evaluate_repulsion_CG (forces.py:416-448) against the unmodified
+    reference in fp64; the ABI reports the enabled lj-family term in the "lj" column."""
+    g = load_golden(system)
+    with np.load(os.path.join(os.path.dirname(__file__), "golden", "repulsion.npz")) as z:
+        r = {k: z[k] for k in z.files if k.startswith(system)}
+    terms, kw = REPULSION_CASES[case]
+    f, e = oracle.forces(g.packed, r[f"{system}_pos"], terms=terms, **kw)
+    fr = r[f"{system}_{case}_f64_forces"]
+    assert np.abs(f - fr).max() <= 1e-9 * np.abs(fr).max()
+    for t in terms:
+        np.testing.assert_allclose(e[:, _cabi.energy_slot(t)], r[f"{system}_{case}_f64_E_{t}"], rtol=1e-10)
