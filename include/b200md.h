@@ -62,7 +62,6 @@ enum b200md_status {
 
 /* per-replica status flags written by the kernels (uint32 per replica) */
 #define B200MD_FLAG_NAN_POS 1u
-#define B200MD_FLAG_PBC_UNSUPPORTED 2u /* non-zero box diagonal: minimum-image path not built yet */
 #define B200MD_FLAG_FORCE_RANGE 4u     /* integrator: the bonded force on an atom exceeded 4096 kcal/mol/A (fixed-point range) */
 
 /*
@@ -166,7 +165,8 @@ int b200md_topology_natoms(const b200md_topology* topo);
 /*
  * Forces.compute (forces.py:82-344) for R replicas: zeroes and fills forces, writes per-term
  * energies.  pos/forces: DEVICE float [R][natoms][3] contiguous; box: DEVICE float [R][3][3] or
- * NULL (= zeros: vacuum, forces.py:107,358-363); energies: DEVICE double [R][8] (FP64-accumulated);
+ * NULL (= zeros: vacuum); a replica with a non-zero box diagonal is evaluated with the minimum-image convention in
+ * every term (wrap_dist, forces.py:107,358-363; off-diagonal entries are ignored like in the reference); energies: DEVICE double [R][8] (FP64-accumulated);
  * status: DEVICE uint32 [R] or NULL.  Asynchronous on `stream`.
  */
 int b200md_forces_compute(const b200md_topology* topo, const b200md_force_opts* opts,

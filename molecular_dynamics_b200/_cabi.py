@@ -31,7 +31,6 @@ TERM_BITS = {"electrostatics": 1 << 0, "lj": 1 << 1, "bonds": 1 << 2, "angles": 
 
 OK, ERR_INVALID_ARGUMENT, ERR_TOO_MANY_ATOMS, ERR_CUDA, ERR_NAN_COORDINATES, ERR_UNSUPPORTED = range(6)
 FLAG_NAN_POS = 1
-FLAG_PBC_UNSUPPORTED = 2
 FLAG_FORCE_RANGE = 4
 
 _i32p, _f32p, _f64p, _u32p = (C.POINTER(C.c_int32), C.POINTER(C.c_float), C.POINTER(C.c_double),

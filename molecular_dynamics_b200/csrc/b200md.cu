@@ -40,7 +40,7 @@ __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, co
     ((uint32_t*)S.mask8)[k] = __ldg((const uint32_t*)T.mask8 + k);
   for (int k = tid; k <= kMaxAtoms; k += kThreads) S.gstart[k] = __ldg(T.gather_start + k);
   for (int k = tid; k < kWarps * kMaxTasks; k += kThreads) S.tasks[k] = __ldg(T.tasks + k);
-  if (tid < 8) S.smd[tid] = 0.0f;
+  if (tid < 8) { S.smd[tid] = 0.0f; S.box[tid] = 0.0f; }
   // slots of disabled / dropped terms are never written: keep them at zero for the gather
   if (FIXED) {
     for (int k = tid; k < 3 * kMaxAtoms; k += kThreads) S.fbi[k] = 0;
@@ -87,7 +87,14 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
         nx = __ldg(p); ny = __ldg(p + 1); nz = __ldg(p + 2);
       }
     }
-    if (box != nullptr && tid < 3 && __ldg(box + r * 9 + tid * 4) != 0.0f) flag |= B200MD_FLAG_PBC_UNSUPPORTED;
+    // box diagonal (forces.py:107); all zero = vacuum, no wrap (forces.py:359)
+    const float b0 = box ? __ldg(box + r * 9) : 0.0f, b1 = box ? __ldg(box + r * 9 + 4) : 0.0f, b2 = box ? __ldg(box + r * 9 + 8) : 0.0f;
+    const bool pbc = b0 != 0.0f || b1 != 0.0f || b2 != 0.0f;
+    if (tid < 3) {
+      const float b = tid == 0 ? b0 : (tid == 1 ? b1 : b2);
+      S.box[tid] = -b;
+      S.box[4 + tid] = b != 0.0f ? 1.0f / b : 0.0f;
+    }
     if (status != nullptr) {
       if (tid == 0) status[r] = 0;
     }
@@ -95,7 +102,8 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
     if (flag && status != nullptr) atomicOr(status + r, flag);
     Energies E;
     E.clear();
-    run_tasks<MODE, true, false>(S, T, P, warp, lane, E);
+    if (pbc) run_tasks<MODE, true, false, true>(S, T, P, warp, lane, E);
+    else run_tasks<MODE, true, false, false>(S, T, P, warp, lane, E);
     if (P.smd_on && tid == kThreads - 1) smd_task(S, P, P.smd_centers ? __ldg(P.smd_centers + r) : P.smd_c0);
     __syncthreads();
     if (tid < N) {
@@ -149,7 +157,13 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       fx = forces[base]; fy = forces[base + 1]; fz = forces[base + 2];
       if (x != x || y != y || z != z) flag |= B200MD_FLAG_NAN_POS;
     }
-    if (box != nullptr && tid < 3 && __ldg(box + r * 9 + tid * 4) != 0.0f) flag |= B200MD_FLAG_PBC_UNSUPPORTED;
+    const float b0 = box ? __ldg(box + r * 9) : 0.0f, b1 = box ? __ldg(box + r * 9 + 4) : 0.0f, b2 = box ? __ldg(box + r * 9 + 8) : 0.0f;
+    const bool pbc = b0 != 0.0f || b1 != 0.0f || b2 != 0.0f;  // forces.py:359: all zero = vacuum, no wrap
+    if (tid < 3) {
+      const float b = tid == 0 ? b0 : (tid == 1 ? b1 : b2);
+      S.box[tid] = -b;
+      S.box[4 + tid] = b != 0.0f ? 1.0f / b : 0.0f;
+    }
     if (status != nullptr && tid == 0) status[r] = 0;
     for (int s = 0; s < I.nsteps; ++s) {
       const unsigned long long gstep = I.step0 + (unsigned long long)s;
@@ -166,9 +180,11 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       Energies E;
       if (report) {
         E.clear();
-        run_tasks<MODE, true, true>(S, T, P, warp, lane, E);
+        if (pbc) run_tasks<MODE, true, true, true>(S, T, P, warp, lane, E);
+        else run_tasks<MODE, true, true, false>(S, T, P, warp, lane, E);
       } else {
-        run_tasks<MODE, false, true>(S, T, P, warp, lane, E);
+        if (pbc) run_tasks<MODE, false, true, true>(S, T, P, warp, lane, E);
+        else run_tasks<MODE, false, true, false>(S, T, P, warp, lane, E);
       }
       if (P.smd_on && tid == kThreads - 1) smd_task(S, P, (float)((double)P.smd_c0 + (double)P.smd_rate * (double)(gstep + 1)));
       __syncthreads();
@@ -906,7 +922,6 @@ extern "C" int b200md_forces_compute_host(const b200md_topology* topo, const b20
       if (e == cudaSuccess)
         for (uint32_t f : st) {
           if (f & B200MD_FLAG_NAN_POS) { rc = fail(B200MD_ERR_NAN_COORDINATES, "Found NaN coordinates."); break; }
-          if (f & B200MD_FLAG_PBC_UNSUPPORTED) { rc = fail(B200MD_ERR_UNSUPPORTED, "non-zero box: periodic wrapping is not implemented"); break; }
         }
     }
   }

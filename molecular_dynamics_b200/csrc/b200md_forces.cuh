@@ -123,9 +123,11 @@ __device__ __forceinline__ u64 pair_eval2(u64 dx, u64 dy, u64 dz, float kqi, u64
 // Lane = i atom; the 8 j atoms arrive as 4 packed pairs (x[], y[], z[], q[] and the 12A / -6B rows are
 // structure-of-arrays, so one LDS.128 delivers two f32x2 operands).  The pass loop is rolled (one body in the
 // instruction cache); the i-side force of a pass is added to this warp's shared-memory partial.
-template <int MODE, bool ENERGY>
+template <int MODE, bool ENERGY, bool PBC>
 __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, int chunk, int passes, int warp,
                                           int lane, Energies& E) {
+  const float4 nbox = PBC ? *(const float4*)S.box : make_float4(0.f, 0.f, 0.f, 0.f);
+  const float4 ibox = PBC ? *(const float4*)(S.box + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
   u64 fjx[kChunk / 2], fjy[kChunk / 2], fjz[kChunk / 2];
 #pragma unroll
   for (int s = 0; s < kChunk / 2; ++s) fjx[s] = fjy[s] = fjz[s] = 0ull;
@@ -161,7 +163,8 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
 #pragma unroll
       for (int k = 0; k < 2; ++k) {
         const int s = 2 * h + k;
-        const u64 dx = sub2(xi, k ? xj.y : xj.x), dy = sub2(yi, k ? yj.y : yj.x), dz = sub2(zi, k ? zj.y : zj.x);
+        u64 dx = sub2(xi, k ? xj.y : xj.x), dy = sub2(yi, k ? yj.y : yj.x), dz = sub2(zi, k ? zj.y : zj.x);
+        if (PBC) { dx = wrap2(dx, nbox.x, ibox.x); dy = wrap2(dy, nbox.y, ibox.y); dz = wrap2(dz, nbox.z, ibox.z); }
         const u64 sc = pair_eval2<MODE, ENERGY>(dx, dy, dz, kqi, kq2, k ? qj.y : qj.x, k ? aj.y : aj.x, k ? bj.y : bj.x,
                                                 (m8 >> (2 * s)) & 1u, (m8 >> (2 * s + 1)) & 1u, P, C, pel, plj);
         ax = fma2(sc, dx, ax); ay = fma2(sc, dy, ay); az = fma2(sc, dz, az);
@@ -227,9 +230,11 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
 // no butterfly, and the whole step stays in packed FP32.  17 packed instructions per two pair evaluations against
 // 26 scalar ones + 3 shuffles per pair of the rotation scheme it replaces (profiles/r01_v10: 46 issue slots per
 // rotation step).  Energies are halved.  diagmask bit j: pair (lane, j) is not evaluated (self, exclusion, padding).
-template <int MODE, bool ENERGY>
+template <int MODE, bool ENERGY, bool PBC>
 __device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams& P, int block, int g0, int ng, int warp,
                                                int lane, Energies& E) {
+  const float4 nbox = PBC ? *(const float4*)S.box : make_float4(0.f, 0.f, 0.f, 0.f);
+  const float4 ibox = PBC ? *(const float4*)(S.box + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
   const int i0 = block * 32;
   const PairConst C = make_pair_const<MODE>(P);
   const float4 pi = S.pos[i0 + lane];
@@ -253,7 +258,8 @@ __device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams&
       const ulonglong2 aj = *(const ulonglong2*)(rowa + 16 * g), bj = *(const ulonglong2*)(rowb + 16 * g);
 #pragma unroll
       for (int k = 0; k < 2; ++k) {
-        const u64 dx = sub2(xi, k ? xj.y : xj.x), dy = sub2(yi, k ? yj.y : yj.x), dz = sub2(zi, k ? zj.y : zj.x);
+        u64 dx = sub2(xi, k ? xj.y : xj.x), dy = sub2(yi, k ? yj.y : yj.x), dz = sub2(zi, k ? zj.y : zj.x);
+        if (PBC) { dx = wrap2(dx, nbox.x, ibox.x); dy = wrap2(dy, nbox.y, ibox.y); dz = wrap2(dz, nbox.z, ibox.z); }
         const u64 sc = pair_eval2<MODE, ENERGY>(dx, dy, dz, kqi, kq2, k ? qj.y : qj.x, k ? aj.y : aj.x, k ? bj.y : bj.x,
                                                 (dm >> (4 * u + 2 * k)) & 1u, (dm >> (4 * u + 2 * k + 1)) & 1u, P, C, pel, plj);
         ax = fma2(sc, dx, ax); ay = fma2(sc, dy, ay); az = fma2(sc, dz, az);
@@ -308,6 +314,16 @@ __device__ __forceinline__ void emit_pm(const Smem& S, uint32_t slot0, uint32_t 
 // ---- packed three-vectors: component pairs (item A, item B) ------------------------------------------
 struct v3p { u64 x, y, z; };
 __device__ __forceinline__ v3p sub3p(v3p a, v3p b) { return {sub2(a.x, b.x), sub2(a.y, b.y), sub2(a.z, b.z)}; }
+// calculate_distances (forces.py:366-370): a - b, minimum image when the replica has a box
+template <bool PBC>
+__device__ __forceinline__ v3p diff3p(const Smem& S, v3p a, v3p b) {
+  v3p d = sub3p(a, b);
+  if (PBC) {
+    const float4 nbox = *(const float4*)S.box, ibox = *(const float4*)(S.box + 4);
+    d.x = wrap2(d.x, nbox.x, ibox.x); d.y = wrap2(d.y, nbox.y, ibox.y); d.z = wrap2(d.z, nbox.z, ibox.z);
+  }
+  return d;
+}
 __device__ __forceinline__ u64 dot3p(v3p a, v3p b) { return fma2(a.z, b.z, fma2(a.y, b.y, mul2(a.x, b.x))); }
 __device__ __forceinline__ u64 neg2(u64 a) { return a ^ 0x8000000080000000ull; }
 __device__ __forceinline__ v3p cross3p(v3p a, v3p b) {
@@ -336,14 +352,14 @@ __device__ __forceinline__ void emit2_pm(const Smem& S, uint32_t sa0, uint32_t s
 }
 
 // evaluate_bonds, forces.py:111-132, 492-501 -- two bonds per lane
-template <bool ENERGY, bool FIXED>
+template <bool ENERGY, bool FIXED, bool PBC>
 __device__ __forceinline__ void bond_task(const Smem& S, const DevTopo& T, const ForceParams& P, int pair, Energies& E) {
   if (pair >= T.nbond2) return;
   const uint2 q = __ldg(T.bond2_idx + pair);
   const float4 prm = __ldg(T.bond2_prm + pair);  // kA, kB, r0A, r0B
   const uint4 sl = FIXED ? make_uint4(0u, 0u, 0u, 0u) : __ldg(T.bond2_slot + pair);
   const uint32_t a0 = q.x & 0xff, a1 = (q.x >> 8) & 0xff, b0 = q.y & 0xff, b1 = (q.y >> 8) & 0xff;
-  const v3p d = sub3p(load3p(S, a0, b0), load3p(S, a1, b1));
+  const v3p d = diff3p<PBC>(S, load3p(S, a0, b0), load3p(S, a1, b1));
   const u64 r2 = dot3p(d, d);
   const u64 rinv = rsqrt2(r2), dist = mul2(r2, rinv);
   float da, db;
@@ -356,13 +372,18 @@ __device__ __forceinline__ void bond_task(const Smem& S, const DevTopo& T, const
   if (ENERGY) {
     // k (r - r0)^2 cancels ~40:1 in (r - r0): the energy (report steps only) takes r in FP64
     const float4 pa0 = S.pos[a0], pa1 = S.pos[a1], pb0 = S.pos[b0], pb1 = S.pos[b1];
+    double bx = 0.0, by = 0.0, bz = 0.0;
+    if (PBC) { bx = -(double)S.box[0]; by = -(double)S.box[1]; bz = -(double)S.box[2]; }
+    auto wrapd = [](double v, double b) { return b != 0.0 ? v - b * rint(v / b) : v; };
     if (keep_a) {
-      const double ddx = (double)pa0.x - (double)pa1.x, ddy = (double)pa0.y - (double)pa1.y, ddz = (double)pa0.z - (double)pa1.z;
+      double ddx = (double)pa0.x - (double)pa1.x, ddy = (double)pa0.y - (double)pa1.y, ddz = (double)pa0.z - (double)pa1.z;
+      if (PBC) { ddx = wrapd(ddx, bx); ddy = wrapd(ddy, by); ddz = wrapd(ddz, bz); }
       const double xd = sqrt(ddx * ddx + ddy * ddy + ddz * ddz) - (double)prm.z;
       E.e[B200MD_E_BONDS] += (double)prm.x * xd * xd;
     }
     if (keep_b) {
-      const double ddx = (double)pb0.x - (double)pb1.x, ddy = (double)pb0.y - (double)pb1.y, ddz = (double)pb0.z - (double)pb1.z;
+      double ddx = (double)pb0.x - (double)pb1.x, ddy = (double)pb0.y - (double)pb1.y, ddz = (double)pb0.z - (double)pb1.z;
+      if (PBC) { ddx = wrapd(ddx, bx); ddy = wrapd(ddy, by); ddz = wrapd(ddz, bz); }
       const double xd = sqrt(ddx * ddx + ddy * ddy + ddz * ddz) - (double)prm.w;
       E.e[B200MD_E_BONDS] += (double)prm.y * xd * xd;
     }
@@ -390,7 +411,7 @@ __device__ __forceinline__ u64 acos2(u64 x) {
 }
 
 // evaluate_angles, forces.py:134-145, 504-537 -- two angles per lane
-template <bool ENERGY, bool FIXED>
+template <bool ENERGY, bool FIXED, bool PBC>
 __device__ __forceinline__ void angle_task(const Smem& S, const DevTopo& T, int pair, Energies& E) {
   if (pair >= T.nangle2) return;
   const uint2 q = __ldg(T.angle2_idx + pair);
@@ -399,7 +420,7 @@ __device__ __forceinline__ void angle_task(const Smem& S, const DevTopo& T, int 
   const uint32_t a0 = q.x & 0xff, a1 = (q.x >> 8) & 0xff, a2 = (q.x >> 16) & 0xff;
   const uint32_t b0 = q.y & 0xff, b1 = (q.y >> 8) & 0xff, b2 = (q.y >> 16) & 0xff;
   const v3p p1 = load3p(S, a1, b1);
-  const v3p r21 = sub3p(load3p(S, a0, b0), p1), r23 = sub3p(load3p(S, a2, b2), p1);
+  const v3p r21 = diff3p<PBC>(S, load3p(S, a0, b0), p1), r23 = diff3p<PBC>(S, load3p(S, a2, b2), p1);
   const u64 n21i = rsqrt2(dot3p(r21, r21)), n23i = rsqrt2(dot3p(r23, r23));
   float cta, ctb;
   upk(mul2(mul2(dot3p(r23, r21), n21i), n23i), cta, ctb);
@@ -451,7 +472,7 @@ __device__ __forceinline__ u64 pair14_2(v3p d, u64 a12, u64 nb6, u64 qq, const F
 // periodicity n, so any number of terms costs the same and there is no branch: cos / sin(n phi) come from
 // (cos phi + i sin phi)^n, phi = -atan2(sinPhi, cosPhi) is never formed.  `nmax` (largest periodicity of the chunk)
 // is warp-uniform.  The 1-4 pair on the end atoms (forces.py:176-226) is fused in (zero parameters if there is none).
-template <bool ENERGY, bool FIXED>
+template <bool ENERGY, bool FIXED, bool PBC>
 __device__ __forceinline__ void dihedral_task(const Smem& S, const DevTopo& T, const ForceParams& P, int pair, int nmax,
                                               Energies& E) {
   if (pair >= T.ndih2) return;
@@ -463,7 +484,7 @@ __device__ __forceinline__ void dihedral_task(const Smem& S, const DevTopo& T, c
   const u64 fs = dup2(FIXED ? kFixedScale : 1.0f);
   v3p f0 = {0ull, 0ull, 0ull}, f1 = f0, f2 = f0, f3 = f0;
   if (T.dih_on) {
-    const v3p r12 = sub3p(p0, p1), r23 = sub3p(p1, p2), r34 = sub3p(p2, p3);
+    const v3p r12 = diff3p<PBC>(S, p0, p1), r23 = diff3p<PBC>(S, p1, p2), r34 = diff3p<PBC>(S, p2, p3);
     const v3p cA = cross3p(r12, r23), cB = cross3p(r23, r34);
     const u64 n23sq = dot3p(r23, r23);
     const u64 rnA = rsqrt2(dot3p(cA, cA)), rnB = rsqrt2(dot3p(cB, cB)), rn23 = rsqrt2(n23sq), n23 = mul2(n23sq, rn23);
@@ -507,7 +528,7 @@ __device__ __forceinline__ void dihedral_task(const Smem& S, const DevTopo& T, c
   if (T.p14_on) {
     const float4 ab = __ldg(T.dih2_p14ab + pair);
     const float2 qq = __ldg(T.dih2_p14q + pair);
-    const v3p d = sub3p(p0, p3);
+    const v3p d = diff3p<PBC>(S, p0, p3);
     const u64 sc = mul2(pair14_2<ENERGY>(d, pk(ab.x, ab.y), pk(ab.z, ab.w), pk(qq.x, qq.y), P, E), fs);
     f0 = {fma2(sc, d.x, f0.x), fma2(sc, d.y, f0.y), fma2(sc, d.z, f0.z)};
     f3 = {fma2(neg2(sc), d.x, f3.x), fma2(neg2(sc), d.y, f3.y), fma2(neg2(sc), d.z, f3.z)};
@@ -519,7 +540,7 @@ __device__ __forceinline__ void dihedral_task(const Smem& S, const DevTopo& T, c
 }
 
 // 1-4 pairs that no packed dihedral owns (their dihedral has k = 0 everywhere, or is a general torsion)
-template <bool ENERGY, bool FIXED>
+template <bool ENERGY, bool FIXED, bool PBC>
 __device__ __forceinline__ void p14_task(const Smem& S, const DevTopo& T, const ForceParams& P, int pair, Energies& E) {
   if (pair >= T.n14_2) return;
   const uint2 q = __ldg(T.p142_idx + pair);
@@ -527,7 +548,7 @@ __device__ __forceinline__ void p14_task(const Smem& S, const DevTopo& T, const 
   const float4 ab = __ldg(T.p142_ab + pair);
   const float2 qq = __ldg(T.p142_q + pair);
   const uint32_t a0 = q.x & 0xff, a1 = (q.x >> 8) & 0xff, b0 = q.y & 0xff, b1 = (q.y >> 8) & 0xff;
-  const v3p d = sub3p(load3p(S, a0, b0), load3p(S, a1, b1));
+  const v3p d = diff3p<PBC>(S, load3p(S, a0, b0), load3p(S, a1, b1));
   const u64 sc = mul2(pair14_2<ENERGY>(d, pk(ab.x, ab.y), pk(ab.z, ab.w), pk(qq.x, qq.y), P, E), dup2(FIXED ? kFixedScale : 1.0f));
   emit2_pm<FIXED>(S, sl.x & 0xffff, sl.x >> 16, sl.z & 0xffff, sl.z >> 16, a0, a1, b0, b1, scale3p(sc, d));
 }
@@ -535,13 +556,19 @@ __device__ __forceinline__ void p14_task(const Smem& S, const DevTopo& T, const 
 // General torsion, one item per lane: evaluate_torsion, forces.py:147-174 / 228-255, 540-602, for what the packed
 // series cannot express -- impropers (either branch), CHARMM harmonic slices, non-integer or > 6 periodicities.
 // Items [0, nspec) are special dihedrals (energy slot "dihedrals"), the rest impropers.
-template <bool ENERGY, bool FIXED>
+template <bool ENERGY, bool FIXED, bool PBC>
 __device__ __forceinline__ void torsion_task(const Smem& S, const DevTopo& T, int item, Energies& E) {
   if (item < T.gen_begin || item >= T.gen_end) return;
   const uint32_t q = __ldg(T.gen_idx + item);
   const uint2 sl = FIXED ? make_uint2(0u, 0u) : __ldg(T.gen_slot + item);
   const float4 p0 = S.pos[q & 0xff], p1 = S.pos[(q >> 8) & 0xff], p2 = S.pos[(q >> 16) & 0xff], p3 = S.pos[q >> 24];
-  const f3 r12 = sub3(p0, p1), r23 = sub3(p1, p2), r34 = sub3(p2, p3);
+  f3 r12 = sub3(p0, p1), r23 = sub3(p1, p2), r34 = sub3(p2, p3);
+  if (PBC) {
+    const float4 nb = *(const float4*)S.box, ib = *(const float4*)(S.box + 4);
+    r12 = {wrap1(r12.x, nb.x, ib.x), wrap1(r12.y, nb.y, ib.y), wrap1(r12.z, nb.z, ib.z)};
+    r23 = {wrap1(r23.x, nb.x, ib.x), wrap1(r23.y, nb.y, ib.y), wrap1(r23.z, nb.z, ib.z)};
+    r34 = {wrap1(r34.x, nb.x, ib.x), wrap1(r34.y, nb.y, ib.y), wrap1(r34.z, nb.z, ib.z)};
+  }
   const f3 cA = cross3(r12, r23), cB = cross3(r23, r34);
   const float nA2 = dot3(cA, cA), nB2 = dot3(cB, cB), n23sq = dot3(r23, r23);
   const float rnA = fast_rsqrt(nA2), rnB = fast_rsqrt(nB2), rn23 = fast_rsqrt(n23sq), n23 = n23sq * rn23;
@@ -599,7 +626,7 @@ __device__ __forceinline__ void torsion_task(const Smem& S, const DevTopo& T, in
 // is a tight loop around its own body: no switch, and the next task word is fetched while the current task runs
 // (the fetch -> decode -> branch chain of a switch-per-task loop cost 33 issue slots and ~150 cycles of exposed
 // latency per task, profiles/r01_v11).
-template <int MODE, bool ENERGY, bool FIXED>
+template <int MODE, bool ENERGY, bool FIXED, bool PBC>
 __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const ForceParams& P, int warp, int lane,
                                           Energies& E) {
   const uint32_t* tk = S.tasks + warp * kMaxTasks;
@@ -618,13 +645,13 @@ __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const
       BODY;                                                                           \
     }                                                                                 \
   }
-  B200MD_TASK_LOOP(0, (tile_task<MODE, ENERGY>(S, P, chunk, passes, warp, lane, E)))
-  B200MD_TASK_LOOP(1, (tile_diag_task<MODE, ENERGY>(S, P, chunk & 0xff, (chunk >> 8) & 0xff, passes, warp, lane, E)))
-  B200MD_TASK_LOOP(2, (dihedral_task<ENERGY, FIXED>(S, T, P, item, (int)passes, E)))
-  B200MD_TASK_LOOP(3, (torsion_task<ENERGY, FIXED>(S, T, item, E)))
-  B200MD_TASK_LOOP(4, (angle_task<ENERGY, FIXED>(S, T, item, E)))
-  B200MD_TASK_LOOP(5, (bond_task<ENERGY, FIXED>(S, T, P, item, E)))
-  B200MD_TASK_LOOP(6, (p14_task<ENERGY, FIXED>(S, T, P, item, E)))
+  B200MD_TASK_LOOP(0, (tile_task<MODE, ENERGY, PBC>(S, P, chunk, passes, warp, lane, E)))
+  B200MD_TASK_LOOP(1, (tile_diag_task<MODE, ENERGY, PBC>(S, P, chunk & 0xff, (chunk >> 8) & 0xff, passes, warp, lane, E)))
+  B200MD_TASK_LOOP(2, (dihedral_task<ENERGY, FIXED, PBC>(S, T, P, item, (int)passes, E)))
+  B200MD_TASK_LOOP(3, (torsion_task<ENERGY, FIXED, PBC>(S, T, item, E)))
+  B200MD_TASK_LOOP(4, (angle_task<ENERGY, FIXED, PBC>(S, T, item, E)))
+  B200MD_TASK_LOOP(5, (bond_task<ENERGY, FIXED, PBC>(S, T, P, item, E)))
+  B200MD_TASK_LOOP(6, (p14_task<ENERGY, FIXED, PBC>(S, T, P, item, E)))
 #undef B200MD_TASK_LOOP
 }
 

@@ -107,6 +107,7 @@ struct Smem {
   double* ered;       // [kWarps][10]
   float* smd;         // [8]: force on atom2 (xyz), -, distance
   double* smd_energy; // [1]
+  float* box;         // [8]: -box diagonal (x, y, z), 0, 1 / box diagonal (0 where the entry is 0), 0
 };
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
@@ -125,7 +126,8 @@ constexpr size_t kOffTasks = kOffGstart + 272;
 constexpr size_t kOffEred = kOffTasks + sizeof(uint32_t) * kWarps * kMaxTasks;
 constexpr size_t kOffSmd = kOffEred + sizeof(double) * kWarps * 10;
 constexpr size_t kOffSmdEnergy = kOffSmd + 32;
-constexpr size_t kOffFbi = kOffSmdEnergy + 16;
+constexpr size_t kOffBox = kOffSmdEnergy + 16;
+constexpr size_t kOffFbi = kOffBox + 32;
 constexpr size_t kOffVel = kOffFbi + sizeof(int) * 3 * kMaxAtoms;
 constexpr size_t kOffSx = kOffVel + sizeof(float4) * kMaxAtoms;
 constexpr size_t kOffAb = kOffSx + sizeof(float) * 4 * kMaxAtoms;
@@ -146,6 +148,7 @@ __host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, i
     s->ered = (double*)(base + kOffEred);
     s->smd = (float*)(base + kOffSmd);
     s->smd_energy = (double*)(base + kOffSmdEnergy);
+    s->box = (float*)(base + kOffBox);
     s->fbi = (int*)(base + kOffFbi);
     s->vel = (float4*)(base + kOffVel);
     s->sx = (float*)(base + kOffSx);
@@ -192,6 +195,17 @@ __device__ __forceinline__ u64 mul2(u64 a, u64 b) { u64 r; asm("mul.rn.f32x2 %0,
 __device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) { u64 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
 __device__ __forceinline__ u64 dup2(float v) { return pk(v, v); }
 __device__ __forceinline__ float hsum2(u64 v) { float a, b; upk(v, a, b); return __fadd_rn(a, b); }
+
+// wrap_dist (forces.py:358-363): d - box * round(d / box), round-half-even through the 1.5 * 2^23 trick (|d / box| < 2^22).
+// nb = -box, ib = 1 / box (0 for a zero box entry: that axis is left alone)
+constexpr float kRoundMagic = 12582912.0f;
+__device__ __forceinline__ u64 wrap2(u64 d, float nb, float ib) {
+  const u64 m = dup2(kRoundMagic);
+  return fma2(dup2(nb), sub2(add2(mul2(d, dup2(ib)), m), m), d);
+}
+__device__ __forceinline__ float wrap1(float d, float nb, float ib) {
+  return __fmaf_rn(nb, __fsub_rn(__fadd_rn(__fmul_rn(d, ib), kRoundMagic), kRoundMagic), d);
+}
 
 struct f3 { float x, y, z; };
 __device__ __forceinline__ f3 sub3(float4 a, float4 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }

@@ -228,8 +228,6 @@ class Forces:
             flags = int(status.max().item()) if R else 0
             if flags & _cabi.FLAG_NAN_POS:
                 raise RuntimeError("Found NaN coordinates.")
-            if flags & 2:
-                raise NotImplementedError("non-zero box: periodic wrapping (forces.py:358-363) has no CUDA path yet")
         if not direct:
             forces.copy_(f)
         if self.external is not None and not isinstance(self.external, SMDBias):  # forces.py:318-323

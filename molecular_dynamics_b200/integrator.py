@@ -102,8 +102,6 @@ class Integrator:
             flags = int(status.max().item()) if R else 0
             if flags & _cabi.FLAG_NAN_POS:
                 raise RuntimeError("Found NaN coordinates.")
-            if flags & _cabi.FLAG_PBC_UNSUPPORTED:
-                raise NotImplementedError("non-zero box: periodic wrapping has no CUDA path yet")
             if flags & _cabi.FLAG_FORCE_RANGE:
                 raise RuntimeError("the bonded force on an atom exceeded 4096 kcal/mol/A: the fused integrator accumulates "
                                    "bonded forces in 2^-17 fixed point and the system has blown up (reduce the timestep "

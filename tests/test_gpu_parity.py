@@ -406,3 +406,46 @@ def test_repulsion_terms_vs_reference_fp64(system, case):
         np.testing.assert_allclose(got, r[f"{system}_{case}_f64_E_{t}"], rtol=2e-6)
     with pytest.raises(NotImplementedError):
         Forces(gpu_par(g), terms=("lj", "repulsion"))
+
+
+@pytest.mark.parametrize("system", ["bb40", "ala10"])
+@pytest.mark.parametrize("mode", sorted(MODES))
+def test_minimum_image_vs_reference_fp64(system, mode):
+    """SURVEY 8 row a3 (wrap_dist, forces.py:358-363): per-replica orthorhombic boxes smaller than the molecule (one
+    replica of the batch in vacuum) against the unmodified reference run in fp64 (tests/golden/pbc.npz)."""
+    g = load_golden(system)
+    with np.load(os.path.join(os.path.dirname(__file__), "golden", "pbc.npz")) as z:
+        r = {k: z[k] for k in z.files if k.startswith(system)}
+    F = Forces(gpu_par(g), **MODES[mode])
+    pos = torch.tensor(r[f"{system}_pos"], device=DEV)
+    box = torch.tensor(r[f"{system}_box"], device=DEV)
+    frc = torch.zeros_like(pos)
+    ene = F.compute_batch(pos, box, frc).cpu().numpy()
+    fr, er = r[f"{system}_{mode}_f64_forces"], r[f"{system}_{mode}_f64_energies"]
+    f = frc.cpu().numpy()
+    assert (np.abs(f - fr).reshape(len(f), -1).max(1) / np.abs(fr).reshape(len(f), -1).max(1)).max() <= 1e-5
+    for k in (2, 3, 4):  # bonds, angles, dihedrals
+        np.testing.assert_allclose(ene[:, k], er[:, k], rtol=2e-6)
+    np.testing.assert_allclose(ene[:, :2].sum(1), er[:, :2].sum(1), rtol=1e-5)  # electrostatics + lj
+
+
+def test_integrator_with_box_short_horizon_vs_oracle():
+    g = load_golden("ala10")
+    pos0 = g["pos"][:4]
+    vel0 = (0.1 * np.random.default_rng(11).standard_normal(pos0.shape)).astype(np.float32)
+    par, s = make_system(g, pos0, vel0)
+    box = np.zeros((4, 3, 3), dtype=np.float32)
+    for r, b in enumerate(([27.0, 24.0, 22.0], [0.0, 0.0, 0.0], [23.0, 30.0, 25.0], [25.0, 25.0, 25.0])):
+        box[r, 0, 0], box[r, 1, 1], box[r, 2, 2] = b
+    s.box[:] = torch.tensor(box, device=DEV)
+    F = Forces(par, cutoff=9.0, rfa=True, switch_dist=7.5)
+    F.compute_batch(s.pos, s.box, s.forces)
+    f0 = s.forces.cpu().numpy().astype(np.float64)
+    integ = Integrator(s, F, timestep=1.0, device=DEV)
+    integ.energy_every = 10
+    integ.step(niter=30)
+    out = oracle.integrate(g.packed, pos0, vel0, f0, nsteps=30, dt=np.float32(integ.dt), energy_every=10, box=box,
+                           cutoff=9.0, rfa=True, switch_dist=7.5)
+    assert np.abs(s.pos.cpu().numpy() - out["pos"]).max() < 3e-4
+    obs = integ.observables.cpu().numpy()
+    np.testing.assert_allclose(obs[:, :, :8].sum(-1), out["observables"][:, :, :8].sum(-1), rtol=2e-5, atol=2e-3)

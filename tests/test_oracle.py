@@ -213,3 +213,17 @@ def test_oracle_repulsion_terms_vs_reference(system, case):
     assert np.abs(f - fr).max() <= 1e-9 * np.abs(fr).max()
     for t in terms:
         np.testing.assert_allclose(e[:, _cabi.energy_slot(t)], r[f"{system}_{case}_f64_E_{t}"], rtol=1e-10)
+
+
+@pytest.mark.parametrize("system", ["bb40", "ala10"])
+@pytest.mark.parametrize("mode", sorted(MODES))
+def test_oracle_minimum_image_vs_reference(system, mode):
+    """wrap_dist (forces.py:358-363) in every term, boxes smaller than the molecule, one replica in
+    vacuum (all-zero box) in the same batch; unmodified reference in fp64 (tools/make_golden_pbc.py)."""
+    g = load_golden(system)
+    with np.load(os.path.join(os.path.dirname(__file__), "golden", "pbc.npz")) as z:
+        r = {k: z[k] for k in z.files if k.startswith(system)}
+    f, e = oracle.forces(g.packed, r[f"{system}_pos"], box=r[f"{system}_box"], **MODES[mode])
+    fr, er = r[f"{system}_{mode}_f64_forces"], r[f"{system}_{mode}_f64_energies"]
+    assert np.abs(f - fr).max() <= 1e-9 * np.abs(fr).max()
+    np.testing.assert_allclose(e, er, rtol=1e-10, atol=1e-9)
