@@ -283,7 +283,8 @@ def run_ours(args):
             b.record()
         barrier()
     launches = lib.b200md_launch_count() - launches0
-    ms = sum(a.elapsed_time(b) for a, b in ev)
+    per_launch = [a.elapsed_time(b) for a, b in ev]
+    ms = sum(per_launch)
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -380,6 +381,7 @@ def run_ours(args):
                        "energy_every": args.energy_every, "dt_fs": 1.0, "natoms": 104,
                        "l2": "flushed between timed steps (256 MiB fill, outside the event pair)",
                        "ns_per_day_aggregate": value * 1.0 * 86400 * 1e-6,
+                       "ms_per_step_median_rank0": statistics.median(per_launch), "ms_per_step_max_rank0": max(per_launch),
                        "replicas_with_nan_after_run": nan_count},
             "clocks": clocks.summary(),
             "e2e": {"value": e2e_value, "unit": "replica-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
