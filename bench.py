@@ -34,7 +34,7 @@ FLOP_PER_REPLICA_STEP = 240824  # SURVEY.md 8d, ALA10 plain NVE (force-only eval
 FLOP_PER_REPLICA_EVAL = 236144
 NOMINAL_FP32_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.5
 TIMEFACTOR = 48.88821
-NCU_DRAM_BYTES_PER_LAUNCH = 31.1e6  # profiles/r01_v15_integrate_kernel.md: 31.08 MB read + 0.04 MB written
+NCU_DRAM_BYTES_PER_LAUNCH = 31.1e6  # profiles/r01_v20_integrate_kernel.md: 31.08 MB read + 0.04 MB written
 BOLTZMAN = 0.001987191
 
 
