@@ -39,7 +39,7 @@ __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, co
   for (int k = tid; k < kMaxChunks * kMaxAtoms / 4; k += kThreads)
     ((uint32_t*)S.mask8)[k] = __ldg((const uint32_t*)T.mask8 + k);
   for (int k = tid; k <= kMaxAtoms; k += kThreads) S.gstart[k] = __ldg(T.gather_start + k);
-  for (int k = tid; k < kWarps * kMaxTasks; k += kThreads) S.tasks[k] = __ldg(T.tasks + k);
+  for (int k = tid; k < kWarps * kMaxTasks; k += kThreads) S.tasks[k] = __ldg((FIXED ? T.tasks : T.tasks_e) + k);
   if (tid < 8) { S.smd[tid] = 0.0f; S.box[tid] = 0.0f; }
   // slots of disabled / dropped terms are never written: keep them at zero for the gather
   if (FIXED) {
@@ -672,52 +672,61 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   T.p14_on = 1;
   T.dih2_stride = (int)dstride;
 
-  // ---- static task schedule: longest-processing-time-first over the 4 warps ----------------------
+  // ---- static task schedules: longest-processing-time-first over the 4 warps ---------------------
+  // Two schedules from two cost models (issue slots per warp, tuned on the GPU with tools/tune_costs.py):
+  // [0] force-only evaluation (the fused integrator), [1] evaluation with energies (single-shot Forces.compute:
+  // energy arithmetic, FP64 bond energies, acosf).  B200MD_COSTS / B200MD_COSTS_E =
+  // "pass,chunk,diaggroup,diag,bond,angle,dih,gen,p14" override them for tuning runs.
   struct Task { uint32_t word; int cost; };
-  std::vector<Task> all;
-  // cost model of the schedule (issue slots per warp); B200MD_COSTS="pass,chunk,diagstep,diag,bond,angle,dih,imp,p14"
-  // overrides it for tuning runs
-  int cm[9] = {105, 120, 52, 30, 77, 230, 380, 400, 100};
-  if (const char* env = getenv("B200MD_COSTS")) sscanf(env, "%d,%d,%d,%d,%d,%d,%d,%d,%d", cm, cm + 1, cm + 2, cm + 3, cm + 4, cm + 5, cm + 6, cm + 7, cm + 8);
+  int cms[2][9] = {{105, 120, 52, 30, 77, 230, 380, 400, 100}, {119, 84, 68, 26, 120, 280, 430, 440, 120}};
+  const char* envs[2] = {getenv("B200MD_COSTS"), getenv("B200MD_COSTS_E")};
   const int nblocks = (N + 31) / 32;
-  if (d->npairs > 0) {
-    for (int c = 4; c < T.nchunks; ++c) {  // off-diagonal: chunk of block J against the full blocks 0..J-1
-      const int passes = c / 4;
-      all.push_back({make_task(TASK_TILE, c, passes), passes * cm[0] + cm[1]});
-    }
-    for (int b = 0; b < nblocks; ++b) {  // diagonal blocks, full shell: tasks of up to 4 groups of 4 j atoms
-      const int n = std::min(32, N - 32 * b), groups = (n + 3) / 4;
-      for (int g0 = 0; g0 < groups; g0 += 4) {
-        const int ng = std::min(4, groups - g0);
-        all.push_back({make_task(TASK_DIAG, (uint32_t)b | ((uint32_t)g0 << 8), ng), ng * cm[2] + cm[3]});
+  std::vector<uint32_t> tasks_v[2];
+  for (int sch = 0; sch < 2; ++sch) {
+    int* cm = cms[sch];
+    if (envs[sch]) sscanf(envs[sch], "%d,%d,%d,%d,%d,%d,%d,%d,%d", cm, cm + 1, cm + 2, cm + 3, cm + 4, cm + 5, cm + 6, cm + 7, cm + 8);
+    std::vector<Task> all;
+    if (d->npairs > 0) {
+      for (int c = 4; c < T.nchunks; ++c) {  // off-diagonal: chunk of block J against the full blocks 0..J-1
+        const int passes = c / 4;
+        all.push_back({make_task(TASK_TILE, c, passes), passes * cm[0] + cm[1]});
+      }
+      for (int b = 0; b < nblocks; ++b) {  // diagonal blocks, full shell: tasks of up to 4 groups of 4 j atoms
+        const int n = std::min(32, N - 32 * b), groups = (n + 3) / 4;
+        for (int g0 = 0; g0 < groups; g0 += 4) {
+          const int ng = std::min(4, groups - g0);
+          all.push_back({make_task(TASK_DIAG, (uint32_t)b | ((uint32_t)g0 << 8), ng), ng * cm[2] + cm[3]});
+        }
       }
     }
-  }
-  // bonded chunks: 32 lanes x 2 items (packed kinds) or 32 items (general torsions)
-  for (int c = 0; c < PB.nchunks; ++c) all.push_back({make_task(TASK_BOND, c, 0), cm[4]});
-  for (int c = 0; c < PA.nchunks; ++c) all.push_back({make_task(TASK_ANGLE, c, 0), cm[5]});
-  for (int c = 0; c < PD.nchunks; ++c) all.push_back({make_task(TASK_DIHEDRAL, c, dih_chunk_nmax[c]), cm[6] + 12 * dih_chunk_nmax[c]});
-  for (int c = 0; c < (NG + 31) / 32; ++c) all.push_back({make_task(TASK_IMPROPER, c, 0), cm[7]});
-  for (int c = 0; c < PP.nchunks; ++c) all.push_back({make_task(TASK_P14, c, 0), cm[8]});
-  std::stable_sort(all.begin(), all.end(), [](const Task& a, const Task& b) { return a.cost > b.cost; });
-  std::vector<uint32_t> tasks((size_t)kWarps * kMaxTasks, 0);
-  int load[kWarps] = {0, 0, 0, 0};
-  std::vector<std::vector<uint32_t>> mine(kWarps);
-  for (const Task& t : all) {
-    int w = 0;
-    for (int k = 1; k < kWarps; ++k) if (load[k] < load[w]) w = k;
-    if ((int)mine[w].size() >= kMaxTasks - 1) { delete topo; fail(B200MD_ERR_UNSUPPORTED, "too many tasks per warp"); return nullptr; }
-    mine[w].push_back(t.word);
-    load[w] += t.cost;
-  }
-  // each warp runs its tasks kind by kind (run_tasks): tiles, diagonal blocks, dihedrals, impropers, angles, bonds, 1-4
-  const uint32_t kind_order[kNumKinds] = {TASK_TILE, TASK_DIAG, TASK_DIHEDRAL, TASK_IMPROPER, TASK_ANGLE, TASK_BOND, TASK_P14};
-  for (int w = 0; w < kWarps; ++w) {
-    int n = 0;
-    T.kend8[w] = make_uint2(0u, 0u);
-    for (int k = 0; k < kNumKinds; ++k) {
-      for (uint32_t word : mine[w]) if ((word & 0xff) == kind_order[k]) tasks[(size_t)w * kMaxTasks + n++] = word;
-      (k < 4 ? T.kend8[w].x : T.kend8[w].y) |= (uint32_t)n << (8 * (k & 3));
+    // bonded chunks: 32 lanes x 2 items (packed kinds) or 32 items (general torsions)
+    for (int c = 0; c < PB.nchunks; ++c) all.push_back({make_task(TASK_BOND, c, 0), cm[4]});
+    for (int c = 0; c < PA.nchunks; ++c) all.push_back({make_task(TASK_ANGLE, c, 0), cm[5]});
+    for (int c = 0; c < PD.nchunks; ++c) all.push_back({make_task(TASK_DIHEDRAL, c, dih_chunk_nmax[c]), cm[6] + 12 * dih_chunk_nmax[c]});
+    for (int c = 0; c < (NG + 31) / 32; ++c) all.push_back({make_task(TASK_IMPROPER, c, 0), cm[7]});
+    for (int c = 0; c < PP.nchunks; ++c) all.push_back({make_task(TASK_P14, c, 0), cm[8]});
+    std::stable_sort(all.begin(), all.end(), [](const Task& a, const Task& b) { return a.cost > b.cost; });
+    std::vector<uint32_t>& tasks = tasks_v[sch];
+    tasks.assign((size_t)kWarps * kMaxTasks, 0);
+    int load[kWarps] = {0, 0, 0, 0};
+    std::vector<std::vector<uint32_t>> mine(kWarps);
+    for (const Task& t : all) {
+      int w = 0;
+      for (int k = 1; k < kWarps; ++k) if (load[k] < load[w]) w = k;
+      if ((int)mine[w].size() >= kMaxTasks - 1) { delete topo; fail(B200MD_ERR_UNSUPPORTED, "too many tasks per warp"); return nullptr; }
+      mine[w].push_back(t.word);
+      load[w] += t.cost;
+    }
+    // each warp runs its tasks kind by kind (run_tasks): tiles, diagonal blocks, dihedrals, general torsions, angles, bonds, 1-4
+    const uint32_t kind_order[kNumKinds] = {TASK_TILE, TASK_DIAG, TASK_DIHEDRAL, TASK_IMPROPER, TASK_ANGLE, TASK_BOND, TASK_P14};
+    for (int w = 0; w < kWarps; ++w) {
+      int n = 0;
+      uint2& k8 = sch ? T.kend8_e[w] : T.kend8[w];
+      k8 = make_uint2(0u, 0u);
+      for (int k = 0; k < kNumKinds; ++k) {
+        for (uint32_t word : mine[w]) if ((word & 0xff) == kind_order[k]) tasks[(size_t)w * kMaxTasks + n++] = word;
+        (k < 4 ? k8.x : k8.y) |= (uint32_t)n << (8 * (k & 3));
+      }
     }
   }
 
@@ -729,7 +738,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   const size_t o_di = B.add(dih2_idx), o_dc = B.add(dih2_coef), o_dk = B.add(dih2_k0), o_ds = B.add(dih2_slot), o_d14 = B.add(dih2_p14ab), o_dq = B.add(dih2_p14q);
   const size_t o_gi = B.add(gen_idx), o_gt = B.add(gen_terms), o_gp = B.add(gen_tp), o_gsl = B.add(gen_slot);
   const size_t o_pi = B.add(p142_idx), o_pp = B.add(p142_ab), o_pq = B.add(p142_q), o_ps = B.add(p142_slot);
-  const size_t o_gs = B.add(gstart), o_tk = B.add(tasks);
+  const size_t o_gs = B.add(gstart), o_tk = B.add(tasks_v[0]), o_tke = B.add(tasks_v[1]);
   auto cleanup = [&](const std::string& msg) { fail(B200MD_ERR_CUDA, msg); if (topo->blob) cudaFree(topo->blob); delete topo; };
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) { cleanup(std::string("cudaSetDevice: ") + cudaGetErrorString(e)); return nullptr; }
@@ -750,6 +759,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   T.p142_slot = (const uint4*)(base + o_ps);
   T.gather_start = (const uint16_t*)(base + o_gs);
   T.tasks = (const uint32_t*)(base + o_tk);
+  T.tasks_e = (const uint32_t*)(base + o_tke);
   T.smem_bytes = (int)smem_layout(nullptr, nullptr, NT, T.nslots, false);
   T.smem_bytes_fixed = (int)smem_layout(nullptr, nullptr, NT, T.nslots, true);
   if (T.smem_bytes > 227 * 1024) { cleanup("topology needs more than 227 KB of shared memory per CTA"); g_last_error = "too much shared memory"; return nullptr; }

@@ -630,7 +630,7 @@ template <int MODE, bool ENERGY, bool FIXED, bool PBC>
 __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const ForceParams& P, int warp, int lane,
                                           Energies& E) {
   const uint32_t* tk = S.tasks + warp * kMaxTasks;
-  const uint2 kends = T.kend8[warp];  // the 7 run ends as bytes: one constant load instead of one per kind
+  const uint2 kends = FIXED ? T.kend8[warp] : T.kend8_e[warp];  // the 7 run ends as bytes: one constant load instead of one per kind
   int t = 0;
   uint32_t next = tk[0];
 #define B200MD_TASK_LOOP(K, BODY)                                                     \

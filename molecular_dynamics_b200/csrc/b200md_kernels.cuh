@@ -64,7 +64,9 @@ struct DevTopo {
   const uint32_t* gen_idx;   const uint2* gen_terms;  const float4* gen_term_prm;  const uint2* gen_slot;
   int nslots;
   const uint16_t* gather_start;  // [129]: slots of atom a are [gather_start[a], gather_start[a+1])
-  const uint32_t* tasks;  // [kWarps][kMaxTasks]
+  const uint32_t* tasks;    // [kWarps][kMaxTasks] schedule of the fused integrator (force-only cost model)
+  const uint32_t* tasks_e;  // [kWarps][kMaxTasks] schedule of the single-shot kernel (cost model with energies)
+  uint2 kend8_e[kWarps];  // the same for tasks_e
   uint2 kend8[kWarps];    // per warp: end index of the k-th run of its kind-sorted task list, one byte per kind
   int smem_bytes, smem_bytes_fixed;
 };
@@ -235,11 +237,13 @@ __device__ __forceinline__ void normal3(unsigned long long seed, unsigned long l
   const float s = 1.0f / 16777216.0f;
   float u0 = ((float)(u[0] >> 8) + 0.5f) * s, u1 = ((float)(u[1] >> 8) + 0.5f) * s;
   float u2 = ((float)(u[2] >> 8) + 0.5f) * s, u3 = ((float)(u[3] >> 8) + 0.5f) * s;
-  float r0 = sqrtf(-2.0f * logf(u0)), r1 = sqrtf(-2.0f * logf(u2));
-  float s1, c1, c3, s3;
-  sincospif(2.0f * u1, &s1, &c1);
-  sincospif(2.0f * u3, &s3, &c3);
-  n[0] = r0 * c1; n[1] = r0 * s1; n[2] = r1 * c3;
+  // Box-Muller on the SFU: r = sqrt(-2 ln u) through MUFU.LG2 / MUFU.SQRT, cos / sin(2 pi u) through MUFU.COS / MUFU.SIN
+  // on the argument reduced to [-pi, pi) (cos(x - pi) = -cos x).  Absolute errors ~1e-6 on a unit-variance kick that is
+  // scaled by vcoeff ~ 1e-2: far below the fp32 rounding of the velocities it is added to.
+  const float two_pi = 6.283185307179586f;
+  float r0 = fast_sqrt(-2.0f * __logf(u0)), r1 = fast_sqrt(-2.0f * __logf(u2));
+  const float a1 = two_pi * (u1 - 0.5f), a3 = two_pi * (u3 - 0.5f);
+  n[0] = -r0 * __cosf(a1); n[1] = -r0 * __sinf(a1); n[2] = -r1 * __cosf(a3);
 }
 
 }  // namespace b200md

@@ -11,8 +11,18 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 NAMES = ["pass", "chunk", "diaggroup", "diag", "bond", "angle", "dih", "gen", "p14"]
 
 
+ENERGY = "--energy" in sys.argv  # tune the single-shot Forces.compute schedule (B200MD_COSTS_E) instead
+
+
 def run(costs):
-    env = dict(os.environ, B200MD_COSTS=",".join(str(int(c)) for c in costs))
+    key = "B200MD_COSTS_E" if ENERGY else "B200MD_COSTS"
+    env = dict(os.environ, **{key: ",".join(str(int(c)) for c in costs)})
+    if ENERGY:
+        out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "profile_forces.py")], env=env, capture_output=True, text=True).stdout
+        try:
+            return float(out.strip().splitlines()[-1].split()[0])
+        except Exception:
+            return 0.0
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--no-cpu", "--no-extra", "--steps", "3", "--warmup", "3", "--inner", "500"],
                          env=env, capture_output=True, text=True).stdout
     try:
@@ -22,7 +32,9 @@ def run(costs):
 
 
 def main():
-    costs = [int(x) for x in (sys.argv[1].split(",") if len(sys.argv) > 1 else "150,120,52,30,110,230,380,400,100".split(","))]
+    args = [x for x in sys.argv[1:] if not x.startswith("--")]
+    default = "140,120,68,30,120,280,430,440,120" if ENERGY else "105,120,52,30,77,230,380,400,100"
+    costs = [int(x) for x in (args[0] if args else default).split(",")]
     best = run(costs)
     print("start", costs, f"{best:.4e}", flush=True)
     for rnd in range(2):
