@@ -9,7 +9,11 @@ C-ABI of include/b200md.h); importing this package never imports the CPU oracle.
 from .forces import Forces, SMDBias
 from .integrator import BOLTZMAN, TIMEFACTOR, Integrator, kinetic_energy, kinetic_to_temp, maxwell_boltzmann
 from .parameters import Parameters, parameters_from_prmtop, parameters_from_psf_yaml
+from .minimizers import minimize_bfgs, minimize_fire
 from .systems import System
+from .utils import LogWriter, TrajectoryWriter, load_checkpoint, save_checkpoint
+from .wrapper import Wrapper
 
 __all__ = ["Forces", "SMDBias", "System", "Integrator", "maxwell_boltzmann", "kinetic_energy", "kinetic_to_temp",
-           "Parameters", "parameters_from_prmtop", "parameters_from_psf_yaml", "TIMEFACTOR", "BOLTZMAN"]
+           "Parameters", "parameters_from_prmtop", "parameters_from_psf_yaml", "TIMEFACTOR", "BOLTZMAN", "minimize_bfgs",
+           "minimize_fire", "LogWriter", "TrajectoryWriter", "save_checkpoint", "load_checkpoint", "Wrapper"]

@@ -63,6 +63,16 @@ class _ReplicaEnergies:
     def __repr__(self):
         return f"_ReplicaEnergies({self.tensor!r})"
 
+    # the tutorial loop logs ``Epot + Ekin`` with Ekin a numpy array (tutorial.ipynb cell 18)
+    def __array__(self, dtype=None, copy=None):
+        a = self.tensor.detach().cpu().numpy()
+        return a.astype(dtype) if dtype is not None else a
+
+    def __add__(self, other):
+        return np.asarray(self) + np.asarray(other)
+
+    __radd__ = __add__
+
 
 class Integrator:
     def __init__(self, systems, forces, timestep, device=None, gamma=None, T=None, seed=0):

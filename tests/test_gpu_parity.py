@@ -449,3 +449,72 @@ def test_integrator_with_box_short_horizon_vs_oracle():
     assert np.abs(s.pos.cpu().numpy() - out["pos"]).max() < 3e-4
     obs = integ.observables.cpu().numpy()
     np.testing.assert_allclose(obs[:, :, :8].sum(-1), out["observables"][:, :, :8].sum(-1), rtol=2e-5, atol=2e-3)
+
+
+def test_checkpoint_resume_is_bitwise(tmp_path):
+    """a Langevin + SMD run resumed from a checkpoint continues bit-identically (counter-based RNG keyed by
+    the global step, deterministic reductions)."""
+    from molecular_dynamics_b200 import load_checkpoint, save_checkpoint
+
+    g = load_golden("ala10")
+    pos0 = g["pos"][:4]
+    vel0 = (0.1 * np.random.default_rng(3).standard_normal(pos0.shape)).astype(np.float32)
+
+    def fresh():
+        par, s = make_system(g, pos0, vel0)
+        F = Forces(par, external=SMDBias([3], [98], fk=1.0, cent_0=14.0, rate_per_step=1e-3))
+        F.compute_batch(s.pos, s.box, s.forces)
+        return s, Integrator(s, F, timestep=1.0, device=DEV, gamma=1.0, T=300.0, seed=7)
+
+    s1, i1 = fresh()
+    i1.step(niter=60)
+    s2, i2 = fresh()
+    i2.step(niter=25)
+    save_checkpoint(str(tmp_path / "ck.pt"), s2, i2)
+    s3, i3 = fresh()
+    load_checkpoint(str(tmp_path / "ck.pt"), s3, i3)
+    assert i3.step_count == 25
+    i3.step(niter=35)
+    assert torch.equal(s1.pos, s3.pos) and torch.equal(s1.vel, s3.vel) and torch.equal(s1.forces, s3.forces)
+
+
+def test_minimizers_relax_perturbed_conformers():
+    """upstream's minimize_bfgs call on one replica, and the batched FIRE minimiser on 32."""
+    import bench
+    from molecular_dynamics_b200 import minimize_bfgs, minimize_fire
+
+    g = load_golden("ala10")
+    pos, vel = bench.synth_inputs(bench.load_ala10(), 32)
+    par, s = make_system(g, pos, vel)
+    F = Forces(par)
+    e0 = F.compute_batch(s.pos, s.box, s.forces).sum(1).cpu().numpy()
+    out = minimize_fire(s, F, steps=400, fmax=5.0)
+    e1 = out["epot"].cpu().numpy()
+    assert (e1 < e0 - 50.0).all(), (e0, e1)            # the 0.05 A perturbation alone stores ~100 kcal/mol in the bonds
+    assert float(out["fmax"].max()) < 60.0             # from several hundred kcal/mol/A
+    assert not torch.isnan(s.pos).any()
+    par1, s1 = make_system(g, pos[:1], vel[:1])
+    F1 = Forces(par1)
+    e0 = float(F1.compute_batch(s1.pos, s1.box, s1.forces).sum())
+    minimize_bfgs(s1, F1, fmax=0.5, steps=200)
+    e1 = float(F1.compute_batch(s1.pos, s1.box, s1.forces).sum())
+    assert e1 < e0 - 100.0 and float(s1.forces.abs().max()) < 20.0
+    with pytest.raises(RuntimeError):
+        minimize_bfgs(s, F)
+
+
+def test_tutorial_loop_shapes():
+    """The tutorial's production loop (tutorial.ipynb cell 18) runs unchanged: Epot + Ekin, Wrapper, LogWriter."""
+    from molecular_dynamics_b200 import Wrapper
+
+    g = load_golden("bb40")
+    par, s = make_system(g, g["frames"][:1], np.zeros_like(g["frames"][:1]))
+    F = Forces(par, cutoff=9.0, rfa=True, switch_dist=7.5)
+    F.compute(s.pos, s.box, s.forces)
+    integ = Integrator(s, F, timestep=1.0, device=DEV, gamma=0.1, T=300.0)
+    wrapper = Wrapper(par.natoms if hasattr(par, "natoms") else len(par.masses), par.bonds, DEV)
+    Ekin, Epot, T = integ.step(niter=10)
+    wrapper.wrap(s.pos, s.box)
+    etot = Epot + Ekin
+    assert isinstance(etot, np.ndarray) and etot.shape == (1,) and np.isfinite(etot).all()
+    assert len(Epot) == 1 and float(Epot[0]) == float(np.asarray(Epot)[0])

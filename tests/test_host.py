@@ -101,3 +101,51 @@ def test_packed_topology_counts():
     for name, w in want.items():
         d = load_golden(name).packed.desc
         assert (d.natoms, d.ntypes, d.nbonds, d.nangles, d.ndihedrals, d.ndihedral_terms, d.n14, d.npairs) == w
+
+
+def test_logwriter_and_trajectory_writer(tmp_path):
+    import csv
+
+    import torch
+
+    from molecular_dynamics_b200 import LogWriter, TrajectoryWriter
+
+    log = LogWriter(path=str(tmp_path / "logs"), keys=("iter", "ns", "epot", "ekin", "etot", "T"), name="monitor.csv")
+    log.write_row({"iter": 10, "ns": 1e-5, "epot": [torch.tensor(-3.5)], "ekin": np.array([2.0]), "etot": np.array([-1.5]), "T": np.array([300.0])})
+    log.write_row({"iter": 20, "ns": 2e-5, "epot": torch.tensor([1.0, 2.0]), "ekin": np.array([2.0, 3.0]), "etot": np.array([3.0, 5.0]), "T": 1})
+    rows = list(csv.reader(open(tmp_path / "logs" / "monitor.csv")))
+    assert rows[0] == ["iter", "ns", "epot", "ekin", "etot", "T"]
+    assert rows[1][0] == "10" and float(rows[1][2]) == -3.5 and float(rows[1][5]) == 300.0
+    assert rows[2][2] == "1.0;2.0"
+    tw = TrajectoryWriter(str(tmp_path / "traj.npy"))
+    for k in range(3):
+        tw.append(torch.full((1, 5, 3), float(k)))
+    assert tw.save() == [str(tmp_path / "traj.npy")]
+    assert np.load(tmp_path / "traj.npy").shape == (3, 5, 3)  # (frames, natoms, 3): the reference's trajectory layout
+    tw = TrajectoryWriter(str(tmp_path / "t2.npy"), layout="tutorial")
+    tw.append(np.zeros((2, 5, 3)))
+    tw.append(np.ones((2, 5, 3)))
+    tw.save()
+    assert np.load(tmp_path / "t2.npy").shape == (2, 5, 3, 2)
+
+
+def test_wrapper_moves_whole_groups_into_the_box():
+    import torch
+
+    from molecular_dynamics_b200 import Wrapper
+
+    bonds = np.array([[0, 1], [1, 2], [4, 5]])
+    w = Wrapper(7, bonds)
+    assert sorted(len(g) for g in w.groups) == [2, 3] and sorted(w.nongrouped.tolist()) == [3, 6]
+    pos = torch.tensor([[[10.5, 0.1, 0.1], [11.0, 0.2, 0.1], [11.5, 0.3, 0.1], [-0.5, 25.0, 3.0],
+                         [0.2, 0.2, -7.9], [0.4, 0.2, -8.1], [3.0, 3.0, 3.0]]])
+    ref = pos.clone()
+    box = torch.zeros(1, 3, 3)
+    w.wrap(pos, box)
+    assert torch.equal(pos, ref)  # vacuum: no-op
+    box[0, 0, 0], box[0, 1, 1], box[0, 2, 2] = 10.0, 10.0, 10.0
+    w.wrap(pos, box)
+    np.testing.assert_allclose(pos[0, :3, 0], [0.5, 1.0, 1.5], atol=1e-6)  # group moved as a whole (centroid 11 -> 1)
+    np.testing.assert_allclose(pos[0, 3], [9.5, 5.0, 3.0], atol=1e-6)
+    np.testing.assert_allclose(pos[0, 4:6, 2], [2.1, 1.9], atol=1e-5)
+    np.testing.assert_allclose(pos[0, 1] - pos[0, 0], ref[0, 1] - ref[0, 0], atol=1e-6)  # intra-group geometry kept
