@@ -146,10 +146,13 @@ typedef struct b200md_integrate_opts {
   int32_t snapshot_every; /* write positions every this many steps (0: never)                   */
 } b200md_integrate_opts;
 
-/* observables recorded per replica at each report: 8 energy slots + Ekin + end-to-end distance */
-#define B200MD_NUM_OBSERVABLES 10
+/* observables recorded per replica at each report: 8 energy slots + Ekin + end-to-end distance + the work done by
+ * the moving SMD restraint since the first step of the call, W = sum_steps fk (c - d) dc (the W_harmonic column of
+ * the data generator's colvars.traj, All_ML_Training_Data/210905_SMD_decaalanine/SMD/output/N/smd_out.colvars.traj) */
+#define B200MD_NUM_OBSERVABLES 11
 #define B200MD_OBS_EKIN 8
 #define B200MD_OBS_E2E_DIST 9
+#define B200MD_OBS_SMD_WORK 10
 
 typedef struct b200md_topology b200md_topology; /* opaque */
 

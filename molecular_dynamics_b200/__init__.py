@@ -11,9 +11,11 @@ from .integrator import BOLTZMAN, TIMEFACTOR, Integrator, kinetic_energy, kineti
 from .parameters import Parameters, parameters_from_prmtop, parameters_from_psf_yaml
 from .minimizers import minimize_bfgs, minimize_fire
 from .systems import System
-from .utils import LogWriter, TrajectoryWriter, load_checkpoint, save_checkpoint
+from .sharding import gather_observables, jarzynski_free_energy, shard_range
+from .utils import LogWriter, TrajectoryWriter, load_checkpoint, read_colvars_traj, save_checkpoint, write_colvars_traj
 from .wrapper import Wrapper
 
 __all__ = ["Forces", "SMDBias", "System", "Integrator", "maxwell_boltzmann", "kinetic_energy", "kinetic_to_temp",
            "Parameters", "parameters_from_prmtop", "parameters_from_psf_yaml", "TIMEFACTOR", "BOLTZMAN", "minimize_bfgs",
-           "minimize_fire", "LogWriter", "TrajectoryWriter", "save_checkpoint", "load_checkpoint", "Wrapper"]
+           "minimize_fire", "LogWriter", "TrajectoryWriter", "save_checkpoint", "load_checkpoint", "Wrapper",
+           "write_colvars_traj", "read_colvars_traj", "jarzynski_free_energy", "gather_observables", "shard_range"]

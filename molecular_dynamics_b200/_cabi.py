@@ -13,9 +13,10 @@ import numpy as np
 import torch
 
 NUM_ENERGIES = 8
-NUM_OBSERVABLES = 10
+NUM_OBSERVABLES = 11
 OBS_EKIN = 8
 OBS_E2E_DIST = 9
+OBS_SMD_WORK = 10
 MAX_ATOMS = 128
 
 # dict order of the reference's result (forces.py:40-50, :100)

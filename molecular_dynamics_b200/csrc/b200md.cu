@@ -165,6 +165,7 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       S.box[4 + tid] = b != 0.0f ? 1.0f / b : 0.0f;
     }
     if (status != nullptr && tid == 0) status[r] = 0;
+    if (tid == kThreads - 1) S.smd_energy[1] = 0.0;  // same thread as smd_task: no barrier needed
     for (int s = 0; s < I.nsteps; ++s) {
       const unsigned long long gstep = I.step0 + (unsigned long long)s;
       // _first_VV: pos += vel dt + 0.5 a dt^2 ; vel += 0.5 dt a
@@ -203,12 +204,13 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       if (report) {
         if (live) E.e[B200MD_OBS_EKIN] = 0.5 * (double)mass * ((double)vx * vx + (double)vy * vy + (double)vz * vz);
         if (P.smd_on && tid == 0) { E.e[B200MD_E_EXTERNAL] += S.smd_energy[0]; E.e[B200MD_OBS_E2E_DIST] = (double)S.smd[4]; }
-        reduce_energies<B200MD_NUM_OBSERVABLES>(S, E, warp, lane);
+        reduce_energies<kNumReduced>(S, E, warp, lane);
         if (tid == 0 && observables != nullptr) {
           const long long slot = I.energy_every > 0 ? (s + 1) / I.energy_every - 1 : 0;
           double* o = observables + (slot * R + r) * B200MD_NUM_OBSERVABLES;
 #pragma unroll
-          for (int k = 0; k < B200MD_NUM_OBSERVABLES; ++k) o[k] = E.e[k];
+          for (int k = 0; k < kNumReduced; ++k) o[k] = E.e[k];
+          o[B200MD_OBS_SMD_WORK] = P.smd_on ? S.smd_energy[1] : 0.0;
         }
       }
       if (I.snapshot_every > 0 && snapshots != nullptr && (s + 1) % I.snapshot_every == 0 && live) {

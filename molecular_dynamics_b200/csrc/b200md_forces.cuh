@@ -7,10 +7,10 @@ namespace b200md {
 
 // Per-thread energy accumulators (FP64; FP32 partial sums are folded in once per pass / item).
 struct Energies {
-  double e[B200MD_NUM_OBSERVABLES];  // 8 energy slots + Ekin + end-to-end distance
+  double e[kNumReduced];  // 8 energy slots + Ekin + end-to-end distance
   __device__ __forceinline__ void clear() {
 #pragma unroll
-    for (int k = 0; k < B200MD_NUM_OBSERVABLES; ++k) e[k] = 0.0;
+    for (int k = 0; k < kNumReduced; ++k) e[k] = 0.0;
   }
 };
 
@@ -666,6 +666,7 @@ __device__ __forceinline__ void smd_task(const Smem& S, const ForceParams& P, fl
   S.smd[0] = (float)(c * dx); S.smd[1] = (float)(c * dy); S.smd[2] = (float)(c * dz);
   S.smd[4] = (float)dist;
   S.smd_energy[0] = 0.5 * (double)P.smd_fk * dev * dev;
+  S.smd_energy[1] += (double)P.smd_fk * dev * (double)P.smd_rate;  // work of the moving restraint, dW = dE/dc dc
 }
 
 // ---- per-atom gather in a fixed order: j-side slot, 4 i-side partials, bonded slots, SMD ------------
@@ -707,14 +708,14 @@ __device__ __forceinline__ void reduce_energies(const Smem& S, Energies& E, int 
     double v = E.e[k];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0) S.ered[warp * B200MD_NUM_OBSERVABLES + k] = v;
+    if (lane == 0) S.ered[warp * kNumReduced + k] = v;
   }
   __syncthreads();
   if (warp == 0 && lane == 0) {
 #pragma unroll
     for (int k = 0; k < NOBS; ++k)
-      E.e[k] = (S.ered[k] + S.ered[B200MD_NUM_OBSERVABLES + k]) +
-               (S.ered[2 * B200MD_NUM_OBSERVABLES + k] + S.ered[3 * B200MD_NUM_OBSERVABLES + k]);
+      E.e[k] = (S.ered[k] + S.ered[kNumReduced + k]) +
+               (S.ered[2 * kNumReduced + k] + S.ered[3 * kNumReduced + k]);
   }
 }
 

@@ -106,9 +106,9 @@ struct Smem {
   float4* vel;        // [128] velocities parked during the task phase of the integrator
   uint16_t* gstart;   // [130]
   uint32_t* tasks;    // [kWarps*kMaxTasks]
-  double* ered;       // [kWarps][10]
+  double* ered;       // [kWarps][kNumReduced]
   float* smd;         // [8]: force on atom2 (xyz), -, distance
-  double* smd_energy; // [1]
+  double* smd_energy; // [2]: restraint energy of this step, work accumulated since the first step of the launch
   float* box;         // [8]: -box diagonal (x, y, z), 0, 1 / box diagonal (0 where the entry is 0), 0
 };
 
@@ -125,8 +125,10 @@ constexpr size_t kOffFi = kOffDiagMask + sizeof(uint32_t) * kMaxAtoms;
 constexpr size_t kOffFj = kOffFi + sizeof(float) * kWarps * 3 * kMaxAtoms;
 constexpr size_t kOffGstart = kOffFj + sizeof(float) * 3 * kMaxAtoms;
 constexpr size_t kOffTasks = kOffGstart + 272;
+// observables that are block-reduced (8 energy slots, Ekin, end-to-end distance); the SMD work lives in S.smd_energy[1]
+constexpr int kNumReduced = 10;
 constexpr size_t kOffEred = kOffTasks + sizeof(uint32_t) * kWarps * kMaxTasks;
-constexpr size_t kOffSmd = kOffEred + sizeof(double) * kWarps * 10;
+constexpr size_t kOffSmd = kOffEred + sizeof(double) * kWarps * kNumReduced;
 constexpr size_t kOffSmdEnergy = kOffSmd + 32;
 constexpr size_t kOffBox = kOffSmdEnergy + 16;
 constexpr size_t kOffFbi = kOffBox + 32;

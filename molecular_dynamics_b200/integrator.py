@@ -91,7 +91,9 @@ class Integrator:
         self.replica0 = 0
         self.energy_every = 0  # 0: record observables after the last step of each step() call only
         self.snapshot_every = 0
-        self.observables = None  # (nreports, R, 10) float64 after step(): 8 energy slots, Ekin, |r_a2 - r_a1|
+        # (nreports, R, 11) float64 after step(): 8 energy slots, Ekin, |r_a2 - r_a1|, SMD work since step 0
+        self.observables = None
+        self.smd_work = None  # (R,) float64: work done by the moving SMD restraint over all step() calls so far
         self.snapshots = None  # (nsnap, R, natoms, 3) float32 when snapshot_every > 0
         self.check_nan = True
 
@@ -139,6 +141,15 @@ class Integrator:
                 raise RuntimeError("the bonded force on an atom exceeded 4096 kcal/mol/A: the fused integrator accumulates "
                                    "bonded forces in 2^-17 fixed point and the system has blown up (reduce the timestep "
                                    "or relax the start structure)")
+        if smd[0]:  # the kernel counts work from the first step of the launch: carry it across calls
+            if self.smd_work is not None and self.smd_work.shape[0] == R:
+                obs[:, :, _cabi.OBS_SMD_WORK] += self.smd_work.to(dev)
+            self.smd_work = obs[-1, :, _cabi.OBS_SMD_WORK].clone()
+            if energy_every > 0 and niter % energy_every:
+                import warnings
+                warnings.warn("niter is not a multiple of energy_every: the SMD work of the trailing steps was not "
+                              "recorded, Integrator.smd_work is undefined from here on")
+                self.smd_work.fill_(float("nan"))
         self.observables, self.snapshots = obs, snaps
         last = obs[-1]
         Ekin = last[:, _cabi.OBS_EKIN].cpu().numpy()

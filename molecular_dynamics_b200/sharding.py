@@ -26,3 +26,29 @@ def gather_observables(local: torch.Tensor, total: int, group=None) -> torch.Ten
     out = torch.empty((world * nmax,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
     dist.all_gather_into_tensor(out, pad, group=group)
     return torch.cat([out[r * nmax: r * nmax + (hi - lo)] for r, (lo, hi) in enumerate(sizes)], dim=0)
+
+
+def jarzynski_free_energy(work: torch.Tensor, temperature: float, group=None):
+    """Free-energy profile along the pulling coordinate from the SMD work of the whole replica ensemble
+    (the reference's SMD data set is the input of exactly this estimate):
+    ``dF = -kT ln < exp(-W / kT) >`` over ALL replicas of all ranks, plus the second-cumulant estimate
+    ``<W> - var(W) / (2 kT)``.  ``work``: this rank's (..., R_local) block, e.g.
+    ``Integrator.observables[:, :, OBS_SMD_WORK]`` -> one value per report.  The exchange is three all-reduces of
+    (...)-sized tensors (max, then the shifted exponential sum with the count and the first two moments)."""
+    from .integrator import BOLTZMAN
+
+    kT = BOLTZMAN * float(temperature)
+    w = work.to(torch.float64)
+    x = -w / kT
+    multi = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+    m = x.amax(dim=-1) if x.shape[-1] else torch.full(x.shape[:-1], -float("inf"), dtype=x.dtype, device=x.device)
+    if multi:
+        dist.all_reduce(m, op=dist.ReduceOp.MAX, group=group)
+    n = torch.full_like(m, float(x.shape[-1]))
+    acc = torch.stack([torch.exp(x - m.unsqueeze(-1)).sum(-1), n, w.sum(-1), (w * w).sum(-1)])
+    if multi:
+        dist.all_reduce(acc, op=dist.ReduceOp.SUM, group=group)
+    se, n, s1, s2 = acc
+    mean = s1 / n
+    var = (s2 / n - mean * mean).clamp_min(0.0) * n / (n - 1).clamp_min(1.0)
+    return {"dF": -kT * (m + torch.log(se / n)), "dF_cumulant2": mean - var / (2.0 * kT), "mean_work": mean, "n": n}

@@ -89,7 +89,8 @@ def save_checkpoint(path, system, integrator=None, extra=None):
              "forces": system.forces.detach().cpu(), "extra": extra}
     if integrator is not None:
         state["integrator"] = {"seed": integrator.seed, "step_count": integrator.step_count, "replica0": integrator.replica0,
-                               "dt": integrator.dt, "gamma": integrator.gamma, "T": integrator.T}
+                               "dt": integrator.dt, "gamma": integrator.gamma, "T": integrator.T,
+                               "smd_work": None if integrator.smd_work is None else integrator.smd_work.detach().cpu()}
     torch.save(state, path)
 
 
@@ -104,4 +105,28 @@ def load_checkpoint(path, system, integrator=None):
     if integrator is not None and "integrator" in state:
         ig = state["integrator"]
         integrator.seed, integrator.step_count, integrator.replica0 = ig["seed"], ig["step_count"], ig["replica0"]
+        integrator.smd_work = ig.get("smd_work")
     return state.get("extra")
+
+
+def write_colvars_traj(path, steps, dist, center, work, name="End2EndDist", bias="harmonic1"):
+    """One replica's SMD record in the layout of the data generator's ``smd_out.colvars.traj``
+    (All_ML_Training_Data/210905_SMD_decaalanine/SMD/output/N/smd_out.colvars.traj: ``# step  End2EndDist
+    x0_End2EndDist  W_harmonic1``, one row per report, ``%.14e`` columns).  ``steps`` (n,) ints, the rest (n,) floats:
+    ``Integrator.observables[:, r, OBS_E2E_DIST]``, the restraint centre and ``[:, r, OBS_SMD_WORK]``."""
+    steps = np.asarray(steps).reshape(-1)
+    cols = [np.asarray(c, dtype=np.float64).reshape(-1) for c in (dist, center, work)]
+    if any(c.shape != steps.shape for c in cols):
+        raise ValueError("steps, dist, center and work must have one entry per report")
+    w = 23
+    with open(path, "w") as fh:
+        fh.write("# " + "step".ljust(11) + name.rjust(w - 2) + ("x0_" + name).rjust(w) + ("W_" + bias).rjust(w) + "\n")
+        for i, s in enumerate(steps):
+            fh.write(f"{int(s):>11d} " + " ".join(f"{c[i]: .14e}".rjust(w - 1) for c in cols) + "\n")
+
+
+def read_colvars_traj(path):
+    """(steps, dist, center, work) arrays from a colvars.traj file (the reference's or ``write_colvars_traj``'s)."""
+    rows = [ln.split() for ln in open(path) if ln.strip() and not ln.startswith("#")]
+    a = np.array(rows, dtype=np.float64)
+    return a[:, 0].astype(np.int64), a[:, 1], a[:, 2], a[:, 3]

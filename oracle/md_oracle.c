@@ -335,7 +335,7 @@ void oracle_normal3(uint64_t seed, uint64_t replica, uint32_t atom, uint64_t ste
 
 /* Integrator.step(niter) of upstream TorchMD, FP64 state.
  * pos/vel/forces double [R][N][3] in/out (forces must be valid at entry), box float [R][9] or NULL.
- * observables double [nreports][R][10] as in b200md_integrate; snapshots double [nsnap][R][N][3]. */
+ * observables double [nreports][R][11] as in b200md_integrate; snapshots double [nsnap][R][N][3]. */
 int oracle_integrate(const b200md_topology_desc* T, const b200md_force_opts* O, const b200md_smd_opts* S,
                      const b200md_integrate_opts* I, int64_t R, double* pos, double* vel, double* forces,
                      const float* box, double* observables, double* snapshots) {
@@ -349,7 +349,7 @@ int oracle_integrate(const b200md_topology_desc* T, const b200md_force_opts* O, 
 #pragma omp parallel for schedule(static)
   for (int64_t r = 0; r < R; ++r) {
     double *p = pos + r * 3 * N, *v = vel + r * 3 * N, *f = forces + r * 3 * N;
-    double b9[9], e[B200MD_NUM_ENERGIES];
+    double b9[9], e[B200MD_NUM_ENERGIES], work = 0.0;
     if (box) for (int k = 0; k < 9; ++k) b9[k] = box[r * 9 + k];
     for (int s = 0; s < I->nsteps; ++s) {
       const uint64_t gstep = I->step0 + (uint64_t)s;
@@ -364,6 +364,8 @@ int oracle_integrate(const b200md_topology_desc* T, const b200md_force_opts* O, 
       /* SMD centre of the step whose forces are being computed: c0 + rate * (global step + 1) */
       double center = (S && S->enabled) ? (double)S->center0 + (double)S->center_rate * (double)(gstep + 1) : 0.0;
       forces_one(T, O, S, center, p, box ? b9 : NULL, f, e);
+      if (S && S->enabled) /* work of the moving restraint: dW = dE/dc dc = fk (c - d) dc */
+        work += (double)S->fk * (center - norm(sub(getpos(p, S->atom2), getpos(p, S->atom1)))) * (double)S->center_rate;
       if (langevin) {
         for (int a = 0; a < N; ++a) {
           double m = T->mass[a], n3[3];
@@ -388,6 +390,7 @@ int oracle_integrate(const b200md_topology_desc* T, const b200md_force_opts* O, 
         for (int k = 0; k < B200MD_NUM_ENERGIES; ++k) o[k] = e[k];
         o[B200MD_OBS_EKIN] = ekin;
         o[B200MD_OBS_E2E_DIST] = (S && S->enabled) ? norm(sub(getpos(p, S->atom2), getpos(p, S->atom1))) : 0.0;
+        o[B200MD_OBS_SMD_WORK] = work;
       }
       if (I->snapshot_every > 0 && snapshots && (s + 1) % I->snapshot_every == 0) {
         int slot = (s + 1) / I->snapshot_every - 1;

@@ -297,6 +297,49 @@ def test_langevin_smd_short_horizon_vs_oracle():
     np.testing.assert_allclose(obs[:, :, _cabi.OBS_E2E_DIST], out["observables"][:, :, _cabi.OBS_E2E_DIST], rtol=1e-5)
     np.testing.assert_allclose(obs[:, :, 7], out["observables"][:, :, 7], rtol=2e-3, atol=1e-4)
     np.testing.assert_allclose(obs[:, :, _cabi.OBS_EKIN], out["observables"][:, :, _cabi.OBS_EKIN], rtol=1e-3)
+    np.testing.assert_allclose(obs[:, :, _cabi.OBS_SMD_WORK], out["observables"][:, :, _cabi.OBS_SMD_WORK], rtol=1e-4,
+                               atol=1e-7)
+
+
+def test_smd_work_accumulates_across_calls_and_feeds_jarzynski(tmp_path):
+    """W(t) per replica in one launch == the same run split over three step() calls (the state is
+    bitwise; the work is an FP64 sum of the same terms regrouped at the call boundaries), the running sum of the
+    recorded distances reproduces it, and the ensemble estimate / colvars file come out of it."""
+    from molecular_dynamics_b200 import jarzynski_free_energy, read_colvars_traj, write_colvars_traj
+
+    g = load_golden("ala10")
+    R = 64
+    pos0 = np.repeat(g["pos"][:1], R, 0)
+    vel0 = (0.1 * np.random.default_rng(9).standard_normal(pos0.shape)).astype(np.float32)
+    rate, fk, c0 = 0.002, 7.2, 13.0
+
+    def run(chunks):
+        par, s = make_system(g, pos0, vel0)
+        F = Forces(par, external=SMDBias([3], [98], fk=fk, cent_0=c0, rate_per_step=rate))
+        F.compute_batch(s.pos, s.box, s.forces)
+        integ = Integrator(s, F, timestep=1.0, device=DEV, gamma=1.0, T=300.0, seed=7)
+        integ.energy_every = 1
+        obs = []
+        for n in chunks:
+            integ.step(niter=n)
+            obs.append(integ.observables.cpu().numpy())
+        return np.concatenate(obs, 0), integ
+
+    one, integ = run([60])
+    three, integ3 = run([20, 25, 15])
+    np.testing.assert_array_equal(one[:, :, _cabi.OBS_E2E_DIST], three[:, :, _cabi.OBS_E2E_DIST])
+    np.testing.assert_allclose(one[:, :, _cabi.OBS_SMD_WORK], three[:, :, _cabi.OBS_SMD_WORK], rtol=1e-13, atol=1e-15)
+    np.testing.assert_array_equal(integ.smd_work.cpu().numpy(), one[-1, :, _cabi.OBS_SMD_WORK])
+    centers = np.float32(c0) + np.float64(np.float32(rate)) * np.arange(1, 61)[:, None]
+    centers = centers.astype(np.float32).astype(np.float64)  # the kernel hands the centre over as a float
+    expect = np.cumsum(np.float32(fk) * (centers - one[:, :, _cabi.OBS_E2E_DIST]) * np.float64(np.float32(rate)), axis=0)
+    np.testing.assert_allclose(one[:, :, _cabi.OBS_SMD_WORK], expect, rtol=1e-5, atol=1e-7)
+    assert np.ptp(one[-1, :, _cabi.OBS_SMD_WORK]) > 0  # replicas diverge under the thermostat
+    r = jarzynski_free_energy(integ.observables[:, :, _cabi.OBS_SMD_WORK], 300.0)
+    assert r["dF"].shape == (60,) and bool((r["dF"] <= r["mean_work"] + 1e-12).all())
+    path = str(tmp_path / "smd_out.colvars.traj")
+    write_colvars_traj(path, np.arange(1, 61), one[:, 0, _cabi.OBS_E2E_DIST], centers[:, 0], one[:, 0, _cabi.OBS_SMD_WORK])
+    np.testing.assert_allclose(read_colvars_traj(path)[3], one[:, 0, _cabi.OBS_SMD_WORK], rtol=1e-13)
 
 
 def test_integrator_chunking_and_sharding_are_bitwise_invariant():
@@ -334,7 +377,7 @@ def test_snapshots_and_reports_layout():
     integ = Integrator(s, F, timestep=0.5, device=DEV)
     integ.energy_every, integ.snapshot_every = 4, 8
     integ.step(niter=16)
-    assert integ.observables.shape == (4, 4, 10) and integ.snapshots.shape == (2, 4, 22, 3)
+    assert integ.observables.shape == (4, 4, _cabi.NUM_OBSERVABLES) and integ.snapshots.shape == (2, 4, 22, 3)
     np.testing.assert_array_equal(integ.snapshots[-1].cpu().numpy(), s.pos.cpu().numpy())
     f0, _ = oracle.forces(g.packed, pos0)
     out = oracle.integrate(g.packed, pos0, np.zeros_like(pos0), f0, nsteps=16, dt=np.float32(integ.dt), energy_every=4,

@@ -149,3 +149,44 @@ def test_wrapper_moves_whole_groups_into_the_box():
     np.testing.assert_allclose(pos[0, 3], [9.5, 5.0, 3.0], atol=1e-6)
     np.testing.assert_allclose(pos[0, 4:6, 2], [2.1, 1.9], atol=1e-5)
     np.testing.assert_allclose(pos[0, 1] - pos[0, 0], ref[0, 1] - ref[0, 0], atol=1e-6)  # intra-group geometry kept
+
+
+def test_colvars_traj_round_trip_and_reference_layout(tmp_path):
+    import os
+
+    from molecular_dynamics_b200 import read_colvars_traj, write_colvars_traj
+
+    ref = os.path.join(os.path.dirname(__file__), "golden", "smd_out_head.colvars.traj")
+    steps, d, c, w = read_colvars_traj(ref)
+    out = str(tmp_path / "mine.colvars.traj")
+    write_colvars_traj(out, steps, d, c, w)
+    s2, d2, c2, w2 = read_colvars_traj(out)
+    np.testing.assert_array_equal(s2, steps)
+    for a, b in ((d, d2), (c, c2), (w, w2)):
+        np.testing.assert_array_equal(a, b)  # %.14e both ways: the text round-trips exactly
+    ref_lines, my_lines = open(ref).read().splitlines(), open(out).read().splitlines()
+    assert my_lines[0].split() == ref_lines[0].split()
+    assert [ln.split() for ln in my_lines[1:6]] == [ln.split() for ln in ref_lines[1:6]]
+    with pytest.raises(ValueError):
+        write_colvars_traj(out, steps, d[:-1], c, w)
+
+
+def test_jarzynski_estimator_single_rank_limits():
+    import torch
+
+    from molecular_dynamics_b200 import BOLTZMAN, jarzynski_free_energy
+
+    kT = BOLTZMAN * 300.0
+    # identical work on every replica: dF = W exactly, zero variance
+    r = jarzynski_free_energy(torch.full((4, 100), 3.25, dtype=torch.float64), 300.0)
+    np.testing.assert_allclose(r["dF"].numpy(), 3.25, rtol=1e-12)
+    np.testing.assert_allclose(r["dF_cumulant2"].numpy(), 3.25, rtol=1e-12)
+    # Gaussian work: dF -> mean - var / 2kT; large offsets must not overflow (shifted exponentials)
+    g = torch.Generator().manual_seed(0)
+    w = 500.0 + 0.3 * torch.randn((200000,), generator=g, dtype=torch.float64)
+    r = jarzynski_free_energy(w, 300.0)
+    assert abs(float(r["dF"]) - (500.0 - 0.09 / (2 * kT))) < 5e-3
+    assert abs(float(r["dF_cumulant2"]) - (500.0 - 0.09 / (2 * kT))) < 5e-3
+    assert float(r["dF"]) <= float(r["mean_work"])  # Jensen: dF <= <W>
+    ref = -kT * (torch.logsumexp(-w / kT, 0) - np.log(w.numel()))
+    np.testing.assert_allclose(float(r["dF"]), float(ref), rtol=1e-12)

@@ -227,3 +227,35 @@ def test_oracle_minimum_image_vs_reference(system, mode):
     fr, er = r[f"{system}_{mode}_f64_forces"], r[f"{system}_{mode}_f64_energies"]
     assert np.abs(f - fr).max() <= 1e-9 * np.abs(fr).max()
     np.testing.assert_allclose(e, er, rtol=1e-10, atol=1e-9)
+
+
+def test_smd_work_definition_matches_reference_colvars_record():
+    """W_harmonic1 of the reference's own NAMD/colvars record (tests/golden/smd_out_head.colvars.traj, copied by
+    tools/make_golden_colvars.py) is sum fk (x0 - x) dx0 with fk = 1: the definition OBS_SMD_WORK restates.  The
+    record is sampled every 50 steps, so the check integrates by trapezoids and allows the sampling error."""
+    from molecular_dynamics_b200.utils import read_colvars_traj
+
+    steps, d, c, w = read_colvars_traj(os.path.join(os.path.dirname(__file__), "golden", "smd_out_head.colvars.traj"))
+    dev = c - d
+    trap = np.concatenate([[0.0], np.cumsum(0.5 * (dev[1:] + dev[:-1]) * np.diff(c))])
+    assert np.abs(trap - w).max() < 2e-3 and abs(w[-1]) > 0.05
+    assert np.sign(w[1]) == np.sign(dev[0])
+
+
+def test_oracle_smd_work_is_the_running_sum_of_its_own_records():
+    g = load_golden("ala10")
+    pos0 = g["pos"][:3]
+    vel0 = (0.05 * np.random.default_rng(11).standard_normal(pos0.shape)).astype(np.float32)
+    rate, fk, c0 = np.float32(0.01), 2.5, 13.0
+    smd = dict(atom1=3, atom2=98, fk=fk, center0=c0, center_rate=rate)
+    f0, _ = oracle.forces(g.packed, pos0, smd=dict(smd, center_rate=0.0))
+    out = oracle.integrate(g.packed, pos0, vel0, f0, nsteps=40, dt=np.float32(1.0 / TIMEFACTOR), energy_every=1, smd=smd)
+    obs = out["observables"]
+    centers = c0 + float(rate) * np.arange(1, 41)[:, None]
+    expect = np.cumsum(fk * (centers - obs[:, :, _cabi.OBS_E2E_DIST]) * float(rate), axis=0)
+    np.testing.assert_allclose(obs[:, :, _cabi.OBS_SMD_WORK], expect, rtol=1e-12, atol=1e-14)
+    # the restraint energy recorded in the external slot is 1/2 fk (c - d)^2 at the same centre
+    np.testing.assert_allclose(obs[:, :, 7], 0.5 * fk * (centers - obs[:, :, _cabi.OBS_E2E_DIST]) ** 2, rtol=1e-10)
+    # without a bias the column stays zero
+    out0 = oracle.integrate(g.packed, pos0, vel0, f0, nsteps=5, dt=np.float32(1.0 / TIMEFACTOR))
+    assert not out0["observables"][:, :, _cabi.OBS_SMD_WORK].any()
