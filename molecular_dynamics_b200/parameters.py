@@ -240,8 +240,14 @@ def build_parameters_yaml(top: Topology, ff: YamlForceField, terms=ALL_TERMS, pr
 
 
 def build_parameters_prmtop(top: Topology, ff: PrmtopForceField, terms=ALL_TERMS, precision=torch.float,
-                            device="cpu") -> Parameters:
-    """prmtop topology + its own parameter tables -> Parameters (parameters read by index)."""
+                            device="cpu", charmm_impropers=False, urey_bradley=False) -> Parameters:
+    """prmtop topology + its own parameter tables -> Parameters (parameters read by index).
+
+    The two CHAMBER-only term families are OFF by default because the reference's route drops them silently
+    (the 22 harmonic impropers and 65 Urey-Bradley terms of the ALA10 prmtop never reach
+    ``Forces``); ``charmm_impropers=True`` adds them as a periodicity-0 improper slice (the reference's CHARMM
+    branch, forces.py:570-576) and ``urey_bradley=True`` as extra rows of the bond list.  The exclusion set does
+    not change: Urey-Bradley pairs are the end atoms of angles, already excluded as 1-3."""
     terms = [t.lower() for t in terms]
     par = Parameters()
     # LJ types: the prmtop's own ATOM_TYPE_INDEX (A/B tables are given over these)
@@ -277,6 +283,23 @@ def build_parameters_prmtop(top: Topology, ff: PrmtopForceField, terms=ALL_TERMS
         par.impropers = torch.tensor(uqimp.astype(np.int64))
         par.improper_params = [{"idx": torch.arange(len(uqimp), dtype=torch.int64),
                                 "params": torch.tensor([ff.improper_term(r) for r in uqimp], dtype=torch.float64)}]
+    if urey_bradley and "bonds" in terms:
+        from .topology_io import chamber_urey_bradley
+
+        pairs, prm = chamber_urey_bradley(ff.sec)
+        if len(pairs):
+            have = par.bonds is not None
+            par.bonds = torch.cat([par.bonds, torch.tensor(pairs)]) if have else torch.tensor(pairs)
+            par.bond_params = torch.cat([par.bond_params, torch.tensor(prm)]) if have else torch.tensor(prm)
+    if charmm_impropers and "impropers" in terms:
+        from .topology_io import chamber_impropers
+
+        quads, prm = chamber_impropers(ff.sec)
+        if len(quads):
+            n0 = 0 if par.impropers is None else len(par.impropers)
+            sl = {"idx": torch.arange(n0, n0 + len(quads), dtype=torch.int64), "params": torch.tensor(prm)}
+            par.impropers = torch.tensor(quads) if n0 == 0 else torch.cat([par.impropers, torch.tensor(quads)])
+            par.improper_params = [sl] if n0 == 0 else list(par.improper_params) + [sl]
     return par.precision_(precision).to_(device)
 
 

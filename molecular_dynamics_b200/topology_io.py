@@ -111,13 +111,32 @@ def read_pdb_coords(path: str) -> np.ndarray:
 
 
 def read_namd_bin(path: str) -> np.ndarray:
-    """NAMD binary coordinate / velocity file: little-endian int32 N, then N*3 float64."""
+    """NAMD binary coordinate / velocity file: little-endian int32 N, then N*3 float64.  Velocities are in NAMD's
+    internal unit, A per 48.88821 fs -- the same TIMEFACTOR the integrator uses, so a ``.vel`` file drops into
+    ``System.vel`` unchanged."""
     with open(path, "rb") as fh:
         raw = fh.read()
     (n,) = struct.unpack("<i", raw[:4])
     if len(raw) != 4 + 24 * n:
         raise ValueError(f"{path}: size {len(raw)} does not match {n} atoms")
     return np.frombuffer(raw, dtype="<f8", offset=4).reshape(n, 3).copy()
+
+
+def read_xsc(path: str) -> dict:
+    """NAMD extended-system file -> {"step", "box" (3, 3) rows a, b, c (zeros in vacuum), "origin" (3,)}.  The
+    ``#$LABELS`` line names the columns; the reference's vacuum runs write only ``step o_x o_y o_z``."""
+    labels, values = None, None
+    with open(path) as fh:
+        for line in fh:
+            if line.startswith("#$LABELS"):
+                labels = line.split()[1:]
+            elif line.strip() and not line.startswith("#"):
+                values = [float(x) for x in line.split()]
+    if labels is None or values is None or len(values) < len(labels):
+        raise ValueError(f"{path}: not an xsc file")
+    rec = dict(zip(labels, values))
+    box = np.array([[rec.get(f"{v}_{c}", 0.0) for c in "xyz"] for v in "abc"], dtype=np.float64)
+    return {"step": int(rec["step"]), "box": box, "origin": np.array([rec.get(f"o_{c}", 0.0) for c in "xyz"])}
 
 
 # ----------------------------------------------------------------------------------------------
@@ -201,6 +220,25 @@ def read_prmtop(path: str):
 
     ff = PrmtopForceField(sec, top, bond_rows=b, angle_rows=a, dihedral_rows=d)
     return top, ff
+
+
+def chamber_urey_bradley(sec):
+    """CHAMBER ``CHARMM_UREY_BRADLEY`` -> (pairs (n, 2) 0-based, params (n, 2) = (k, r0)): harmonic 1-3 terms
+    ``k (r - r0)^2``, i.e. extra rows of the bond list.  Atom indices in the CHARMM sections are
+    plain 1-based, not the 3*index coordinate offsets of the AMBER sections."""
+    rows = np.array(sec.get("CHARMM_UREY_BRADLEY", []), dtype=np.int64).reshape(-1, 3)
+    k = np.array(sec.get("CHARMM_UREY_BRADLEY_FORCE_CONSTANT", []), dtype=np.float64)
+    r0 = np.array(sec.get("CHARMM_UREY_BRADLEY_EQUIL_VALUE", []), dtype=np.float64)
+    return rows[:, :2] - 1, np.stack([k[rows[:, 2] - 1], r0[rows[:, 2] - 1]], axis=1)
+
+
+def chamber_impropers(sec):
+    """CHAMBER ``CHARMM_IMPROPERS`` -> (quads (n, 4) 0-based, params (n, 3) = (k, psi0, 0)): harmonic impropers
+    ``k (psi - psi0)^2``; periodicity 0 selects the reference's CHARMM branch (forces.py:570-576)."""
+    rows = np.array(sec.get("CHARMM_IMPROPERS", []), dtype=np.int64).reshape(-1, 5)
+    k = np.array(sec.get("CHARMM_IMPROPER_FORCE_CONSTANT", []), dtype=np.float64)
+    p0 = np.array(sec.get("CHARMM_IMPROPER_PHASE", []), dtype=np.float64)
+    return rows[:, :4] - 1, np.stack([k[rows[:, 4] - 1], p0[rows[:, 4] - 1], np.zeros(len(rows))], axis=1)
 
 
 class PrmtopForceField:

@@ -561,3 +561,51 @@ def test_tutorial_loop_shapes():
     etot = Epot + Ekin
     assert isinstance(etot, np.ndarray) and etot.shape == (1,) and np.isfinite(etot).all()
     assert len(Epot) == 1 and float(Epot[0]) == float(np.asarray(Epot)[0])
+
+
+class _Chamber:
+    """ALA10 with every CHAMBER term family switched on: 22 harmonic CHARMM impropers (general torsion
+    path, periodicity 0) and 65 Urey-Bradley 1-3 terms as extra bond rows."""
+
+    def __init__(self):
+        from molecular_dynamics_b200.parameters import parameters_from_prmtop
+        from molecular_dynamics_b200.topology_io import read_pdb_coords
+
+        gold = os.path.join(os.path.dirname(__file__), "golden")
+        self.par = parameters_from_prmtop(os.path.join(gold, "full_da-1.3.prmtop"), precision=torch.float64,
+                                          charmm_impropers=True, urey_bradley=True)
+        base = read_pdb_coords(os.path.join(gold, "smd_ini.pdb")).astype(np.float64)
+        rng = np.random.default_rng(21)
+        self.pos = (base[None] + 0.04 * rng.standard_normal((6,) + base.shape)).astype(np.float32)
+        self.pos[0] = base
+        self.ava_idx = _cabi.make_pair_index(self.par.natoms, self.par.get_exclusions())
+        self.packed = _cabi.PackedTopology(self.par, self.ava_idx)
+
+
+@pytest.mark.parametrize("mode", sorted(MODES))
+def test_chamber_impropers_and_urey_bradley_vs_oracle(mode):
+    g = _Chamber()
+    f_ref, e_ref = oracle.forces(g.packed, g.pos.astype(np.float64), **MODES[mode])
+    f, e, F = run_gpu(g, g.pos, **MODES[mode])
+    check(g, g.pos, f, e, f_ref, e_ref, mode)
+    assert e[0, _cabi.energy_slot("impropers")] > 1.0  # the 22 impropers are evaluated, not dropped
+    np.testing.assert_array_equal(F.ava_idx.cpu().numpy(), g.ava_idx)
+
+
+def test_chamber_fused_integrator_short_horizon_vs_oracle():
+    g = _Chamber()
+    pos0 = g.pos[:3]
+    vel0 = (0.05 * np.random.default_rng(2).standard_normal(pos0.shape)).astype(np.float32)
+    par, s = make_system(g, pos0, vel0)
+    F = Forces(par)
+    F.compute_batch(s.pos, s.box, s.forces)
+    f0 = s.forces.cpu().numpy().astype(np.float64)
+    integ = Integrator(s, F, timestep=1.0, device=DEV)
+    integ.energy_every = 10
+    integ.step(niter=40)
+    out = oracle.integrate(g.packed, pos0, vel0, f0, nsteps=40, dt=np.float32(integ.dt), energy_every=10)
+    assert np.abs(s.pos.cpu().numpy() - out["pos"]).max() < 3e-4
+    obs = integ.observables.cpu().numpy()
+    np.testing.assert_allclose(obs[:, :, :8].sum(-1), out["observables"][:, :, :8].sum(-1), rtol=2e-5, atol=2e-3)
+    k = _cabi.energy_slot("impropers")
+    np.testing.assert_allclose(obs[:, :, k], out["observables"][:, :, k], rtol=2e-3, atol=1e-3)

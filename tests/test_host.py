@@ -190,3 +190,33 @@ def test_jarzynski_estimator_single_rank_limits():
     assert float(r["dF"]) <= float(r["mean_work"])  # Jensen: dF <= <W>
     ref = -kT * (torch.logsumexp(-w / kT, 0) - np.log(w.numel()))
     np.testing.assert_allclose(float(r["dF"]), float(ref), rtol=1e-12)
+
+
+def test_namd_restart_files_against_the_chamber_prmtop():
+    """read_namd_bin / read_xsc on the reference's own restart of replica 3 (copied by tools/make_golden_chamber.py).
+    The run used rigidBonds ALL, so every X-H distance in the .coor file equals the prmtop's equilibrium length: one
+    check that pins the binary reader, the prmtop bond table and its atom indexing together.  The .vel file is in
+    A / 48.88821 fs, the integrator's unit: the kinetic temperature over the unconstrained degrees of freedom comes
+    out at the thermostat's 300 K within the fluctuation of 259 degrees of freedom."""
+    import os
+
+    from molecular_dynamics_b200 import BOLTZMAN
+    from molecular_dynamics_b200.parameters import parameters_from_prmtop
+    from molecular_dynamics_b200.topology_io import read_namd_bin, read_xsc
+
+    gold = os.path.join(os.path.dirname(__file__), "golden")
+    x = read_namd_bin(os.path.join(gold, "smd_out.restart.coor"))
+    v = read_namd_bin(os.path.join(gold, "smd_out.restart.vel"))
+    xsc = read_xsc(os.path.join(gold, "smd_out.restart.xsc"))
+    assert x.shape == v.shape == (104, 3) and xsc["step"] == 500000 and not xsc["box"].any()
+    par = parameters_from_prmtop(os.path.join(gold, "full_da-1.3.prmtop"), precision=torch.float64)
+    b, bp, m = par.bonds.numpy(), par.bond_params.numpy(), par.masses.numpy().ravel()
+    r = np.linalg.norm(x[b[:, 0]] - x[b[:, 1]], axis=1)
+    xh = (m[b[:, 0]] < 1.5) | (m[b[:, 1]] < 1.5)
+    assert xh.sum() == 53 and np.abs(r[xh] - bp[xh, 1]).max() < 1e-6
+    assert np.abs(r[~xh] - bp[~xh, 1]).max() < 0.2  # the heavy-atom bonds fluctuate thermally
+    ekin = 0.5 * (m[:, None] * v ** 2).sum()
+    temp = 2.0 * ekin / ((3 * 104 - 53) * BOLTZMAN)
+    assert 200.0 < temp < 400.0
+    with pytest.raises(ValueError):
+        read_namd_bin(os.path.join(gold, "smd_out.restart.xsc"))

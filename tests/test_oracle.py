@@ -259,3 +259,54 @@ def test_oracle_smd_work_is_the_running_sum_of_its_own_records():
     # without a bias the column stays zero
     out0 = oracle.integrate(g.packed, pos0, vel0, f0, nsteps=5, dt=np.float32(1.0 / TIMEFACTOR))
     assert not out0["observables"][:, :, _cabi.OBS_SMD_WORK].any()
+
+
+def _chamber_system(**kw):
+    import torch
+
+    from molecular_dynamics_b200.parameters import parameters_from_prmtop
+    from molecular_dynamics_b200.topology_io import read_pdb_coords
+
+    gold = os.path.join(os.path.dirname(__file__), "golden")
+    par = parameters_from_prmtop(os.path.join(gold, "full_da-1.3.prmtop"), precision=torch.float64, **kw)
+    pos = read_pdb_coords(os.path.join(gold, "smd_ini.pdb"))[None].astype(np.float64)
+    pidx = _cabi.make_pair_index(par.natoms, par.get_exclusions(("bonds", "angles", "1-4")))
+    return par, pos, _cabi.PackedTopology(par, pidx)
+
+
+def test_chamber_prmtop_route_against_namd_step0_energies():
+    """Loose external anchor of the prmtop -> Parameters route (otherwise "unpinned"): NAMD's own
+    energies of the reference's start structure with the same CHARMM22 force field
+    (tests/golden/namd_step0_energies.json, made by tools/make_golden_chamber.py).  NAMD constrains the X-H bonds
+    before evaluating (rigidBonds ALL), so BOND is not comparable, ELECT contains the GB term, and the rest agrees to
+    a fraction of a percent: enough to catch a wrong unit, phase convention, 1-4 table or dropped term family."""
+    import json
+
+    namd = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "namd_step0_energies.json")))["energies"]
+    slot = _cabi.energy_slot
+    # the reference's behaviour: CHARMM impropers and Urey-Bradley silently dropped
+    par, pos, packed = _chamber_system()
+    assert par.impropers is None and len(par.bonds) == 103
+    _, e0 = oracle.forces(packed, pos)
+    assert e0[0, slot("impropers")] == 0.0
+    assert abs(e0[0, slot("dihedrals")] - namd["DIHED"]) < 1e-3 * namd["DIHED"]
+    # opt-in: all CHAMBER term families
+    par, pos, packed = _chamber_system(charmm_impropers=True, urey_bradley=True)
+    assert len(par.impropers) == 22 and len(par.bonds) == 103 + 65
+    assert bool((par.improper_params[0]["params"][:, 2] == 0).all())
+    _, e = oracle.forces(packed, pos)
+    assert abs(e[0, slot("impropers")] - namd["IMPRP"]) < 5e-3 * namd["IMPRP"]
+    np.testing.assert_allclose(e[0, slot("dihedrals")], e0[0, slot("dihedrals")], rtol=1e-14)
+    ub = e[0, slot("bonds")] - e0[0, slot("bonds")]
+    assert 4.0 < ub < 7.0  # 65 Urey-Bradley terms
+    assert abs(e[0, slot("angles")] + ub - namd["ANGLE"]) < 0.03 * namd["ANGLE"]  # hydrogens moved by the constraints
+    # VDW = LJ + 1-4 LJ (CHARMM 1-4 table); evaluate without charges so the slot holds only that
+    par.charges = par.charges * 0
+    _, ev = oracle.forces(_cabi.PackedTopology(par, _cabi.make_pair_index(par.natoms, par.get_exclusions())), pos)
+    assert ev[0, slot("electrostatics")] == 0.0
+    assert abs(ev[0, slot("lj")] - namd["VDW"]) < 5e-3 * abs(namd["VDW"])
+    # the exclusion set is unchanged by the Urey-Bradley rows (they are 1-3 pairs)
+    par0, _, _ = _chamber_system()
+    a = _cabi.make_pair_index(par.natoms, par.get_exclusions())
+    b = _cabi.make_pair_index(par0.natoms, par0.get_exclusions())
+    np.testing.assert_array_equal(a, b)
