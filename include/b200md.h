@@ -62,6 +62,7 @@ enum b200md_status {
 
 /* per-replica status flags written by the kernels (uint32 per replica) */
 #define B200MD_FLAG_NAN_POS 1u
+#define B200MD_FLAG_CONSTRAINT 2u      /* integrator, rigid_bonds: SHAKE / RATTLE did not converge for a hydrogen group */
 #define B200MD_FLAG_FORCE_RANGE 4u     /* integrator: the bonded force on an atom exceeded 4096 kcal/mol/A (fixed-point range) */
 
 /*
@@ -144,7 +145,16 @@ typedef struct b200md_integrate_opts {
   int32_t nsteps;      /* niter                                                                 */
   int32_t energy_every;   /* record observables every this many steps (0: only after the last)  */
   int32_t snapshot_every; /* write positions every this many steps (0: never)                   */
+  /* != 0: hold every bond with a hydrogen end at its equilibrium length (NAMD "rigidBonds all", the setting of the
+   * reference's data generator, All_ML_Training_Data/210905_SMD_decaalanine/SMD/output/N/smd.namd: it is what lets
+   * that run take 2 fs steps).  SHAKE on the positions after the first half step, RATTLE on the velocities after
+   * the second.  Constraint set, derived from the topology at b200md_topology_create: an atom with 0.5 < mass < 3.5
+   * is a hydrogen; it is tied to the partner of its bond row with the smallest req (so Urey-Bradley 1-3 rows in the
+   * bond list stay harmonic), at that row's req.  Hydrogens must hang on heavy atoms, at most 3 per heavy atom
+   * (else B200MD_ERR_UNSUPPORTED).  Group vectors are plain differences: keep bonded groups whole under PBC. */
+  int32_t rigid_bonds;
 } b200md_integrate_opts;
+
 
 /* observables recorded per replica at each report: 8 energy slots + Ekin + end-to-end distance + the work done by
  * the moving SMD restraint since the first step of the call, W = sum_steps fk (c - d) dc (the W_harmonic column of
@@ -164,6 +174,9 @@ void b200md_topology_destroy(b200md_topology* topo);
  * (natoms x 4 uint32, bit j of row i set iff pair (i,j) is NOT evaluated), copied to host `out`. */
 int b200md_topology_exclusion_mask(const b200md_topology* topo, uint32_t* out /* [natoms*4] */);
 int b200md_topology_natoms(const b200md_topology* topo);
+/* number of rigid bonds b200md_integrate holds with rigid_bonds != 0 (degrees of freedom = 3 natoms - this),
+ * or -1 when the topology has a hydrogen group the constraint kernel does not support */
+int b200md_topology_num_constraints(const b200md_topology* topo);
 
 /*
  * Forces.compute (forces.py:82-344) for R replicas: zeroes and fills forces, writes per-term

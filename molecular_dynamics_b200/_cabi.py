@@ -32,6 +32,7 @@ TERM_BITS = {"electrostatics": 1 << 0, "lj": 1 << 1, "bonds": 1 << 2, "angles": 
 
 OK, ERR_INVALID_ARGUMENT, ERR_TOO_MANY_ATOMS, ERR_CUDA, ERR_NAN_COORDINATES, ERR_UNSUPPORTED = range(6)
 FLAG_NAN_POS = 1
+FLAG_CONSTRAINT = 2
 FLAG_FORCE_RANGE = 4
 
 _i32p, _f32p, _f64p, _u32p = (C.POINTER(C.c_int32), C.POINTER(C.c_float), C.POINTER(C.c_double),
@@ -68,7 +69,7 @@ class SmdOpts(C.Structure):
 class IntegrateOpts(C.Structure):
     _fields_ = [("dt", C.c_float), ("gamma", C.c_float), ("temperature", C.c_float), ("seed", C.c_uint64),
                 ("step0", C.c_uint64), ("replica0", C.c_int64), ("nsteps", C.c_int32),
-                ("energy_every", C.c_int32), ("snapshot_every", C.c_int32)]
+                ("energy_every", C.c_int32), ("snapshot_every", C.c_int32), ("rigid_bonds", C.c_int32)]
 
 
 # ----------------------------------------------------------------------------------------------
@@ -178,6 +179,8 @@ def declare_signatures(lib):
     lib.b200md_topology_exclusion_mask.argtypes = [vp, vp]
     lib.b200md_topology_natoms.restype = C.c_int
     lib.b200md_topology_natoms.argtypes = [vp]
+    lib.b200md_topology_num_constraints.restype = C.c_int
+    lib.b200md_topology_num_constraints.argtypes = [vp]
     lib.b200md_forces_compute.restype = C.c_int
     lib.b200md_forces_compute.argtypes = [vp, C.POINTER(ForceOpts), C.POINTER(SmdOpts), C.c_int64, vp, vp, vp, vp,
                                           vp, vp]
@@ -200,7 +203,7 @@ def declare_signatures(lib):
 
 EXPORTED_SYMBOLS = (
     "b200md_topology_create", "b200md_topology_destroy", "b200md_topology_exclusion_mask",
-    "b200md_topology_natoms", "b200md_forces_compute", "b200md_integrate", "b200md_forces_compute_host",
+    "b200md_topology_natoms", "b200md_topology_num_constraints", "b200md_forces_compute", "b200md_integrate", "b200md_forces_compute_host",
     "b200md_fp32_peak_tflops", "b200md_launch_count", "b200md_last_error", "b200md_version",
 )
 

@@ -124,7 +124,7 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
 // Integrator.step(niter) of upstream TorchMD fused with Forces.compute: positions, velocities and
 // forces of a replica stay in registers / shared memory for all nsteps; HBM sees only the initial
 // load, the final store, the observable records and the optional snapshots.
-template <int MODE>
+template <int MODE, bool RIGID>
 __global__ void __launch_bounds__(kThreads, 4)
 integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const long long R, float* __restrict__ pos,
                  float* __restrict__ vel, float* __restrict__ forces, const float* __restrict__ box,
@@ -146,6 +146,8 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
   const bool langevin = I.temperature > 0.0f;
   const float vcoef = langevin ? sqrtf(2.0f * I.gamma * invm * kBoltzman * I.temperature * dt) : 0.0f;
   const float vdamp = I.gamma * dt;
+  const float inv_dt = 1.0f / dt;
+  const int cmax = RIGID ? (int)((T.cnmax >> (8 * warp)) & 0xffu) : 0;
   for (long long r = blockIdx.x; r < R; r += gridDim.x) {
     __syncthreads();
     float x = 0.f, y = 0.f, z = 0.f, vx = 0.f, vy = 0.f, vz = 0.f, fx = 0.f, fy = 0.f, fz = 0.f;
@@ -166,11 +168,25 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
     }
     if (status != nullptr && tid == 0) status[r] = 0;
     if (tid == kThreads - 1) S.smd_energy[1] = 0.0;  // same thread as smd_task: no barrier needed
+    if (RIGID && live) S.pos[tid] = make_float4(x, y, z, q);  // SHAKE reads x(t) from here (visible after its barrier)
     for (int s = 0; s < I.nsteps; ++s) {
       const unsigned long long gstep = I.step0 + (unsigned long long)s;
       // _first_VV: pos += vel dt + 0.5 a dt^2 ; vel += 0.5 dt a
       vx = fmaf(hdt_m, fx, vx); vy = fmaf(hdt_m, fy, vy); vz = fmaf(hdt_m, fz, vz);
       x = fmaf(dt, vx, x); y = fmaf(dt, vy, y); z = fmaf(dt, vz, z);
+      if (RIGID) {  // SHAKE: S.pos still holds x(t); publish the unconstrained x(t + dt), collect displacements
+        S.sx[tid] = x; S.sx[kMaxAtoms + tid] = y; S.sx[2 * kMaxAtoms + tid] = z;
+        S.vel[tid] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        __syncthreads();
+        if (tid < T.ngroups) {
+          const bool ok = cmax > 1 ? shake_group<3>(S, T, tid) : shake_group<1>(S, T, tid);
+          if (!ok) flag |= B200MD_FLAG_CONSTRAINT;
+        }
+        __syncthreads();
+        const float4 d = S.vel[tid];
+        x += d.x; y += d.y; z += d.z;
+        vx = fmaf(d.x, inv_dt, vx); vy = fmaf(d.y, inv_dt, vy); vz = fmaf(d.z, inv_dt, vz);
+      }
       if (live) {
         S.pos[tid] = make_float4(x, y, z, q);
         S.sx[tid] = x; S.sx[kMaxAtoms + tid] = y; S.sx[2 * kMaxAtoms + tid] = z; S.sx[3 * kMaxAtoms + tid] = q;
@@ -201,6 +217,16 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       }
       // _second_VV
       vx = fmaf(hdt_m, fx, vx); vy = fmaf(hdt_m, fy, vy); vz = fmaf(hdt_m, fz, vz);
+      if (RIGID) {  // RATTLE: take the components along the rigid bonds out of v(t + dt)
+        S.vel[tid] = make_float4(vx, vy, vz, 0.0f);
+        __syncthreads();
+        if (tid < T.ngroups) {
+          if (cmax > 1) rattle_group<3>(S, T, tid); else rattle_group<1>(S, T, tid);
+        }
+        __syncthreads();
+        const float4 vv = S.vel[tid];
+        vx = vv.x; vy = vv.y; vz = vv.z;
+      }
       if (report) {
         if (live) E.e[B200MD_OBS_EKIN] = 0.5 * (double)mass * ((double)vx * vx + (double)vy * vy + (double)vz * vz);
         if (P.smd_on && tid == 0) { E.e[B200MD_E_EXTERNAL] += S.smd_energy[0]; E.e[B200MD_OBS_E2E_DIST] = (double)S.smd[4]; }
@@ -732,6 +758,51 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
     }
   }
 
+  // ---- rigid X-H bonds (include/b200md.h, b200md_integrate_opts.rigid_bonds) -------------------------
+  std::vector<int4> cgroup(kMaxAtoms, make_int4(0, 0, 0, 0));
+  std::vector<float4> cdist2(kMaxAtoms, make_float4(1.0f, 1.0f, 1.0f, 0.0f));
+  std::vector<float4> cweight(kMaxAtoms, make_float4(1.0f, 1.0f, 1.0f, 1.0f));
+  T.ncons = 0; T.ngroups = 0; T.cnmax = 0;
+  {
+    auto is_h = [&](int a) { return d->mass[a] > 0.5f && d->mass[a] < 3.5f; };
+    std::vector<int> partner(N, -1);
+    std::vector<float> req(N, 0.0f);
+    for (int b = 0; b < d->nbonds; ++b) {  // a hydrogen is tied through its shortest bond row (Urey-Bradley rows are longer)
+      const int i = d->bond_idx[2 * b], j = d->bond_idx[2 * b + 1];
+      const float r0 = d->bond_prm[2 * b + 1];
+      for (int side = 0; side < 2; ++side) {
+        const int hh = side ? j : i, other = side ? i : j;
+        if (is_h(hh) && (partner[hh] < 0 || r0 < req[hh])) { partner[hh] = other; req[hh] = r0; }
+      }
+    }
+    std::vector<std::vector<int>> kids(N);
+    for (int a = 0; a < N && T.ncons >= 0; ++a) {
+      if (partner[a] < 0) continue;
+      const int p = partner[a];
+      if (is_h(p) || kids[p].size() >= 3 || !(req[a] > 0.0f)) { T.ncons = -1; break; }
+      kids[p].push_back(a);
+      T.ncons += 1;
+    }
+    if (T.ncons > 0) {
+      std::vector<int> parents;
+      for (int p = 0; p < N; ++p) if (!kids[p].empty()) parents.push_back(p);
+      std::stable_sort(parents.begin(), parents.end(), [&](int a, int b) { return kids[a].size() > kids[b].size(); });
+      T.ngroups = (int)parents.size();
+      for (int gi = 0; gi < T.ngroups; ++gi) {
+        const int p = parents[gi], n = (int)kids[p].size();
+        int hh[3] = {p, p, p};
+        float dd[3] = {1.0f, 1.0f, 1.0f}, ww[3] = {1.0f, 1.0f, 1.0f};
+        for (int k = 0; k < n; ++k) { hh[k] = kids[p][k]; dd[k] = req[hh[k]] * req[hh[k]]; ww[k] = 1.0f / d->mass[hh[k]]; }
+        cgroup[gi] = make_int4(p | (n << 8), hh[0], hh[1], hh[2]);
+        cdist2[gi] = make_float4(dd[0], dd[1], dd[2], 0.0f);
+        cweight[gi] = make_float4(1.0f / d->mass[p], ww[0], ww[1], ww[2]);
+        const int w = gi / 32;
+        const uint32_t cur = (T.cnmax >> (8 * w)) & 0xffu;
+        if ((uint32_t)n > cur) T.cnmax = (T.cnmax & ~(0xffu << (8 * w))) | ((uint32_t)n << (8 * w));
+      }
+    }
+  }
+
   // ---- upload --------------------------------------------------------------------------------------
   BlobBuilder B;
   const size_t o_ab = B.add(ab), o_q = B.add(charge), o_m = B.add(mass), o_ro = B.add(rowoff), o_mask = B.add(mask8), o_rot = B.add(diagmask);
@@ -741,6 +812,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   const size_t o_gi = B.add(gen_idx), o_gt = B.add(gen_terms), o_gp = B.add(gen_tp), o_gsl = B.add(gen_slot);
   const size_t o_pi = B.add(p142_idx), o_pp = B.add(p142_ab), o_pq = B.add(p142_q), o_ps = B.add(p142_slot);
   const size_t o_gs = B.add(gstart), o_tk = B.add(tasks_v[0]), o_tke = B.add(tasks_v[1]);
+  const size_t o_cg = B.add(cgroup), o_cd = B.add(cdist2), o_cw = B.add(cweight);
   auto cleanup = [&](const std::string& msg) { fail(B200MD_ERR_CUDA, msg); if (topo->blob) cudaFree(topo->blob); delete topo; };
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) { cleanup(std::string("cudaSetDevice: ") + cudaGetErrorString(e)); return nullptr; }
@@ -762,6 +834,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   T.gather_start = (const uint16_t*)(base + o_gs);
   T.tasks = (const uint32_t*)(base + o_tk);
   T.tasks_e = (const uint32_t*)(base + o_tke);
+  T.cgroup = (const int4*)(base + o_cg); T.cdist2 = (const float4*)(base + o_cd); T.cweight = (const float4*)(base + o_cw);
   T.smem_bytes = (int)smem_layout(nullptr, nullptr, NT, T.nslots, false);
   T.smem_bytes_fixed = (int)smem_layout(nullptr, nullptr, NT, T.nslots, true);
   if (T.smem_bytes > 227 * 1024) { cleanup("topology needs more than 227 KB of shared memory per CTA"); g_last_error = "too much shared memory"; return nullptr; }
@@ -770,8 +843,10 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   topo->num_sms = prop.multiProcessorCount;
   topo->occ_forces[0] = query_occupancy(forces_kernel<0>, T.smem_bytes);
   topo->occ_forces[1] = query_occupancy(forces_kernel<1>, T.smem_bytes);
-  topo->occ_integrate[0] = query_occupancy(integrate_kernel<0>, T.smem_bytes_fixed);
-  topo->occ_integrate[1] = query_occupancy(integrate_kernel<1>, T.smem_bytes_fixed);
+  topo->occ_integrate[0] = query_occupancy(integrate_kernel<0, false>, T.smem_bytes_fixed);
+  topo->occ_integrate[1] = query_occupancy(integrate_kernel<1, false>, T.smem_bytes_fixed);
+  query_occupancy(integrate_kernel<0, true>, T.smem_bytes_fixed);  // also raises the dynamic shared-memory limit
+  query_occupancy(integrate_kernel<1, true>, T.smem_bytes_fixed);
   if (topo->occ_forces[0] < 1 || topo->occ_integrate[0] < 1) { cleanup("kernel does not fit on an SM"); return nullptr; }
   g_last_error.clear();
   return topo;
@@ -783,6 +858,8 @@ extern "C" void b200md_topology_destroy(b200md_topology* topo) {
   if (topo->blob) cudaFree(topo->blob);
   delete topo;
 }
+
+extern "C" int b200md_topology_num_constraints(const b200md_topology* topo) { return topo ? topo->dev.ncons : -1; }
 
 extern "C" int b200md_topology_exclusion_mask(const b200md_topology* topo, uint32_t* out) {
   if (!topo || !out) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
@@ -879,6 +956,8 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
   if (!topo || !io || !pos || !vel || !forces) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
   if (R < 0 || io->nsteps < 0) return fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica or step count");
   if (R == 0 || io->nsteps == 0) return B200MD_OK;
+  if (io->rigid_bonds != 0 && topo->dev.ncons < 0)
+    return fail(B200MD_ERR_UNSUPPORTED, "rigid_bonds: a hydrogen is bonded to a hydrogen, or a heavy atom carries more than 3");
   ForceParams P;
   int rc = make_force_params(topo, fopts, smd, true, &P);
   if (rc) return rc;
@@ -895,10 +974,12 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
   const long long cap = (long long)topo->num_sms * topo->occ_integrate[mode];
   const int grid = (int)((io->nsteps >= 32 && R < (1ll << 30)) ? R : std::min<long long>(R, cap));
   cudaStream_t st = (cudaStream_t)stream;
-  if (mode == 0)
-    integrate_kernel<0><<<grid, kThreads, T.smem_bytes_fixed, st>>>(T, P, I, R, pos, vel, forces, box, observables, snapshots, status);
-  else
-    integrate_kernel<1><<<grid, kThreads, T.smem_bytes_fixed, st>>>(T, P, I, R, pos, vel, forces, box, observables, snapshots, status);
+  const bool rigid = io->rigid_bonds != 0 && T.ncons > 0;
+#define B200MD_LAUNCH_INTEGRATE(M, RG) \
+  integrate_kernel<M, RG><<<grid, kThreads, T.smem_bytes_fixed, st>>>(T, P, I, R, pos, vel, forces, box, observables, snapshots, status)
+  if (mode == 0) { if (rigid) B200MD_LAUNCH_INTEGRATE(0, true); else B200MD_LAUNCH_INTEGRATE(0, false); }
+  else { if (rigid) B200MD_LAUNCH_INTEGRATE(1, true); else B200MD_LAUNCH_INTEGRATE(1, false); }
+#undef B200MD_LAUNCH_INTEGRATE
   g_launches.fetch_add(1);
   CUDA_TRY(cudaGetLastError());
   return B200MD_OK;

@@ -700,6 +700,145 @@ __device__ __forceinline__ void gather_forces(const Smem& S, const ForceParams& 
   }
 }
 
+// ---- rigid X-H bonds: SHAKE on the positions, RATTLE on the velocities ------------------------------
+// One lane per hydrogen group (heavy atom p with its n <= 3 hydrogens): the groups do not share atoms, so the lanes
+// are independent.  The group's n constraints are solved TOGETHER: Newton iterations on the n multipliers with the
+// exact n x n Jacobian for the positions (the matrix form of SHAKE; quadratic convergence, so a fixed 3 iterations
+// take a 2 fs step's ~1e-2 relative violation below fp32 resolution), one linear solve for the velocities (RATTLE is
+// linear in its multipliers).  No data-dependent trip counts.  The step is issue-bound, so what counts is warp
+// instructions, not lanes: the host sorts the groups by size and packs them into the lanes of the first warps
+// (ALA10: 51 groups -> 2 warps instead of the 4 a lane-per-parent-atom mapping would run), and a warp whose groups
+// all have one hydrogen runs the K = 1 instantiation (a scalar Newton iteration) instead of the 3 x 3 one.
+constexpr int kShakeNewtonIters = 3;
+constexpr float kShakeTol = 4.0e-6f;  // accepted |d^2 - r^2| / d^2 after the last iteration (flag beyond it)
+
+// x = A^-1 b by cofactors (A is strongly diagonally dominant here: m_H << m_parent); K = 1: a division
+template <int K>
+__device__ __forceinline__ void solve_k(const float (&A)[K][K], const float (&b)[K], float (&x)[K]) {
+  if constexpr (K == 1) {
+    x[0] = b[0] * fast_rcp(A[0][0]);
+  } else {
+    const float c00 = A[1][1] * A[2][2] - A[1][2] * A[2][1], c01 = A[1][2] * A[2][0] - A[1][0] * A[2][2],
+                c02 = A[1][0] * A[2][1] - A[1][1] * A[2][0];
+    const float inv = fast_rcp(A[0][0] * c00 + A[0][1] * c01 + A[0][2] * c02);
+    const float c10 = A[0][2] * A[2][1] - A[0][1] * A[2][2], c11 = A[0][0] * A[2][2] - A[0][2] * A[2][0],
+                c12 = A[0][1] * A[2][0] - A[0][0] * A[2][1];
+    const float c20 = A[0][1] * A[1][2] - A[0][2] * A[1][1], c21 = A[0][2] * A[1][0] - A[0][0] * A[1][2],
+                c22 = A[0][0] * A[1][1] - A[0][1] * A[1][0];
+    x[0] = (c00 * b[0] + c10 * b[1] + c20 * b[2]) * inv;
+    x[1] = (c01 * b[0] + c11 * b[1] + c21 * b[2]) * inv;
+    x[2] = (c02 * b[0] + c12 * b[1] + c22 * b[2]) * inv;
+  }
+}
+
+// In:  S.pos = x(t) (constraints hold), S.sx = unconstrained x(t + dt).  Out: S.vel[a].xyz = displacement that
+// restores the constraints of atom a's group (the slots were zeroed by their owners).  Displacements, not
+// positions, travel through shared memory: the velocity correction d / dt keeps its relative precision.
+// With multipliers l_k along the old bond vectors s_k = x_p(t) - x_hk(t):
+//   d_p = w_p sum_k l_k s_k,  d_hk = -w_hk l_k s_k,  r_k(l) = u_k + d_p - d_hk,  sigma_k = |r_k|^2 - d_k^2 = 0.
+template <int K>
+__device__ __forceinline__ bool shake_group(const Smem& S, const DevTopo& T, int gi) {
+  const int4 g = __ldg(T.cgroup + gi);  // (parent | n << 8, h0, h1, h2)
+  const float4 d2v = __ldg(T.cdist2 + gi), wv = __ldg(T.cweight + gi);
+  const int p = g.x & 0xff, n = g.x >> 8;
+  const int h[3] = {g.y, g.z, g.w};
+  const float d2[3] = {d2v.x, d2v.y, d2v.z};
+  const float wp = wv.x, whv[3] = {wv.y, wv.z, wv.w};
+  const float4 po = S.pos[p];
+  const float pnx = S.sx[p], pny = S.sx[kMaxAtoms + p], pnz = S.sx[2 * kMaxAtoms + p];
+  float wh[K], sx[K], sy[K], sz[K], ux[K], uy[K], uz[K], lam[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const int a = k < n ? h[k] : p;  // an unused row degenerates to s = u = 0 and is given the identity below
+    const float4 ho = S.pos[a];
+    wh[k] = whv[k];
+    sx[k] = po.x - ho.x; sy[k] = po.y - ho.y; sz[k] = po.z - ho.z;
+    ux[k] = pnx - S.sx[a]; uy[k] = pny - S.sx[kMaxAtoms + a]; uz[k] = pnz - S.sx[2 * kMaxAtoms + a];
+    lam[k] = 0.0f;
+  }
+  float dpx = 0.0f, dpy = 0.0f, dpz = 0.0f;
+#pragma unroll
+  for (int it = 0; it < kShakeNewtonIters; ++it) {
+    float A[K][K], b[K], rx[K], ry[K], rz[K], dl[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      rx[k] = fmaf(wh[k] * lam[k], sx[k], ux[k] + dpx);
+      ry[k] = fmaf(wh[k] * lam[k], sy[k], uy[k] + dpy);
+      rz[k] = fmaf(wh[k] * lam[k], sz[k], uz[k] + dpz);
+      b[k] = k < n ? d2[k] - (rx[k] * rx[k] + ry[k] * ry[k] + rz[k] * rz[k]) : 0.0f;
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k)
+#pragma unroll
+      for (int l = 0; l < K; ++l) {
+        const float sr = rx[k] * sx[l] + ry[k] * sy[l] + rz[k] * sz[l];
+        A[k][l] = 2.0f * sr * (k == l ? wp + wh[k] : wp);
+        if (k >= n || l >= n) A[k][l] = k == l ? 1.0f : 0.0f;
+      }
+    solve_k<K>(A, b, dl);
+    dpx = 0.0f; dpy = 0.0f; dpz = 0.0f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      lam[k] += dl[k];
+      dpx = fmaf(wp * lam[k], sx[k], dpx); dpy = fmaf(wp * lam[k], sy[k], dpy); dpz = fmaf(wp * lam[k], sz[k], dpz);
+    }
+  }
+  bool ok = true;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    if (k < n) {
+      const float hx = -wh[k] * lam[k] * sx[k], hy = -wh[k] * lam[k] * sy[k], hz = -wh[k] * lam[k] * sz[k];
+      const float rx = ux[k] + (dpx - hx), ry = uy[k] + (dpy - hy), rz = uz[k] + (dpz - hz);
+      ok = ok && fabsf(d2[k] - (rx * rx + ry * ry + rz * rz)) <= kShakeTol * d2[k];
+      S.vel[h[k]] = make_float4(hx, hy, hz, 0.0f);
+    }
+  }
+  S.vel[p] = make_float4(dpx, dpy, dpz, 0.0f);
+  return ok;
+}
+
+// In: S.pos = x(t + dt) (constraints hold), S.vel = v after the second half kick.  Out: S.vel without the
+// components along the rigid bonds:  v_p -= w_p sum_l m_l r_l,  v_hk += w_hk m_k r_k  with
+//   sum_l m_l (w_p r_k.r_l + delta_kl w_hk r_k.r_k) = r_k.(v_p - v_hk).
+template <int K>
+__device__ __forceinline__ void rattle_group(const Smem& S, const DevTopo& T, int gi) {
+  const int4 g = __ldg(T.cgroup + gi);
+  const float4 wv = __ldg(T.cweight + gi);
+  const int p = g.x & 0xff, n = g.x >> 8;
+  const int h[3] = {g.y, g.z, g.w};
+  const float wp = wv.x, whv[3] = {wv.y, wv.z, wv.w};
+  const float4 pp = S.pos[p];
+  float4 vp = S.vel[p];
+  float wh[K], rx[K], ry[K], rz[K], vx[K], vy[K], vz[K], A[K][K], b[K], mu[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const int a = k < n ? h[k] : p;
+    const float4 hp = S.pos[a], hv = S.vel[a];
+    wh[k] = whv[k];
+    rx[k] = pp.x - hp.x; ry[k] = pp.y - hp.y; rz[k] = pp.z - hp.z;
+    vx[k] = hv.x; vy[k] = hv.y; vz[k] = hv.z;
+    b[k] = rx[k] * (vp.x - vx[k]) + ry[k] * (vp.y - vy[k]) + rz[k] * (vp.z - vz[k]);
+  }
+#pragma unroll
+  for (int k = 0; k < K; ++k)
+#pragma unroll
+    for (int l = 0; l < K; ++l) {
+      const float rr = rx[k] * rx[l] + ry[k] * ry[l] + rz[k] * rz[l];
+      A[k][l] = rr * (k == l ? wp + wh[k] : wp);
+      if (k >= n || l >= n) A[k][l] = k == l ? 1.0f : 0.0f;
+    }
+  solve_k<K>(A, b, mu);
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    if (k < n) {
+      vp.x = fmaf(-wp * mu[k], rx[k], vp.x); vp.y = fmaf(-wp * mu[k], ry[k], vp.y); vp.z = fmaf(-wp * mu[k], rz[k], vp.z);
+      S.vel[h[k]] = make_float4(fmaf(wh[k] * mu[k], rx[k], vx[k]), fmaf(wh[k] * mu[k], ry[k], vy[k]),
+                                fmaf(wh[k] * mu[k], rz[k], vz[k]), 0.0f);
+    }
+  }
+  S.vel[p] = vp;
+}
+
 // ---- block reduction of the first NOBS FP64 accumulators (fixed order); thread 0 ends with the totals -------
 template <int NOBS>
 __device__ __forceinline__ void reduce_energies(const Smem& S, Energies& E, int warp, int lane) {

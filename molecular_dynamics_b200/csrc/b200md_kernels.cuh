@@ -69,6 +69,14 @@ struct DevTopo {
   uint2 kend8_e[kWarps];  // the same for tasks_e
   uint2 kend8[kWarps];    // per warp: end index of the k-th run of its kind-sorted task list, one byte per kind
   int smem_bytes, smem_bytes_fixed;
+  // rigid X-H bonds (b200md_integrate_opts.rigid_bonds): star groups, one per heavy atom that carries hydrogens,
+  // sorted by size (largest first) and handled by thread g of the CTA
+  const int4* cgroup;     // [128] (parent | nH << 8, h0, h1, h2)
+  const float4* cdist2;   // [128] squared lengths of the group's constraints
+  const float4* cweight;  // [128] 1 / mass of the parent and of its hydrogens
+  int ncons;              // total; -1: a group the kernel cannot hold (see include/b200md.h)
+  int ngroups;
+  uint32_t cnmax;         // byte w: largest group among the lanes of warp w (selects the 1 x 1 or 3 x 3 solve)
 };
 
 struct ForceParams {

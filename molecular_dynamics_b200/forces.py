@@ -58,11 +58,13 @@ def _integrate_op(pos: torch.Tensor, vel: torch.Tensor, forces: torch.Tensor, bo
                   observables: torch.Tensor, snapshots: torch.Tensor, status: torch.Tensor, handle: int, terms: int,
                   cutoff: float, rfa: bool, eps: float, switch_dist: float, smd_on: bool, smd_a1: int, smd_a2: int,
                   smd_fk: float, smd_c0: float, smd_rate: float, dt: float, gamma: float, temperature: float,
-                  seed: int, step0: int, replica0: int, nsteps: int, energy_every: int, snapshot_every: int) -> None:
+                  seed: int, step0: int, replica0: int, nsteps: int, energy_every: int, snapshot_every: int,
+                  rigid_bonds: bool = False) -> None:
     lib = _cabi.load_library()
     fo = _cabi.ForceOpts(terms, cutoff, int(rfa), eps, switch_dist)
     so = _cabi.SmdOpts(int(smd_on), smd_a1, smd_a2, smd_fk, smd_c0, smd_rate, None)
-    io = _cabi.IntegrateOpts(dt, gamma, temperature, seed, step0, replica0, nsteps, energy_every, snapshot_every)
+    io = _cabi.IntegrateOpts(dt, gamma, temperature, seed, step0, replica0, nsteps, energy_every, snapshot_every,
+                             int(rigid_bonds))
     snaps = _ptr(snapshots) if snapshots.numel() else None
     _check(lib.b200md_integrate(C.c_void_p(handle), C.byref(fo), C.byref(so), C.byref(io), pos.shape[0], _ptr(pos),
                                 _ptr(vel), _ptr(forces), _ptr(box), _ptr(observables), snaps, _ptr(status),

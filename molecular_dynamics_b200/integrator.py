@@ -75,7 +75,11 @@ class _ReplicaEnergies:
 
 
 class Integrator:
-    def __init__(self, systems, forces, timestep, device=None, gamma=None, T=None, seed=0):
+    def __init__(self, systems, forces, timestep, device=None, gamma=None, T=None, seed=0, rigid_bonds=False):
+        """Upstream's signature plus ``seed`` (counter-based RNG) and ``rigid_bonds``: hold every bond with a hydrogen
+        end at its equilibrium length (NAMD ``rigidBonds all``, the setting of the reference's data generator, which
+        is what allows its 2 fs step): SHAKE / RATTLE inside the fused kernel.  The start structure should satisfy
+        the constraints (the first step projects it onto them otherwise, at the price of a velocity kick)."""
         self.dt = timestep / TIMEFACTOR
         self.systems = systems
         self.forces = forces
@@ -96,6 +100,8 @@ class Integrator:
         self.smd_work = None  # (R,) float64: work done by the moving SMD restraint over all step() calls so far
         self.snapshots = None  # (nsnap, R, natoms, 3) float32 when snapshot_every > 0
         self.check_nan = True
+        self.rigid_bonds = bool(rigid_bonds)
+        self.num_constraints = 0  # known after the first step(): rigid bonds held, 3 N - this degrees of freedom
 
     def step(self, niter=1):
         s, f = self.systems, self.forces
@@ -131,12 +137,19 @@ class Integrator:
         torch.ops.b200md.integrate(pos, vel, frc, box, obs, snaps, status, f._handle(dev), *f._opts(), smd[0], smd[1],
                                    smd[2], smd[3], smd_c0, smd[5], float(self.dt), float(self.gamma),
                                    float(self.T) if self.T else 0.0, self.seed, self.step_count, self.replica0,
-                                   int(niter), int(energy_every), int(self.snapshot_every))
+                                   int(niter), int(energy_every), int(self.snapshot_every), self.rigid_bonds)
         self.step_count += int(niter)
+        if self.rigid_bonds:
+            import ctypes
+
+            self.num_constraints = max(0, _cabi.load_library().b200md_topology_num_constraints(ctypes.c_void_p(f._handle(dev))))
         if self.check_nan:
             flags = int(status.max().item()) if R else 0
             if flags & _cabi.FLAG_NAN_POS:
                 raise RuntimeError("Found NaN coordinates.")
+            if flags & _cabi.FLAG_CONSTRAINT:
+                raise RuntimeError("SHAKE / RATTLE did not converge for a hydrogen group: the rigid bonds were far from "
+                                   "their lengths (start from a constrained structure or reduce the timestep)")
             if flags & _cabi.FLAG_FORCE_RANGE:
                 raise RuntimeError("the bonded force on an atom exceeded 4096 kcal/mol/A: the fused integrator accumulates "
                                    "bonded forces in 2^-17 fixed point and the system has blown up (reduce the timestep "
@@ -154,6 +167,8 @@ class Integrator:
         last = obs[-1]
         Ekin = last[:, _cabi.OBS_EKIN].cpu().numpy()
         T = kinetic_to_temp(Ekin, N)
+        if self.num_constraints:  # each rigid bond removes a degree of freedom
+            T = T * (3.0 * N / (3.0 * N - self.num_constraints))
         keys = list(f.energies) + ["external"]
         cols = [_cabi.energy_slot(k) for k in keys]
         pot = last[:, cols].sum(dim=1).to(pos.dtype)

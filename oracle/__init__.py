@@ -104,7 +104,7 @@ def forces(packed: "_cabi.PackedTopology", pos, box=None, smd=None, smd_centers=
 
 
 def integrate(packed, pos, vel, forces_in, nsteps, dt, gamma=0.0, temperature=0.0, seed=0, step0=0, replica0=0,
-              energy_every=0, snapshot_every=0, box=None, smd=None, **fopts):
+              energy_every=0, snapshot_every=0, box=None, smd=None, rigid_bonds=False, **fopts):
     """Integrator.step(nsteps) in FP64.  Returns dict(pos, vel, forces, observables, snapshots)."""
     p = np.array(pos, dtype=np.float64, order="C")
     v = np.array(vel, dtype=np.float64, order="C")
@@ -116,7 +116,7 @@ def integrate(packed, pos, vel, forces_in, nsteps, dt, gamma=0.0, temperature=0.
     obs = np.zeros((nrep, R, _cabi.NUM_OBSERVABLES), dtype=np.float64)
     snaps = np.zeros((nsnap, R, N, 3), dtype=np.float64) if nsnap else None
     io = _cabi.IntegrateOpts(float(dt), float(gamma), float(temperature), int(seed), int(step0), int(replica0),
-                             int(nsteps), int(energy_every), int(snapshot_every))
+                             int(nsteps), int(energy_every), int(snapshot_every), int(bool(rigid_bonds)))
     fo, so = force_opts(**fopts), smd_opts(smd)
     rc = lib().oracle_integrate(C.byref(packed.desc), C.byref(fo), C.byref(so), C.byref(io), R, _ptr(p), _ptr(v),
                                 _ptr(f), _ptr(box), _ptr(obs), _ptr(snaps))

@@ -333,6 +333,76 @@ void oracle_normal3(uint64_t seed, uint64_t replica, uint32_t atom, uint64_t ste
   n[2] = r1 * cos(2.0 * M_PI * u3);
 }
 
+/* Rigid X-H bonds (b200md_integrate_opts.rigid_bonds; NAMD "rigidBonds all" of the reference's data generator,
+ * All_ML_Training_Data/210905_SMD_decaalanine/SMD/output/N/smd.namd).  No code of the reference implements this
+ * (NAMD is an external program): the constraint SET follows the rule stated in include/b200md.h, the algorithm is
+ * textbook SHAKE (Ryckaert, Ciccotti, Berendsen 1977) for the positions and RATTLE (Andersen 1983) for the
+ * velocities, swept over a flat list of constraints in FP64 to a tolerance of 1e-12.  Parity "unpinned" for this
+ * option: anchored on properties (bond lengths held, energy conserved at 2 fs, the reference's own restart files
+ * satisfy the same constraint set). */
+typedef struct { int i, j; double d2; } cons_t;
+
+static int build_constraints(const b200md_topology_desc* T, cons_t* out /* [natoms] */) {
+  int n = 0;
+  for (int a = 0; a < T->natoms; ++a) {
+    if (!(T->mass[a] > 0.5f && T->mass[a] < 3.5f)) continue;
+    int best = -1;
+    for (int b = 0; b < T->nbonds; ++b)
+      if ((T->bond_idx[2 * b] == a || T->bond_idx[2 * b + 1] == a) &&
+          (best < 0 || T->bond_prm[2 * b + 1] < T->bond_prm[2 * best + 1]))
+        best = b;
+    if (best < 0) continue;
+    int other = T->bond_idx[2 * best] == a ? T->bond_idx[2 * best + 1] : T->bond_idx[2 * best];
+    double d = T->bond_prm[2 * best + 1];
+    out[n++] = (cons_t){other, a, d * d};
+  }
+  return n;
+}
+
+/* p: unconstrained x(t+dt), p_old: x(t); moves p onto the constraints, corrects v by dx/dt */
+static int shake(const cons_t* c, int nc, const float* mass, const double* p_old, double* p, double* v, double dt) {
+  for (int it = 0; it < 1000; ++it) {
+    int done = 1;
+    for (int k = 0; k < nc; ++k) {
+      const int i = c[k].i, j = c[k].j;
+      v3 r = sub(getpos(p, i), getpos(p, j)), s = sub(getpos(p_old, i), getpos(p_old, j));
+      double diff = c[k].d2 - dot(r, r);
+      if (fabs(diff) > 1e-12 * c[k].d2) {
+        done = 0;
+        double wi = 1.0 / mass[i], wj = 1.0 / mass[j];
+        double g = diff / (2.0 * dot(s, r) * (wi + wj));
+        double di[3] = {g * wi * s.x, g * wi * s.y, g * wi * s.z}, dj[3] = {-g * wj * s.x, -g * wj * s.y, -g * wj * s.z};
+        for (int x = 0; x < 3; ++x) {
+          p[3 * i + x] += di[x]; v[3 * i + x] += di[x] / dt;
+          p[3 * j + x] += dj[x]; v[3 * j + x] += dj[x] / dt;
+        }
+      }
+    }
+    if (done) return 0;
+  }
+  return 1;
+}
+
+static int rattle(const cons_t* c, int nc, const float* mass, const double* p, double* v) {
+  for (int it = 0; it < 1000; ++it) {
+    int done = 1;
+    for (int k = 0; k < nc; ++k) {
+      const int i = c[k].i, j = c[k].j;
+      v3 r = sub(getpos(p, i), getpos(p, j)), u = sub(getpos(v, i), getpos(v, j));
+      double rv = dot(r, u);
+      if (fabs(rv) > 1e-13 * c[k].d2) {
+        done = 0;
+        double wi = 1.0 / mass[i], wj = 1.0 / mass[j];
+        double g = rv / (c[k].d2 * (wi + wj));
+        v[3 * i] -= g * wi * r.x; v[3 * i + 1] -= g * wi * r.y; v[3 * i + 2] -= g * wi * r.z;
+        v[3 * j] += g * wj * r.x; v[3 * j + 1] += g * wj * r.y; v[3 * j + 2] += g * wj * r.z;
+      }
+    }
+    if (done) return 0;
+  }
+  return 1;
+}
+
 /* Integrator.step(niter) of upstream TorchMD, FP64 state.
  * pos/vel/forces double [R][N][3] in/out (forces must be valid at entry), box float [R][9] or NULL.
  * observables double [nreports][R][11] as in b200md_integrate; snapshots double [nsnap][R][N][3]. */
@@ -346,13 +416,18 @@ int oracle_integrate(const b200md_topology_desc* T, const b200md_force_opts* O, 
   const int nsnap = I->snapshot_every > 0 ? I->nsteps / I->snapshot_every : 0;
   (void)nrep;
   (void)nsnap;
+  cons_t* cons = (cons_t*)malloc(sizeof(cons_t) * (size_t)(N > 0 ? N : 1));
+  const int ncons = I->rigid_bonds ? build_constraints(T, cons) : 0;
+  int failed = 0;
 #pragma omp parallel for schedule(static)
   for (int64_t r = 0; r < R; ++r) {
     double *p = pos + r * 3 * N, *v = vel + r * 3 * N, *f = forces + r * 3 * N;
     double b9[9], e[B200MD_NUM_ENERGIES], work = 0.0;
+    double* p_old = ncons ? (double*)malloc(sizeof(double) * 3 * (size_t)N) : NULL;
     if (box) for (int k = 0; k < 9; ++k) b9[k] = box[r * 9 + k];
     for (int s = 0; s < I->nsteps; ++s) {
       const uint64_t gstep = I->step0 + (uint64_t)s;
+      if (ncons) memcpy(p_old, p, sizeof(double) * 3 * (size_t)N);
       for (int a = 0; a < N; ++a) { /* _first_VV */
         double m = T->mass[a];
         for (int c = 0; c < 3; ++c) {
@@ -361,6 +436,7 @@ int oracle_integrate(const b200md_topology_desc* T, const b200md_force_opts* O, 
           v[3 * a + c] += 0.5 * dt * acc;
         }
       }
+      if (ncons && shake(cons, ncons, T->mass, p_old, p, v, dt)) failed = 1;
       /* SMD centre of the step whose forces are being computed: c0 + rate * (global step + 1) */
       double center = (S && S->enabled) ? (double)S->center0 + (double)S->center_rate * (double)(gstep + 1) : 0.0;
       forces_one(T, O, S, center, p, box ? b9 : NULL, f, e);
@@ -374,14 +450,14 @@ int oracle_integrate(const b200md_topology_desc* T, const b200md_force_opts* O, 
           for (int c = 0; c < 3; ++c) v[3 * a + c] += -gamma * v[3 * a + c] * dt + vc * n3[c];
         }
       }
-      double ekin = 0.0;
       for (int a = 0; a < N; ++a) { /* _second_VV */
         double m = T->mass[a];
-        for (int c = 0; c < 3; ++c) {
-          v[3 * a + c] += 0.5 * dt * f[3 * a + c] / m;
-          ekin += 0.5 * m * v[3 * a + c] * v[3 * a + c];
-        }
+        for (int c = 0; c < 3; ++c) v[3 * a + c] += 0.5 * dt * f[3 * a + c] / m;
       }
+      if (ncons && rattle(cons, ncons, T->mass, p, v)) failed = 1;
+      double ekin = 0.0;
+      for (int a = 0; a < N; ++a)
+        for (int c = 0; c < 3; ++c) ekin += 0.5 * (double)T->mass[a] * v[3 * a + c] * v[3 * a + c];
       const int last = (s == I->nsteps - 1);
       int report = I->energy_every > 0 ? ((s + 1) % I->energy_every == 0) : last;
       if (report && observables) {
@@ -397,6 +473,8 @@ int oracle_integrate(const b200md_topology_desc* T, const b200md_force_opts* O, 
         memcpy(snapshots + ((int64_t)slot * R + r) * 3 * N, p, sizeof(double) * 3 * (size_t)N);
       }
     }
+    free(p_old);
   }
-  return B200MD_OK;
+  free(cons);
+  return failed ? B200MD_ERR_UNSUPPORTED : B200MD_OK;
 }

@@ -609,3 +609,116 @@ def test_chamber_fused_integrator_short_horizon_vs_oracle():
     np.testing.assert_allclose(obs[:, :, :8].sum(-1), out["observables"][:, :, :8].sum(-1), rtol=2e-5, atol=2e-3)
     k = _cabi.energy_slot("impropers")
     np.testing.assert_allclose(obs[:, :, k], out["observables"][:, :, k], rtol=2e-3, atol=1e-3)
+
+
+class _Restart:
+    """ALA10 from the CHAMBER prmtop as the reference loads it, started from the reference's own NAMD restart of
+    replica 3 (rigidBonds ALL: all 53 X-H bonds at their lengths, 300 K velocities)."""
+
+    def __init__(self, R=4):
+        from molecular_dynamics_b200.parameters import parameters_from_prmtop
+        from molecular_dynamics_b200.topology_io import read_namd_bin
+
+        gold = os.path.join(os.path.dirname(__file__), "golden")
+        self.par = parameters_from_prmtop(os.path.join(gold, "full_da-1.3.prmtop"), precision=torch.float64)
+        x = read_namd_bin(os.path.join(gold, "smd_out.restart.coor"))
+        v = read_namd_bin(os.path.join(gold, "smd_out.restart.vel"))
+        rng = np.random.default_rng(4)
+        self.pos = np.repeat(x[None], R, 0).astype(np.float32)
+        self.vel = (v[None] * (1.0 + 0.2 * rng.standard_normal((R, 1, 1)))).astype(np.float32)
+        self.vel[0] = v
+        self.ava_idx = _cabi.make_pair_index(self.par.natoms, self.par.get_exclusions())
+        self.packed = _cabi.PackedTopology(self.par, self.ava_idx)
+        b, m = self.par.bonds.numpy(), self.par.masses.numpy().ravel()
+        xh = (m[b[:, 0]] < 1.5) | (m[b[:, 1]] < 1.5)
+        self.xh = b[xh]
+        self.req = self.par.bond_params.numpy()[xh, 1].astype(np.float32).astype(np.float64)
+
+    def bond_error(self, pos):
+        """max |r - req| over the rigid bonds, in units of the fp32 spacing of the largest coordinate (the restart is
+        not centred: coordinates reach 40 A, where a float resolves 3.8e-6 A)."""
+        p = np.asarray(pos, dtype=np.float64)
+        err = np.abs(np.linalg.norm(p[:, self.xh[:, 0]] - p[:, self.xh[:, 1]], axis=-1) - self.req).max()
+        return err / float(np.spacing(np.float32(np.abs(p).max())))
+
+
+@pytest.mark.parametrize("mode", sorted(MODES))
+def test_rigid_bonds_short_horizon_vs_oracle(mode):
+    """SURVEY 8f N4 (constraints): SHAKE / RATTLE in the fused kernel against the FP64 oracle, 2 fs steps."""
+    g = _Restart()
+    par, s = make_system(g, g.pos, g.vel)
+    F = Forces(par, **MODES[mode])
+    F.compute_batch(s.pos, s.box, s.forces)
+    f0 = s.forces.cpu().numpy().astype(np.float64)
+    integ = Integrator(s, F, timestep=2.0, device=DEV, rigid_bonds=True)
+    integ.energy_every = 10
+    ekin, pot, T = integ.step(niter=40)
+    assert integ.num_constraints == 53
+    out = oracle.integrate(g.packed, g.pos, g.vel, f0, nsteps=40, dt=np.float32(integ.dt), energy_every=10,
+                           rigid_bonds=True, **MODES[mode])
+    assert np.abs(s.pos.cpu().numpy() - out["pos"]).max() < 5e-4
+    assert np.abs(s.vel.cpu().numpy() - out["vel"]).max() < 5e-3 * np.abs(out["vel"]).max()
+    assert g.bond_error(s.pos.cpu().numpy()) < 3.0  # a few spacings of the stored fp32 coordinates
+    obs = integ.observables.cpu().numpy()
+    np.testing.assert_allclose(obs[:, :, _cabi.OBS_EKIN], out["observables"][:, :, _cabi.OBS_EKIN], rtol=1e-3)
+    np.testing.assert_allclose(obs[:, :, :8].sum(-1), out["observables"][:, :, :8].sum(-1), rtol=2e-5, atol=5e-3)
+    # temperature over 3 N - 53 degrees of freedom
+    np.testing.assert_allclose(T, 2.0 * ekin / ((3 * 104 - 53) * 0.001987191), rtol=1e-6)
+    # velocities carry no component along the rigid bonds
+    v, x = s.vel.cpu().numpy().astype(np.float64), s.pos.cpu().numpy().astype(np.float64)
+    rv = ((x[:, g.xh[:, 0]] - x[:, g.xh[:, 1]]) * (v[:, g.xh[:, 0]] - v[:, g.xh[:, 1]])).sum(-1)
+    assert np.abs(rv).max() < 2e-5
+
+
+def test_rigid_bonds_2fs_langevin_and_energy_conservation():
+    g = _Restart(R=256)
+    # NVE, 2 fs, 5 000 steps = 10 ps: bonds held, total energy without drift beyond the integrator's own fluctuation
+    par, s = make_system(g, g.pos, g.vel)
+    F = Forces(par)
+    F.compute_batch(s.pos, s.box, s.forces)
+    integ = Integrator(s, F, timestep=2.0, device=DEV, rigid_bonds=True)
+    integ.energy_every = 50
+    integ.step(niter=5000)
+    assert g.bond_error(s.pos.cpu().numpy()) < 3.0
+    obs = integ.observables.cpu().numpy()
+    etot = obs[:, :, :8].sum(-1) + obs[:, :, _cabi.OBS_EKIN]
+    drift = np.abs(etot[-20:].mean(0) - etot[:20].mean(0))
+    assert np.median(drift) < 0.5 and drift.max() < 2.0, (np.median(drift), drift.max())
+    # Langevin at 300 K, 2 fs: the thermostat temperature is reached over 3 N - 53 degrees of freedom
+    par, s = make_system(g, g.pos, g.vel)
+    F = Forces(par)
+    F.compute_batch(s.pos, s.box, s.forces)
+    integ = Integrator(s, F, timestep=2.0, device=DEV, gamma=5.0, T=300.0, seed=3, rigid_bonds=True)
+    integ.energy_every = 50
+    integ.step(niter=1000)
+    temps = []
+    for _ in range(4):
+        temps.append(integ.step(niter=500)[2])
+    assert abs(np.mean(temps) - 300.0) < 8.0, np.mean(temps)
+    assert g.bond_error(s.pos.cpu().numpy()) < 3.0
+
+
+def test_rigid_bonds_is_a_noop_without_hydrogens_and_refuses_unsupported_groups():
+    g = load_golden("bb40")
+    pos0 = g["frames"][:4]
+    vel0 = (0.05 * np.random.default_rng(1).standard_normal(pos0.shape)).astype(np.float32)
+    res = []
+    for rigid in (False, True):
+        par, s = make_system(g, pos0, vel0)
+        F = Forces(par)
+        F.compute_batch(s.pos, s.box, s.forces)
+        integ = Integrator(s, F, timestep=1.0, device=DEV, rigid_bonds=rigid)
+        integ.step(niter=20)
+        res.append(s.pos.cpu().numpy())
+    np.testing.assert_array_equal(res[0], res[1])
+    # a hydrogen hanging on a hydrogen-mass atom is not a group the kernel holds: refused, not mis-integrated
+    g = _Restart(R=2)
+    m = g.par.masses.numpy().ravel()
+    parent = int(g.xh[0, 0] if m[g.xh[0, 0]] > 1.5 else g.xh[0, 1])
+    g.par.masses[parent] = 1.008
+    par, s = make_system(g, g.pos, g.vel)
+    F = Forces(par)
+    F.compute_batch(s.pos, s.box, s.forces)
+    integ = Integrator(s, F, timestep=2.0, device=DEV, rigid_bonds=True)
+    with pytest.raises(NotImplementedError, match="rigid_bonds"):
+        integ.step(niter=2)
