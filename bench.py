@@ -369,6 +369,26 @@ def run_ours(args):
         integ3.energy_every, integ3.check_nan = args.energy_every, False
         t3 = timed(lambda: integ3.step(niter=nst), 2)
         extra["langevin_smd"] = {"value": R * nst / t3, "unit": "replica-steps/s", "replicas": R, "md_steps_per_launch": nst}
+        # the ML callers' loss (cgan.py:345-360): per-term energies + torsion angles of a generated batch, forward and
+        # backward through the batched Energy adapter (the reference rebuilds an Energy object per sample: 41-105
+        # evaluations/s on a V100)
+        from molecular_dynamics_b200 import Energy
+        colvar = {"name": "E2End Harm", "fk": 1.0, "cent_0": 12.0, "cent_1": 34.0, "T": 1.0, "group1": [3], "group2": [98]}
+        en = Energy(parameters=par, colvar=colvar, device=dev)
+        en.forces.check_nan = False
+        B5 = 4096
+        x5 = torch.tensor(pos_h[:B5] if len(pos_h) >= B5 else np.resize(pos_h, (B5, 104, 3)), device=dev).requires_grad_(True)
+        t5 = torch.linspace(0.0, 1.0, B5, device=dev)
+
+        def adapter_step():
+            x5.grad = None
+            ene, phis = en.calc_energy_batch(x5, t5)
+            loss = sum(v for k, v in ene.items() if k != "E2End Harm").sum() / B5 + 200.0 * ene["E2End Harm"].sum() / B5
+            loss.backward()
+
+        t5s = timed(adapter_step, 5)
+        extra["energy_adapter_forward_backward"] = {"value": B5 / t5s, "unit": "conformers/s", "batch": B5,
+                                                    "ms_per_batch": 1e3 * t5s, "launches_per_batch": 4}
         # the data generator's own protocol (smd.namd: rigidBonds ALL, 2 fs, Langevin 300 K, SMD): SHAKE / RATTLE in the kernel
         sys4 = System(104, R, torch.float, dev)
         sys4.pos[:] = torch.tensor(pos_h, device=dev)

@@ -203,6 +203,18 @@ int b200md_integrate(const b200md_topology* topo, const b200md_force_opts* fopts
                      int64_t nreplicas, float* pos, float* vel, float* forces, const float* box,
                      double* observables, float* snapshots, uint32_t* status, void* stream);
 
+/* Energy.calc_phi of the ML callers (cGAN/cGAN_D_pos-2.3.2/cgan.py:166-207; the angle of forces.py:541-552):
+ * phi[r][d] = -atan2(sin, cos) of proper dihedral par.dihedrals[d], for every replica; minimum image with the box
+ * diagonal when it is not zero.  pos DEVICE float [R][natoms][3], box DEVICE float [R][9] or NULL,
+ * phi DEVICE float [R][ndihedrals]. */
+int b200md_topology_ndihedrals(const b200md_topology* topo);
+int b200md_dihedral_angles(const b200md_topology* topo, int64_t nreplicas, const float* pos, const float* box,
+                           float* phi, void* stream);
+/* its backward for autograd (cgan.py:351-360 differentiates through the Energy adapter):
+ * grad_pos[r][a][:] = sum_d grad_phi[r][d] * d phi[r][d] / d pos[r][a]; at most 512 dihedrals. */
+int b200md_dihedral_angles_backward(const b200md_topology* topo, int64_t nreplicas, const float* pos, const float* box,
+                                    const float* grad_phi, float* grad_pos, void* stream);
+
 /* Host-buffer convenience (the end-to-end call a non-torch host would make): copies pos in,
  * runs b200md_forces_compute, copies forces/energies out; synchronous. */
 int b200md_forces_compute_host(const b200md_topology* topo, const b200md_force_opts* opts,

@@ -6,6 +6,7 @@ mirrors ``torchmd.forces.Forces`` / ``torchmd.systems.System`` (the reference's 
 upstream ``torchmd.integrator``.  The compute path is libb200md.so (hand-written sm_100a CUDA behind the
 C-ABI of include/b200md.h); importing this package never imports the CPU oracle.
 """
+from .energy import Energy
 from .forces import Forces, SMDBias
 from .integrator import BOLTZMAN, TIMEFACTOR, Integrator, kinetic_energy, kinetic_to_temp, maxwell_boltzmann
 from .parameters import Parameters, parameters_from_prmtop, parameters_from_psf_yaml
@@ -15,7 +16,7 @@ from .sharding import gather_observables, jarzynski_free_energy, shard_range
 from .utils import LogWriter, TrajectoryWriter, load_checkpoint, read_colvars_traj, save_checkpoint, write_colvars_traj
 from .wrapper import Wrapper
 
-__all__ = ["Forces", "SMDBias", "System", "Integrator", "maxwell_boltzmann", "kinetic_energy", "kinetic_to_temp",
+__all__ = ["Forces", "SMDBias", "Energy", "System", "Integrator", "maxwell_boltzmann", "kinetic_energy", "kinetic_to_temp",
            "Parameters", "parameters_from_prmtop", "parameters_from_psf_yaml", "TIMEFACTOR", "BOLTZMAN", "minimize_bfgs",
            "minimize_fire", "LogWriter", "TrajectoryWriter", "save_checkpoint", "load_checkpoint", "Wrapper",
            "write_colvars_traj", "read_colvars_traj", "jarzynski_free_energy", "gather_observables", "shard_range"]

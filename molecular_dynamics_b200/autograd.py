@@ -57,12 +57,23 @@ class _EnergyFunction(torch.autograd.Function):
         b = box.to(device=pos.device, dtype=torch.float32).contiguous()
         grad = torch.zeros_like(pos)
         tmp = torch.empty_like(pos)
+        # columns that carry the same weight on every replica share a launch: the ML callers' loss
+        # sum(terms) + 200 * E2End (cgan.py:351-353) needs two, not one per column
+        groups = []
         for c in cols:
-            if c == 7:
-                fobj._launch(pos, b, tmp, terms_mask=0, with_smd=True)
+            for grp in groups:
+                if torch.equal(g[:, c], g[:, grp[0]]):
+                    grp.append(c)
+                    break
             else:
-                fobj._launch(pos, b, tmp, terms_mask=_COLUMN_TERMS[c](mask), with_smd=False)
-            grad -= g[:, c:c + 1, None] * tmp
+                groups.append([c])
+        for grp in groups:
+            tmask = 0
+            for c in grp:
+                if c != 7:
+                    tmask |= _COLUMN_TERMS[c](mask)
+            fobj._launch(pos, b, tmp, terms_mask=tmask, with_smd=7 in grp)
+            grad -= g[:, grp[0]:grp[0] + 1, None] * tmp
         return grad.to(ctx.in_dtype), None, None, None
 
 
@@ -80,3 +91,21 @@ def energies_with_grad(fobj, pos, box, forces):
         col[:, 7] = ext_ene.reshape(-1).to(ene.dtype) - ext_ene.detach().reshape(-1).to(ene.dtype)
         ene = ene + col
     return ene
+
+
+class _DihedralAngles(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pos, fobj, box):
+        p = pos.detach().contiguous()
+        ctx.fobj, ctx.box = fobj, box
+        ctx.save_for_backward(p)
+        return fobj._phi_launch(p, box)
+
+    @staticmethod
+    def backward(ctx, g):
+        (p,) = ctx.saved_tensors
+        return ctx.fobj._phi_launch(p, ctx.box, grad_phi=g.to(torch.float32).contiguous()), None, None
+
+
+def dihedral_angles_with_grad(fobj, pos, box):
+    return _DihedralAngles.apply(pos, fobj, box)

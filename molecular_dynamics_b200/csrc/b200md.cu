@@ -256,6 +256,105 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
   }
 }
 
+// ---- Energy.calc_phi (cGAN/cGAN_D_pos-2.3.2/cgan.py:166-207, the angle of forces.py:541-552) -------------------
+// One CTA per replica: positions staged in shared memory by coalesced loads, lane d evaluates dihedral d, output
+// rows are written coalesced.  HBM-bound: 12 N bytes in, 4 ndihedrals out per replica.
+struct PhiGeom {
+  float ax, ay, az, bx, by, bz;      // crossA = r12 x r23, crossB = r23 x r34
+  float r12x, r12y, r12z, r23x, r23y, r23z, r34x, r34y, r34z;
+};
+
+__device__ __forceinline__ float wrap_scalar(float d, float b) { return b != 0.0f ? d - b * rintf(d / b) : d; }
+
+__device__ __forceinline__ PhiGeom phi_geometry(const float4* pos, uchar4 q, const float* bx) {
+  const float4 p0 = pos[q.x], p1 = pos[q.y], p2 = pos[q.z], p3 = pos[q.w];
+  PhiGeom g;
+  g.r12x = wrap_scalar(p0.x - p1.x, bx[0]); g.r12y = wrap_scalar(p0.y - p1.y, bx[1]); g.r12z = wrap_scalar(p0.z - p1.z, bx[2]);
+  g.r23x = wrap_scalar(p1.x - p2.x, bx[0]); g.r23y = wrap_scalar(p1.y - p2.y, bx[1]); g.r23z = wrap_scalar(p1.z - p2.z, bx[2]);
+  g.r34x = wrap_scalar(p2.x - p3.x, bx[0]); g.r34y = wrap_scalar(p2.y - p3.y, bx[1]); g.r34z = wrap_scalar(p2.z - p3.z, bx[2]);
+  g.ax = g.r12y * g.r23z - g.r12z * g.r23y; g.ay = g.r12z * g.r23x - g.r12x * g.r23z; g.az = g.r12x * g.r23y - g.r12y * g.r23x;
+  g.bx = g.r23y * g.r34z - g.r23z * g.r34y; g.by = g.r23z * g.r34x - g.r23x * g.r34z; g.bz = g.r23x * g.r34y - g.r23y * g.r34x;
+  return g;
+}
+
+__device__ __forceinline__ void stage_replica(float4* spos, float* sbox, const float* pos, const float* box, long long r,
+                                              int N, int tid) {
+  if (tid < N) {
+    const long long base = (r * N + tid) * 3;
+    spos[tid] = make_float4(pos[base], pos[base + 1], pos[base + 2], 0.0f);
+  }
+  if (tid < 3) sbox[tid] = box ? __ldg(box + r * 9 + 4 * tid) : 0.0f;
+  // forces.py:359 / cgan.py:185: a box of zeros is vacuum; the reference wraps with every component otherwise
+}
+
+__global__ void __launch_bounds__(kThreads) dihedral_angles_kernel(const DevTopo T, const long long R,
+                                                                   const float* __restrict__ pos,
+                                                                   const float* __restrict__ box, float* __restrict__ phi) {
+  __shared__ float4 spos[kMaxAtoms];
+  __shared__ float sbox[4];
+  const int tid = threadIdx.x;
+  for (long long r = blockIdx.x; r < R; r += gridDim.x) {
+    __syncthreads();
+    stage_replica(spos, sbox, pos, box, r, T.natoms, tid);
+    __syncthreads();
+    for (int d = tid; d < T.nphi; d += kThreads) {
+      const PhiGeom g = phi_geometry(spos, T.phi_idx[d], sbox);
+      // crossC = r23 x crossA;  cos = A.B / (|A||B|),  sin = C.B / (|C||B|),  phi = -atan2(sin, cos)
+      const float cx = g.r23y * g.az - g.r23z * g.ay, cy = g.r23z * g.ax - g.r23x * g.az, cz = g.r23x * g.ay - g.r23y * g.ax;
+      const float na = sqrtf(g.ax * g.ax + g.ay * g.ay + g.az * g.az), nb = sqrtf(g.bx * g.bx + g.by * g.by + g.bz * g.bz);
+      const float nc = sqrtf(cx * cx + cy * cy + cz * cz);
+      const float cosp = (g.ax * g.bx + g.ay * g.by + g.az * g.bz) / nb / na;
+      const float sinp = (cx * g.bx + cy * g.by + cz * g.bz) / nb / nc;
+      phi[r * T.nphi + d] = -atan2f(sinp, cosp);
+    }
+  }
+}
+
+// grad_pos[a] = sum over the dihedrals d that contain a of grad_phi[d] * d phi_d / d x_a.  Atom-major gather (each
+// lane recomputes the geometry of the dihedrals its atom sits in): no atomics, fixed order, bit-reproducible.
+// d phi / d x follows from the reference's torsion forces with coeff = 1 (forces.py:578-600):
+//   g0 = -|r23| / |A|^2 A,  g3 = |r23| / |B|^2 B,  s = (r12.r23 / |r23|^2) g0 - (r34.r23 / |r23|^2) g3,
+//   d phi / d x = (g0, -g0 - s, -g3 + s, g3).
+__global__ void __launch_bounds__(kThreads) dihedral_angles_backward_kernel(const DevTopo T, const long long R,
+                                                                            const float* __restrict__ pos,
+                                                                            const float* __restrict__ box,
+                                                                            const float* __restrict__ grad_phi,
+                                                                            float* __restrict__ grad_pos) {
+  __shared__ float4 spos[kMaxAtoms];
+  __shared__ float sbox[4];
+  __shared__ float sg[512];  // grad_phi row of the replica (host guarantees nphi <= 512 for this path)
+  const int tid = threadIdx.x;
+  for (long long r = blockIdx.x; r < R; r += gridDim.x) {
+    __syncthreads();
+    stage_replica(spos, sbox, pos, box, r, T.natoms, tid);
+    for (int d = tid; d < T.nphi; d += kThreads) sg[d] = grad_phi[r * T.nphi + d];
+    __syncthreads();
+    if (tid < T.natoms) {
+      float gx = 0.0f, gy = 0.0f, gz = 0.0f;
+      const int i1 = T.phi_start[tid + 1];
+      for (int i = T.phi_start[tid]; i < i1; ++i) {
+        const int item = T.phi_items[i], d = item & 0x3fff, role = item >> 14;
+        const PhiGeom g = phi_geometry(spos, T.phi_idx[d], sbox);
+        const float n23sq = g.r23x * g.r23x + g.r23y * g.r23y + g.r23z * g.r23z, n23 = sqrtf(n23sq);
+        const float f0 = -n23 / (g.ax * g.ax + g.ay * g.ay + g.az * g.az), f3 = n23 / (g.bx * g.bx + g.by * g.by + g.bz * g.bz);
+        const float g0x = f0 * g.ax, g0y = f0 * g.ay, g0z = f0 * g.az, g3x = f3 * g.bx, g3y = f3 * g.by, g3z = f3 * g.bz;
+        const float ff1 = (g.r12x * g.r23x + g.r12y * g.r23y + g.r12z * g.r23z) / n23sq;
+        const float ff2 = (g.r34x * g.r23x + g.r34y * g.r23y + g.r34z * g.r23z) / n23sq;
+        const float sx = ff1 * g0x - ff2 * g3x, sy = ff1 * g0y - ff2 * g3y, sz = ff1 * g0z - ff2 * g3z;
+        float dx, dy, dz;
+        if (role == 0) { dx = g0x; dy = g0y; dz = g0z; }
+        else if (role == 1) { dx = -g0x - sx; dy = -g0y - sy; dz = -g0z - sz; }
+        else if (role == 2) { dx = -g3x + sx; dy = -g3y + sy; dz = -g3z + sz; }
+        else { dx = g3x; dy = g3y; dz = g3z; }
+        const float w = sg[d];
+        gx = fmaf(w, dx, gx); gy = fmaf(w, dy, gy); gz = fmaf(w, dz, gz);
+      }
+      const long long base = (r * T.natoms + tid) * 3;
+      grad_pos[base] = gx; grad_pos[base + 1] = gy; grad_pos[base + 2] = gz;
+    }
+  }
+}
+
 // FP32 FMA throughput micro-benchmark (the roofline denominator): 8 independent chains per thread.
 __global__ void __launch_bounds__(256) fma_peak_kernel(float* out, int iters, float a, float b) {
   float v[8];
@@ -803,6 +902,23 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
     }
   }
 
+  // ---- proper-dihedral angle output (calc_phi) ------------------------------------------------------
+  std::vector<uchar4> phi_idx;
+  std::vector<uint16_t> phi_start(kMaxAtoms + 1, 0), phi_items;
+  T.nphi = d->ndihedrals;
+  if (T.nphi > 0x3fff) { delete topo; fail(B200MD_ERR_UNSUPPORTED, "more than 16383 dihedrals"); return nullptr; }
+  for (int q = 0; q < d->ndihedrals; ++q) {
+    const int32_t* a4 = d->dihedral_idx + 4 * q;
+    phi_idx.push_back(make_uchar4((unsigned char)a4[0], (unsigned char)a4[1], (unsigned char)a4[2], (unsigned char)a4[3]));
+  }
+  for (int a = 0; a < kMaxAtoms; ++a) {
+    phi_start[a] = (uint16_t)phi_items.size();
+    for (int q = 0; q < d->ndihedrals; ++q)
+      for (int role = 0; role < 4; ++role)
+        if (d->dihedral_idx[4 * q + role] == a) phi_items.push_back((uint16_t)(q | (role << 14)));
+  }
+  phi_start[kMaxAtoms] = (uint16_t)phi_items.size();
+
   // ---- upload --------------------------------------------------------------------------------------
   BlobBuilder B;
   const size_t o_ab = B.add(ab), o_q = B.add(charge), o_m = B.add(mass), o_ro = B.add(rowoff), o_mask = B.add(mask8), o_rot = B.add(diagmask);
@@ -813,6 +929,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   const size_t o_pi = B.add(p142_idx), o_pp = B.add(p142_ab), o_pq = B.add(p142_q), o_ps = B.add(p142_slot);
   const size_t o_gs = B.add(gstart), o_tk = B.add(tasks_v[0]), o_tke = B.add(tasks_v[1]);
   const size_t o_cg = B.add(cgroup), o_cd = B.add(cdist2), o_cw = B.add(cweight);
+  const size_t o_phi = B.add(phi_idx), o_phs = B.add(phi_start), o_phit = B.add(phi_items);
   auto cleanup = [&](const std::string& msg) { fail(B200MD_ERR_CUDA, msg); if (topo->blob) cudaFree(topo->blob); delete topo; };
   cudaError_t e = cudaSetDevice(device);
   if (e != cudaSuccess) { cleanup(std::string("cudaSetDevice: ") + cudaGetErrorString(e)); return nullptr; }
@@ -834,6 +951,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   T.gather_start = (const uint16_t*)(base + o_gs);
   T.tasks = (const uint32_t*)(base + o_tk);
   T.tasks_e = (const uint32_t*)(base + o_tke);
+  T.phi_idx = (const uchar4*)(base + o_phi); T.phi_start = (const uint16_t*)(base + o_phs); T.phi_items = (const uint16_t*)(base + o_phit);
   T.cgroup = (const int4*)(base + o_cg); T.cdist2 = (const float4*)(base + o_cd); T.cweight = (const float4*)(base + o_cw);
   T.smem_bytes = (int)smem_layout(nullptr, nullptr, NT, T.nslots, false);
   T.smem_bytes_fixed = (int)smem_layout(nullptr, nullptr, NT, T.nslots, true);
@@ -857,6 +975,35 @@ extern "C" void b200md_topology_destroy(b200md_topology* topo) {
   cudaSetDevice(topo->device);
   if (topo->blob) cudaFree(topo->blob);
   delete topo;
+}
+
+extern "C" int b200md_topology_ndihedrals(const b200md_topology* topo) { return topo ? topo->dev.nphi : -1; }
+
+extern "C" int b200md_dihedral_angles(const b200md_topology* topo, int64_t R, const float* pos, const float* box,
+                                      float* phi, void* stream) {
+  if (!topo || !pos || !phi) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
+  if (R < 0) return fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica count");
+  if (R == 0 || topo->dev.nphi == 0) return B200MD_OK;
+  CUDA_TRY(cudaSetDevice(topo->device));
+  const int grid = (int)std::min<long long>(R, (long long)topo->num_sms * 16);
+  dihedral_angles_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(topo->dev, R, pos, box, phi);
+  g_launches.fetch_add(1);
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
+}
+
+extern "C" int b200md_dihedral_angles_backward(const b200md_topology* topo, int64_t R, const float* pos, const float* box,
+                                               const float* grad_phi, float* grad_pos, void* stream) {
+  if (!topo || !pos || !grad_phi || !grad_pos) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
+  if (R < 0) return fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica count");
+  if (topo->dev.nphi > 512) return fail(B200MD_ERR_UNSUPPORTED, "dihedral-angle backward holds at most 512 dihedrals per replica");
+  if (R == 0) return B200MD_OK;
+  CUDA_TRY(cudaSetDevice(topo->device));
+  const int grid = (int)std::min<long long>(R, (long long)topo->num_sms * 16);
+  dihedral_angles_backward_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(topo->dev, R, pos, box, grad_phi, grad_pos);
+  g_launches.fetch_add(1);
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
 }
 
 extern "C" int b200md_topology_num_constraints(const b200md_topology* topo) { return topo ? topo->dev.ncons : -1; }

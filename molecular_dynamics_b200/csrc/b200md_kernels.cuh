@@ -69,6 +69,11 @@ struct DevTopo {
   uint2 kend8_e[kWarps];  // the same for tasks_e
   uint2 kend8[kWarps];    // per warp: end index of the k-th run of its kind-sorted task list, one byte per kind
   int smem_bytes, smem_bytes_fixed;
+  // proper-dihedral angle output (Energy.calc_phi of the ML callers) and its backward
+  int nphi;                      // = par.dihedrals rows
+  const uchar4* phi_idx;         // [nphi] atoms of dihedral d
+  const uint16_t* phi_start;     // [129] items of atom a are [phi_start[a], phi_start[a + 1])
+  const uint16_t* phi_items;     // [4 nphi] dihedral | role << 14 (role = position of the atom in the quadruple)
   // rigid X-H bonds (b200md_integrate_opts.rigid_bonds): star groups, one per heavy atom that carries hydrogens,
   // sorted by size (largest first) and handled by thread g of the CTA
   const int4* cgroup;     // [128] (parent | nH << 8, h0, h1, h2)

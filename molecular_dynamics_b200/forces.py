@@ -239,6 +239,37 @@ class Forces:
         self.last_energies = ene
         return ene
 
+    # -- Energy.calc_phi of the ML callers ---------------------------------------------------------
+    def dihedral_angles(self, pos, box=None):
+        """Proper-dihedral angles of every replica, (R, ndihedrals) in ``pos.dtype``, rows in ``par.dihedrals`` order
+        (``Energy.calc_phi``, cGAN/cGAN_D_pos-2.3.2/cgan.py:166-207: phi = -atan2(sin, cos) as in forces.py:541-552).
+        One launch for the whole batch; differentiable w.r.t. ``pos`` when it requires grad."""
+        from .autograd import dihedral_angles_with_grad
+
+        self._require_cuda(pos, "pos")
+        if pos.dtype != torch.float32:
+            raise TypeError("the CUDA path computes in float32: pass precision=torch.float tensors")
+        if pos.shape[1] != self.natoms:
+            raise ValueError(f"pos has {pos.shape[1]} atoms, parameters have {self.natoms}")
+        return dihedral_angles_with_grad(self, pos, box)
+
+    def _phi_launch(self, pos, box, grad_phi=None):
+        lib = _cabi.load_library()
+        dev = pos.device
+        h = C.c_void_p(self._handle(dev))
+        R = pos.shape[0]
+        nd = lib.b200md_topology_ndihedrals(h)
+        b = None if box is None else box.detach().to(device=dev, dtype=torch.float32).contiguous()
+        bp = _ptr(b) if b is not None else None
+        with torch.cuda.device(dev):
+            if grad_phi is None:
+                out = torch.empty((R, nd), dtype=torch.float32, device=dev)
+                _check(lib.b200md_dihedral_angles(h, R, _ptr(pos), bp, _ptr(out), _stream_ptr(dev)))
+            else:
+                out = torch.empty((R, self.natoms, 3), dtype=torch.float32, device=dev)
+                _check(lib.b200md_dihedral_angles_backward(h, R, _ptr(pos), bp, _ptr(grad_phi), _ptr(out), _stream_ptr(dev)))
+        return out
+
     # -- reference-shaped entry point --------------------------------------------------------------
     def compute(self, pos, box, forces, returnDetails=False, explicit_forces=True):
         """Forces.compute of the reference (forces.py:82-344): zeroes and fills ``forces`` in place and

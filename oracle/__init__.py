@@ -54,6 +54,8 @@ def lib():
         L.oracle_integrate.argtypes = [C.POINTER(_cabi.TopologyDesc), C.POINTER(_cabi.ForceOpts),
                                        C.POINTER(_cabi.SmdOpts), C.POINTER(_cabi.IntegrateOpts), C.c_int64,
                                        vp, vp, vp, vp, vp, vp]
+        L.oracle_dihedral_angles.restype = C.c_int
+        L.oracle_dihedral_angles.argtypes = [C.POINTER(_cabi.TopologyDesc), C.c_int64, vp, vp, vp]
         L.oracle_normal3.restype = None
         L.oracle_normal3.argtypes = [C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint64, vp]
         L.oracle_philox4x32_10.restype = None
@@ -101,6 +103,18 @@ def forces(packed: "_cabi.PackedTopology", pos, box=None, smd=None, smd_centers=
     if rc != 0:
         raise RuntimeError(f"oracle_forces failed with status {rc}")
     return f, e
+
+
+def dihedral_angles(packed, pos, box=None):
+    """Energy.calc_phi in FP64: pos (R, N, 3) float64 -> (R, ndihedrals) float64."""
+    p = np.ascontiguousarray(pos, dtype=np.float64)
+    R, N, _ = p.shape
+    box = None if box is None else np.ascontiguousarray(box, dtype=np.float32).reshape(R, 9)
+    out = np.zeros((R, packed.desc.ndihedrals), dtype=np.float64)
+    rc = lib().oracle_dihedral_angles(C.byref(packed.desc), R, _ptr(p), _ptr(box), _ptr(out))
+    if rc != 0:
+        raise RuntimeError(f"oracle_dihedral_angles failed with status {rc}")
+    return out
 
 
 def integrate(packed, pos, vel, forces_in, nsteps, dt, gamma=0.0, temperature=0.0, seed=0, step0=0, replica0=0,

@@ -281,6 +281,30 @@ static void forces_one(const b200md_topology_desc* T, const b200md_force_opts* O
   }
 }
 
+/* Energy.calc_phi of the ML callers (cGAN/cGAN_D_pos-2.3.2/cgan.py:166-207; same expressions as forces.py:541-552):
+ * r12 = x0 - x1, r23 = x1 - x2, r34 = x2 - x3 (wrapped), A = r12 x r23, B = r23 x r34, Cv = r23 x A,
+ * cos = A.(B/|B|)/|A|, sin = Cv.(B/|B|)/|Cv|, phi = -atan2(sin, cos).  pos double [R][N][3] so that finite
+ * differences of this function check the analytic backward; phi double [R][ndihedrals]. */
+int oracle_dihedral_angles(const b200md_topology_desc* T, int64_t R, const double* pos, const float* box, double* phi) {
+  const int N = T->natoms;
+  for (int64_t r = 0; r < R; ++r) {
+    const double* p = pos + r * 3 * N;
+    double b[3] = {0, 0, 0};
+    if (box) { b[0] = box[r * 9]; b[1] = box[r * 9 + 4]; b[2] = box[r * 9 + 8]; }
+    const int vacuum = b[0] == 0.0 && b[1] == 0.0 && b[2] == 0.0;
+    for (int d = 0; d < T->ndihedrals; ++d) {
+      const int32_t* q = T->dihedral_idx + 4 * d;
+      v3 r12 = wrap(sub(getpos(p, q[0]), getpos(p, q[1])), b, vacuum);
+      v3 r23 = wrap(sub(getpos(p, q[1]), getpos(p, q[2])), b, vacuum);
+      v3 r34 = wrap(sub(getpos(p, q[2]), getpos(p, q[3])), b, vacuum);
+      v3 A = cross(r12, r23), B = cross(r23, r34), Cv = cross(r23, A);
+      v3 nB = scale(B, 1.0 / norm(B));
+      phi[r * T->ndihedrals + d] = -atan2(dot(Cv, nB) / norm(Cv), dot(A, nB) / norm(A));
+    }
+  }
+  return B200MD_OK;
+}
+
 /* Forces.compute for R replicas.  pos float [R][N][3] (the fp32 inputs the GPU path sees), box float
  * [R][9] or NULL, smd_centers float [R] or NULL (then S->center0).  forces double [R][N][3],
  * energies double [R][8].  Returns B200MD_ERR_NAN_COORDINATES like forces.py:91-92. */

@@ -722,3 +722,85 @@ def test_rigid_bonds_is_a_noop_without_hydrogens_and_refuses_unsupported_groups(
     integ = Integrator(s, F, timestep=2.0, device=DEV, rigid_bonds=True)
     with pytest.raises(NotImplementedError, match="rigid_bonds"):
         integ.step(niter=2)
+
+
+def _wrap_angle(a):
+    return (a + np.pi) % (2 * np.pi) - np.pi
+
+
+@pytest.mark.parametrize("system", ["ala10", "bb40"])
+def test_dihedral_angles_and_backward_vs_oracle(system):
+    """Energy.calc_phi batched (cgan.py:166-207) and its analytic backward."""
+    g = load_golden(system)
+    pos = (g["pos"] if system == "ala10" else g["frames"])[:12].astype(np.float32)
+    par = gpu_par(g)
+    F = Forces(par)
+    p = torch.tensor(pos, device=DEV, requires_grad=True)
+    phi = F.dihedral_angles(p)
+    ref = oracle.dihedral_angles(g.packed, pos.astype(np.float64))
+    assert phi.shape == ref.shape == (len(pos), len(g.par.dihedrals))
+    assert np.abs(_wrap_angle(phi.detach().cpu().numpy() - ref)).max() < 2e-5
+    # backward of L = sum w phi against central differences of the FP64 oracle
+    rng = np.random.default_rng(0)
+    w = rng.standard_normal(ref.shape)
+    (phi * torch.tensor(w, device=DEV, dtype=torch.float32)).sum().backward()
+    grad = p.grad.cpu().numpy().astype(np.float64)
+    h = 1e-5
+    for _ in range(40):
+        r, a, c = rng.integers(len(pos)), rng.integers(pos.shape[1]), rng.integers(3)
+        pp, pm = pos.astype(np.float64), pos.astype(np.float64)
+        pp[r, a, c] += h
+        pm[r, a, c] -= h
+        d = _wrap_angle(oracle.dihedral_angles(g.packed, pp[r:r + 1]) - oracle.dihedral_angles(g.packed, pm[r:r + 1]))
+        fd = (w[r] * d[0]).sum() / (2 * h)
+        assert abs(grad[r, a, c] - fd) < 2e-4 * max(1.0, np.abs(grad[r]).max()), (r, a, c, grad[r, a, c], fd)
+    # minimum image: shifting atoms by box vectors leaves the angles unchanged
+    box = np.zeros((len(pos), 3, 3), dtype=np.float32)
+    box[:, 0, 0], box[:, 1, 1], box[:, 2, 2] = 60.0, 70.0, 80.0
+    shifted = pos.copy()
+    shifted[:, ::3, 0] += 60.0
+    shifted[:, 1::4, 2] -= 80.0
+    phib = F.dihedral_angles(torch.tensor(shifted, device=DEV), torch.tensor(box, device=DEV))
+    assert np.abs(_wrap_angle(phib.cpu().numpy() - ref)).max() < 1e-4
+
+
+def test_batched_energy_adapter_matches_per_sample_and_backpropagates():
+    """The ML callers' loss (cgan.py:345-360): sum over the batch of (sum of terms + 200 * E2End) / B, here from two
+    launches forward and two backward instead of a rebuilt Energy object per sample."""
+    from molecular_dynamics_b200 import Energy
+
+    g = load_golden("ala10")
+    pos = g["pos"][:16].astype(np.float32)
+    B = len(pos)
+    colvar = {"name": "E2End Harm", "fk": 1.0, "cent_0": 12.0, "cent_1": 34.0, "T": 1.0, "group1": [3], "group2": [98]}
+    en = Energy(parameters=gpu_par(g), colvar=colvar, device=DEV)
+    times = np.linspace(0.0, 1.0, B).astype(np.float32)
+    x = torch.tensor(pos, device=DEV, requires_grad=True)
+    lib = _cabi.load_library()
+    n0 = lib.b200md_launch_count()
+    ene, phis = en.calc_energy_batch(x, torch.tensor(times))
+    assert lib.b200md_launch_count() - n0 == 2
+    total = sum(v for k, v in ene.items() if k != "E2End Harm").sum() / B + 200.0 * ene["E2End Harm"].sum() / B
+    n0 = lib.b200md_launch_count()
+    total.backward()
+    assert lib.b200md_launch_count() - n0 == 2  # {all terms}, {restraint}: columns with equal weights share a launch
+    # oracle: the adapter's settings (cutoff 9, reaction field, switch 7.5), per-sample centres
+    mode = dict(cutoff=9, rfa=True, switch_dist=7.5)
+    cen = (12.0 + 22.0 * times).astype(np.float32)
+    smd = dict(atom1=3, atom2=98, fk=1.0, center0=0.0)
+    f_all, e_all = oracle.forces(g.packed, pos, smd=smd, smd_centers=cen, **mode)
+    f_terms, e_terms = oracle.forces(g.packed, pos, **mode)
+    want = e_terms.sum() / B + 200.0 * e_all[:, 7].sum() / B
+    assert abs(float(total.detach()) - want) < 2e-5 * abs(want)
+    grad_ref = -(f_terms + 200.0 * (f_all - f_terms)) / B
+    err = np.abs(x.grad.cpu().numpy() - grad_ref).max() / np.abs(grad_ref).max()
+    assert err < 2e-5, err
+    np.testing.assert_allclose(ene["E2End Harm"].detach().cpu().numpy(), e_all[:, 7], rtol=2e-5, atol=1e-6)
+    # per-sample adapter call: same numbers, reference-shaped return value
+    pot, phi0 = en.calc_energy(pos[B - 1].reshape(104, 3, 1), float(times[B - 1]))
+    assert set(pot[0]) == set(ene) and phi0.shape == (len(g.par.dihedrals),)
+    for k in ene:
+        np.testing.assert_allclose(float(pot[0][k]), float(ene[k][B - 1]), rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(phi0.cpu().numpy(), phis[B - 1].detach().cpu().numpy(), atol=1e-6)
+    ref_phi = oracle.dihedral_angles(g.packed, pos.astype(np.float64))
+    assert np.abs(_wrap_angle(phis.detach().cpu().numpy() - ref_phi)).max() < 2e-5
