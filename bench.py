@@ -369,6 +369,21 @@ def run_ours(args):
         integ3.energy_every, integ3.check_nan = args.energy_every, False
         t3 = timed(lambda: integ3.step(niter=nst), 2)
         extra["langevin_smd"] = {"value": R * nst / t3, "unit": "replica-steps/s", "replicas": R, "md_steps_per_launch": nst}
+        # snapshot-write path (north star: "achieved HBM GB/s for the snapshot-write path"): positions of every replica
+        # written every 10 / every step (observables only after the last step, so that the cost seen is the write path's)
+        for every in (10, 1):
+            sys6 = System(104, R, torch.float, dev)
+            sys6.pos[:] = torch.tensor(pos_h, device=dev)
+            sys6.vel[:] = torch.tensor(vel_h, device=dev)
+            forces.compute_batch(sys6.pos, sys6.box, sys6.forces)
+            integ6 = Integrator(sys6, forces, timestep=1.0, device=dev)
+            integ6.energy_every, integ6.snapshot_every, integ6.check_nan = 0, every, False
+            n6 = 200
+            t6 = timed(lambda: integ6.step(niter=n6), 2)
+            wbytes = (n6 // every) * R * 104 * 12
+            extra[f"snapshots_every_{every}"] = {"value": R * n6 / t6, "unit": "replica-steps/s", "hbm_write_GBps": wbytes / t6 / 1e9,
+                                                "bytes_per_snapshot_per_replica": 104 * 12}
+            del sys6, integ6
         # the ML callers' loss (cgan.py:345-360): per-term energies + torsion angles of a generated batch, forward and
         # backward through the batched Energy adapter (the reference rebuilds an Energy object per sample: 41-105
         # evaluations/s on a V100)
