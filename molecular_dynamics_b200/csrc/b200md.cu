@@ -45,7 +45,7 @@ __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, co
   if (FIXED) {
     for (int k = tid; k < 3 * kMaxAtoms; k += kThreads) S.fbi[k] = 0;
   } else {
-    for (int k = tid; k < 4 * T.nslots; k += kThreads) S.fb[k] = 0.0f;
+    for (int k = tid; k < 3 * S.fbs; k += kThreads) S.fb[k] = 0.0f;
   }
   // chunks without a tile task (no non-bonded term enabled) must read as zero in the gather
   for (int k = tid; k < 3 * kMaxAtoms; k += kThreads) S.fj[k] = 0.0f;

@@ -294,7 +294,7 @@ __device__ __forceinline__ void emit(const Smem& S, uint32_t slot, uint32_t atom
     atomicAdd(S.fbi + kMaxAtoms + atom, __float2int_rn(y));
     atomicAdd(S.fbi + 2 * kMaxAtoms + atom, __float2int_rn(z));
   } else {
-    ((float4*)S.fb)[slot] = make_float4(x, y, z, 0.0f);
+    S.fb[slot] = x; S.fb[S.fbs + slot] = y; S.fb[2 * S.fbs + slot] = z;
   }
 }
 // +v to (slot0, atom0) and -v to (slot1, atom1) from one conversion
@@ -306,8 +306,8 @@ __device__ __forceinline__ void emit_pm(const Smem& S, uint32_t slot0, uint32_t 
     atomicAdd(S.fbi + atom0, ix); atomicAdd(S.fbi + kMaxAtoms + atom0, iy); atomicAdd(S.fbi + 2 * kMaxAtoms + atom0, iz);
     atomicAdd(S.fbi + atom1, -ix); atomicAdd(S.fbi + kMaxAtoms + atom1, -iy); atomicAdd(S.fbi + 2 * kMaxAtoms + atom1, -iz);
   } else {
-    ((float4*)S.fb)[slot0] = make_float4(x, y, z, 0.0f);
-    ((float4*)S.fb)[slot1] = make_float4(-x, -y, -z, 0.0f);
+    S.fb[slot0] = x; S.fb[S.fbs + slot0] = y; S.fb[2 * S.fbs + slot0] = z;
+    S.fb[slot1] = -x; S.fb[S.fbs + slot1] = -y; S.fb[2 * S.fbs + slot1] = -z;
   }
 }
 
@@ -690,8 +690,7 @@ __device__ __forceinline__ void gather_forces(const Smem& S, const ForceParams& 
     const int g1 = S.gstart[a + 1];
 #pragma unroll 4
     for (int g = S.gstart[a]; g < g1; ++g) {
-      const float4 v = ((const float4*)S.fb)[g];
-      fx += v.x; fy += v.y; fz += v.z;
+      fx += S.fb[g]; fy += S.fb[S.fbs + g]; fz += S.fb[2 * S.fbs + g];
     }
   }
   if (P.smd_on) {

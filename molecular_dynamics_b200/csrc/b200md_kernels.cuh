@@ -114,7 +114,8 @@ struct Smem {
   uint32_t* diagmask;  // [128]
   float* fi;          // [kWarps][3][128]
   float* fj;          // [3][128]
-  float* fb;          // [nslots] float4: atom-major bonded force slots (slot mode)
+  float* fb;          // [3][fbs]: atom-major bonded force slots (slot mode), one plane per component
+  int fbs;            // plane stride = nslots rounded up to 32
   int* fbi;           // [3][128] fixed-point bonded force accumulators (fixed mode)
   float4* vel;        // [128] velocities parked during the task phase of the integrator
   uint16_t* gstart;   // [130]
@@ -172,8 +173,10 @@ __host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, i
     s->ta = (float*)(base + kOffAb);
     s->tb = (float*)(base + kOffAb + tab);
     s->fb = (float*)(base + off_fb);
+    s->fbs = ((nslots > 0 ? nslots : 1) + 31) & ~31;
   }
-  return fixed ? off_fb : off_fb + sizeof(float4) * (size_t)(nslots > 0 ? nslots : 1);
+  // 12 bytes per slot (three planes) instead of a float4: ALA10's 1 612 slots then leave room for 4 CTAs per SM
+  return fixed ? off_fb : off_fb + 3 * sizeof(float) * (size_t)(((nslots > 0 ? nslots : 1) + 31) & ~31);
 }
 
 // ---- small math helpers ---------------------------------------------------------------------
