@@ -800,7 +800,116 @@ def test_batched_energy_adapter_matches_per_sample_and_backpropagates():
     pot, phi0 = en.calc_energy(pos[B - 1].reshape(104, 3, 1), float(times[B - 1]))
     assert set(pot[0]) == set(ene) and phi0.shape == (len(g.par.dihedrals),)
     for k in ene:
-        np.testing.assert_allclose(float(pot[0][k]), float(ene[k][B - 1]), rtol=1e-6, atol=1e-6)
+        np.testing.assert_allclose(float(pot[0][k].detach()), float(ene[k][B - 1].detach()), rtol=1e-6, atol=1e-6)
     np.testing.assert_allclose(phi0.cpu().numpy(), phis[B - 1].detach().cpu().numpy(), atol=1e-6)
     ref_phi = oracle.dihedral_angles(g.packed, pos.astype(np.float64))
     assert np.abs(_wrap_angle(phis.detach().cpu().numpy() - ref_phi)).max() < 2e-5
+
+
+class _RandomMolecule:
+    """Seeded random topology for the packing paths no fixed fixture reaches: atom counts around the 32-lane block
+    edges and at the 128-atom limit, branched bonds, several terms per dihedral with periodicities on both sides of
+    the Fourier-series limit (6) and non-integer ones, harmonic (periodicity 0) slices, zero-k dihedrals that reduce
+    to their 1-4 pair, random LJ tables.  The oracle restates forces.py for arbitrary parameter objects, so it is the
+    reference here."""
+
+    def __init__(self, natoms, seed, R=3):
+        rng = np.random.default_rng(seed)
+        N = natoms
+        # start structure: a helix (no collinear triples, which make torsion gradients singular), jittered
+        t = np.arange(N) * rng.uniform(0.9, 1.1)
+        a_h, b_h = rng.uniform(1.5, 1.8), rng.uniform(0.8, 1.0)
+        base = np.stack([a_h * np.cos(t), a_h * np.sin(t), b_h * t], 1)
+        self.pos = (base[None] + 0.08 * rng.standard_normal((R, N, 3))).astype(np.float32)
+        ntypes = int(rng.integers(1, 7))
+        sig, eps = rng.uniform(1.5, 3.4, ntypes), rng.uniform(0.02, 0.25, ntypes)
+        s = 0.5 * (sig[:, None] + sig[None, :])
+        e = np.sqrt(eps[:, None] * eps[None, :])
+        arrs = {"mapped_atom_types": rng.integers(0, ntypes, N), "A": 4 * e * s ** 12, "B": 4 * e * s ** 6,
+                "charges": rng.uniform(-0.6, 0.6, N), "masses": rng.choice([1.008, 12.011, 14.007, 15.999], N).reshape(N, 1)}
+        bonds = [(i, i + 1) for i in range(N - 1)]
+        for _ in range(N // 6):  # branches / rings between lattice neighbours further along the snake
+            i = int(rng.integers(0, N - 3))
+            j = int(min(N - 1, i + rng.integers(2, 6)))
+            if (i, j) not in bonds:
+                bonds.append((i, j))
+        bonds = np.array(sorted(set(bonds)))
+        dist0 = np.linalg.norm(base[bonds[:, 0]] - base[bonds[:, 1]], axis=1)
+        arrs["bonds"] = bonds
+        arrs["bond_params"] = np.stack([rng.uniform(100, 450, len(bonds)), dist0 + rng.uniform(-0.1, 0.1, len(bonds))], 1)
+        if N >= 3:
+            ang = np.array([(i, i + 1, i + 2) for i in range(N - 2)])
+            arrs["angles"] = ang
+            arrs["angle_params"] = np.stack([rng.uniform(20, 90, len(ang)), rng.uniform(1.5, 2.3, len(ang))], 1)
+        if N >= 4:
+            dih = np.array([(i, i + 1, i + 2, i + 3) for i in range(N - 3)])
+            nd = len(dih)
+            arrs["dihedrals"] = dih
+            nsl = int(rng.integers(1, 4))
+            arrs["dihedral_nslices"] = np.array(nsl)
+            for j in range(nsl):
+                idx = np.sort(rng.choice(nd, size=max(1, nd // (j + 1)), replace=False)) if j else np.arange(nd)
+                per = rng.choice([1, 2, 3, 4, 6], len(idx)).astype(np.float64)
+                k = rng.uniform(0.0, 2.5, len(idx))
+                if j == 0:
+                    k[rng.random(len(idx)) < 0.25] = 0.0  # zero-k dihedrals: only their 1-4 pair survives
+                if j == 1:
+                    per[rng.random(len(idx)) < 0.3] = rng.choice([7.0, 8.0, 2.5])  # beyond the series / non-integer
+                if j == 2 and seed % 2:
+                    per[:] = 0.0  # a CHARMM harmonic slice (forces.py:570-576)
+                    k *= 10.0
+                arrs[f"dihedral_idx_{j}"] = idx
+                arrs[f"dihedral_params_{j}"] = np.stack([k, rng.uniform(-np.pi, np.pi, len(idx)), per], 1)
+            ex = np.zeros((N, N), bool)
+            ex[bonds[:, 0], bonds[:, 1]] = ex[bonds[:, 1], bonds[:, 0]] = True
+            ex[ang[:, 0], ang[:, 2]] = ex[ang[:, 2], ang[:, 0]] = True
+            keep = ~ex[dih[:, 0], dih[:, 3]]
+            if keep.any():
+                i14 = dih[keep][:, [0, 3]]
+                arrs["idx14"] = i14
+                arrs["nonbonded_14_params"] = np.stack([rng.uniform(1e2, 5e3, len(i14)), rng.uniform(1, 50, len(i14)),
+                                                        rng.choice([1.0, 2.0], len(i14)), rng.choice([1.0, 1.2], len(i14))], 1)
+            nimp = N // 5
+            if nimp:
+                c = rng.integers(1, N - 2, nimp)
+                imp = np.stack([c, c - 1, c + 1, np.minimum(c + 2, N - 1)], 1)
+                arrs["impropers"] = imp
+                arrs["improper_nslices"] = np.array(1)
+                arrs["improper_idx_0"] = np.arange(nimp)
+                harmonic = seed % 3 == 0
+                arrs["improper_params_0"] = np.stack([rng.uniform(1, 40, nimp), rng.uniform(-0.4, 0.4, nimp) if harmonic
+                                                      else rng.choice([0.0, np.pi], nimp),
+                                                      np.zeros(nimp) if harmonic else np.full(nimp, 2.0)], 1)
+        self.par = Parameters.from_arrays(arrs, precision=torch.float64)
+        self.ava_idx = _cabi.make_pair_index(N, self.par.get_exclusions())
+        self.packed = _cabi.PackedTopology(self.par, self.ava_idx)
+
+
+@pytest.mark.parametrize("natoms,seed", [(2, 20), (3, 21), (4, 0), (9, 1), (31, 2), (32, 3), (33, 4), (57, 5), (64, 6), (65, 7), (96, 8), (97, 9),
+                                         (104, 10), (127, 11), (128, 12), (128, 13)])
+def test_random_topologies_vs_oracle(natoms, seed):
+    g = _RandomMolecule(natoms, seed)
+    for mode in ("plain", "rf"):
+        f_ref, e_ref = oracle.forces(g.packed, g.pos, **MODES[mode])
+        f, e, F = run_gpu(g, g.pos, **MODES[mode])
+        ferr = np.abs(f - f_ref).reshape(len(f), -1).max(1) / np.abs(f_ref).reshape(len(f), -1).max(1)
+        assert ferr.max() < 3e-5, (mode, ferr.max())
+        coul, lj = pair_scales(g, g.pos)
+        scale = np.abs(e_ref).sum(1) + coul + lj + torsion_scale(g.par, "dihedrals") + torsion_scale(g.par, "impropers")
+        assert (np.abs(e - e_ref).max(1) <= 3e-6 * scale).all(), (mode, (np.abs(e - e_ref).max(1) / scale).max())
+        np.testing.assert_array_equal(F.ava_idx.cpu().numpy().reshape(-1, 2), g.ava_idx.reshape(-1, 2))
+    # the fused integrator on the same topology (fixed-point bonded accumulation, static schedule, bank spreading)
+    vel0 = (0.02 * np.random.default_rng(seed).standard_normal(g.pos.shape)).astype(np.float32)
+    par, s = make_system(g, g.pos, vel0)
+    F = Forces(par)
+    F.compute_batch(s.pos, s.box, s.forces)
+    f0 = s.forces.cpu().numpy().astype(np.float64)
+    integ = Integrator(s, F, timestep=0.5, device=DEV)
+    integ.energy_every = 5
+    integ.step(niter=10)
+    out = oracle.integrate(g.packed, g.pos, vel0, f0, nsteps=10, dt=np.float32(integ.dt), energy_every=5)
+    assert np.abs(s.pos.cpu().numpy() - out["pos"]).max() < 2e-4
+    obs = integ.observables.cpu().numpy()
+    ref = out["observables"]
+    sc = np.abs(ref[:, :, :8]).sum(-1) + 1.0
+    assert (np.abs(obs[:, :, :8].sum(-1) - ref[:, :, :8].sum(-1)) <= 2e-4 * sc).all()
