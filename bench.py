@@ -331,15 +331,20 @@ def run_ours(args):
     extra = {}
     if world == 1 and not args.no_extra:
         def timed(fn, reps):
+            """seconds per call: median over three event-timed groups of `reps` calls (the shared boxes show a host
+            interference spike of tens of ms about once a second, which a single short group can catch)"""
             fn()
             torch.cuda.synchronize()
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record()
-            for _ in range(reps):
-                fn()
-            b.record()
-            torch.cuda.synchronize()
-            return a.elapsed_time(b) * 1e-3 / reps
+            groups = []
+            for _ in range(3):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                for _ in range(reps):
+                    fn()
+                b.record()
+                torch.cuda.synchronize()
+                groups.append(a.elapsed_time(b) * 1e-3 / reps)
+            return statistics.median(groups)
 
         # configs[1]: batched energy + force evaluation over 65 536 conformers (Forces.compute, one launch)
         R2 = 65536

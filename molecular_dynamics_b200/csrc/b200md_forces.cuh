@@ -93,9 +93,9 @@ __device__ __forceinline__ u64 pair_eval2(u64 dx, u64 dy, u64 dz, float kqi, u64
   const u64 glj1 = fma2(a12, r6, nb6);
   if (MODE == 0) {
     const u64 gc = mul2(qq, rinv);
-    if (ENERGY) {
+    if (ENERGY) {  // A r^-12 - B r^-6 = r6 (glj1 + nb6) / 12: plj collects 12 E, the 1/12 is applied once per fold
       pel = add2(pel, gc);
-      plj = add2(plj, mul2(fma2(mul2(a12, C.c12), r6, mul2(nb6, C.c6)), r6));
+      plj = fma2(add2(glj1, nb6), r6, plj);
     }
     return mul2(fma2(glj1, r6, gc), r2inv);
   } else {
@@ -108,7 +108,7 @@ __device__ __forceinline__ u64 pair_eval2(u64 dx, u64 dy, u64 dz, float kqi, u64
     const u64 t2 = mul2(t, t);
     const u64 sv = fma2(mul2(t2, t), fma2(t, fma2(t, C.cm6, C.c15), C.cm10), C.one);
     const u64 nsd = mul2(mul2(t2, fma2(t, fma2(t, C.c30, C.cm60), C.c30)), C.inv_sw);
-    u64 elj = mul2(fma2(mul2(a12, C.c12), r6, mul2(nb6, C.c6)), r6);
+    u64 elj = mul2(mul2(add2(glj1, nb6), r6), C.c12);
     glj = fma2(sv, glj, mul2(elj, nsd));
     elj = mul2(elj, sv);
     if (ENERGY) {
@@ -139,6 +139,7 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
   float4 pi_n = S.pos[lane];
   int roff_n = S.ab_row_off[lane];
   uint32_t m8_n = S.mask8[chunk * kMaxAtoms + lane];
+  u64 pel = 0ull, plj = 0ull;
 #pragma unroll 1
   for (int p = 0; p < passes; ++p) {
     asm volatile("" ::: "memory");  // re-read the 8 broadcast j atoms every pass instead of pinning 32 registers
@@ -154,7 +155,7 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
       roff_n = S.ab_row_off[in];
       m8_n = S.mask8[chunk * kMaxAtoms + in];
     }
-    u64 pel = 0ull, plj = 0ull, ax = 0ull, ay = 0ull, az = 0ull;
+    u64 ax = 0ull, ay = 0ull, az = 0ull;
 #pragma unroll
     for (int h = 0; h < kChunk / 4; ++h) {
       const ulonglong2 xj = *(const ulonglong2*)(sj + 4 * h), yj = *(const ulonglong2*)(sj + kMaxAtoms + 4 * h),
@@ -173,11 +174,11 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
     }
     float* f = fiw + p * 32;
     f[0] = __fadd_rn(f[0], hsum2(ax)); f[kMaxAtoms] = __fadd_rn(f[kMaxAtoms], hsum2(ay)); f[2 * kMaxAtoms] = __fadd_rn(f[2 * kMaxAtoms], hsum2(az));
-    if (ENERGY) {
-      float a, b;
-      upk(pel, a, b); E.e[B200MD_E_ELECTROSTATICS] += (double)a + (double)b;
-      upk(plj, a, b); E.e[B200MD_E_LJ] += (double)a + (double)b;
-    }
+  }
+  if (ENERGY) {  // per-lane FP32 partial sums of the whole tile (<= 4 passes x 8 pairs), folded into FP64 once
+    float a, b;
+    upk(pel, a, b); E.e[B200MD_E_ELECTROSTATICS] += (double)a + (double)b;
+    upk(plj, a, b); E.e[B200MD_E_LJ] += (double)(MODE == 0 ? __fmul_rn(__fadd_rn(a, b), 1.0f / 12.0f) : __fadd_rn(a, b));
   }
   float fj[kChunk][3];
 #pragma unroll
@@ -272,7 +273,7 @@ __device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams&
   if (ENERGY) {
     float a, b;
     upk(pel, a, b); E.e[B200MD_E_ELECTROSTATICS] += 0.5 * ((double)a + (double)b);
-    upk(plj, a, b); E.e[B200MD_E_LJ] += 0.5 * ((double)a + (double)b);
+    upk(plj, a, b); E.e[B200MD_E_LJ] += (double)(MODE == 0 ? __fmul_rn(__fadd_rn(a, b), 0.5f / 12.0f) : __fmul_rn(__fadd_rn(a, b), 0.5f));
   }
 }
 
