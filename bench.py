@@ -34,6 +34,22 @@ FLOP_PER_REPLICA_STEP = 240824  # SURVEY.md 8d, ALA10 plain NVE (force-only eval
 FLOP_PER_REPLICA_EVAL = 236144
 NOMINAL_FP32_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.5
 TIMEFACTOR = 48.88821
+def hbm_view(R, S, energy_every, ms_per_launch):
+    """Algorithmic HBM bytes of one integrate launch (state read + written once, observable records) against the
+    measured copy bandwidth of MEASURED_PEAKS.json (driver-written), when that file is present."""
+    nrep = S // energy_every if energy_every > 0 else 1
+    nbytes = R * (2 * 3 * 104 * 12 + nrep * 11 * 8 + 4)
+    peak = None
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "MEASURED_PEAKS.json")) as fh:
+            peak = float(json.load(fh)["hbm_gbs"])
+    except Exception:
+        pass
+    ach = nbytes / (ms_per_launch * 1e-3) / 1e9
+    return {"algorithmic_bytes_per_launch": nbytes, "achieved": ach, "peak": peak, "unit": "GB/s",
+            "frac": ach / peak if peak else None, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peak else None}
+
+
 NCU_DRAM_BYTES_PER_LAUNCH = 31.1e6  # profiles/r01_v20_integrate_kernel.md: 31.08 MB read + 0.04 MB written
 BOLTZMAN = 0.001987191
 
@@ -458,7 +474,10 @@ def run_ours(args):
                          "peak_source": "measured live: b200md_fp32_peak_tflops (dependent-FMA kernel, all SMs)",
                          "nominal_peak": NOMINAL_FP32_TFLOPS, "frac_of_nominal": achieved / NOMINAL_FP32_TFLOPS,
                          "flop_per_replica_step": FLOP_PER_REPLICA_STEP, "kernel": "integrate_kernel<0>",
-                         "kernel_ms_per_launch": ms / args.steps},
+                         "kernel_ms_per_launch": ms / args.steps,
+                         "bound_note": "FP32 CUDA-core kernel: neither the HBM nor the tensor-core roofline binds it; the "
+                                       "HBM view of the same launch is given under 'hbm'",
+                         "hbm": hbm_view(R, S, args.energy_every, ms / args.steps)},
         }
         if extra:
             line["extra"] = extra
