@@ -35,6 +35,7 @@ def main():
     ap.add_argument("--oracle-replicas", type=int, default=8)
     ap.add_argument("--dt", type=float, default=1.0)
     ap.add_argument("--every", type=int, default=100)
+    ap.add_argument("--rigid", action="store_true", help="rigid X-H bonds (SHAKE / RATTLE), e.g. with --dt 2.0")
     a = ap.parse_args()
     import torch
 
@@ -52,7 +53,12 @@ def main():
     F = Forces(par)
     F.compute_batch(s.pos, s.box, s.forces)
     f0 = s.forces.cpu().numpy().astype(np.float64)
-    integ = Integrator(s, F, timestep=a.dt, device=dev)
+    integ = Integrator(s, F, timestep=a.dt, device=dev, rigid_bonds=a.rigid)
+    if a.rigid:  # the synthetic start is not on the constraint surface: project it, then restart the clock
+        integ.step(niter=1)
+        F.compute_batch(s.pos, s.box, s.forces)
+        f0 = s.forces.cpu().numpy().astype(np.float64)
+        pos, vel = s.pos.cpu().numpy(), s.vel.cpu().numpy()
     integ.energy_every = a.every
     chunks = []
     done = 0
@@ -64,14 +70,15 @@ def main():
     obs = np.concatenate(chunks, 0)
     etot = obs[:, :, :8].sum(-1) + obs[:, :, _cabi.OBS_EKIN]
     d, r = drift_stats(etot)
-    out = {"dt_fs": a.dt, "steps": a.steps, "replicas": a.replicas, "energy_every": a.every,
+    out = {"dt_fs": a.dt, "rigid_bonds": bool(a.rigid), "steps": a.steps, "replicas": a.replicas, "energy_every": a.every,
            "gpu": {"etot0_mean": float(etot[0].mean()), "ekin_mean": float(obs[:, :, _cabi.OBS_EKIN].mean()),
                    "drift_mean": float(d.mean()), "drift_abs_max": float(np.abs(d).max()), "drift_std": float(d.std()),
                    "rms_fluct_mean": float(r.mean()), "rms_fluct_max": float(r.max())}}
     if a.oracle_steps > 0:
         packed = _cabi.PackedTopology(Parameters.from_arrays({k[4:]: v for k, v in g.items() if k.startswith("par_")}), g["ava_idx"])
         ro = a.oracle_replicas
-        o = oracle.integrate(packed, pos[:ro], vel[:ro], f0[:ro], nsteps=a.oracle_steps, dt=np.float32(integ.dt), energy_every=a.every)
+        o = oracle.integrate(packed, pos[:ro], vel[:ro], f0[:ro], nsteps=a.oracle_steps, dt=np.float32(integ.dt), energy_every=a.every,
+                             rigid_bonds=a.rigid)
         eo = o["observables"][:, :, :8].sum(-1) + o["observables"][:, :, _cabi.OBS_EKIN]
         do, ro_ = drift_stats(eo)
         nrep = a.oracle_steps // a.every
