@@ -215,6 +215,13 @@ int b200md_dihedral_angles(const b200md_topology* topo, int64_t nreplicas, const
 int b200md_dihedral_angles_backward(const b200md_topology* topo, int64_t nreplicas, const float* pos, const float* box,
                                     const float* grad_phi, float* grad_pos, void* stream);
 
+/* Puts a start structure on the constraint surface of b200md_integrate's rigid_bonds option: positions are projected
+ * along their present X-H bond vectors (SHAKE, relinearised 4 times), the bond-parallel components are taken out of
+ * the velocities (RATTLE).  In place; vel and status may be NULL.  (The first rigid step of b200md_integrate does
+ * the same projection on a start that is off the surface; this call does it without stepping.) */
+int b200md_constrain(const b200md_topology* topo, int64_t nreplicas, float* pos, float* vel, uint32_t* status,
+                     void* stream);
+
 /* Host-buffer convenience (the end-to-end call a non-torch host would make): copies pos in,
  * runs b200md_forces_compute, copies forces/energies out; synchronous. */
 int b200md_forces_compute_host(const b200md_topology* topo, const b200md_force_opts* opts,

@@ -185,6 +185,8 @@ def declare_signatures(lib):
     lib.b200md_dihedral_angles.argtypes = [vp, C.c_int64, vp, vp, vp, vp]
     lib.b200md_dihedral_angles_backward.restype = C.c_int
     lib.b200md_dihedral_angles_backward.argtypes = [vp, C.c_int64, vp, vp, vp, vp, vp]
+    lib.b200md_constrain.restype = C.c_int
+    lib.b200md_constrain.argtypes = [vp, C.c_int64, vp, vp, vp, vp]
     lib.b200md_topology_num_constraints.restype = C.c_int
     lib.b200md_topology_num_constraints.argtypes = [vp]
     lib.b200md_forces_compute.restype = C.c_int
@@ -210,7 +212,7 @@ def declare_signatures(lib):
 EXPORTED_SYMBOLS = (
     "b200md_topology_create", "b200md_topology_destroy", "b200md_topology_exclusion_mask",
     "b200md_topology_natoms", "b200md_topology_num_constraints", "b200md_topology_ndihedrals",
-    "b200md_dihedral_angles", "b200md_dihedral_angles_backward", "b200md_forces_compute", "b200md_integrate", "b200md_forces_compute_host",
+    "b200md_dihedral_angles", "b200md_dihedral_angles_backward", "b200md_constrain", "b200md_forces_compute", "b200md_integrate", "b200md_forces_compute_host",
     "b200md_fp32_peak_tflops", "b200md_launch_count", "b200md_last_error", "b200md_version",
 )
 

@@ -355,6 +355,60 @@ __global__ void __launch_bounds__(kThreads) dihedral_angles_backward_kernel(cons
   }
 }
 
+// Projection of a start structure onto the rigid-bond constraints (b200md_constrain): positions by SHAKE along the
+// present bond vectors (x(t) = the unconstrained x itself), velocities by RATTLE.  One CTA per replica; only the
+// three arrays the group solvers read are set up in the shared-memory view.
+__global__ void __launch_bounds__(kThreads) constrain_kernel(const DevTopo T, const long long R, float* __restrict__ pos,
+                                                             float* __restrict__ vel, uint32_t* __restrict__ status) {
+  __shared__ float4 spos[kMaxAtoms];
+  __shared__ float4 svel[kMaxAtoms];
+  __shared__ float ssx[4 * kMaxAtoms];
+  Smem S{};
+  S.pos = spos; S.vel = svel; S.sx = ssx;
+  const int tid = threadIdx.x, warp = tid >> 5, N = T.natoms;
+  const int cmax = (int)((T.cnmax >> (8 * warp)) & 0xffu);
+  const bool live = tid < N;
+  for (long long r = blockIdx.x; r < R; r += gridDim.x) {
+    __syncthreads();
+    const long long base = (r * N + tid) * 3;
+    float x = 0.f, y = 0.f, z = 0.f, vx = 0.f, vy = 0.f, vz = 0.f;
+    if (live) {
+      x = pos[base]; y = pos[base + 1]; z = pos[base + 2];
+      if (vel) { vx = vel[base]; vy = vel[base + 1]; vz = vel[base + 2]; }
+    }
+    uint32_t flag = 0;
+    bool ok = true;
+    for (int sweep = 0; sweep < 4; ++sweep) {  // far-off starts: the linearisation point follows the projection
+      spos[tid] = make_float4(x, y, z, 0.0f);
+      ssx[tid] = x; ssx[kMaxAtoms + tid] = y; ssx[2 * kMaxAtoms + tid] = z;
+      svel[tid] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+      __syncthreads();
+      ok = true;
+      if (tid < T.ngroups) ok = cmax > 1 ? shake_group<3>(S, T, tid) : shake_group<1>(S, T, tid);
+      __syncthreads();
+      const float4 d = svel[tid];
+      x += d.x; y += d.y; z += d.z;
+      __syncthreads();
+    }
+    if (!ok) flag |= B200MD_FLAG_CONSTRAINT;
+    spos[tid] = make_float4(x, y, z, 0.0f);
+    svel[tid] = make_float4(vx, vy, vz, 0.0f);
+    __syncthreads();
+    if (tid < T.ngroups) { if (cmax > 1) rattle_group<3>(S, T, tid); else rattle_group<1>(S, T, tid); }
+    __syncthreads();
+    if (live) {
+      const float4 v = svel[tid];
+      pos[base] = x; pos[base + 1] = y; pos[base + 2] = z;
+      if (vel) { vel[base] = v.x; vel[base + 1] = v.y; vel[base + 2] = v.z; }
+    }
+    if (status != nullptr) {
+      if (tid == 0) status[r] = 0;
+      __syncthreads();
+      if (flag) atomicOr(status + r, flag);
+    }
+  }
+}
+
 // FP32 FMA throughput micro-benchmark (the roofline denominator): 8 independent chains per thread.
 __global__ void __launch_bounds__(256) fma_peak_kernel(float* out, int iters, float a, float b) {
   float v[8];
@@ -975,6 +1029,21 @@ extern "C" void b200md_topology_destroy(b200md_topology* topo) {
   cudaSetDevice(topo->device);
   if (topo->blob) cudaFree(topo->blob);
   delete topo;
+}
+
+extern "C" int b200md_constrain(const b200md_topology* topo, int64_t R, float* pos, float* vel, uint32_t* status,
+                                void* stream) {
+  if (!topo || !pos) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
+  if (R < 0) return fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica count");
+  if (topo->dev.ncons < 0)
+    return fail(B200MD_ERR_UNSUPPORTED, "rigid_bonds: a hydrogen is bonded to a hydrogen, or a heavy atom carries more than 3");
+  if (R == 0 || topo->dev.ncons == 0) return B200MD_OK;
+  CUDA_TRY(cudaSetDevice(topo->device));
+  const int grid = (int)std::min<long long>(R, (long long)topo->num_sms * 8);
+  constrain_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(topo->dev, R, pos, vel, status);
+  g_launches.fetch_add(1);
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
 }
 
 extern "C" int b200md_topology_ndihedrals(const b200md_topology* topo) { return topo ? topo->dev.nphi : -1; }

@@ -78,8 +78,8 @@ class Integrator:
     def __init__(self, systems, forces, timestep, device=None, gamma=None, T=None, seed=0, rigid_bonds=False):
         """Upstream's signature plus ``seed`` (counter-based RNG) and ``rigid_bonds``: hold every bond with a hydrogen
         end at its equilibrium length (NAMD ``rigidBonds all``, the setting of the reference's data generator, which
-        is what allows its 2 fs step): SHAKE / RATTLE inside the fused kernel.  The start structure should satisfy
-        the constraints (the first step projects it onto them otherwise, at the price of a velocity kick)."""
+        is what allows its 2 fs step): SHAKE / RATTLE inside the fused kernel.  A start structure off the constraint
+        surface is projected onto it by the first step (``apply_constraints`` does the same without stepping)."""
         self.dt = timestep / TIMEFACTOR
         self.systems = systems
         self.forces = forces
@@ -102,6 +102,35 @@ class Integrator:
         self.check_nan = True
         self.rigid_bonds = bool(rigid_bonds)
         self.num_constraints = 0  # known after the first step(): rigid bonds held, 3 N - this degrees of freedom
+
+    def apply_constraints(self):
+        """Put ``systems.pos`` / ``systems.vel`` on the constraint surface of ``rigid_bonds`` (positions along their
+        present X-H bond vectors, bond-parallel velocity components removed) without taking a step: for start structures
+        that were not produced by a constrained run, before a minimisation, an energy evaluation or a checkpoint.  (The
+        first rigid step would otherwise do the same projection.)  One kernel launch for all replicas."""
+        import ctypes
+
+        s, f = self.systems, self.forces
+        for name in ("pos", "vel"):
+            t = getattr(s, name)
+            if not t.is_cuda or t.dtype != torch.float32:
+                raise RuntimeError(f"System.{name} must be a float32 CUDA tensor: the B200 path has no CPU fallback")
+            if not t.is_contiguous():
+                setattr(s, name, t.detach().contiguous())
+        dev = s.pos.device
+        R = s.pos.shape[0]
+        status = torch.zeros(R, dtype=torch.int32, device=dev)
+        lib = _cabi.load_library()
+        with torch.cuda.device(dev):
+            rc = lib.b200md_constrain(ctypes.c_void_p(f._handle(dev)), R, ctypes.c_void_p(s.pos.data_ptr()),
+                                      ctypes.c_void_p(s.vel.data_ptr()), ctypes.c_void_p(status.data_ptr()),
+                                      ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+        if rc == _cabi.ERR_UNSUPPORTED:
+            raise NotImplementedError(_cabi.last_error())
+        if rc != _cabi.OK:
+            raise RuntimeError(f"b200md error {rc}: {_cabi.last_error()}")
+        if R and int(status.max().item()) & _cabi.FLAG_CONSTRAINT:
+            raise RuntimeError("SHAKE did not converge for a hydrogen group: the start structure is too far from its bond lengths")
 
     def step(self, niter=1):
         s, f = self.systems, self.forces

@@ -56,6 +56,8 @@ def lib():
                                        vp, vp, vp, vp, vp, vp]
         L.oracle_dihedral_angles.restype = C.c_int
         L.oracle_dihedral_angles.argtypes = [C.POINTER(_cabi.TopologyDesc), C.c_int64, vp, vp, vp]
+        L.oracle_constrain.restype = C.c_int
+        L.oracle_constrain.argtypes = [C.POINTER(_cabi.TopologyDesc), C.c_int64, vp, vp]
         L.oracle_normal3.restype = None
         L.oracle_normal3.argtypes = [C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint64, vp]
         L.oracle_philox4x32_10.restype = None
@@ -103,6 +105,16 @@ def forces(packed: "_cabi.PackedTopology", pos, box=None, smd=None, smd_centers=
     if rc != 0:
         raise RuntimeError(f"oracle_forces failed with status {rc}")
     return f, e
+
+
+def constrain(packed, pos, vel=None):
+    """b200md_constrain in FP64: returns (pos, vel) on the rigid-bond constraint surface."""
+    p = np.array(pos, dtype=np.float64, order="C")
+    v = None if vel is None else np.array(vel, dtype=np.float64, order="C")
+    rc = lib().oracle_constrain(C.byref(packed.desc), p.shape[0], _ptr(p), _ptr(v))
+    if rc != 0:
+        raise RuntimeError(f"oracle_constrain failed with status {rc}")
+    return p, v
 
 
 def dihedral_angles(packed, pos, box=None):

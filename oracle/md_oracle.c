@@ -427,6 +427,27 @@ static int rattle(const cons_t* c, int nc, const float* mass, const double* p, d
   return 1;
 }
 
+/* b200md_constrain: start structure onto the constraint surface (positions along their present bond vectors,
+ * relinearised 4 times like the kernel; then the velocities).  pos / vel double [R][N][3] in place, vel may be NULL. */
+int oracle_constrain(const b200md_topology_desc* T, int64_t R, double* pos, double* vel) {
+  const int N = T->natoms;
+  cons_t* cons = (cons_t*)malloc(sizeof(cons_t) * (size_t)(N > 0 ? N : 1));
+  const int nc = build_constraints(T, cons);
+  double* p_old = (double*)malloc(sizeof(double) * 3 * (size_t)N);
+  double* vdummy = (double*)calloc(3 * (size_t)N, sizeof(double));
+  int failed = 0;
+  for (int64_t r = 0; r < R && nc > 0; ++r) {
+    double* p = pos + r * 3 * N;
+    for (int sweep = 0; sweep < 4; ++sweep) {
+      memcpy(p_old, p, sizeof(double) * 3 * (size_t)N);
+      if (shake(cons, nc, T->mass, p_old, p, vdummy, 1.0)) failed = 1;
+    }
+    if (vel && rattle(cons, nc, T->mass, p, vel + r * 3 * N)) failed = 1;
+  }
+  free(cons); free(p_old); free(vdummy);
+  return failed ? B200MD_ERR_UNSUPPORTED : B200MD_OK;
+}
+
 /* Integrator.step(niter) of upstream TorchMD, FP64 state.
  * pos/vel/forces double [R][N][3] in/out (forces must be valid at entry), box float [R][9] or NULL.
  * observables double [nreports][R][11] as in b200md_integrate; snapshots double [nsnap][R][N][3]. */

@@ -913,3 +913,39 @@ def test_random_topologies_vs_oracle(natoms, seed):
     ref = out["observables"]
     sc = np.abs(ref[:, :, :8]).sum(-1) + 1.0
     assert (np.abs(obs[:, :, :8].sum(-1) - ref[:, :, :8].sum(-1)) <= 2e-4 * sc).all()
+
+
+def test_apply_constraints_projects_a_perturbed_start_like_the_oracle():
+    g = _Restart(R=8)
+    rng = np.random.default_rng(6)
+    m = g.par.masses.numpy().ravel()
+    hyd = m < 1.5
+    bad = g.pos.copy()
+    bad[:, hyd] += (0.05 * rng.standard_normal(bad[:, hyd].shape)).astype(np.float32)  # hydrogens off their bond lengths
+    ek0 = 0.5 * (m[None, :, None] * g.vel.astype(np.float64) ** 2).sum((1, 2))
+
+    def first_step(project):
+        par, s = make_system(g, bad, g.vel)
+        F = Forces(par)
+        integ = Integrator(s, F, timestep=2.0, device=DEV, rigid_bonds=True)
+        if project:
+            integ.apply_constraints()
+        state = s.pos.cpu().numpy(), s.vel.cpu().numpy()
+        F.compute_batch(s.pos, s.box, s.forces)
+        ekin, _, _ = integ.step(niter=1)
+        return state, ekin, integ, s
+
+    assert g.bond_error(bad) > 1000.0
+    (p, v), ekin, integ, s = first_step(True)
+    assert g.bond_error(p) < 3.0
+    po, vo = oracle.constrain(g.packed, bad, g.vel)
+    assert np.abs(p - po).max() < 2e-5 and np.abs(v - vo).max() < 2e-5 * max(1.0, np.abs(vo).max())
+    # the first rigid step of an unprojected start does the same projection itself (SHAKE, and RATTLE takes the
+    # bond-parallel velocity correction out again): both starts continue with the same kinetic energy
+    _, ekin_unprojected, _, _ = first_step(False)
+    assert np.abs(ekin - ek0).max() < 0.2 * ek0.mean(), (ekin - ek0)
+    assert np.abs(ekin - ekin_unprojected).max() < 0.03 * ek0.mean()
+    # idempotent
+    before = s.pos.clone()
+    integ.apply_constraints()
+    assert float((s.pos - before).abs().max()) < 2e-5

@@ -351,3 +351,23 @@ def test_oracle_rigid_bonds_hold_and_conserve_energy_at_2fs():
     a = oracle.integrate(g.packed, p0, v0, f0, nsteps=5, dt=dt, rigid_bonds=True)
     c = oracle.integrate(g.packed, p0, v0, f0, nsteps=5, dt=dt)
     np.testing.assert_array_equal(a["pos"], c["pos"])
+
+
+def test_oracle_constrain_projects_a_perturbed_start():
+    par, _, packed = _chamber_system()
+    pos0, vel0 = _restart_state()
+    rng = np.random.default_rng(3)
+    bad = pos0 + 0.05 * rng.standard_normal(pos0.shape)
+    p, v = oracle.constrain(packed, bad, vel0)
+    b, bp, m = par.bonds.numpy(), par.bond_params.numpy().astype(np.float32).astype(np.float64), par.masses.numpy().ravel()
+    xh = (m[b[:, 0]] < 1.5) | (m[b[:, 1]] < 1.5)
+    rij = p[0, b[xh, 0]] - p[0, b[xh, 1]]
+    assert np.abs(np.linalg.norm(rij, axis=1) - bp[xh, 1]).max() < 1e-9
+    assert np.abs((rij * (v[0, b[xh, 0]] - v[0, b[xh, 1]])).sum(1)).max() < 1e-9
+    # mass-weighted: the centre of mass of every group stays, so does the molecule's (masses as the C-ABI carries them)
+    mf = m.astype(np.float32).astype(np.float64)
+    np.testing.assert_allclose((mf[:, None] * p[0]).sum(0), (mf[:, None] * bad[0]).sum(0), rtol=0, atol=1e-8)
+    np.testing.assert_allclose((mf[:, None] * v[0]).sum(0), (mf[:, None] * vel0[0]).sum(0), rtol=0, atol=1e-8)
+    # a structure that is already on the surface does not move
+    p2, v2 = oracle.constrain(packed, p, v)
+    assert np.abs(p2 - p).max() < 1e-10 and np.abs(v2 - v).max() < 1e-10
