@@ -949,3 +949,16 @@ def test_apply_constraints_projects_a_perturbed_start_like_the_oracle():
     before = s.pos.clone()
     integ.apply_constraints()
     assert float((s.pos - before).abs().max()) < 2e-5
+
+
+def test_dihedral_angles_kernel_against_the_reference_data_sets_phi_psi():
+    """The batched calc_phi kernel against the phi / psi angles the reference's data set stores beside its backbone
+    frames (tests/golden/bb40_phi_psi.npy; the oracle is pinned on the same fixture in tests/test_oracle.py)."""
+    from test_oracle import _phi_psi_fixture
+
+    g, frames, rows, want = _phi_psi_fixture()
+    F = Forces(gpu_par(g))
+    phi = F.dihedral_angles(torch.tensor(frames, device=DEV, dtype=torch.float32))
+    got = np.degrees(phi.cpu().numpy().astype(np.float64))[:, rows]
+    diff = (got - want + 180.0) % 360.0 - 180.0
+    assert np.abs(diff).max() < 0.02, np.abs(diff).max()

@@ -371,3 +371,29 @@ def test_oracle_constrain_projects_a_perturbed_start():
     # a structure that is already on the surface does not move
     p2, v2 = oracle.constrain(packed, p, v)
     assert np.abs(p2 - p).max() < 1e-10 and np.abs(v2 - v).max() < 1e-10
+
+
+def _phi_psi_fixture():
+    """frames (64, 40, 3) and, per frame, the reference data set's own phi (residues 1..8) and psi (residues 0..7) in
+    degrees, with the rows of par.dihedrals that are those angles (backbone order N, CA, C, O per residue)."""
+    g = load_golden("bb40")
+    a = np.load(os.path.join(os.path.dirname(__file__), "golden", "bb40_phi_psi.npy"))
+    quads = [tuple(int(x) for x in q) for q in g.par.dihedrals.numpy()]
+    rows, want = [], []
+    for r in range(8):
+        rows.append(quads.index((4 * r, 4 * r + 1, 4 * r + 2, 4 * r + 4)))  # psi_r: N CA C N'
+        want.append(a[:, 4 * r, 4])
+        rows.append(quads.index((4 * r + 2, 4 * r + 4, 4 * r + 5, 4 * r + 6)))  # phi_{r+1}: C N' CA' C'
+        want.append(a[:, 4 * (r + 1), 3])
+    return g, a[:, :, :3], np.array(rows), np.stack(want, 1).astype(np.float64)
+
+
+def test_dihedral_angles_against_the_reference_data_sets_phi_psi():
+    """Energy.calc_phi restated (oracle_dihedral_angles) reproduces the phi / psi columns the reference's data set
+    stores beside its backbone coordinates (tests/golden/bb40_phi_psi.npy, tools/make_golden_phipsi.py): sign
+    convention, atom order and units pinned on 64 frames x 16 angles."""
+    g, frames, rows, want = _phi_psi_fixture()
+    phi = np.degrees(oracle.dihedral_angles(g.packed, frames.astype(np.float64)))[:, rows]
+    diff = (phi - want + 180.0) % 360.0 - 180.0
+    assert np.abs(diff).max() < 0.02, np.abs(diff).max()
+    assert np.abs(want).max() > 150.0 and (want > 0).any() and (want < 0).any()  # both signs, near the branch cut
