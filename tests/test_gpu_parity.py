@@ -962,3 +962,27 @@ def test_dihedral_angles_kernel_against_the_reference_data_sets_phi_psi():
     got = np.degrees(phi.cpu().numpy().astype(np.float64))[:, rows]
     diff = (got - want + 180.0) % 360.0 - 180.0
     assert np.abs(diff).max() < 0.02, np.abs(diff).max()
+
+
+def test_chamber_energies_on_gpu_against_namd_at_the_restart_frame():
+    """The CUDA path end to end (prmtop loader -> Forces -> kernel) against NAMD's own energies of the reference's
+    restart frame (see tests/test_oracle.py::test_chamber_prmtop_route_pinned_by_namd_energies_at_the_restart_frame)."""
+    import json
+
+    from molecular_dynamics_b200.parameters import parameters_from_prmtop
+    from molecular_dynamics_b200.topology_io import read_namd_bin
+
+    gold = os.path.join(os.path.dirname(__file__), "golden")
+    namd = json.load(open(os.path.join(gold, "namd_step0_energies.json")))["restart_step_500000"]["energies"]
+    x = torch.tensor(read_namd_bin(os.path.join(gold, "smd_out.restart.coor"))[None], dtype=torch.float32, device=DEV)
+    slot = _cabi.energy_slot
+    res = {}
+    for name, kw in (("plain", {}), ("full", dict(charmm_impropers=True, urey_bradley=True))):
+        par = parameters_from_prmtop(os.path.join(gold, "full_da-1.3.prmtop"), device=DEV, **kw)
+        s = System(104, 1, torch.float, DEV)
+        res[name] = Forces(par).compute_batch(x, s.box, s.forces).cpu().numpy()[0]
+    ub = res["full"][slot("bonds")] - res["plain"][slot("bonds")]
+    assert abs(res["plain"][slot("bonds")] - namd["BOND"]) < 2e-3
+    assert abs(res["full"][slot("angles")] + ub - namd["ANGLE"]) < 2e-3
+    assert abs(res["full"][slot("dihedrals")] - namd["DIHED"]) < 2e-3
+    assert abs(res["full"][slot("impropers")] - namd["IMPRP"]) < 2e-3

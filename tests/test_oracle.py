@@ -397,3 +397,36 @@ def test_dihedral_angles_against_the_reference_data_sets_phi_psi():
     diff = (phi - want + 180.0) % 360.0 - 180.0
     assert np.abs(diff).max() < 0.02, np.abs(diff).max()
     assert np.abs(want).max() > 150.0 and (want > 0).any() and (want < 0).any()  # both signs, near the branch cut
+
+
+def test_chamber_prmtop_route_pinned_by_namd_energies_at_the_restart_frame():
+    """Tight external anchor of prmtop -> Parameters -> forces: NAMD's own ENERGY line of step
+    500000 of replica 3 (tests/golden/namd_step0_energies.json, "restart_step_500000") belongs to the binary restart
+    files in tests/golden/.  Those coordinates satisfy NAMD's rigid bonds, so the bonded columns compare directly:
+    BOND, ANGLE (= angles + Urey-Bradley), DIHED, IMPRP to the 4 decimals NAMD prints, and KINETIC / TEMP pin the
+    velocity unit and the 3 N - 53 degrees of freedom.  VDW differs by NAMD's force-switched 15-16 A cutoff; ELECT
+    contains the generalised-Born term."""
+    import json
+
+    from molecular_dynamics_b200 import BOLTZMAN
+
+    namd = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "namd_step0_energies.json")))
+    namd = namd["restart_step_500000"]["energies"]
+    pos, vel = _restart_state()
+    slot = _cabi.energy_slot
+    par0, _, packed0 = _chamber_system()
+    par, _, packed = _chamber_system(charmm_impropers=True, urey_bradley=True)
+    _, e0 = oracle.forces(packed0, pos)
+    _, e = oracle.forces(packed, pos)
+    ub = e[0, slot("bonds")] - e0[0, slot("bonds")]
+    assert abs(e0[0, slot("bonds")] - namd["BOND"]) < 2e-4
+    assert abs(e[0, slot("angles")] + ub - namd["ANGLE"]) < 2e-4
+    assert abs(e[0, slot("dihedrals")] - namd["DIHED"]) < 2e-4
+    assert abs(e[0, slot("impropers")] - namd["IMPRP"]) < 2e-4
+    par.charges = par.charges * 0
+    _, ev = oracle.forces(_cabi.PackedTopology(par, _cabi.make_pair_index(par.natoms, par.get_exclusions())), pos)
+    assert abs(ev[0, slot("lj")] - namd["VDW"]) < 0.1  # no switching function here
+    m = par.masses.numpy().ravel()
+    ekin = 0.5 * (m[:, None] * vel[0] ** 2).sum()
+    assert abs(ekin - namd["KINETIC"]) < 2e-4
+    assert abs(2.0 * ekin / ((3 * 104 - 53) * BOLTZMAN) - namd["TEMP"]) < 2e-3

@@ -34,6 +34,17 @@ if __name__ == "__main__":
            "note": "NAMD applies rigidBonds ALL to the hydrogens before this evaluation and uses GBIS + a switched VDW, "
                    "so BOND and ELECT are not comparable and the other columns agree only to a fraction of a percent",
            "energies": dict(zip(titles, energy))}
+    # the production run of replica 3: its last ENERGY line (step 500000) belongs to the restart files copied above,
+    # whose coordinates satisfy the constraints, so the bonded columns compare without the caveat of step 0
+    log3 = f"{REF}/All_ML_Training_Data/210905_SMD_decaalanine/SMD/output/3/slurm_namdsim2-output.log"
+    t3 = e3 = None
+    for line in open(log3):
+        if line.startswith("ETITLE:") and t3 is None:
+            t3 = line.split()[1:]
+        if line.startswith("ENERGY:") and line.split()[1] == "500000":
+            e3 = [float(x) for x in line.split()[1:]]
+    rec["restart_step_500000"] = {"source": log3[len(REF) + 1:] + " (ENERGY line of step 500000 = smd_out.restart.{coor,vel})",
+                                  "energies": dict(zip(t3, e3))}
     with open(os.path.join(DST, "namd_step0_energies.json"), "w") as fh:
         json.dump(rec, fh, indent=1)
     print(rec["energies"])
