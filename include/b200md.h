@@ -22,6 +22,11 @@ extern "C" {
 #endif
 
 #define B200MD_MAX_ATOMS 128   /* one CTA per replica; atoms live in 4 x 32-lane blocks          */
+/* Above B200MD_MAX_ATOMS a topology takes the large-solute kernels (the adk-1.0.prmtop system named at
+ * V_Calculations/Test-10_diALA/potcalc.py:114 is the reference's example): same entry points and semantics; the replica
+ * state lives in HBM, pairs run as 32 x 32 tiles with a dense exclusion bit matrix, one launch sequence per MD step.
+ * Not available there: rigid_bonds, b200md_constrain, b200md_dihedral_angles* (B200MD_ERR_UNSUPPORTED). */
+#define B200MD_MAX_ATOMS_LARGE 32768
 #define B200MD_NUM_ENERGIES 8  /* order of Forces.energies + "external" (forces.py:40-50,100)     */
 
 /* energy slots, in the reference's default dict order (forces.py:41-49, :100) */
@@ -171,8 +176,10 @@ b200md_topology* b200md_topology_create(const b200md_topology_desc* desc, int de
 void b200md_topology_destroy(b200md_topology* topo);
 
 /* Integer artefacts for the bit-exact checks: the exclusion bitmask rows built from pair_idx
- * (natoms x 4 uint32, bit j of row i set iff pair (i,j) is NOT evaluated), copied to host `out`. */
-int b200md_topology_exclusion_mask(const b200md_topology* topo, uint32_t* out /* [natoms*4] */);
+ * (natoms x W uint32, bit j % 32 of word j / 32 of row i set iff pair (i,j) is NOT evaluated), copied to host `out`.
+ * W = b200md_topology_mask_words: 4 up to B200MD_MAX_ATOMS atoms, ceil(natoms / 32) above. */
+int b200md_topology_exclusion_mask(const b200md_topology* topo, uint32_t* out /* [natoms*W] */);
+int b200md_topology_mask_words(const b200md_topology* topo);
 int b200md_topology_natoms(const b200md_topology* topo);
 /* number of rigid bonds b200md_integrate holds with rigid_bonds != 0 (degrees of freedom = 3 natoms - this),
  * or -1 when the topology has a hydrogen group the constraint kernel does not support */

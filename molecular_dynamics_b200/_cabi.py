@@ -17,7 +17,8 @@ NUM_OBSERVABLES = 11
 OBS_EKIN = 8
 OBS_E2E_DIST = 9
 OBS_SMD_WORK = 10
-MAX_ATOMS = 128
+MAX_ATOMS = 128  # one-CTA-per-replica kernels; above it (up to MAX_ATOMS_LARGE) the large-solute kernels run
+MAX_ATOMS_LARGE = 32768
 
 # dict order of the reference's result (forces.py:40-50, :100)
 ENERGY_SLOTS = ("electrostatics", "lj", "bonds", "angles", "dihedrals", "1-4", "impropers", "external")
@@ -179,6 +180,8 @@ def declare_signatures(lib):
     lib.b200md_topology_exclusion_mask.argtypes = [vp, vp]
     lib.b200md_topology_natoms.restype = C.c_int
     lib.b200md_topology_natoms.argtypes = [vp]
+    lib.b200md_topology_mask_words.restype = C.c_int
+    lib.b200md_topology_mask_words.argtypes = [vp]
     lib.b200md_topology_ndihedrals.restype = C.c_int
     lib.b200md_topology_ndihedrals.argtypes = [vp]
     lib.b200md_dihedral_angles.restype = C.c_int
@@ -211,7 +214,7 @@ def declare_signatures(lib):
 
 EXPORTED_SYMBOLS = (
     "b200md_topology_create", "b200md_topology_destroy", "b200md_topology_exclusion_mask",
-    "b200md_topology_natoms", "b200md_topology_num_constraints", "b200md_topology_ndihedrals",
+    "b200md_topology_natoms", "b200md_topology_mask_words", "b200md_topology_num_constraints", "b200md_topology_ndihedrals",
     "b200md_dihedral_angles", "b200md_dihedral_angles_backward", "b200md_constrain", "b200md_forces_compute", "b200md_integrate", "b200md_forces_compute_host",
     "b200md_fp32_peak_tflops", "b200md_launch_count", "b200md_last_error", "b200md_version",
 )

@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "b200md_forces.cuh"
+#include "b200md_large.cuh"
 
 using namespace b200md;
 
@@ -454,6 +455,10 @@ struct b200md_topology {
   void* blob = nullptr;
   std::vector<uint32_t> mask_rows;  // [natoms][4], bit j set <=> pair (i, j) not evaluated
   int occ_forces[2] = {0, 0}, occ_integrate[2] = {0, 0};
+  // solutes above 128 atoms (b200md_large.cuh): the per-replica state no longer fits one CTA
+  bool large = false;
+  LargeTopo ldev{};
+  int mask_words = 4;  // uint32 words per row of mask_rows
 };
 
 namespace {
@@ -569,10 +574,12 @@ int query_occupancy(K kernel, int smem) {
 
 }  // namespace
 
+static b200md_topology* create_large(const b200md_topology_desc* d, int device);
+
 extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d, int device) {
   if (!d || d->natoms <= 0 || d->ntypes <= 0) { fail(B200MD_ERR_INVALID_ARGUMENT, "empty topology"); return nullptr; }
-  if (d->natoms > kMaxAtoms) {
-    fail(B200MD_ERR_TOO_MANY_ATOMS, "natoms > 128: the one-CTA-per-replica kernels hold a replica on chip");
+  if (d->natoms > B200MD_MAX_ATOMS_LARGE) {
+    fail(B200MD_ERR_TOO_MANY_ATOMS, "natoms > 32768: the all-pairs kernels keep a dense exclusion bit matrix");
     return nullptr;
   }
   const int N = d->natoms, NT = d->ntypes;
@@ -588,6 +595,8 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   }
   for (int a = 0; a < N; ++a)
     if (d->atom_type[a] < 0 || d->atom_type[a] >= NT) { fail(B200MD_ERR_INVALID_ARGUMENT, "atom type out of range"); return nullptr; }
+
+  if (N > kMaxAtoms) return create_large(d, device);
 
   auto* topo = new b200md_topology();
   topo->device = device;
@@ -1024,6 +1033,202 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   return topo;
 }
 
+// ---- solutes above 128 atoms: packing (b200md_large.cuh) ---------------------------------------------------------
+static b200md_topology* create_large(const b200md_topology_desc* d, int device) {
+  const int N = d->natoms, NT = d->ntypes;
+  if (NT > 104) { fail(B200MD_ERR_UNSUPPORTED, "more than 104 LJ types: the type-pair tables must fit in shared memory"); return nullptr; }
+  auto* topo = new b200md_topology();
+  topo->device = device;
+  topo->natoms = N;
+  topo->large = true;
+  topo->dev.natoms = N; topo->dev.ntypes = NT;
+  topo->dev.ncons = -1;  // rigid bonds are a feature of the fused one-CTA-per-replica integrator
+  topo->dev.nphi = d->ndihedrals;
+  const int W = (N + 31) / 32, NP = 32 * W;
+  topo->mask_words = W;
+  // exclusion bit matrix from the pair list (= Forces.ava_idx): bit set <=> NOT evaluated; symmetric (full shell)
+  std::vector<uint32_t> mask((size_t)NP * W, 0xffffffffu);
+  for (int k = 0; k < d->npairs; ++k) {
+    const int i = d->pair_idx[2 * k], j = d->pair_idx[2 * k + 1];
+    if (i == j) continue;
+    mask[(size_t)i * W + j / 32] &= ~(1u << (j % 32));
+    mask[(size_t)j * W + i / 32] &= ~(1u << (i % 32));
+  }
+  topo->mask_rows.assign(mask.begin(), mask.begin() + (size_t)N * W);
+  std::vector<int> atype(NP, 0);
+  std::vector<float> charge(NP, 0.f), mass(NP, 1.f), t12a((size_t)NT * NT), t6b((size_t)NT * NT);
+  for (int a = 0; a < N; ++a) {
+    atype[a] = d->atom_type[a];
+    charge[a] = d->charge ? d->charge[a] : 0.f;
+    mass[a] = d->mass ? d->mass[a] : 1.f;
+  }
+  for (int k = 0; k < NT * NT; ++k) { t12a[k] = 12.0f * d->lj_a[k]; t6b[k] = 6.0f * d->lj_b[k]; }
+  std::vector<int2> bidx(d->nbonds), i14(d->n14);
+  std::vector<float2> bprm(d->nbonds), aprm(d->nangles);
+  std::vector<int> aidx(d->angle_idx, d->angle_idx + 3 * (size_t)d->nangles);
+  std::vector<float4> p14(d->n14);
+  for (int k = 0; k < d->nbonds; ++k) { bidx[k] = make_int2(d->bond_idx[2 * k], d->bond_idx[2 * k + 1]); bprm[k] = make_float2(d->bond_prm[2 * k], d->bond_prm[2 * k + 1]); }
+  for (int k = 0; k < d->nangles; ++k) aprm[k] = make_float2(d->angle_prm[2 * k], d->angle_prm[2 * k + 1]);
+  for (int k = 0; k < d->n14; ++k) { i14[k] = make_int2(d->idx14[2 * k], d->idx14[2 * k + 1]); p14[k] = make_float4(d->prm14[4 * k], d->prm14[4 * k + 1], d->prm14[4 * k + 2], d->prm14[4 * k + 3]); }
+  // torsion terms grouped by their quadruple, slice order kept inside a group (forces.py:559-576)
+  auto group_terms = [&](int n, const int32_t* idx, int nt, const int32_t* owner, const float* prm, const int32_t* harm,
+                         std::vector<int4>& q, std::vector<int>& start, std::vector<float4>& term) -> bool {
+    q.resize(n); start.assign(n + 1, 0); term.resize(nt);
+    for (int k = 0; k < n; ++k) q[k] = make_int4(idx[4 * k], idx[4 * k + 1], idx[4 * k + 2], idx[4 * k + 3]);
+    for (int t = 0; t < nt; ++t) { if (owner[t] < 0 || owner[t] >= n) return false; ++start[owner[t] + 1]; }
+    for (int k = 0; k < n; ++k) start[k + 1] += start[k];
+    std::vector<int> cur(start.begin(), start.end() - 1);
+    for (int t = 0; t < nt; ++t) term[cur[owner[t]]++] = make_float4(prm[3 * t], prm[3 * t + 1], prm[3 * t + 2], harm[t] ? 1.0f : 0.0f);
+    return true;
+  };
+  std::vector<int4> dq, iq; std::vector<int> ds, is; std::vector<float4> dt, it;
+  if (!group_terms(d->ndihedrals, d->dihedral_idx, d->ndihedral_terms, d->dihedral_term_owner, d->dihedral_term_prm, d->dihedral_term_harmonic, dq, ds, dt) ||
+      !group_terms(d->nimpropers, d->improper_idx, d->nimproper_terms, d->improper_term_owner, d->improper_term_prm, d->improper_term_harmonic, iq, is, it)) {
+    delete topo; fail(B200MD_ERR_INVALID_ARGUMENT, "torsion term owner out of range"); return nullptr;
+  }
+  BlobBuilder B;
+  const size_t o_type = B.add(atype), o_q = B.add(charge), o_m = B.add(mass), o_a = B.add(t12a), o_b = B.add(t6b), o_mask = B.add(mask),
+               o_bi = B.add(bidx), o_bp = B.add(bprm), o_ai = B.add(aidx), o_ap = B.add(aprm), o_dq = B.add(dq), o_ds = B.add(ds),
+               o_dt = B.add(dt), o_i14 = B.add(i14), o_p14 = B.add(p14), o_iq = B.add(iq), o_is = B.add(is), o_it = B.add(it);
+  cudaDeviceProp prop;
+  if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess ||
+      cudaMalloc(&topo->blob, B.bytes.size()) != cudaSuccess ||
+      cudaMemcpy(topo->blob, B.bytes.data(), B.bytes.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
+    if (topo->blob) cudaFree(topo->blob);
+    delete topo; fail(B200MD_ERR_CUDA, "device allocation of the packed topology failed"); return nullptr;
+  }
+  topo->num_sms = prop.multiProcessorCount;
+  const char* base = (const char*)topo->blob;
+  LargeTopo& L = topo->ldev;
+  L.natoms = N; L.ntypes = NT; L.nwords = W;
+  L.atom_type = (const int*)(base + o_type); L.charge = (const float*)(base + o_q); L.mass = (const float*)(base + o_m);
+  L.tab12a = (const float*)(base + o_a); L.tab6b = (const float*)(base + o_b); L.mask = (const uint32_t*)(base + o_mask);
+  L.nbonds = d->nbonds; L.nangles = d->nangles; L.ndih = d->ndihedrals; L.n14 = d->n14; L.nimp = d->nimpropers;
+  L.bond_idx = (const int2*)(base + o_bi); L.bond_prm = (const float2*)(base + o_bp);
+  L.angle_idx = (const int*)(base + o_ai); L.angle_prm = (const float2*)(base + o_ap);
+  L.dih_idx = (const int4*)(base + o_dq); L.dih_start = (const int*)(base + o_ds); L.dih_term = (const float4*)(base + o_dt);
+  L.idx14 = (const int2*)(base + o_i14); L.prm14 = (const float4*)(base + o_p14);
+  L.imp_idx = (const int4*)(base + o_iq); L.imp_start = (const int*)(base + o_is); L.imp_term = (const float4*)(base + o_it);
+  const int tab_bytes = 2 * NT * NT * (int)sizeof(float);
+  if (tab_bytes > 40 * 1024) {
+    cudaFuncSetAttribute(large_pairs_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tab_bytes);
+    cudaFuncSetAttribute(large_pairs_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tab_bytes);
+    cudaFuncSetAttribute(large_pairs_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tab_bytes);
+    cudaFuncSetAttribute(large_pairs_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tab_bytes);
+  }
+  g_last_error.clear();
+  return topo;
+}
+
+// Workspace of one large-solute call, stream-ordered (cudaMallocAsync): the int64 bonded-force accumulator, the per-CTA
+// energy partials, the per-replica energies / kinetic-energy partials / SMD record of the integrator.
+struct LargeWork {
+  cudaStream_t st;
+  long long* fbond = nullptr; double* partial = nullptr; double* energies = nullptr; double* ekin = nullptr; double* smd = nullptr;
+  int nbonded_blocks = 0, npart = 0, nek = 0;
+  ~LargeWork() {
+    if (fbond) cudaFreeAsync(fbond, st);
+    if (partial) cudaFreeAsync(partial, st);
+    if (energies) cudaFreeAsync(energies, st);
+    if (ekin) cudaFreeAsync(ekin, st);
+    if (smd) cudaFreeAsync(smd, st);
+  }
+};
+
+static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, bool smd, LargeWork& w) {
+  const LargeTopo& L = topo->ldev;
+  const long long items = (long long)L.nbonds + L.nangles + L.ndih + L.n14 + L.nimp;
+  // enough bonded CTAs to fill the GPU at small replica counts, never more than the items need
+  const long long want = std::max<long long>(1, (4ll * topo->num_sms + R - 1) / R);
+  w.nbonded_blocks = (int)std::max<long long>(1, std::min<long long>(want, (items + kLBondedThreads - 1) / kLBondedThreads));
+  w.npart = w.nbonded_blocks + L.nwords;
+  w.nek = (L.natoms + 255) / 256;
+  CUDA_TRY(cudaMallocAsync(&w.fbond, sizeof(long long) * 3 * (size_t)R * L.natoms, w.st));
+  CUDA_TRY(cudaMallocAsync(&w.partial, sizeof(double) * (size_t)R * w.npart * B200MD_NUM_ENERGIES, w.st));
+  if (integrator) {
+    CUDA_TRY(cudaMallocAsync(&w.energies, sizeof(double) * (size_t)R * B200MD_NUM_ENERGIES, w.st));
+    CUDA_TRY(cudaMallocAsync(&w.ekin, sizeof(double) * (size_t)R * w.nek, w.st));
+    if (smd) {
+      CUDA_TRY(cudaMallocAsync(&w.smd, sizeof(double) * 2 * (size_t)R, w.st));
+      CUDA_TRY(cudaMemsetAsync(w.smd, 0, sizeof(double) * 2 * (size_t)R, w.st));
+    }
+  }
+  return B200MD_OK;
+}
+
+// One Forces.compute over R replicas: zero the accumulator, bonded items, pair tiles (+ the force row), energies.
+static int large_forces(const b200md_topology* topo, const ForceParams& P, int64_t R, const float* pos, const float* box,
+                        float* forces, double* energies, uint32_t* status, double smd_center, bool with_energy, LargeWork& w) {
+  const LargeTopo& L = topo->ldev;
+  cudaStream_t st = w.st;
+  const int gy = (int)std::min<int64_t>(R, 65535);
+  CUDA_TRY(cudaMemsetAsync(w.fbond, 0, sizeof(long long) * 3 * (size_t)R * L.natoms, st));
+  large_bonded_kernel<<<dim3(w.nbonded_blocks, gy), kLBondedThreads, 0, st>>>(L, P, R, pos, box, w.fbond, w.partial, w.npart,
+                                                                             P.smd_centers, smd_center, w.smd);
+  const int tab_bytes = 2 * L.ntypes * L.ntypes * (int)sizeof(float);
+  const dim3 grid(L.nwords, gy);
+#define B200MD_LAUNCH_LPAIRS(M, E) \
+  large_pairs_kernel<M, E><<<grid, kLThreads, tab_bytes, st>>>(L, P, R, pos, box, w.fbond, forces, w.partial, w.npart, w.nbonded_blocks, status)
+  if (P.has_cutoff) { if (with_energy) B200MD_LAUNCH_LPAIRS(1, true); else B200MD_LAUNCH_LPAIRS(1, false); }
+  else { if (with_energy) B200MD_LAUNCH_LPAIRS(0, true); else B200MD_LAUNCH_LPAIRS(0, false); }
+#undef B200MD_LAUNCH_LPAIRS
+  g_launches.fetch_add(2);
+  if (with_energy) {
+    const long long n = (long long)R * B200MD_NUM_ENERGIES;
+    large_finish_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(R, w.partial, w.npart, energies);
+    g_launches.fetch_add(1);
+  }
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
+}
+
+static int large_forces_compute(const b200md_topology* topo, const ForceParams& P, int64_t R, const float* pos, const float* box,
+                                float* forces, double* energies, uint32_t* status, void* stream) {
+  LargeWork w;
+  w.st = (cudaStream_t)stream;
+  int rc = large_alloc(topo, R, false, false, w);
+  if (rc) return rc;
+  if (status) CUDA_TRY(cudaMemsetAsync(status, 0, sizeof(uint32_t) * (size_t)R, w.st));
+  return large_forces(topo, P, R, pos, box, forces, energies, status, (double)P.smd_c0, true, w);
+}
+
+// Integrator.step(niter) for large solutes: the upstream sequence as separate launches per step (the state lives in HBM)
+static int large_integrate(const b200md_topology* topo, const ForceParams& P, const StepParams& I, int64_t R, float* pos,
+                           float* vel, float* forces, const float* box, double* observables, float* snapshots,
+                           uint32_t* status, void* stream) {
+  const LargeTopo& L = topo->ldev;
+  LargeWork w;
+  w.st = (cudaStream_t)stream;
+  int rc = large_alloc(topo, R, true, P.smd_on != 0, w);
+  if (rc) return rc;
+  cudaStream_t st = w.st;
+  if (status) CUDA_TRY(cudaMemsetAsync(status, 0, sizeof(uint32_t) * (size_t)R, st));
+  const long long natom = (long long)R * L.natoms;
+  const size_t frame = sizeof(float) * 3 * (size_t)natom;
+  for (int s = 0; s < I.nsteps; ++s) {
+    const unsigned long long gstep = I.step0 + (unsigned long long)s;
+    const bool report = I.energy_every > 0 ? ((s + 1) % I.energy_every == 0) : (s == I.nsteps - 1);
+    large_vv1_kernel<<<(unsigned)((natom + 255) / 256), 256, 0, st>>>(L, I.dt, R, pos, vel, forces);
+    const double center = (double)P.smd_c0 + (double)P.smd_rate * (double)(gstep + 1);
+    rc = large_forces(topo, P, R, pos, box, forces, w.energies, status, center, report, w);
+    if (rc) return rc;
+    large_vv2_kernel<<<dim3(w.nek, (unsigned)std::min<int64_t>(R, 65535)), 256, 0, st>>>(L, I, gstep, R, vel, forces, pos, report ? w.ekin : nullptr, status);
+    g_launches.fetch_add(2);
+    if (report && observables != nullptr) {
+      const long long slot = I.energy_every > 0 ? (s + 1) / I.energy_every - 1 : 0;
+      large_observe_kernel<<<(unsigned)((R + 127) / 128), 128, 0, st>>>(R, w.energies, w.ekin, w.nek, w.smd,
+                                                                        observables + slot * R * B200MD_NUM_OBSERVABLES);
+      g_launches.fetch_add(1);
+    }
+    if (I.snapshot_every > 0 && snapshots != nullptr && (s + 1) % I.snapshot_every == 0) {
+      const long long slot = (s + 1) / I.snapshot_every - 1;
+      CUDA_TRY(cudaMemcpyAsync((char*)snapshots + slot * frame, pos, frame, cudaMemcpyDeviceToDevice, st));
+    }
+  }
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
+}
+
 extern "C" void b200md_topology_destroy(b200md_topology* topo) {
   if (!topo) return;
   cudaSetDevice(topo->device);
@@ -1035,6 +1240,7 @@ extern "C" int b200md_constrain(const b200md_topology* topo, int64_t R, float* p
                                 void* stream) {
   if (!topo || !pos) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
   if (R < 0) return fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica count");
+  if (topo->large) return fail(B200MD_ERR_UNSUPPORTED, "rigid bonds need natoms <= 128");
   if (topo->dev.ncons < 0)
     return fail(B200MD_ERR_UNSUPPORTED, "rigid_bonds: a hydrogen is bonded to a hydrogen, or a heavy atom carries more than 3");
   if (R == 0 || topo->dev.ncons == 0) return B200MD_OK;
@@ -1052,6 +1258,7 @@ extern "C" int b200md_dihedral_angles(const b200md_topology* topo, int64_t R, co
                                       float* phi, void* stream) {
   if (!topo || !pos || !phi) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
   if (R < 0) return fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica count");
+  if (topo->large) return fail(B200MD_ERR_UNSUPPORTED, "the dihedral-angle kernels need natoms <= 128");
   if (R == 0 || topo->dev.nphi == 0) return B200MD_OK;
   CUDA_TRY(cudaSetDevice(topo->device));
   const int grid = (int)std::min<long long>(R, (long long)topo->num_sms * 16);
@@ -1065,6 +1272,7 @@ extern "C" int b200md_dihedral_angles_backward(const b200md_topology* topo, int6
                                                const float* grad_phi, float* grad_pos, void* stream) {
   if (!topo || !pos || !grad_phi || !grad_pos) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
   if (R < 0) return fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica count");
+  if (topo->large) return fail(B200MD_ERR_UNSUPPORTED, "the dihedral-angle kernels need natoms <= 128");
   if (topo->dev.nphi > 512) return fail(B200MD_ERR_UNSUPPORTED, "dihedral-angle backward holds at most 512 dihedrals per replica");
   if (R == 0) return B200MD_OK;
   CUDA_TRY(cudaSetDevice(topo->device));
@@ -1084,6 +1292,7 @@ extern "C" int b200md_topology_exclusion_mask(const b200md_topology* topo, uint3
 }
 
 extern "C" int b200md_topology_natoms(const b200md_topology* topo) { return topo ? topo->natoms : -1; }
+extern "C" int b200md_topology_mask_words(const b200md_topology* topo) { return topo ? topo->mask_words : -1; }
 
 // ---- launch helpers ---------------------------------------------------------------------------------
 static int make_force_params(const b200md_topology* topo, const b200md_force_opts* o, const b200md_smd_opts* smd,
@@ -1150,6 +1359,10 @@ extern "C" int b200md_forces_compute(const b200md_topology* topo, const b200md_f
   ForceParams P;
   int rc = make_force_params(topo, opts, smd, false, &P);
   if (rc) return rc;
+  if (topo->large) {
+    CUDA_TRY(cudaSetDevice(topo->device));
+    return large_forces_compute(topo, P, R, pos, box, forces, energies, status, stream);
+  }
   DevTopo T = apply_terms(topo->dev, opts->terms);
   CUDA_TRY(cudaSetDevice(topo->device));
   const int mode = P.has_cutoff ? 1 : 0;
@@ -1172,6 +1385,8 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
   if (!topo || !io || !pos || !vel || !forces) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
   if (R < 0 || io->nsteps < 0) return fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica or step count");
   if (R == 0 || io->nsteps == 0) return B200MD_OK;
+  if (io->rigid_bonds != 0 && topo->large)
+    return fail(B200MD_ERR_UNSUPPORTED, "rigid_bonds needs natoms <= 128 (the constraint solve lives in the fused one-CTA-per-replica kernel)");
   if (io->rigid_bonds != 0 && topo->dev.ncons < 0)
     return fail(B200MD_ERR_UNSUPPORTED, "rigid_bonds: a hydrogen is bonded to a hydrogen, or a heavy atom carries more than 3");
   ForceParams P;
@@ -1183,6 +1398,7 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
   I.seed = io->seed; I.step0 = io->step0; I.replica0 = io->replica0;
   I.nsteps = io->nsteps; I.energy_every = io->energy_every; I.snapshot_every = io->snapshot_every;
   CUDA_TRY(cudaSetDevice(topo->device));
+  if (topo->large) return large_integrate(topo, P, I, R, pos, vel, forces, box, observables, snapshots, status, stream);
   const int mode = P.has_cutoff ? 1 : 0;
   // long launches: one CTA per replica, so the hardware block scheduler hands a finished SM its next replica
   // (a static grid-stride split of 8 192 replicas over 740 resident CTAs ends with a 12th round on 52 CTAs);

@@ -164,9 +164,11 @@ class Forces:
             pass
 
     def exclusion_mask(self, device="cuda"):
-        """(natoms, 4) uint32 bitmask the kernels use (bit j of row i set <=> pair not evaluated)."""
+        """(natoms, W) uint32 bitmask the kernels use (bit j % 32 of word j // 32 of row i set <=> pair (i, j) not
+        evaluated); W = 4 up to 128 atoms, ceil(natoms / 32) for the large-solute kernels."""
         h = self._handle(torch.device(device))
-        out = np.zeros((self.natoms, 4), dtype=np.uint32)
+        words = _cabi.load_library().b200md_topology_mask_words(C.c_void_p(h))
+        out = np.zeros((self.natoms, words), dtype=np.uint32)
         _check(_cabi.load_library().b200md_topology_exclusion_mask(C.c_void_p(h), out.ctypes.data_as(C.c_void_p)))
         return out
 

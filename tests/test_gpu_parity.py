@@ -986,3 +986,106 @@ def test_chamber_energies_on_gpu_against_namd_at_the_restart_frame():
     assert abs(res["full"][slot("angles")] + ub - namd["ANGLE"]) < 2e-3
     assert abs(res["full"][slot("dihedrals")] - namd["DIHED"]) < 2e-3
     assert abs(res["full"][slot("impropers")] - namd["IMPRP"]) < 2e-3
+
+
+# ---- solutes above 128 atoms: the large-solute kernels (csrc/b200md_large.cuh) --------------------------------------
+@pytest.mark.parametrize("natoms,seed", [(129, 30), (160, 31), (257, 32), (300, 33), (1000, 34)])
+def test_large_solute_forces_vs_oracle(natoms, seed):
+    """SURVEY 8f N4 (larger solutes, e.g. the adk system named at V_Calculations/Test-10_diALA/potcalc.py:114): above 128
+    atoms the same Forces.compute runs as bonded-item + 32 x 32 pair-tile kernels; same tolerances as the on-chip path."""
+    g = _RandomMolecule(natoms, seed, R=2)
+    for mode in ("plain", "rf"):
+        f_ref, e_ref = oracle.forces(g.packed, g.pos, **MODES[mode])
+        f, e, F = run_gpu(g, g.pos, **MODES[mode])
+        ferr = np.abs(f - f_ref).reshape(len(f), -1).max(1) / np.abs(f_ref).reshape(len(f), -1).max(1)
+        assert ferr.max() < 1e-5, (mode, ferr.max())
+        coul, lj = pair_scales(g, g.pos)
+        scale = np.abs(e_ref).sum(1) + coul + lj + torsion_scale(g.par, "dihedrals") + torsion_scale(g.par, "impropers")
+        assert (np.abs(e - e_ref).max(1) <= 1e-6 * scale).all(), (mode, (np.abs(e - e_ref).max(1) / scale).max())
+        # bonded kinds run in FP64: their slots agree with the oracle far below the fp32 pair tolerance
+        for slot in (2, 3, 4, 6):
+            np.testing.assert_allclose(e[:, slot], e_ref[:, slot], rtol=1e-9, atol=1e-9)
+        np.testing.assert_array_equal(F.ava_idx.cpu().numpy().reshape(-1, 2), g.ava_idx.reshape(-1, 2))
+    # integer artefact: the exclusion bit matrix is the complement of the reference's pair list
+    m = F.exclusion_mask(DEV)
+    assert m.shape == (natoms, (natoms + 31) // 32)
+    bits = ((m[:, :, None] >> np.arange(32, dtype=np.uint32)) & 1).reshape(natoms, -1)[:, :natoms].astype(bool)
+    allowed = np.zeros((natoms, natoms), bool)
+    allowed[g.ava_idx[:, 0], g.ava_idx[:, 1]] = allowed[g.ava_idx[:, 1], g.ava_idx[:, 0]] = True
+    np.testing.assert_array_equal(~bits, allowed)
+
+
+def test_large_solute_term_subsets_box_and_smd_vs_oracle():
+    g = _RandomMolecule(200, 40, R=3)
+    # per-replica boxes (one replica in vacuum), cutoff / reaction field / switch
+    box = np.zeros((3, 3, 3), dtype=np.float32)
+    for r, b in enumerate(([31.0, 28.0, 40.0], [0.0, 0.0, 0.0], [26.0, 33.0, 37.0])):
+        box[r, 0, 0], box[r, 1, 1], box[r, 2, 2] = b
+    par = gpu_par(g)
+    p = torch.tensor(g.pos, device=DEV)
+    s = System(200, 3, torch.float, DEV)
+    s.box[:] = torch.tensor(box, device=DEV)
+    F = Forces(par, **MODES["rf"])
+    e = F.compute_batch(p, s.box, s.forces).cpu().numpy()
+    f_ref, e_ref = oracle.forces(g.packed, g.pos, box=box.reshape(3, 9), **MODES["rf"])
+    f = s.forces.cpu().numpy()
+    assert np.abs(f - f_ref).max() / np.abs(f_ref).max() < 1e-5
+    coul, lj = pair_scales(g, g.pos)
+    assert (np.abs(e - e_ref).max(1) <= 3e-6 * (np.abs(e_ref).sum(1) + coul + lj)).all()
+    # term subsets + the SMD restraint with per-replica centres
+    smd = dict(atom1=3, atom2=190, fk=1.5, center0=0.0)
+    cen = np.array([150.0, 160.0, 170.0], dtype=np.float32)
+    for terms in (("bonds", "angles"), ("lj",), ("electrostatics", "dihedrals", "1-4"), ("repulsion", "impropers")):
+        f_ref, e_ref = oracle.forces(g.packed, g.pos, smd=smd, smd_centers=cen, terms=terms)
+        f, e, _ = run_gpu(g, g.pos, smd=smd, centers=cen, terms=terms)
+        assert np.abs(f - f_ref).max() / np.abs(f_ref).max() < 1e-5, terms
+        np.testing.assert_allclose(e, e_ref, rtol=2e-6, atol=2e-6 * np.abs(e_ref).max())
+
+
+def test_large_solute_integrator_vs_oracle_and_bitwise_determinism():
+    g = _RandomMolecule(300, 41, R=3)
+    vel0 = (0.02 * np.random.default_rng(41).standard_normal(g.pos.shape)).astype(np.float32)
+    rate = 1e-3
+
+    def run(replica0=500, sl=slice(None)):
+        par, s = make_system(g, g.pos[sl], vel0[sl])
+        F = Forces(par, external=SMDBias([3], [290], fk=1.0, cent_0=240.0, rate_per_step=rate))
+        F.compute_batch(s.pos, s.box, s.forces)
+        f0 = s.forces.cpu().numpy().astype(np.float64)
+        integ = Integrator(s, F, timestep=0.5, device=DEV, gamma=1.0, T=300.0, seed=9)
+        integ.energy_every = 5
+        integ.snapshot_every = 10
+        integ.replica0 = replica0
+        integ.step(niter=20)
+        return s, integ, f0
+
+    s, integ, f0 = run()
+    out = oracle.integrate(g.packed, g.pos, vel0, f0, nsteps=20, dt=np.float32(integ.dt), gamma=np.float32(integ.gamma),
+                           temperature=300.0, seed=9, replica0=500, energy_every=5, snapshot_every=10,
+                           smd=dict(atom1=3, atom2=290, fk=1.0, center0=240.0, center_rate=np.float32(rate)))
+    assert np.abs(s.pos.cpu().numpy() - out["pos"]).max() < 3e-4
+    assert np.abs(s.vel.cpu().numpy() - out["vel"]).max() < 3e-4 * max(1.0, np.abs(out["vel"]).max())
+    obs, ref = integ.observables.cpu().numpy(), out["observables"]
+    sc = np.abs(ref[:, :, :8]).sum(-1) + 1.0
+    assert (np.abs(obs[:, :, :8].sum(-1) - ref[:, :, :8].sum(-1)) <= 2e-4 * sc).all()
+    np.testing.assert_allclose(obs[:, :, _cabi.OBS_EKIN], ref[:, :, _cabi.OBS_EKIN], rtol=1e-3)
+    np.testing.assert_allclose(obs[:, :, _cabi.OBS_E2E_DIST], ref[:, :, _cabi.OBS_E2E_DIST], rtol=1e-5)
+    np.testing.assert_allclose(obs[:, :, _cabi.OBS_SMD_WORK], ref[:, :, _cabi.OBS_SMD_WORK], rtol=1e-4, atol=1e-7)
+    assert np.abs(integ.snapshots.cpu().numpy() - out["snapshots"]).max() < 3e-4
+    # same run again, and replica 2 alone as its own shard: bit-identical (integer force accumulation, fixed-order
+    # reductions, RNG keyed by the global replica index)
+    s2, integ2, _ = run()
+    assert torch.equal(s.pos, s2.pos) and torch.equal(s.vel, s2.vel) and torch.equal(integ.observables, integ2.observables)
+    s3, integ3, _ = run(replica0=502, sl=slice(2, 3))
+    assert torch.equal(s.pos[2:3], s3.pos) and torch.equal(integ.observables[:, 2:3], integ3.observables)
+
+
+def test_large_solute_unsupported_options_raise():
+    g = _RandomMolecule(140, 42, R=1)
+    par, s = make_system(g, g.pos, np.zeros_like(g.pos))
+    F = Forces(par)
+    F.compute_batch(s.pos, s.box, s.forces)
+    with pytest.raises((RuntimeError, NotImplementedError, ValueError)):
+        Integrator(s, F, timestep=1.0, device=DEV, rigid_bonds=True).step(niter=1)
+    with pytest.raises((RuntimeError, NotImplementedError, ValueError)):
+        F.dihedral_angles(s.pos)
