@@ -451,6 +451,34 @@ def run_ours(args):
                                                  "md_steps_per_launch": nst, "dt_fs": 2.0,
                                                  "ns_per_day_aggregate": R * nst / t4 * 2.0 * 86400 * 1e-6}
 
+        # SURVEY 8f N4, solutes above 128 atoms (csrc/b200md_large.cuh): a bundle of 10 deca-alanine chains as ONE
+        # 1 040-atom topology (Parameters.tiled), chains 40 A apart on a line; Forces.compute and Langevin steps
+        copies, RL = 10, 256
+        parL = par.tiled(copies)
+        NL = 104 * copies
+        shift = torch.arange(copies, device=dev, dtype=torch.float32).repeat_interleave(104)[None, :, None] * \
+            torch.tensor([40.0, 0.0, 0.0], device=dev)
+        posL = torch.tensor(pos_h[:RL], device=dev).repeat(1, copies, 1) + shift
+        sysL = System(NL, RL, torch.float, dev)
+        sysL.pos[:] = posL
+        sysL.vel[:] = torch.tensor(vel_h[:RL], device=dev).repeat(1, copies, 1)
+        fL = Forces(parL)
+        fL.check_nan = False
+        npairL = int(fL.ava_idx.shape[0])
+        tL = timed(lambda: fL.compute_batch(sysL.pos, sysL.box, sysL.forces), 3)
+        flopL = 36 * npairL + copies * (FLOP_PER_REPLICA_EVAL - 36 * 4820)
+        extra["large_solute_1040_atoms_forces_compute"] = {
+            "value": RL / tL, "unit": "replica-evaluations/s", "replicas": RL, "natoms": NL, "unique_pairs": npairL,
+            "ms_per_call": 1e3 * tL, "tflops": RL / tL * flopL / 1e12, "launches_per_call": 4,
+            "note": "full-shell pair tiles: every pair is evaluated from both of its atoms, the flop count credits it once"}
+        integL = Integrator(sysL, fL, timestep=1.0, device=dev, gamma=1.0, T=300.0, seed=44)
+        integL.energy_every, integL.check_nan = 10, False
+        tL2 = timed(lambda: integL.step(niter=20), 2)
+        extra["large_solute_1040_atoms_langevin"] = {"value": RL * 20 / tL2, "unit": "replica-steps/s", "replicas": RL,
+                                                    "natoms": NL, "md_steps_per_call": 20,
+                                                    "tflops": RL * 20 / tL2 * (flopL + 60 * NL) / 1e12}
+        del sysL, posL
+
     if rank == 0:
         peak = lib.b200md_fp32_peak_tflops(local, 4096)
         achieved = value / world * FLOP_PER_REPLICA_STEP / 1e12  # per GPU

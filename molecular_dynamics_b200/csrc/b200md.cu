@@ -459,6 +459,11 @@ struct b200md_topology {
   bool large = false;
   LargeTopo ldev{};
   int mask_words = 4;  // uint32 words per row of mask_rows
+  // grow-only device workspace of the large-solute calls (bonded-force accumulator, energy partials ...), reused from
+  // call to call: stream-ordered on `ws_stream`; a call on another stream first waits for that one
+  mutable void* ws = nullptr;
+  mutable size_t ws_bytes = 0;
+  mutable cudaStream_t ws_stream = nullptr;
 };
 
 namespace {
@@ -1120,19 +1125,12 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   return topo;
 }
 
-// Workspace of one large-solute call, stream-ordered (cudaMallocAsync): the int64 bonded-force accumulator, the per-CTA
-// energy partials, the per-replica energies / kinetic-energy partials / SMD record of the integrator.
+// Workspace of one large-solute call, carved from the topology's grow-only device buffer: the int64 bonded-force
+// accumulator, the per-CTA energy partials, the per-replica energies / kinetic-energy partials / SMD record of the integrator.
 struct LargeWork {
   cudaStream_t st;
   long long* fbond = nullptr; double* partial = nullptr; double* energies = nullptr; double* ekin = nullptr; double* smd = nullptr;
   int nbonded_blocks = 0, npart = 0, nek = 0;
-  ~LargeWork() {
-    if (fbond) cudaFreeAsync(fbond, st);
-    if (partial) cudaFreeAsync(partial, st);
-    if (energies) cudaFreeAsync(energies, st);
-    if (ekin) cudaFreeAsync(ekin, st);
-    if (smd) cudaFreeAsync(smd, st);
-  }
 };
 
 static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, bool smd, LargeWork& w) {
@@ -1143,13 +1141,26 @@ static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, 
   w.nbonded_blocks = (int)std::max<long long>(1, std::min<long long>(want, (items + kLBondedThreads - 1) / kLBondedThreads));
   w.npart = w.nbonded_blocks + L.nwords;
   w.nek = (L.natoms + 255) / 256;
-  CUDA_TRY(cudaMallocAsync(&w.fbond, sizeof(long long) * 3 * (size_t)R * L.natoms, w.st));
-  CUDA_TRY(cudaMallocAsync(&w.partial, sizeof(double) * (size_t)R * w.npart * B200MD_NUM_ENERGIES, w.st));
+  auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+  const size_t b_f = up(sizeof(long long) * 3 * (size_t)R * L.natoms), b_p = up(sizeof(double) * (size_t)R * w.npart * B200MD_NUM_ENERGIES);
+  const size_t b_e = integrator ? up(sizeof(double) * (size_t)R * B200MD_NUM_ENERGIES) : 0, b_k = integrator ? up(sizeof(double) * (size_t)R * w.nek) : 0;
+  const size_t b_s = (integrator && smd) ? up(sizeof(double) * 2 * (size_t)R) : 0;
+  const size_t total = b_f + b_p + b_e + b_k + b_s;
+  if (topo->ws != nullptr && topo->ws_stream != w.st) CUDA_TRY(cudaStreamSynchronize(topo->ws_stream));
+  if (total > topo->ws_bytes) {
+    if (topo->ws != nullptr) { CUDA_TRY(cudaStreamSynchronize(topo->ws_stream)); cudaFree(topo->ws); topo->ws = nullptr; topo->ws_bytes = 0; }
+    CUDA_TRY(cudaMalloc(&topo->ws, total));
+    topo->ws_bytes = total;
+  }
+  topo->ws_stream = w.st;
+  char* base = (char*)topo->ws;
+  w.fbond = (long long*)base; base += b_f;
+  w.partial = (double*)base; base += b_p;
   if (integrator) {
-    CUDA_TRY(cudaMallocAsync(&w.energies, sizeof(double) * (size_t)R * B200MD_NUM_ENERGIES, w.st));
-    CUDA_TRY(cudaMallocAsync(&w.ekin, sizeof(double) * (size_t)R * w.nek, w.st));
+    w.energies = (double*)base; base += b_e;
+    w.ekin = (double*)base; base += b_k;
     if (smd) {
-      CUDA_TRY(cudaMallocAsync(&w.smd, sizeof(double) * 2 * (size_t)R, w.st));
+      w.smd = (double*)base;
       CUDA_TRY(cudaMemsetAsync(w.smd, 0, sizeof(double) * 2 * (size_t)R, w.st));
     }
   }
@@ -1233,6 +1244,7 @@ extern "C" void b200md_topology_destroy(b200md_topology* topo) {
   if (!topo) return;
   cudaSetDevice(topo->device);
   if (topo->blob) cudaFree(topo->blob);
+  if (topo->ws) cudaFree(topo->ws);
   delete topo;
 }
 

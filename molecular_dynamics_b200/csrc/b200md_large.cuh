@@ -14,7 +14,8 @@
 //   large_finish_kernel  per-replica energies = fixed-order sum of the per-CTA FP64 partials;
 //   large_vv1 / large_vv2 / large_observe   the velocity-Verlet halves, the Langevin kick (same Philox stream as the
 //                        fused kernel: keyed by seed, global replica, atom, global step) and the observable record.
-// Pair arithmetic is the scalar pair_eval<MODE, ENERGY> of b200md_forces.cuh (FP32 with FP64 energy accumulation).
+// Pair arithmetic is the packed pair_eval2<MODE, ENERGY> of b200md_forces.cuh (two j atoms per FFMA2 issue slot, FP32
+// with FP64 energy accumulation).
 #pragma once
 #include "b200md_forces.cuh"
 
@@ -227,35 +228,52 @@ large_bonded_kernel(const LargeTopo T, const ForceParams P, const long long R, c
 }
 
 // grid (nwords, min(R, 65535)).  Shared memory: the two type-pair tables (2 ntypes^2 floats, dynamic) + statics.
+// The j tile of a warp is staged structure-of-arrays (x[32], y[32], z[32], q[32], type[32]) so that one broadcast LDS.64
+// delivers the operands of TWO j atoms as a packed f32x2: the pair arithmetic is pair_eval2 (FFMA2 / FMUL2 / FADD2, one
+// issue slot per two pairs), like the on-chip tiles.
 template <int MODE, bool ENERGY, bool PBC>
 __device__ __forceinline__ void large_pairs_body(const LargeTopo& T, const ForceParams& P, const float* __restrict__ p,
-                                                 const float* sA, const float* sB, float4* sj, int* stj, const float3 nbox,
-                                                 const float3 ibox, int ib, int warp, int lane, float xi, float yi, float zi,
-                                                 float kqi, int trow, float& fx, float& fy, float& fz, double& eel, double& elj) {
+                                                 const float* sA, const float* sB, float* sj /* [4][32] */, int* stj,
+                                                 const float3 nbox, const float3 ibox, int ib, int warp, int lane, float xi,
+                                                 float yi, float zi, float kqi, int trow, float& fx, float& fy, float& fz,
+                                                 double& eel, double& elj) {
   const int N = T.natoms;
   const uint32_t* mrow = T.mask + (size_t)(32 * ib + lane) * T.nwords;
+  const PairConst C = make_pair_const<MODE>(P);
+  const u64 xi2 = dup2(xi), yi2 = dup2(yi), zi2 = dup2(zi), kq2 = dup2(kqi);
+  const float* tA = sA + trow;
+  const float* tB = sB + trow;
+  u64 ax = 0ull, ay = 0ull, az = 0ull;
   for (int jt = warp; jt < T.nwords; jt += kLThreads / 32) {
     const int j = 32 * jt + lane;
-    float4 pj = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (j < N) pj = make_float4(__ldg(p + 3 * j), __ldg(p + 3 * j + 1), __ldg(p + 3 * j + 2), __ldg(T.charge + j) * P.el_on);
-    __syncwarp();
-    sj[lane] = pj;
-    stj[lane] = __ldg(T.atom_type + j);
-    __syncwarp();
+    float jx = 0.f, jy = 0.f, jz = 0.f, jq = 0.f;
+    if (j < N) { jx = __ldg(p + 3 * j); jy = __ldg(p + 3 * j + 1); jz = __ldg(p + 3 * j + 2); jq = __ldg(T.charge + j) * P.el_on; }
+    const int jtype = __ldg(T.atom_type + j);
     const uint32_t m = __ldg(mrow + jt);
+    __syncwarp();
+    sj[lane] = jx; sj[32 + lane] = jy; sj[64 + lane] = jz; sj[96 + lane] = jq;
+    stj[lane] = jtype;
+    __syncwarp();
     if (__all_sync(0xffffffffu, m == 0xffffffffu)) continue;
-    float pel = 0.0f, plj = 0.0f;
+    u64 pel = 0ull, plj = 0ull;
 #pragma unroll 4
-    for (int jj = 0; jj < 32; ++jj) {
-      const float4 q = sj[jj];
-      const int tj = stj[jj];
-      float dx = __fsub_rn(xi, q.x), dy = __fsub_rn(yi, q.y), dz = __fsub_rn(zi, q.z);
-      if (PBC) { dx = wrap1(dx, nbox.x, ibox.x); dy = wrap1(dy, nbox.y, ibox.y); dz = wrap1(dz, nbox.z, ibox.z); }
-      const float s = pair_eval<MODE, ENERGY>(dx, dy, dz, kqi, q.w, sA[trow + tj], sB[trow + tj], (m >> jj) & 1u, P, pel, plj);
-      fx = __fmaf_rn(s, dx, fx); fy = __fmaf_rn(s, dy, fy); fz = __fmaf_rn(s, dz, fz);
+    for (int jj = 0; jj < 32; jj += 2) {
+      const u64 xj = *(const u64*)(sj + jj), yj = *(const u64*)(sj + 32 + jj), zj = *(const u64*)(sj + 64 + jj);
+      const u64 qj = *(const u64*)(sj + 96 + jj);
+      const int2 tj = *(const int2*)(stj + jj);
+      const u64 a12 = pk(tA[tj.x], tA[tj.y]), nb6 = pk(tB[tj.x], tB[tj.y]);
+      u64 dx = sub2(xi2, xj), dy = sub2(yi2, yj), dz = sub2(zi2, zj);
+      if (PBC) { dx = wrap2(dx, nbox.x, ibox.x); dy = wrap2(dy, nbox.y, ibox.y); dz = wrap2(dz, nbox.z, ibox.z); }
+      const u64 sc = pair_eval2<MODE, ENERGY>(dx, dy, dz, kqi, kq2, qj, a12, nb6, (m >> jj) & 1u, (m >> (jj + 1)) & 1u, P, C, pel, plj);
+      ax = fma2(sc, dx, ax); ay = fma2(sc, dy, ay); az = fma2(sc, dz, az);
     }
-    if (ENERGY) { eel += (double)pel; elj += (double)plj; }
+    if (ENERGY) {  // FP32 partial sums of one tile (2 x 16 pairs per lane), folded into FP64 once
+      float a, b;
+      upk(pel, a, b); eel += (double)a + (double)b;
+      upk(plj, a, b); elj += (double)(MODE == 0 ? __fmul_rn(__fadd_rn(a, b), 1.0f / 12.0f) : __fadd_rn(a, b));
+    }
   }
+  fx = hsum2(ax); fy = hsum2(ay); fz = hsum2(az);
 }
 
 template <int MODE, bool ENERGY>
@@ -266,8 +284,8 @@ large_pairs_kernel(const LargeTopo T, const ForceParams P, const long long R, co
   extern __shared__ __align__(16) char lsmem[];
   float* sA = (float*)lsmem;
   float* sB = sA + T.ntypes * T.ntypes;
-  __shared__ float4 sj[kLThreads / 32][32];
-  __shared__ int stj[kLThreads / 32][32];
+  __shared__ __align__(16) float sj[kLThreads / 32][4 * 32];
+  __shared__ __align__(16) int stj[kLThreads / 32][32];
   __shared__ float sf[kLThreads / 32][3][32];
   __shared__ double sred[(kLThreads / 32) * 2];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;

@@ -131,6 +131,25 @@ class Parameters:
         par.to_(device)
         return par
 
+    def tiled(self, copies):
+        """Parameters of ``copies`` identical molecules side by side in one topology (a bundle of chains): atom
+        indices of copy c are shifted by c * natoms, per-atom and per-item parameters are repeated, the type-pair tables
+        are shared.  Molecules of one topology interact through the non-bonded terms like any other atoms."""
+        a = self.to_arrays()
+        n = len(a["masses"])
+        out = {}
+        for k, v in a.items():
+            if k in ("A", "B") or k.endswith("_nslices"):
+                out[k] = v
+            elif k in ("bonds", "angles", "dihedrals", "idx14", "impropers"):
+                out[k] = np.concatenate([v + c * n for c in range(copies)])
+            elif k.startswith(("dihedral_idx_", "improper_idx_")):
+                rows = len(a["dihedrals" if k.startswith("dihedral") else "impropers"])
+                out[k] = np.concatenate([v + c * rows for c in range(copies)])
+            else:  # per-atom arrays, per-item parameter rows, per-slice parameter rows
+                out[k] = np.concatenate([v] * copies)
+        return Parameters.from_arrays(out, precision=self.precision, device=self.device)
+
     def save(self, path):
         np.savez_compressed(path, **self.to_arrays())
 

@@ -220,3 +220,24 @@ def test_namd_restart_files_against_the_chamber_prmtop():
     assert 200.0 < temp < 400.0
     with pytest.raises(ValueError):
         read_namd_bin(os.path.join(gold, "smd_out.restart.xsc"))
+
+
+def test_parameters_tiled_is_copies_of_the_molecule():
+    """Parameters.tiled (bundle of chains in one topology, used by the large-solute bench): bonded energies of three
+    far-apart copies are three times the molecule's, the pair list grows by the inter-molecular pairs."""
+    import oracle
+    from molecular_dynamics_b200 import Parameters, _cabi
+
+    with np.load(os.path.join(os.path.dirname(__file__), "golden", "ala10.npz")) as z:
+        g = {k: z[k] for k in z.files}
+    par = Parameters.from_arrays({k[4:]: v for k, v in g.items() if k.startswith("par_")})
+    p3 = par.tiled(3)
+    assert len(p3.masses) == 312 and len(p3.bonds) == 3 * len(par.bonds) and len(p3.idx14) == 3 * len(par.idx14)
+    idx1 = _cabi.make_pair_index(104, par.get_exclusions())
+    idx3 = _cabi.make_pair_index(312, p3.get_exclusions())
+    assert len(idx3) == 3 * len(idx1) + 3 * 104 * 104
+    pos = g["pos"][:1]
+    pos3 = np.concatenate([pos + np.float32(64.0 * c) for c in range(3)], 1)
+    _, e1 = oracle.forces(_cabi.PackedTopology(par, idx1), pos)
+    _, e3 = oracle.forces(_cabi.PackedTopology(p3, idx3), pos3)
+    np.testing.assert_allclose(e3[0, 2:5], 3 * e1[0, 2:5], rtol=2e-5)
