@@ -1114,7 +1114,7 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   L.dih_idx = (const int4*)(base + o_dq); L.dih_start = (const int*)(base + o_ds); L.dih_term = (const float4*)(base + o_dt);
   L.idx14 = (const int2*)(base + o_i14); L.prm14 = (const float4*)(base + o_p14);
   L.imp_idx = (const int4*)(base + o_iq); L.imp_start = (const int*)(base + o_is); L.imp_term = (const float4*)(base + o_it);
-  const int tab_bytes = 2 * NT * NT * (int)sizeof(float);
+  const int tab_bytes = 2 * NT * large_tab_stride(NT) * (int)sizeof(float);
   if (tab_bytes > 40 * 1024) {
     cudaFuncSetAttribute(large_pairs_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tab_bytes);
     cudaFuncSetAttribute(large_pairs_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tab_bytes);
@@ -1137,7 +1137,7 @@ static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, 
   const LargeTopo& L = topo->ldev;
   const long long items = (long long)L.nbonds + L.nangles + L.ndih + L.n14 + L.nimp;
   // enough bonded CTAs to fill the GPU at small replica counts, never more than the items need
-  const long long want = std::max<long long>(1, (4ll * topo->num_sms + R - 1) / R);
+  const long long want = std::max<long long>(1, (16ll * topo->num_sms + R - 1) / R);
   w.nbonded_blocks = (int)std::max<long long>(1, std::min<long long>(want, (items + kLBondedThreads - 1) / kLBondedThreads));
   w.npart = w.nbonded_blocks + L.nwords;
   w.nek = (L.natoms + 255) / 256;
@@ -1176,7 +1176,7 @@ static int large_forces(const b200md_topology* topo, const ForceParams& P, int64
   CUDA_TRY(cudaMemsetAsync(w.fbond, 0, sizeof(long long) * 3 * (size_t)R * L.natoms, st));
   large_bonded_kernel<<<dim3(w.nbonded_blocks, gy), kLBondedThreads, 0, st>>>(L, P, R, pos, box, w.fbond, w.partial, w.npart,
                                                                              P.smd_centers, smd_center, w.smd);
-  const int tab_bytes = 2 * L.ntypes * L.ntypes * (int)sizeof(float);
+  const int tab_bytes = 2 * L.ntypes * large_tab_stride(L.ntypes) * (int)sizeof(float);
   const dim3 grid(L.nwords, gy);
 #define B200MD_LAUNCH_LPAIRS(M, E) \
   large_pairs_kernel<M, E><<<grid, kLThreads, tab_bytes, st>>>(L, P, R, pos, box, w.fbond, forces, w.partial, w.npart, w.nbonded_blocks, status)

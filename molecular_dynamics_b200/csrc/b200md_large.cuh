@@ -227,33 +227,50 @@ large_bonded_kernel(const LargeTopo T, const ForceParams P, const long long R, c
   }
 }
 
+template <int OFF>
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v) : "r"(addr), "n"(OFF));
+  return v;
+}
+// Row stride of the shared-memory type-pair table in entries: odd, so that the (12 A, -6 B) entries of one column sit
+// in distinct banks for up to 16 row types (lanes differ in their row = type of i, the column = type of j is uniform)
+__host__ __device__ inline int large_tab_stride(int ntypes) { return ntypes | 1; }
+
 // grid (nwords, min(R, 65535)).  Shared memory: the two type-pair tables (2 ntypes^2 floats, dynamic) + statics.
 // The j tile of a warp is staged structure-of-arrays (x[32], y[32], z[32], q[32], type[32]) so that one broadcast LDS.64
 // delivers the operands of TWO j atoms as a packed f32x2: the pair arithmetic is pair_eval2 (FFMA2 / FMUL2 / FADD2, one
 // issue slot per two pairs), like the on-chip tiles.
 template <int MODE, bool ENERGY, bool PBC>
 __device__ __forceinline__ void large_pairs_body(const LargeTopo& T, const ForceParams& P, const float* __restrict__ p,
-                                                 const float* sA, const float* sB, float* sj /* [4][32] */, int* stj,
+                                                 const uint32_t tbase, float* sj /* [4][32] */, int* stj,
                                                  const float3 nbox, const float3 ibox, int ib, int warp, int lane, float xi,
-                                                 float yi, float zi, float kqi, int trow, float& fx, float& fy, float& fz,
+                                                 float yi, float zi, float kqi, float& fx, float& fy, float& fz,
                                                  double& eel, double& elj) {
   const int N = T.natoms;
   const uint32_t* mrow = T.mask + (size_t)(32 * ib + lane) * T.nwords;
   const PairConst C = make_pair_const<MODE>(P);
   const u64 xi2 = dup2(xi), yi2 = dup2(yi), zi2 = dup2(zi), kq2 = dup2(kqi);
-  const float* tA = sA + trow;
-  const float* tB = sB + trow;
   u64 ax = 0ull, ay = 0ull, az = 0ull;
-  for (int jt = warp; jt < T.nwords; jt += kLThreads / 32) {
+  // the j atoms, their table offsets and the mask word of the NEXT tile are fetched while the current one is evaluated
+  float jx = 0.f, jy = 0.f, jz = 0.f, jq = 0.f;
+  int jtype = 0;
+  uint32_t mn = 0xffffffffu;
+  auto fetch = [&](int jt) {
     const int j = 32 * jt + lane;
-    float jx = 0.f, jy = 0.f, jz = 0.f, jq = 0.f;
+    jx = jy = jz = jq = 0.f;
     if (j < N) { jx = __ldg(p + 3 * j); jy = __ldg(p + 3 * j + 1); jz = __ldg(p + 3 * j + 2); jq = __ldg(T.charge + j) * P.el_on; }
-    const int jtype = __ldg(T.atom_type + j);
-    const uint32_t m = __ldg(mrow + jt);
+    jtype = __ldg(T.atom_type + j) * 8;  // byte offset of the (12 A, -6 B) entry in this lane's table row
+    mn = __ldg(mrow + jt);
+  };
+  if (warp < T.nwords) fetch(warp);
+  for (int jt = warp; jt < T.nwords; jt += kLThreads / 32) {
+    const uint32_t m = mn;
     __syncwarp();
     sj[lane] = jx; sj[32 + lane] = jy; sj[64 + lane] = jz; sj[96 + lane] = jq;
     stj[lane] = jtype;
     __syncwarp();
+    if (jt + kLThreads / 32 < T.nwords) fetch(jt + kLThreads / 32);
     if (__all_sync(0xffffffffu, m == 0xffffffffu)) continue;
     u64 pel = 0ull, plj = 0ull;
 #pragma unroll 4
@@ -261,7 +278,7 @@ __device__ __forceinline__ void large_pairs_body(const LargeTopo& T, const Force
       const u64 xj = *(const u64*)(sj + jj), yj = *(const u64*)(sj + 32 + jj), zj = *(const u64*)(sj + 64 + jj);
       const u64 qj = *(const u64*)(sj + 96 + jj);
       const int2 tj = *(const int2*)(stj + jj);
-      const u64 a12 = pk(tA[tj.x], tA[tj.y]), nb6 = pk(tB[tj.x], tB[tj.y]);
+      const u64 a12 = pk(lds_f32<0>(tbase + tj.x), lds_f32<0>(tbase + tj.y)), nb6 = pk(lds_f32<4>(tbase + tj.x), lds_f32<4>(tbase + tj.y));
       u64 dx = sub2(xi2, xj), dy = sub2(yi2, yj), dz = sub2(zi2, zj);
       if (PBC) { dx = wrap2(dx, nbox.x, ibox.x); dy = wrap2(dy, nbox.y, ibox.y); dz = wrap2(dz, nbox.z, ibox.z); }
       const u64 sc = pair_eval2<MODE, ENERGY>(dx, dy, dz, kqi, kq2, qj, a12, nb6, (m >> jj) & 1u, (m >> (jj + 1)) & 1u, P, C, pel, plj);
@@ -282,8 +299,8 @@ large_pairs_kernel(const LargeTopo T, const ForceParams P, const long long R, co
                    const float* __restrict__ box, const long long* __restrict__ fbond, float* __restrict__ forces,
                    double* __restrict__ partial, const int npart, const int part0, uint32_t* __restrict__ status) {
   extern __shared__ __align__(16) char lsmem[];
-  float* sA = (float*)lsmem;
-  float* sB = sA + T.ntypes * T.ntypes;
+  float* sAB = (float*)lsmem;  // [ntypes][stride] entries (12 A tab_a, 6 B tab_b)
+  const int tstride = large_tab_stride(T.ntypes);
   __shared__ __align__(16) float sj[kLThreads / 32][4 * 32];
   __shared__ __align__(16) int stj[kLThreads / 32][32];
   __shared__ float sf[kLThreads / 32][3][32];
@@ -291,12 +308,13 @@ large_pairs_kernel(const LargeTopo T, const ForceParams P, const long long R, co
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int N = T.natoms, ib = blockIdx.x;
   for (int k = tid; k < T.ntypes * T.ntypes; k += kLThreads) {
-    sA[k] = __ldg(T.tab12a + k) * P.tab_a;
-    sB[k] = __ldg(T.tab6b + k) * P.tab_b;
+    const int t = k / T.ntypes, u = k - t * T.ntypes;
+    sAB[2 * (t * tstride + u)] = __ldg(T.tab12a + k) * P.tab_a;
+    sAB[2 * (t * tstride + u) + 1] = __ldg(T.tab6b + k) * P.tab_b;
   }
   const int i = 32 * ib + lane;
   const bool live = i < N;
-  const int trow = __ldg(T.atom_type + i) * T.ntypes;
+  const uint32_t tbase = (uint32_t)__cvta_generic_to_shared(sAB) + (uint32_t)(__ldg(T.atom_type + i) * tstride * 8);
   const float kqi = __fmul_rn(__ldg(T.charge + i) * P.el_on, kElecFactor);
   const bool nonbonded = (P.terms & (B200MD_T_ELECTROSTATICS | B200MD_T_LJ | B200MD_T_REPULSION | B200MD_T_REPULSIONCG)) != 0;
   __syncthreads();
@@ -312,8 +330,8 @@ large_pairs_kernel(const LargeTopo T, const ForceParams P, const long long R, co
     float fx = 0.f, fy = 0.f, fz = 0.f;
     double e[2] = {0.0, 0.0};
     if (nonbonded) {
-      if (pbc) large_pairs_body<MODE, ENERGY, true>(T, P, p, sA, sB, sj[warp], stj[warp], nbox, ibox, ib, warp, lane, xi, yi, zi, kqi, trow, fx, fy, fz, e[0], e[1]);
-      else large_pairs_body<MODE, ENERGY, false>(T, P, p, sA, sB, sj[warp], stj[warp], nbox, ibox, ib, warp, lane, xi, yi, zi, kqi, trow, fx, fy, fz, e[0], e[1]);
+      if (pbc) large_pairs_body<MODE, ENERGY, true>(T, P, p, tbase, sj[warp], stj[warp], nbox, ibox, ib, warp, lane, xi, yi, zi, kqi, fx, fy, fz, e[0], e[1]);
+      else large_pairs_body<MODE, ENERGY, false>(T, P, p, tbase, sj[warp], stj[warp], nbox, ibox, ib, warp, lane, xi, yi, zi, kqi, fx, fy, fz, e[0], e[1]);
     }
     sf[warp][0][lane] = fx; sf[warp][1][lane] = fy; sf[warp][2][lane] = fz;
     __syncthreads();
