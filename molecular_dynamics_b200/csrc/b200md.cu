@@ -1130,6 +1130,7 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
 struct LargeWork {
   cudaStream_t st;
   long long* fbond = nullptr; double* partial = nullptr; double* energies = nullptr; double* ekin = nullptr; double* smd = nullptr;
+  float* bbox = nullptr;
   int nbonded_blocks = 0, npart = 0, nek = 0;
 };
 
@@ -1145,7 +1146,8 @@ static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, 
   const size_t b_f = up(sizeof(long long) * 3 * (size_t)R * L.natoms), b_p = up(sizeof(double) * (size_t)R * w.npart * B200MD_NUM_ENERGIES);
   const size_t b_e = integrator ? up(sizeof(double) * (size_t)R * B200MD_NUM_ENERGIES) : 0, b_k = integrator ? up(sizeof(double) * (size_t)R * w.nek) : 0;
   const size_t b_s = (integrator && smd) ? up(sizeof(double) * 2 * (size_t)R) : 0;
-  const size_t total = b_f + b_p + b_e + b_k + b_s;
+  const size_t b_b = up(sizeof(float) * 8 * (size_t)R * L.nwords);
+  const size_t total = b_f + b_p + b_e + b_k + b_s + b_b;
   if (topo->ws != nullptr && topo->ws_stream != w.st) CUDA_TRY(cudaStreamSynchronize(topo->ws_stream));
   if (total > topo->ws_bytes) {
     if (topo->ws != nullptr) { CUDA_TRY(cudaStreamSynchronize(topo->ws_stream)); cudaFree(topo->ws); topo->ws = nullptr; topo->ws_bytes = 0; }
@@ -1156,6 +1158,7 @@ static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, 
   char* base = (char*)topo->ws;
   w.fbond = (long long*)base; base += b_f;
   w.partial = (double*)base; base += b_p;
+  w.bbox = (float*)base; base += b_b;
   if (integrator) {
     w.energies = (double*)base; base += b_e;
     w.ekin = (double*)base; base += b_k;
@@ -1178,8 +1181,15 @@ static int large_forces(const b200md_topology* topo, const ForceParams& P, int64
                                                                              P.smd_centers, smd_center, w.smd);
   const int tab_bytes = 2 * L.ntypes * large_tab_stride(L.ntypes) * (int)sizeof(float);
   const dim3 grid(L.nwords, gy);
+  const bool pairs_on = (P.terms & (B200MD_T_ELECTROSTATICS | B200MD_T_LJ | B200MD_T_REPULSION | B200MD_T_REPULSIONCG)) != 0;
+  const float* bbox = nullptr;
+  if (P.has_cutoff && pairs_on && L.nwords > 4) {  // tile bounding boxes for the cutoff skip (vacuum replicas use them)
+    large_bbox_kernel<<<dim3((L.nwords + 3) / 4, gy), 128, 0, st>>>(L, R, pos, w.bbox);
+    g_launches.fetch_add(1);
+    bbox = w.bbox;
+  }
 #define B200MD_LAUNCH_LPAIRS(M, E) \
-  large_pairs_kernel<M, E><<<grid, kLThreads, tab_bytes, st>>>(L, P, R, pos, box, w.fbond, forces, w.partial, w.npart, w.nbonded_blocks, status)
+  large_pairs_kernel<M, E><<<grid, kLThreads, tab_bytes, st>>>(L, P, R, pos, box, w.fbond, forces, w.partial, w.npart, w.nbonded_blocks, status, bbox)
   if (P.has_cutoff) { if (with_energy) B200MD_LAUNCH_LPAIRS(1, true); else B200MD_LAUNCH_LPAIRS(1, false); }
   else { if (with_energy) B200MD_LAUNCH_LPAIRS(0, true); else B200MD_LAUNCH_LPAIRS(0, false); }
 #undef B200MD_LAUNCH_LPAIRS

@@ -227,6 +227,33 @@ large_bonded_kernel(const LargeTopo T, const ForceParams P, const long long R, c
   }
 }
 
+// Axis-aligned bounding box of every 32-atom tile of every replica (cutoff mode, vacuum replicas): lets a warp of the
+// pair kernel drop a j tile none of its i atoms can reach.  One warp per tile; bbox[(r * nwords + tile) * 8 + {0..2, 4..6}] = lo, hi.
+__global__ void __launch_bounds__(128)
+large_bbox_kernel(const LargeTopo T, const long long R, const float* __restrict__ pos, float* __restrict__ bbox) {
+  const int lane = threadIdx.x & 31, tile = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (tile >= T.nwords) return;
+  const int j = 32 * tile + lane;
+  for (long long r = blockIdx.y; r < R; r += gridDim.y) {
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    if (j < T.natoms) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) lo[c] = hi[c] = __ldg(pos + (r * T.natoms + j) * 3 + c);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        lo[c] = fminf(lo[c], __shfl_xor_sync(0xffffffffu, lo[c], o));
+        hi[c] = fmaxf(hi[c], __shfl_xor_sync(0xffffffffu, hi[c], o));
+      }
+    if (lane < 3) {
+      bbox[(r * T.nwords + tile) * 8 + lane] = lane == 0 ? lo[0] : (lane == 1 ? lo[1] : lo[2]);
+      bbox[(r * T.nwords + tile) * 8 + 4 + lane] = lane == 0 ? hi[0] : (lane == 1 ? hi[1] : hi[2]);
+    }
+  }
+}
+
 template <int OFF>
 __device__ __forceinline__ float lds_f32(uint32_t addr) {
   float v;
@@ -245,8 +272,8 @@ template <int MODE, bool ENERGY, bool PBC>
 __device__ __forceinline__ void large_pairs_body(const LargeTopo& T, const ForceParams& P, const float* __restrict__ p,
                                                  const uint32_t tbase, float* sj /* [4][32] */, int* stj,
                                                  const float3 nbox, const float3 ibox, int ib, int warp, int lane, float xi,
-                                                 float yi, float zi, float kqi, float& fx, float& fy, float& fz,
-                                                 double& eel, double& elj) {
+                                                 float yi, float zi, float kqi, const float* __restrict__ bb, float& fx,
+                                                 float& fy, float& fz, double& eel, double& elj) {
   const int N = T.natoms;
   const uint32_t* mrow = T.mask + (size_t)(32 * ib + lane) * T.nwords;
   const PairConst C = make_pair_const<MODE>(P);
@@ -256,7 +283,14 @@ __device__ __forceinline__ void large_pairs_body(const LargeTopo& T, const Force
   float jx = 0.f, jy = 0.f, jz = 0.f, jq = 0.f;
   int jtype = 0;
   uint32_t mn = 0xffffffffu;
+  // cutoff mode, vacuum: the tile's bounding box against this lane's i atom.  Component-wise |xi - box| <= |xi - xj| for
+  // every atom of the tile and fp32 subtraction / fma are monotonic, so d2 <= r2 of every pair of the lane: a tile that all
+  // lanes place beyond the cutoff holds only pairs the cutoff test of pair_eval2 would zero -- results are bit-identical
+  const bool boxtest = MODE == 1 && !PBC && bb != nullptr;
+  float4 blo = make_float4(0.f, 0.f, 0.f, 0.f), bhi = blo;
+  const bool live_i = 32 * ib + lane < N;
   auto fetch = [&](int jt) {
+    if (boxtest) { blo = __ldg((const float4*)(bb + 8 * jt)); bhi = __ldg((const float4*)(bb + 8 * jt + 4)); }
     const int j = 32 * jt + lane;
     jx = jy = jz = jq = 0.f;
     if (j < N) { jx = __ldg(p + 3 * j); jy = __ldg(p + 3 * j + 1); jz = __ldg(p + 3 * j + 2); jq = __ldg(T.charge + j) * P.el_on; }
@@ -266,12 +300,18 @@ __device__ __forceinline__ void large_pairs_body(const LargeTopo& T, const Force
   if (warp < T.nwords) fetch(warp);
   for (int jt = warp; jt < T.nwords; jt += kLThreads / 32) {
     const uint32_t m = mn;
+    bool far = false;
+    if (boxtest) {
+      const float ex = fmaxf(fmaxf(__fsub_rn(blo.x, xi), __fsub_rn(xi, bhi.x)), 0.0f), ey = fmaxf(fmaxf(__fsub_rn(blo.y, yi), __fsub_rn(yi, bhi.y)), 0.0f);
+      const float ez = fmaxf(fmaxf(__fsub_rn(blo.z, zi), __fsub_rn(zi, bhi.z)), 0.0f);
+      far = !live_i || !(__fmaf_rn(ez, ez, __fmaf_rn(ey, ey, __fmul_rn(ex, ex))) <= P.rc2);
+    }
     __syncwarp();
     sj[lane] = jx; sj[32 + lane] = jy; sj[64 + lane] = jz; sj[96 + lane] = jq;
     stj[lane] = jtype;
     __syncwarp();
     if (jt + kLThreads / 32 < T.nwords) fetch(jt + kLThreads / 32);
-    if (__all_sync(0xffffffffu, m == 0xffffffffu)) continue;
+    if (__all_sync(0xffffffffu, far || m == 0xffffffffu)) continue;
     u64 pel = 0ull, plj = 0ull;
 #pragma unroll 4
     for (int jj = 0; jj < 32; jj += 2) {
@@ -297,7 +337,8 @@ template <int MODE, bool ENERGY>
 __global__ void __launch_bounds__(kLThreads)
 large_pairs_kernel(const LargeTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
                    const float* __restrict__ box, const long long* __restrict__ fbond, float* __restrict__ forces,
-                   double* __restrict__ partial, const int npart, const int part0, uint32_t* __restrict__ status) {
+                   double* __restrict__ partial, const int npart, const int part0, uint32_t* __restrict__ status,
+                   const float* __restrict__ bbox) {
   extern __shared__ __align__(16) char lsmem[];
   float* sAB = (float*)lsmem;  // [ntypes][stride] entries (12 A tab_a, 6 B tab_b)
   const int tstride = large_tab_stride(T.ntypes);
@@ -330,8 +371,9 @@ large_pairs_kernel(const LargeTopo T, const ForceParams P, const long long R, co
     float fx = 0.f, fy = 0.f, fz = 0.f;
     double e[2] = {0.0, 0.0};
     if (nonbonded) {
-      if (pbc) large_pairs_body<MODE, ENERGY, true>(T, P, p, tbase, sj[warp], stj[warp], nbox, ibox, ib, warp, lane, xi, yi, zi, kqi, fx, fy, fz, e[0], e[1]);
-      else large_pairs_body<MODE, ENERGY, false>(T, P, p, tbase, sj[warp], stj[warp], nbox, ibox, ib, warp, lane, xi, yi, zi, kqi, fx, fy, fz, e[0], e[1]);
+      if (pbc) large_pairs_body<MODE, ENERGY, true>(T, P, p, tbase, sj[warp], stj[warp], nbox, ibox, ib, warp, lane, xi, yi, zi, kqi, nullptr, fx, fy, fz, e[0], e[1]);
+      else large_pairs_body<MODE, ENERGY, false>(T, P, p, tbase, sj[warp], stj[warp], nbox, ibox, ib, warp, lane, xi, yi, zi, kqi,
+                                                 bbox ? bbox + r * T.nwords * 8 : nullptr, fx, fy, fz, e[0], e[1]);
     }
     sf[warp][0][lane] = fx; sf[warp][1][lane] = fy; sf[warp][2][lane] = fz;
     __syncthreads();

@@ -1089,3 +1089,39 @@ def test_large_solute_unsupported_options_raise():
         Integrator(s, F, timestep=1.0, device=DEV, rigid_bonds=True).step(niter=1)
     with pytest.raises((RuntimeError, NotImplementedError, ValueError)):
         F.dihedral_angles(s.pos)
+
+
+def test_large_solute_bundle_of_ala10_chains_vs_oracle():
+    """A compact large solute from real conformers: 6 deca-alanine chains 14 A apart as one 624-atom topology
+    (Parameters.tiled), plain and cutoff / reaction field / switch (where whole j tiles beyond the cutoff are dropped by
+    their bounding boxes, which must not change a bit of the result), against the oracle."""
+    g = load_golden("ala10")
+    copies, R = 6, 3
+    parL = g.par.tiled(copies)
+    N = 104 * copies
+    shift = np.repeat(np.arange(copies), 104)[None, :, None] * np.array([0.0, 10.0, 10.0])  # closest inter-chain pair > 5 A
+    frames = g["base_frames"][:R * copies].reshape(R, copies * 104, 3)
+    pos = (frames + shift).astype(np.float32)
+    idx = _cabi.make_pair_index(N, parL.get_exclusions())
+    packed = _cabi.PackedTopology(parL, idx)
+    parG = Parameters.from_arrays(parL.to_arrays(), device=DEV)
+    for mode in ("plain", "rf"):
+        F = Forces(parG, **MODES[mode])
+        s = System(N, R, torch.float, DEV)
+        e = F.compute_batch(torch.tensor(pos, device=DEV), s.box, s.forces).cpu().numpy()
+        f = s.forces.cpu().numpy()
+        f_ref, e_ref = oracle.forces(packed, pos, **MODES[mode])
+        assert np.abs(f - f_ref).max() / np.abs(f_ref).max() < 1e-5, mode
+        np.testing.assert_allclose(e[:, 2:5], e_ref[:, 2:5], rtol=1e-9)
+        np.testing.assert_allclose(e[:, :2], e_ref[:, :2], rtol=2e-5, atol=2e-3)
+    # the same conformers far apart in a box: minimum image brings them back into range, no tile may be dropped
+    box = np.zeros((R, 3, 3), dtype=np.float32)
+    box[:, 0, 0], box[:, 1, 1], box[:, 2, 2] = 80.0, 120.0, 120.0
+    posb = pos.copy()
+    posb[:, 104:208, 0] += 160.0  # chain 1 shifted by two box lengths (box y, z = 80: the 50 A bundle stays clear of its images)
+    F = Forces(parG, **MODES["rf"])
+    s = System(N, R, torch.float, DEV)
+    s.box[:] = torch.tensor(box, device=DEV)
+    F.compute_batch(torch.tensor(posb, device=DEV), s.box, s.forces)
+    f_ref, _ = oracle.forces(packed, posb, box=box.reshape(R, 9), **MODES["rf"])
+    assert np.abs(s.forces.cpu().numpy() - f_ref).max() / np.abs(f_ref).max() < 1e-5
