@@ -1077,24 +1077,30 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   for (int k = 0; k < d->n14; ++k) { i14[k] = make_int2(d->idx14[2 * k], d->idx14[2 * k + 1]); p14[k] = make_float4(d->prm14[4 * k], d->prm14[4 * k + 1], d->prm14[4 * k + 2], d->prm14[4 * k + 3]); }
   // torsion terms grouped by their quadruple, slice order kept inside a group (forces.py:559-576)
   auto group_terms = [&](int n, const int32_t* idx, int nt, const int32_t* owner, const float* prm, const int32_t* harm,
-                         std::vector<int4>& q, std::vector<int>& start, std::vector<float4>& term) -> bool {
-    q.resize(n); start.assign(n + 1, 0); term.resize(nt);
+                         std::vector<int4>& q, std::vector<int>& start, std::vector<float4>& term, std::vector<double2>& cs) -> bool {
+    q.resize(n); start.assign(n + 1, 0); term.resize(nt); cs.resize(nt);
     for (int k = 0; k < n; ++k) q[k] = make_int4(idx[4 * k], idx[4 * k + 1], idx[4 * k + 2], idx[4 * k + 3]);
     for (int t = 0; t < nt; ++t) { if (owner[t] < 0 || owner[t] >= n) return false; ++start[owner[t] + 1]; }
     for (int k = 0; k < n; ++k) start[k + 1] += start[k];
     std::vector<int> cur(start.begin(), start.end() - 1);
-    for (int t = 0; t < nt; ++t) term[cur[owner[t]]++] = make_float4(prm[3 * t], prm[3 * t + 1], prm[3 * t + 2], harm[t] ? 1.0f : 0.0f);
+    for (int t = 0; t < nt; ++t) {
+      const float per = prm[3 * t + 2];
+      const bool integer = !harm[t] && per >= 1.0f && per <= 6.0f && per == floorf(per);
+      const int at = cur[owner[t]]++;
+      term[at] = make_float4(prm[3 * t], prm[3 * t + 1], per, harm[t] ? 1.0f : (integer ? 2.0f : 0.0f));
+      cs[at] = make_double2(cos((double)prm[3 * t + 1]), sin((double)prm[3 * t + 1]));
+    }
     return true;
   };
-  std::vector<int4> dq, iq; std::vector<int> ds, is; std::vector<float4> dt, it;
-  if (!group_terms(d->ndihedrals, d->dihedral_idx, d->ndihedral_terms, d->dihedral_term_owner, d->dihedral_term_prm, d->dihedral_term_harmonic, dq, ds, dt) ||
-      !group_terms(d->nimpropers, d->improper_idx, d->nimproper_terms, d->improper_term_owner, d->improper_term_prm, d->improper_term_harmonic, iq, is, it)) {
+  std::vector<int4> dq, iq; std::vector<int> ds, is; std::vector<float4> dt, it; std::vector<double2> dcs, ics;
+  if (!group_terms(d->ndihedrals, d->dihedral_idx, d->ndihedral_terms, d->dihedral_term_owner, d->dihedral_term_prm, d->dihedral_term_harmonic, dq, ds, dt, dcs) ||
+      !group_terms(d->nimpropers, d->improper_idx, d->nimproper_terms, d->improper_term_owner, d->improper_term_prm, d->improper_term_harmonic, iq, is, it, ics)) {
     delete topo; fail(B200MD_ERR_INVALID_ARGUMENT, "torsion term owner out of range"); return nullptr;
   }
   BlobBuilder B;
   const size_t o_type = B.add(atype), o_q = B.add(charge), o_m = B.add(mass), o_a = B.add(t12a), o_b = B.add(t6b), o_mask = B.add(mask),
                o_bi = B.add(bidx), o_bp = B.add(bprm), o_ai = B.add(aidx), o_ap = B.add(aprm), o_dq = B.add(dq), o_ds = B.add(ds),
-               o_dt = B.add(dt), o_i14 = B.add(i14), o_p14 = B.add(p14), o_iq = B.add(iq), o_is = B.add(is), o_it = B.add(it);
+               o_dt = B.add(dt), o_i14 = B.add(i14), o_p14 = B.add(p14), o_iq = B.add(iq), o_is = B.add(is), o_it = B.add(it), o_dcs = B.add(dcs), o_ics = B.add(ics);
   cudaDeviceProp prop;
   if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess ||
       cudaMalloc(&topo->blob, B.bytes.size()) != cudaSuccess ||
@@ -1113,6 +1119,7 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   L.angle_idx = (const int*)(base + o_ai); L.angle_prm = (const float2*)(base + o_ap);
   L.dih_idx = (const int4*)(base + o_dq); L.dih_start = (const int*)(base + o_ds); L.dih_term = (const float4*)(base + o_dt);
   L.idx14 = (const int2*)(base + o_i14); L.prm14 = (const float4*)(base + o_p14);
+  L.dih_cs = (const double2*)(base + o_dcs); L.imp_cs = (const double2*)(base + o_ics);
   L.imp_idx = (const int4*)(base + o_iq); L.imp_start = (const int*)(base + o_is); L.imp_term = (const float4*)(base + o_it);
   const int tab_bytes = 2 * NT * large_tab_stride(NT) * (int)sizeof(float);
   if (tab_bytes > 40 * 1024) {

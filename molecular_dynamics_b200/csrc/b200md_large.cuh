@@ -38,7 +38,8 @@ struct LargeTopo {
   int nbonds, nangles, ndih, n14, nimp;
   const int2* bond_idx;   const float2* bond_prm;
   const int* angle_idx;   const float2* angle_prm;   // 3 ints per angle
-  const int4* dih_idx;    const int* dih_start;  const float4* dih_term;   // terms of dihedral d: [dih_start[d], dih_start[d+1]); (k, phi0, per, harmonic)
+  const int4* dih_idx;    const int* dih_start;  const float4* dih_term;   // terms of dihedral d: [dih_start[d], dih_start[d+1]); (k, phi0, per, kind)
+  const double2* dih_cs;  const double2* imp_cs;                          // (cos phi0, sin phi0) per term; kind: 0 AMBER, 1 harmonic, 2 AMBER with integer per 1..6
   const int2* idx14;      const float4* prm14;                            // A, B, scnb, scee
   const int4* imp_idx;    const int* imp_start;  const float4* imp_term;
 };
@@ -61,21 +62,42 @@ __device__ __forceinline__ void ladd(long long* f, int i, d3 a, double s) {
   atomicAdd((unsigned long long*)(f + 3 * i + 2), (unsigned long long)__double2ll_rn(s * a.z * kLFixScale));
 }
 
-// evaluate_torsion (forces.py:540-602) for one quadruple with its terms; returns the energy
-__device__ __forceinline__ double ltorsion(const float* p, const double* bx, bool vac, int4 q, const float4* term, int t0, int t1,
-                                           long long* f) {
+// evaluate_torsion (forces.py:540-602) for one quadruple with its terms; returns the energy.
+// Terms of the AMBER branch with an integer periodicity 1..6 (marker 2) never form phi: cos / sin(n phi) come from
+// (cos phi + i sin phi)^n and cos / sin(phi0) from the host (FP64), which takes atan2, sin and cos out of the common case
+// (the FP64 transcendentals were most of this kernel's instructions).  Other terms use phi = -atan2(sin, cos) as written.
+__device__ __forceinline__ double ltorsion(const float* p, const double* bx, bool vac, int4 q, const float4* term,
+                                           const double2* term_cs, int t0, int t1, long long* f) {
   const d3 r12 = lwrap(dsub(lpos(p, q.x), lpos(p, q.y)), bx, vac);
   const d3 r23 = lwrap(dsub(lpos(p, q.y), lpos(p, q.z)), bx, vac);
   const d3 r34 = lwrap(dsub(lpos(p, q.z), lpos(p, q.w)), bx, vac);
   const d3 cA = dcross(r12, r23), cB = dcross(r23, r34), cC = dcross(r23, cA);
   const double nA = sqrt(ddot(cA, cA)), nB = sqrt(ddot(cB, cB)), nC = sqrt(ddot(cC, cC));
   const d3 ncB = dscale(cB, 1.0 / nB);
-  const double phi = -atan2(ddot(cC, ncB) / nC, ddot(cA, ncB) / nA);
+  const double cosPhi = ddot(cA, ncB) / nA, sinPhi = ddot(cC, ncB) / nC;  // forces.py:548-551; phi = -atan2(sinPhi, cosPhi)
+  const double hinv = 1.0 / sqrt(cosPhi * cosPhi + sinPhi * sinPhi);
+  const double c1 = cosPhi * hinv, s1 = -sinPhi * hinv;  // cos phi, sin phi
+  double phi = 0.0;
+  bool have_phi = false;
   double pot = 0.0, coeff = 0.0;
   for (int t = t0; t < t1; ++t) {
     const float4 tp = __ldg(term + t);
     const double k0 = tp.x, phi0 = tp.y, per = tp.z;
-    if (tp.w == 0.0f) {  // AMBER branch, forces.py:565-569
+    if (tp.w == 2.0f) {  // AMBER branch, integer periodicity: k (1 + cos(n phi - phi0)), forces.py:565-569
+      const double2 cs0 = term_cs[t];
+      const int n = (int)tp.z;
+      double cn = c1, sn = s1;
+      for (int k = 1; k < n; ++k) {
+        const double cc = cn * c1 - sn * s1;
+        sn = sn * c1 + cn * s1;
+        cn = cc;
+      }
+      pot += k0 * (1.0 + (cn * cs0.x + sn * cs0.y));
+      coeff += -per * k0 * (sn * cs0.x - cn * cs0.y);
+      continue;
+    }
+    if (!have_phi) { phi = -atan2(sinPhi, cosPhi); have_phi = true; }
+    if (tp.w == 0.0f) {  // AMBER branch, any periodicity
       const double ad = per * phi - phi0;
       pot += k0 * (1.0 + cos(ad));
       coeff += -per * k0 * sin(ad);
@@ -181,7 +203,7 @@ large_bonded_kernel(const LargeTopo T, const ForceParams P, const long long R, c
         ladd(f, q1, {f0.x + f2.x, f0.y + f2.y, f0.z + f2.z}, -1.0);
       } else if (g < e3) {  // forces.py:147-174
         const int d = g - e2;
-        e[B200MD_E_DIHEDRALS] += ltorsion(p, bx, vac, __ldg(T.dih_idx + d), T.dih_term, __ldg(T.dih_start + d), __ldg(T.dih_start + d + 1), f);
+        e[B200MD_E_DIHEDRALS] += ltorsion(p, bx, vac, __ldg(T.dih_idx + d), T.dih_term, T.dih_cs, __ldg(T.dih_start + d), __ldg(T.dih_start + d + 1), f);
       } else if (g < e4) {  // forces.py:176-226: never cut, switched or reaction-field corrected
         const int k = g - e3;
         const int2 ij = __ldg(T.idx14 + k);
@@ -202,7 +224,7 @@ large_bonded_kernel(const LargeTopo T, const ForceParams P, const long long R, c
         ladd(f, ij.y, d, -c);
       } else {  // forces.py:228-255
         const int d = g - e4;
-        e[B200MD_E_IMPROPERS] += ltorsion(p, bx, vac, __ldg(T.imp_idx + d), T.imp_term, __ldg(T.imp_start + d), __ldg(T.imp_start + d + 1), f);
+        e[B200MD_E_IMPROPERS] += ltorsion(p, bx, vac, __ldg(T.imp_idx + d), T.imp_term, T.imp_cs, __ldg(T.imp_start + d), __ldg(T.imp_start + d + 1), f);
       }
     }
     if (P.smd_on && blockIdx.x == 0 && tid == 0) {  // potcalc.py:75-89, not wrapped
