@@ -224,6 +224,8 @@ def run_reference(args):
     }))
 
 
+WORKLOAD_NAME_C4 = ("configs[3]: ALA10 Langevin 300 K (gamma 1/ps) with the steered-MD end-to-end restraint (atoms 3 / 98, "
+                    "fk 1, centre 12 -> 34 A), fused persistent kernel, dt=1fs, plain all-pairs LJ+Coulomb")
 WORKLOAD_NAME = ("configs[2]: ALA10 NVE velocity-Verlet, 8192 replicas per GPU, fused persistent kernel, "
                  "dt=1fs, plain all-pairs LJ+Coulomb")
 
@@ -257,14 +259,23 @@ def run_ours(args):
     R, S = args.replicas, args.inner
     replica0 = rank * R
     pos_h, vel_h = synth_inputs(g, R, replica0)
-    forces = Forces(par)
+    config4 = args.workload == "langevin_smd"
+    if config4:  # BASELINE.json configs[3]: Langevin 300 K, gamma 1/ps, SMD restraint on atoms 3 / 98 moving 12 -> 34 A
+        from molecular_dynamics_b200 import SMDBias
+        total_steps = (args.warmup + args.steps + 8) * S
+        forces = Forces(par, external=SMDBias([3], [98], fk=1.0, cent_0=12.0, rate_per_step=22.0 / total_steps))
+    else:
+        forces = Forces(par)
     forces.check_nan = False
     system = System(104, R, torch.float, dev)
     system.pos[:] = torch.tensor(pos_h, device=dev)
     system.vel[:] = torch.tensor(vel_h, device=dev)
     forces.compute_batch(system.pos, system.box, system.forces)
     frc_h = system.forces.cpu().numpy()
-    integ = Integrator(system, forces, timestep=1.0, device=dev)
+    if config4:
+        integ = Integrator(system, forces, timestep=1.0, device=dev, gamma=1.0, T=300.0, seed=42)
+    else:
+        integ = Integrator(system, forces, timestep=1.0, device=dev)
     integ.energy_every = args.energy_every
     integ.replica0 = replica0
     integ.check_nan = False
@@ -481,12 +492,13 @@ def run_ours(args):
 
     if rank == 0:
         peak = lib.b200md_fp32_peak_tflops(local, 4096)
-        achieved = value / world * FLOP_PER_REPLICA_STEP / 1e12  # per GPU
+        flop_step = FLOP_PER_REPLICA_STEP + (15 * 104 if config4 else 0)  # +15 N_atom for the Langevin kick
+        achieved = value / world * flop_step / 1e12  # per GPU
         line = {
             "metric": "ALA10 replica-steps/s", "value": value, "unit": "replica-steps/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD_NAME, "replicas_per_gpu": R, "md_steps_per_launch": S,
+            "config": {"workload": WORKLOAD_NAME_C4 if config4 else WORKLOAD_NAME, "replicas_per_gpu": R, "md_steps_per_launch": S,
                        "energy_every": args.energy_every, "dt_fs": 1.0, "natoms": 104,
                        "l2": "flushed between timed steps (256 MiB fill, outside the event pair)",
                        "ns_per_day_aggregate": value * 1.0 * 86400 * 1e-6,
@@ -501,7 +513,7 @@ def run_ours(args):
                          "traffic_source": "ncu --set full of one 50-step launch, profiles/ (dram read + write; the state is read once per launch whatever its length)",
                          "peak_source": "measured live: b200md_fp32_peak_tflops (dependent-FMA kernel, all SMs)",
                          "nominal_peak": NOMINAL_FP32_TFLOPS, "frac_of_nominal": achieved / NOMINAL_FP32_TFLOPS,
-                         "flop_per_replica_step": FLOP_PER_REPLICA_STEP, "kernel": "integrate_kernel<0>",
+                         "flop_per_replica_step": flop_step, "kernel": "integrate_kernel<0>",
                          "kernel_ms_per_launch": ms / args.steps,
                          "bound_note": "FP32 CUDA-core kernel: neither the HBM nor the tensor-core roofline binds it; the "
                                        "HBM view of the same launch is given under 'hbm'",
@@ -537,6 +549,9 @@ def main():
     ap.add_argument("--replicas", type=int, default=8192, help="replicas per GPU")
     ap.add_argument("--inner", type=int, default=1000, help="MD steps per launch (Integrator.step niter)")
     ap.add_argument("--energy-every", type=int, default=100)
+    ap.add_argument("--workload", default="nve", choices=["nve", "langevin_smd"],
+                    help="nve = configs[2] (the metric's configuration, default); langevin_smd = configs[3] "
+                         "(use --replicas 4096 at 8 GPUs for its 32 768 replicas)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extra", action="store_true", help="skip the secondary workloads (configs[1], configs[3])")
     args = ap.parse_args()
