@@ -35,6 +35,8 @@ def main():
     ap.add_argument("--oracle-replicas", type=int, default=8)
     ap.add_argument("--dt", type=float, default=1.0)
     ap.add_argument("--every", type=int, default=100)
+    ap.add_argument("--copies", type=int, default=1,
+                    help="> 1: a bundle of this many chains 40 A apart as ONE topology (Parameters.tiled): the large-solute kernels")
     ap.add_argument("--rigid", action="store_true", help="rigid X-H bonds (SHAKE / RATTLE), e.g. with --dt 2.0")
     a = ap.parse_args()
     import torch
@@ -46,8 +48,16 @@ def main():
     g = bench.load_ala10()
     dev = torch.device("cuda", 0)
     par = Parameters.from_arrays({k[4:]: v for k, v in g.items() if k.startswith("par_")}, device=dev)
-    pos, vel = bench.synth_inputs(g, a.replicas)
-    s = System(104, a.replicas, torch.float, dev)
+    pos, vel = bench.synth_inputs(g, a.replicas * a.copies)
+    par_cpu = Parameters.from_arrays({k[4:]: v for k, v in g.items() if k.startswith("par_")})
+    pair_idx = g["ava_idx"]
+    if a.copies > 1:
+        par, par_cpu = par.tiled(a.copies), par_cpu.tiled(a.copies)
+        shift = (np.repeat(np.arange(a.copies), 104)[None, :, None] * np.array([40.0, 0.0, 0.0])).astype(np.float32)
+        pos = pos.reshape(a.replicas, a.copies * 104, 3) + shift
+        vel = vel.reshape(a.replicas, a.copies * 104, 3)
+        pair_idx = _cabi.make_pair_index(104 * a.copies, par_cpu.get_exclusions())
+    s = System(104 * a.copies, a.replicas, torch.float, dev)
     s.pos[:] = torch.tensor(pos, device=dev)
     s.vel[:] = torch.tensor(vel, device=dev)
     F = Forces(par)
@@ -70,12 +80,12 @@ def main():
     obs = np.concatenate(chunks, 0)
     etot = obs[:, :, :8].sum(-1) + obs[:, :, _cabi.OBS_EKIN]
     d, r = drift_stats(etot)
-    out = {"dt_fs": a.dt, "rigid_bonds": bool(a.rigid), "steps": a.steps, "replicas": a.replicas, "energy_every": a.every,
+    out = {"dt_fs": a.dt, "natoms": 104 * a.copies, "rigid_bonds": bool(a.rigid), "steps": a.steps, "replicas": a.replicas, "energy_every": a.every,
            "gpu": {"etot0_mean": float(etot[0].mean()), "ekin_mean": float(obs[:, :, _cabi.OBS_EKIN].mean()),
                    "drift_mean": float(d.mean()), "drift_abs_max": float(np.abs(d).max()), "drift_std": float(d.std()),
                    "rms_fluct_mean": float(r.mean()), "rms_fluct_max": float(r.max())}}
     if a.oracle_steps > 0:
-        packed = _cabi.PackedTopology(Parameters.from_arrays({k[4:]: v for k, v in g.items() if k.startswith("par_")}), g["ava_idx"])
+        packed = _cabi.PackedTopology(par_cpu, pair_idx)
         ro = a.oracle_replicas
         o = oracle.integrate(packed, pos[:ro], vel[:ro], f0[:ro], nsteps=a.oracle_steps, dt=np.float32(integ.dt), energy_every=a.every,
                              rigid_bonds=a.rigid)
