@@ -1144,9 +1144,10 @@ struct LargeWork {
 static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, bool smd, LargeWork& w) {
   const LargeTopo& L = topo->ldev;
   const long long items = (long long)L.nbonds + L.nangles + L.ndih + L.n14 + L.nimp;
-  // enough bonded CTAs to fill the GPU at small replica counts, never more than the items need
-  const long long want = std::max<long long>(1, (16ll * topo->num_sms + R - 1) / R);
-  w.nbonded_blocks = (int)std::max<long long>(1, std::min<long long>(want, (items + kLBondedThreads - 1) / kLBondedThreads));
+  // bonded CTAs per replica: a function of the topology only (4 items per thread, at most 64 CTAs), so that the order of the
+  // FP64 energy partials -- and with it every bit of a replica's result -- does not depend on the replica count of the call
+  (void)R;
+  w.nbonded_blocks = (int)std::max<long long>(1, std::min<long long>(64, (items + 4 * kLBondedThreads - 1) / (4 * kLBondedThreads)));
   w.npart = w.nbonded_blocks + L.nwords;
   w.nek = (L.natoms + 255) / 256;
   auto up = [](size_t x) { return (x + 255) & ~size_t(255); };

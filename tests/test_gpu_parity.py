@@ -1125,3 +1125,23 @@ def test_large_solute_bundle_of_ala10_chains_vs_oracle():
     F.compute_batch(torch.tensor(posb, device=DEV), s.box, s.forces)
     f_ref, _ = oracle.forces(packed, posb, box=box.reshape(R, 9), **MODES["rf"])
     assert np.abs(s.forces.cpu().numpy() - f_ref).max() / np.abs(f_ref).max() < 1e-5
+
+
+def test_large_solute_results_do_not_depend_on_the_batch():
+    """The launch geometry per replica (i-blocks, bonded CTAs, order of the energy partials) is a function of the topology
+    only: a replica's forces and energies are bit-identical whatever batch it is evaluated in."""
+    g = _RandomMolecule(1000, 50, R=2)
+    par = gpu_par(g)
+    F = Forces(par)
+    rng = np.random.default_rng(50)
+    pos = (g.pos[rng.integers(0, 2, 48)] + 0.01 * rng.standard_normal((48, 1000, 3))).astype(np.float32)
+    p = torch.tensor(pos, device=DEV)
+    s = System(1000, 48, torch.float, DEV)
+    e = F.compute_batch(p, s.box, s.forces)
+    for sl in (slice(0, 1), slice(17, 18), slice(40, 43)):
+        n = sl.stop - sl.start
+        s1 = System(1000, n, torch.float, DEV)
+        e1 = F.compute_batch(p[sl].contiguous(), s1.box, s1.forces)
+        assert torch.equal(s1.forces, s.forces[sl]) and torch.equal(e1, e[sl])
+    f_ref, e_ref = oracle.forces(g.packed, pos[:2])
+    assert np.abs(s.forces[:2].cpu().numpy() - f_ref).max() / np.abs(f_ref).max() < 1e-5
