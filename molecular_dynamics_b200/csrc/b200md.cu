@@ -464,6 +464,10 @@ struct b200md_topology {
   mutable void* ws = nullptr;
   mutable size_t ws_bytes = 0;
   mutable cudaStream_t ws_stream = nullptr;
+  // second stream of the large-solute calls: the latency-bound FP64 bonded kernel runs beside the throughput-bound pair
+  // kernel (fork / join by events, so the caller's stream still orders the call as a whole)
+  mutable cudaStream_t aux = nullptr;
+  mutable cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 
 namespace {
@@ -1184,9 +1188,22 @@ static int large_forces(const b200md_topology* topo, const ForceParams& P, int64
   const LargeTopo& L = topo->ldev;
   cudaStream_t st = w.st;
   const int gy = (int)std::min<int64_t>(R, 65535);
-  CUDA_TRY(cudaMemsetAsync(w.fbond, 0, sizeof(long long) * 3 * (size_t)R * L.natoms, st));
-  large_bonded_kernel<<<dim3(w.nbonded_blocks, gy), kLBondedThreads, 0, st>>>(L, P, R, pos, box, w.fbond, w.partial, w.npart,
+  static const bool overlap_on = !(getenv("B200MD_LARGE_OVERLAP") && atoi(getenv("B200MD_LARGE_OVERLAP")) == 0);
+  if (overlap_on && topo->aux == nullptr) {
+    CUDA_TRY(cudaStreamCreateWithFlags(&topo->aux, cudaStreamNonBlocking));
+    CUDA_TRY(cudaEventCreateWithFlags(&topo->ev_fork, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventCreateWithFlags(&topo->ev_join, cudaEventDisableTiming));
+  }
+  cudaStream_t sb = overlap_on ? topo->aux : st;  // stream of the bonded kernel
+  if (overlap_on) {
+    CUDA_TRY(cudaEventRecord(topo->ev_fork, st));
+    CUDA_TRY(cudaStreamWaitEvent(sb, topo->ev_fork, 0));
+  }
+  CUDA_TRY(cudaMemsetAsync(w.fbond, 0, sizeof(long long) * 3 * (size_t)R * L.natoms, sb));
+  large_bonded_kernel<<<dim3(w.nbonded_blocks, gy), kLBondedThreads, 0, sb>>>(L, P, R, pos, box, w.fbond, w.partial, w.npart,
                                                                              P.smd_centers, smd_center, w.smd);
+  if (overlap_on) CUDA_TRY(cudaEventRecord(topo->ev_join, sb));
+  long long* fb_pairs = overlap_on ? nullptr : w.fbond;
   const int tab_bytes = 2 * L.ntypes * large_tab_stride(L.ntypes) * (int)sizeof(float);
   const dim3 grid(L.nwords, gy);
   const bool pairs_on = (P.terms & (B200MD_T_ELECTROSTATICS | B200MD_T_LJ | B200MD_T_REPULSION | B200MD_T_REPULSIONCG)) != 0;
@@ -1197,11 +1214,17 @@ static int large_forces(const b200md_topology* topo, const ForceParams& P, int64
     bbox = w.bbox;
   }
 #define B200MD_LAUNCH_LPAIRS(M, E) \
-  large_pairs_kernel<M, E><<<grid, kLThreads, tab_bytes, st>>>(L, P, R, pos, box, w.fbond, forces, w.partial, w.npart, w.nbonded_blocks, status, bbox)
+  large_pairs_kernel<M, E><<<grid, kLThreads, tab_bytes, st>>>(L, P, R, pos, box, fb_pairs, forces, w.partial, w.npart, w.nbonded_blocks, status, bbox)
   if (P.has_cutoff) { if (with_energy) B200MD_LAUNCH_LPAIRS(1, true); else B200MD_LAUNCH_LPAIRS(1, false); }
   else { if (with_energy) B200MD_LAUNCH_LPAIRS(0, true); else B200MD_LAUNCH_LPAIRS(0, false); }
 #undef B200MD_LAUNCH_LPAIRS
   g_launches.fetch_add(2);
+  if (overlap_on) {  // join: the bonded accumulator and its energy partials are complete from here on
+    CUDA_TRY(cudaStreamWaitEvent(st, topo->ev_join, 0));
+    const long long n3 = 3ll * R * L.natoms;
+    large_combine_kernel<<<(unsigned)((n3 + 255) / 256), 256, 0, st>>>(n3, w.fbond, forces);
+    g_launches.fetch_add(1);
+  }
   if (with_energy) {
     const long long n = (long long)R * B200MD_NUM_ENERGIES;
     large_finish_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(R, w.partial, w.npart, energies);
@@ -1263,6 +1286,9 @@ extern "C" void b200md_topology_destroy(b200md_topology* topo) {
   cudaSetDevice(topo->device);
   if (topo->blob) cudaFree(topo->blob);
   if (topo->ws) cudaFree(topo->ws);
+  if (topo->aux) cudaStreamDestroy(topo->aux);
+  if (topo->ev_fork) cudaEventDestroy(topo->ev_fork);
+  if (topo->ev_join) cudaEventDestroy(topo->ev_join);
   delete topo;
 }
 

@@ -403,8 +403,9 @@ large_pairs_kernel(const LargeTopo T, const ForceParams P, const long long R, co
       const int a = tid / 3, c = tid - 3 * a, ia = 32 * ib + a;
       if (ia < N) {
         const float s = __fadd_rn(__fadd_rn(sf[0][c][a], sf[1][c][a]), __fadd_rn(sf[2][c][a], sf[3][c][a]));
-        const double fb = (double)fbond[(r * N + ia) * 3 + c] * kLFixInv;
-        forces[(r * N + ia) * 3 + c] = (float)((double)s + fb);
+        // fbond == nullptr: the bonded kernel runs concurrently on a second stream, large_combine_kernel adds it afterwards
+        const double fb = fbond != nullptr ? (double)fbond[(r * N + ia) * 3 + c] * kLFixInv : 0.0;
+        forces[(r * N + ia) * 3 + c] = fbond != nullptr ? (float)((double)s + fb) : s;
       }
     }
     if (ENERGY) {
@@ -420,6 +421,12 @@ large_pairs_kernel(const LargeTopo T, const ForceParams P, const long long R, co
       __syncthreads();
     }
   }
+}
+
+// forces = pair row (fp32) + bonded accumulator: the same expression, hence the same bits, as the fused epilogue above
+__global__ void large_combine_kernel(const long long n, const long long* __restrict__ fbond, float* __restrict__ forces) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g < n) forces[g] = (float)((double)forces[g] + (double)fbond[g] * kLFixInv);
 }
 
 // energies[r][k] = sum over the npart per-CTA partials, in index order

@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--replicas", type=int, default=256)
     ap.add_argument("--mode", default="plain")
     ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--integrate", type=int, default=0, help="> 0: also time Integrator.step(niter) (Langevin 300 K, 1 fs)")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     with np.load(os.path.join(ROOT, "tests", "golden", "ala10.npz")) as z:
@@ -49,6 +50,24 @@ def main():
     flop = (36 + (8 if kw else 0)) * npair
     print(f"N {N} R {a.replicas} mode {a.mode}: {1e3 * t:.3f} ms per Forces.compute, {a.replicas / t:.4g} evaluations/s, "
           f"{a.replicas * npair / t:.4g} unique pairs/s, {a.replicas * flop / t / 1e12:.2f} TFLOP/s (pair flops, unique pairs)")
+
+
+    if a.integrate > 0:
+        from molecular_dynamics_b200 import Integrator
+
+        s.vel[:] = 0.01 * torch.randn(s.vel.shape, device=dev, generator=torch.Generator(device=dev).manual_seed(1))
+        integ = Integrator(s, F, timestep=1.0, device=dev, gamma=1.0, T=300.0, seed=3)
+        integ.energy_every, integ.check_nan = 10, False
+        integ.step(niter=a.integrate)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(a.reps):
+            integ.step(niter=a.integrate)
+        e1.record()
+        torch.cuda.synchronize()
+        t = e0.elapsed_time(e1) * 1e-3 / (a.reps * a.integrate)
+        print(f"N {N} R {a.replicas} mode {a.mode}: Langevin step {1e6 * t:.1f} us, {a.replicas / t:.4g} replica-steps/s, "
+              f"{a.replicas / t * 1e-6 * 86400:.4g} aggregate ns/day")
 
 
 if __name__ == "__main__":
