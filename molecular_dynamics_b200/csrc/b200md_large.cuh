@@ -9,8 +9,11 @@
 //   large_pairs_kernel   all-pairs LJ + Coulomb, FULL shell: CTA = one 32-atom i-block of one replica, lane = i atom,
 //                        the 4 warps split the j tiles of 32 atoms (staged per warp in shared memory, read as
 //                        broadcasts), exclusions are one 32-bit mask word per (i atom, j tile); no j-side force, no
-//                        atomics; the warps' partial sums meet in shared memory in a fixed order, the bonded
-//                        accumulator is added and the force row is written once, coalesced;
+//                        atomics; the warps' partial sums meet in shared memory in a fixed order and the force row is
+//                        written once, coalesced (with the bonded accumulator added when the bonded kernel ran before it
+//                        on the same stream; by default that kernel runs beside this one on a second stream and
+//                        large_combine_kernel adds the accumulator afterwards: same expression, same bits);
+//   large_bbox_kernel    cutoff mode: bounding box of every 32-atom tile, so a warp can drop j tiles beyond the cutoff;
 //   large_finish_kernel  per-replica energies = fixed-order sum of the per-CTA FP64 partials;
 //   large_vv1 / large_vv2 / large_observe   the velocity-Verlet halves, the Langevin kick (same Philox stream as the
 //                        fused kernel: keyed by seed, global replica, atom, global step) and the observable record.
