@@ -1145,3 +1145,13 @@ def test_large_solute_results_do_not_depend_on_the_batch():
         assert torch.equal(s1.forces, s.forces[sl]) and torch.equal(e1, e[sl])
     f_ref, e_ref = oracle.forces(g.packed, pos[:2])
     assert np.abs(s.forces[:2].cpu().numpy() - f_ref).max() / np.abs(f_ref).max() < 1e-5
+
+
+@pytest.mark.parametrize("mode", list(MODES))
+def test_large_solute_vs_reference_fp64(mode):
+    """The large-solute kernels against the unmodified reference itself (tests/golden/ala10x3.npz, 312 atoms, fp64 run of
+    TorchMD_Fix/forces.py on the same fp32 positions): same tolerances as the 104-atom fixtures."""
+    g = load_golden("ala10x3")
+    f, e, F = run_gpu(g, g["pos"], **MODES[mode])
+    check(g, g["pos"], f, e, g[f"ref_{mode}_f64_forces"], g[f"ref_{mode}_f64_energies"], mode)
+    np.testing.assert_array_equal(F.ava_idx.cpu().numpy(), g.ava_idx)

@@ -430,3 +430,18 @@ def test_chamber_prmtop_route_pinned_by_namd_energies_at_the_restart_frame():
     ekin = 0.5 * (m[:, None] * vel[0] ** 2).sum()
     assert abs(ekin - namd["KINETIC"]) < 2e-4
     assert abs(2.0 * ekin / ((3 * 104 - 53) * BOLTZMAN) - namd["TEMP"]) < 2e-3
+
+
+@pytest.mark.parametrize("mode", list(MODES))
+def test_oracle_matches_reference_fp64_above_128_atoms(mode):
+    """tests/golden/ala10x3.npz (tools/make_golden_large.py): the unmodified reference on a 312-atom solute -- three
+    deca-alanine chains in one topology -- pins the oracle (and Parameters.tiled, make_pair_index) where the large-solute
+    CUDA kernels run."""
+    g = load_golden("ala10x3")
+    assert g.par.natoms == 312
+    mine = _cabi.make_pair_index(312, g.par.get_exclusions(("bonds", "angles", "1-4")))
+    np.testing.assert_array_equal(mine, g.ava_idx)
+    f, e = oracle.forces(g.packed, g["pos"], **MODES[mode])
+    ref_f, ref_e = g[f"ref_{mode}_f64_forces"], g[f"ref_{mode}_f64_energies"]
+    np.testing.assert_allclose(e, ref_e, rtol=1e-11, atol=1e-10)
+    assert np.abs(f - ref_f).max() <= 1e-11 * np.abs(ref_f).max()
