@@ -12,9 +12,13 @@ S = 1000, energies recorded every 100).  value = replica-steps/s over all GPUs w
 e2e = the same through the public API with pinned HOST buffers (H2D of pos/vel/forces and D2H of
 pos/vel/observables inside the timed region).
 
---impl reference times the reference's CPU implementation of the same path (oracle/torchmd_port.py, the
-torch-op restatement with the reference's per-replica Python loop: /root/reference is not on the GPU box)
-on all host cores, each step being a bounded sample of the same workload.
+--impl reference times the reference's CPU implementation of the same path on all host cores, each step being a
+bounded sample of the same workload: the reference's OWN TorchMD_Fix/forces.py (copied unmodified into oracle/_ref/ by
+tools/make_oracle_ref.py; git-ignored, shipped to the GPU box) under the restated upstream velocity-Verlet loop
+(cpu_baseline.kind "reference"), or, where oracle/_ref is missing, the torch-op port oracle/torchmd_port.py ("port").
+
+--workload forces is BASELINE.json configs[1] as a first-class line: one Forces.compute launch over 65 536 conformers
+(energies in FP64 + forces; --no-energies for the force-only launch the autograd backward uses).
 """
 import argparse
 import json
@@ -50,7 +54,7 @@ def hbm_view(R, S, energy_every, ms_per_launch):
             "frac": ach / peak if peak else None, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peak else None}
 
 
-NCU_DRAM_BYTES_PER_LAUNCH = 31.1e6  # profiles/r01_v20_integrate_kernel.md: 31.08 MB read + 0.04 MB written
+NCU_DRAM_BYTES_PER_LAUNCH = 31.1e6  # profiles/r01_v22_integrate_kernel.md (v23 identical): 31.12 MB read + 0.05 MB written
 BOLTZMAN = 0.001987191
 
 
@@ -129,37 +133,63 @@ class ClockSampler:
 _WORKER_CACHE = {}
 
 
+def cpu_kind():
+    """"reference": oracle/_ref holds the reference's own forces.py; "port": only the torch restatement is here."""
+    from oracle import ref_arm
+
+    return "reference" if ref_arm.available() else "port"
+
+
 def _port_worker(args):
-    """One host core: `nrep` replicas x `nsteps` MD steps with the torch port (1 torch thread)."""
+    """One host core: `nrep` replicas x `nsteps` MD steps (or, nsteps == 0, `nrep` Forces.compute evaluations) with
+    the reference's own forces.py when oracle/_ref is present, else with the torch port (1 torch thread)."""
     import torch
 
     torch.set_num_threads(1)
     from molecular_dynamics_b200 import _cabi
     from molecular_dynamics_b200.parameters import Parameters
+    from oracle import ref_arm
     from oracle import torchmd_port as port
 
-    replica0, nrep, nsteps, dt = args
-    if "top" not in _WORKER_CACHE:
+    replica0, nrep, nsteps, dt, fkw = args
+    use_ref = ref_arm.available()
+    key = ("ref" if use_ref else "port", tuple(sorted(fkw.items())))
+    if key not in _WORKER_CACHE:
         g = load_ala10()
         par = Parameters.from_arrays({k[4:]: v for k, v in g.items() if k.startswith("par_")})
-        packed = _cabi.PackedTopology(par, g["ava_idx"])
-        _WORKER_CACHE["g"], _WORKER_CACHE["top"] = g, port.PortTopology(packed, torch.float32)
-    g, top = _WORKER_CACHE["g"], _WORKER_CACHE["top"]
+        if use_ref:
+            _WORKER_CACHE[key] = (g, par, ref_arm.module("forces").Forces(par, **fkw))
+        else:
+            _WORKER_CACHE[key] = (g, par, port.PortTopology(_cabi.PackedTopology(par, g["ava_idx"]), torch.float32))
+    g, par, top = _WORKER_CACHE[key]
     pos, vel = synth_inputs(g, nrep, replica0)
     pos, vel = torch.tensor(pos), torch.tensor(vel)
     frc = torch.zeros_like(pos)
-    port.compute(top, pos, frc)
-    t0 = time.perf_counter()
-    port.integrate(top, pos, vel, frc, nsteps, dt)
+    box = torch.zeros((nrep, 3, 3))
+    if use_ref:
+        top.compute(pos, box, frc)
+        t0 = time.perf_counter()
+        if nsteps:
+            ref_arm.integrate(top, par.masses, pos, vel, frc, box, nsteps, dt)
+        else:
+            top.compute(pos, box, frc, returnDetails=True)
+    else:
+        port.compute(top, pos, frc, **fkw)
+        t0 = time.perf_counter()
+        if nsteps:
+            port.integrate(top, pos, vel, frc, nsteps, dt, **fkw)
+        else:
+            port.compute(top, pos, frc, **fkw)
     return time.perf_counter() - t0
 
 
-def cpu_port_rate(cores, nrep_per_core, nsteps, pool=None):
-    """replica-steps/s of the torch port over `cores` worker processes (max over workers' wall time)."""
+def cpu_port_rate(cores, nrep_per_core, nsteps, pool=None, fkw=None):
+    """replica-steps/s (nsteps == 0: replica-evaluations/s) of the CPU implementation over `cores` worker processes
+    (max over workers' wall time)."""
     import multiprocessing as mp
 
     dt = 1.0 / TIMEFACTOR
-    jobs = [(c * nrep_per_core, nrep_per_core, nsteps, dt) for c in range(cores)]
+    jobs = [(c * nrep_per_core, nrep_per_core, nsteps, dt, dict(fkw or {})) for c in range(cores)]
     own = pool is None
     if own:
         pool = mp.get_context("spawn").Pool(cores)
@@ -171,7 +201,7 @@ def cpu_port_rate(cores, nrep_per_core, nsteps, pool=None):
         if own:
             pool.close()
             pool.join()
-    return cores * nrep_per_core * nsteps / max(times), max(times), wall
+    return cores * nrep_per_core * max(nsteps, 1) / max(times), max(times), wall
 
 
 def cpu_c_oracle_rate(nrep, nsteps):
@@ -190,6 +220,18 @@ def cpu_c_oracle_rate(nrep, nsteps):
     return nrep * nsteps / (time.perf_counter() - t0)
 
 
+def bench_config(args, R, S):
+    """config keys shared by both arms (the reference arm adds its bounded `sample`)."""
+    if args.workload == "forces":
+        return {"workload": WORKLOAD_NAME_FORCES, "replicas_per_gpu": R, "mode": args.forces_mode,
+                "energies": not args.no_energies, "natoms": 104}
+    return {"workload": WORKLOAD_NAME_C4 if args.workload == "langevin_smd" else WORKLOAD_NAME, "replicas_per_gpu": R,
+            "md_steps_per_launch": S, "energy_every": args.energy_every, "dt_fs": 1.0, "natoms": 104}
+
+
+FORCES_MODES = {"plain": {}, "rf": {"cutoff": 9.0, "rfa": True, "switch_dist": 7.5}}
+
+
 def run_reference(args):
     """--impl reference: the CPU path on all host cores, same metric/config, bounded sample per step."""
     rank = int(os.environ.get("RANK", "0"))
@@ -198,28 +240,40 @@ def run_reference(args):
     import multiprocessing as mp
 
     cores = os.cpu_count() or 1
-    nrep, nsteps = 4, 400  # per core and per bench step: 1 600 replica-steps x ~1.3 ms = ~2 s of CPU work
+    kind = cpu_kind()
+    what = ("the reference's own TorchMD_Fix/forces.py (oracle/_ref, unmodified)" if kind == "reference"
+            else "torch port of TorchMD_Fix/forces.py (oracle/torchmd_port.py)")
+    if args.workload == "forces":
+        nrep, nsteps, fkw = 256, 0, FORCES_MODES[args.forces_mode]  # 256 evaluations per core per bench step (~1 s)
+        unit, metric = "replica-evaluations/s", "ALA10 replica-evaluations/s"
+        sample = f"{cores} procs x {nrep} Forces.compute evaluations per bench step ({what}, fp32, 1 thread each)"
+    else:
+        nrep, nsteps, fkw = 4, 400, {}  # per core and per bench step: 1 600 replica-steps x ~1.3 ms = ~2 s of CPU work
+        unit, metric = "replica-steps/s", "ALA10 replica-steps/s"
+        sample = (f"{cores} procs x {nrep} replicas x {nsteps} MD steps per bench step ({what} + upstream VV loop, fp32, "
+                  f"1 thread each)")
     pool = mp.get_context("spawn").Pool(cores)
     try:
         for _ in range(max(1, min(args.warmup, 1))):
-            cpu_port_rate(cores, nrep, nsteps, pool)
+            cpu_port_rate(cores, nrep, nsteps, pool, fkw)
         units, wall = 0, 0.0
         for _ in range(args.steps):
-            _, slowest, _ = cpu_port_rate(cores, nrep, nsteps, pool)
+            _, slowest, _ = cpu_port_rate(cores, nrep, nsteps, pool, fkw)
             wall += slowest  # slowest worker's compute time: the step ends when the last core finishes
-            units += cores * nrep * nsteps
+            units += cores * nrep * max(nsteps, 1)
     finally:
         pool.close()
         pool.join()
     value = units / wall
-    sample = f"{cores} procs x {nrep} replicas x {nsteps} MD steps per bench step (torch port of TorchMD_Fix/forces.py + upstream VV loop, fp32, 1 thread each)"
+    cfg = bench_config(args, args.replicas, args.inner)
+    cfg["sample"] = sample
     print(json.dumps({
-        "impl": "reference", "metric": "ALA10 replica-steps/s", "value": value, "unit": "replica-steps/s",
+        "impl": "reference", "metric": metric, "value": value, "unit": unit,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD_NAME, "sample": sample},
-        "cpu_baseline": {"value": value, "unit": "replica-steps/s", "cores": cores, "kind": "port", "sample": sample},
-        "e2e": {"value": value, "unit": "replica-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "config": cfg,
+        "cpu_baseline": {"value": value, "unit": unit, "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
 
@@ -228,6 +282,8 @@ WORKLOAD_NAME_C4 = ("configs[3]: ALA10 Langevin 300 K (gamma 1/ps) with the stee
                     "fk 1, centre 12 -> 34 A), fused persistent kernel, dt=1fs, plain all-pairs LJ+Coulomb")
 WORKLOAD_NAME = ("configs[2]: ALA10 NVE velocity-Verlet, 8192 replicas per GPU, fused persistent kernel, "
                  "dt=1fs, plain all-pairs LJ+Coulomb")
+WORKLOAD_NAME_FORCES = ("configs[1]: ALA10 batched energy+force evaluation (Forces.compute) over 65536 synthetic perturbed "
+                        "conformers per GPU, one launch")
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -330,6 +386,8 @@ def run_ours(args):
     h2d = hp.numel() * 4 * 3
     d2h = out_p.numel() * 4 * 2 + out_o.numel() * 8
 
+    forces.check_nan = integ.check_nan = True  # the public call as a user makes it: the NaN / range flag read is inside
+
     def e2e_step():
         system.pos.copy_(hp, non_blocking=True)
         system.vel.copy_(hv, non_blocking=True)
@@ -353,6 +411,47 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = world * R * S * e2e_steps / float(t.item())
+    forces.check_nan = integ.check_nan = False
+
+    # ---- strong scaling: a FIXED total (configs[2]'s 8 192 replicas) split over the ranks, same launches ------------
+    strong = None
+    if args.strong_total > 0 and not config4:
+        from molecular_dynamics_b200.sharding import shard_range
+        lo, hi = shard_range(args.strong_total, rank, world)
+        Rs = hi - lo
+        ps, vs = synth_inputs(g, Rs, lo)
+        sys_s = System(104, Rs, torch.float, dev)
+        sys_s.pos[:] = torch.tensor(ps, device=dev)
+        sys_s.vel[:] = torch.tensor(vs, device=dev)
+        forces.compute_batch(sys_s.pos, sys_s.box, sys_s.forces)
+        integ_s = Integrator(sys_s, forces, timestep=1.0, device=dev)
+        integ_s.energy_every, integ_s.replica0, integ_s.check_nan = args.energy_every, lo, False
+
+        def strong_step():
+            integ_s.step(niter=S)
+            if world > 1:
+                gather_observables(integ_s.observables[-1], args.strong_total)
+
+        for _ in range(2):
+            strong_step()
+        nst = max(3, min(args.steps, 5))
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(nst)]
+        barrier()
+        for a, b in evs:
+            flush.fill_(1)
+            a.record()
+            strong_step()
+            b.record()
+        barrier()
+        ts = torch.tensor([sum(a.elapsed_time(b) for a, b in evs)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+        strong = {"replicas_total": args.strong_total, "replicas_per_gpu": Rs, "md_steps_per_launch": S, "steps": nst,
+                  "value": args.strong_total * S * nst / (float(ts.item()) * 1e-3), "unit": "replica-steps/s",
+                  "ms_per_step": float(ts.item()) / nst, "scaling": "strong",
+                  "note": "the same fused launches over a fixed total of replicas split across the ranks; device-timed, "
+                          "max over ranks, L2 flushed between launches"}
+        del sys_s, integ_s
 
     # ---- secondary workloads (BASELINE.json configs[1] and configs[3]); reported under "extra", N = 1 only -----
     extra = {}
@@ -385,8 +484,12 @@ def run_ours(args):
             f2.check_nan = False
             t2 = timed(lambda: f2.compute_batch(sys2.pos, sys2.box, sys2.forces), 5)
             flop = FLOP_PER_REPLICA_EVAL + (8 * 4820 if kw else 0)
+            t2f = timed(lambda: f2.compute_batch(sys2.pos, sys2.box, sys2.forces, energies=False), 5)
             extra[f"forces_compute_65536_{label}"] = {"value": R2 / t2, "unit": "replica-evaluations/s", "ms_per_launch": 1e3 * t2,
-                                                      "tflops": R2 / t2 * flop / 1e12}
+                                                      "tflops": R2 / t2 * flop / 1e12,
+                                                      "note": "forces fp32 + all 8 energy terms in FP64 (energy pass)",
+                                                      "force_only": {"value": R2 / t2f, "ms_per_launch": 1e3 * t2f,
+                                                                     "tflops": R2 / t2f * flop / 1e12}}
         del sys2, big
         # configs[3]: Langevin 300 K, gamma = 1/ps, steered-MD end-to-end restraint moving 12 -> 34 A
         from molecular_dynamics_b200 import SMDBias
@@ -498,10 +601,9 @@ def run_ours(args):
             "metric": "ALA10 replica-steps/s", "value": value, "unit": "replica-steps/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD_NAME_C4 if config4 else WORKLOAD_NAME, "replicas_per_gpu": R, "md_steps_per_launch": S,
-                       "energy_every": args.energy_every, "dt_fs": 1.0, "natoms": 104,
-                       "l2": "flushed between timed steps (256 MiB fill, outside the event pair)",
-                       "ns_per_day_aggregate": value * 1.0 * 86400 * 1e-6,
+            "config": {**bench_config(args, R, S),
+                       "l2": "flushed between timed steps (256 MiB fill, outside the event pair)"},
+            "detail": {"ns_per_day_aggregate": value * 1.0 * 86400 * 1e-6,
                        "ms_per_step_median_rank0": statistics.median(per_launch), "ms_per_step_max_rank0": max(per_launch),
                        "replicas_with_nan_after_run": nan_count},
             "clocks": clocks.summary(),
@@ -511,7 +613,8 @@ def run_ours(args):
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                          "frac": achieved / peak if peak > 0 else None, "traffic": NCU_DRAM_BYTES_PER_LAUNCH,
                          "traffic_source": "ncu --set full of one 50-step launch, profiles/ (dram read + write; the state is read once per launch whatever its length)",
-                         "peak_source": "measured live: b200md_fp32_peak_tflops (dependent-FMA kernel, all SMs)",
+                         "peak_source": "builder-measured FMA peak, live in this run: b200md_fp32_peak_tflops (dependent-FMA kernel, "
+                                        "all SMs); MEASURED_PEAKS.json carries no FP32 CUDA-core figure, see frac_of_nominal",
                          "nominal_peak": NOMINAL_FP32_TFLOPS, "frac_of_nominal": achieved / NOMINAL_FP32_TFLOPS,
                          "flop_per_replica_step": flop_step, "kernel": "integrate_kernel<0>",
                          "kernel_ms_per_launch": ms / args.steps,
@@ -519,22 +622,155 @@ def run_ours(args):
                                        "HBM view of the same launch is given under 'hbm'",
                          "hbm": hbm_view(R, S, args.energy_every, ms / args.steps)},
         }
+        if strong is not None:
+            extra["strong_scaling"] = strong
         if extra:
             line["extra"] = extra
         if world == 1 and not args.no_cpu:
             cores = os.cpu_count() or 1
             rate, slowest, _ = cpu_port_rate(cores, 4, 3000)
+            kind = cpu_kind()
+            what = ("the reference's own TorchMD_Fix/forces.py (oracle/_ref, unmodified)" if kind == "reference"
+                    else "torch port of TorchMD_Fix/forces.py (oracle/torchmd_port.py)")
             line["cpu_baseline"] = {
-                "value": rate, "unit": "replica-steps/s", "cores": cores, "kind": "port",
-                "sample": f"{cores} procs x 4 replicas x 3000 MD steps of the same workload, torch port of "
-                          f"TorchMD_Fix/forces.py + upstream VV loop (oracle/torchmd_port.py), fp32, 1 thread each; "
-                          f"slowest worker {slowest:.1f} s"}
+                "value": rate, "unit": "replica-steps/s", "cores": cores, "kind": kind,
+                "sample": f"{cores} procs x 4 replicas x 3000 MD steps of the same workload, {what} + upstream VV loop, "
+                          f"fp32, 1 thread each; slowest worker {slowest:.1f} s"}
             try:
                 line["cpu_baseline_c_oracle"] = {
                     "value": cpu_c_oracle_rate(64 * cores, 20), "unit": "replica-steps/s", "cores": cores,
                     "kind": "port", "sample": f"{64 * cores} replicas x 20 MD steps, oracle/md_oracle.c FP64, OpenMP"}
             except Exception as exc:  # the C oracle is optional here
                 line["cpu_baseline_c_oracle"] = {"error": str(exc)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_ours_forces(args):
+    """--workload forces: BASELINE.json configs[1].  One bench step = one Forces.compute launch over R conformers
+    (forces_kernel<MODE>: fp32 forces + the FP64 energy pass); R = 65 536 per GPU, replicas sharded over the ranks with
+    no collective on the data path (the per-replica energies are all-gathered as the reporting step)."""
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import __graft_entry__ as entry
+
+    if not os.path.exists(entry.LIB):
+        entry.build()
+    from molecular_dynamics_b200 import Forces, Parameters, System, _cabi
+    from molecular_dynamics_b200.sharding import gather_observables
+
+    lib = _cabi.load_library()
+    g = load_ala10()
+    par = Parameters.from_arrays({k[4:]: v for k, v in g.items() if k.startswith("par_")}, device=dev)
+    R = args.replicas
+    want_e = not args.no_energies
+    pos_h, _ = synth_inputs(g, R, rank * R)
+    kw = FORCES_MODES[args.forces_mode]
+    F = Forces(par, **kw)
+    F.check_nan = False
+    system = System(104, R, torch.float, dev)
+    system.pos[:] = torch.tensor(pos_h, device=dev)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+
+    def one_step():
+        e = F.compute_batch(system.pos, system.box, system.forces, energies=want_e)
+        if world > 1 and e is not None:
+            gather_observables(e, world * R)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        one_step()
+    barrier()
+    launches0 = lib.b200md_launch_count()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    with ClockSampler(local) as clocks:
+        barrier()
+        for a, b in ev:
+            flush.fill_(1)
+            a.record()
+            one_step()
+            b.record()
+        barrier()
+    launches = lib.b200md_launch_count() - launches0
+    per_launch = [a.elapsed_time(b) for a, b in ev]
+    t = torch.tensor([sum(per_launch)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = world * R * args.steps / (ms * 1e-3)
+
+    # end to end: pinned host positions in, forces + energies back to the host, NaN flag read inside
+    hp = torch.tensor(pos_h).pin_memory()
+    out_f = torch.empty_like(hp).pin_memory()
+    out_e = torch.empty((R, 8), dtype=torch.float64).pin_memory()
+    F.check_nan = True
+
+    def e2e_step():
+        system.pos.copy_(hp, non_blocking=True)
+        e = F.compute_batch(system.pos, system.box, system.forces, energies=want_e)
+        out_f.copy_(system.forces, non_blocking=True)
+        if e is not None:
+            out_e.copy_(e, non_blocking=True)
+        torch.cuda.synchronize()
+
+    e2e_steps = max(3, min(args.steps, 10))
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * R * e2e_steps / float(t.item())
+    if rank == 0:
+        peak = lib.b200md_fp32_peak_tflops(local, 4096)
+        flop = FLOP_PER_REPLICA_EVAL + (8 * 4820 if kw else 0)
+        achieved = value / world * flop / 1e12
+        hbm_bytes = R * (2 * 104 * 12 + (64 if want_e else 0) + 4)
+        line = {
+            "metric": "ALA10 replica-evaluations/s", "value": value, "unit": "replica-evaluations/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {**bench_config(args, R, 0), "l2": "flushed between timed steps (256 MiB fill, outside the event pair)"},
+            "detail": {"ms_per_step_median_rank0": statistics.median(per_launch)},
+            "clocks": clocks.summary(),
+            "e2e": {"value": e2e_value, "unit": "replica-evaluations/s", "h2d_bytes_per_step": hp.numel() * 4,
+                    "d2h_bytes_per_step": out_f.numel() * 4 + (out_e.numel() * 8 if want_e else 0), "steps": e2e_steps},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                         "frac": achieved / peak if peak > 0 else None, "traffic": None,
+                         "peak_source": "builder-measured FMA peak, live in this run (b200md_fp32_peak_tflops)",
+                         "nominal_peak": NOMINAL_FP32_TFLOPS, "frac_of_nominal": achieved / NOMINAL_FP32_TFLOPS,
+                         "flop_per_replica_evaluation": flop, "kernel": f"forces_kernel<{1 if kw else 0}>",
+                         "kernel_ms_per_launch": ms / args.steps,
+                         "hbm": {"algorithmic_bytes_per_launch": hbm_bytes, "achieved_GBps": hbm_bytes / (ms / args.steps * 1e-3) / 1e9},
+                         "bound_note": "FP32 CUDA-core kernel (+ an FP64 energy pass when energies are on); the flop count is "
+                                       "SURVEY 8d's force-evaluation figure and gives the FP64 energy arithmetic no credit"},
+        }
+        if world == 1 and not args.no_cpu:
+            cores = os.cpu_count() or 1
+            rate, slowest, _ = cpu_port_rate(cores, 1024, 0, fkw=kw)
+            kind = cpu_kind()
+            line["cpu_baseline"] = {"value": rate, "unit": "replica-evaluations/s", "cores": cores, "kind": kind,
+                                    "sample": f"{cores} procs x 1024 Forces.compute evaluations of the same conformers "
+                                              f"({'oracle/_ref forces.py, unmodified' if kind == 'reference' else 'torch port'}, fp32, "
+                                              f"1 thread each); slowest worker {slowest:.1f} s"}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -549,14 +785,24 @@ def main():
     ap.add_argument("--replicas", type=int, default=8192, help="replicas per GPU")
     ap.add_argument("--inner", type=int, default=1000, help="MD steps per launch (Integrator.step niter)")
     ap.add_argument("--energy-every", type=int, default=100)
-    ap.add_argument("--workload", default="nve", choices=["nve", "langevin_smd"],
+    ap.add_argument("--workload", default="nve", choices=["nve", "langevin_smd", "forces"],
                     help="nve = configs[2] (the metric's configuration, default); langevin_smd = configs[3] "
-                         "(use --replicas 4096 at 8 GPUs for its 32 768 replicas)")
+                         "(use --replicas 4096 at 8 GPUs for its 32 768 replicas); forces = configs[1] (one "
+                         "Forces.compute launch over --replicas conformers, default 65 536)")
+    ap.add_argument("--forces-mode", default="plain", choices=sorted(FORCES_MODES),
+                    help="--workload forces: plain all-pairs, or rf = cutoff 9 A + reaction field + switch 7.5 A")
+    ap.add_argument("--no-energies", action="store_true", help="--workload forces: force-only launches (no FP64 energy pass)")
+    ap.add_argument("--strong-total", type=int, default=8192,
+                    help="replicas of the strong-scaling leg, split over the ranks (0: skip the leg)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extra", action="store_true", help="skip the secondary workloads (configs[1], configs[3])")
     args = ap.parse_args()
+    if args.workload == "forces" and args.replicas == 8192:
+        args.replicas = 65536
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "forces":
+        run_ours_forces(args)
     else:
         run_ours(args)
 

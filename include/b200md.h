@@ -189,8 +189,10 @@ int b200md_topology_num_constraints(const b200md_topology* topo);
  * Forces.compute (forces.py:82-344) for R replicas: zeroes and fills forces, writes per-term
  * energies.  pos/forces: DEVICE float [R][natoms][3] contiguous; box: DEVICE float [R][3][3] or
  * NULL (= zeros: vacuum); a replica with a non-zero box diagonal is evaluated with the minimum-image convention in
- * every term (wrap_dist, forces.py:107,358-363; off-diagonal entries are ignored like in the reference); energies: DEVICE double [R][8] (FP64-accumulated);
- * status: DEVICE uint32 [R] or NULL.  Asynchronous on `stream`.
+ * every term (wrap_dist, forces.py:107,358-363; off-diagonal entries are ignored like in the reference); energies: DEVICE
+ * double [R][8], every term evaluated in FP64 from the fp32 positions (the reference run in torch.double on the same
+ * inputs), or NULL: forces only (what a backward pass needs; skips the energy pass); status: DEVICE uint32 [R] or
+ * NULL.  Asynchronous on `stream`.
  */
 int b200md_forces_compute(const b200md_topology* topo, const b200md_force_opts* opts,
                           const b200md_smd_opts* smd, int64_t nreplicas, const float* pos,
@@ -202,7 +204,8 @@ int b200md_forces_compute(const b200md_topology* topo, const b200md_force_opts* 
  * pos/vel/forces on chip for all nsteps).  pos/vel/forces are updated in place.  `forces` must hold
  * the forces at `pos` on entry (as left by a previous compute / integrate call).
  * observables: DEVICE double [nreports][R][B200MD_NUM_OBSERVABLES], nreports =
- *   (energy_every > 0 ? nsteps / energy_every : 1); snapshots: DEVICE float
+ *   (energy_every > 0 ? ceil(nsteps / energy_every) : 1): one record every energy_every steps and one after the
+ *   last step of the call when nsteps is not a multiple; snapshots: DEVICE float
  *   [nsteps / snapshot_every][R][natoms][3] or NULL.
  */
 int b200md_integrate(const b200md_topology* topo, const b200md_force_opts* fopts,

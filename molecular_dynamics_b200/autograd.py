@@ -7,7 +7,8 @@ the energies come from a kernel, so the graph edge is provided by an autograd.Fu
     d(sum_k g_k E_k)/d pos = - sum_k g_k F_k
 
 When every enabled term of a replica receives the same upstream weight the total force of the forward
-launch is reused; otherwise the per-term forces F_k are recomputed with one extra launch per term group.
+launch is reused; otherwise the per-term forces F_k are recomputed with one force-only launch per group of
+columns that share a weight (``energies=False``: the FP64 energy pass is skipped).
 """
 from __future__ import annotations
 
@@ -20,7 +21,7 @@ _B = _cabi.TERM_BITS
 # electrostatics, forces.py:202-226)
 _COLUMN_TERMS = {
     0: lambda m: (m & _B["electrostatics"]) | (m & _B["1-4"]),
-    1: lambda m: (m & _B["lj"]) | (m & _B["1-4"]),
+    1: lambda m: (m & (_B["lj"] | _B["repulsion"] | _B["repulsioncg"])) | (m & _B["1-4"]),
     2: lambda m: m & _B["bonds"],
     3: lambda m: m & _B["angles"],
     4: lambda m: m & _B["dihedrals"],
@@ -28,12 +29,31 @@ _COLUMN_TERMS = {
 }
 
 
+def _term_mask(mask, col):
+    """Term bits of the launch that reproduces the forces behind energy column ``col`` (the kernels evaluate the 1-4
+    pairs of any launch whose mask carries 1-4 together with lj / electrostatics; dihedrals need not be on)."""
+    return _COLUMN_TERMS[col](mask)
+
+
 class _EnergyFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, pos, fobj, box, forces):
+        from .forces import SMDBias
+
         ene = fobj.compute_batch(pos, box, forces)
         ctx.fobj = fobj
-        ctx.save_for_backward(pos.detach().contiguous(), box.detach(), forces.detach().clone())
+        # the SMD centre of THIS forward: Energy.calc_energy_batch overwrites bias.center on every call, and a loss
+        # may hold several forwards before its backward (real and fake batch, gradient accumulation)
+        ctx.smd_center = None
+        if isinstance(fobj.external, SMDBias):
+            c = fobj.external.center
+            ctx.smd_center = c.detach().clone() if isinstance(c, torch.Tensor) else float(c)
+        ftot = forces.detach().to(torch.float32).clone()
+        if fobj._last_ext_force is not None:
+            # a generic external object's force is already inside `forces`, and its own torch ops carry its gradient
+            # (energies_with_grad): keep it out of the force this Function differentiates with
+            ftot -= fobj._last_ext_force.to(ftot.dtype)
+        ctx.save_for_backward(pos.detach().to(torch.float32).contiguous(), box.detach(), ftot)
         ctx.in_dtype = pos.dtype
         return ene.to(pos.dtype)
 
@@ -48,11 +68,13 @@ class _EnergyFunction(torch.autograd.Function):
         smd = isinstance(fobj.external, SMDBias)
         if smd:
             cols.append(7)
-        if not cols:
-            return torch.zeros_like(pos), None, None, None
-        gsel = g[:, cols]
+        extra = list(fobj._extra_pair_terms)  # further lj-family terms: columns 8, 9 of the energy tensor
+        allcols = cols + [_cabi.NUM_ENERGIES + k for k in range(len(extra))]
+        if not allcols:
+            return torch.zeros_like(pos).to(ctx.in_dtype), None, None, None
+        gsel = g[:, allcols]
         if bool((gsel == gsel[:, :1]).all()):  # uniform weight per replica: reuse the forward launch
-            grad = -gsel[:, :1, None] * ftot
+            grad = -gsel[:, :1, None].to(ftot.dtype) * ftot
             return grad.to(ctx.in_dtype), None, None, None
         b = box.to(device=pos.device, dtype=torch.float32).contiguous()
         grad = torch.zeros_like(pos)
@@ -71,9 +93,12 @@ class _EnergyFunction(torch.autograd.Function):
             tmask = 0
             for c in grp:
                 if c != 7:
-                    tmask |= _COLUMN_TERMS[c](mask)
-            fobj._launch(pos, b, tmp, terms_mask=tmask, with_smd=7 in grp)
-            grad -= g[:, grp[0]:grp[0] + 1, None] * tmp
+                    tmask |= _term_mask(mask, c)
+            fobj._launch(pos, b, tmp, terms_mask=tmask, with_smd=7 in grp, energies=False, smd_center=ctx.smd_center)
+            grad -= g[:, grp[0]:grp[0] + 1, None].to(tmp.dtype) * tmp
+        for k, term in enumerate(extra):
+            fobj._launch(pos, b, tmp, terms_mask=_B[term], with_smd=False, energies=False)
+            grad -= g[:, _cabi.NUM_ENERGIES + k:_cabi.NUM_ENERGIES + k + 1, None].to(tmp.dtype) * tmp
         return grad.to(ctx.in_dtype), None, None, None
 
 
@@ -96,15 +121,15 @@ def energies_with_grad(fobj, pos, box, forces):
 class _DihedralAngles(torch.autograd.Function):
     @staticmethod
     def forward(ctx, pos, fobj, box):
-        p = pos.detach().contiguous()
-        ctx.fobj, ctx.box = fobj, box
+        p = pos.detach().to(torch.float32).contiguous()
+        ctx.fobj, ctx.box, ctx.in_dtype = fobj, box, pos.dtype
         ctx.save_for_backward(p)
-        return fobj._phi_launch(p, box)
+        return fobj._phi_launch(p, box).to(pos.dtype)
 
     @staticmethod
     def backward(ctx, g):
         (p,) = ctx.saved_tensors
-        return ctx.fobj._phi_launch(p, ctx.box, grad_phi=g.to(torch.float32).contiguous()), None, None
+        return ctx.fobj._phi_launch(p, ctx.box, grad_phi=g.to(torch.float32).contiguous()).to(ctx.in_dtype), None, None
 
 
 def dihedral_angles_with_grad(fobj, pos, box):

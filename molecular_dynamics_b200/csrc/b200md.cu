@@ -40,7 +40,7 @@ __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, co
   for (int k = tid; k < kMaxChunks * kMaxAtoms / 4; k += kThreads)
     ((uint32_t*)S.mask8)[k] = __ldg((const uint32_t*)T.mask8 + k);
   for (int k = tid; k <= kMaxAtoms; k += kThreads) S.gstart[k] = __ldg(T.gather_start + k);
-  for (int k = tid; k < kWarps * kMaxTasks; k += kThreads) S.tasks[k] = __ldg((FIXED ? T.tasks : T.tasks_e) + k);
+  for (int k = tid; k < kWarps * kMaxTasks; k += kThreads) S.tasks[k] = __ldg(T.tasks + k);
   if (tid < 8) { S.smd[tid] = 0.0f; S.box[tid] = 0.0f; }
   // slots of disabled / dropped terms are never written: keep them at zero for the gather
   if (FIXED) {
@@ -53,7 +53,14 @@ __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, co
   for (int k = tid; k < kWarps * 3 * kMaxAtoms; k += kThreads) S.fi[k] = 0.0f;  // i-side partials: armed here, re-armed by the gather
 }
 
+// Positions in double for the energy pass (S.pd overlays vel + sx: callers put a barrier on either side).
+__device__ __forceinline__ void stage_pd(const Smem& S, int tid, float x, float y, float z, float q) {
+  S.pd[tid] = (double)x; S.pd[kMaxAtoms + tid] = (double)y; S.pd[2 * kMaxAtoms + tid] = (double)z;
+  S.pd[3 * kMaxAtoms + tid] = (double)q;
+}
+
 // Forces.compute (forces.py:82-344) for a batch of replicas: one CTA per replica (grid-stride).
+// energies == nullptr: forces only (the autograd backward and compute_batch(..., energies=False)).
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 4)
 forces_kernel(const DevTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
@@ -78,8 +85,8 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
   for (long long r = blockIdx.x; r < R; r += gridDim.x) {
     __syncthreads();  // previous replica fully consumed (and tables staged)
     uint32_t flag = 0;
+    const float x = nx, y = ny, z = nz;
     if (tid < N) {
-      const float x = nx, y = ny, z = nz;
       if (x != x || y != y || z != z) flag |= B200MD_FLAG_NAN_POS;
       S.pos[tid] = make_float4(x, y, z, q);
       S.sx[tid] = x; S.sx[kMaxAtoms + tid] = y; S.sx[2 * kMaxAtoms + tid] = z; S.sx[3 * kMaxAtoms + tid] = q;
@@ -101,10 +108,8 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
     }
     __syncthreads();
     if (flag && status != nullptr) atomicOr(status + r, flag);
-    Energies E;
-    E.clear();
-    if (pbc) run_tasks<MODE, true, false, true>(S, T, P, warp, lane, E);
-    else run_tasks<MODE, true, false, false>(S, T, P, warp, lane, E);
+    if (pbc) run_tasks<MODE, false, true>(S, T, P, warp, lane);
+    else run_tasks<MODE, false, false>(S, T, P, warp, lane);
     if (P.smd_on && tid == kThreads - 1) smd_task(S, P, P.smd_centers ? __ldg(P.smd_centers + r) : P.smd_c0);
     __syncthreads();
     if (tid < N) {
@@ -113,18 +118,42 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
       float* f = forces + (r * N + tid) * 3;
       f[0] = fx; f[1] = fy; f[2] = fz;
     }
-    if (P.smd_on && tid == 0) E.e[B200MD_E_EXTERNAL] += S.smd_energy[0];
-    reduce_energies<B200MD_NUM_ENERGIES>(S, E, warp, lane);
-    if (tid == 0) {
+    if (energies != nullptr) {  // FP64 energy pass; S.sx is free from here on (the force tasks are done)
+      stage_pd(S, tid, x, y, z, tid < N ? q : 0.0f);
+      __syncthreads();
+      Energies E;
+      E.clear();
+      energy_pass<MODE>(S, T, P, pbc, tid, E);
+      if (P.smd_on && tid == 0) E.e[B200MD_E_EXTERNAL] += S.smd_energy[0];
+      reduce_energies<B200MD_NUM_ENERGIES>(S, E, warp, lane);
+      if (tid == 0) {
 #pragma unroll
-      for (int k = 0; k < B200MD_NUM_ENERGIES; ++k) energies[r * B200MD_NUM_ENERGIES + k] = E.e[k];
+        for (int k = 0; k < B200MD_NUM_ENERGIES; ++k) energies[r * B200MD_NUM_ENERGIES + k] = E.e[k];
+      }
     }
   }
 }
 
-// Integrator.step(niter) of upstream TorchMD fused with Forces.compute: positions, velocities and
-// forces of a replica stay in registers / shared memory for all nsteps; HBM sees only the initial
-// load, the final store, the observable records and the optional snapshots.
+__device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u32(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Integrator.step(niter) of upstream TorchMD fused with Forces.compute: positions, velocities and forces of a
+// replica stay in registers / shared memory for a whole SLICE of steps.
+//
+// Work distribution (time slicing): the launch is `nslices` x R units, a unit = `slice_len` consecutive steps of one
+// replica.  The persistent CTAs (one wave: grid <= resident CTAs) draw units slice-major from a global ticket
+// counter; between its slices a replica's state parks in the caller's own pos / vel / forces arrays (3.7 KB, L2).  A
+// CTA that draws slice s of replica r waits for `slice_done[r] >= s` -- the unit with that ticket was drawn earlier,
+// so whoever holds it is running: no deadlock, and a wait only happens when R is within a wave of the resident
+// count.  The arithmetic of a step does not depend on the slicing, so results are bit-identical for every slice
+// length; what it buys is a tail of one slice instead of one whole launch per replica (592 resident CTAs: 1 024
+// replicas x 1 000 steps took two full waves).
 template <int MODE, bool RIGID>
 __global__ void __launch_bounds__(kThreads, 4)
 integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const long long R, float* __restrict__ pos,
@@ -149,15 +178,30 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
   const float vdamp = I.gamma * dt;
   const float inv_dt = 1.0f / dt;
   const int cmax = RIGID ? (int)((T.cnmax >> (8 * warp)) & 0xffu) : 0;
-  for (long long r = blockIdx.x; r < R; r += gridDim.x) {
+  const unsigned long long nunits = (unsigned long long)R * (unsigned long long)I.nslices;
+  for (;;) {
+    __syncthreads();  // the previous unit is complete in every thread (S.tick may be rewritten)
+    if (tid == 0) *S.tick = atomicAdd(I.ticket, 1ull);
     __syncthreads();
+    const unsigned long long unit = *S.tick;
+    if (unit >= nunits) break;
+    const int slice = (int)(unit / (unsigned long long)R);
+    const long long r = (long long)(unit - (unsigned long long)slice * (unsigned long long)R);
+    const int s_begin = slice * I.slice_len, s_end = min(I.nsteps, s_begin + I.slice_len);
+    if (slice > 0) {  // the replica's previous slice must have parked its state
+      if (tid == 0) {
+        while (ld_acquire_u32(I.slice_done + r) < (unsigned int)slice) __nanosleep(100);
+      }
+      __syncthreads();
+      __threadfence();
+    }
     float x = 0.f, y = 0.f, z = 0.f, vx = 0.f, vy = 0.f, vz = 0.f, fx = 0.f, fy = 0.f, fz = 0.f;
     uint32_t flag = 0;
     const long long base = (r * N + tid) * 3;
-    if (live) {
-      x = pos[base]; y = pos[base + 1]; z = pos[base + 2];
-      vx = vel[base]; vy = vel[base + 1]; vz = vel[base + 2];
-      fx = forces[base]; fy = forces[base + 1]; fz = forces[base + 2];
+    if (live) {  // L2 loads: another SM may have written this state a moment ago
+      x = __ldcg(pos + base); y = __ldcg(pos + base + 1); z = __ldcg(pos + base + 2);
+      vx = __ldcg(vel + base); vy = __ldcg(vel + base + 1); vz = __ldcg(vel + base + 2);
+      fx = __ldcg(forces + base); fy = __ldcg(forces + base + 1); fz = __ldcg(forces + base + 2);
       if (x != x || y != y || z != z) flag |= B200MD_FLAG_NAN_POS;
     }
     const float b0 = box ? __ldg(box + r * 9) : 0.0f, b1 = box ? __ldg(box + r * 9 + 4) : 0.0f, b2 = box ? __ldg(box + r * 9 + 8) : 0.0f;
@@ -167,10 +211,11 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       S.box[tid] = -b;
       S.box[4 + tid] = b != 0.0f ? 1.0f / b : 0.0f;
     }
-    if (status != nullptr && tid == 0) status[r] = 0;
-    if (tid == kThreads - 1) S.smd_energy[1] = 0.0;  // same thread as smd_task: no barrier needed
+    if (status != nullptr && tid == 0 && slice == 0) status[r] = 0;
+    // work of the moving restraint since the first step of the launch; same thread as smd_task: no barrier needed
+    if (tid == kThreads - 1) S.smd_energy[1] = (slice > 0 && P.smd_on) ? __ldcg(I.smd_work + r) : 0.0;
     if (RIGID && live) S.pos[tid] = make_float4(x, y, z, q);  // SHAKE reads x(t) from here (visible after its barrier)
-    for (int s = 0; s < I.nsteps; ++s) {
+    for (int s = s_begin; s < s_end; ++s) {
       const unsigned long long gstep = I.step0 + (unsigned long long)s;
       // _first_VV: pos += vel dt + 0.5 a dt^2 ; vel += 0.5 dt a
       vx = fmaf(hdt_m, fx, vx); vy = fmaf(hdt_m, fy, vy); vz = fmaf(hdt_m, fz, vz);
@@ -194,16 +239,10 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       }
       S.vel[tid] = make_float4(vx, vy, vz, 0.0f);  // parked: frees 6 registers across the task phase
       __syncthreads();
-      const bool report = I.energy_every > 0 ? ((s + 1) % I.energy_every == 0) : (s == I.nsteps - 1);
-      Energies E;
-      if (report) {
-        E.clear();
-        if (pbc) run_tasks<MODE, true, true, true>(S, T, P, warp, lane, E);
-        else run_tasks<MODE, true, true, false>(S, T, P, warp, lane, E);
-      } else {
-        if (pbc) run_tasks<MODE, false, true, true>(S, T, P, warp, lane, E);
-        else run_tasks<MODE, false, true, false>(S, T, P, warp, lane, E);
-      }
+      // a record every energy_every steps and after the last step of the call (what step() returns is the end state)
+      const bool report = (I.energy_every > 0 && (s + 1) % I.energy_every == 0) || s == I.nsteps - 1;
+      if (pbc) run_tasks<MODE, true, true>(S, T, P, warp, lane);
+      else run_tasks<MODE, true, false>(S, T, P, warp, lane);
       if (P.smd_on && tid == kThreads - 1) smd_task(S, P, (float)((double)P.smd_c0 + (double)P.smd_rate * (double)(gstep + 1)));
       __syncthreads();
       {
@@ -228,12 +267,18 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
         const float4 vv = S.vel[tid];
         vx = vv.x; vy = vv.y; vz = vv.z;
       }
-      if (report) {
+      if (report) {  // FP64 energies of x(t + dt): the parked velocities and the SoA copy are dead until the next step
+        __syncthreads();  // every thread has read its S.vel entry
+        stage_pd(S, tid, x, y, z, live ? q : 0.0f);
+        __syncthreads();
+        Energies E;
+        E.clear();
+        energy_pass<MODE>(S, T, P, pbc, tid, E);
         if (live) E.e[B200MD_OBS_EKIN] = 0.5 * (double)mass * ((double)vx * vx + (double)vy * vy + (double)vz * vz);
         if (P.smd_on && tid == 0) { E.e[B200MD_E_EXTERNAL] += S.smd_energy[0]; E.e[B200MD_OBS_E2E_DIST] = (double)S.smd[4]; }
         reduce_energies<kNumReduced>(S, E, warp, lane);
         if (tid == 0 && observables != nullptr) {
-          const long long slot = I.energy_every > 0 ? (s + 1) / I.energy_every - 1 : 0;
+          const long long slot = I.energy_every > 0 ? s / I.energy_every : 0;
           double* o = observables + (slot * R + r) * B200MD_NUM_OBSERVABLES;
 #pragma unroll
           for (int k = 0; k < kNumReduced; ++k) o[k] = E.e[k];
@@ -252,8 +297,13 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       forces[base] = fx; forces[base + 1] = fy; forces[base + 2] = fz;
       if (x != x || y != y || z != z) flag |= B200MD_FLAG_NAN_POS;
     }
-    __syncthreads();
     if (flag && status != nullptr) atomicOr(status + r, flag);
+    if (I.nslices > 1) {  // park: publish the state, then the slice count (release)
+      if (P.smd_on && tid == kThreads - 1) I.smd_work[r] = S.smd_energy[1];
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) st_release_u32(I.slice_done + r, (unsigned int)(slice + 1));
+    }
   }
 }
 
@@ -446,6 +496,21 @@ static int fail(int code, const std::string& msg) {
     if (_e != cudaSuccess)                                                                     \
       return fail(B200MD_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));        \
   } while (0)
+
+// Entry points run on the topology's device and put the caller's current device back afterwards (a host that drives
+// several GPUs from one thread must not find its current device changed by a library call).
+struct DeviceGuard {
+  int prev = -1;
+  cudaError_t err;
+  explicit DeviceGuard(int device) {
+    err = cudaGetDevice(&prev);
+    if (err == cudaSuccess && prev != device) err = cudaSetDevice(device); else if (err == cudaSuccess) prev = -1;
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+#define B200MD_ON_DEVICE(dev)                                                                  \
+  DeviceGuard _guard(dev);                                                                     \
+  if (_guard.err != cudaSuccess) return fail(B200MD_ERR_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(_guard.err))
 
 struct b200md_topology {
   int device = 0;
@@ -871,17 +936,16 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   T.p14_on = 1;
   T.dih2_stride = (int)dstride;
 
-  // ---- static task schedules: longest-processing-time-first over the 4 warps ---------------------
-  // Two schedules from two cost models (issue slots per warp, tuned on the GPU with tools/tune_costs.py):
-  // [0] force-only evaluation (the fused integrator), [1] evaluation with energies (single-shot Forces.compute:
-  // energy arithmetic, FP64 bond energies, acosf).  B200MD_COSTS / B200MD_COSTS_E =
-  // "pass,chunk,diaggroup,diag,bond,angle,dih,gen,p14" override them for tuning runs.
+  // ---- static task schedule: longest-processing-time-first over the 4 warps -----------------------
+  // Cost model = issue slots per warp of the force-only tasks, tuned on the GPU with tools/tune_costs.py (the
+  // energies are a separate, evenly strided pass).  B200MD_COSTS = "pass,chunk,diaggroup,diag,bond,angle,dih,gen,p14"
+  // overrides it for tuning runs.
   struct Task { uint32_t word; int cost; };
-  int cms[2][9] = {{105, 120, 52, 30, 77, 230, 380, 400, 100}, {119, 84, 68, 26, 120, 280, 430, 440, 120}};
-  const char* envs[2] = {getenv("B200MD_COSTS"), getenv("B200MD_COSTS_E")};
+  int cms[1][9] = {{105, 120, 52, 30, 77, 230, 380, 400, 100}};
+  const char* envs[1] = {getenv("B200MD_COSTS")};
   const int nblocks = (N + 31) / 32;
-  std::vector<uint32_t> tasks_v[2];
-  for (int sch = 0; sch < 2; ++sch) {
+  std::vector<uint32_t> tasks_v[1];
+  for (int sch = 0; sch < 1; ++sch) {
     int* cm = cms[sch];
     if (envs[sch]) sscanf(envs[sch], "%d,%d,%d,%d,%d,%d,%d,%d,%d", cm, cm + 1, cm + 2, cm + 3, cm + 4, cm + 5, cm + 6, cm + 7, cm + 8);
     std::vector<Task> all;
@@ -920,7 +984,7 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
     const uint32_t kind_order[kNumKinds] = {TASK_TILE, TASK_DIAG, TASK_DIHEDRAL, TASK_IMPROPER, TASK_ANGLE, TASK_BOND, TASK_P14};
     for (int w = 0; w < kWarps; ++w) {
       int n = 0;
-      uint2& k8 = sch ? T.kend8_e[w] : T.kend8[w];
+      uint2& k8 = T.kend8[w];
       k8 = make_uint2(0u, 0u);
       for (int k = 0; k < kNumKinds; ++k) {
         for (uint32_t word : mine[w]) if ((word & 0xff) == kind_order[k]) tasks[(size_t)w * kMaxTasks + n++] = word;
@@ -991,6 +1055,51 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   }
   phi_start[kMaxAtoms] = (uint16_t)phi_items.size();
 
+  // ---- FP64 energy pass: plain item lists in topology order (energy_pass, b200md_forces.cuh) -----------
+  std::vector<uint32_t> e_pair(std::max(d->npairs, 1), 0), e14_idx(std::max(d->n14, 1), 0), eb_idx(std::max(d->nbonds, 1), 0),
+      ea_idx(std::max(d->nangles, 1), 0), et_idx(std::max(ND + d->nimpropers, 1), 0);
+  std::vector<double2> e_ab((size_t)NT * NT);
+  std::vector<double> e14_prm((size_t)3 * std::max(d->n14, 1), 0.0);
+  std::vector<float2> eb_prm(std::max(d->nbonds, 1)), ea_prm(std::max(d->nangles, 1));
+  for (int k = 0; k < NT * NT; ++k) e_ab[k] = make_double2((double)d->lj_a[k], (double)d->lj_b[k]);
+  for (int k = 0; k < d->npairs; ++k) {
+    const int i = d->pair_idx[2 * k], j = d->pair_idx[2 * k + 1];
+    e_pair[k] = (uint32_t)i | ((uint32_t)j << 8) | ((uint32_t)(d->atom_type[i] * NT + d->atom_type[j]) << 16);
+  }
+  for (int k = 0; k < d->n14; ++k) {  // forces.py:197-226: A / scnb, B / scnb, K qi qj / scee
+    const int i = d->idx14[2 * k], j = d->idx14[2 * k + 1];
+    const float* p4 = d->prm14 + 4 * k;
+    const double qi = d->charge ? d->charge[i] : 0.0, qj = d->charge ? d->charge[j] : 0.0;
+    e14_idx[k] = (uint32_t)i | ((uint32_t)j << 8);
+    e14_prm[3 * k] = (double)p4[0] / (double)p4[2];
+    e14_prm[3 * k + 1] = (double)p4[1] / (double)p4[2];
+    e14_prm[3 * k + 2] = 332.06371307417066 * qi * qj / (double)p4[3];
+  }
+  for (int k = 0; k < d->nbonds; ++k) { eb_idx[k] = pack4(d->bond_idx + 2 * k, 2); eb_prm[k] = make_float2(d->bond_prm[2 * k], d->bond_prm[2 * k + 1]); }
+  for (int k = 0; k < d->nangles; ++k) { ea_idx[k] = pack4(d->angle_idx + 3 * k, 3); ea_prm[k] = make_float2(d->angle_prm[2 * k], d->angle_prm[2 * k + 1]); }
+  // torsion terms grouped by their quadruple, slice order kept inside a group (forces.py:559-576); dihedrals, then impropers
+  std::vector<int> et_start(ND + d->nimpropers + 1, 0);
+  std::vector<float4> et_term(std::max(d->ndihedral_terms + d->nimproper_terms, 1));
+  std::vector<double2> et_cs(et_term.size());
+  {
+    for (int q = 0; q < ND; ++q) et_idx[q] = pack4(d->dihedral_idx + 4 * q, 4);
+    for (int q = 0; q < d->nimpropers; ++q) et_idx[ND + q] = pack4(d->improper_idx + 4 * q, 4);
+    for (int t = 0; t < d->ndihedral_terms; ++t) ++et_start[d->dihedral_term_owner[t] + 1];
+    for (int t = 0; t < d->nimproper_terms; ++t) ++et_start[ND + d->improper_term_owner[t] + 1];
+    for (int q = 0; q < ND + d->nimpropers; ++q) et_start[q + 1] += et_start[q];
+    std::vector<int> cur(et_start.begin(), et_start.end() - 1);
+    auto put = [&](int owner, const float* prm3, int harmonic) {
+      const float per = prm3[2];
+      const bool integer = !harmonic && per >= 1.0f && per <= 64.0f && per == floorf(per);
+      const int at = cur[owner]++;
+      et_term[at] = make_float4(prm3[0], prm3[1], per, harmonic ? 1.0f : (integer ? 2.0f : 0.0f));
+      et_cs[at] = make_double2(cos((double)prm3[1]), sin((double)prm3[1]));
+    };
+    for (int t = 0; t < d->ndihedral_terms; ++t) put(d->dihedral_term_owner[t], d->dihedral_term_prm + 3 * t, d->dihedral_term_harmonic[t]);
+    for (int t = 0; t < d->nimproper_terms; ++t) put(ND + d->improper_term_owner[t], d->improper_term_prm + 3 * t, d->improper_term_harmonic[t]);
+  }
+  T.ne_pair = d->npairs; T.ne_14 = d->n14; T.ne_bond = d->nbonds; T.ne_angle = d->nangles; T.ne_dih = ND; T.ne_imp = d->nimpropers;
+
   // ---- upload --------------------------------------------------------------------------------------
   BlobBuilder B;
   const size_t o_ab = B.add(ab), o_q = B.add(charge), o_m = B.add(mass), o_ro = B.add(rowoff), o_mask = B.add(mask8), o_rot = B.add(diagmask);
@@ -999,11 +1108,15 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   const size_t o_di = B.add(dih2_idx), o_dc = B.add(dih2_coef), o_dk = B.add(dih2_k0), o_ds = B.add(dih2_slot), o_d14 = B.add(dih2_p14ab), o_dq = B.add(dih2_p14q);
   const size_t o_gi = B.add(gen_idx), o_gt = B.add(gen_terms), o_gp = B.add(gen_tp), o_gsl = B.add(gen_slot);
   const size_t o_pi = B.add(p142_idx), o_pp = B.add(p142_ab), o_pq = B.add(p142_q), o_ps = B.add(p142_slot);
-  const size_t o_gs = B.add(gstart), o_tk = B.add(tasks_v[0]), o_tke = B.add(tasks_v[1]);
+  const size_t o_gs = B.add(gstart), o_tk = B.add(tasks_v[0]);
+  const size_t o_ep = B.add(e_pair), o_eab = B.add(e_ab), o_e14i = B.add(e14_idx), o_e14p = B.add(e14_prm), o_ebi = B.add(eb_idx),
+               o_ebp = B.add(eb_prm), o_eai = B.add(ea_idx), o_eap = B.add(ea_prm), o_eti = B.add(et_idx), o_ets = B.add(et_start),
+               o_ett = B.add(et_term), o_etc = B.add(et_cs);
   const size_t o_cg = B.add(cgroup), o_cd = B.add(cdist2), o_cw = B.add(cweight);
   const size_t o_phi = B.add(phi_idx), o_phs = B.add(phi_start), o_phit = B.add(phi_items);
   auto cleanup = [&](const std::string& msg) { fail(B200MD_ERR_CUDA, msg); if (topo->blob) cudaFree(topo->blob); delete topo; };
-  cudaError_t e = cudaSetDevice(device);
+  DeviceGuard guard(device);
+  cudaError_t e = guard.err;
   if (e != cudaSuccess) { cleanup(std::string("cudaSetDevice: ") + cudaGetErrorString(e)); return nullptr; }
   e = cudaMalloc(&topo->blob, B.bytes.size());
   if (e != cudaSuccess) { topo->blob = nullptr; cleanup(std::string("cudaMalloc: ") + cudaGetErrorString(e)); return nullptr; }
@@ -1022,7 +1135,12 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   T.p142_slot = (const uint4*)(base + o_ps);
   T.gather_start = (const uint16_t*)(base + o_gs);
   T.tasks = (const uint32_t*)(base + o_tk);
-  T.tasks_e = (const uint32_t*)(base + o_tke);
+  T.e_pair = (const uint32_t*)(base + o_ep); T.e_ab = (const double2*)(base + o_eab);
+  T.e14_idx = (const uint32_t*)(base + o_e14i); T.e14_prm = (const double*)(base + o_e14p);
+  T.eb_idx = (const uint32_t*)(base + o_ebi); T.eb_prm = (const float2*)(base + o_ebp);
+  T.ea_idx = (const uint32_t*)(base + o_eai); T.ea_prm = (const float2*)(base + o_eap);
+  T.et_idx = (const uint32_t*)(base + o_eti); T.et_start = (const int*)(base + o_ets);
+  T.et_term = (const float4*)(base + o_ett); T.et_cs = (const double2*)(base + o_etc);
   T.phi_idx = (const uchar4*)(base + o_phi); T.phi_start = (const uint16_t*)(base + o_phs); T.phi_items = (const uint16_t*)(base + o_phit);
   T.cgroup = (const int4*)(base + o_cg); T.cdist2 = (const float4*)(base + o_cd); T.cweight = (const float4*)(base + o_cw);
   T.smem_bytes = (int)smem_layout(nullptr, nullptr, NT, T.nslots, false);
@@ -1071,7 +1189,8 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
     charge[a] = d->charge ? d->charge[a] : 0.f;
     mass[a] = d->mass ? d->mass[a] : 1.f;
   }
-  for (int k = 0; k < NT * NT; ++k) { t12a[k] = 12.0f * d->lj_a[k]; t6b[k] = 6.0f * d->lj_b[k]; }
+  std::vector<double2> tab64((size_t)NT * NT);
+  for (int k = 0; k < NT * NT; ++k) { t12a[k] = 12.0f * d->lj_a[k]; t6b[k] = 6.0f * d->lj_b[k]; tab64[k] = make_double2((double)d->lj_a[k], (double)d->lj_b[k]); }
   std::vector<int2> bidx(d->nbonds), i14(d->n14);
   std::vector<float2> bprm(d->nbonds), aprm(d->nangles);
   std::vector<int> aidx(d->angle_idx, d->angle_idx + 3 * (size_t)d->nangles);
@@ -1104,9 +1223,10 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   BlobBuilder B;
   const size_t o_type = B.add(atype), o_q = B.add(charge), o_m = B.add(mass), o_a = B.add(t12a), o_b = B.add(t6b), o_mask = B.add(mask),
                o_bi = B.add(bidx), o_bp = B.add(bprm), o_ai = B.add(aidx), o_ap = B.add(aprm), o_dq = B.add(dq), o_ds = B.add(ds),
-               o_dt = B.add(dt), o_i14 = B.add(i14), o_p14 = B.add(p14), o_iq = B.add(iq), o_is = B.add(is), o_it = B.add(it), o_dcs = B.add(dcs), o_ics = B.add(ics);
+               o_dt = B.add(dt), o_i14 = B.add(i14), o_p14 = B.add(p14), o_iq = B.add(iq), o_is = B.add(is), o_it = B.add(it), o_dcs = B.add(dcs), o_ics = B.add(ics), o_t64 = B.add(tab64);
   cudaDeviceProp prop;
-  if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess ||
+  DeviceGuard guard(device);
+  if (guard.err != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess ||
       cudaMalloc(&topo->blob, B.bytes.size()) != cudaSuccess ||
       cudaMemcpy(topo->blob, B.bytes.data(), B.bytes.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
     if (topo->blob) cudaFree(topo->blob);
@@ -1118,6 +1238,7 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   L.natoms = N; L.ntypes = NT; L.nwords = W;
   L.atom_type = (const int*)(base + o_type); L.charge = (const float*)(base + o_q); L.mass = (const float*)(base + o_m);
   L.tab12a = (const float*)(base + o_a); L.tab6b = (const float*)(base + o_b); L.mask = (const uint32_t*)(base + o_mask);
+  L.tab64 = (const double2*)(base + o_t64);
   L.nbonds = d->nbonds; L.nangles = d->nangles; L.ndih = d->ndihedrals; L.n14 = d->n14; L.nimp = d->nimpropers;
   L.bond_idx = (const int2*)(base + o_bi); L.bond_prm = (const float2*)(base + o_bp);
   L.angle_idx = (const int*)(base + o_ai); L.angle_prm = (const float2*)(base + o_ap);
@@ -1241,7 +1362,7 @@ static int large_forces_compute(const b200md_topology* topo, const ForceParams& 
   int rc = large_alloc(topo, R, false, false, w);
   if (rc) return rc;
   if (status) CUDA_TRY(cudaMemsetAsync(status, 0, sizeof(uint32_t) * (size_t)R, w.st));
-  return large_forces(topo, P, R, pos, box, forces, energies, status, (double)P.smd_c0, true, w);
+  return large_forces(topo, P, R, pos, box, forces, energies, status, (double)P.smd_c0, energies != nullptr, w);
 }
 
 // Integrator.step(niter) for large solutes: the upstream sequence as separate launches per step (the state lives in HBM)
@@ -1259,7 +1380,7 @@ static int large_integrate(const b200md_topology* topo, const ForceParams& P, co
   const size_t frame = sizeof(float) * 3 * (size_t)natom;
   for (int s = 0; s < I.nsteps; ++s) {
     const unsigned long long gstep = I.step0 + (unsigned long long)s;
-    const bool report = I.energy_every > 0 ? ((s + 1) % I.energy_every == 0) : (s == I.nsteps - 1);
+    const bool report = (I.energy_every > 0 && (s + 1) % I.energy_every == 0) || s == I.nsteps - 1;
     large_vv1_kernel<<<(unsigned)((natom + 255) / 256), 256, 0, st>>>(L, I.dt, R, pos, vel, forces);
     const double center = (double)P.smd_c0 + (double)P.smd_rate * (double)(gstep + 1);
     rc = large_forces(topo, P, R, pos, box, forces, w.energies, status, center, report, w);
@@ -1267,7 +1388,7 @@ static int large_integrate(const b200md_topology* topo, const ForceParams& P, co
     large_vv2_kernel<<<dim3(w.nek, (unsigned)std::min<int64_t>(R, 65535)), 256, 0, st>>>(L, I, gstep, R, vel, forces, pos, report ? w.ekin : nullptr, status);
     g_launches.fetch_add(2);
     if (report && observables != nullptr) {
-      const long long slot = I.energy_every > 0 ? (s + 1) / I.energy_every - 1 : 0;
+      const long long slot = I.energy_every > 0 ? s / I.energy_every : 0;
       large_observe_kernel<<<(unsigned)((R + 127) / 128), 128, 0, st>>>(R, w.energies, w.ekin, w.nek, w.smd,
                                                                         observables + slot * R * B200MD_NUM_OBSERVABLES);
       g_launches.fetch_add(1);
@@ -1283,7 +1404,7 @@ static int large_integrate(const b200md_topology* topo, const ForceParams& P, co
 
 extern "C" void b200md_topology_destroy(b200md_topology* topo) {
   if (!topo) return;
-  cudaSetDevice(topo->device);
+  DeviceGuard guard(topo->device);
   if (topo->blob) cudaFree(topo->blob);
   if (topo->ws) cudaFree(topo->ws);
   if (topo->aux) cudaStreamDestroy(topo->aux);
@@ -1300,7 +1421,7 @@ extern "C" int b200md_constrain(const b200md_topology* topo, int64_t R, float* p
   if (topo->dev.ncons < 0)
     return fail(B200MD_ERR_UNSUPPORTED, "rigid_bonds: a hydrogen is bonded to a hydrogen, or a heavy atom carries more than 3");
   if (R == 0 || topo->dev.ncons == 0) return B200MD_OK;
-  CUDA_TRY(cudaSetDevice(topo->device));
+  B200MD_ON_DEVICE(topo->device);
   const int grid = (int)std::min<long long>(R, (long long)topo->num_sms * 8);
   constrain_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(topo->dev, R, pos, vel, status);
   g_launches.fetch_add(1);
@@ -1316,7 +1437,7 @@ extern "C" int b200md_dihedral_angles(const b200md_topology* topo, int64_t R, co
   if (R < 0) return fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica count");
   if (topo->large) return fail(B200MD_ERR_UNSUPPORTED, "the dihedral-angle kernels need natoms <= 128");
   if (R == 0 || topo->dev.nphi == 0) return B200MD_OK;
-  CUDA_TRY(cudaSetDevice(topo->device));
+  B200MD_ON_DEVICE(topo->device);
   const int grid = (int)std::min<long long>(R, (long long)topo->num_sms * 16);
   dihedral_angles_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(topo->dev, R, pos, box, phi);
   g_launches.fetch_add(1);
@@ -1331,7 +1452,7 @@ extern "C" int b200md_dihedral_angles_backward(const b200md_topology* topo, int6
   if (topo->large) return fail(B200MD_ERR_UNSUPPORTED, "the dihedral-angle kernels need natoms <= 128");
   if (topo->dev.nphi > 512) return fail(B200MD_ERR_UNSUPPORTED, "dihedral-angle backward holds at most 512 dihedrals per replica");
   if (R == 0) return B200MD_OK;
-  CUDA_TRY(cudaSetDevice(topo->device));
+  B200MD_ON_DEVICE(topo->device);
   const int grid = (int)std::min<long long>(R, (long long)topo->num_sms * 16);
   dihedral_angles_backward_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(topo->dev, R, pos, box, grad_phi, grad_pos);
   g_launches.fetch_add(1);
@@ -1368,11 +1489,16 @@ static int make_force_params(const b200md_topology* topo, const b200md_force_opt
   const bool sw = P->has_cutoff && o->switch_dist > 0.0f && (o->terms & B200MD_T_LJ);  // forces.py:402 (evaluate_LJ only)
   P->rs = sw ? o->switch_dist : INFINITY;
   P->inv_sw = sw ? 1.0f / (o->cutoff - o->switch_dist) : 0.0f;
+  P->rc_d = (double)o->cutoff;
+  P->rs_d = sw ? (double)o->switch_dist : (double)INFINITY;
+  P->inv_sw_d = sw ? 1.0 / ((double)o->cutoff - (double)o->switch_dist) : 0.0;
   if (o->rfa) {
     if (!P->has_cutoff) return fail(B200MD_ERR_INVALID_ARGUMENT, "rfa needs a cutoff");
     const double eps = o->solvent_dielectric, rc = o->cutoff, denom = 2.0 * eps + 1.0;  // forces.py:466-468
-    P->krf = (float)((1.0 / (rc * rc * rc)) * (eps - 1.0) / denom);
-    P->crf = (float)((1.0 / rc) * (3.0 * eps) / denom);
+    P->krf_d = (1.0 / (rc * rc * rc)) * (eps - 1.0) / denom;
+    P->crf_d = (1.0 / rc) * (3.0 * eps) / denom;
+    P->krf = (float)P->krf_d;
+    P->crf = (float)P->crf_d;
   }
   P->lj_on = (o->terms & B200MD_T_LJ) ? 1.0f : 0.0f;
   P->tab_a = (o->terms & (B200MD_T_LJ | B200MD_T_REPULSION)) ? 1.0f : 0.0f;
@@ -1409,18 +1535,18 @@ static DevTopo apply_terms(const DevTopo& in, uint32_t terms) {
 extern "C" int b200md_forces_compute(const b200md_topology* topo, const b200md_force_opts* opts,
                                      const b200md_smd_opts* smd, int64_t R, const float* pos, const float* box,
                                      float* forces, double* energies, uint32_t* status, void* stream) {
-  if (!topo || !pos || !forces || !energies) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
+  if (!topo || !pos || !forces) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
   if (R < 0) return fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica count");
   if (R == 0) return B200MD_OK;
   ForceParams P;
   int rc = make_force_params(topo, opts, smd, false, &P);
   if (rc) return rc;
   if (topo->large) {
-    CUDA_TRY(cudaSetDevice(topo->device));
+    B200MD_ON_DEVICE(topo->device);
     return large_forces_compute(topo, P, R, pos, box, forces, energies, status, stream);
   }
   DevTopo T = apply_terms(topo->dev, opts->terms);
-  CUDA_TRY(cudaSetDevice(topo->device));
+  B200MD_ON_DEVICE(topo->device);
   const int mode = P.has_cutoff ? 1 : 0;
   const long long cap = (long long)topo->num_sms * topo->occ_forces[mode];
   const int grid = (int)std::min<long long>(R, cap);
@@ -1449,20 +1575,44 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
   int rc = make_force_params(topo, fopts, smd, true, &P);
   if (rc) return rc;
   DevTopo T = apply_terms(topo->dev, fopts->terms);
-  StepParams I;
+  StepParams I{};
   I.dt = io->dt; I.gamma = io->gamma; I.temperature = io->temperature;
   I.seed = io->seed; I.step0 = io->step0; I.replica0 = io->replica0;
   I.nsteps = io->nsteps; I.energy_every = io->energy_every; I.snapshot_every = io->snapshot_every;
-  CUDA_TRY(cudaSetDevice(topo->device));
+  B200MD_ON_DEVICE(topo->device);
   if (topo->large) return large_integrate(topo, P, I, R, pos, vel, forces, box, observables, snapshots, status, stream);
   const int mode = P.has_cutoff ? 1 : 0;
-  // long launches: one CTA per replica, so the hardware block scheduler hands a finished SM its next replica
-  // (a static grid-stride split of 8 192 replicas over 740 resident CTAs ends with a 12th round on 52 CTAs);
-  // short launches keep the grid-stride loop to stage the tables once per resident CTA
-  const long long cap = (long long)topo->num_sms * topo->occ_integrate[mode];
-  const int grid = (int)((io->nsteps >= 32 && R < (1ll << 30)) ? R : std::min<long long>(R, cap));
   cudaStream_t st = (cudaStream_t)stream;
   const bool rigid = io->rigid_bonds != 0 && T.ncons > 0;
+  // One wave of persistent CTAs draws (slice, replica) units from a ticket counter (integrate_kernel).  Slice length:
+  // about 16 rounds of units over the resident CTAs, so that the tail of a launch is a few percent of it, within
+  // [8, 64] steps (parking a replica costs ~3 us against ~7 us per step); B200MD_SLICE overrides it for experiments.
+  const long long cap = (long long)topo->num_sms * topo->occ_integrate[mode];
+  const int grid = (int)std::min<long long>(R, cap);
+  long long slice = (long long)io->nsteps * R / (cap * 16);
+  slice = std::max<long long>(8, std::min<long long>(64, slice));
+  if (const char* e = getenv("B200MD_SLICE")) { const long long v = atoll(e); if (v > 0) slice = v; }
+  slice = std::min<long long>(slice, io->nsteps);
+  I.slice_len = (int)slice;
+  I.nslices = (int)((io->nsteps + slice - 1) / slice);
+  {  // ticket counter, per-replica slice counts and (SMD) carried work: grow-only workspace of the handle, zeroed per launch
+    auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+    const size_t b_t = 256, b_d = I.nslices > 1 ? up(sizeof(unsigned int) * (size_t)R) : 0;
+    const size_t b_w = (I.nslices > 1 && P.smd_on) ? up(sizeof(double) * (size_t)R) : 0;
+    const size_t total = b_t + b_d + b_w;
+    if (topo->ws != nullptr && topo->ws_stream != st) CUDA_TRY(cudaStreamSynchronize(topo->ws_stream));
+    if (total > topo->ws_bytes) {
+      if (topo->ws != nullptr) { CUDA_TRY(cudaStreamSynchronize(topo->ws_stream)); cudaFree(topo->ws); topo->ws = nullptr; topo->ws_bytes = 0; }
+      CUDA_TRY(cudaMalloc(&topo->ws, total));
+      topo->ws_bytes = total;
+    }
+    topo->ws_stream = st;
+    char* wbase = (char*)topo->ws;
+    I.ticket = (unsigned long long*)wbase;
+    I.slice_done = b_d ? (unsigned int*)(wbase + b_t) : nullptr;
+    I.smd_work = b_w ? (double*)(wbase + b_t + b_d) : nullptr;
+    CUDA_TRY(cudaMemsetAsync(wbase, 0, b_t + b_d, st));
+  }
 #define B200MD_LAUNCH_INTEGRATE(M, RG) \
   integrate_kernel<M, RG><<<grid, kThreads, T.smem_bytes_fixed, st>>>(T, P, I, R, pos, vel, forces, box, observables, snapshots, status)
   if (mode == 0) { if (rigid) B200MD_LAUNCH_INTEGRATE(0, true); else B200MD_LAUNCH_INTEGRATE(0, false); }
@@ -1480,7 +1630,7 @@ extern "C" int b200md_forces_compute_host(const b200md_topology* topo, const b20
   if (!topo || !pos_host || !forces_host || !energies_host) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
   if (R <= 0) return R == 0 ? B200MD_OK : fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica count");
   if (smd && smd->enabled && smd->centers) return fail(B200MD_ERR_UNSUPPORTED, "per-replica SMD centres need device memory");
-  CUDA_TRY(cudaSetDevice(topo->device));
+  B200MD_ON_DEVICE(topo->device);
   const size_t n3 = (size_t)R * topo->natoms * 3;
   float *dpos = nullptr, *dbox = nullptr, *dfrc = nullptr;
   double* dene = nullptr;
@@ -1512,7 +1662,8 @@ extern "C" int b200md_forces_compute_host(const b200md_topology* topo, const b20
 }
 
 extern "C" double b200md_fp32_peak_tflops(int device, int iters) {
-  if (cudaSetDevice(device) != cudaSuccess) { fail(B200MD_ERR_CUDA, "cudaSetDevice failed"); return -1.0; }
+  DeviceGuard guard(device);
+  if (guard.err != cudaSuccess) { fail(B200MD_ERR_CUDA, "cudaSetDevice failed"); return -1.0; }
   cudaDeviceProp prop;
   cudaGetDeviceProperties(&prop, device);
   const int blocks = prop.multiProcessorCount * 8, threads = 256;

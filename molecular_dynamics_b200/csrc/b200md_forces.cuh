@@ -5,7 +5,7 @@
 
 namespace b200md {
 
-// Per-thread energy accumulators (FP64; FP32 partial sums are folded in once per pass / item).
+// Per-thread energy accumulators of the FP64 energy pass.
 struct Energies {
   double e[kNumReduced];  // 8 energy slots + Ekin + end-to-end distance
   __device__ __forceinline__ void clear() {
@@ -18,14 +18,13 @@ struct Energies {
 // :451-489).  MODE 0: no cutoff, plain Coulomb.  MODE 1: cutoff with optional reaction field and
 // LJ switching.  Returns s = -(dE/dr)/r so that F_i += s * d, F_j -= s * d with d = r_i - r_j.
 //
-// The force path is written with explicit round-to-nearest intrinsics so that the ENERGY and the
-// force-only instantiations produce bit-identical forces (no compiler-chosen FMA contraction): a
-// trajectory does not depend on how often energies are reported.  (a12, nb6) = (12 A, -6 B).
-// Energies come from the same r^-1, r^-6 (a Newton step on rsqrt was tried and changed nothing measurable:
-// the energy error is set by the fp32 rounding of dx, dy, dz, not by MUFU.RSQ).
-template <int MODE, bool ENERGY>
+// The force path is written with explicit round-to-nearest intrinsics so that the results do not depend on
+// compiler-chosen FMA contraction (every instantiation rounds identically).  (a12, nb6) = (12 A, -6 B).  Energies are not
+// computed here: the fp32 rounding of dx, dy, dz limits a pair energy to ~1e-7 relative, and the lj / electrostatics
+// sums cancel up to 1000:1 -- they come from the FP64 energy pass below.
+template <int MODE>
 __device__ __forceinline__ float pair_eval(float dx, float dy, float dz, float kqi, float qj, float a12, float nb6,
-                                           bool excl, const ForceParams& P, float& pel, float& plj) {
+                                           bool excl, const ForceParams& P) {
   const float r2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
   float rinv = fast_rsqrt(r2);
   if (MODE == 1) excl = excl || !(r2 <= P.rc2);
@@ -36,10 +35,6 @@ __device__ __forceinline__ float pair_eval(float dx, float dy, float dz, float k
   const float glj1 = __fmaf_rn(a12, r6, nb6);  // 12 A r^-6 - 6 B;  glj1 * r6 = -r dE_lj/dr
   if (MODE == 0) {
     const float gc = __fmul_rn(qq, rinv);  // K qi qj / r = -r dE_c/dr
-    if (ENERGY) {
-      pel += gc;
-      plj += __fmul_rn(__fmaf_rn(__fmul_rn(a12, 1.0f / 12.0f), r6, __fmul_rn(nb6, 1.0f / 6.0f)), r6);
-    }
     return __fmul_rn(__fmaf_rn(glj1, r6, gc), r2inv);
   } else {
     const float gc = __fmul_rn(qq, __fmaf_rn(-2.0f * P.krf, r2, rinv));  // -r * forces.py:478
@@ -51,13 +46,8 @@ __device__ __forceinline__ float pair_eval(float dx, float dy, float dz, float k
     const float t2 = __fmul_rn(t, t);
     const float sv = __fmaf_rn(__fmul_rn(t2, t), __fmaf_rn(t, __fmaf_rn(t, -6.0f, 15.0f), -10.0f), 1.0f);
     const float nsd = __fmul_rn(__fmul_rn(t2, __fmaf_rn(t, __fmaf_rn(t, 30.0f, -60.0f), 30.0f)), P.inv_sw);
-    float elj = __fmul_rn(__fmaf_rn(__fmul_rn(a12, 1.0f / 12.0f), r6, __fmul_rn(nb6, 1.0f / 6.0f)), r6);
+    const float elj = __fmul_rn(__fmaf_rn(__fmul_rn(a12, 1.0f / 12.0f), r6, __fmul_rn(nb6, 1.0f / 6.0f)), r6);
     glj = __fmaf_rn(sv, glj, __fmul_rn(elj, nsd));
-    elj = __fmul_rn(elj, sv);
-    if (ENERGY) {
-      pel += __fmul_rn(qq, __fadd_rn(rinv, __fmaf_rn(P.krf, r2, -P.crf)));  // forces.py:476
-      plj += elj;
-    }
     return __fmul_rn(__fadd_rn(glj, gc), r2inv);
   }
 }
@@ -77,9 +67,9 @@ __device__ __forceinline__ PairConst make_pair_const(const ForceParams& P) {
   }
   return C;
 }
-template <int MODE, bool ENERGY>
+template <int MODE>
 __device__ __forceinline__ u64 pair_eval2(u64 dx, u64 dy, u64 dz, float kqi, u64 kq2, u64 qj, u64 a12, u64 nb6, bool e0,
-                                          bool e1, const ForceParams& P, const PairConst& C, u64& pel, u64& plj) {
+                                          bool e1, const ForceParams& P, const PairConst& C) {
   const u64 r2 = fma2(dz, dz, fma2(dy, dy, mul2(dx, dx)));
   float r2a, r2b;
   upk(r2, r2a, r2b);
@@ -93,10 +83,6 @@ __device__ __forceinline__ u64 pair_eval2(u64 dx, u64 dy, u64 dz, float kqi, u64
   const u64 glj1 = fma2(a12, r6, nb6);
   if (MODE == 0) {
     const u64 gc = mul2(qq, rinv);
-    if (ENERGY) {  // A r^-12 - B r^-6 = r6 (glj1 + nb6) / 12: plj collects 12 E, the 1/12 is applied once per fold
-      pel = add2(pel, gc);
-      plj = fma2(add2(glj1, nb6), r6, plj);
-    }
     return mul2(fma2(glj1, r6, gc), r2inv);
   } else {
     const u64 gc = mul2(qq, fma2(C.m2krf, r2, rinv));
@@ -108,13 +94,8 @@ __device__ __forceinline__ u64 pair_eval2(u64 dx, u64 dy, u64 dz, float kqi, u64
     const u64 t2 = mul2(t, t);
     const u64 sv = fma2(mul2(t2, t), fma2(t, fma2(t, C.cm6, C.c15), C.cm10), C.one);
     const u64 nsd = mul2(mul2(t2, fma2(t, fma2(t, C.c30, C.cm60), C.c30)), C.inv_sw);
-    u64 elj = mul2(mul2(add2(glj1, nb6), r6), C.c12);
+    const u64 elj = mul2(mul2(add2(glj1, nb6), r6), C.c12);  // A r^-12 - B r^-6 = r6 (glj1 + nb6) / 12
     glj = fma2(sv, glj, mul2(elj, nsd));
-    elj = mul2(elj, sv);
-    if (ENERGY) {
-      pel = add2(pel, mul2(qq, add2(rinv, fma2(C.krf, r2, C.ncrf))));
-      plj = add2(plj, elj);
-    }
     return mul2(add2(glj, gc), r2inv);
   }
 }
@@ -123,9 +104,9 @@ __device__ __forceinline__ u64 pair_eval2(u64 dx, u64 dy, u64 dz, float kqi, u64
 // Lane = i atom; the 8 j atoms arrive as 4 packed pairs (x[], y[], z[], q[] and the 12A / -6B rows are
 // structure-of-arrays, so one LDS.128 delivers two f32x2 operands).  The pass loop is rolled (one body in the
 // instruction cache); the i-side force of a pass is added to this warp's shared-memory partial.
-template <int MODE, bool ENERGY, bool PBC>
+template <int MODE, bool PBC>
 __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, int chunk, int passes, int warp,
-                                          int lane, Energies& E) {
+                                          int lane) {
   const float4 nbox = PBC ? *(const float4*)S.box : make_float4(0.f, 0.f, 0.f, 0.f);
   const float4 ibox = PBC ? *(const float4*)(S.box + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
   u64 fjx[kChunk / 2], fjy[kChunk / 2], fjz[kChunk / 2];
@@ -139,7 +120,6 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
   float4 pi_n = S.pos[lane];
   int roff_n = S.ab_row_off[lane];
   uint32_t m8_n = S.mask8[chunk * kMaxAtoms + lane];
-  u64 pel = 0ull, plj = 0ull;
 #pragma unroll 1
   for (int p = 0; p < passes; ++p) {
     asm volatile("" ::: "memory");  // re-read the 8 broadcast j atoms every pass instead of pinning 32 registers
@@ -166,19 +146,14 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
         const int s = 2 * h + k;
         u64 dx = sub2(xi, k ? xj.y : xj.x), dy = sub2(yi, k ? yj.y : yj.x), dz = sub2(zi, k ? zj.y : zj.x);
         if (PBC) { dx = wrap2(dx, nbox.x, ibox.x); dy = wrap2(dy, nbox.y, ibox.y); dz = wrap2(dz, nbox.z, ibox.z); }
-        const u64 sc = pair_eval2<MODE, ENERGY>(dx, dy, dz, kqi, kq2, k ? qj.y : qj.x, k ? aj.y : aj.x, k ? bj.y : bj.x,
-                                                (m8 >> (2 * s)) & 1u, (m8 >> (2 * s + 1)) & 1u, P, C, pel, plj);
+        const u64 sc = pair_eval2<MODE>(dx, dy, dz, kqi, kq2, k ? qj.y : qj.x, k ? aj.y : aj.x, k ? bj.y : bj.x,
+                                        (m8 >> (2 * s)) & 1u, (m8 >> (2 * s + 1)) & 1u, P, C);
         ax = fma2(sc, dx, ax); ay = fma2(sc, dy, ay); az = fma2(sc, dz, az);
         fjx[s] = fma2(sc, dx, fjx[s]); fjy[s] = fma2(sc, dy, fjy[s]); fjz[s] = fma2(sc, dz, fjz[s]);
       }
     }
     float* f = fiw + p * 32;
     f[0] = __fadd_rn(f[0], hsum2(ax)); f[kMaxAtoms] = __fadd_rn(f[kMaxAtoms], hsum2(ay)); f[2 * kMaxAtoms] = __fadd_rn(f[2 * kMaxAtoms], hsum2(az));
-  }
-  if (ENERGY) {  // per-lane FP32 partial sums of the whole tile (<= 4 passes x 8 pairs), folded into FP64 once
-    float a, b;
-    upk(pel, a, b); E.e[B200MD_E_ELECTROSTATICS] += (double)a + (double)b;
-    upk(plj, a, b); E.e[B200MD_E_LJ] += (double)(MODE == 0 ? __fmul_rn(__fadd_rn(a, b), 1.0f / 12.0f) : __fadd_rn(a, b));
   }
   float fj[kChunk][3];
 #pragma unroll
@@ -227,13 +202,13 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
 // ---- TASK_DIAG: pairs inside one 32-atom block, full shell -----------------------------------------------
 // Lane l owns atom 32*block + l and meets `ng` groups of 4 atoms of its own block as broadcast j atoms, exactly
 // like a tile pass but WITHOUT a j side: every unordered pair is evaluated by both of its lanes (identical
-// r^2, hence identical s and identical energy terms), so there is no partner force to hand back, no shuffle and
+// r^2, hence identical s), so there is no partner force to hand back, no shuffle and
 // no butterfly, and the whole step stays in packed FP32.  17 packed instructions per two pair evaluations against
 // 26 scalar ones + 3 shuffles per pair of the rotation scheme it replaces (profiles/r01_v10: 46 issue slots per
-// rotation step).  Energies are halved.  diagmask bit j: pair (lane, j) is not evaluated (self, exclusion, padding).
-template <int MODE, bool ENERGY, bool PBC>
+// rotation step).  diagmask bit j: pair (lane, j) is not evaluated (self, exclusion, padding).
+template <int MODE, bool PBC>
 __device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams& P, int block, int g0, int ng, int warp,
-                                               int lane, Energies& E) {
+                                               int lane) {
   const float4 nbox = PBC ? *(const float4*)S.box : make_float4(0.f, 0.f, 0.f, 0.f);
   const float4 ibox = PBC ? *(const float4*)(S.box + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
   const int i0 = block * 32;
@@ -246,7 +221,7 @@ __device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams&
   const char* rowb = (const char*)S.tb + roff;
   const float* sj = S.sx + i0 + 4 * g0;
   uint32_t dm = S.diagmask[i0 + lane] >> (4 * g0);
-  u64 pel = 0ull, plj = 0ull, ax = 0ull, ay = 0ull, az = 0ull;
+  u64 ax = 0ull, ay = 0ull, az = 0ull;
   // two groups (4 packed pair steps) per iteration: four independent dependency chains to interleave.  An odd `ng`
   // only occurs at the ragged end of a block, where the extra group is padding (all of its mask bits are set).
 #pragma unroll 1
@@ -261,8 +236,8 @@ __device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams&
       for (int k = 0; k < 2; ++k) {
         u64 dx = sub2(xi, k ? xj.y : xj.x), dy = sub2(yi, k ? yj.y : yj.x), dz = sub2(zi, k ? zj.y : zj.x);
         if (PBC) { dx = wrap2(dx, nbox.x, ibox.x); dy = wrap2(dy, nbox.y, ibox.y); dz = wrap2(dz, nbox.z, ibox.z); }
-        const u64 sc = pair_eval2<MODE, ENERGY>(dx, dy, dz, kqi, kq2, k ? qj.y : qj.x, k ? aj.y : aj.x, k ? bj.y : bj.x,
-                                                (dm >> (4 * u + 2 * k)) & 1u, (dm >> (4 * u + 2 * k + 1)) & 1u, P, C, pel, plj);
+        const u64 sc = pair_eval2<MODE>(dx, dy, dz, kqi, kq2, k ? qj.y : qj.x, k ? aj.y : aj.x, k ? bj.y : bj.x,
+                                        (dm >> (4 * u + 2 * k)) & 1u, (dm >> (4 * u + 2 * k + 1)) & 1u, P, C);
         ax = fma2(sc, dx, ax); ay = fma2(sc, dy, ay); az = fma2(sc, dz, az);
       }
     }
@@ -270,11 +245,6 @@ __device__ __forceinline__ void tile_diag_task(const Smem& S, const ForceParams&
   }
   float* f = S.fi + warp * 3 * kMaxAtoms + i0 + lane;
   f[0] = __fadd_rn(f[0], hsum2(ax)); f[kMaxAtoms] = __fadd_rn(f[kMaxAtoms], hsum2(ay)); f[2 * kMaxAtoms] = __fadd_rn(f[2 * kMaxAtoms], hsum2(az));
-  if (ENERGY) {
-    float a, b;
-    upk(pel, a, b); E.e[B200MD_E_ELECTROSTATICS] += 0.5 * ((double)a + (double)b);
-    upk(plj, a, b); E.e[B200MD_E_LJ] += (double)(MODE == 0 ? __fmul_rn(__fadd_rn(a, b), 0.5f / 12.0f) : __fmul_rn(__fadd_rn(a, b), 0.5f));
-  }
 }
 
 // ---- bonded items: where a force vector goes ---------------------------------------------------------
@@ -353,8 +323,8 @@ __device__ __forceinline__ void emit2_pm(const Smem& S, uint32_t sa0, uint32_t s
 }
 
 // evaluate_bonds, forces.py:111-132, 492-501 -- two bonds per lane
-template <bool ENERGY, bool FIXED, bool PBC>
-__device__ __forceinline__ void bond_task(const Smem& S, const DevTopo& T, const ForceParams& P, int pair, Energies& E) {
+template <bool FIXED, bool PBC>
+__device__ __forceinline__ void bond_task(const Smem& S, const DevTopo& T, const ForceParams& P, int pair) {
   if (pair >= T.nbond2) return;
   const uint2 q = __ldg(T.bond2_idx + pair);
   const float4 prm = __ldg(T.bond2_prm + pair);  // kA, kB, r0A, r0B
@@ -370,29 +340,10 @@ __device__ __forceinline__ void bond_task(const Smem& S, const DevTopo& T, const
   const u64 k2 = pk(keep_a ? fs * prm.x : 0.0f, keep_b ? fs * prm.y : 0.0f);
   const u64 c = mul2(mul2(k2, sub2(dist, pk(prm.z, prm.w))), rinv);  // -(dE/dr) / r (scaled)
   emit2_pm<FIXED>(S, sl.x & 0xffff, sl.x >> 16, sl.z & 0xffff, sl.z >> 16, a0, a1, b0, b1, scale3p(c, d));
-  if (ENERGY) {
-    // k (r - r0)^2 cancels ~40:1 in (r - r0): the energy (report steps only) takes r in FP64
-    const float4 pa0 = S.pos[a0], pa1 = S.pos[a1], pb0 = S.pos[b0], pb1 = S.pos[b1];
-    double bx = 0.0, by = 0.0, bz = 0.0;
-    if (PBC) { bx = -(double)S.box[0]; by = -(double)S.box[1]; bz = -(double)S.box[2]; }
-    auto wrapd = [](double v, double b) { return b != 0.0 ? v - b * rint(v / b) : v; };
-    if (keep_a) {
-      double ddx = (double)pa0.x - (double)pa1.x, ddy = (double)pa0.y - (double)pa1.y, ddz = (double)pa0.z - (double)pa1.z;
-      if (PBC) { ddx = wrapd(ddx, bx); ddy = wrapd(ddy, by); ddz = wrapd(ddz, bz); }
-      const double xd = sqrt(ddx * ddx + ddy * ddy + ddz * ddz) - (double)prm.z;
-      E.e[B200MD_E_BONDS] += (double)prm.x * xd * xd;
-    }
-    if (keep_b) {
-      double ddx = (double)pb0.x - (double)pb1.x, ddy = (double)pb0.y - (double)pb1.y, ddz = (double)pb0.z - (double)pb1.z;
-      if (PBC) { ddx = wrapd(ddx, bx); ddy = wrapd(ddy, by); ddz = wrapd(ddz, bz); }
-      const double xd = sqrt(ddx * ddx + ddy * ddy + ddz * ddz) - (double)prm.w;
-      E.e[B200MD_E_BONDS] += (double)prm.y * xd * xd;
-    }
-  }
 }
 
 // acos on [-1, 1] without branches: sqrt(1 - |x|) * P7(|x|) (Abramowitz & Stegun 4.4.46, |error| <= 2e-8 + fp32
-// rounding), reflected for x < 0.  Used for the FORCE of the angle term; energies take acosf.
+// rounding), reflected for x < 0.  Used for the FORCE of the angle term; the energy pass takes acos in FP64.
 __device__ __forceinline__ u64 acos2(u64 x) {
   float xa, xb;
   upk(x, xa, xb);
@@ -412,8 +363,8 @@ __device__ __forceinline__ u64 acos2(u64 x) {
 }
 
 // evaluate_angles, forces.py:134-145, 504-537 -- two angles per lane
-template <bool ENERGY, bool FIXED, bool PBC>
-__device__ __forceinline__ void angle_task(const Smem& S, const DevTopo& T, int pair, Energies& E) {
+template <bool FIXED, bool PBC>
+__device__ __forceinline__ void angle_task(const Smem& S, const DevTopo& T, int pair) {
   if (pair >= T.nangle2) return;
   const uint2 q = __ldg(T.angle2_idx + pair);
   const float4 prm = __ldg(T.angle2_prm + pair);  // kA, kB, theta0A, theta0B
@@ -428,10 +379,6 @@ __device__ __forceinline__ void angle_task(const Smem& S, const DevTopo& T, int 
   cta = fminf(fmaxf(cta, -1.0f), 1.0f); ctb = fminf(fmaxf(ctb, -1.0f), 1.0f);
   const u64 ct = pk(cta, ctb);
   const u64 dth = sub2(acos2(ct), pk(prm.z, prm.w));
-  if (ENERGY) {
-    const float da = acosf(cta) - prm.z, db = acosf(ctb) - prm.w;
-    E.e[B200MD_E_ANGLES] += (double)(prm.x * da * da) + (double)(prm.y * db * db);
-  }
   float sa, sb;
   upk(fma2(neg2(ct), ct, dup2(1.0f)), sa, sb);
   const float fs = FIXED ? -2.0f * kFixedScale : -2.0f;
@@ -449,8 +396,7 @@ __device__ __forceinline__ void angle_task(const Smem& S, const DevTopo& T, int 
 
 // Two LJ + Coulomb pairs with their own (12 A', -6 B', K qi qj') parameters: forces.py:176-226 (1-4 pairs are
 // never cut, switched or reaction-field corrected).  Returns s with F_a += s d, F_b -= s d, d = r_a - r_b.
-template <bool ENERGY>
-__device__ __forceinline__ u64 pair14_2(v3p d, u64 a12, u64 nb6, u64 qq, const ForceParams& P, Energies& E) {
+__device__ __forceinline__ u64 pair14_2(v3p d, u64 a12, u64 nb6, u64 qq, const ForceParams& P) {
   const u64 r2 = dot3p(d, d);
   u64 rinv = rsqrt2(r2);
   rinv = mul2(rinv, fma2(mul2(mul2(r2, rinv), dup2(-0.5f)), rinv, dup2(1.5f)));  // Newton step: the value is raised to r^-12
@@ -458,13 +404,6 @@ __device__ __forceinline__ u64 pair14_2(v3p d, u64 a12, u64 nb6, u64 qq, const F
   a12 = mul2(a12, dup2(P.lj_on)); nb6 = mul2(nb6, dup2(P.lj_on)); qq = mul2(qq, dup2(P.el_on));
   const u64 ec = mul2(qq, rinv);
   const u64 glj = mul2(fma2(a12, r6, nb6), r6);
-  if (ENERGY) {
-    float a, b;
-    upk(mul2(fma2(mul2(a12, dup2(1.0f / 12.0f)), r6, mul2(nb6, dup2(1.0f / 6.0f))), r6), a, b);
-    E.e[B200MD_E_LJ] += (double)a + (double)b;
-    upk(ec, a, b);
-    E.e[B200MD_E_ELECTROSTATICS] += (double)a + (double)b;
-  }
   return mul2(add2(glj, ec), r2inv);
 }
 
@@ -473,9 +412,8 @@ __device__ __forceinline__ u64 pair14_2(v3p d, u64 a12, u64 nb6, u64 qq, const F
 // periodicity n, so any number of terms costs the same and there is no branch: cos / sin(n phi) come from
 // (cos phi + i sin phi)^n, phi = -atan2(sinPhi, cosPhi) is never formed.  `nmax` (largest periodicity of the chunk)
 // is warp-uniform.  The 1-4 pair on the end atoms (forces.py:176-226) is fused in (zero parameters if there is none).
-template <bool ENERGY, bool FIXED, bool PBC>
-__device__ __forceinline__ void dihedral_task(const Smem& S, const DevTopo& T, const ForceParams& P, int pair, int nmax,
-                                              Energies& E) {
+template <bool FIXED, bool PBC>
+__device__ __forceinline__ void dihedral_task(const Smem& S, const DevTopo& T, const ForceParams& P, int pair, int nmax) {
   if (pair >= T.ndih2) return;
   const uint2 q = __ldg(T.dih2_idx + pair);
   const uint4 sl = FIXED ? make_uint4(0u, 0u, 0u, 0u) : __ldg(T.dih2_slot + pair);
@@ -494,7 +432,7 @@ __device__ __forceinline__ void dihedral_task(const Smem& S, const DevTopo& T, c
     const u64 cosPhi = mul2(dot3p(cA, cB), rab), sinPhi = mul2(mul2(n23, dot3p(r12, cB)), rab);
     const u64 hinv = rsqrt2(fma2(cosPhi, cosPhi, mul2(sinPhi, sinPhi)));
     const u64 c = mul2(cosPhi, hinv), s = neg2(mul2(sinPhi, hinv));  // cos / sin of phi = -atan2(sinPhi, cosPhi)
-    u64 cn = c, sn = s, coeff = 0ull, pot = 0ull;
+    u64 cn = c, sn = s, coeff = 0ull;
     const float4* cf = T.dih2_coef + pair;
 #pragma unroll 1
     for (int n = 1; n <= nmax; ++n) {
@@ -502,16 +440,9 @@ __device__ __forceinline__ void dihedral_task(const Smem& S, const DevTopo& T, c
       cf += T.dih2_stride;
       const u64 ca = pk(k4.x, k4.y), cb = pk(k4.z, k4.w);
       coeff = fma2(cb, cn, fma2(neg2(ca), sn, coeff));  // dE/dphi += n (b_n cos(n phi) - a_n sin(n phi))
-      if (ENERGY) pot = fma2(fma2(ca, cn, mul2(cb, sn)), dup2(1.0f / (float)n), pot);
       const u64 t0 = fma2(cn, c, neg2(mul2(sn, s)));
       sn = fma2(cn, s, mul2(sn, c));
       cn = t0;
-    }
-    if (ENERGY) {
-      const float2 k0 = __ldg(T.dih2_k0 + pair);
-      float a, b;
-      upk(pot, a, b);
-      E.e[B200MD_E_DIHEDRALS] += ((double)k0.x + (double)a) + ((double)k0.y + (double)b);
     }
     // OpenMM-style projection (forces.py:582-600), coefficient pre-scaled for the fixed-point accumulators
     coeff = mul2(mul2(coeff, fs), n23);
@@ -530,7 +461,7 @@ __device__ __forceinline__ void dihedral_task(const Smem& S, const DevTopo& T, c
     const float4 ab = __ldg(T.dih2_p14ab + pair);
     const float2 qq = __ldg(T.dih2_p14q + pair);
     const v3p d = diff3p<PBC>(S, p0, p3);
-    const u64 sc = mul2(pair14_2<ENERGY>(d, pk(ab.x, ab.y), pk(ab.z, ab.w), pk(qq.x, qq.y), P, E), fs);
+    const u64 sc = mul2(pair14_2(d, pk(ab.x, ab.y), pk(ab.z, ab.w), pk(qq.x, qq.y), P), fs);
     f0 = {fma2(sc, d.x, f0.x), fma2(sc, d.y, f0.y), fma2(sc, d.z, f0.z)};
     f3 = {fma2(neg2(sc), d.x, f3.x), fma2(neg2(sc), d.y, f3.y), fma2(neg2(sc), d.z, f3.z)};
   }
@@ -541,8 +472,8 @@ __device__ __forceinline__ void dihedral_task(const Smem& S, const DevTopo& T, c
 }
 
 // 1-4 pairs that no packed dihedral owns (their dihedral has k = 0 everywhere, or is a general torsion)
-template <bool ENERGY, bool FIXED, bool PBC>
-__device__ __forceinline__ void p14_task(const Smem& S, const DevTopo& T, const ForceParams& P, int pair, Energies& E) {
+template <bool FIXED, bool PBC>
+__device__ __forceinline__ void p14_task(const Smem& S, const DevTopo& T, const ForceParams& P, int pair) {
   if (pair >= T.n14_2) return;
   const uint2 q = __ldg(T.p142_idx + pair);
   const uint4 sl = FIXED ? make_uint4(0u, 0u, 0u, 0u) : __ldg(T.p142_slot + pair);
@@ -550,15 +481,15 @@ __device__ __forceinline__ void p14_task(const Smem& S, const DevTopo& T, const 
   const float2 qq = __ldg(T.p142_q + pair);
   const uint32_t a0 = q.x & 0xff, a1 = (q.x >> 8) & 0xff, b0 = q.y & 0xff, b1 = (q.y >> 8) & 0xff;
   const v3p d = diff3p<PBC>(S, load3p(S, a0, b0), load3p(S, a1, b1));
-  const u64 sc = mul2(pair14_2<ENERGY>(d, pk(ab.x, ab.y), pk(ab.z, ab.w), pk(qq.x, qq.y), P, E), dup2(FIXED ? kFixedScale : 1.0f));
+  const u64 sc = mul2(pair14_2(d, pk(ab.x, ab.y), pk(ab.z, ab.w), pk(qq.x, qq.y), P), dup2(FIXED ? kFixedScale : 1.0f));
   emit2_pm<FIXED>(S, sl.x & 0xffff, sl.x >> 16, sl.z & 0xffff, sl.z >> 16, a0, a1, b0, b1, scale3p(sc, d));
 }
 
 // General torsion, one item per lane: evaluate_torsion, forces.py:147-174 / 228-255, 540-602, for what the packed
 // series cannot express -- impropers (either branch), CHARMM harmonic slices, non-integer or > 6 periodicities.
 // Items [0, nspec) are special dihedrals (energy slot "dihedrals"), the rest impropers.
-template <bool ENERGY, bool FIXED, bool PBC>
-__device__ __forceinline__ void torsion_task(const Smem& S, const DevTopo& T, int item, Energies& E) {
+template <bool FIXED, bool PBC>
+__device__ __forceinline__ void torsion_task(const Smem& S, const DevTopo& T, int item) {
   if (item < T.gen_begin || item >= T.gen_end) return;
   const uint32_t q = __ldg(T.gen_idx + item);
   const uint2 sl = FIXED ? make_uint2(0u, 0u) : __ldg(T.gen_slot + item);
@@ -579,7 +510,7 @@ __device__ __forceinline__ void torsion_task(const Smem& S, const DevTopo& T, in
   const float hinv = fast_rsqrt(fmaf(cosPhi, cosPhi, sinPhi * sinPhi));
   const float c = cosPhi * hinv, s = -sinPhi * hinv;  // cos / sin of phi = -atan2(sinPhi, cosPhi)
   const uint2 tr = __ldg(T.gen_terms + item);
-  float pot = 0.0f, coeff = 0.0f;
+  float coeff = 0.0f;
   for (uint32_t t = tr.x; t < tr.x + tr.y; ++t) {
     const float4 tp = __ldg(T.gen_term_prm + t);  // k0, per | marker, c0, s0
     if (tp.y > 0.0f) {                            // AMBER, integer periodicity (forces.py:565-569)
@@ -589,7 +520,6 @@ __device__ __forceinline__ void torsion_task(const Smem& S, const DevTopo& T, in
         sn = fmaf(cn, s, sn * c);
         cn = t0;
       }
-      pot += tp.x * (1.0f + fmaf(cn, tp.z, sn * tp.w));      // k (1 + cos(n phi - phi0))
       coeff -= tp.y * tp.x * fmaf(sn, tp.z, -cn * tp.w);     // -n k sin(n phi - phi0)
     } else {
       const float phi = atan2f(s, c);
@@ -597,17 +527,12 @@ __device__ __forceinline__ void torsion_task(const Smem& S, const DevTopo& T, in
         float ad = phi - tp.z;
         const float pi_f = 3.14159265358979323846f;
         if (ad < -pi_f) ad += 2.0f * pi_f; else if (ad > pi_f) ad -= 2.0f * pi_f;
-        pot += tp.x * ad * ad;
         coeff += 2.0f * tp.x * ad;
       } else {                              // AMBER with a non-integer periodicity: general path
-        float sn, cs;
-        sincosf(fmaf(tp.w, phi, -tp.z), &sn, &cs);
-        pot += tp.x * (1.0f + cs);
-        coeff -= tp.w * tp.x * sn;
+        coeff -= tp.w * tp.x * sinf(fmaf(tp.w, phi, -tp.z));  // E = k (1 + cos(per phi - phi0))
       }
     }
   }
-  if (ENERGY) E.e[item < T.nspec ? B200MD_E_DIHEDRALS : B200MD_E_IMPROPERS] += (double)pot;
   if (FIXED) coeff *= kFixedScale;
   // OpenMM-style projection (forces.py:582-600)
   const float ff0 = -coeff * n23 * (rnA * rnA), ff3 = coeff * n23 * (rnB * rnB);
@@ -622,16 +547,158 @@ __device__ __forceinline__ void torsion_task(const Smem& S, const DevTopo& T, in
   emit<FIXED>(S, sl.y >> 16, q >> 24, -bx, -by, -bz);
 }
 
+// =====================================================================================================
+// FP64 energy pass: every term of Forces.compute (forces.py:82-344) evaluated in double from the fp32 positions,
+// the arithmetic of the reference run in torch.double on the same fp32-rounded inputs (the contract is
+// 1e-6 relative PER TERM; lj / electrostatics cancel up to 1000:1, so fp32 pair terms cannot meet it).  Forces never
+// come from here.  Item lists in topology order, one item per thread, strided by the CTA; per-thread FP64
+// accumulators are block-reduced in a fixed order afterwards (reduce_energies).  Positions are read from S.pd
+// (x[128], y[128], z[128], q[128] in double, written by the caller from its registers).
+// =====================================================================================================
+constexpr double kElecFactorD = 332.06371307417066;  // forces.py:373-376 with the reference's scipy constants
+
+struct dv3 { double x, y, z; };
+// calculate_distances (forces.py:366-370) in double; `pbc` is uniform over the CTA (one replica), so a run-time flag costs
+// a predictable branch instead of a second copy of the FP64 code
+__device__ __forceinline__ dv3 ediff(const Smem& S, bool pbc, int i, int j) {
+  dv3 d = {S.pd[i] - S.pd[j], S.pd[kMaxAtoms + i] - S.pd[kMaxAtoms + j], S.pd[2 * kMaxAtoms + i] - S.pd[2 * kMaxAtoms + j]};
+  if (pbc) {  // wrap_dist, forces.py:358-363 (S.box holds -box; a zero entry leaves its axis alone)
+    const double bx = -(double)S.box[0], by = -(double)S.box[1], bz = -(double)S.box[2];
+    if (bx != 0.0) d.x -= bx * rint(d.x / bx);
+    if (by != 0.0) d.y -= by * rint(d.y / by);
+    if (bz != 0.0) d.z -= bz * rint(d.z / bz);
+  }
+  return d;
+}
+__device__ __forceinline__ double edot(dv3 a, dv3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ dv3 ecross(dv3 a, dv3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+
+// evaluate_torsion (forces.py:540-576), energy only.  Integer-periodicity AMBER terms never form phi: cos / sin(n phi)
+// come from (cos phi + i sin phi)^n, cos / sin(phi0) from the host in FP64.
+__device__ __noinline__ double etorsion(const Smem& S, const DevTopo& T, bool pbc, int d) {
+  const uint32_t q = __ldg(T.et_idx + d);
+  const int a0 = q & 0xff, a1 = (q >> 8) & 0xff, a2 = (q >> 16) & 0xff, a3 = q >> 24;
+  const dv3 r12 = ediff(S, pbc, a0, a1), r23 = ediff(S, pbc, a1, a2), r34 = ediff(S, pbc, a2, a3);
+  const dv3 cA = ecross(r12, r23), cB = ecross(r23, r34), cC = ecross(r23, cA);
+  const double inA = rsqrt(edot(cA, cA)), inB = rsqrt(edot(cB, cB)), inC = rsqrt(edot(cC, cC));
+  const double cosPhi = edot(cA, cB) * inB * inA, sinPhi = edot(cC, cB) * inB * inC;  // forces.py:548-551
+  const double hinv = rsqrt(cosPhi * cosPhi + sinPhi * sinPhi);
+  const double c1 = cosPhi * hinv, s1 = -sinPhi * hinv;  // cos / sin of phi = -atan2(sinPhi, cosPhi)
+  double phi = 0.0, pot = 0.0;
+  bool have_phi = false;
+  const int t1 = __ldg(T.et_start + d + 1);
+  for (int t = __ldg(T.et_start + d); t < t1; ++t) {
+    const float4 tp = __ldg(T.et_term + t);
+    const double k0 = tp.x;
+    if (tp.w == 2.0f) {  // k (1 + cos(n phi - phi0)), forces.py:565-567
+      const double2 cs0 = __ldg(T.et_cs + t);
+      double cn = c1, sn = s1;
+      for (int k = 1; k < (int)tp.z; ++k) {
+        const double cc = cn * c1 - sn * s1;
+        sn = sn * c1 + cn * s1;
+        cn = cc;
+      }
+      pot += k0 * (1.0 + (cn * cs0.x + sn * cs0.y));
+      continue;
+    }
+    if (!have_phi) { phi = -atan2(sinPhi, cosPhi); have_phi = true; }
+    if (tp.w == 0.0f) {
+      pot += k0 * (1.0 + cos((double)tp.z * phi - (double)tp.y));
+    } else {  // CHARMM harmonic, forces.py:570-574
+      double ad = phi - (double)tp.y;
+      if (ad < -M_PI) ad += 2.0 * M_PI; else if (ad > M_PI) ad -= 2.0 * M_PI;
+      pot += k0 * ad * ad;
+    }
+  }
+  return pot;
+}
+
+template <int MODE>
+__device__ __noinline__ void energy_pass(const Smem& S, const DevTopo& T, const ForceParams& P, bool pbc, int tid, Energies& E) {
+  double eel = 0.0, elj = 0.0, ebond = 0.0, eang = 0.0, edih = 0.0, eimp = 0.0;
+  // ---- non-bonded pairs = Forces.ava_idx (forces.py:258-316); the row-major list keeps i warp-uniform and j consecutive
+  if (P.terms & (B200MD_T_ELECTROSTATICS | B200MD_T_LJ | B200MD_T_REPULSION | B200MD_T_REPULSIONCG)) {
+    const double ta = (double)P.tab_a, tb = (double)P.tab_b, rc2 = P.rc_d * P.rc_d;
+    for (int k = tid; k < T.ne_pair; k += kThreads) {
+      const uint32_t w = __ldg(T.e_pair + k);
+      const int i = w & 0xff, j = (w >> 8) & 0xff;
+      const dv3 d = ediff(S, pbc, i, j);
+      const double r2 = edot(d, d);
+      if (MODE == 1 && !(r2 <= rc2)) continue;  // _filter_by_cutoff, forces.py:75-80
+      const double rinv = rsqrt(r2), r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
+      const double2 ab = __ldg(T.e_ab + (w >> 16));
+      const double qq = kElecFactorD * S.pd[3 * kMaxAtoms + i] * S.pd[3 * kMaxAtoms + j];
+      double lj = (ta * ab.x * r6 + tb * ab.y) * r6;  // lj: A r^-12 - B r^-6; repulsion: A r^-12; repulsioncg: B r^-6
+      if (MODE == 1) {
+        const double r = r2 * rinv;
+        if (r > P.rs_d) {  // forces.py:401-411 (rs_d = +inf without a switch)
+          const double t = (r - P.rs_d) * P.inv_sw_d;
+          lj *= 1.0 + t * t * t * (-10.0 + t * (15.0 - t * 6.0));
+        }
+        eel += qq * (rinv + P.krf_d * r2 - P.crf_d);  // forces.py:476 (krf = crf = 0 without rfa)
+      } else {
+        eel += qq * rinv;
+      }
+      elj += lj;
+    }
+  }
+  // ---- 1-4 pairs (forces.py:176-226): never cut, switched or reaction-field corrected
+  if (T.p14_on) {
+    const double ljon = (double)P.lj_on, elon = (double)P.el_on;
+    for (int k = tid; k < T.ne_14; k += kThreads) {
+      const uint32_t w = __ldg(T.e14_idx + k);
+      const dv3 d = ediff(S, pbc, w & 0xff, (w >> 8) & 0xff);
+      const double r2 = edot(d, d), rinv = rsqrt(r2), r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
+      elj += ljon * (__ldg(T.e14_prm + 3 * k) * r6 - __ldg(T.e14_prm + 3 * k + 1)) * r6;
+      eel += elon * __ldg(T.e14_prm + 3 * k + 2) * rinv;
+    }
+  }
+  // ---- bonds (forces.py:111-132, 492-501)
+  if (T.nbond2 > 0) {
+    for (int k = tid; k < T.ne_bond; k += kThreads) {
+      const uint32_t w = __ldg(T.eb_idx + k);
+      const float2 kp = __ldg(T.eb_prm + k);
+      const dv3 d = ediff(S, pbc, w & 0xff, (w >> 8) & 0xff);
+      const double dist = sqrt(edot(d, d));
+      if (P.has_cutoff && !(dist <= P.rc_d)) continue;
+      const double x = dist - (double)kp.y;
+      ebond += (double)kp.x * x * x;
+    }
+  }
+  // ---- angles (forces.py:134-145, 504-518)
+  if (T.nangle2 > 0) {
+    for (int k = tid; k < T.ne_angle; k += kThreads) {
+      const uint32_t w = __ldg(T.ea_idx + k);
+      const float2 kp = __ldg(T.ea_prm + k);
+      const int a1 = (w >> 8) & 0xff;
+      const dv3 r21 = ediff(S, pbc, w & 0xff, a1), r23 = ediff(S, pbc, (w >> 16) & 0xff, a1);
+      double ct = edot(r23, r21) * rsqrt(edot(r21, r21)) * rsqrt(edot(r23, r23));
+      ct = ct < -1.0 ? -1.0 : (ct > 1.0 ? 1.0 : ct);
+      const double dth = acos(ct) - (double)kp.y;
+      eang += (double)kp.x * dth * dth;
+    }
+  }
+  // ---- proper torsions and impropers (forces.py:147-174, 228-255)
+  {
+    const int k0 = T.dih_on ? 0 : T.ne_dih, k1 = T.gen_end > T.nspec ? T.ne_dih + T.ne_imp : T.ne_dih;  // enabled kinds
+    for (int k = k0 + tid; k < k1; k += kThreads) {
+      const double e = etorsion(S, T, pbc, k);
+      if (k < T.ne_dih) edih += e; else eimp += e;
+    }
+  }
+  E.e[B200MD_E_ELECTROSTATICS] += eel; E.e[B200MD_E_LJ] += elj; E.e[B200MD_E_BONDS] += ebond;
+  E.e[B200MD_E_ANGLES] += eang; E.e[B200MD_E_DIHEDRALS] += edih; E.e[B200MD_E_IMPROPERS] += eimp;
+}
+
 // ---- all tasks of this warp for one force evaluation; positions must be in S.pos ------------------
 // The warp's static task list is sorted by kind on the host (T.kend[warp][k] = end of the k-th run), so every kind
 // is a tight loop around its own body: no switch, and the next task word is fetched while the current task runs
 // (the fetch -> decode -> branch chain of a switch-per-task loop cost 33 issue slots and ~150 cycles of exposed
 // latency per task, profiles/r01_v11).
-template <int MODE, bool ENERGY, bool FIXED, bool PBC>
-__device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const ForceParams& P, int warp, int lane,
-                                          Energies& E) {
+template <int MODE, bool FIXED, bool PBC>
+__device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const ForceParams& P, int warp, int lane) {
   const uint32_t* tk = S.tasks + warp * kMaxTasks;
-  const uint2 kends = FIXED ? T.kend8[warp] : T.kend8_e[warp];  // the 7 run ends as bytes: one constant load instead of one per kind
+  const uint2 kends = T.kend8[warp];  // the 7 run ends as bytes: one constant load instead of one per kind
   int t = 0;
   uint32_t next = tk[0];
 #define B200MD_TASK_LOOP(K, BODY)                                                     \
@@ -646,13 +713,13 @@ __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const
       BODY;                                                                           \
     }                                                                                 \
   }
-  B200MD_TASK_LOOP(0, (tile_task<MODE, ENERGY, PBC>(S, P, chunk, passes, warp, lane, E)))
-  B200MD_TASK_LOOP(1, (tile_diag_task<MODE, ENERGY, PBC>(S, P, chunk & 0xff, (chunk >> 8) & 0xff, passes, warp, lane, E)))
-  B200MD_TASK_LOOP(2, (dihedral_task<ENERGY, FIXED, PBC>(S, T, P, item, (int)passes, E)))
-  B200MD_TASK_LOOP(3, (torsion_task<ENERGY, FIXED, PBC>(S, T, item, E)))
-  B200MD_TASK_LOOP(4, (angle_task<ENERGY, FIXED, PBC>(S, T, item, E)))
-  B200MD_TASK_LOOP(5, (bond_task<ENERGY, FIXED, PBC>(S, T, P, item, E)))
-  B200MD_TASK_LOOP(6, (p14_task<ENERGY, FIXED, PBC>(S, T, P, item, E)))
+  B200MD_TASK_LOOP(0, (tile_task<MODE, PBC>(S, P, chunk, passes, warp, lane)))
+  B200MD_TASK_LOOP(1, (tile_diag_task<MODE, PBC>(S, P, chunk & 0xff, (chunk >> 8) & 0xff, passes, warp, lane)))
+  B200MD_TASK_LOOP(2, (dihedral_task<FIXED, PBC>(S, T, P, item, (int)passes)))
+  B200MD_TASK_LOOP(3, (torsion_task<FIXED, PBC>(S, T, item)))
+  B200MD_TASK_LOOP(4, (angle_task<FIXED, PBC>(S, T, item)))
+  B200MD_TASK_LOOP(5, (bond_task<FIXED, PBC>(S, T, P, item)))
+  B200MD_TASK_LOOP(6, (p14_task<FIXED, PBC>(S, T, P, item)))
 #undef B200MD_TASK_LOOP
 }
 

@@ -1,12 +1,16 @@
 // b200md_kernels.cuh -- device code of the B200-native TorchMD force-field + integrator path.
 //
 // Mapping: one CTA of 128 threads (4 warps) per replica.  Positions (+ charge) live in
-// shared memory as float4[128]; the non-bonded half matrix is cut into "j-chunks" of 8 atoms; a warp
-// that owns a chunk sweeps the 32-lane i-blocks below it, every lane keeping its own i-atom force in
-// registers and 8 x 3 j-force partials that are butterfly-reduced with warp shuffles once per chunk.
-// Bonded terms are type-uniform chunks of 32 items whose force vectors go to private shared-memory
-// slots and are gathered per atom in a fixed order, so every reduction is deterministic and there is
-// not a single atomic on the force path.
+// shared memory as float4[128] and structure-of-arrays; the off-diagonal part of the non-bonded half
+// matrix is cut into "j-chunks" of 8 atoms: a warp that owns a chunk sweeps the 32-lane i-blocks below
+// it in packed FP32 (two j atoms per FFMA2), the i-side force of a pass goes to the warp's shared-memory
+// partial row, the 8 x 3 j-force partials are butterfly-reduced with warp shuffles once per chunk; the
+// diagonal 32 x 32 blocks are evaluated full shell.  Bonded terms run two items per lane in packed FP32;
+// their force vectors go to private atom-major slots summed in a fixed order (single-shot
+// Forces.compute) or to 2^-17 fixed-point shared-memory integer atomics (fused integrator): every
+// reduction is associative or fixed-order, hence bit-reproducible.  Energies are NOT part of the force
+// tasks: a separate FP64 pass (energy_pass, b200md_forces.cuh) evaluates every term in double from the
+// fp32 positions whenever energies are wanted (Forces.compute, report steps of the integrator).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -64,10 +68,18 @@ struct DevTopo {
   const uint32_t* gen_idx;   const uint2* gen_terms;  const float4* gen_term_prm;  const uint2* gen_slot;
   int nslots;
   const uint16_t* gather_start;  // [129]: slots of atom a are [gather_start[a], gather_start[a+1])
-  const uint32_t* tasks;    // [kWarps][kMaxTasks] schedule of the fused integrator (force-only cost model)
-  const uint32_t* tasks_e;  // [kWarps][kMaxTasks] schedule of the single-shot kernel (cost model with energies)
-  uint2 kend8_e[kWarps];  // the same for tasks_e
-  uint2 kend8[kWarps];    // per warp: end index of the k-th run of its kind-sorted task list, one byte per kind
+  const uint32_t* tasks;    // [kWarps][kMaxTasks] static schedule of the force tasks (issue-slot cost model)
+  uint2 kend8[kWarps];      // per warp: end index of the k-th run of its kind-sorted task list, one byte per kind
+  // FP64 energy pass (energy_pass): plain item lists in topology order, one item per thread
+  int ne_pair, ne_14, ne_bond, ne_angle, ne_dih, ne_imp;
+  const uint32_t* e_pair;   // [ne_pair] i | j << 8 | (type_i * ntypes + type_j) << 16: Forces.ava_idx, row-major
+  const double2* e_ab;      // [ntypes^2] (A, B) of par.A / par.B (forces.py:379-383)
+  const uint32_t* e14_idx;  // [ne_14] i | j << 8
+  const double* e14_prm;    // [3 ne_14] A / scnb, B / scnb, K qi qj / scee (forces.py:197-226)
+  const uint32_t* eb_idx;   const float2* eb_prm;   // bonds: i | j << 8; (k, r0)
+  const uint32_t* ea_idx;   const float2* ea_prm;   // angles: 3 x u8; (k, theta0)
+  const uint32_t* et_idx;   const int* et_start;    // torsions, dihedrals [0, ne_dih) then impropers: 4 x u8; terms [start[d], start[d + 1])
+  const float4* et_term;    const double2* et_cs;   // (k, phi0, per, kind: 0 AMBER, 1 harmonic, 2 AMBER with integer per); (cos phi0, sin phi0)
   int smem_bytes, smem_bytes_fixed;
   // proper-dihedral angle output (Energy.calc_phi of the ML callers) and its backward
   int nphi;                      // = par.dihedrals rows
@@ -94,6 +106,8 @@ struct ForceParams {
   int smd_on, smd_a1, smd_a2;
   float smd_fk, smd_c0, smd_rate;
   const float* smd_centers;
+  // the same constants in double for the FP64 energy pass (computed on the host from the float options)
+  double rc_d, rs_d, inv_sw_d, krf_d, crf_d;
 };
 
 struct StepParams {
@@ -101,6 +115,13 @@ struct StepParams {
   unsigned long long seed, step0;
   long long replica0;
   int nsteps, energy_every, snapshot_every;
+  // time slicing (b200md.cu, integrate_kernel): a work unit is `slice_len` consecutive steps of one replica; units are
+  // handed out slice-major from a global ticket counter, a replica's state parks in the caller's pos / vel / forces
+  // arrays between its slices
+  int slice_len, nslices;
+  unsigned long long* ticket;   // [1], zeroed before the launch
+  unsigned int* slice_done;     // [R] slices of replica r that are complete, zeroed before the launch
+  double* smd_work;             // [R] work of the moving restraint carried from slice to slice (SMD only)
 };
 
 // ---- shared-memory carve-up -----------------------------------------------------------------
@@ -124,6 +145,9 @@ struct Smem {
   float* smd;         // [8]: force on atom2 (xyz), -, distance
   double* smd_energy; // [2]: restraint energy of this step, work accumulated since the first step of the launch
   float* box;         // [8]: -box diagonal (x, y, z), 0, 1 / box diagonal (0 where the entry is 0), 0
+  double* pd;         // [4][128] x, y, z, q in double for the energy pass: OVERLAYS vel + sx (free between the force
+                      // gather of a step and the staging of the next one)
+  unsigned long long* tick;  // [1] ticket of the unit this CTA works on (integrator)
 };
 
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
@@ -145,11 +169,13 @@ constexpr size_t kOffEred = kOffTasks + sizeof(uint32_t) * kWarps * kMaxTasks;
 constexpr size_t kOffSmd = kOffEred + sizeof(double) * kWarps * kNumReduced;
 constexpr size_t kOffSmdEnergy = kOffSmd + 32;
 constexpr size_t kOffBox = kOffSmdEnergy + 16;
-constexpr size_t kOffFbi = kOffBox + 32;
+constexpr size_t kOffTick = kOffBox + 32;
+constexpr size_t kOffFbi = kOffTick + 16;
 constexpr size_t kOffVel = kOffFbi + sizeof(int) * 3 * kMaxAtoms;
 constexpr size_t kOffSx = kOffVel + sizeof(float4) * kMaxAtoms;
 constexpr size_t kOffAb = kOffSx + sizeof(float) * 4 * kMaxAtoms;
-static_assert(kOffAb % 16 == 0 && kOffFi % 16 == 0 && kOffEred % 16 == 0, "shared-memory layout must stay 16-byte aligned");
+static_assert(kOffAb % 16 == 0 && kOffFi % 16 == 0 && kOffEred % 16 == 0 && kOffVel % 16 == 0, "shared-memory layout must stay 16-byte aligned");
+static_assert(kOffAb - kOffVel == sizeof(double) * 4 * kMaxAtoms, "the FP64 position overlay needs exactly the vel + sx area");
 
 __host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, int nslots, bool fixed) {
   const size_t tab = align16(sizeof(float) * (size_t)ntypes * kTabStride);
@@ -167,6 +193,8 @@ __host__ __device__ inline size_t smem_layout(Smem* s, char* base, int ntypes, i
     s->smd = (float*)(base + kOffSmd);
     s->smd_energy = (double*)(base + kOffSmdEnergy);
     s->box = (float*)(base + kOffBox);
+    s->tick = (unsigned long long*)(base + kOffTick);
+    s->pd = (double*)(base + kOffVel);
     s->fbi = (int*)(base + kOffFbi);
     s->vel = (float4*)(base + kOffVel);
     s->sx = (float*)(base + kOffSx);

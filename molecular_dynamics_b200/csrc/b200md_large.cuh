@@ -17,8 +17,10 @@
 //   large_finish_kernel  per-replica energies = fixed-order sum of the per-CTA FP64 partials;
 //   large_vv1 / large_vv2 / large_observe   the velocity-Verlet halves, the Langevin kick (same Philox stream as the
 //                        fused kernel: keyed by seed, global replica, atom, global step) and the observable record.
-// Pair arithmetic is the packed pair_eval2<MODE, ENERGY> of b200md_forces.cuh (two j atoms per FFMA2 issue slot, FP32
-// with FP64 energy accumulation).
+// Pair FORCES are the packed pair_eval2<MODE> of b200md_forces.cuh (two j atoms per FFMA2 issue slot, FP32).  Pair
+// ENERGIES (ENERGY instantiation) are evaluated in FP64 from the fp32 positions, half shell (tiles above the diagonal
+// and j > i inside the diagonal tile): the lj / electrostatics sums cancel too far for fp32 pair terms to meet the
+// 1e-6-per-term contract.
 #pragma once
 #include "b200md_forces.cuh"
 
@@ -37,6 +39,7 @@ struct LargeTopo {
   const float* mass;           // [32 nwords] (padding: 1)
   const float* tab12a;         // [ntypes^2] 12 A
   const float* tab6b;          // [ntypes^2]  6 B
+  const double2* tab64;        // [ntypes^2] (A, B) in double for the FP64 pair energies
   const uint32_t* mask;        // [32 nwords][nwords] bit j of word w: pair (i, 32 w + j) is NOT evaluated
   int nbonds, nangles, ndih, n14, nimp;
   const int2* bond_idx;   const float2* bond_prm;
@@ -295,7 +298,7 @@ __host__ __device__ inline int large_tab_stride(int ntypes) { return ntypes | 1;
 // issue slot per two pairs), like the on-chip tiles.
 template <int MODE, bool ENERGY, bool PBC>
 __device__ __forceinline__ void large_pairs_body(const LargeTopo& T, const ForceParams& P, const float* __restrict__ p,
-                                                 const uint32_t tbase, float* sj /* [4][32] */, int* stj,
+                                                 const uint32_t tbase, float* sj /* [4][32] */, int* stj, double* sjd /* [4][32] */,
                                                  const float3 nbox, const float3 ibox, int ib, int warp, int lane, float xi,
                                                  float yi, float zi, float kqi, const float* __restrict__ bb, float& fx,
                                                  float& fy, float& fz, double& eel, double& elj) {
@@ -334,10 +337,10 @@ __device__ __forceinline__ void large_pairs_body(const LargeTopo& T, const Force
     __syncwarp();
     sj[lane] = jx; sj[32 + lane] = jy; sj[64 + lane] = jz; sj[96 + lane] = jq;
     stj[lane] = jtype;
+    if (ENERGY && jt >= ib) { sjd[lane] = (double)jx; sjd[32 + lane] = (double)jy; sjd[64 + lane] = (double)jz; sjd[96 + lane] = (double)jq; }
     __syncwarp();
     if (jt + kLThreads / 32 < T.nwords) fetch(jt + kLThreads / 32);
     if (__all_sync(0xffffffffu, far || m == 0xffffffffu)) continue;
-    u64 pel = 0ull, plj = 0ull;
 #pragma unroll 4
     for (int jj = 0; jj < 32; jj += 2) {
       const u64 xj = *(const u64*)(sj + jj), yj = *(const u64*)(sj + 32 + jj), zj = *(const u64*)(sj + 64 + jj);
@@ -346,13 +349,42 @@ __device__ __forceinline__ void large_pairs_body(const LargeTopo& T, const Force
       const u64 a12 = pk(lds_f32<0>(tbase + tj.x), lds_f32<0>(tbase + tj.y)), nb6 = pk(lds_f32<4>(tbase + tj.x), lds_f32<4>(tbase + tj.y));
       u64 dx = sub2(xi2, xj), dy = sub2(yi2, yj), dz = sub2(zi2, zj);
       if (PBC) { dx = wrap2(dx, nbox.x, ibox.x); dy = wrap2(dy, nbox.y, ibox.y); dz = wrap2(dz, nbox.z, ibox.z); }
-      const u64 sc = pair_eval2<MODE, ENERGY>(dx, dy, dz, kqi, kq2, qj, a12, nb6, (m >> jj) & 1u, (m >> (jj + 1)) & 1u, P, C, pel, plj);
+      const u64 sc = pair_eval2<MODE>(dx, dy, dz, kqi, kq2, qj, a12, nb6, (m >> jj) & 1u, (m >> (jj + 1)) & 1u, P, C);
       ax = fma2(sc, dx, ax); ay = fma2(sc, dy, ay); az = fma2(sc, dz, az);
     }
-    if (ENERGY) {  // FP32 partial sums of one tile (2 x 16 pairs per lane), folded into FP64 once
-      float a, b;
-      upk(pel, a, b); eel += (double)a + (double)b;
-      upk(plj, a, b); elj += (double)(MODE == 0 ? __fmul_rn(__fadd_rn(a, b), 1.0f / 12.0f) : __fadd_rn(a, b));
+    if (ENERGY && jt >= ib) {  // FP64 energies of the unordered pairs this tile owns (forces.py:379-413, 451-489 in double)
+      const double xd = (double)xi, yd = (double)yi, zd = (double)zi;
+      const double kq = kLElec * (double)(__ldg(T.charge + 32 * ib + lane) * P.el_on);
+      const double rc2 = P.rc_d * P.rc_d, ta = (double)P.tab_a, tb = (double)P.tab_b;
+      const double2* trow = T.tab64 + (size_t)__ldg(T.atom_type + 32 * ib + lane) * T.ntypes;
+      const int jfirst = jt == ib ? lane + 1 : 0;  // diagonal tile: j > i
+      for (int jj = 0; jj < 32; ++jj) {
+        if (jj < jfirst || ((m >> jj) & 1u)) continue;
+        double dx = xd - sjd[jj], dy = yd - sjd[32 + jj], dz = zd - sjd[64 + jj];
+        if (PBC) {
+          const double bx = -(double)nbox.x, by = -(double)nbox.y, bz = -(double)nbox.z;
+          if (bx != 0.0) dx -= bx * rint(dx / bx);
+          if (by != 0.0) dy -= by * rint(dy / by);
+          if (bz != 0.0) dz -= bz * rint(dz / bz);
+        }
+        const double r2 = dx * dx + dy * dy + dz * dz;
+        if (MODE == 1 && !(r2 <= rc2)) continue;
+        const double rinv = rsqrt(r2), r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
+        const double2 ab = __ldg(trow + (stj[jj] >> 3));
+        const double qq = kq * sjd[96 + jj];
+        double lj = (ta * ab.x * r6 + tb * ab.y) * r6;
+        if (MODE == 1) {
+          const double r = r2 * rinv;
+          if (r > P.rs_d) {
+            const double t = (r - P.rs_d) * P.inv_sw_d;
+            lj *= 1.0 + t * t * t * (-10.0 + t * (15.0 - t * 6.0));
+          }
+          eel += qq * (rinv + P.krf_d * r2 - P.crf_d);
+        } else {
+          eel += qq * rinv;
+        }
+        elj += lj;
+      }
     }
   }
   fx = hsum2(ax); fy = hsum2(ay); fz = hsum2(az);
@@ -369,6 +401,7 @@ large_pairs_kernel(const LargeTopo T, const ForceParams P, const long long R, co
   const int tstride = large_tab_stride(T.ntypes);
   __shared__ __align__(16) float sj[kLThreads / 32][4 * 32];
   __shared__ __align__(16) int stj[kLThreads / 32][32];
+  __shared__ double sjd[ENERGY ? kLThreads / 32 : 1][ENERGY ? 4 * 32 : 1];
   __shared__ float sf[kLThreads / 32][3][32];
   __shared__ double sred[(kLThreads / 32) * 2];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -396,8 +429,9 @@ large_pairs_kernel(const LargeTopo T, const ForceParams P, const long long R, co
     float fx = 0.f, fy = 0.f, fz = 0.f;
     double e[2] = {0.0, 0.0};
     if (nonbonded) {
-      if (pbc) large_pairs_body<MODE, ENERGY, true>(T, P, p, tbase, sj[warp], stj[warp], nbox, ibox, ib, warp, lane, xi, yi, zi, kqi, nullptr, fx, fy, fz, e[0], e[1]);
-      else large_pairs_body<MODE, ENERGY, false>(T, P, p, tbase, sj[warp], stj[warp], nbox, ibox, ib, warp, lane, xi, yi, zi, kqi,
+      double* sd = sjd[ENERGY ? warp : 0];
+      if (pbc) large_pairs_body<MODE, ENERGY, true>(T, P, p, tbase, sj[warp], stj[warp], sd, nbox, ibox, ib, warp, lane, xi, yi, zi, kqi, nullptr, fx, fy, fz, e[0], e[1]);
+      else large_pairs_body<MODE, ENERGY, false>(T, P, p, tbase, sj[warp], stj[warp], sd, nbox, ibox, ib, warp, lane, xi, yi, zi, kqi,
                                                  bbox ? bbox + r * T.nwords * 8 : nullptr, fx, fy, fz, e[0], e[1]);
     }
     sf[warp][0][lane] = fx; sf[warp][1][lane] = fy; sf[warp][2][lane] = fz;
@@ -412,7 +446,6 @@ large_pairs_kernel(const LargeTopo T, const ForceParams P, const long long R, co
       }
     }
     if (ENERGY) {
-      e[0] *= 0.5; e[1] *= 0.5;  // full shell: every pair was met from both of its atoms with identical terms
       lreduce<2, kLThreads>(e, sred, tid);
       if (tid == 0) {
         double* o = partial + (r * npart + part0 + ib) * B200MD_NUM_ENERGIES;

@@ -49,8 +49,10 @@ def _forces_compute_op(pos: torch.Tensor, box: torch.Tensor, forces: torch.Tenso
     fo = _cabi.ForceOpts(terms, cutoff, int(rfa), eps, switch_dist)
     cen = smd_centers.data_ptr() if smd_centers.numel() else None
     so = _cabi.SmdOpts(int(smd_on), smd_a1, smd_a2, smd_fk, smd_c0, 0.0, cen)
-    _check(lib.b200md_forces_compute(C.c_void_p(handle), C.byref(fo), C.byref(so), pos.shape[0], _ptr(pos),
-                                     _ptr(box), _ptr(forces), _ptr(energies), _ptr(status), _stream_ptr(pos.device)))
+    ene = _ptr(energies) if energies.numel() else None  # empty: forces only (the library skips the FP64 energy pass)
+    with torch.cuda.device(pos.device):
+        _check(lib.b200md_forces_compute(C.c_void_p(handle), C.byref(fo), C.byref(so), pos.shape[0], _ptr(pos),
+                                         _ptr(box), _ptr(forces), ene, _ptr(status), _stream_ptr(pos.device)))
 
 
 @torch.library.custom_op("b200md::integrate", mutates_args=("pos", "vel", "forces", "observables", "snapshots", "status"))
@@ -66,9 +68,10 @@ def _integrate_op(pos: torch.Tensor, vel: torch.Tensor, forces: torch.Tensor, bo
     io = _cabi.IntegrateOpts(dt, gamma, temperature, seed, step0, replica0, nsteps, energy_every, snapshot_every,
                              int(rigid_bonds))
     snaps = _ptr(snapshots) if snapshots.numel() else None
-    _check(lib.b200md_integrate(C.c_void_p(handle), C.byref(fo), C.byref(so), C.byref(io), pos.shape[0], _ptr(pos),
-                                _ptr(vel), _ptr(forces), _ptr(box), _ptr(observables), snaps, _ptr(status),
-                                _stream_ptr(pos.device)))
+    with torch.cuda.device(pos.device):
+        _check(lib.b200md_integrate(C.c_void_p(handle), C.byref(fo), C.byref(so), C.byref(io), pos.shape[0], _ptr(pos),
+                                    _ptr(vel), _ptr(forces), _ptr(box), _ptr(observables), snaps, _ptr(status),
+                                    _stream_ptr(pos.device)))
 
 
 class SMDBias:
@@ -118,9 +121,12 @@ class Forces:
                 raise ValueError(f"Force term {et} is not implemented.")
         if "1-4" in self.energies and "dihedrals" not in self.energies:
             raise RuntimeError("You cannot enable 1-4 interactions without enabling dihedrals")
-        if sum(et in self.energies for et in ("lj", "repulsion", "repulsioncg")) > 1:
-            raise NotImplementedError("at most one of 'lj', 'repulsion', 'repulsioncg' per Forces object: the CUDA path "
-                                      "has one pair-table slot (forces.py:281-311 would evaluate them one after another)")
+        # forces.py:268-316 evaluates every enabled pair term of the lj family over the same pair list, one after the
+        # other.  The kernels have ONE pair-table slot per launch: the first family term rides with everything else,
+        # each further one gets its own launch (that term alone) whose forces are added and whose energy is reported
+        # in its own column behind the 8 standard ones.
+        family = [et for et in self.energies if et in ("lj", "repulsion", "repulsioncg")]
+        self._extra_pair_terms = family[1:]
         self.natoms = len(parameters.masses)
         self.require_distances = any(f in self.nonbonded for f in self.energies)
         self._pair_idx = (_cabi.make_pair_index(self.natoms, parameters.get_exclusions(exclusions))
@@ -136,10 +142,12 @@ class Forces:
             raise ValueError("rfa=True needs a cutoff (forces.py:467 divides by cutoff**3)")
         self._terms_mask = 0
         for et in self.energies:
-            self._terms_mask |= _cabi.TERM_BITS[et]
+            if et not in self._extra_pair_terms:
+                self._terms_mask |= _cabi.TERM_BITS[et]
         self._packed = _cabi.PackedTopology(parameters, self._pair_idx)
         self._handles = {}  # device index -> native handle
-        self.last_energies = None  # (R, 8) float64 tensor of the last compute, FP64-accumulated
+        self.last_energies = None  # (R, 8) float64 tensor of the last compute (FP64 energy pass)
+        self._last_ext_force = None  # detached force of a generic external object in the last compute_batch
 
     # -- native handle management ----------------------------------------------------------------
     def _handle(self, device):
@@ -176,12 +184,20 @@ class Forces:
         return (self._terms_mask, float(self.cutoff) if self.cutoff is not None else 0.0, bool(self.rfa),
                 float(self.solventDielectric), float(self.switch_dist) if self.switch_dist is not None else 0.0)
 
-    def _smd_args(self, R, device):
+    def column(self, term):
+        """Column of the energy tensor ``compute_batch`` returns that holds ``term``: the 8 standard slots
+        (``_cabi.ENERGY_SLOTS``; the first enabled term of the lj family uses the "lj" column), then one column per
+        further lj-family term."""
+        if term in self._extra_pair_terms:
+            return _cabi.NUM_ENERGIES + self._extra_pair_terms.index(term)
+        return _cabi.energy_slot(term)
+
+    def _smd_args(self, R, device, center=None):
         ext = self.external
         empty = torch.empty(0, dtype=torch.float32, device=device)
         if not isinstance(ext, SMDBias):
             return (False, 0, 0, 0.0, 0.0), empty
-        c = ext.center
+        c = ext.center if center is None else center
         if isinstance(c, torch.Tensor) and c.numel() > 1:
             cen = c.to(device=device, dtype=torch.float32).contiguous()
             if cen.numel() != R:
@@ -195,16 +211,18 @@ class Forces:
             raise RuntimeError(f"{what} must be a CUDA tensor: the B200 path has no CPU fallback")
 
     # -- low-level launch ------------------------------------------------------------------------
-    def _launch(self, pos, box, forces, terms_mask=None, with_smd=True):
-        """One b200md::forces_compute launch; ``forces`` must be a contiguous float32 CUDA tensor."""
+    def _launch(self, pos, box, forces, terms_mask=None, with_smd=True, energies=True, smd_center=None):
+        """One b200md::forces_compute launch; ``forces`` must be a contiguous float32 CUDA tensor.  ``energies=False``
+        skips the FP64 energy pass (returns an empty tensor); ``smd_center`` overrides ``external.center`` (the
+        autograd backward passes the centre its forward used)."""
         R = pos.shape[0]
         dev = pos.device
-        ene = torch.empty((R, _cabi.NUM_ENERGIES), dtype=torch.float64, device=dev)
+        ene = torch.empty((R if energies else 0, _cabi.NUM_ENERGIES), dtype=torch.float64, device=dev)
         status = torch.empty(R, dtype=torch.int32, device=dev)
         opts = list(self._opts())
         if terms_mask is not None:
             opts[0] = terms_mask
-        (smd_on, a1, a2, fk, c0), cen = self._smd_args(R, dev)
+        (smd_on, a1, a2, fk, c0), cen = self._smd_args(R, dev, smd_center)
         if not with_smd:
             smd_on, cen = False, torch.empty(0, dtype=torch.float32, device=dev)
         torch.ops.b200md.forces_compute(pos, box, forces, ene, status, self._handle(dev), *opts, smd_on, a1, a2, fk,
@@ -212,32 +230,46 @@ class Forces:
         return ene, status
 
     # -- batched fast path -----------------------------------------------------------------------
-    def compute_batch(self, pos, box, forces):
-        """Evaluate all replicas; fills ``forces`` in place and returns the (R, 8) float64 energy tensor
-        (columns in ``_cabi.ENERGY_SLOTS`` order).  No Python work per replica."""
+    def compute_batch(self, pos, box, forces, energies=True):
+        """Evaluate all replicas; fills ``forces`` in place and returns the (R, 8) float64 energy tensor (columns in
+        ``_cabi.ENERGY_SLOTS`` order; see ``column`` for objects with several lj-family terms).  Energies are evaluated
+        in FP64 from the fp32 positions.  ``energies=False``: forces only, returns None.  No Python work per replica.
+        ``pos`` / ``forces`` may be float64 tensors (``precision=torch.double`` systems, systems.py:32-36): the kernels
+        compute forces in fp32, so they are converted on the way in and out."""
         self._require_cuda(pos, "pos")
         self._require_cuda(forces, "forces")
-        if pos.dtype != torch.float32:
-            raise TypeError("the CUDA path computes in float32: pass precision=torch.float tensors")
+        if pos.dtype not in (torch.float32, torch.float64):
+            raise TypeError("positions must be float32 or float64 tensors")
         R, N, _ = pos.shape
         if N != self.natoms:
             raise ValueError(f"pos has {N} atoms, parameters have {self.natoms}")
         dev = pos.device
-        p = pos.detach().contiguous()  # System.set_positions hands over a permuted view (Q17)
+        p = pos.detach().to(torch.float32).contiguous()  # System.set_positions hands over a permuted view (Q17)
         direct = forces.is_contiguous() and forces.dtype == torch.float32 and forces.device == dev
         f = forces if direct else torch.empty((R, N, 3), dtype=torch.float32, device=dev)
         b = box.detach().to(device=dev, dtype=torch.float32).contiguous()
-        ene, status = self._launch(p, b, f)
+        ene, status = self._launch(p, b, f, energies=energies)
+        for term in self._extra_pair_terms:  # forces.py:268-316: the further pair terms of the lj family, one launch each
+            f2 = torch.empty_like(f)
+            e2, _ = self._launch(p, b, f2, terms_mask=_cabi.TERM_BITS[term], with_smd=False, energies=energies)
+            f += f2
+            if energies:
+                ene = torch.cat([ene, e2[:, _cabi.energy_slot(term):_cabi.energy_slot(term) + 1]], dim=1)
         if self.check_nan:
             flags = int(status.max().item()) if R else 0
             if flags & _cabi.FLAG_NAN_POS:
                 raise RuntimeError("Found NaN coordinates.")
         if not direct:
             forces.copy_(f)
+        self._last_ext_force = None
         if self.external is not None and not isinstance(self.external, SMDBias):  # forces.py:318-323
             ext_ene, ext_force = self.external.calculate(pos.detach(), box)
-            ene[:, 7] += ext_ene.detach().to(ene.dtype).reshape(-1)
-            forces += ext_force.detach()
+            if energies:
+                ene[:, 7] += ext_ene.detach().to(ene.dtype).reshape(-1)
+            forces += ext_force.detach().to(forces.dtype)
+            self._last_ext_force = ext_force.detach()
+        if not energies:
+            return None
         self.last_energies = ene
         return ene
 
@@ -249,8 +281,8 @@ class Forces:
         from .autograd import dihedral_angles_with_grad
 
         self._require_cuda(pos, "pos")
-        if pos.dtype != torch.float32:
-            raise TypeError("the CUDA path computes in float32: pass precision=torch.float tensors")
+        if pos.dtype not in (torch.float32, torch.float64):
+            raise TypeError("positions must be float32 or float64 tensors")
         if pos.shape[1] != self.natoms:
             raise ValueError(f"pos has {pos.shape[1]} atoms, parameters have {self.natoms}")
         return dihedral_angles_with_grad(self, pos, box)
@@ -283,7 +315,7 @@ class Forces:
         else:
             ene = self.compute_batch(pos, box, forces).to(pos.dtype)
         keys = list(self.energies) + ["external"]
-        cols = [_cabi.energy_slot(k) for k in keys]
+        cols = [self.column(k) for k in keys]
         if not explicit_forces:  # Q13: return the summed tensor
             return ene[:, cols].sum().reshape(1)
         pot = []

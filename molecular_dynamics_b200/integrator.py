@@ -3,8 +3,11 @@ V_Calculations/Test-1/tutorial.ipynb:212,313,374): ``Integrator(systems, forces,
 gamma, T).step(niter) -> (Ekin, pot, T)`` and ``maxwell_boltzmann(masses, T, replicas)``.
 
 ``step(niter)`` is ONE kernel launch: velocity Verlet (+ Langevin kick) fused with the force evaluation,
-the replica's positions / velocities / forces staying on chip for all ``niter`` steps
-(b200md_integrate, include/b200md.h).  Semantics restated from upstream:
+the replica's positions / velocities / forces staying on chip for whole slices of the ``niter`` steps
+(b200md_integrate, include/b200md.h).  A ``Forces`` object the fused kernel cannot express (a generic ``external``
+object with its own ``calculate``, several pair terms of the lj family at once) takes the same loop as separate
+launches per step, ``Forces.compute_batch`` in the middle, on the same stream.  Semantics restated from upstream
+(SURVEY.md 3.2):
 
     for _ in range(niter):
         pos += vel*dt + 0.5*(F/m)*dt^2 ; vel += 0.5*dt*F/m          # _first_VV
@@ -146,18 +149,22 @@ class Integrator:
         R, N, _ = pos.shape
         dev = pos.device
         box = s.box.to(device=dev, dtype=torch.float32).contiguous()
+        ext = f.external
+        if (ext is not None and not isinstance(ext, SMDBias)) or f._extra_pair_terms:
+            return self._step_unfused(int(niter))
         energy_every = self.energy_every if 0 < self.energy_every <= niter else 0  # shorter call: report at its end
-        nrep = niter // energy_every if energy_every > 0 else 1
+        nrep = -(-niter // energy_every) if energy_every > 0 else 1  # + a record after the last step of the call
         nsnap = niter // self.snapshot_every if self.snapshot_every > 0 else 0
         obs = torch.zeros((nrep, R, _cabi.NUM_OBSERVABLES), dtype=torch.float64, device=dev)
         snaps = torch.empty((nsnap, R, N, 3), dtype=torch.float32, device=dev)
         status = torch.empty(R, dtype=torch.int32, device=dev)
-        ext = f.external
-        if ext is not None and not isinstance(ext, SMDBias):
-            raise NotImplementedError("the fused integrator supports only the SMDBias external term")
         if isinstance(ext, SMDBias):  # centre of the restraint after global step g: center + rate * g
             c = ext.center
             if isinstance(c, torch.Tensor):
+                if c.numel() > 1:
+                    raise ValueError("the fused integrator moves ONE restraint centre (center + rate_per_step * step) for "
+                                     "all replicas: SMDBias.center is a per-replica tensor (left by "
+                                     "Energy.calc_energy_batch?); set a scalar centre first")
                 c = float(c.reshape(-1)[0])
             smd = (True, ext.atom1, ext.atom2, ext.fk, float(c), ext.rate_per_step)
         else:
@@ -186,12 +193,7 @@ class Integrator:
         if smd[0]:  # the kernel counts work from the first step of the launch: carry it across calls
             if self.smd_work is not None and self.smd_work.shape[0] == R:
                 obs[:, :, _cabi.OBS_SMD_WORK] += self.smd_work.to(dev)
-            self.smd_work = obs[-1, :, _cabi.OBS_SMD_WORK].clone()
-            if energy_every > 0 and niter % energy_every:
-                import warnings
-                warnings.warn("niter is not a multiple of energy_every: the SMD work of the trailing steps was not "
-                              "recorded, Integrator.smd_work is undefined from here on")
-                self.smd_work.fill_(float("nan"))
+            self.smd_work = obs[-1, :, _cabi.OBS_SMD_WORK].clone()  # the last record is the end of the call
         self.observables, self.snapshots = obs, snaps
         last = obs[-1]
         Ekin = last[:, _cabi.OBS_EKIN].cpu().numpy()
@@ -202,3 +204,41 @@ class Integrator:
         cols = [_cabi.energy_slot(k) for k in keys]
         pot = last[:, cols].sum(dim=1).to(pos.dtype)
         return Ekin, _ReplicaEnergies(pot), T
+
+    def _step_unfused(self, niter):
+        """Upstream's loop as launches per step, for what the fused kernel cannot hold: a generic ``external`` object
+        (forces.py:318-323: anything with ``calculate(pos, box) -> (energy (R,), force (R, N, 3))``) and several pair
+        terms of the lj family in one ``Forces`` object (forces.py:268-316).  Everything stays on the GPU and on the
+        current stream: two elementwise updates and one ``Forces.compute_batch`` (kernel launches + the hook's torch
+        ops) per step; the Langevin noise comes from a torch generator keyed by (seed, step)."""
+        s, f = self.systems, self.forces
+        if self.rigid_bonds:
+            raise NotImplementedError("rigid_bonds lives in the fused kernel: not available with a generic external "
+                                      "object or several lj-family terms")
+        pos, vel, frc = s.pos, s.vel, s.forces
+        R, N, _ = pos.shape
+        dev = pos.device
+        m = f.par.masses.to(device=dev, dtype=torch.float32).reshape(1, N, 1)
+        dt = float(self.dt)
+        ene = None
+        for _ in range(niter):
+            vel += (0.5 * dt) * frc / m  # _first_VV: pos += vel dt + 0.5 a dt^2 ; vel += 0.5 dt a
+            pos += dt * vel
+            ene = f.compute_batch(pos, s.box, frc)
+            if self.T:
+                gen = torch.Generator(device=dev).manual_seed((self.seed * 1000003 + self.step_count) & 0x7FFFFFFFFFFFFFFF)
+                noise = torch.randn(pos.shape, generator=gen, device=dev, dtype=torch.float32)
+                vel += -self.gamma * dt * vel + self.vcoeff.to(dev).reshape(1, N, 1) * noise
+            vel += (0.5 * dt) * frc / m  # _second_VV
+            self.step_count += 1
+        obs = torch.zeros((1, R, _cabi.NUM_OBSERVABLES), dtype=torch.float64, device=dev)
+        obs[0, :, :_cabi.NUM_ENERGIES] = ene[:, :_cabi.NUM_ENERGIES]
+        for k, _term in enumerate(f._extra_pair_terms):  # further lj-family terms: folded into the "lj" column of the record
+            obs[0, :, 1] += ene[:, _cabi.NUM_ENERGIES + k]
+        ekin = kinetic_energy(m.to(torch.float64), vel.to(torch.float64)).reshape(-1)
+        obs[0, :, _cabi.OBS_EKIN] = ekin
+        self.observables = obs
+        self.snapshots = torch.empty((0, R, N, 3), dtype=torch.float32, device=dev)
+        Ekin = ekin.cpu().numpy()
+        cols = [f.column(k) for k in list(f.energies) + ["external"]]
+        return Ekin, _ReplicaEnergies(ene[:, cols].sum(dim=1).to(pos.dtype)), kinetic_to_temp(Ekin, N)

@@ -84,7 +84,9 @@ class TrajectoryWriter:
 
 def save_checkpoint(path, system, integrator=None, extra=None):
     """pos / vel / box / forces (+ the integrator's counter-based RNG state: seed, global step, first global replica).
-    With the fused integrator's deterministic reductions a run resumed from a checkpoint continues bit-identically."""
+    With the fused integrator's deterministic reductions a run resumed from a checkpoint continues bit-identically.
+    The file holds tensors, numbers and plain containers only (``extra`` included), so that it loads with
+    ``weights_only=True``: a checkpoint from somewhere else cannot execute code when it is read."""
     state = {"pos": system.pos.detach().cpu(), "vel": system.vel.detach().cpu(), "box": system.box.detach().cpu(),
              "forces": system.forces.detach().cpu(), "extra": extra}
     if integrator is not None:
@@ -95,7 +97,7 @@ def save_checkpoint(path, system, integrator=None, extra=None):
 
 
 def load_checkpoint(path, system, integrator=None):
-    state = torch.load(path, map_location="cpu", weights_only=False)
+    state = torch.load(path, map_location="cpu", weights_only=True)  # tensors / numbers / containers: no unpickling of code
     for name in ("pos", "vel", "box", "forces"):
         t = getattr(system, name)
         src = state[name]

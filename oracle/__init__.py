@@ -137,7 +137,7 @@ def integrate(packed, pos, vel, forces_in, nsteps, dt, gamma=0.0, temperature=0.
     f = np.array(forces_in, dtype=np.float64, order="C")
     R, N, _ = p.shape
     box = None if box is None else np.ascontiguousarray(box, dtype=np.float32).reshape(R, 9)
-    nrep = nsteps // energy_every if energy_every > 0 else 1
+    nrep = -(-nsteps // energy_every) if energy_every > 0 else 1
     nsnap = nsteps // snapshot_every if snapshot_every > 0 else 0
     obs = np.zeros((nrep, R, _cabi.NUM_OBSERVABLES), dtype=np.float64)
     snaps = np.zeros((nsnap, R, N, 3), dtype=np.float64) if nsnap else None

@@ -457,7 +457,7 @@ int oracle_integrate(const b200md_topology_desc* T, const b200md_force_opts* O, 
   const int N = T->natoms;
   const double dt = I->dt, gamma = I->gamma;
   const int langevin = I->temperature > 0.0f;
-  const int nrep = I->energy_every > 0 ? I->nsteps / I->energy_every : 1;
+  const int nrep = I->energy_every > 0 ? (I->nsteps + I->energy_every - 1) / I->energy_every : 1;
   const int nsnap = I->snapshot_every > 0 ? I->nsteps / I->snapshot_every : 0;
   (void)nrep;
   (void)nsnap;
@@ -504,9 +504,9 @@ int oracle_integrate(const b200md_topology_desc* T, const b200md_force_opts* O, 
       for (int a = 0; a < N; ++a)
         for (int c = 0; c < 3; ++c) ekin += 0.5 * (double)T->mass[a] * v[3 * a + c] * v[3 * a + c];
       const int last = (s == I->nsteps - 1);
-      int report = I->energy_every > 0 ? ((s + 1) % I->energy_every == 0) : last;
+      int report = (I->energy_every > 0 && (s + 1) % I->energy_every == 0) || last;
       if (report && observables) {
-        int slot = I->energy_every > 0 ? (s + 1) / I->energy_every - 1 : 0;
+        int slot = I->energy_every > 0 ? s / I->energy_every : 0;
         double* o = observables + ((int64_t)slot * R + r) * B200MD_NUM_OBSERVABLES;
         for (int k = 0; k < B200MD_NUM_ENERGIES; ++k) o[k] = e[k];
         o[B200MD_OBS_EKIN] = ekin;

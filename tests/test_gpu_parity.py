@@ -4,10 +4,8 @@ golden fixtures produced by the reference's own forces.py.
 Tolerances (BASELINE.json north_star, calibrated in SURVEY.md 8c):
   * integer artefacts (pair list, exclusion mask)             bit-exact
   * forces   max|dF| / max|F| per replica                     <= 1e-5
-  * energies per term vs fp64 reference                       <= 1e-6 relative (bonds, angles, dihedrals);
-    non-bonded sums (lj, electrostatics) <= 1e-6 of sum|pair terms| (they cancel up to ~1000:1, so 1e-6 of
-    the total would need fp64 pair arithmetic; the reference's own fp32 run is at 1e-6 / 3.5e-6 of the
-    totals); harmonic impropers <= 5e-6.  Achieved values: profiles/*parity_report.md.
+  * energies per term and total vs fp64 reference              <= 1e-6 relative, every slot (the kernels evaluate
+    energies in FP64 from the fp32 positions; forces stay fp32).  Achieved values: profiles/*parity_report.md.
 """
 import os
 
@@ -47,59 +45,24 @@ def run_gpu(g, pos, smd=None, centers=None, **kw):
     return s.forces.cpu().numpy().astype(np.float64), ene.cpu().numpy(), F
 
 
-def pair_scales(g, pos):
-    """Per replica: sum over evaluated pairs of |K qi qj / r| and of |A r^-12| + |B r^-6| -- the magnitude the
-    individual fp32 pair terms carry before they cancel in the sum."""
-    par = g.par
-    q = par.charges.numpy().astype(np.float64)
-    ty = par.mapped_atom_types.numpy()
-    A, B = par.A.numpy().astype(np.float64), par.B.numpy().astype(np.float64)
-    p = pos.astype(np.float64)
-    idx = g.ava_idx
-    d = np.linalg.norm(p[:, idx[:, 0]] - p[:, idx[:, 1]], axis=-1)
-    coul = (332.06371307417066 * np.abs(q[idx[:, 0]] * q[idx[:, 1]]) / d).sum(1)
-    lj = (A[ty[idx[:, 0]], ty[idx[:, 1]]] / d ** 12 + np.abs(B[ty[idx[:, 0]], ty[idx[:, 1]]]) / d ** 6).sum(1)
-    if par.idx14 is not None:
-        i14 = par.idx14.numpy()
-        p14 = par.nonbonded_14_params.numpy().astype(np.float64)
-        d = np.linalg.norm(p[:, i14[:, 0]] - p[:, i14[:, 1]], axis=-1)
-        coul = coul + (332.06371307417066 * np.abs(q[i14[:, 0]] * q[i14[:, 1]]) / p14[:, 3] / d).sum(1)
-        lj = lj + ((np.abs(p14[:, 0]) / d ** 12 + np.abs(p14[:, 1]) / d ** 6) / p14[:, 2]).sum(1)
-    return coul, lj
-
-
-def torsion_scale(par, which):
-    """sum of 2|k| over the AMBER terms of the dihedral / improper slices: k (1 + cos(n phi - phi0)) cancels to ~0
-    near its minimum, so the fp32 error of a term is relative to k, not to the term."""
-    slices = par.dihedral_params if which == "dihedrals" else par.improper_params
-    if slices is None:
-        return 0.0
-    return float(sum(2.0 * sl["params"][:, 0].abs().sum() for sl in slices if bool((sl["params"][:, 2] > 0).all())))
-
-
-# relative tolerance per energy slot.  Non-bonded sums are judged against the magnitude of their pair terms
-# (they cancel up to ~1000:1; the reference's own fp32 run deviates 1e-6 (lj) / 3.5e-6 (electrostatics) from
-# its fp64 run, SURVEY.md 7.3); harmonic impropers k*(phi-phi0)^2 amplify the fp32 angle error 2/(phi-phi0).
-SLOT_TOL = {"electrostatics": 1e-6, "lj": 1e-6, "bonds": 1e-6, "angles": 1e-6, "dihedrals": 1e-6, "1-4": 0.0,
-            "impropers": 5e-6, "external": 2e-6}
+def check_energies(e, e_ref, what=""):
+    """north_star: every per-term energy and the total within 1e-6 RELATIVE of the fp64 reference (the reference's own
+    arithmetic in torch.double on the same fp32-rounded positions and parameters).  The kernels evaluate every term in
+    FP64 (energy_pass), so the literal contract holds -- no re-denomination by the magnitude of the cancelling pair
+    terms.  atol only covers slots that are exactly zero in the reference ("1-4", disabled terms)."""
+    e, e_ref = np.asarray(e), np.asarray(e_ref)
+    for k, name in enumerate(_cabi.ENERGY_SLOTS):
+        err = np.abs(e[..., k] - e_ref[..., k])
+        assert (err <= E_TOL * np.abs(e_ref[..., k]) + 1e-9).all(), \
+            f"{name}: {(err / (np.abs(e_ref[..., k]) + 1e-30)).max():.3e} {what}"
+    tot, tot_ref = e.sum(-1), e_ref.sum(-1)
+    assert (np.abs(tot - tot_ref) <= E_TOL * np.abs(tot_ref) + 1e-9).all(), f"total {what}"
 
 
 def check(g, pos, f, e, f_ref, e_ref, mode):
     ferr = np.abs(f - f_ref).reshape(len(f), -1).max(1) / np.abs(f_ref).reshape(len(f), -1).max(1)
     assert ferr.max() <= F_TOL, f"force error {ferr.max():.3e}"
-    coul, lj = pair_scales(g, np.asarray(pos))
-    for k, name in enumerate(_cabi.ENERGY_SLOTS):
-        err = np.abs(e[:, k] - e_ref[:, k])
-        scale = np.abs(e_ref[:, k])
-        if name == "electrostatics" and np.abs(e_ref[:, k]).max() > 0:
-            scale = np.maximum(scale, coul)
-        if name == "lj" and np.abs(e_ref[:, k]).max() > 0:
-            scale = np.maximum(scale, lj)
-        if name in ("dihedrals", "impropers") and np.abs(e_ref[:, k]).max() > 0:
-            scale = np.maximum(scale, torsion_scale(g.par, name))
-        assert (err <= SLOT_TOL[name] * scale + 1e-9).all(), f"{name}: {(err / (scale + 1e-30)).max():.3e} ({mode})"
-    tot, tot_ref = e.sum(1), e_ref.sum(1)
-    assert (np.abs(tot - tot_ref) <= 1e-6 * (np.abs(e_ref).sum(1) + coul + lj)).all()
+    check_energies(e, e_ref, mode)
     return ferr.max()
 
 
@@ -388,45 +351,44 @@ def test_snapshots_and_reports_layout():
 
 
 def test_nve_energy_drift_100k_steps_matches_fp64_oracle():
-    """BASELINE.json configs[2] check: NVE drift of E_pot + E_kin over 100 000 fused steps (dt = 1 fs, bench conformers),
-    and the same statistic against the FP64 oracle over the horizon the oracle finishes in seconds.  Trajectories
-    diverge chaotically, so the comparison is statistical (tools/nve_drift.py, profiles/r01_nve_drift.jsonl:
-    GPU 0.20 +- 0.22 kcal/mol per 100 ps at E_tot = 552, RMS fluctuation 0.49; oracle and GPU agree over 10 ps)."""
+    """BASELINE.json configs[2] at its own size: 8 192 replicas x 100 000 fused NVE steps (dt = 1 fs, bench conformers)
+    on the GPU, and the FP64 oracle over the SAME 100 000 steps on the first 16 of those replicas.  Trajectories diverge
+    chaotically after ~1e3 steps, so "matches" is a statement about ensemble statistics: the drift of E_pot + E_kin per
+    replica (least-squares slope x run length) and the RMS fluctuation about the fit.  Tolerance = three standard
+    errors of the difference of the two ensemble means (sigma from the ensembles themselves), not a fixed number."""
     import bench
     import sys as _sys
     _sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
-    from nve_drift import drift_stats
+    from nve_drift import compare_ensembles, drift_stats
 
     g = load_golden("ala10")
-    R, RO, NO = 16, 8, 5000
+    R, RO, NSTEPS, EVERY = 8192, 16, 100000, 200
     pos, vel = bench.synth_inputs(bench.load_ala10(), R)
     par, s = make_system(g, pos, vel)
     F = Forces(par)
     F.compute_batch(s.pos, s.box, s.forces)
-    f0 = s.forces.cpu().numpy().astype(np.float64)
+    f0 = s.forces[:RO].cpu().numpy().astype(np.float64)
     integ = Integrator(s, F, timestep=1.0, device=DEV)
-    integ.energy_every = 100
+    integ.energy_every = EVERY
     chunks = []
     for _ in range(5):
-        integ.step(niter=20000)
-        chunks.append(integ.observables.cpu().numpy())
-    obs = np.concatenate(chunks, 0)
-    etot = obs[:, :, :8].sum(-1) + obs[:, :, _cabi.OBS_EKIN]
-    assert np.isfinite(etot).all()
-    drift, rms = drift_stats(etot)
-    assert np.abs(drift).max() < 1.5 and abs(drift.mean()) < 0.6, drift  # kcal/mol per 100 ps at E_tot ~ 550
-    assert rms.max() < 1.0, rms
-    out = oracle.integrate(g.packed, pos[:RO], vel[:RO], f0[:RO], nsteps=NO, dt=np.float32(integ.dt), energy_every=100)
+        integ.step(niter=NSTEPS // 5)
+        o = integ.observables
+        chunks.append((o[:, :, :8].sum(-1) + o[:, :, _cabi.OBS_EKIN]).cpu().numpy())
+    etot = np.concatenate(chunks, 0)
+    assert etot.shape == (NSTEPS // EVERY, R) and np.isfinite(etot).all()
+    out = oracle.integrate(g.packed, pos[:RO], vel[:RO], f0, nsteps=NSTEPS, dt=np.float32(integ.dt), energy_every=EVERY)
     eo = out["observables"][:, :, :8].sum(-1) + out["observables"][:, :, _cabi.OBS_EKIN]
-    do, ro = drift_stats(eo)
-    dg, rg = drift_stats(etot[:NO // 100, :RO])
-    assert np.abs(etot[0, :RO] - eo[0]).max() < 0.05          # still the same trajectory after 100 steps
-    assert abs(dg.mean() - do.mean()) < 0.25, (dg, do)        # same transient drift over the common horizon
-    assert abs(rg.mean() / ro.mean() - 1.0) < 0.3, (rg, ro)   # same fluctuation amplitude
+    assert np.abs(etot[0, :RO] - eo[0]).max() < 0.05  # still the same trajectories after 200 steps
+    cmp = compare_ensembles(drift_stats(etot), drift_stats(eo))
+    assert abs(cmp["drift_diff"]) < 3.0 * cmp["drift_diff_se"], cmp
+    assert abs(cmp["rms_diff"]) < 3.0 * cmp["rms_diff_se"], cmp
+    # and the size of it: the ensemble drifts by well under 1e-3 of E_tot (~550 kcal/mol) over 100 ps
+    assert abs(cmp["gpu_drift_mean"]) < 0.5 and cmp["gpu_rms_mean"] < 1.0, cmp
 
 
 @pytest.mark.parametrize("system", ["bb40", "ala10"])
-@pytest.mark.parametrize("case", ["rep_plain", "rep_cut", "cg_plain", "cg_rf"])
+@pytest.mark.parametrize("case", ["rep_plain", "rep_cut", "cg_plain", "cg_rf", "combo_plain", "combo_cut"])
 def test_repulsion_terms_vs_reference_fp64(system, case):
     """SURVEY 8 row a12 (forces.py:416-448): CUDA path against the unmodified reference run in fp64
     (tests/golden/repulsion.npz, tools/make_golden_repulsion.py)."""
@@ -446,9 +408,7 @@ def test_repulsion_terms_vs_reference_fp64(system, case):
     assert set(pot[0]) == set(terms) | {"external"}
     for t in terms:
         got = np.array([float(p[t]) for p in pot])
-        np.testing.assert_allclose(got, r[f"{system}_{case}_f64_E_{t}"], rtol=2e-6)
-    with pytest.raises(NotImplementedError):
-        Forces(gpu_par(g), terms=("lj", "repulsion"))
+        np.testing.assert_allclose(got, r[f"{system}_{case}_f64_E_{t}"], rtol=1e-6, atol=1e-9)
 
 
 @pytest.mark.parametrize("system", ["bb40", "ala10"])
@@ -467,9 +427,7 @@ def test_minimum_image_vs_reference_fp64(system, mode):
     fr, er = r[f"{system}_{mode}_f64_forces"], r[f"{system}_{mode}_f64_energies"]
     f = frc.cpu().numpy()
     assert (np.abs(f - fr).reshape(len(f), -1).max(1) / np.abs(fr).reshape(len(f), -1).max(1)).max() <= 1e-5
-    for k in (2, 3, 4):  # bonds, angles, dihedrals
-        np.testing.assert_allclose(ene[:, k], er[:, k], rtol=2e-6)
-    np.testing.assert_allclose(ene[:, :2].sum(1), er[:, :2].sum(1), rtol=1e-5)  # electrostatics + lj
+    check_energies(ene, er, f"minimum image, {system} {mode}")
 
 
 def test_integrator_with_box_short_horizon_vs_oracle():
@@ -894,9 +852,7 @@ def test_random_topologies_vs_oracle(natoms, seed):
         f, e, F = run_gpu(g, g.pos, **MODES[mode])
         ferr = np.abs(f - f_ref).reshape(len(f), -1).max(1) / np.abs(f_ref).reshape(len(f), -1).max(1)
         assert ferr.max() < 3e-5, (mode, ferr.max())
-        coul, lj = pair_scales(g, g.pos)
-        scale = np.abs(e_ref).sum(1) + coul + lj + torsion_scale(g.par, "dihedrals") + torsion_scale(g.par, "impropers")
-        assert (np.abs(e - e_ref).max(1) <= 3e-6 * scale).all(), (mode, (np.abs(e - e_ref).max(1) / scale).max())
+        check_energies(e, e_ref, f"random topology {natoms} atoms, {mode}")
         np.testing.assert_array_equal(F.ava_idx.cpu().numpy().reshape(-1, 2), g.ava_idx.reshape(-1, 2))
     # the fused integrator on the same topology (fixed-point bonded accumulation, static schedule, bank spreading)
     vel0 = (0.02 * np.random.default_rng(seed).standard_normal(g.pos.shape)).astype(np.float32)
@@ -999,11 +955,9 @@ def test_large_solute_forces_vs_oracle(natoms, seed):
         f, e, F = run_gpu(g, g.pos, **MODES[mode])
         ferr = np.abs(f - f_ref).reshape(len(f), -1).max(1) / np.abs(f_ref).reshape(len(f), -1).max(1)
         assert ferr.max() < 1e-5, (mode, ferr.max())
-        coul, lj = pair_scales(g, g.pos)
-        scale = np.abs(e_ref).sum(1) + coul + lj + torsion_scale(g.par, "dihedrals") + torsion_scale(g.par, "impropers")
-        assert (np.abs(e - e_ref).max(1) <= 1e-6 * scale).all(), (mode, (np.abs(e - e_ref).max(1) / scale).max())
-        # bonded kinds run in FP64: their slots agree with the oracle far below the fp32 pair tolerance
-        for slot in (2, 3, 4, 6):
+        check_energies(e, e_ref, f"large random topology {natoms} atoms, {mode}")
+        # every kind runs in FP64: the slots agree with the oracle far below the contract
+        for slot in range(8):
             np.testing.assert_allclose(e[:, slot], e_ref[:, slot], rtol=1e-9, atol=1e-9)
         np.testing.assert_array_equal(F.ava_idx.cpu().numpy().reshape(-1, 2), g.ava_idx.reshape(-1, 2))
     # integer artefact: the exclusion bit matrix is the complement of the reference's pair list
@@ -1030,8 +984,7 @@ def test_large_solute_term_subsets_box_and_smd_vs_oracle():
     f_ref, e_ref = oracle.forces(g.packed, g.pos, box=box.reshape(3, 9), **MODES["rf"])
     f = s.forces.cpu().numpy()
     assert np.abs(f - f_ref).max() / np.abs(f_ref).max() < 1e-5
-    coul, lj = pair_scales(g, g.pos)
-    assert (np.abs(e - e_ref).max(1) <= 3e-6 * (np.abs(e_ref).sum(1) + coul + lj)).all()
+    check_energies(e, e_ref, "large solute, per-replica boxes")
     # term subsets + the SMD restraint with per-replica centres
     smd = dict(atom1=3, atom2=190, fk=1.5, center0=0.0)
     cen = np.array([150.0, 160.0, 170.0], dtype=np.float32)
@@ -1039,7 +992,7 @@ def test_large_solute_term_subsets_box_and_smd_vs_oracle():
         f_ref, e_ref = oracle.forces(g.packed, g.pos, smd=smd, smd_centers=cen, terms=terms)
         f, e, _ = run_gpu(g, g.pos, smd=smd, centers=cen, terms=terms)
         assert np.abs(f - f_ref).max() / np.abs(f_ref).max() < 1e-5, terms
-        np.testing.assert_allclose(e, e_ref, rtol=2e-6, atol=2e-6 * np.abs(e_ref).max())
+        check_energies(e, e_ref, f"large solute {terms}")
 
 
 def test_large_solute_integrator_vs_oracle_and_bitwise_determinism():
@@ -1112,8 +1065,7 @@ def test_large_solute_bundle_of_ala10_chains_vs_oracle():
         f = s.forces.cpu().numpy()
         f_ref, e_ref = oracle.forces(packed, pos, **MODES[mode])
         assert np.abs(f - f_ref).max() / np.abs(f_ref).max() < 1e-5, mode
-        np.testing.assert_allclose(e[:, 2:5], e_ref[:, 2:5], rtol=1e-9)
-        np.testing.assert_allclose(e[:, :2], e_ref[:, :2], rtol=2e-5, atol=2e-3)
+        np.testing.assert_allclose(e, e_ref, rtol=1e-9, atol=1e-9)  # FP64 energies, pair terms included
     # the same conformers far apart in a box: minimum image brings them back into range, no tile may be dropped
     box = np.zeros((R, 3, 3), dtype=np.float32)
     box[:, 0, 0], box[:, 1, 1], box[:, 2, 2] = 80.0, 120.0, 120.0
@@ -1155,3 +1107,232 @@ def test_large_solute_vs_reference_fp64(mode):
     f, e, F = run_gpu(g, g["pos"], **MODES[mode])
     check(g, g["pos"], f, e, g[f"ref_{mode}_f64_forces"], g[f"ref_{mode}_f64_energies"], mode)
     np.testing.assert_array_equal(F.ava_idx.cpu().numpy(), g.ava_idx)
+
+
+# ---- round 2: time slicing, force-only launches, boundary gaps ---------------------------------------------------
+def _slicing_run(g, R, niter, slice_len, rigid=False):
+    rng = np.random.default_rng(11)
+    pos0 = (g["pos"][rng.integers(0, len(g["pos"]), R)] + 0.02 * rng.standard_normal((R, 104, 3))).astype(np.float32)
+    vel0 = (0.01 * rng.standard_normal(pos0.shape)).astype(np.float32)
+    par, s = make_system(g, pos0, vel0)
+    F = Forces(par, external=SMDBias([3], [98], fk=1.0, cent_0=14.0, rate_per_step=1e-3))
+    F.compute_batch(s.pos, s.box, s.forces)
+    integ = Integrator(s, F, timestep=1.0, device=DEV, gamma=1.0, T=300.0, seed=5, rigid_bonds=rigid)
+    integ.energy_every, integ.snapshot_every = 6, 9
+    if rigid:
+        integ.apply_constraints()
+    old = os.environ.get("B200MD_SLICE")
+    try:
+        if slice_len is None:
+            os.environ.pop("B200MD_SLICE", None)
+        else:
+            os.environ["B200MD_SLICE"] = str(slice_len)
+        integ.step(niter=niter)
+    finally:
+        if old is None:
+            os.environ.pop("B200MD_SLICE", None)
+        else:
+            os.environ["B200MD_SLICE"] = old
+    torch.cuda.synchronize()
+    return [t.cpu().numpy() for t in (s.pos, s.vel, s.forces, integ.observables, integ.snapshots)]
+
+
+@pytest.mark.parametrize("R,rigid", [(40, False), (700, False), (40, True)])
+def test_time_slicing_is_bitwise_invariant(R, rigid):
+    """The fused integrator hands out (slice of steps, replica) units from a ticket counter and parks a replica's state
+    in HBM between its slices (csrc/b200md.cu, integrate_kernel).  A step's arithmetic does not depend on the slicing:
+    positions, velocities, forces, every observable record (SMD work carried across slices included) and the snapshots
+    are bit-identical for one slice per launch, the default, and slices of 1 and 7 steps -- also with more replicas
+    than resident CTAs and with the rigid-bond kernel."""
+    g = load_golden("ala10")
+    niter = 37
+    ref = _slicing_run(g, R, niter, niter, rigid)
+    assert np.isfinite(ref[0]).all()
+    for sl in (None, 1, 7):
+        out = _slicing_run(g, R, niter, sl, rigid)
+        for a, b in zip(ref, out):
+            np.testing.assert_array_equal(a, b)
+
+
+def test_force_only_launch_matches_and_backward_uses_it():
+    """compute_batch(..., energies=False) skips the FP64 energy pass (NULL energies in the C-ABI): same force bits."""
+    g = load_golden("ala10")
+    for mode in MODES:
+        F = Forces(gpu_par(g), **MODES[mode])
+        p = torch.tensor(g["pos"], device=DEV)
+        s1, s2 = System(104, len(p), torch.float, DEV), System(104, len(p), torch.float, DEV)
+        e = F.compute_batch(p, s1.box, s1.forces)
+        assert F.compute_batch(p, s2.box, s2.forces, energies=False) is None
+        assert torch.equal(s1.forces, s2.forces) and e.shape == (len(p), 8)
+
+
+def test_report_after_the_last_step_when_niter_is_not_a_multiple():
+    """Integrator.step returns the energies of the END state (upstream's contract): with energy_every = 4 and 10 steps the
+    records are steps 4, 8 and 10."""
+    g = load_golden("diala")
+    pos0 = g["pos"]
+    par, s = make_system(g, pos0, np.zeros_like(pos0))
+    F = Forces(par)
+    F.compute_batch(s.pos, s.box, s.forces)
+    f0 = s.forces.cpu().numpy().astype(np.float64)
+    integ = Integrator(s, F, timestep=0.5, device=DEV)
+    integ.energy_every = 4
+    ekin, pot, T = integ.step(niter=10)
+    assert integ.observables.shape[0] == 3
+    out = oracle.integrate(g.packed, pos0, np.zeros_like(pos0), f0, nsteps=10, dt=np.float32(integ.dt), energy_every=4)
+    ref = out["observables"]
+    assert ref.shape[0] == 3
+    np.testing.assert_allclose(integ.observables.cpu().numpy()[:, :, :8].sum(-1), ref[:, :, :8].sum(-1), rtol=2e-5, atol=2e-3)
+    e_end = F.compute_batch(s.pos, s.box, torch.empty_like(s.forces)).sum(1).cpu().numpy()
+    np.testing.assert_allclose(np.asarray(pot), e_end, rtol=1e-6)
+
+
+def test_ctypes_only_host_entry_point_vs_reference_fp64():
+    """The binding INTEGRATION.md promises a non-torch host: b200md_topology_create -> b200md_forces_compute_host with
+    plain numpy buffers through ctypes (no torch tensor, op or stream on the call path), compared with the stored fp64
+    output of the reference's forces.py on bb40.npz."""
+    import ctypes as C
+
+    g = load_golden("bb40")
+    lib = _cabi.load_library()
+    pos = np.ascontiguousarray(g["pos"], dtype=np.float32)
+    R, N, _ = pos.shape
+    h = lib.b200md_topology_create(C.byref(g.packed.desc), 0)
+    assert h, _cabi.last_error()
+    try:
+        for mode, kw in MODES.items():
+            fo = _cabi.ForceOpts(sum(_cabi.TERM_BITS[t] for t in ("electrostatics", "lj", "bonds", "angles", "dihedrals", "1-4", "impropers")),
+                                 float(kw.get("cutoff", 0.0)), int(kw.get("rfa", False)), 78.5, float(kw.get("switch_dist", 0.0)))
+            so = _cabi.SmdOpts(0, 0, 0, 0.0, 0.0, 0.0, None)
+            frc = np.full((R, N, 3), np.nan, dtype=np.float32)
+            ene = np.full((R, 8), np.nan, dtype=np.float64)
+            status = np.full(R, 99, dtype=np.uint32)
+            rc = lib.b200md_forces_compute_host(C.c_void_p(h), C.byref(fo), C.byref(so), R, pos.ctypes.data_as(C.c_void_p), None,
+                                                frc.ctypes.data_as(C.c_void_p), ene.ctypes.data_as(C.c_void_p),
+                                                status.ctypes.data_as(C.c_void_p))
+            assert rc == _cabi.OK, _cabi.last_error()
+            assert (status == 0).all()
+            check(g, pos, frc.astype(np.float64), ene, g[f"ref_{mode}_f64_forces"], g[f"ref_{mode}_f64_energies"], f"host {mode}")
+        bad = pos.copy()
+        bad[0, 0, 0] = np.nan
+        rc = lib.b200md_forces_compute_host(C.c_void_p(h), C.byref(fo), C.byref(so), R, bad.ctypes.data_as(C.c_void_p), None,
+                                            frc.ctypes.data_as(C.c_void_p), ene.ctypes.data_as(C.c_void_p), None)
+        assert rc == _cabi.ERR_NAN_COORDINATES and "NaN" in _cabi.last_error()
+    finally:
+        lib.b200md_topology_destroy(C.c_void_p(h))
+
+
+class _ToyExternal:
+    """forces.py:318-323: anything with calculate(pos, box) -> (energy (R,), force (R, N, 3)).  A harmonic tether of every
+    atom to the origin, written with torch ops so that it also carries an autograd edge."""
+
+    def __init__(self, k):
+        self.k = k
+
+    def calculate(self, pos, box):
+        return 0.5 * self.k * (pos * pos).sum(dim=(1, 2)), -self.k * pos
+
+
+def test_generic_external_object_in_compute_autograd_and_integrator():
+    g = load_golden("bb40")
+    pos0 = g["pos"][:3]
+    k = 0.05
+    # compute: energy in the "external" column, force added (forces.py:318-323)
+    F = Forces(gpu_par(g), external=_ToyExternal(k))
+    F0 = Forces(gpu_par(g))
+    p = torch.tensor(pos0, device=DEV)
+    s, s0 = System(40, 3, torch.float, DEV), System(40, 3, torch.float, DEV)
+    e, e0 = F.compute_batch(p, s.box, s.forces), F0.compute_batch(p, s0.box, s0.forces)
+    np.testing.assert_allclose(e[:, 7].cpu().numpy(), 0.5 * k * (pos0.astype(np.float64) ** 2).sum((1, 2)), rtol=1e-6)
+    np.testing.assert_allclose((s.forces - s0.forces).cpu().numpy(), -k * pos0, rtol=1e-4, atol=1e-5)
+    # autograd with equal weights on every term: the external gradient is counted once (ADVICE r1)
+    pg = p.clone().requires_grad_(True)
+    tot = F.compute(pg, s.box, torch.zeros_like(s.forces), explicit_forces=False)
+    tot.backward()
+    np.testing.assert_allclose(pg.grad.cpu().numpy(), -s.forces.cpu().numpy(), rtol=1e-5, atol=1e-4)
+    # Integrator.step: launches per step with the hook in between, against the oracle driven the same way on the host
+    vel0 = np.zeros_like(pos0)
+    par, sy = make_system(g, pos0, vel0)
+    Fi = Forces(par, external=_ToyExternal(k))
+    Fi.compute_batch(sy.pos, sy.box, sy.forces)
+    integ = Integrator(sy, Fi, timestep=0.5, device=DEV)
+    ekin, pot, T = integ.step(niter=12)
+    x = pos0.astype(np.float64)
+    v = np.zeros_like(x)
+    f, _ = oracle.forces(g.packed, x.astype(np.float32))
+    f = f - k * x
+    m = g.par.masses.numpy().astype(np.float64).reshape(1, -1, 1)
+    dt = float(np.float32(integ.dt))
+    for _ in range(12):
+        v += 0.5 * dt * f / m
+        x += dt * v
+        f, en = oracle.forces(g.packed, x)
+        f = f - k * x
+        v += 0.5 * dt * f / m
+    assert np.abs(sy.pos.cpu().numpy() - x).max() < 2e-4
+    np.testing.assert_allclose(np.asarray(pot), en.sum(1) + 0.5 * k * (x ** 2).sum((1, 2)), rtol=2e-5)
+    np.testing.assert_allclose(ekin, (0.5 * m * v * v).sum((1, 2)), rtol=2e-3)
+
+
+def test_two_forwards_before_one_backward_keep_their_own_smd_centres():
+    """the backward of the batched Energy adapter must use the restraint centres of ITS forward, not whatever
+    bias.center holds when backward runs (real + fake batch, gradient accumulation; different batch sizes)."""
+    from molecular_dynamics_b200 import Energy
+
+    g = load_golden("ala10")
+    colvar = {"name": "E2End Harm", "fk": 1.0, "cent_0": 12.0, "cent_1": 34.0, "T": 1.0, "group1": [3], "group2": [98]}
+    en = Energy(parameters=gpu_par(g), colvar=colvar, device=DEV)
+    xa = torch.tensor(g["pos"][:4], device=DEV)
+    xb = torch.tensor(g["pos"][:3] + 0.01, device=DEV)
+    ta, tb = torch.tensor([0.1, 0.3, 0.5, 0.7], device=DEV), torch.tensor([0.9, 0.2, 0.6], device=DEV)
+
+    def loss(ene):
+        return sum(v for k, v in ene.items() if k != "E2End Harm").sum() + 200.0 * ene["E2End Harm"].sum()
+
+    # separately
+    grads = []
+    for x, t in ((xa, ta), (xb, tb)):
+        xg = x.clone().requires_grad_(True)
+        loss(en.calc_energy_batch(xg, t)[0]).backward()
+        grads.append(xg.grad.clone())
+    # both forwards first, one backward
+    xga, xgb = xa.clone().requires_grad_(True), xb.clone().requires_grad_(True)
+    la = loss(en.calc_energy_batch(xga, ta)[0])
+    lb = loss(en.calc_energy_batch(xgb, tb)[0])
+    (la + lb).backward()
+    assert torch.equal(xga.grad, grads[0]) and torch.equal(xgb.grad, grads[1])
+
+
+def test_double_precision_tensors_are_accepted():
+    """systems.py:32-36: the reference classes take precision=torch.double.  The drop-in accepts float64 positions / forces
+    (kernels compute forces in fp32, energies in FP64) and hands results back in the caller's dtype."""
+    g = load_golden("ala10")
+    F = Forces(gpu_par(g), **MODES["rf"])
+    s = System(104, len(g["pos"]), torch.double, DEV)
+    s.pos[:] = torch.tensor(g["pos"], device=DEV, dtype=torch.double)
+    pot = F.compute(s.pos, s.box, s.forces, returnDetails=True)
+    assert s.forces.dtype == torch.float64 and pot[0]["lj"].dtype == torch.float64
+    e = np.array([[float(p[k]) for k in _cabi.ENERGY_SLOTS] for p in pot])
+    check(g, g["pos"], s.forces.cpu().numpy(), e, g["ref_rf_f64_forces"], g["ref_rf_f64_energies"], "double tensors")
+    phi = F.dihedral_angles(s.pos)
+    assert phi.dtype == torch.float64
+
+
+def test_library_calls_leave_the_current_device_alone():
+    """an entry point runs on the topology's device and restores the caller's current device."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    g = load_golden("bb40")
+    par = Parameters.from_arrays(g.par.to_arrays(), device="cuda:1")
+    F = Forces(par)
+    p = torch.tensor(g["pos"], device="cuda:1")
+    s = System(40, len(p), torch.float, "cuda:1")
+    torch.cuda.set_device(0)
+    e = F.compute_batch(p, s.box, s.forces)
+    assert torch.cuda.current_device() == 0
+    integ = Integrator(s, F, timestep=0.5, device="cuda:1")
+    s.pos[:] = p
+    integ.step(niter=3)
+    assert torch.cuda.current_device() == 0
+    f_ref, e_ref = oracle.forces(g.packed, g["pos"])
+    check_energies(e.cpu().numpy(), e_ref, "cuda:1")

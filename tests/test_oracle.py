@@ -196,6 +196,9 @@ REPULSION_CASES = {  # tools/make_golden_repulsion.py
     "rep_cut": (("repulsion", "bonds"), {"cutoff": 9.0, "switch_dist": 7.5}),
     "cg_plain": (("repulsioncg", "electrostatics", "bonds"), {}),
     "cg_rf": (("repulsioncg", "electrostatics", "angles"), {"cutoff": 9.0, "rfa": True, "switch_dist": 7.5}),
+    # several pair terms of the lj family at once (forces.py:268-316 evaluates each enabled one; only "lj" is switched)
+    "combo_plain": (("lj", "repulsion", "electrostatics", "bonds"), {}),
+    "combo_cut": (("repulsioncg", "lj", "repulsion", "angles"), {"cutoff": 9.0, "switch_dist": 7.5}),
 }
 
 
@@ -211,8 +214,12 @@ def test_oracle_repulsion_terms_vs_reference(system, case):
     f, e = oracle.forces(g.packed, r[f"{system}_pos"], terms=terms, **kw)
     fr = r[f"{system}_{case}_f64_forces"]
     assert np.abs(f - fr).max() <= 1e-9 * np.abs(fr).max()
+    family = [t for t in terms if t in ("lj", "repulsion", "repulsioncg")]
     for t in terms:
-        np.testing.assert_allclose(e[:, _cabi.energy_slot(t)], r[f"{system}_{case}_f64_E_{t}"], rtol=1e-10)
+        if t not in family:
+            np.testing.assert_allclose(e[:, _cabi.energy_slot(t)], r[f"{system}_{case}_f64_E_{t}"], rtol=1e-10)
+    # the oracle (like one launch of the ABI) books every enabled term of the lj family in the "lj" column
+    np.testing.assert_allclose(e[:, 1], sum(r[f"{system}_{case}_f64_E_{t}"] for t in family), rtol=1e-10)
 
 
 @pytest.mark.parametrize("system", ["bb40", "ala10"])

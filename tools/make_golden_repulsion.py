@@ -23,6 +23,9 @@ CASES = {  # name -> (terms, Forces kwargs)
     "rep_cut": (("repulsion", "bonds"), {"cutoff": 9.0, "switch_dist": 7.5}),
     "cg_plain": (("repulsioncg", "electrostatics", "bonds"), {}),
     "cg_rf": (("repulsioncg", "electrostatics", "angles"), {"cutoff": 9.0, "rfa": True, "switch_dist": 7.5}),
+    # several pair terms of the lj family at once (forces.py:268-316 evaluates each enabled one; only "lj" is switched)
+    "combo_plain": (("lj", "repulsion", "electrostatics", "bonds"), {}),
+    "combo_cut": (("repulsioncg", "lj", "repulsion", "angles"), {"cutoff": 9.0, "switch_dist": 7.5}),
 }
 
 

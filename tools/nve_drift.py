@@ -27,14 +27,26 @@ def drift_stats(etot):
     return slope * (n - 1), np.sqrt(((etot - fit) ** 2).mean(0))
 
 
+def compare_ensembles(gpu, ora):
+    """(drift, rms) per replica of two ensembles -> difference of the ensemble means with its standard error
+    sqrt(s_g^2 / n_g + s_o^2 / n_o): the yardstick of "the drift matches the reference"."""
+    (dg, rg), (do, ro) = gpu, ora
+    se = lambda a, b: float(np.sqrt(a.var(ddof=1) / len(a) + b.var(ddof=1) / len(b)))
+    return {"gpu_drift_mean": float(dg.mean()), "gpu_drift_std": float(dg.std(ddof=1)), "gpu_rms_mean": float(rg.mean()),
+            "oracle_drift_mean": float(do.mean()), "oracle_drift_std": float(do.std(ddof=1)), "oracle_rms_mean": float(ro.mean()),
+            "n_gpu": int(len(dg)), "n_oracle": int(len(do)),
+            "drift_diff": float(dg.mean() - do.mean()), "drift_diff_se": se(dg, do),
+            "rms_diff": float(rg.mean() - ro.mean()), "rms_diff_se": se(rg, ro)}
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--replicas", type=int, default=64)
+    ap.add_argument("--replicas", type=int, default=8192)
     ap.add_argument("--steps", type=int, default=100000)
-    ap.add_argument("--oracle-steps", type=int, default=10000)
-    ap.add_argument("--oracle-replicas", type=int, default=8)
+    ap.add_argument("--oracle-steps", type=int, default=100000)
+    ap.add_argument("--oracle-replicas", type=int, default=16)
     ap.add_argument("--dt", type=float, default=1.0)
-    ap.add_argument("--every", type=int, default=100)
+    ap.add_argument("--every", type=int, default=200)
     ap.add_argument("--copies", type=int, default=1,
                     help="> 1: a bundle of this many chains 40 A apart as ONE topology (Parameters.tiled): the large-solute kernels")
     ap.add_argument("--rigid", action="store_true", help="rigid X-H bonds (SHAKE / RATTLE), e.g. with --dt 2.0")
@@ -75,7 +87,7 @@ def main():
     while done < a.steps:  # launches of <= 20 000 steps (observable buffer stays small)
         n = min(20000, a.steps - done)
         integ.step(niter=n)
-        chunks.append(integ.observables.cpu().numpy())
+        chunks.append(integ.observables[:, :, :_cabi.OBS_EKIN + 1].cpu().numpy())
         done += n
     obs = np.concatenate(chunks, 0)
     etot = obs[:, :, :8].sum(-1) + obs[:, :, _cabi.OBS_EKIN]
@@ -97,6 +109,8 @@ def main():
                               "rms_fluct_mean": float(ro_.mean())}
         out["gpu_same_horizon"] = {"drift_mean": float(dg.mean()), "drift_abs_max": float(np.abs(dg).max()), "rms_fluct_mean": float(rg.mean()),
                                    "etot_first_report_max_abs_diff": float(np.abs(etot[0, :ro] - eo[0]).max())}
+        # the whole GPU ensemble over the oracle's horizon against the oracle's ensemble: difference of means, standard error
+        out["ensemble_comparison"] = compare_ensembles(drift_stats(etot[:nrep]), (do, ro_))
     print(json.dumps(out))
 
 
