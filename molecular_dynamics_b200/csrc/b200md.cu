@@ -241,8 +241,8 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
       __syncthreads();
       // a record every energy_every steps and after the last step of the call (what step() returns is the end state)
       const bool report = (I.energy_every > 0 && (s + 1) % I.energy_every == 0) || s == I.nsteps - 1;
-      if (pbc) run_tasks<MODE, true, true>(S, T, P, warp, lane);
-      else run_tasks<MODE, true, false>(S, T, P, warp, lane);
+      if (pbc) run_tasks<MODE, true, true, !RIGID>(S, T, P, warp, lane);
+      else run_tasks<MODE, true, false, !RIGID>(S, T, P, warp, lane);
       if (P.smd_on && tid == kThreads - 1) smd_task(S, P, (float)((double)P.smd_c0 + (double)P.smd_rate * (double)(gstep + 1)));
       __syncthreads();
       {

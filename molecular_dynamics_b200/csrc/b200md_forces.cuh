@@ -104,7 +104,7 @@ __device__ __forceinline__ u64 pair_eval2(u64 dx, u64 dy, u64 dz, float kqi, u64
 // Lane = i atom; the 8 j atoms arrive as 4 packed pairs (x[], y[], z[], q[] and the 12A / -6B rows are
 // structure-of-arrays, so one LDS.128 delivers two f32x2 operands).  The pass loop is rolled (one body in the
 // instruction cache); the i-side force of a pass is added to this warp's shared-memory partial.
-template <int MODE, bool PBC>
+template <int MODE, bool PBC, bool SKIP>
 __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, int chunk, int passes, int warp,
                                           int lane) {
   const float4 nbox = PBC ? *(const float4*)S.box : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -134,6 +134,28 @@ __device__ __forceinline__ void tile_task(const Smem& S, const ForceParams& P, i
       pi_n = S.pos[in];
       roff_n = S.ab_row_off[in];
       m8_n = S.mask8[chunk * kMaxAtoms + in];
+    }
+    if (MODE == 1 && SKIP) {
+      // Cutoff mode: a pass whose 32 x 8 pairs are ALL beyond the cutoff contributes exactly zero (pair_eval2 zeroes every
+      // term of such a pair), so it is skipped on a warp vote -- bit-identical results.  The r^2 below are the expressions
+      // pair_eval2 evaluates (same operands, same order): the compiler merges them, the test costs the compares and a vote.
+      // For the extended deca-alanine conformers of the benchmark (end-to-end 31 A, cutoff 9 A) 6 of the 15 passes drop out.
+      // (SKIP = false: the rigid-bond instantiation, where the test's live registers would spill.)
+      bool in = false;
+#pragma unroll
+      for (int h = 0; h < kChunk / 4; ++h) {
+        const ulonglong2 xj = *(const ulonglong2*)(sj + 4 * h), yj = *(const ulonglong2*)(sj + kMaxAtoms + 4 * h),
+                         zj = *(const ulonglong2*)(sj + 2 * kMaxAtoms + 4 * h);
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          u64 dx = sub2(xi, k ? xj.y : xj.x), dy = sub2(yi, k ? yj.y : yj.x), dz = sub2(zi, k ? zj.y : zj.x);
+          if (PBC) { dx = wrap2(dx, nbox.x, ibox.x); dy = wrap2(dy, nbox.y, ibox.y); dz = wrap2(dz, nbox.z, ibox.z); }
+          float ra, rb;
+          upk(fma2(dz, dz, fma2(dy, dy, mul2(dx, dx))), ra, rb);
+          in = in || ra <= P.rc2 || rb <= P.rc2;
+        }
+      }
+      if (!__any_sync(0xffffffffu, in)) continue;
     }
     u64 ax = 0ull, ay = 0ull, az = 0ull;
 #pragma unroll
@@ -695,7 +717,7 @@ __device__ __noinline__ void energy_pass(const Smem& S, const DevTopo& T, const 
 // is a tight loop around its own body: no switch, and the next task word is fetched while the current task runs
 // (the fetch -> decode -> branch chain of a switch-per-task loop cost 33 issue slots and ~150 cycles of exposed
 // latency per task, profiles/r01_v11).
-template <int MODE, bool FIXED, bool PBC>
+template <int MODE, bool FIXED, bool PBC, bool SKIP = true>
 __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const ForceParams& P, int warp, int lane) {
   const uint32_t* tk = S.tasks + warp * kMaxTasks;
   const uint2 kends = T.kend8[warp];  // the 7 run ends as bytes: one constant load instead of one per kind
@@ -713,7 +735,7 @@ __device__ __forceinline__ void run_tasks(const Smem& S, const DevTopo& T, const
       BODY;                                                                           \
     }                                                                                 \
   }
-  B200MD_TASK_LOOP(0, (tile_task<MODE, PBC>(S, P, chunk, passes, warp, lane)))
+  B200MD_TASK_LOOP(0, (tile_task<MODE, PBC, SKIP>(S, P, chunk, passes, warp, lane)))
   B200MD_TASK_LOOP(1, (tile_diag_task<MODE, PBC>(S, P, chunk & 0xff, (chunk >> 8) & 0xff, passes, warp, lane)))
   B200MD_TASK_LOOP(2, (dihedral_task<FIXED, PBC>(S, T, P, item, (int)passes)))
   B200MD_TASK_LOOP(3, (torsion_task<FIXED, PBC>(S, T, item)))
