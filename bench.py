@@ -453,6 +453,43 @@ def run_ours(args):
                           "max over ranks, L2 flushed between launches"}
         del sys_s, integ_s
 
+    # ---- configs[4]: replica-count sweep, TOTAL replicas split over the ranks (1 000 NVE steps per launch) ----------
+    sweep = []
+    if args.sweep and not config4:
+        from molecular_dynamics_b200.sharding import shard_range
+        for Rt in [int(v) for v in args.sweep.split(",") if v]:
+            lo, hi = shard_range(Rt, rank, world)
+            Rs = hi - lo
+            idx = (np.arange(lo, hi) % R)  # inputs of global replica g = those of replica g mod R of the main run
+            sys_w = System(104, Rs, torch.float, dev)
+            sys_w.pos[:] = torch.tensor(pos_h[idx], device=dev)
+            sys_w.vel[:] = torch.tensor(vel_h[idx], device=dev)
+            forces.compute_batch(sys_w.pos, sys_w.box, sys_w.forces)
+            integ_w = Integrator(sys_w, forces, timestep=1.0, device=dev)
+            integ_w.energy_every, integ_w.replica0, integ_w.check_nan = args.energy_every, lo, False
+
+            def sweep_step():
+                integ_w.step(niter=S)
+                if world > 1:
+                    gather_observables(integ_w.observables[-1], Rt)
+
+            sweep_step()
+            nsw = 3
+            evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(nsw)]
+            barrier()
+            for a, b in evs:
+                flush.fill_(1)
+                a.record()
+                sweep_step()
+                b.record()
+            barrier()
+            tw = torch.tensor([sum(a.elapsed_time(b) for a, b in evs)], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+            sweep.append({"replicas_total": Rt, "replicas_per_gpu": Rs, "value": Rt * S * nsw / (float(tw.item()) * 1e-3),
+                          "unit": "replica-steps/s", "ms_per_launch": float(tw.item()) / nsw})
+            del sys_w, integ_w
+
     # ---- secondary workloads (BASELINE.json configs[1] and configs[3]); reported under "extra", N = 1 only -----
     extra = {}
     if world == 1 and not args.no_extra:
@@ -624,6 +661,8 @@ def run_ours(args):
         }
         if strong is not None:
             extra["strong_scaling"] = strong
+        if sweep:
+            extra["replica_sweep"] = sweep
         if extra:
             line["extra"] = extra
         if world == 1 and not args.no_cpu:
@@ -792,6 +831,8 @@ def main():
     ap.add_argument("--forces-mode", default="plain", choices=sorted(FORCES_MODES),
                     help="--workload forces: plain all-pairs, or rf = cutoff 9 A + reaction field + switch 7.5 A")
     ap.add_argument("--no-energies", action="store_true", help="--workload forces: force-only launches (no FP64 energy pass)")
+    ap.add_argument("--sweep", default="", help="comma-separated TOTAL replica counts of the configs[4] sweep (split over the ranks), "
+                                                "e.g. 1024,4096,16384,65536,262144; reported under extra.replica_sweep")
     ap.add_argument("--strong-total", type=int, default=8192,
                     help="replicas of the strong-scaling leg, split over the ranks (0: skip the leg)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

@@ -239,6 +239,19 @@ int b200md_forces_compute_host(const b200md_topology* topo, const b200md_force_o
                                const float* box_host, float* forces_host, double* energies_host,
                                uint32_t* status_host);
 
+/* Batched FIRE minimiser, the update between two force evaluations as one kernel (the batched form of the tutorial's
+ * minimize_bfgs call, V_Calculations/Test-1/tutorial.ipynb cell 14; upstream torchmd.minimizers is not part of the
+ * reference).  state: DEVICE float [R][4] = (dt, alpha, steps since the last uphill move, max|F| of this call's forces):
+ * initialise to (dt_start, alpha_start, 0, 0).  pos / vel are updated in place from `forces` (= forces at pos); the
+ * caller evaluates the forces at the new positions (b200md_forces_compute with energies = NULL) and calls again, reading
+ * state[:, 3] every few iterations for the convergence test max|F| <= fmax. */
+typedef struct b200md_fire_opts {
+  float dt_max, max_move, f_inc, f_dec, alpha_start, f_alpha;
+  int32_t n_min;
+} b200md_fire_opts;
+int b200md_fire_update(int device, int64_t nreplicas, int32_t natoms, float* pos, float* vel, const float* forces,
+                       float* state, const b200md_fire_opts* opts, void* stream);
+
 /* FP32 FMA throughput micro-benchmark used as the roofline denominator: runs `iters` dependent
  * FMA chains on every SM and returns achieved TFLOP/s (<0 on error). */
 double b200md_fp32_peak_tflops(int device, int iters);

@@ -73,6 +73,11 @@ class IntegrateOpts(C.Structure):
                 ("energy_every", C.c_int32), ("snapshot_every", C.c_int32), ("rigid_bonds", C.c_int32)]
 
 
+class FireOpts(C.Structure):
+    _fields_ = [("dt_max", C.c_float), ("max_move", C.c_float), ("f_inc", C.c_float), ("f_dec", C.c_float),
+                ("alpha_start", C.c_float), ("f_alpha", C.c_float), ("n_min", C.c_int32)]
+
+
 # ----------------------------------------------------------------------------------------------
 # flattening
 # ----------------------------------------------------------------------------------------------
@@ -201,6 +206,8 @@ def declare_signatures(lib):
     lib.b200md_forces_compute_host.restype = C.c_int
     lib.b200md_forces_compute_host.argtypes = [vp, C.POINTER(ForceOpts), C.POINTER(SmdOpts), C.c_int64, vp, vp, vp,
                                                vp, vp]
+    lib.b200md_fire_update.restype = C.c_int
+    lib.b200md_fire_update.argtypes = [C.c_int, C.c_int64, C.c_int32, vp, vp, vp, vp, C.POINTER(FireOpts), vp]
     lib.b200md_fp32_peak_tflops.restype = C.c_double
     lib.b200md_fp32_peak_tflops.argtypes = [C.c_int, C.c_int]
     lib.b200md_launch_count.restype = C.c_int64
@@ -216,7 +223,7 @@ EXPORTED_SYMBOLS = (
     "b200md_topology_create", "b200md_topology_destroy", "b200md_topology_exclusion_mask",
     "b200md_topology_natoms", "b200md_topology_mask_words", "b200md_topology_num_constraints", "b200md_topology_ndihedrals",
     "b200md_dihedral_angles", "b200md_dihedral_angles_backward", "b200md_constrain", "b200md_forces_compute", "b200md_integrate", "b200md_forces_compute_host",
-    "b200md_fp32_peak_tflops", "b200md_launch_count", "b200md_last_error", "b200md_version",
+    "b200md_fire_update", "b200md_fp32_peak_tflops", "b200md_launch_count", "b200md_last_error", "b200md_version",
 )
 
 

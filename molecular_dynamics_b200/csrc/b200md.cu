@@ -13,6 +13,7 @@
 
 #include "b200md_forces.cuh"
 #include "b200md_large.cuh"
+#include "b200md_minimize.cuh"
 
 using namespace b200md;
 
@@ -1659,6 +1660,21 @@ extern "C" int b200md_forces_compute_host(const b200md_topology* topo, const b20
   cudaFree(dpos); cudaFree(dbox); cudaFree(dfrc); cudaFree(dene); cudaFree(dst);
   if (e != cudaSuccess) return fail(B200MD_ERR_CUDA, cudaGetErrorString(e));
   return rc;
+}
+
+extern "C" int b200md_fire_update(int device, int64_t R, int32_t natoms, float* pos, float* vel, const float* forces,
+                                  float* state, const b200md_fire_opts* opts, void* stream) {
+  if (!pos || !vel || !forces || !state || !opts) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
+  if (R < 0 || natoms <= 0 || (long long)natoms * 3 > 0x7fffffffll) return fail(B200MD_ERR_INVALID_ARGUMENT, "bad replica or atom count");
+  if (R == 0) return B200MD_OK;
+  B200MD_ON_DEVICE(device);
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  const int grid = (int)std::min<long long>(R, (long long)sms * 8);
+  fire_update_kernel<<<grid, kFireThreads, 0, (cudaStream_t)stream>>>(R, natoms * 3, pos, vel, forces, (float4*)state, *opts);
+  g_launches.fetch_add(1);
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
 }
 
 extern "C" double b200md_fp32_peak_tflops(int device, int iters) {

@@ -579,6 +579,18 @@ __device__ __forceinline__ void torsion_task(const Smem& S, const DevTopo& T, in
 // =====================================================================================================
 constexpr double kElecFactorD = 332.06371307417066;  // forces.py:373-376 with the reference's scipy constants
 
+// 1 / sqrt(x) in double for x of ordinary magnitude (squared distances, squared norms of cross products): the hardware
+// seed (MUFU.RSQ64H through rsqrt.approx.ftz.f64, ~2^-20 relative) and ONE third-order correction
+// y (1 + e / 2 + 3 e^2 / 8), e = 1 - x y^2, which leaves e^3 ~ 1e-18: 5 FP64 instructions on one dependency chain against
+// the ~15 of the library's rsqrt() with its special-case handling.  The energy pass is bound by the FP64 pipe
+// (64 DFMA / clock / SM), so this chain length is what a pair costs.
+__device__ __forceinline__ double drsqrt(double x) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+  const double e = fma(-x * y, y, 1.0);
+  return fma(y, e * fma(0.375, e, 0.5), y);
+}
+
 struct dv3 { double x, y, z; };
 // calculate_distances (forces.py:366-370) in double; `pbc` is uniform over the CTA (one replica), so a run-time flag costs
 // a predictable branch instead of a second copy of the FP64 code
@@ -592,8 +604,10 @@ __device__ __forceinline__ dv3 ediff(const Smem& S, bool pbc, int i, int j) {
   }
   return d;
 }
-__device__ __forceinline__ double edot(dv3 a, dv3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
-__device__ __forceinline__ dv3 ecross(dv3 a, dv3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+__device__ __forceinline__ double edot(dv3 a, dv3 b) { return fma(a.z, b.z, fma(a.y, b.y, a.x * b.x)); }
+__device__ __forceinline__ dv3 ecross(dv3 a, dv3 b) {
+  return {fma(a.y, b.z, -(a.z * b.y)), fma(a.z, b.x, -(a.x * b.z)), fma(a.x, b.y, -(a.y * b.x))};
+}
 
 // evaluate_torsion (forces.py:540-576), energy only.  Integer-periodicity AMBER terms never form phi: cos / sin(n phi)
 // come from (cos phi + i sin phi)^n, cos / sin(phi0) from the host in FP64.
@@ -602,9 +616,9 @@ __device__ __noinline__ double etorsion(const Smem& S, const DevTopo& T, bool pb
   const int a0 = q & 0xff, a1 = (q >> 8) & 0xff, a2 = (q >> 16) & 0xff, a3 = q >> 24;
   const dv3 r12 = ediff(S, pbc, a0, a1), r23 = ediff(S, pbc, a1, a2), r34 = ediff(S, pbc, a2, a3);
   const dv3 cA = ecross(r12, r23), cB = ecross(r23, r34), cC = ecross(r23, cA);
-  const double inA = rsqrt(edot(cA, cA)), inB = rsqrt(edot(cB, cB)), inC = rsqrt(edot(cC, cC));
+  const double inA = drsqrt(edot(cA, cA)), inB = drsqrt(edot(cB, cB)), inC = drsqrt(edot(cC, cC));
   const double cosPhi = edot(cA, cB) * inB * inA, sinPhi = edot(cC, cB) * inB * inC;  // forces.py:548-551
-  const double hinv = rsqrt(cosPhi * cosPhi + sinPhi * sinPhi);
+  const double hinv = drsqrt(fma(cosPhi, cosPhi, sinPhi * sinPhi));
   const double c1 = cosPhi * hinv, s1 = -sinPhi * hinv;  // cos / sin of phi = -atan2(sinPhi, cosPhi)
   double phi = 0.0, pot = 0.0;
   bool have_phi = false;
@@ -616,11 +630,11 @@ __device__ __noinline__ double etorsion(const Smem& S, const DevTopo& T, bool pb
       const double2 cs0 = __ldg(T.et_cs + t);
       double cn = c1, sn = s1;
       for (int k = 1; k < (int)tp.z; ++k) {
-        const double cc = cn * c1 - sn * s1;
-        sn = sn * c1 + cn * s1;
+        const double cc = fma(cn, c1, -(sn * s1));
+        sn = fma(sn, c1, cn * s1);
         cn = cc;
       }
-      pot += k0 * (1.0 + (cn * cs0.x + sn * cs0.y));
+      pot += k0 * (1.0 + fma(cn, cs0.x, sn * cs0.y));
       continue;
     }
     if (!have_phi) { phi = -atan2(sinPhi, cosPhi); have_phi = true; }
@@ -635,34 +649,87 @@ __device__ __noinline__ double etorsion(const Smem& S, const DevTopo& T, bool pb
   return pot;
 }
 
+// Shared-memory double load by 32-bit shared address: inside the (not inlined) energy pass the compiler cannot prove
+// that S.pd points to shared memory and would emit generic LD instead of LDS.
+__device__ __forceinline__ double lds_f64(uint32_t saddr, int idx) {
+  double v;
+  asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(saddr + 8u * (uint32_t)idx));
+  return v;
+}
+struct EPairConst {  // loop invariants of the pair loop, in registers
+  uint32_t pd;       // shared address of S.pd
+  double ta, tb, rs, inv_sw, rc2, krf, ncrf, bx, by, bz;
+};
+
+// One non-bonded pair of Forces.ava_idx in double (forces.py:379-413, 451-489): (electrostatics, lj-family) energies.
+// Straight-line (selects, no branches): the caller unrolls four of these so that their dependency chains overlap.
+template <int MODE, bool PBC>
+__device__ __forceinline__ void epair(const EPairConst& C, const double2* __restrict__ tab, uint32_t w, double scale, double& eel,
+                                      double& elj) {
+  const int i = w & 0xff, j = (w >> 8) & 0xff;
+  double dx = lds_f64(C.pd, i) - lds_f64(C.pd, j), dy = lds_f64(C.pd, kMaxAtoms + i) - lds_f64(C.pd, kMaxAtoms + j),
+         dz = lds_f64(C.pd, 2 * kMaxAtoms + i) - lds_f64(C.pd, 2 * kMaxAtoms + j);
+  if (PBC) {  // wrap_dist, forces.py:358-363; a zero box entry leaves its axis alone
+    if (C.bx != 0.0) dx -= C.bx * rint(dx / C.bx);
+    if (C.by != 0.0) dy -= C.by * rint(dy / C.by);
+    if (C.bz != 0.0) dz -= C.bz * rint(dz / C.bz);
+  }
+  const double r2 = fma(dz, dz, fma(dy, dy, dx * dx));
+  const double2 ab = __ldg(tab + (w >> 16));
+  const double rinv = drsqrt(r2), r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
+  const double qq = lds_f64(C.pd, 3 * kMaxAtoms + i) * lds_f64(C.pd, 3 * kMaxAtoms + j) * scale;  // scale = K, or 0 for a padding slot
+  double lj = fma(C.ta * ab.x, r6, C.tb * ab.y) * r6;  // lj: A r^-12 - B r^-6; repulsion: A r^-12; repulsioncg: B r^-6
+  lj = scale != 0.0 ? lj : 0.0;
+  if (MODE == 1) {
+    const double r = r2 * rinv;
+    const double t = fmax((r - C.rs) * C.inv_sw, 0.0);  // forces.py:401-411; rs = +inf (t = NaN -> 0) without a switch
+    lj *= fma(t * t * t, fma(t, fma(t, -6.0, 15.0), -10.0), 1.0);
+    const bool in = r2 <= C.rc2;  // _filter_by_cutoff, forces.py:75-80
+    eel += in ? qq * (rinv + fma(C.krf, r2, C.ncrf)) : 0.0;  // forces.py:476 (krf = crf = 0 without rfa)
+    elj += in ? lj : 0.0;
+  } else {
+    eel = fma(qq, rinv, eel);
+    elj += lj;
+  }
+}
+
+// Forces.ava_idx (forces.py:258-316); the row-major list keeps i warp-uniform and j consecutive.  Four pairs per thread
+// and iteration with their own accumulators: the FP64 chain of a pair is serial (~25 dependent instructions), and four
+// warps per scheduler do not hide that on their own.
+template <int MODE, bool PBC>
+__device__ __forceinline__ void epair_loop(const EPairConst& C, const DevTopo& T, int tid, double& eel, double& elj) {
+  double el[4] = {0.0, 0.0, 0.0, 0.0}, lj[4] = {0.0, 0.0, 0.0, 0.0};
+  const uint32_t* __restrict__ list = T.e_pair;
+  const double2* __restrict__ tab = T.e_ab;
+  const int n = T.ne_pair;
+  for (int k0 = tid; k0 < n; k0 += 4 * kThreads) {
+    uint32_t w[4];
+    double sc[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int k = k0 + u * kThreads;
+      const bool live = k < n;
+      w[u] = __ldg(list + (live ? k : k0));  // a padding slot re-reads a valid pair with weight 0
+      sc[u] = live ? kElecFactorD : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) epair<MODE, PBC>(C, tab, w[u], sc[u], el[u], lj[u]);
+  }
+  eel = (el[0] + el[1]) + (el[2] + el[3]);
+  elj = (lj[0] + lj[1]) + (lj[2] + lj[3]);
+}
+
 template <int MODE>
 __device__ __noinline__ void energy_pass(const Smem& S, const DevTopo& T, const ForceParams& P, bool pbc, int tid, Energies& E) {
   double eel = 0.0, elj = 0.0, ebond = 0.0, eang = 0.0, edih = 0.0, eimp = 0.0;
-  // ---- non-bonded pairs = Forces.ava_idx (forces.py:258-316); the row-major list keeps i warp-uniform and j consecutive
   if (P.terms & (B200MD_T_ELECTROSTATICS | B200MD_T_LJ | B200MD_T_REPULSION | B200MD_T_REPULSIONCG)) {
-    const double ta = (double)P.tab_a, tb = (double)P.tab_b, rc2 = P.rc_d * P.rc_d;
-    for (int k = tid; k < T.ne_pair; k += kThreads) {
-      const uint32_t w = __ldg(T.e_pair + k);
-      const int i = w & 0xff, j = (w >> 8) & 0xff;
-      const dv3 d = ediff(S, pbc, i, j);
-      const double r2 = edot(d, d);
-      if (MODE == 1 && !(r2 <= rc2)) continue;  // _filter_by_cutoff, forces.py:75-80
-      const double rinv = rsqrt(r2), r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
-      const double2 ab = __ldg(T.e_ab + (w >> 16));
-      const double qq = kElecFactorD * S.pd[3 * kMaxAtoms + i] * S.pd[3 * kMaxAtoms + j];
-      double lj = (ta * ab.x * r6 + tb * ab.y) * r6;  // lj: A r^-12 - B r^-6; repulsion: A r^-12; repulsioncg: B r^-6
-      if (MODE == 1) {
-        const double r = r2 * rinv;
-        if (r > P.rs_d) {  // forces.py:401-411 (rs_d = +inf without a switch)
-          const double t = (r - P.rs_d) * P.inv_sw_d;
-          lj *= 1.0 + t * t * t * (-10.0 + t * (15.0 - t * 6.0));
-        }
-        eel += qq * (rinv + P.krf_d * r2 - P.crf_d);  // forces.py:476 (krf = crf = 0 without rfa)
-      } else {
-        eel += qq * rinv;
-      }
-      elj += lj;
-    }
+    EPairConst C;
+    C.pd = (uint32_t)__cvta_generic_to_shared(S.pd);
+    C.ta = (double)P.tab_a; C.tb = (double)P.tab_b; C.rs = P.rs_d; C.inv_sw = P.inv_sw_d; C.rc2 = P.rc_d * P.rc_d;
+    C.krf = P.krf_d; C.ncrf = -P.crf_d;
+    C.bx = -(double)S.box[0]; C.by = -(double)S.box[1]; C.bz = -(double)S.box[2];
+    if (pbc) epair_loop<MODE, true>(C, T, tid, eel, elj);
+    else epair_loop<MODE, false>(C, T, tid, eel, elj);
   }
   // ---- 1-4 pairs (forces.py:176-226): never cut, switched or reaction-field corrected
   if (T.p14_on) {
@@ -670,8 +737,8 @@ __device__ __noinline__ void energy_pass(const Smem& S, const DevTopo& T, const 
     for (int k = tid; k < T.ne_14; k += kThreads) {
       const uint32_t w = __ldg(T.e14_idx + k);
       const dv3 d = ediff(S, pbc, w & 0xff, (w >> 8) & 0xff);
-      const double r2 = edot(d, d), rinv = rsqrt(r2), r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
-      elj += ljon * (__ldg(T.e14_prm + 3 * k) * r6 - __ldg(T.e14_prm + 3 * k + 1)) * r6;
+      const double r2 = edot(d, d), rinv = drsqrt(r2), r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
+      elj += ljon * fma(__ldg(T.e14_prm + 3 * k), r6, -__ldg(T.e14_prm + 3 * k + 1)) * r6;
       eel += elon * __ldg(T.e14_prm + 3 * k + 2) * rinv;
     }
   }
@@ -681,10 +748,10 @@ __device__ __noinline__ void energy_pass(const Smem& S, const DevTopo& T, const 
       const uint32_t w = __ldg(T.eb_idx + k);
       const float2 kp = __ldg(T.eb_prm + k);
       const dv3 d = ediff(S, pbc, w & 0xff, (w >> 8) & 0xff);
-      const double dist = sqrt(edot(d, d));
-      if (P.has_cutoff && !(dist <= P.rc_d)) continue;
+      const double r2 = edot(d, d), dist = r2 * drsqrt(r2);
       const double x = dist - (double)kp.y;
-      ebond += (double)kp.x * x * x;
+      const bool keep = !P.has_cutoff || dist <= P.rc_d;
+      ebond += keep ? (double)kp.x * x * x : 0.0;
     }
   }
   // ---- angles (forces.py:134-145, 504-518)
@@ -694,7 +761,7 @@ __device__ __noinline__ void energy_pass(const Smem& S, const DevTopo& T, const 
       const float2 kp = __ldg(T.ea_prm + k);
       const int a1 = (w >> 8) & 0xff;
       const dv3 r21 = ediff(S, pbc, w & 0xff, a1), r23 = ediff(S, pbc, (w >> 16) & 0xff, a1);
-      double ct = edot(r23, r21) * rsqrt(edot(r21, r21)) * rsqrt(edot(r23, r23));
+      double ct = edot(r23, r21) * drsqrt(edot(r21, r21)) * drsqrt(edot(r23, r23));
       ct = ct < -1.0 ? -1.0 : (ct > 1.0 ? 1.0 : ct);
       const double dth = acos(ct) - (double)kp.y;
       eang += (double)kp.x * dth * dth;

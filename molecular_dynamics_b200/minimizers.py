@@ -4,8 +4,8 @@
 ``torchmd.minimizers.minimize_bfgs``: scipy L-BFGS-B over the coordinates of ONE replica, gradients from
 ``forces.compute``).  ``minimize_fire(system, forces, ...)`` is the batched form for thousands of replicas: FIRE
 (Bitzek et al., PRL 97, 170201) with per-replica time step and mixing, one ``Forces.compute_batch`` launch per
-iteration, state and arithmetic on the GPU — the tool to relax perturbed conformers before a batched MD run.
-Host plumbing (torch ops), not a kernel: the force evaluation is the hot part and is the CUDA path.
+iteration and one fused update kernel (``b200md_fire_update``, csrc/b200md_minimize.cuh) -- the tool to relax
+perturbed conformers before a batched MD run.
 """
 from __future__ import annotations
 
@@ -36,38 +36,43 @@ def minimize_bfgs(system, forces, fmax=0.5, steps=1000):
 
 
 def minimize_fire(system, forces, steps=1000, fmax=0.5, dt_start=0.02, dt_max=0.2, max_move=0.1, n_min=5, f_inc=1.1,
-                  f_dec=0.5, alpha_start=0.1, f_alpha=0.99):
+                  f_dec=0.5, alpha_start=0.1, f_alpha=0.99, check_every=10):
     """Batched FIRE on every replica of ``system`` (in place).  Stops when max |F| <= fmax (kcal/mol/A) on all replicas
-    or after ``steps`` force evaluations.  Returns dict(epot (R,), fmax (R,), iterations)."""
-    pos = system.pos
-    R = pos.shape[0]
+    or after ``steps`` force evaluations.  Returns dict(epot (R,), fmax (R,), iterations).
+
+    Two launches per iteration and nothing else: ``b200md_fire_update`` (one kernel: the per-replica reductions F.v,
+    |v|, |F|, max|F|, the time-step / mixing logic, velocity and position update with the displacement cap) and a
+    force-only ``Forces.compute_batch``.  The convergence flag (per-replica max|F|, left on the device by the update
+    kernel) is read every ``check_every`` iterations instead of every one -- the only host synchronisation of the loop;
+    energies are evaluated once, at the end."""
+    import ctypes as C
+
+    from . import _cabi
+
+    pos, frc = system.pos, system.forces
+    if not pos.is_cuda or pos.dtype != torch.float32 or not pos.is_contiguous() or not frc.is_contiguous():
+        raise RuntimeError("minimize_fire needs contiguous float32 CUDA tensors in System.pos / System.forces")
+    R, N, _ = pos.shape
     dev = pos.device
-    frc = system.forces
+    lib = _cabi.load_library()
     vel = torch.zeros_like(pos)
-    dt = torch.full((R, 1, 1), dt_start, device=dev, dtype=pos.dtype)
-    alpha = torch.full((R, 1, 1), alpha_start, device=dev, dtype=pos.dtype)
-    npos = torch.zeros((R, 1, 1), device=dev, dtype=pos.dtype)
-    ene = forces.compute_batch(pos, system.box, frc)
+    state = torch.zeros((R, 4), dtype=torch.float32, device=dev)
+    state[:, 0], state[:, 1] = dt_start, alpha_start
+    opts = _cabi.FireOpts(dt_max, max_move, f_inc, f_dec, alpha_start, f_alpha, int(n_min))
+    forces.compute_batch(pos, system.box, frc, energies=False)
     it = 0
-    for it in range(1, steps + 1):
-        fnorm = frc.flatten(1).norm(dim=1).clamp_min(1e-30).view(R, 1, 1)
-        if float(frc.abs().amax()) <= fmax:
+    index = dev.index if dev.index is not None else torch.cuda.current_device()
+    while it < steps:
+        rc = lib.b200md_fire_update(index, R, N, C.c_void_p(pos.data_ptr()), C.c_void_p(vel.data_ptr()), C.c_void_p(frc.data_ptr()),
+                                    C.c_void_p(state.data_ptr()), C.byref(opts), C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+        if rc != _cabi.OK:
+            raise RuntimeError(f"b200md error {rc}: {_cabi.last_error()}")
+        it += 1
+        if it % check_every == 0 and float(state[:, 3].max()) <= fmax:
+            # state[:, 3] is max|F| of the forces the update just consumed: converged one iteration ago -- the move it made
+            # from there is downhill by construction, keep it
+            forces.compute_batch(pos, system.box, frc, energies=False)
             break
-        power = (frc * vel).flatten(1).sum(1).view(R, 1, 1)
-        vnorm = vel.flatten(1).norm(dim=1).view(R, 1, 1)
-        vel = (1.0 - alpha) * vel + alpha * frc * (vnorm / fnorm)
-        up = power > 0
-        npos = torch.where(up, npos + 1, torch.zeros_like(npos))
-        grow = up & (npos > n_min)
-        dt = torch.where(grow, (dt * f_inc).clamp_max(dt_max), dt)
-        alpha = torch.where(grow, alpha * f_alpha, alpha)
-        dt = torch.where(up, dt, dt * f_dec)
-        alpha = torch.where(up, alpha, torch.full_like(alpha, alpha_start))
-        vel = torch.where(up, vel, torch.zeros_like(vel))
-        vel = vel + dt * frc
-        step = dt * vel
-        smax = step.flatten(1).abs().amax(1).view(R, 1, 1)
-        step = step * (max_move / smax.clamp_min(max_move))  # no atom moves more than max_move per iteration
-        pos += step
-        ene = forces.compute_batch(pos, system.box, frc)
+        forces.compute_batch(pos, system.box, frc, energies=False)
+    ene = forces.compute_batch(pos, system.box, frc)
     return {"epot": ene.sum(1), "fmax": frc.flatten(1).abs().amax(1), "iterations": it}

@@ -1235,7 +1235,7 @@ class _ToyExternal:
 
 def test_generic_external_object_in_compute_autograd_and_integrator():
     g = load_golden("bb40")
-    pos0 = g["pos"][:3]
+    pos0 = np.ascontiguousarray(g["frames"][:3], dtype=np.float32)
     k = 0.05
     # compute: energy in the "external" column, force added (forces.py:318-323)
     F = Forces(gpu_par(g), external=_ToyExternal(k))
@@ -1336,3 +1336,43 @@ def test_library_calls_leave_the_current_device_alone():
     assert torch.cuda.current_device() == 0
     f_ref, e_ref = oracle.forces(g.packed, g["pos"])
     check_energies(e.cpu().numpy(), e_ref, "cuda:1")
+
+
+def test_fire_update_kernel_vs_restatement():
+    """the fused FIRE update kernel (b200md_fire_update) against its FP64 restatement (oracle/fire_reference.py),
+    iteration by iteration on the same force field: 25 iterations from perturbed ALA10 conformers, including uphill
+    steps (velocity reset, time-step cut) and capped displacements."""
+    import ctypes as C
+
+    import bench
+    from oracle.fire_reference import fire_update
+
+    g = load_golden("ala10")
+    R = 8
+    pos0, _ = bench.synth_inputs(bench.load_ala10(), R)
+    par, s = make_system(g, pos0, np.zeros_like(pos0))
+    F = Forces(par)
+    lib = _cabi.load_library()
+    opts = _cabi.FireOpts(0.2, 0.1, 1.1, 0.5, 0.1, 0.99, 5)
+    vel = torch.zeros_like(s.pos)
+    state = torch.zeros((R, 4), dtype=torch.float32, device=DEV)
+    state[:, 0], state[:, 1] = 0.05, 0.1
+    x, v = pos0.astype(np.float64), np.zeros(pos0.shape)
+    dt, alpha, npos = np.full(R, 0.05), np.full(R, 0.1), np.zeros(R)
+    sr = System(104, R, torch.float, DEV)
+    ups = 0
+    for it in range(25):
+        F.compute_batch(s.pos, s.box, s.forces, energies=False)
+        rc = lib.b200md_fire_update(0, R, 104, C.c_void_p(s.pos.data_ptr()), C.c_void_p(vel.data_ptr()), C.c_void_p(s.forces.data_ptr()),
+                                    C.c_void_p(state.data_ptr()), C.byref(opts), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        assert rc == _cabi.OK, _cabi.last_error()
+        sr.pos[:] = torch.tensor(x.astype(np.float32), device=DEV)
+        F.compute_batch(sr.pos, sr.box, sr.forces, energies=False)
+        x, v, dt, alpha, npos = fire_update(x, v, sr.forces.cpu().numpy().astype(np.float64), dt, alpha, npos)
+        st = state.cpu().numpy()
+        ups += int((npos == 0).sum())
+        np.testing.assert_allclose(st[:, 0], dt, rtol=1e-5)
+        np.testing.assert_allclose(st[:, 1], alpha, rtol=1e-5)
+        np.testing.assert_array_equal(st[:, 2], npos)
+        assert np.abs(s.pos.cpu().numpy() - x).max() < 2e-4, it
+    assert ups > 0  # the comparison saw uphill resets
