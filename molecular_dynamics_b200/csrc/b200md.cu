@@ -60,13 +60,12 @@ __device__ __forceinline__ void stage_pd(const Smem& S, int tid, float x, float 
   S.pd[3 * kMaxAtoms + tid] = (double)q;
 }
 
-// Forces.compute (forces.py:82-344) for a batch of replicas: one CTA per replica (grid-stride).
-// energies == nullptr: forces only (the autograd backward and compute_batch(..., energies=False)).
+// Forces.compute (forces.py:82-344), the FORCES of a batch of replicas: one CTA per replica (grid-stride).  The energies
+// are a kernel of their own (energy_kernel below), launched behind this one when the caller wants them.
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 4)
 forces_kernel(const DevTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
-              const float* __restrict__ box, float* __restrict__ forces, double* __restrict__ energies,
-              uint32_t* __restrict__ status) {
+              const float* __restrict__ box, float* __restrict__ forces, uint32_t* __restrict__ status) {
   extern __shared__ __align__(16) char smem_raw[];
   Smem S;
   smem_layout(&S, smem_raw, T.ntypes, T.nslots, false);
@@ -119,18 +118,53 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
       float* f = forces + (r * N + tid) * 3;
       f[0] = fx; f[1] = fy; f[2] = fz;
     }
-    if (energies != nullptr) {  // FP64 energy pass; S.sx is free from here on (the force tasks are done)
-      stage_pd(S, tid, x, y, z, tid < N ? q : 0.0f);
-      __syncthreads();
-      Energies E;
-      E.clear();
-      energy_pass<MODE>(S, T, P, pbc, tid, E);
-      if (P.smd_on && tid == 0) E.e[B200MD_E_EXTERNAL] += S.smd_energy[0];
-      reduce_energies<B200MD_NUM_ENERGIES>(S, E, warp, lane);
-      if (tid == 0) {
+  }
+}
+
+// The ENERGIES of Forces.compute (forces.py:82-344) for a batch of replicas, every term in FP64 from the fp32 positions
+// (energy_pass_impl, b200md_forces.cuh): one CTA per replica (grid-stride), positions converted to double in shared
+// memory once, item lists read through L1.  A kernel of its own rather than a tail of forces_kernel: it wants what that
+// kernel cannot give -- 4 KB of shared memory per CTA, so that the ~40 KB of item lists stay L1-resident (beside
+// forces_kernel's 4 x 52 KB of shared memory the unified L1 keeps 20 KB and every list read went to L2: 2.9 stall cycles
+// per issue on the long scoreboard, profiles/r02_forces_kernel.md), and twice the resident warps to cover the FP64
+// dependency chains.  FP64-pipe bound (B200: 64 DFMA / clock / SM).
+template <int MODE>
+__global__ void __launch_bounds__(kThreads, 6)
+energy_kernel(const DevTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
+              const float* __restrict__ box, double* __restrict__ energies) {
+  __shared__ __align__(16) double spd[4 * kMaxAtoms];
+  __shared__ double sered[kWarps * kNumReduced];
+  __shared__ float sbox[8];
+  Smem S{};
+  S.pd = spd; S.ered = sered; S.box = sbox;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, N = T.natoms;
+  const float q = tid < N ? __ldg(T.charge + tid) * P.el_on : 0.0f;
+  for (long long r = blockIdx.x; r < R; r += gridDim.x) {
+    float x = 0.f, y = 0.f, z = 0.f;
+    if (tid < N) {
+      const float* p = pos + (r * N + tid) * 3;
+      x = __ldg(p); y = __ldg(p + 1); z = __ldg(p + 2);
+    }
+    const float b0 = box ? __ldg(box + r * 9) : 0.0f, b1 = box ? __ldg(box + r * 9 + 4) : 0.0f, b2 = box ? __ldg(box + r * 9 + 8) : 0.0f;
+    const bool pbc = b0 != 0.0f || b1 != 0.0f || b2 != 0.0f;
+    __syncthreads();  // the previous replica's reads of spd / sered are done
+    stage_pd(S, tid, x, y, z, q);
+    if (tid < 3) sbox[tid] = -(tid == 0 ? b0 : (tid == 1 ? b1 : b2));
+    __syncthreads();
+    Energies E;
+    E.clear();
+    energy_pass_impl<MODE>(S, T, P, pbc, tid, E);
+    if (P.smd_on && tid == 0) {  // potcalc.py:75-89, as smd_task evaluates it for the force
+      const float center = P.smd_centers ? __ldg(P.smd_centers + r) : P.smd_c0;
+      const double dx = spd[P.smd_a2] - spd[P.smd_a1], dy = spd[kMaxAtoms + P.smd_a2] - spd[kMaxAtoms + P.smd_a1],
+                   dz = spd[2 * kMaxAtoms + P.smd_a2] - spd[2 * kMaxAtoms + P.smd_a1];
+      const double dev = (double)center - sqrt(dx * dx + dy * dy + dz * dz);
+      E.e[B200MD_E_EXTERNAL] += 0.5 * (double)P.smd_fk * dev * dev;
+    }
+    reduce_energies<B200MD_NUM_ENERGIES>(S, E, warp, lane);
+    if (tid == 0) {
 #pragma unroll
-        for (int k = 0; k < B200MD_NUM_ENERGIES; ++k) energies[r * B200MD_NUM_ENERGIES + k] = E.e[k];
-      }
+      for (int k = 0; k < B200MD_NUM_ENERGIES; ++k) energies[r * B200MD_NUM_ENERGIES + k] = E.e[k];
     }
   }
 }
@@ -520,7 +554,7 @@ struct b200md_topology {
   DevTopo dev{};
   void* blob = nullptr;
   std::vector<uint32_t> mask_rows;  // [natoms][4], bit j set <=> pair (i, j) not evaluated
-  int occ_forces[2] = {0, 0}, occ_integrate[2] = {0, 0};
+  int occ_forces[2] = {0, 0}, occ_integrate[2] = {0, 0}, occ_energy[2] = {1, 1};
   // solutes above 128 atoms (b200md_large.cuh): the per-replica state no longer fits one CTA
   bool large = false;
   LargeTopo ldev{};
@@ -1152,6 +1186,8 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
   topo->num_sms = prop.multiProcessorCount;
   topo->occ_forces[0] = query_occupancy(forces_kernel<0>, T.smem_bytes);
   topo->occ_forces[1] = query_occupancy(forces_kernel<1>, T.smem_bytes);
+  topo->occ_energy[0] = std::max(1, query_occupancy(energy_kernel<0>, 0));
+  topo->occ_energy[1] = std::max(1, query_occupancy(energy_kernel<1>, 0));
   topo->occ_integrate[0] = query_occupancy(integrate_kernel<0, false>, T.smem_bytes_fixed);
   topo->occ_integrate[1] = query_occupancy(integrate_kernel<1, false>, T.smem_bytes_fixed);
   query_occupancy(integrate_kernel<0, true>, T.smem_bytes_fixed);  // also raises the dynamic shared-memory limit
@@ -1553,10 +1589,16 @@ extern "C" int b200md_forces_compute(const b200md_topology* topo, const b200md_f
   const int grid = (int)std::min<long long>(R, cap);
   cudaStream_t st = (cudaStream_t)stream;
   if (mode == 0)
-    forces_kernel<0><<<grid, kThreads, T.smem_bytes, st>>>(T, P, R, pos, box, forces, energies, status);
+    forces_kernel<0><<<grid, kThreads, T.smem_bytes, st>>>(T, P, R, pos, box, forces, status);
   else
-    forces_kernel<1><<<grid, kThreads, T.smem_bytes, st>>>(T, P, R, pos, box, forces, energies, status);
+    forces_kernel<1><<<grid, kThreads, T.smem_bytes, st>>>(T, P, R, pos, box, forces, status);
   g_launches.fetch_add(1);
+  if (energies != nullptr) {  // FP64 energies: a second kernel on the same stream (energy_kernel)
+    const int egrid = (int)std::min<long long>(R, (long long)topo->num_sms * topo->occ_energy[mode]);
+    if (mode == 0) energy_kernel<0><<<egrid, kThreads, 0, st>>>(T, P, R, pos, box, energies);
+    else energy_kernel<1><<<egrid, kThreads, 0, st>>>(T, P, R, pos, box, energies);
+    g_launches.fetch_add(1);
+  }
   CUDA_TRY(cudaGetLastError());
   return B200MD_OK;
 }

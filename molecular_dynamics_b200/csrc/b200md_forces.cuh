@@ -591,16 +591,28 @@ __device__ __forceinline__ double drsqrt(double x) {
   return fma(y, e * fma(0.375, e, 0.5), y);
 }
 
+// Shared-memory double load by 32-bit shared address: inside the (not inlined) energy pass the compiler cannot prove
+// that S.pd points to shared memory and would emit generic LD instead of LDS.
+__device__ __forceinline__ double lds_f64(uint32_t saddr, int idx) {
+  double v;
+  asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(saddr + 8u * (uint32_t)idx));
+  return v;
+}
+struct EPairConst {  // loop invariants of the pair loop, in registers
+  uint32_t pd;       // shared address of S.pd
+  double ta, tb, rs, inv_sw, rc2, krf, ncrf, bx, by, bz;
+};
+
 struct dv3 { double x, y, z; };
 // calculate_distances (forces.py:366-370) in double; `pbc` is uniform over the CTA (one replica), so a run-time flag costs
 // a predictable branch instead of a second copy of the FP64 code
-__device__ __forceinline__ dv3 ediff(const Smem& S, bool pbc, int i, int j) {
-  dv3 d = {S.pd[i] - S.pd[j], S.pd[kMaxAtoms + i] - S.pd[kMaxAtoms + j], S.pd[2 * kMaxAtoms + i] - S.pd[2 * kMaxAtoms + j]};
-  if (pbc) {  // wrap_dist, forces.py:358-363 (S.box holds -box; a zero entry leaves its axis alone)
-    const double bx = -(double)S.box[0], by = -(double)S.box[1], bz = -(double)S.box[2];
-    if (bx != 0.0) d.x -= bx * rint(d.x / bx);
-    if (by != 0.0) d.y -= by * rint(d.y / by);
-    if (bz != 0.0) d.z -= bz * rint(d.z / bz);
+__device__ __forceinline__ dv3 ediff(const EPairConst& C, bool pbc, int i, int j) {
+  dv3 d = {lds_f64(C.pd, i) - lds_f64(C.pd, j), lds_f64(C.pd, kMaxAtoms + i) - lds_f64(C.pd, kMaxAtoms + j),
+           lds_f64(C.pd, 2 * kMaxAtoms + i) - lds_f64(C.pd, 2 * kMaxAtoms + j)};
+  if (pbc) {  // wrap_dist, forces.py:358-363; a zero box entry leaves its axis alone
+    if (C.bx != 0.0) d.x -= C.bx * rint(d.x / C.bx);
+    if (C.by != 0.0) d.y -= C.by * rint(d.y / C.by);
+    if (C.bz != 0.0) d.z -= C.bz * rint(d.z / C.bz);
   }
   return d;
 }
@@ -611,15 +623,17 @@ __device__ __forceinline__ dv3 ecross(dv3 a, dv3 b) {
 
 // evaluate_torsion (forces.py:540-576), energy only.  Integer-periodicity AMBER terms never form phi: cos / sin(n phi)
 // come from (cos phi + i sin phi)^n, cos / sin(phi0) from the host in FP64.
-__device__ __noinline__ double etorsion(const Smem& S, const DevTopo& T, bool pbc, int d) {
+__device__ __forceinline__ double etorsion(const EPairConst& C, const DevTopo& T, bool pbc, int d) {
   const uint32_t q = __ldg(T.et_idx + d);
   const int a0 = q & 0xff, a1 = (q >> 8) & 0xff, a2 = (q >> 16) & 0xff, a3 = q >> 24;
-  const dv3 r12 = ediff(S, pbc, a0, a1), r23 = ediff(S, pbc, a1, a2), r34 = ediff(S, pbc, a2, a3);
-  const dv3 cA = ecross(r12, r23), cB = ecross(r23, r34), cC = ecross(r23, cA);
-  const double inA = drsqrt(edot(cA, cA)), inB = drsqrt(edot(cB, cB)), inC = drsqrt(edot(cC, cC));
-  const double cosPhi = edot(cA, cB) * inB * inA, sinPhi = edot(cC, cB) * inB * inC;  // forces.py:548-551
-  const double hinv = drsqrt(fma(cosPhi, cosPhi, sinPhi * sinPhi));
-  const double c1 = cosPhi * hinv, s1 = -sinPhi * hinv;  // cos / sin of phi = -atan2(sinPhi, cosPhi)
+  const dv3 r12 = ediff(C, pbc, a0, a1), r23 = ediff(C, pbc, a1, a2), r34 = ediff(C, pbc, a2, a3);
+  const dv3 cA = ecross(r12, r23), cB = ecross(r23, r34);
+  // forces.py:548-551: cosPhi = A.B / (|A||B|), sinPhi = C.B / (|C||B|) with C = r23 x A.  r23 is perpendicular to A, so
+  // |C| = |r23||A| and C.B = |r23|^2 (r12.B): sinPhi = |r23| (r12.B) / (|A||B|) -- the same numbers to 1e-16 without the
+  // third cross product, its norm and a renormalisation
+  const double n23sq = edot(r23, r23), iab = drsqrt(edot(cA, cA)) * drsqrt(edot(cB, cB));
+  const double cosPhi = edot(cA, cB) * iab, sinPhi = n23sq * drsqrt(n23sq) * edot(r12, cB) * iab;
+  const double c1 = cosPhi, s1 = -sinPhi;  // cos / sin of phi = -atan2(sinPhi, cosPhi)
   double phi = 0.0, pot = 0.0;
   bool have_phi = false;
   const int t1 = __ldg(T.et_start + d + 1);
@@ -648,18 +662,6 @@ __device__ __noinline__ double etorsion(const Smem& S, const DevTopo& T, bool pb
   }
   return pot;
 }
-
-// Shared-memory double load by 32-bit shared address: inside the (not inlined) energy pass the compiler cannot prove
-// that S.pd points to shared memory and would emit generic LD instead of LDS.
-__device__ __forceinline__ double lds_f64(uint32_t saddr, int idx) {
-  double v;
-  asm("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(saddr + 8u * (uint32_t)idx));
-  return v;
-}
-struct EPairConst {  // loop invariants of the pair loop, in registers
-  uint32_t pd;       // shared address of S.pd
-  double ta, tb, rs, inv_sw, rc2, krf, ncrf, bx, by, bz;
-};
 
 // One non-bonded pair of Forces.ava_idx in double (forces.py:379-413, 451-489): (electrostatics, lj-family) energies.
 // Straight-line (selects, no branches): the caller unrolls four of these so that their dependency chains overlap.
@@ -720,14 +722,14 @@ __device__ __forceinline__ void epair_loop(const EPairConst& C, const DevTopo& T
 }
 
 template <int MODE>
-__device__ __noinline__ void energy_pass(const Smem& S, const DevTopo& T, const ForceParams& P, bool pbc, int tid, Energies& E) {
+__device__ __forceinline__ void energy_pass_impl(const Smem& S, const DevTopo& T, const ForceParams& P, bool pbc, int tid, Energies& E) {
   double eel = 0.0, elj = 0.0, ebond = 0.0, eang = 0.0, edih = 0.0, eimp = 0.0;
+  EPairConst C;
+  C.pd = (uint32_t)__cvta_generic_to_shared(S.pd);
+  C.ta = (double)P.tab_a; C.tb = (double)P.tab_b; C.rs = P.rs_d; C.inv_sw = P.inv_sw_d; C.rc2 = P.rc_d * P.rc_d;
+  C.krf = P.krf_d; C.ncrf = -P.crf_d;
+  C.bx = -(double)S.box[0]; C.by = -(double)S.box[1]; C.bz = -(double)S.box[2];
   if (P.terms & (B200MD_T_ELECTROSTATICS | B200MD_T_LJ | B200MD_T_REPULSION | B200MD_T_REPULSIONCG)) {
-    EPairConst C;
-    C.pd = (uint32_t)__cvta_generic_to_shared(S.pd);
-    C.ta = (double)P.tab_a; C.tb = (double)P.tab_b; C.rs = P.rs_d; C.inv_sw = P.inv_sw_d; C.rc2 = P.rc_d * P.rc_d;
-    C.krf = P.krf_d; C.ncrf = -P.crf_d;
-    C.bx = -(double)S.box[0]; C.by = -(double)S.box[1]; C.bz = -(double)S.box[2];
     if (pbc) epair_loop<MODE, true>(C, T, tid, eel, elj);
     else epair_loop<MODE, false>(C, T, tid, eel, elj);
   }
@@ -736,7 +738,7 @@ __device__ __noinline__ void energy_pass(const Smem& S, const DevTopo& T, const 
     const double ljon = (double)P.lj_on, elon = (double)P.el_on;
     for (int k = tid; k < T.ne_14; k += kThreads) {
       const uint32_t w = __ldg(T.e14_idx + k);
-      const dv3 d = ediff(S, pbc, w & 0xff, (w >> 8) & 0xff);
+      const dv3 d = ediff(C, pbc, w & 0xff, (w >> 8) & 0xff);
       const double r2 = edot(d, d), rinv = drsqrt(r2), r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
       elj += ljon * fma(__ldg(T.e14_prm + 3 * k), r6, -__ldg(T.e14_prm + 3 * k + 1)) * r6;
       eel += elon * __ldg(T.e14_prm + 3 * k + 2) * rinv;
@@ -747,7 +749,7 @@ __device__ __noinline__ void energy_pass(const Smem& S, const DevTopo& T, const 
     for (int k = tid; k < T.ne_bond; k += kThreads) {
       const uint32_t w = __ldg(T.eb_idx + k);
       const float2 kp = __ldg(T.eb_prm + k);
-      const dv3 d = ediff(S, pbc, w & 0xff, (w >> 8) & 0xff);
+      const dv3 d = ediff(C, pbc, w & 0xff, (w >> 8) & 0xff);
       const double r2 = edot(d, d), dist = r2 * drsqrt(r2);
       const double x = dist - (double)kp.y;
       const bool keep = !P.has_cutoff || dist <= P.rc_d;
@@ -760,7 +762,7 @@ __device__ __noinline__ void energy_pass(const Smem& S, const DevTopo& T, const 
       const uint32_t w = __ldg(T.ea_idx + k);
       const float2 kp = __ldg(T.ea_prm + k);
       const int a1 = (w >> 8) & 0xff;
-      const dv3 r21 = ediff(S, pbc, w & 0xff, a1), r23 = ediff(S, pbc, (w >> 16) & 0xff, a1);
+      const dv3 r21 = ediff(C, pbc, w & 0xff, a1), r23 = ediff(C, pbc, (w >> 16) & 0xff, a1);
       double ct = edot(r23, r21) * drsqrt(edot(r21, r21)) * drsqrt(edot(r23, r23));
       ct = ct < -1.0 ? -1.0 : (ct > 1.0 ? 1.0 : ct);
       const double dth = acos(ct) - (double)kp.y;
@@ -771,12 +773,19 @@ __device__ __noinline__ void energy_pass(const Smem& S, const DevTopo& T, const 
   {
     const int k0 = T.dih_on ? 0 : T.ne_dih, k1 = T.gen_end > T.nspec ? T.ne_dih + T.ne_imp : T.ne_dih;  // enabled kinds
     for (int k = k0 + tid; k < k1; k += kThreads) {
-      const double e = etorsion(S, T, pbc, k);
+      const double e = etorsion(C, T, pbc, k);
       if (k < T.ne_dih) edih += e; else eimp += e;
     }
   }
   E.e[B200MD_E_ELECTROSTATICS] += eel; E.e[B200MD_E_LJ] += elj; E.e[B200MD_E_BONDS] += ebond;
   E.e[B200MD_E_ANGLES] += eang; E.e[B200MD_E_DIHEDRALS] += edih; E.e[B200MD_E_IMPROPERS] += eimp;
+}
+
+// Inside the fused integrator the pass runs on report steps only: a call keeps its code (FP64 transcendentals) out of
+// the hot instruction stream.  energy_kernel (b200md.cu) inlines energy_pass_impl instead.
+template <int MODE>
+__device__ __noinline__ void energy_pass(const Smem& S, const DevTopo& T, const ForceParams& P, bool pbc, int tid, Energies& E) {
+  energy_pass_impl<MODE>(S, T, P, pbc, tid, E);
 }
 
 // ---- all tasks of this warp for one force evaluation; positions must be in S.pos ------------------
