@@ -131,7 +131,8 @@ forces_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 6)
 energy_kernel(const DevTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
-              const float* __restrict__ box, double* __restrict__ energies) {
+              const float* __restrict__ box, const long long box_mod, double* __restrict__ energies, const int estride,
+              const int nslots) {
   __shared__ __align__(16) double spd[4 * kMaxAtoms];
   __shared__ double sered[kWarps * kNumReduced];
   __shared__ float sbox[8];
@@ -145,7 +146,8 @@ energy_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
       const float* p = pos + (r * N + tid) * 3;
       x = __ldg(p); y = __ldg(p + 1); z = __ldg(p + 2);
     }
-    const float b0 = box ? __ldg(box + r * 9) : 0.0f, b1 = box ? __ldg(box + r * 9 + 4) : 0.0f, b2 = box ? __ldg(box + r * 9 + 8) : 0.0f;
+    const long long rb = r % box_mod;  // records of the fused integrator: record (slot, replica) uses the replica's box
+    const float b0 = box ? __ldg(box + rb * 9) : 0.0f, b1 = box ? __ldg(box + rb * 9 + 4) : 0.0f, b2 = box ? __ldg(box + rb * 9 + 8) : 0.0f;
     const bool pbc = b0 != 0.0f || b1 != 0.0f || b2 != 0.0f;
     __syncthreads();  // the previous replica's reads of spd / sered are done
     stage_pd(S, tid, x, y, z, q);
@@ -154,7 +156,7 @@ energy_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
     Energies E;
     E.clear();
     energy_pass_impl<MODE>(S, T, P, pbc, tid, E);
-    if (P.smd_on && tid == 0) {  // potcalc.py:75-89, as smd_task evaluates it for the force
+    if (P.smd_on && tid == 0 && nslots == B200MD_NUM_ENERGIES) {  // potcalc.py:75-89, as smd_task evaluates it for the force
       const float center = P.smd_centers ? __ldg(P.smd_centers + r) : P.smd_c0;
       const double dx = spd[P.smd_a2] - spd[P.smd_a1], dy = spd[kMaxAtoms + P.smd_a2] - spd[kMaxAtoms + P.smd_a1],
                    dz = spd[2 * kMaxAtoms + P.smd_a2] - spd[2 * kMaxAtoms + P.smd_a1];
@@ -164,7 +166,8 @@ energy_kernel(const DevTopo T, const ForceParams P, const long long R, const flo
     reduce_energies<B200MD_NUM_ENERGIES>(S, E, warp, lane);
     if (tid == 0) {
 #pragma unroll
-      for (int k = 0; k < B200MD_NUM_ENERGIES; ++k) energies[r * B200MD_NUM_ENERGIES + k] = E.e[k];
+      for (int k = 0; k < B200MD_NUM_ENERGIES; ++k)
+        if (k < nslots) energies[r * estride + k] = E.e[k];
     }
   }
 }
@@ -302,22 +305,45 @@ integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const
         const float4 vv = S.vel[tid];
         vx = vv.x; vy = vv.y; vz = vv.z;
       }
-      if (report) {  // FP64 energies of x(t + dt): the parked velocities and the SoA copy are dead until the next step
-        __syncthreads();  // every thread has read its S.vel entry
-        stage_pd(S, tid, x, y, z, live ? q : 0.0f);
-        __syncthreads();
-        Energies E;
-        E.clear();
-        energy_pass<MODE>(S, T, P, pbc, tid, E);
-        if (live) E.e[B200MD_OBS_EKIN] = 0.5 * (double)mass * ((double)vx * vx + (double)vy * vy + (double)vz * vz);
-        if (P.smd_on && tid == 0) { E.e[B200MD_E_EXTERNAL] += S.smd_energy[0]; E.e[B200MD_OBS_E2E_DIST] = (double)S.smd[4]; }
-        reduce_energies<kNumReduced>(S, E, warp, lane);
-        if (tid == 0 && observables != nullptr) {
-          const long long slot = I.energy_every > 0 ? s / I.energy_every : 0;
-          double* o = observables + (slot * R + r) * B200MD_NUM_OBSERVABLES;
+      if (report) {
+        const long long slot = I.energy_every > 0 ? s / I.energy_every : 0;
+        if (I.report_pos != nullptr) {
+          // Deferred energies: the record's positions go to HBM (coalesced, 1 248 B) and energy_kernel evaluates the seven
+          // force-field terms of every record behind this launch, at its own occupancy and with L1-resident item lists.
+          // Here only what needs the velocities or the restraint state: Ekin (fixed-order FP64 block sum), the
+          // restraint's energy, distance and work.
+          if (live) {
+            float* o = I.report_pos + ((slot * R + r) * N + tid) * 3;
+            o[0] = x; o[1] = y; o[2] = z;
+          }
+          double ek = live ? 0.5 * (double)mass * ((double)vx * vx + (double)vy * vy + (double)vz * vz) : 0.0;
 #pragma unroll
-          for (int k = 0; k < kNumReduced; ++k) o[k] = E.e[k];
-          o[B200MD_OBS_SMD_WORK] = P.smd_on ? S.smd_energy[1] : 0.0;
+          for (int o = 16; o > 0; o >>= 1) ek += __shfl_xor_sync(0xffffffffu, ek, o);
+          if (lane == 0) S.ered[warp] = ek;
+          __syncthreads();
+          if (tid == 0 && observables != nullptr) {
+            double* o = observables + (slot * R + r) * B200MD_NUM_OBSERVABLES;
+            o[B200MD_E_EXTERNAL] = P.smd_on ? S.smd_energy[0] : 0.0;
+            o[B200MD_OBS_EKIN] = (S.ered[0] + S.ered[1]) + (S.ered[2] + S.ered[3]);
+            o[B200MD_OBS_E2E_DIST] = P.smd_on ? (double)S.smd[4] : 0.0;
+            o[B200MD_OBS_SMD_WORK] = P.smd_on ? S.smd_energy[1] : 0.0;
+          }
+        } else {  // FP64 energies of x(t + dt) in place: the parked velocities and the SoA copy are dead until the next step
+          __syncthreads();  // every thread has read its S.vel entry
+          stage_pd(S, tid, x, y, z, live ? q : 0.0f);
+          __syncthreads();
+          Energies E;
+          E.clear();
+          energy_pass<MODE>(S, T, P, pbc, tid, E);
+          if (live) E.e[B200MD_OBS_EKIN] = 0.5 * (double)mass * ((double)vx * vx + (double)vy * vy + (double)vz * vz);
+          if (P.smd_on && tid == 0) { E.e[B200MD_E_EXTERNAL] += S.smd_energy[0]; E.e[B200MD_OBS_E2E_DIST] = (double)S.smd[4]; }
+          reduce_energies<kNumReduced>(S, E, warp, lane);
+          if (tid == 0 && observables != nullptr) {
+            double* o = observables + (slot * R + r) * B200MD_NUM_OBSERVABLES;
+#pragma unroll
+            for (int k = 0; k < kNumReduced; ++k) o[k] = E.e[k];
+            o[B200MD_OBS_SMD_WORK] = P.smd_on ? S.smd_energy[1] : 0.0;
+          }
         }
       }
       if (I.snapshot_every > 0 && snapshots != nullptr && (s + 1) % I.snapshot_every == 0 && live) {
@@ -1595,8 +1621,8 @@ extern "C" int b200md_forces_compute(const b200md_topology* topo, const b200md_f
   g_launches.fetch_add(1);
   if (energies != nullptr) {  // FP64 energies: a second kernel on the same stream (energy_kernel)
     const int egrid = (int)std::min<long long>(R, (long long)topo->num_sms * topo->occ_energy[mode]);
-    if (mode == 0) energy_kernel<0><<<egrid, kThreads, 0, st>>>(T, P, R, pos, box, energies);
-    else energy_kernel<1><<<egrid, kThreads, 0, st>>>(T, P, R, pos, box, energies);
+    if (mode == 0) energy_kernel<0><<<egrid, kThreads, 0, st>>>(T, P, R, pos, box, R, energies, B200MD_NUM_ENERGIES, B200MD_NUM_ENERGIES);
+    else energy_kernel<1><<<egrid, kThreads, 0, st>>>(T, P, R, pos, box, R, energies, B200MD_NUM_ENERGIES, B200MD_NUM_ENERGIES);
     g_launches.fetch_add(1);
   }
   CUDA_TRY(cudaGetLastError());
@@ -1638,11 +1664,19 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
   slice = std::min<long long>(slice, io->nsteps);
   I.slice_len = (int)slice;
   I.nslices = (int)((io->nsteps + slice - 1) / slice);
+  long long nrec = 1;
   {  // ticket counter, per-replica slice counts and (SMD) carried work: grow-only workspace of the handle, zeroed per launch
     auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
     const size_t b_t = 256, b_d = I.nslices > 1 ? up(sizeof(unsigned int) * (size_t)R) : 0;
     const size_t b_w = (I.nslices > 1 && P.smd_on) ? up(sizeof(double) * (size_t)R) : 0;
-    const size_t total = b_t + b_d + b_w;
+    // deferred energies (energy_kernel behind the launch): positions of every record, unless that buffer would pass
+    // B200MD_DEFER_ENERGY_MB (default 1024; 0: always evaluate the energies inside the fused kernel)
+    nrec = io->energy_every > 0 ? (io->nsteps + io->energy_every - 1) / io->energy_every : 1;
+    size_t b_r = up(sizeof(float) * 3 * (size_t)T.natoms * (size_t)R * (size_t)nrec);
+    long long budget_mb = 1024;
+    if (const char* e = getenv("B200MD_DEFER_ENERGY_MB")) budget_mb = atoll(e);
+    if (observables == nullptr || (long long)(b_r >> 20) >= budget_mb) b_r = 0;
+    const size_t total = b_t + b_d + b_w + b_r;
     if (topo->ws != nullptr && topo->ws_stream != st) CUDA_TRY(cudaStreamSynchronize(topo->ws_stream));
     if (total > topo->ws_bytes) {
       if (topo->ws != nullptr) { CUDA_TRY(cudaStreamSynchronize(topo->ws_stream)); cudaFree(topo->ws); topo->ws = nullptr; topo->ws_bytes = 0; }
@@ -1654,6 +1688,7 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
     I.ticket = (unsigned long long*)wbase;
     I.slice_done = b_d ? (unsigned int*)(wbase + b_t) : nullptr;
     I.smd_work = b_w ? (double*)(wbase + b_t + b_d) : nullptr;
+    I.report_pos = b_r ? (float*)(wbase + b_t + b_d + b_w) : nullptr;
     CUDA_TRY(cudaMemsetAsync(wbase, 0, b_t + b_d, st));
   }
 #define B200MD_LAUNCH_INTEGRATE(M, RG) \
@@ -1662,6 +1697,13 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
   else { if (rigid) B200MD_LAUNCH_INTEGRATE(1, true); else B200MD_LAUNCH_INTEGRATE(1, false); }
 #undef B200MD_LAUNCH_INTEGRATE
   g_launches.fetch_add(1);
+  if (I.report_pos != nullptr) {  // the force-field energies of every record, FP64, in one launch behind the steps
+    const long long nev = nrec * R;
+    const int egrid = (int)std::min<long long>(nev, (long long)topo->num_sms * topo->occ_energy[mode]);
+    if (mode == 0) energy_kernel<0><<<egrid, kThreads, 0, st>>>(T, P, nev, I.report_pos, box, R, observables, B200MD_NUM_OBSERVABLES, B200MD_E_EXTERNAL);
+    else energy_kernel<1><<<egrid, kThreads, 0, st>>>(T, P, nev, I.report_pos, box, R, observables, B200MD_NUM_OBSERVABLES, B200MD_E_EXTERNAL);
+    g_launches.fetch_add(1);
+  }
   CUDA_TRY(cudaGetLastError());
   return B200MD_OK;
 }

@@ -122,6 +122,9 @@ struct StepParams {
   unsigned long long* ticket;   // [1], zeroed before the launch
   unsigned int* slice_done;     // [R] slices of replica r that are complete, zeroed before the launch
   double* smd_work;             // [R] work of the moving restraint carried from slice to slice (SMD only)
+  // deferred energies: on a report step the kernel writes the positions here ([nreports][R][natoms][3]) and energy_kernel
+  // evaluates the 7 force-field terms of all records behind the launch; nullptr: FP64 energy pass inside the kernel
+  float* report_pos;
 };
 
 // ---- shared-memory carve-up -----------------------------------------------------------------
