@@ -22,48 +22,18 @@ struct Energies {
 // compiler-chosen FMA contraction (every instantiation rounds identically).  (a12, nb6) = (12 A, -6 B).  Energies are not
 // computed here: the fp32 rounding of dx, dy, dz limits a pair energy to ~1e-7 relative, and the lj / electrostatics
 // sums cancel up to 1000:1 -- they come from the FP64 energy pass below.
-template <int MODE>
-__device__ __forceinline__ float pair_eval(float dx, float dy, float dz, float kqi, float qj, float a12, float nb6,
-                                           bool excl, const ForceParams& P) {
-  const float r2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
-  float rinv = fast_rsqrt(r2);
-  if (MODE == 1) excl = excl || !(r2 <= P.rc2);
-  rinv = excl ? 0.0f : rinv;
-  const float r2inv = __fmul_rn(rinv, rinv);
-  const float r6 = __fmul_rn(__fmul_rn(r2inv, r2inv), r2inv);
-  const float qq = __fmul_rn((MODE == 1 && excl) ? 0.0f : kqi, qj);
-  const float glj1 = __fmaf_rn(a12, r6, nb6);  // 12 A r^-6 - 6 B;  glj1 * r6 = -r dE_lj/dr
-  if (MODE == 0) {
-    const float gc = __fmul_rn(qq, rinv);  // K qi qj / r = -r dE_c/dr
-    return __fmul_rn(__fmaf_rn(glj1, r6, gc), r2inv);
-  } else {
-    const float gc = __fmul_rn(qq, __fmaf_rn(-2.0f * P.krf, r2, rinv));  // -r * forces.py:478
-    float glj = __fmul_rn(glj1, r6);
-    const float r = __fmul_rn(r2, rinv);
-    // forces.py:401-411 (pot*deriv/dist as written).  t is clamped at 0 below the switch distance (and for
-    // switch_dist = None, where rs = +inf makes it NaN): sv = 1, sd = 0 there, which leaves glj and elj untouched.
-    const float t = fmaxf(__fmul_rn(r - P.rs, P.inv_sw), 0.0f);
-    const float t2 = __fmul_rn(t, t);
-    const float sv = __fmaf_rn(__fmul_rn(t2, t), __fmaf_rn(t, __fmaf_rn(t, -6.0f, 15.0f), -10.0f), 1.0f);
-    const float nsd = __fmul_rn(__fmul_rn(t2, __fmaf_rn(t, __fmaf_rn(t, 30.0f, -60.0f), 30.0f)), P.inv_sw);
-    const float elj = __fmul_rn(__fmaf_rn(__fmul_rn(a12, 1.0f / 12.0f), r6, __fmul_rn(nb6, 1.0f / 6.0f)), r6);
-    glj = __fmaf_rn(sv, glj, __fmul_rn(elj, nsd));
-    return __fmul_rn(__fadd_rn(glj, gc), r2inv);
-  }
-}
-
-// Two pairs of one i atom (j, j+1) in packed f32x2: the same operations in the same order as pair_eval, one issue
-// slot per two fp32 results.  Only rsqrt and the exclusion selects are per half.
-struct PairConst {  // loop-invariant packed constants
-  u64 c12, c6, m2krf, krf, ncrf, rs, inv_sw, cm6, c15, cm10, one, c30, cm60;
+// Two pairs of one i atom (j, j+1) in packed f32x2: one issue slot per two fp32 results.  Only rsqrt and the exclusion
+// selects are per half.
+struct PairConst {  // loop-invariant packed constants (MODE 1)
+  u64 m2krf, rs, inv_sw, cm6, c15, cm10, one, nsdc;
 };
 template <int MODE>
 __device__ __forceinline__ PairConst make_pair_const(const ForceParams& P) {
   PairConst C;
-  C.c12 = dup2(1.0f / 12.0f); C.c6 = dup2(1.0f / 6.0f);
   if (MODE == 1) {
-    C.m2krf = dup2(-2.0f * P.krf); C.krf = dup2(P.krf); C.ncrf = dup2(-P.crf); C.rs = dup2(P.rs); C.inv_sw = dup2(P.inv_sw);
-    C.cm6 = dup2(-6.0f); C.c15 = dup2(15.0f); C.cm10 = dup2(-10.0f); C.one = dup2(1.0f); C.c30 = dup2(30.0f); C.cm60 = dup2(-60.0f);
+    C.m2krf = dup2(-2.0f * P.krf); C.rs = dup2(P.rs); C.inv_sw = dup2(P.inv_sw);
+    C.cm6 = dup2(-6.0f); C.c15 = dup2(15.0f); C.cm10 = dup2(-10.0f); C.one = dup2(1.0f);
+    C.nsdc = dup2(30.0f / 12.0f * P.inv_sw);  // -s'(t) = 30 t^2 (1 - t)^2 / (rc - rs), with the 1/12 of 12 E_lj folded in
   }
   return C;
 }
@@ -79,24 +49,29 @@ __device__ __forceinline__ u64 pair_eval2(u64 dx, u64 dy, u64 dz, float kqi, u64
   const u64 rinv = pk(ia, ib);
   const u64 r2inv = mul2(rinv, rinv);
   const u64 r6 = mul2(mul2(r2inv, r2inv), r2inv);
-  const u64 qq = mul2(MODE == 1 ? pk(e0 ? 0.0f : kqi, e1 ? 0.0f : kqi) : kq2, qj);
+  // An excluded / cut-off pair has rinv = 0: r2inv = 0 multiplies the whole coefficient below, so its (finite) reaction-field
+  // term needs no select of its own
+  const u64 qq = mul2(kq2, qj);
   const u64 glj1 = fma2(a12, r6, nb6);
   if (MODE == 0) {
     const u64 gc = mul2(qq, rinv);
     return mul2(fma2(glj1, r6, gc), r2inv);
   } else {
-    const u64 gc = mul2(qq, fma2(C.m2krf, r2, rinv));
-    u64 glj = mul2(glj1, r6);
+    const u64 gc = mul2(qq, fma2(C.m2krf, r2, rinv));  // -r * forces.py:478
+    const u64 glj = mul2(glj1, r6);
+    // forces.py:401-411 (pot * deriv / dist as written): F <- s F + E s' / r with t = (r - rs) / (rc - rs) clamped at 0 below
+    // the switch distance (and for switch_dist = None, where rs = +inf makes it NaN): s = 1, s' = 0 there.
+    //   s(t) = 1 + t^3 (-10 + 15 t - 6 t^2),   -s'(t) (rc - rs) = 30 t^2 (1 - t)^2 = 30 (t - t^2)^2,   12 E_lj = glj + nb6 r6
     const u64 r = mul2(r2, rinv);
     float ta, tb;
     upk(mul2(sub2(r, C.rs), C.inv_sw), ta, tb);
     const u64 t = pk(fmaxf(ta, 0.0f), fmaxf(tb, 0.0f));
     const u64 t2 = mul2(t, t);
     const u64 sv = fma2(mul2(t2, t), fma2(t, fma2(t, C.cm6, C.c15), C.cm10), C.one);
-    const u64 nsd = mul2(mul2(t2, fma2(t, fma2(t, C.c30, C.cm60), C.c30)), C.inv_sw);
-    const u64 elj = mul2(mul2(add2(glj1, nb6), r6), C.c12);  // A r^-12 - B r^-6 = r6 (glj1 + nb6) / 12
-    glj = fma2(sv, glj, mul2(elj, nsd));
-    return mul2(add2(glj, gc), r2inv);
+    const u64 q = sub2(t, t2);
+    const u64 nsd = mul2(mul2(q, q), C.nsdc);
+    const u64 elj12 = fma2(nb6, r6, glj);
+    return mul2(add2(fma2(sv, glj, mul2(elj12, nsd)), gc), r2inv);
   }
 }
 
