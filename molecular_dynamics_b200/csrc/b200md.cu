@@ -192,8 +192,11 @@ __device__ __forceinline__ void st_release_u32(unsigned int* p, unsigned int v) 
 // count.  The arithmetic of a step does not depend on the slicing, so results are bit-identical for every slice
 // length; what it buys is a tail of one slice instead of one whole launch per replica (592 resident CTAs: 1 024
 // replicas x 1 000 steps took two full waves).
+// 5 CTAs per SM (<= 102 registers): the task loops fit without spills (ptxas moves ~200 bytes of per-launch state to local
+// memory, outside them), and the fifth CTA is worth +2 % (9.08e7 vs 8.91e7 replica-steps/s); at 6 (80 registers) the pair
+// loops spill and the rate drops to 7.1e7.
 template <int MODE, bool RIGID>
-__global__ void __launch_bounds__(kThreads, 4)
+__global__ void __launch_bounds__(kThreads, 5)
 integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const long long R, float* __restrict__ pos,
                  float* __restrict__ vel, float* __restrict__ forces, const float* __restrict__ box,
                  double* __restrict__ observables, float* __restrict__ snapshots, uint32_t* __restrict__ status) {
@@ -1655,11 +1658,12 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
   const bool rigid = io->rigid_bonds != 0 && T.ncons > 0;
   // One wave of persistent CTAs draws (slice, replica) units from a ticket counter (integrate_kernel).  Slice length:
   // about 16 rounds of units over the resident CTAs, so that the tail of a launch is a few percent of it, within
-  // [8, 64] steps (parking a replica costs ~3 us against ~7 us per step); B200MD_SLICE overrides it for experiments.
+  // [8, 128] steps (parking a replica costs ~3 us against ~8 us per step: 8.73 / 8.85 / 8.91 / 8.93e7 replica-steps/s at
+  // 16 / 32 / 64 / 128 for 8 192 replicas x 1 000 steps); B200MD_SLICE overrides it for experiments.
   const long long cap = (long long)topo->num_sms * topo->occ_integrate[mode];
   const int grid = (int)std::min<long long>(R, cap);
   long long slice = (long long)io->nsteps * R / (cap * 16);
-  slice = std::max<long long>(8, std::min<long long>(64, slice));
+  slice = std::max<long long>(8, std::min<long long>(128, slice));
   if (const char* e = getenv("B200MD_SLICE")) { const long long v = atoll(e); if (v > 0) slice = v; }
   slice = std::min<long long>(slice, io->nsteps);
   I.slice_len = (int)slice;
