@@ -194,9 +194,10 @@ __device__ __forceinline__ void st_release_u32(unsigned int* p, unsigned int v) 
 // replicas x 1 000 steps took two full waves).
 // 5 CTAs per SM (<= 102 registers): the task loops fit without spills (ptxas moves ~200 bytes of per-launch state to local
 // memory, outside them), and the fifth CTA is worth +2 % (9.08e7 vs 8.91e7 replica-steps/s); at 6 (80 registers) the pair
-// loops spill and the rate drops to 7.1e7.
+// loops spill and the rate drops to 7.1e7.  The cutoff mode and the rigid-bond instantiation need their 128 registers
+// (at 5 CTAs: 6.77e7 vs 7.23e7 and 6.38e7 vs 6.64e7) and stay at 4.
 template <int MODE, bool RIGID>
-__global__ void __launch_bounds__(kThreads, 5)
+__global__ void __launch_bounds__(kThreads, (MODE == 0 && !RIGID) ? 5 : 4)
 integrate_kernel(const DevTopo T, const ForceParams P, const StepParams I, const long long R, float* __restrict__ pos,
                  float* __restrict__ vel, float* __restrict__ forces, const float* __restrict__ box,
                  double* __restrict__ observables, float* __restrict__ snapshots, uint32_t* __restrict__ status) {
