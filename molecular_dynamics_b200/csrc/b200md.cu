@@ -917,7 +917,9 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
     for (int it : *K.seq) for (int c = 0; c < K.arity; ++c) per_atom_count[K.idx[K.arity * it + c]]++;
   std::vector<uint16_t> gstart(kMaxAtoms + 2, 0);
   int nslots = 0;
-  for (int a = 0; a < kMaxAtoms; ++a) { gstart[a] = (uint16_t)nslots; nslots += per_atom_count[a]; }
+  // an atom's range is padded to a multiple of 4 slots (the padding is zeroed at staging and never written): the gather
+  // reads it with LDS.128
+  for (int a = 0; a < kMaxAtoms; ++a) { gstart[a] = (uint16_t)nslots; nslots += (per_atom_count[a] + 3) & ~3; }
   gstart[kMaxAtoms] = gstart[kMaxAtoms + 1] = (uint16_t)nslots;
   if (nslots > 65534) { delete topo; fail(B200MD_ERR_UNSUPPORTED, "too many bonded force contributions"); return nullptr; }
   T.nslots = nslots + 1;  // + the trash slot

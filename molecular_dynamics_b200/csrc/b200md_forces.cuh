@@ -828,10 +828,11 @@ __device__ __forceinline__ void gather_forces(const Smem& S, const ForceParams& 
     fx += (float)ix * kFixedInv; fy += (float)iy * kFixedInv; fz += (float)iz * kFixedInv;
     S.fbi[a] = 0; S.fbi[kMaxAtoms + a] = 0; S.fbi[2 * kMaxAtoms + a] = 0;
   } else {
-    const int g1 = S.gstart[a + 1];
-#pragma unroll 4
-    for (int g = S.gstart[a]; g < g1; ++g) {
-      fx += S.fb[g]; fy += S.fb[S.fbs + g]; fz += S.fb[2 * S.fbs + g];
+    const int g1 = S.gstart[a + 1];  // ranges are multiples of 4 slots, planes 128-byte aligned: one LDS.128 per plane and quad
+#pragma unroll 2
+    for (int g = S.gstart[a]; g < g1; g += 4) {
+      const float4 vx = *(const float4*)(S.fb + g), vy = *(const float4*)(S.fb + S.fbs + g), vz = *(const float4*)(S.fb + 2 * S.fbs + g);
+      fx += (vx.x + vx.y) + (vx.z + vx.w); fy += (vy.x + vy.y) + (vy.z + vy.w); fz += (vz.x + vz.y) + (vz.z + vz.w);
     }
   }
   if (P.smd_on) {
