@@ -57,7 +57,7 @@ __device__ __forceinline__ void stage_tables(const Smem& S, const DevTopo& T, co
 // Positions in double for the energy pass (S.pd overlays vel + sx: callers put a barrier on either side).
 __device__ __forceinline__ void stage_pd(const Smem& S, int tid, float x, float y, float z, float q) {
   S.pd[tid] = (double)x; S.pd[kMaxAtoms + tid] = (double)y; S.pd[2 * kMaxAtoms + tid] = (double)z;
-  S.pd[3 * kMaxAtoms + tid] = (double)q;
+  S.pd[3 * kMaxAtoms + tid] = (double)q * 18.222615429025844;  // q sqrt(K), K = 332.06371307417066: pair products are K qi qj
 }
 
 // Forces.compute (forces.py:82-344), the FORCES of a batch of replicas: one CTA per replica (grid-stride).  The energies

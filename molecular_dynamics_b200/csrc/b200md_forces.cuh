@@ -640,8 +640,10 @@ __device__ __forceinline__ double etorsion(const EPairConst& C, const DevTopo& T
 
 // One non-bonded pair of Forces.ava_idx in double (forces.py:379-413, 451-489): (electrostatics, lj-family) energies.
 // Straight-line (selects, no branches): the caller unrolls four of these so that their dependency chains overlap.
-template <int MODE, bool PBC>
-__device__ __forceinline__ void epair(const EPairConst& C, const double2* __restrict__ tab, uint32_t w, double scale, double& eel,
+// S.pd carries q sqrt(K): the charge product below is K qi qj.  LJ = true: the plain "lj" term (A r^-12 - B r^-6) without
+// the two table scalings the repulsion / combination cases need.
+template <int MODE, bool PBC, bool LJ>
+__device__ __forceinline__ void epair(const EPairConst& C, const double2* __restrict__ tab, uint32_t w, bool live, double& eel,
                                       double& elj) {
   const int i = w & 0xff, j = (w >> 8) & 0xff;
   double dx = lds_f64(C.pd, i) - lds_f64(C.pd, j), dy = lds_f64(C.pd, kMaxAtoms + i) - lds_f64(C.pd, kMaxAtoms + j),
@@ -654,9 +656,10 @@ __device__ __forceinline__ void epair(const EPairConst& C, const double2* __rest
   const double r2 = fma(dz, dz, fma(dy, dy, dx * dx));
   const double2 ab = __ldg(tab + (w >> 16));
   const double rinv = drsqrt(r2), r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
-  const double qq = lds_f64(C.pd, 3 * kMaxAtoms + i) * lds_f64(C.pd, 3 * kMaxAtoms + j) * scale;  // scale = K, or 0 for a padding slot
-  double lj = fma(C.ta * ab.x, r6, C.tb * ab.y) * r6;  // lj: A r^-12 - B r^-6; repulsion: A r^-12; repulsioncg: B r^-6
-  lj = scale != 0.0 ? lj : 0.0;
+  double qq = lds_f64(C.pd, 3 * kMaxAtoms + i) * lds_f64(C.pd, 3 * kMaxAtoms + j);
+  double lj = (LJ ? fma(ab.x, r6, -ab.y) : fma(C.ta * ab.x, r6, C.tb * ab.y)) * r6;  // lj: A r^-12 - B r^-6; repulsion: A r^-12; repulsioncg: B r^-6
+  qq = live ? qq : 0.0;  // a padding slot re-reads a valid pair with weight 0
+  lj = live ? lj : 0.0;
   if (MODE == 1) {
     const double r = r2 * rinv;
     const double t = fmax((r - C.rs) * C.inv_sw, 0.0);  // forces.py:401-411; rs = +inf (t = NaN -> 0) without a switch
@@ -673,7 +676,7 @@ __device__ __forceinline__ void epair(const EPairConst& C, const double2* __rest
 // Forces.ava_idx (forces.py:258-316); the row-major list keeps i warp-uniform and j consecutive.  Four pairs per thread
 // and iteration with their own accumulators: the FP64 chain of a pair is serial (~25 dependent instructions), and four
 // warps per scheduler do not hide that on their own.
-template <int MODE, bool PBC>
+template <int MODE, bool PBC, bool LJ>
 __device__ __forceinline__ void epair_loop(const EPairConst& C, const DevTopo& T, int tid, double& eel, double& elj) {
   double el[4] = {0.0, 0.0, 0.0, 0.0}, lj[4] = {0.0, 0.0, 0.0, 0.0};
   const uint32_t* __restrict__ list = T.e_pair;
@@ -681,16 +684,15 @@ __device__ __forceinline__ void epair_loop(const EPairConst& C, const DevTopo& T
   const int n = T.ne_pair;
   for (int k0 = tid; k0 < n; k0 += 4 * kThreads) {
     uint32_t w[4];
-    double sc[4];
+    bool live[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const int k = k0 + u * kThreads;
-      const bool live = k < n;
-      w[u] = __ldg(list + (live ? k : k0));  // a padding slot re-reads a valid pair with weight 0
-      sc[u] = live ? kElecFactorD : 0.0;
+      live[u] = k < n;
+      w[u] = __ldg(list + (live[u] ? k : k0));
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) epair<MODE, PBC>(C, tab, w[u], sc[u], el[u], lj[u]);
+    for (int u = 0; u < 4; ++u) epair<MODE, PBC, LJ>(C, tab, w[u], live[u], el[u], lj[u]);
   }
   eel = (el[0] + el[1]) + (el[2] + el[3]);
   elj = (lj[0] + lj[1]) + (lj[2] + lj[3]);
@@ -705,8 +707,10 @@ __device__ __forceinline__ void energy_pass_impl(const Smem& S, const DevTopo& T
   C.krf = P.krf_d; C.ncrf = -P.crf_d;
   C.bx = -(double)S.box[0]; C.by = -(double)S.box[1]; C.bz = -(double)S.box[2];
   if (P.terms & (B200MD_T_ELECTROSTATICS | B200MD_T_LJ | B200MD_T_REPULSION | B200MD_T_REPULSIONCG)) {
-    if (pbc) epair_loop<MODE, true>(C, T, tid, eel, elj);
-    else epair_loop<MODE, false>(C, T, tid, eel, elj);
+    const bool plain_lj = P.tab_a == 1.0f && P.tab_b == -1.0f;
+    if (pbc) epair_loop<MODE, true, false>(C, T, tid, eel, elj);  // periodic replicas: one general instantiation
+    else if (plain_lj) epair_loop<MODE, false, true>(C, T, tid, eel, elj);
+    else epair_loop<MODE, false, false>(C, T, tid, eel, elj);
   }
   // ---- 1-4 pairs (forces.py:176-226): never cut, switched or reaction-field corrected
   if (T.p14_on) {
