@@ -1677,10 +1677,10 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
     const size_t b_t = 256, b_d = I.nslices > 1 ? up(sizeof(unsigned int) * (size_t)R) : 0;
     const size_t b_w = (I.nslices > 1 && P.smd_on) ? up(sizeof(double) * (size_t)R) : 0;
     // deferred energies (energy_kernel behind the launch): positions of every record, unless that buffer would pass
-    // B200MD_DEFER_ENERGY_MB (default 1024; 0: always evaluate the energies inside the fused kernel)
+    // B200MD_DEFER_ENERGY_MB (default 8192; 0: always evaluate the energies inside the fused kernel)
     nrec = io->energy_every > 0 ? (io->nsteps + io->energy_every - 1) / io->energy_every : 1;
     size_t b_r = up(sizeof(float) * 3 * (size_t)T.natoms * (size_t)R * (size_t)nrec);
-    long long budget_mb = 1024;
+    long long budget_mb = 8192;
     if (const char* e = getenv("B200MD_DEFER_ENERGY_MB")) budget_mb = atoll(e);
     if (observables == nullptr || (long long)(b_r >> 20) >= budget_mb) b_r = 0;
     const size_t total = b_t + b_d + b_w + b_r;
