@@ -1660,12 +1660,13 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
   cudaStream_t st = (cudaStream_t)stream;
   const bool rigid = io->rigid_bonds != 0 && T.ncons > 0;
   // One wave of persistent CTAs draws (slice, replica) units from a ticket counter (integrate_kernel).  Slice length:
-  // about 16 rounds of units over the resident CTAs, so that the tail of a launch is a few percent of it, within
+  // about 40 rounds of units over the resident CTAs, so that the tail of a launch is a few percent of it (1 024 replicas x
+  // 1 000 steps: 8.45 / 8.50 / 8.44 / 8.33 / 8.29e7 replica-steps/s at slices of 16 / 32 / 64 / 86 / 128 steps), within
   // [8, 128] steps (parking a replica costs ~3 us against ~8 us per step: 8.73 / 8.85 / 8.91 / 8.93e7 replica-steps/s at
   // 16 / 32 / 64 / 128 for 8 192 replicas x 1 000 steps); B200MD_SLICE overrides it for experiments.
   const long long cap = (long long)topo->num_sms * topo->occ_integrate[mode];
   const int grid = (int)std::min<long long>(R, cap);
-  long long slice = (long long)io->nsteps * R / (cap * 16);
+  long long slice = (long long)io->nsteps * R / (cap * 40);
   slice = std::max<long long>(8, std::min<long long>(128, slice));
   if (const char* e = getenv("B200MD_SLICE")) { const long long v = atoll(e); if (v > 0) slice = v; }
   slice = std::min<long long>(slice, io->nsteps);
