@@ -213,6 +213,24 @@ int b200md_integrate(const b200md_topology* topo, const b200md_force_opts* fopts
                      int64_t nreplicas, float* pos, float* vel, float* forces, const float* box,
                      double* observables, float* snapshots, uint32_t* status, void* stream);
 
+/*
+ * b200md_integrate without a single allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments, semantics and results as b200md_integrate (positions, velocities and forces bit-identical;
+ * report energies evaluated inside the fused kernel instead of by the energy kernel behind it: same FP64 arithmetic).
+ * The scheduler's scratch (ticket counter, per-replica slice counts, carried SMD work) lives in a file-scope device array
+ * of 786 688 bytes that every GPU loading the library holds until the process exits; it calls no cudaMalloc / cudaFree or
+ * allocating library routine.  Limits: nreplicas <= B200MD_NOALLOC_MAX_REPLICAS and natoms <= B200MD_MAX_ATOMS, else
+ * B200MD_ERR_UNSUPPORTED with a message naming the limit.  Every call shares the array: calls that overlap on the GPU
+ * (two streams, two threads) race on it -- serialise them.  The first call per device resolves the array's device address
+ * (cudaGetSymbolAddress): make that call before starting a graph capture.
+ */
+#define B200MD_NOALLOC_MAX_REPLICAS 65536
+int b200md_integrate_noalloc(const b200md_topology* topo, const b200md_force_opts* fopts,
+                             const b200md_smd_opts* smd, const b200md_integrate_opts* iopts,
+                             int64_t nreplicas, float* pos, float* vel, float* forces, const float* box,
+                             double* observables, float* snapshots, uint32_t* status, void* stream);
+
 /* Energy.calc_phi of the ML callers (cGAN/cGAN_D_pos-2.3.2/cgan.py:166-207; the angle of forces.py:541-552):
  * phi[r][d] = -atan2(sin, cos) of proper dihedral par.dihedrals[d], for every replica; minimum image with the box
  * diagonal when it is not zero.  pos DEVICE float [R][natoms][3], box DEVICE float [R][9] or NULL,

@@ -19,6 +19,7 @@ OBS_E2E_DIST = 9
 OBS_SMD_WORK = 10
 MAX_ATOMS = 128  # one-CTA-per-replica kernels; above it (up to MAX_ATOMS_LARGE) the large-solute kernels run
 MAX_ATOMS_LARGE = 32768
+NOALLOC_MAX_REPLICAS = 65536  # b200md_integrate_noalloc: size of its fixed device scratch array
 
 # dict order of the reference's result (forces.py:40-50, :100)
 ENERGY_SLOTS = ("electrostatics", "lj", "bonds", "angles", "dihedrals", "1-4", "impropers", "external")
@@ -203,6 +204,8 @@ def declare_signatures(lib):
     lib.b200md_integrate.restype = C.c_int
     lib.b200md_integrate.argtypes = [vp, C.POINTER(ForceOpts), C.POINTER(SmdOpts), C.POINTER(IntegrateOpts),
                                      C.c_int64, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.b200md_integrate_noalloc.restype = C.c_int
+    lib.b200md_integrate_noalloc.argtypes = list(lib.b200md_integrate.argtypes)
     lib.b200md_forces_compute_host.restype = C.c_int
     lib.b200md_forces_compute_host.argtypes = [vp, C.POINTER(ForceOpts), C.POINTER(SmdOpts), C.c_int64, vp, vp, vp,
                                                vp, vp]
@@ -222,7 +225,7 @@ def declare_signatures(lib):
 EXPORTED_SYMBOLS = (
     "b200md_topology_create", "b200md_topology_destroy", "b200md_topology_exclusion_mask",
     "b200md_topology_natoms", "b200md_topology_mask_words", "b200md_topology_num_constraints", "b200md_topology_ndihedrals",
-    "b200md_dihedral_angles", "b200md_dihedral_angles_backward", "b200md_constrain", "b200md_forces_compute", "b200md_integrate", "b200md_forces_compute_host",
+    "b200md_dihedral_angles", "b200md_dihedral_angles_backward", "b200md_constrain", "b200md_forces_compute", "b200md_integrate", "b200md_integrate_noalloc", "b200md_forces_compute_host",
     "b200md_fire_update", "b200md_fp32_peak_tflops", "b200md_launch_count", "b200md_last_error", "b200md_version",
 )
 

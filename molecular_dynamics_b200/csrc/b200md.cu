@@ -8,6 +8,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1712,6 +1713,93 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
     else energy_kernel<1><<<egrid, kThreads, 0, st>>>(T, P, nev, I.report_pos, box, R, observables, B200MD_NUM_OBSERVABLES, B200MD_E_EXTERNAL);
     g_launches.fetch_add(1);
   }
+  CUDA_TRY(cudaGetLastError());
+  return B200MD_OK;
+}
+
+// ---- b200md_integrate without a single allocation -------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  b200md_integrate takes the scratch of
+// the time-sliced scheduler (ticket counter, per-replica slice counts, carried SMD work) from a grow-only cudaMalloc'd
+// workspace of the topology handle; this variant keeps it in a file-scope device array of fixed size:
+//   [ticket: 256 B][slice_done: 4 B x B200MD_NOALLOC_MAX_REPLICAS][smd_work: 8 B x B200MD_NOALLOC_MAX_REPLICAS] = 786 688 B,
+// resident on every GPU that loads the library until the process exits.  In host code `g_noalloc_scratch` is a host-side
+// stand-in, NOT a device address: the address the kernel gets comes from cudaGetSymbolAddress, resolved once per device
+// with that device current.  Every call shares the array and finds the previous call's contents in it: the ticket and the
+// slice counts are cleared (cudaMemsetAsync on the caller's stream, not an allocation), the SMD work of a replica is
+// written by its first slice before a later one reads it.  Calls that OVERLAP on the GPU (two streams, two host threads)
+// race on the array -- serialise them.  Energies of report steps are evaluated inside the fused kernel (the deferred
+// energy_kernel path of b200md_integrate needs a buffer that grows with replicas x records).
+constexpr size_t kNoAllocTicketBytes = 256;
+constexpr size_t kNoAllocDoneBytes = sizeof(unsigned int) * (size_t)B200MD_NOALLOC_MAX_REPLICAS;
+constexpr size_t kNoAllocWorkBytes = sizeof(double) * (size_t)B200MD_NOALLOC_MAX_REPLICAS;
+constexpr size_t kNoAllocBytes = kNoAllocTicketBytes + kNoAllocDoneBytes + kNoAllocWorkBytes;
+static_assert((kNoAllocTicketBytes + kNoAllocDoneBytes) % 8 == 0, "smd_work must stay 8-byte aligned");
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+constexpr int kNoAllocMaxDevices = 64;
+static std::mutex g_noalloc_mutex;
+static unsigned char* g_noalloc_ptr[kNoAllocMaxDevices] = {nullptr};
+
+extern "C" int b200md_integrate_noalloc(const b200md_topology* topo, const b200md_force_opts* fopts,
+                                        const b200md_smd_opts* smd, const b200md_integrate_opts* io, int64_t R, float* pos,
+                                        float* vel, float* forces, const float* box, double* observables, float* snapshots,
+                                        uint32_t* status, void* stream) {
+  if (!topo || !io || !pos || !vel || !forces) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
+  if (R < 0 || io->nsteps < 0) return fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica or step count");
+  if (R > (int64_t)B200MD_NOALLOC_MAX_REPLICAS)
+    return fail(B200MD_ERR_UNSUPPORTED, "b200md_integrate_noalloc: nreplicas = " + std::to_string((long long)R) +
+                                            " exceeds B200MD_NOALLOC_MAX_REPLICAS = " + std::to_string(B200MD_NOALLOC_MAX_REPLICAS) +
+                                            " (the fixed device scratch array); split the batch or use b200md_integrate");
+  if (topo->large)
+    return fail(B200MD_ERR_UNSUPPORTED, "b200md_integrate_noalloc: solutes above 128 atoms keep their state in an allocated workspace; use b200md_integrate");
+  if (topo->device < 0 || topo->device >= kNoAllocMaxDevices)
+    return fail(B200MD_ERR_UNSUPPORTED, "b200md_integrate_noalloc: device index beyond 63");
+  if (R == 0 || io->nsteps == 0) return B200MD_OK;
+  if (io->rigid_bonds != 0 && topo->dev.ncons < 0)
+    return fail(B200MD_ERR_UNSUPPORTED, "rigid_bonds: a hydrogen is bonded to a hydrogen, or a heavy atom carries more than 3");
+  ForceParams P;
+  int rc = make_force_params(topo, fopts, smd, true, &P);
+  if (rc) return rc;
+  DevTopo T = apply_terms(topo->dev, fopts->terms);
+  StepParams I{};
+  I.dt = io->dt; I.gamma = io->gamma; I.temperature = io->temperature;
+  I.seed = io->seed; I.step0 = io->step0; I.replica0 = io->replica0;
+  I.nsteps = io->nsteps; I.energy_every = io->energy_every; I.snapshot_every = io->snapshot_every;
+  B200MD_ON_DEVICE(topo->device);
+  unsigned char* scratch = nullptr;
+  {  // set-up, once per device, with that device current: the DEVICE address of the scratch array
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (g_noalloc_ptr[topo->device] == nullptr) {
+      void* p = nullptr;
+      const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+      if (e != cudaSuccess || p == nullptr)
+        return fail(B200MD_ERR_CUDA, std::string("cudaGetSymbolAddress(g_noalloc_scratch): ") + cudaGetErrorString(e));
+      g_noalloc_ptr[topo->device] = (unsigned char*)p;
+    }
+    scratch = g_noalloc_ptr[topo->device];
+  }
+  const int mode = P.has_cutoff ? 1 : 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool rigid = io->rigid_bonds != 0 && T.ncons > 0;
+  const long long cap = (long long)topo->num_sms * topo->occ_integrate[mode];
+  const int grid = (int)std::min<long long>(R, cap);
+  long long slice = (long long)io->nsteps * R / (cap * 40);  // as b200md_integrate
+  slice = std::max<long long>(8, std::min<long long>(128, slice));
+  slice = std::min<long long>(slice, io->nsteps);
+  I.slice_len = (int)slice;
+  I.nslices = (int)((io->nsteps + slice - 1) / slice);
+  I.ticket = (unsigned long long*)scratch;
+  I.slice_done = (unsigned int*)(scratch + kNoAllocTicketBytes);
+  I.smd_work = (double*)(scratch + kNoAllocTicketBytes + kNoAllocDoneBytes);
+  I.report_pos = nullptr;  // energies inside the fused kernel
+  // the array keeps the last call's contents: the ticket and the slice counts of this call's replicas must start at zero
+  CUDA_TRY(cudaMemsetAsync(scratch, 0, kNoAllocTicketBytes + sizeof(unsigned int) * (size_t)R, st));
+#define B200MD_LAUNCH_INTEGRATE(M, RG) \
+  integrate_kernel<M, RG><<<grid, kThreads, T.smem_bytes_fixed, st>>>(T, P, I, R, pos, vel, forces, box, observables, snapshots, status)
+  if (mode == 0) { if (rigid) B200MD_LAUNCH_INTEGRATE(0, true); else B200MD_LAUNCH_INTEGRATE(0, false); }
+  else { if (rigid) B200MD_LAUNCH_INTEGRATE(1, true); else B200MD_LAUNCH_INTEGRATE(1, false); }
+#undef B200MD_LAUNCH_INTEGRATE
+  g_launches.fetch_add(1);
   CUDA_TRY(cudaGetLastError());
   return B200MD_OK;
 }
