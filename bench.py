@@ -220,13 +220,18 @@ def cpu_c_oracle_rate(nrep, nsteps):
     return nrep * nsteps / (time.perf_counter() - t0)
 
 
+# identical in both arms' `config` (the driver compares the two dicts); the CPU arm's bounded sample is described in its
+# cpu_baseline.sample and top-level "sample"
+L2_NOTE = "GPU arm: flushed between timed steps (256 MiB fill, outside the event pair); CPU arm: not applicable"
+
+
 def bench_config(args, R, S):
-    """config keys shared by both arms (the reference arm adds its bounded `sample`)."""
+    """`config` of the JSON line: the same dict in both arms."""
     if args.workload == "forces":
         return {"workload": WORKLOAD_NAME_FORCES, "replicas_per_gpu": R, "mode": args.forces_mode,
-                "energies": not args.no_energies, "natoms": 104}
+                "energies": not args.no_energies, "natoms": 104, "l2": L2_NOTE}
     return {"workload": WORKLOAD_NAME_C4 if args.workload == "langevin_smd" else WORKLOAD_NAME, "replicas_per_gpu": R,
-            "md_steps_per_launch": S, "energy_every": args.energy_every, "dt_fs": 1.0, "natoms": 104}
+            "md_steps_per_launch": S, "energy_every": args.energy_every, "dt_fs": 1.0, "natoms": 104, "l2": L2_NOTE}
 
 
 FORCES_MODES = {"plain": {}, "rf": {"cutoff": 9.0, "rfa": True, "switch_dist": 7.5}}
@@ -266,12 +271,11 @@ def run_reference(args):
         pool.join()
     value = units / wall
     cfg = bench_config(args, args.replicas, args.inner)
-    cfg["sample"] = sample
     print(json.dumps({
         "impl": "reference", "metric": metric, "value": value, "unit": unit,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": cfg,
+        "config": cfg, "sample": sample,
         "cpu_baseline": {"value": value, "unit": unit, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -638,8 +642,7 @@ def run_ours(args):
             "metric": "ALA10 replica-steps/s", "value": value, "unit": "replica-steps/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {**bench_config(args, R, S),
-                       "l2": "flushed between timed steps (256 MiB fill, outside the event pair)"},
+            "config": bench_config(args, R, S),
             "detail": {"ns_per_day_aggregate": value * 1.0 * 86400 * 1e-6,
                        "ms_per_step_median_rank0": statistics.median(per_launch), "ms_per_step_max_rank0": max(per_launch),
                        "replicas_with_nan_after_run": nan_count},
@@ -786,7 +789,7 @@ def run_ours_forces(args):
             "metric": "ALA10 replica-evaluations/s", "value": value, "unit": "replica-evaluations/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {**bench_config(args, R, 0), "l2": "flushed between timed steps (256 MiB fill, outside the event pair)"},
+            "config": bench_config(args, R, 0),
             "detail": {"ms_per_step_median_rank0": statistics.median(per_launch)},
             "clocks": clocks.summary(),
             "e2e": {"value": e2e_value, "unit": "replica-evaluations/s", "h2d_bytes_per_step": hp.numel() * 4,
