@@ -814,6 +814,25 @@ extern "C" b200md_topology* b200md_topology_create(const b200md_topology_desc* d
     }
     dclass[q] = zero ? 2 : (fast ? 0 : 1);
   }
+  // Lane filling: zero-k dihedrals leave the packed list and hand their 1-4 pair to the (cheaper) 1-4 list -- but a ragged
+  // tail of that list costs a whole task for a few lanes (ALA10: 72 = 64 + 8).  When the tail fits into the free lanes of the
+  // last dihedral chunk, that many zero-k dihedrals stay packed (zero coefficients, their 1-4 pair fused) instead.
+  {
+    int nfast = 0, nzero14 = 0;
+    std::vector<char> has14(ND, 0);
+    for (int k = 0; k < d->n14; ++k)
+      for (int q = 0; q < ND; ++q) {
+        const int32_t* a4 = d->dihedral_idx + 4 * q;
+        const int i = d->idx14[2 * k], j = d->idx14[2 * k + 1];
+        if (!has14[q] && ((a4[0] == i && a4[3] == j) || (a4[0] == j && a4[3] == i))) { has14[q] = 1; break; }
+      }
+    for (int q = 0; q < ND; ++q) { nfast += dclass[q] == 0; nzero14 += dclass[q] == 2 && has14[q]; }
+    int tail = nzero14 % 64;
+    const int room = (64 - nfast % 64) % 64;
+    if (tail > 0 && tail <= room && !getenv("B200MD_NO_TAIL_FILL"))
+      for (int q = ND - 1; q >= 0 && tail > 0; --q)
+        if (dclass[q] == 2 && has14[q]) { dclass[q] = 0; --tail; }
+  }
   std::vector<int> fastd, gend;
   for (int q = 0; q < ND; ++q) (dclass[q] == 0 ? fastd : gend).push_back(q);
   gend.erase(std::remove_if(gend.begin(), gend.end(), [&](int q) { return dclass[q] == 2; }), gend.end());
