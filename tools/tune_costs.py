@@ -11,20 +11,12 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 NAMES = ["pass", "chunk", "diaggroup", "diag", "bond", "angle", "dih", "gen", "p14"]
 
 
-ENERGY = "--energy" in sys.argv  # tune the single-shot Forces.compute schedule (B200MD_COSTS_E) instead
-
-
 def run(costs):
-    key = "B200MD_COSTS_E" if ENERGY else "B200MD_COSTS"
-    env = dict(os.environ, **{key: ",".join(str(int(c)) for c in costs)})
-    if ENERGY:
-        out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "profile_forces.py")], env=env, capture_output=True, text=True).stdout
-        try:
-            return float(out.strip().splitlines()[-1].split()[0])
-        except Exception:
-            return 0.0
-    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--no-cpu", "--no-extra", "--steps", "3", "--warmup", "3", "--inner", "500"],
-                         env=env, capture_output=True, text=True).stdout
+    """one schedule (the force tasks carry no energy arithmetic any more: the fused integrator and the single-shot
+    forces_kernel share it), timed on the bench workload"""
+    env = dict(os.environ, B200MD_COSTS=",".join(str(int(c)) for c in costs))
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--no-cpu", "--no-extra", "--strong-total", "0", "--steps", "5",
+                          "--warmup", "3", "--inner", "500", "--energy-every", "0"], env=env, capture_output=True, text=True).stdout
     try:
         return json.loads(out.strip().splitlines()[-1])["value"]
     except Exception:
@@ -33,7 +25,7 @@ def run(costs):
 
 def main():
     args = [x for x in sys.argv[1:] if not x.startswith("--")]
-    default = "140,120,68,30,120,280,430,440,120" if ENERGY else "105,120,52,30,77,230,380,400,100"
+    default = "105,120,52,30,77,230,380,400,100"
     costs = [int(x) for x in (args[0] if args else default).split(",")]
     best = run(costs)
     print("start", costs, f"{best:.4e}", flush=True)
