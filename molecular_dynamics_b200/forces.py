@@ -148,6 +148,7 @@ class Forces:
         self._handles = {}  # device index -> native handle
         self.last_energies = None  # (R, 8) float64 tensor of the last compute (FP64 energy pass)
         self._last_ext_force = None  # detached force of a generic external object in the last compute_batch
+        self._host_state = {}  # device index -> staging buffers and streams of compute_batch_host
 
     # -- native handle management ----------------------------------------------------------------
     def _handle(self, device):
@@ -272,6 +273,74 @@ class Forces:
             return None
         self.last_energies = ene
         return ene
+
+    # -- host buffers in, host buffers out: copies overlapped with the kernels -----------------------
+    def compute_batch_host(self, pos, forces_out=None, energies_out=None, box=None, energies=True, chunks=8, device="cuda"):
+        """``Forces.compute`` for a batch that lives in HOST memory (pinned for full speed): ``pos`` (R, N, 3) float32 CPU
+        tensor → ``(forces_out, energies_out)`` CPU tensors (allocated pinned when not given; ``energies_out`` is None with
+        ``energies=False``).  The batch is cut into ``chunks`` pieces that flow through three streams -- host→device copy,
+        kernels, device→host copy -- so the two PCIe directions and the kernels overlap instead of running back to back
+        (65 536 ALA10 conformers: 164 MB over PCIe against 2.3 ms of kernels).  Device staging buffers are kept on the
+        object between calls.  Synchronous: returns when the results are in the host buffers; raises on NaN coordinates
+        like ``compute``.  SMD per-replica centres and generic ``external`` objects: use ``compute_batch``."""
+        if pos.is_cuda or pos.dtype != torch.float32 or pos.dim() != 3 or pos.shape[1] != self.natoms:
+            raise ValueError(f"pos must be a float32 CPU tensor of shape (R, {self.natoms}, 3)")
+        if self.external is not None and not (isinstance(self.external, SMDBias) and not isinstance(self.external.center, torch.Tensor)):
+            raise NotImplementedError("compute_batch_host supports no external term beyond an SMDBias with one scalar centre")
+        if self._extra_pair_terms:
+            raise NotImplementedError("compute_batch_host evaluates one pair term of the lj family; use compute_batch")
+        dev = torch.device(device)
+        if dev.index is None:
+            dev = torch.device("cuda", torch.cuda.current_device())
+        R, N, _ = pos.shape
+        pos = pos.contiguous()
+        if forces_out is None:
+            forces_out = torch.empty((R, N, 3), dtype=torch.float32).pin_memory()
+        if energies and energies_out is None:
+            energies_out = torch.empty((R, _cabi.NUM_ENERGIES), dtype=torch.float64).pin_memory()
+        hbox = None if box is None else box.to(dtype=torch.float32).contiguous()
+        st = self._host_state.get(dev.index)
+        if st is None or st["R"] < R:
+            st = {"R": R, "pos": torch.empty((R, N, 3), dtype=torch.float32, device=dev),
+                  "frc": torch.empty((R, N, 3), dtype=torch.float32, device=dev),
+                  "box": torch.zeros((R, 3, 3), dtype=torch.float32, device=dev),
+                  "s_in": torch.cuda.Stream(dev), "s_k": torch.cuda.Stream(dev), "s_out": torch.cuda.Stream(dev)}
+            self._host_state[dev.index] = st
+        s_in, s_k, s_out = st["s_in"], st["s_k"], st["s_out"]
+        start = torch.cuda.current_stream(dev).record_event()  # work queued by the caller before this call comes first
+        for s_ in (s_in, s_k, s_out):
+            s_.wait_event(start)
+        nchunk = max(1, min(int(chunks), R))
+        bounds = [R * k // nchunk for k in range(nchunk + 1)]
+        keep, flags = [], []
+        for k in range(nchunk):
+            lo, hi = bounds[k], bounds[k + 1]
+            if hi == lo:
+                continue
+            with torch.cuda.stream(s_in):
+                st["pos"][lo:hi].copy_(pos[lo:hi], non_blocking=True)
+                if hbox is not None:
+                    st["box"][lo:hi].copy_(hbox[lo:hi], non_blocking=True)
+                elif k == 0 and st.get("box_dirty"):
+                    st["box"].zero_()
+                e_in = s_in.record_event()
+            with torch.cuda.stream(s_k):
+                s_k.wait_event(e_in)
+                ene, status = self._launch(st["pos"][lo:hi], st["box"][lo:hi], st["frc"][lo:hi], energies=energies)
+                e_k = s_k.record_event()
+            with torch.cuda.stream(s_out):
+                s_out.wait_event(e_k)
+                forces_out[lo:hi].copy_(st["frc"][lo:hi], non_blocking=True)
+                if energies:
+                    energies_out[lo:hi].copy_(ene, non_blocking=True)
+                flags.append(status.max())
+            keep.append((ene, status))  # alive until the synchronisation below (they were allocated on s_k, read on s_out)
+        st["box_dirty"] = hbox is not None
+        s_out.synchronize()
+        torch.cuda.current_stream(dev).wait_stream(s_out)
+        if self.check_nan and flags and int(torch.stack(flags).max().item()) & _cabi.FLAG_NAN_POS:
+            raise RuntimeError("Found NaN coordinates.")
+        return forces_out, (energies_out if energies else None)
 
     # -- Energy.calc_phi of the ML callers ---------------------------------------------------------
     def dihedral_angles(self, pos, box=None):

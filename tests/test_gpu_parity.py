@@ -1166,6 +1166,33 @@ def test_force_only_launch_matches_and_backward_uses_it():
         assert torch.equal(s1.forces, s2.forces) and e.shape == (len(p), 8)
 
 
+def test_compute_batch_host_pipelines_copies_and_matches_compute_batch():
+    """Forces.compute_batch_host: host buffers in and out, the batch cut into chunks over three streams.  Same kernels on the
+    same inputs: bit-identical to compute_batch, for ragged chunk sizes, with a box, force-only, and twice in a row."""
+    g = load_golden("ala10")
+    rng = np.random.default_rng(3)
+    R = 1001
+    pos = (g["pos"][rng.integers(0, len(g["pos"]), R)] + 0.02 * rng.standard_normal((R, 104, 3))).astype(np.float32)
+    hp = torch.tensor(pos).pin_memory()
+    box = torch.zeros((R, 3, 3))
+    box[::3, 0, 0], box[::3, 1, 1], box[::3, 2, 2] = 41.0, 38.0, 44.0
+    for mode, b in (("plain", None), ("rf", box)):
+        F = Forces(gpu_par(g), **MODES[mode])
+        dp = torch.tensor(pos, device=DEV)
+        db = torch.zeros((R, 3, 3), device=DEV) if b is None else b.to(DEV)
+        f_ref = torch.empty_like(dp)
+        e_ref = F.compute_batch(dp, db, f_ref)
+        for chunks in (1, 7, 8):
+            f, e = F.compute_batch_host(hp, box=b, chunks=chunks, device=DEV)
+            assert f.is_pinned() and torch.equal(f, f_ref.cpu()) and torch.equal(e, e_ref.cpu()), (mode, chunks)
+        f2, e2 = F.compute_batch_host(hp, box=b, energies=False, device=DEV)
+        assert e2 is None and torch.equal(f2, f_ref.cpu())
+    bad = hp.clone()
+    bad[500, 3, 1] = float("nan")
+    with pytest.raises(RuntimeError, match="NaN"):
+        F.compute_batch_host(bad, device=DEV)
+
+
 def test_report_after_the_last_step_when_niter_is_not_a_multiple():
     """Integrator.step returns the energies of the END state (upstream's contract): with energy_every = 4 and 10 steps the
     records are steps 4, 8 and 10."""
