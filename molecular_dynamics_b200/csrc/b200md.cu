@@ -1309,7 +1309,65 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
       !group_terms(d->nimpropers, d->improper_idx, d->nimproper_terms, d->improper_term_owner, d->improper_term_prm, d->improper_term_harmonic, iq, is, it, ics)) {
     delete topo; fail(B200MD_ERR_INVALID_ARGUMENT, "torsion term owner out of range"); return nullptr;
   }
+  // bonded forces by windows of kLWin atoms (b200md_large.cuh, large_bonded_forces_kernel): per window the items that
+  // touch it, and per (item, role) the shared-memory slot of the contribution -- atom-major inside the window, in the fixed
+  // order bonds, angles, dihedrals, 1-4 pairs, impropers
+  const long long nitems = (long long)d->nbonds + d->nangles + d->ndihedrals + d->n14 + d->nimpropers;
+  if (nitems >= (1ll << 31)) { delete topo; fail(B200MD_ERR_UNSUPPORTED, "more than 2^31 bonded items"); return nullptr; }
+  const int nwin = (N + kLWin - 1) / kLWin;
+  std::vector<int> gstart(N + 1, 0), win_start(nwin + 1, 0);
+  std::vector<uint32_t> win_item;
+  std::vector<ushort4> win_slot;
+  int win_slots_max = 1, halo_max = 0;
+  std::vector<int> win_lo(nwin, 0), win_n(nwin, 0);
+  {
+    struct Kind { const int32_t* idx; int n, arity; };
+    const Kind kinds[5] = {{d->bond_idx, d->nbonds, 2}, {d->angle_idx, d->nangles, 3}, {d->dihedral_idx, d->ndihedrals, 4},
+                           {d->idx14, d->n14, 2}, {d->improper_idx, d->nimpropers, 4}};
+    for (const Kind& K : kinds)
+      for (int it = 0; it < K.n; ++it)
+        for (int c = 0; c < K.arity; ++c) ++gstart[K.idx[K.arity * it + c] + 1];
+    for (int a = 0; a < N; ++a) gstart[a + 1] += gstart[a];
+    for (int w = 0; w < nwin; ++w) win_slots_max = std::max(win_slots_max, gstart[std::min(N, kLWin * (w + 1))] - gstart[kLWin * w]);
+    if (win_slots_max >= 0xffff || (size_t)win_slots_max * 12 > 200 * 1024) {
+      delete topo; fail(B200MD_ERR_UNSUPPORTED, "a window of 64 atoms carries more bonded contributions than fit in shared memory"); return nullptr;
+    }
+    std::vector<int> cur(gstart.begin(), gstart.end() - 1);
+    std::vector<std::vector<std::pair<uint32_t, ushort4>>> per(nwin);
+    uint32_t g = 0;
+    for (const Kind& K : kinds)
+      for (int it = 0; it < K.n; ++it, ++g) {
+        int wins[4], nw = 0;
+        unsigned short sl[4][4];
+        for (int c = 0; c < K.arity; ++c) {
+          const int a = K.idx[K.arity * it + c], w = a / kLWin;
+          int k = 0;
+          while (k < nw && wins[k] != w) ++k;
+          if (k == nw) { wins[nw++] = w; for (int q = 0; q < 4; ++q) sl[k][q] = 0xffff; }
+          sl[k][c] = (unsigned short)(cur[a]++ - gstart[kLWin * w]);
+        }
+        for (int k = 0; k < nw; ++k) per[wins[k]].push_back({g, make_ushort4(sl[k][0], sl[k][1], sl[k][2], sl[k][3])});
+      }
+    std::vector<int> lo(nwin, N), hi(nwin, -1);  // atoms the items of a window reference: [lo, hi]
+    g = 0;
+    for (const Kind& K : kinds)
+      for (int it = 0; it < K.n; ++it, ++g) {
+        int amin = N, amax = -1;
+        for (int c = 0; c < K.arity; ++c) { amin = std::min(amin, (int)K.idx[K.arity * it + c]); amax = std::max(amax, (int)K.idx[K.arity * it + c]); }
+        for (int c = 0; c < K.arity; ++c) {
+          const int w = K.idx[K.arity * it + c] / kLWin;
+          lo[w] = std::min(lo[w], amin); hi[w] = std::max(hi[w], amax);
+        }
+      }
+    for (int w = 0; w < nwin; ++w) {
+      win_start[w + 1] = win_start[w] + (int)per[w].size();
+      for (const auto& e : per[w]) { win_item.push_back(e.first); win_slot.push_back(e.second); }
+      if (hi[w] >= lo[w] && hi[w] - lo[w] + 1 <= kLHalo) { win_lo[w] = lo[w]; win_n[w] = hi[w] - lo[w] + 1; halo_max = std::max(halo_max, win_n[w]); }
+    }
+    if (win_item.empty()) { win_item.push_back(0); win_slot.push_back(make_ushort4(0xffff, 0xffff, 0xffff, 0xffff)); }
+  }
   BlobBuilder B;
+  const size_t o_wst = B.add(win_start), o_wit = B.add(win_item), o_wsl = B.add(win_slot), o_gst = B.add(gstart), o_wlo = B.add(win_lo), o_wn = B.add(win_n);
   const size_t o_type = B.add(atype), o_q = B.add(charge), o_m = B.add(mass), o_a = B.add(t12a), o_b = B.add(t6b), o_mask = B.add(mask),
                o_bi = B.add(bidx), o_bp = B.add(bprm), o_ai = B.add(aidx), o_ap = B.add(aprm), o_dq = B.add(dq), o_ds = B.add(ds),
                o_dt = B.add(dt), o_i14 = B.add(i14), o_p14 = B.add(p14), o_iq = B.add(iq), o_is = B.add(is), o_it = B.add(it), o_dcs = B.add(dcs), o_ics = B.add(ics), o_t64 = B.add(tab64);
@@ -1328,6 +1386,9 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   L.atom_type = (const int*)(base + o_type); L.charge = (const float*)(base + o_q); L.mass = (const float*)(base + o_m);
   L.tab12a = (const float*)(base + o_a); L.tab6b = (const float*)(base + o_b); L.mask = (const uint32_t*)(base + o_mask);
   L.tab64 = (const double2*)(base + o_t64);
+  L.win_start = (const int*)(base + o_wst); L.win_item = (const uint32_t*)(base + o_wit); L.win_slot = (const ushort4*)(base + o_wsl);
+  L.gstart = (const int*)(base + o_gst); L.nwin = nwin; L.win_slots_max = win_slots_max; L.halo_max = halo_max;
+  L.win_lo = (const int*)(base + o_wlo); L.win_n = (const int*)(base + o_wn);
   L.nbonds = d->nbonds; L.nangles = d->nangles; L.ndih = d->ndihedrals; L.n14 = d->n14; L.nimp = d->nimpropers;
   L.bond_idx = (const int2*)(base + o_bi); L.bond_prm = (const float2*)(base + o_bp);
   L.angle_idx = (const int*)(base + o_ai); L.angle_prm = (const float2*)(base + o_ap);
@@ -1335,12 +1396,16 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   L.idx14 = (const int2*)(base + o_i14); L.prm14 = (const float4*)(base + o_p14);
   L.dih_cs = (const double2*)(base + o_dcs); L.imp_cs = (const double2*)(base + o_ics);
   L.imp_idx = (const int4*)(base + o_iq); L.imp_start = (const int*)(base + o_is); L.imp_term = (const float4*)(base + o_it);
-  const int tab_bytes = 2 * NT * large_tab_stride(NT) * (int)sizeof(float);
-  if (tab_bytes > 40 * 1024) {
-    cudaFuncSetAttribute(large_pairs_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tab_bytes);
-    cudaFuncSetAttribute(large_pairs_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tab_bytes);
-    cudaFuncSetAttribute(large_pairs_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tab_bytes);
-    cudaFuncSetAttribute(large_pairs_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, tab_bytes);
+  const int dyn_bytes = large_dyn_bytes(L);
+  if (dyn_bytes > 200 * 1024) {
+    cudaFree(topo->blob); delete topo;
+    fail(B200MD_ERR_UNSUPPORTED, "type tables + the bonded slots of a 64-atom window exceed shared memory"); return nullptr;
+  }
+  if (dyn_bytes > 32 * 1024) {
+    cudaFuncSetAttribute(large_forces_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_bytes);
+    cudaFuncSetAttribute(large_forces_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_bytes);
+    cudaFuncSetAttribute(large_forces_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_bytes);
+    cudaFuncSetAttribute(large_forces_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_bytes);
   }
   g_last_error.clear();
   return topo;
@@ -1350,7 +1415,7 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
 // accumulator, the per-CTA energy partials, the per-replica energies / kinetic-energy partials / SMD record of the integrator.
 struct LargeWork {
   cudaStream_t st;
-  long long* fbond = nullptr; double* partial = nullptr; double* energies = nullptr; double* ekin = nullptr; double* smd = nullptr;
+  double* partial = nullptr; double* energies = nullptr; double* ekin = nullptr; double* smd = nullptr;
   float* bbox = nullptr;
   int nbonded_blocks = 0, npart = 0, nek = 0;
 };
@@ -1362,10 +1427,11 @@ static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, 
   // FP64 energy partials -- and with it every bit of a replica's result -- does not depend on the replica count of the call
   (void)R;
   w.nbonded_blocks = (int)std::max<long long>(1, std::min<long long>(64, (items + 4 * kLBondedThreads - 1) / (4 * kLBondedThreads)));
-  w.npart = w.nbonded_blocks + L.nwords;
+  w.npart = w.nbonded_blocks + L.nwin;
   w.nek = (L.natoms + 255) / 256;
   auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
-  const size_t b_f = up(sizeof(long long) * 3 * (size_t)R * L.natoms), b_p = up(sizeof(double) * (size_t)R * w.npart * B200MD_NUM_ENERGIES);
+  const size_t b_f = 0;
+  const size_t b_p = up(sizeof(double) * (size_t)R * w.npart * B200MD_NUM_ENERGIES);
   const size_t b_e = integrator ? up(sizeof(double) * (size_t)R * B200MD_NUM_ENERGIES) : 0, b_k = integrator ? up(sizeof(double) * (size_t)R * w.nek) : 0;
   const size_t b_s = (integrator && smd) ? up(sizeof(double) * 2 * (size_t)R) : 0;
   const size_t b_b = up(sizeof(float) * 8 * (size_t)R * L.nwords);
@@ -1378,7 +1444,6 @@ static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, 
   }
   topo->ws_stream = w.st;
   char* base = (char*)topo->ws;
-  w.fbond = (long long*)base; base += b_f;
   w.partial = (double*)base; base += b_p;
   w.bbox = (float*)base; base += b_b;
   if (integrator) {
@@ -1394,7 +1459,8 @@ static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, 
 
 // One Forces.compute over R replicas: zero the accumulator, bonded items, pair tiles (+ the force row), energies.
 static int large_forces(const b200md_topology* topo, const ForceParams& P, int64_t R, const float* pos, const float* box,
-                        float* forces, double* energies, uint32_t* status, double smd_center, bool with_energy, LargeWork& w) {
+                        float* forces, double* energies, uint32_t* status, double smd_center, bool with_energy, LargeWork& w,
+                        bool bbox_ready = false) {
   const LargeTopo& L = topo->ldev;
   cudaStream_t st = w.st;
   const int gy = (int)std::min<int64_t>(R, 65535);
@@ -1404,38 +1470,39 @@ static int large_forces(const b200md_topology* topo, const ForceParams& P, int64
     CUDA_TRY(cudaEventCreateWithFlags(&topo->ev_fork, cudaEventDisableTiming));
     CUDA_TRY(cudaEventCreateWithFlags(&topo->ev_join, cudaEventDisableTiming));
   }
-  cudaStream_t sb = overlap_on ? topo->aux : st;  // stream of the bonded kernel
-  if (overlap_on) {
-    CUDA_TRY(cudaEventRecord(topo->ev_fork, st));
-    CUDA_TRY(cudaStreamWaitEvent(sb, topo->ev_fork, 0));
+  // Forces: one launch (large_forces_kernel: bonded windows + pair tiles).  Bonded energies (FP64, item-centric) only read
+  // the positions: on a report step they run beside it on a second stream.
+  cudaStream_t sb = overlap_on ? topo->aux : st;
+  if (with_energy) {
+    if (overlap_on) {
+      CUDA_TRY(cudaEventRecord(topo->ev_fork, st));
+      CUDA_TRY(cudaStreamWaitEvent(sb, topo->ev_fork, 0));
+    }
+    large_bonded_energy_kernel<<<dim3(w.nbonded_blocks, gy), kLBondedThreads, 0, sb>>>(L, P, R, pos, box, w.partial, w.npart,
+                                                                                      P.smd_centers, smd_center);
+    if (overlap_on) CUDA_TRY(cudaEventRecord(topo->ev_join, sb));
+    g_launches.fetch_add(1);
   }
-  CUDA_TRY(cudaMemsetAsync(w.fbond, 0, sizeof(long long) * 3 * (size_t)R * L.natoms, sb));
-  large_bonded_kernel<<<dim3(w.nbonded_blocks, gy), kLBondedThreads, 0, sb>>>(L, P, R, pos, box, w.fbond, w.partial, w.npart,
-                                                                             P.smd_centers, smd_center, w.smd);
-  if (overlap_on) CUDA_TRY(cudaEventRecord(topo->ev_join, sb));
-  long long* fb_pairs = overlap_on ? nullptr : w.fbond;
-  const int tab_bytes = 2 * L.ntypes * large_tab_stride(L.ntypes) * (int)sizeof(float);
-  const dim3 grid(L.nwords, gy);
+  const int dyn_bytes = large_dyn_bytes(L);
+  const dim3 grid(L.nwin, gy);
   const bool pairs_on = (P.terms & (B200MD_T_ELECTROSTATICS | B200MD_T_LJ | B200MD_T_REPULSION | B200MD_T_REPULSIONCG)) != 0;
   const float* bbox = nullptr;
   if (P.has_cutoff && pairs_on && L.nwords > 4) {  // tile bounding boxes for the cutoff skip (vacuum replicas use them)
-    large_bbox_kernel<<<dim3((L.nwords + 3) / 4, gy), 128, 0, st>>>(L, R, pos, w.bbox);
-    g_launches.fetch_add(1);
+    if (!bbox_ready) {  // (the integrator's fused half-kick kernel has written them already)
+      large_bbox_kernel<<<dim3((L.nwords + 3) / 4, gy), 128, 0, st>>>(L, R, pos, w.bbox);
+      g_launches.fetch_add(1);
+    }
     bbox = w.bbox;
   }
-#define B200MD_LAUNCH_LPAIRS(M, E) \
-  large_pairs_kernel<M, E><<<grid, kLThreads, tab_bytes, st>>>(L, P, R, pos, box, fb_pairs, forces, w.partial, w.npart, w.nbonded_blocks, status, bbox)
+#define B200MD_LAUNCH_LPAIRS(M, E)                                                                                                         \
+  large_forces_kernel<M, E><<<grid, kLThreads, dyn_bytes, st>>>(L, P, R, pos, box, forces, w.partial, w.npart, w.nbonded_blocks, status, bbox, \
+                                                                P.smd_centers, smd_center, w.smd)
   if (P.has_cutoff) { if (with_energy) B200MD_LAUNCH_LPAIRS(1, true); else B200MD_LAUNCH_LPAIRS(1, false); }
   else { if (with_energy) B200MD_LAUNCH_LPAIRS(0, true); else B200MD_LAUNCH_LPAIRS(0, false); }
 #undef B200MD_LAUNCH_LPAIRS
-  g_launches.fetch_add(2);
-  if (overlap_on) {  // join: the bonded accumulator and its energy partials are complete from here on
-    CUDA_TRY(cudaStreamWaitEvent(st, topo->ev_join, 0));
-    const long long n3 = 3ll * R * L.natoms;
-    large_combine_kernel<<<(unsigned)((n3 + 255) / 256), 256, 0, st>>>(n3, w.fbond, forces);
-    g_launches.fetch_add(1);
-  }
+  g_launches.fetch_add(1);
   if (with_energy) {
+    if (overlap_on) CUDA_TRY(cudaStreamWaitEvent(st, topo->ev_join, 0));  // join: the bonded energy partials are complete
     const long long n = (long long)R * B200MD_NUM_ENERGIES;
     large_finish_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(R, w.partial, w.npart, energies);
     g_launches.fetch_add(1);
@@ -1467,15 +1534,28 @@ static int large_integrate(const b200md_topology* topo, const ForceParams& P, co
   if (status) CUDA_TRY(cudaMemsetAsync(status, 0, sizeof(uint32_t) * (size_t)R, st));
   const long long natom = (long long)R * L.natoms;
   const size_t frame = sizeof(float) * 3 * (size_t)natom;
+  // Between two force evaluations the second half-kick of step s, the first half-kick of step s + 1 and the tile bounding
+  // boxes are ONE launch (large_vv2_kernel with fuse_next) -- except where pos must stay x(t + dt): snapshot steps and the
+  // last step of the call.
+  const bool want_bbox = P.has_cutoff && L.nwords > 4 &&
+                         (P.terms & (B200MD_T_ELECTROSTATICS | B200MD_T_LJ | B200MD_T_REPULSION | B200MD_T_REPULSIONCG)) != 0;
+  bool fused_prev = false;
   for (int s = 0; s < I.nsteps; ++s) {
     const unsigned long long gstep = I.step0 + (unsigned long long)s;
     const bool report = (I.energy_every > 0 && (s + 1) % I.energy_every == 0) || s == I.nsteps - 1;
-    large_vv1_kernel<<<(unsigned)((natom + 255) / 256), 256, 0, st>>>(L, I.dt, R, pos, vel, forces);
+    if (!fused_prev) {
+      large_vv1_kernel<<<(unsigned)((natom + 255) / 256), 256, 0, st>>>(L, I.dt, R, pos, vel, forces);
+      g_launches.fetch_add(1);
+    }
     const double center = (double)P.smd_c0 + (double)P.smd_rate * (double)(gstep + 1);
-    rc = large_forces(topo, P, R, pos, box, forces, w.energies, status, center, report, w);
+    rc = large_forces(topo, P, R, pos, box, forces, w.energies, status, center, report, w, fused_prev && want_bbox);
     if (rc) return rc;
-    large_vv2_kernel<<<dim3(w.nek, (unsigned)std::min<int64_t>(R, 65535)), 256, 0, st>>>(L, I, gstep, R, vel, forces, pos, report ? w.ekin : nullptr, status);
-    g_launches.fetch_add(2);
+    const bool snap = I.snapshot_every > 0 && snapshots != nullptr && (s + 1) % I.snapshot_every == 0;
+    const bool fuse = s + 1 < I.nsteps && !snap;
+    large_vv2_kernel<<<dim3(w.nek, (unsigned)std::min<int64_t>(R, 65535)), 256, 0, st>>>(L, I, gstep, R, vel, forces, pos, report ? w.ekin : nullptr,
+                                                                                       status, fuse ? 1 : 0, (fuse && want_bbox) ? w.bbox : nullptr);
+    fused_prev = fuse;
+    g_launches.fetch_add(1);
     if (report && observables != nullptr) {
       const long long slot = I.energy_every > 0 ? s / I.energy_every : 0;
       large_observe_kernel<<<(unsigned)((R + 127) / 128), 128, 0, st>>>(R, w.energies, w.ekin, w.nek, w.smd,

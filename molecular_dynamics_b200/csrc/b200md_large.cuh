@@ -28,8 +28,6 @@ namespace b200md {
 
 constexpr int kLThreads = 128;  // pair kernel: 4 warps on one i-block
 constexpr int kLBondedThreads = 128;
-constexpr double kLFixScale = 1073741824.0;  // 2^30 per kcal/mol/A: range +-8.6e9, resolution 9.3e-10
-constexpr double kLFixInv = 1.0 / 1073741824.0;
 constexpr double kLElec = 332.06371307417066;
 
 struct LargeTopo {
@@ -48,82 +46,206 @@ struct LargeTopo {
   const double2* dih_cs;  const double2* imp_cs;                          // (cos phi0, sin phi0) per term; kind: 0 AMBER, 1 harmonic, 2 AMBER with integer per 1..6
   const int2* idx14;      const float4* prm14;                            // A, B, scnb, scee
   const int4* imp_idx;    const int* imp_start;  const float4* imp_term;
+  // bonded forces by WINDOWS of kLWin atoms (large_bonded_forces_kernel): window w evaluates the entries
+  // [win_start[w], win_start[w + 1]) = every item that touches one of its atoms (index into the concatenated list
+  // [bonds | angles | dihedrals | 1-4 | impropers]); win_slot holds, per role of the item, the shared-memory slot of that
+  // contribution (0xffff: the atom belongs to another window).  Slots are atom-major: atom a of the window owns
+  // [gstart[a], gstart[a + 1]) - gstart[first atom of the window], in the fixed order bonds, angles, dihedrals, 1-4, impropers.
+  const int* win_start;      // [nwin + 1]
+  const uint32_t* win_item;  // [entries]
+  const ushort4* win_slot;   // [entries]
+  const int* gstart;         // [natoms + 1]
+  const int* win_lo;         // [nwin] first atom the window's items reference
+  const int* win_n;          // [nwin] how many atoms from win_lo they span, 0 when more than kLHalo (then read from HBM)
+  int nwin, win_slots_max, halo_max;  // windows; largest slot count / staged span of a window (shared memory = 12 bytes x each)
 };
+constexpr int kLWin = 64, kLHalo = 320;
 
-struct d3 { double x, y, z; };
-__device__ __forceinline__ d3 dsub(d3 a, d3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
-__device__ __forceinline__ d3 dcross(d3 a, d3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
-__device__ __forceinline__ double ddot(d3 a, d3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
-__device__ __forceinline__ d3 dscale(d3 a, double s) { return {a.x * s, a.y * s, a.z * s}; }
-__device__ __forceinline__ d3 lpos(const float* p, int i) { return {(double)p[3 * i], (double)p[3 * i + 1], (double)p[3 * i + 2]}; }
+// Bonded items are written once, on a scalar type T: T = float evaluates the FORCES (what every step needs; the
+// one-thread-per-item kernel was FP64 throughout in round 1 and, at 109 us per step of 256 x 1 040 atoms, the largest
+// kernel of a cutoff-mode step), T = double evaluates the ENERGIES of report steps (FORCE = false: no atomics).  An
+// ENERGY launch runs both, so the forces -- and with them the trajectory -- do not depend on how often energies are recorded.
+template <typename T> struct v3t { T x, y, z; };
+template <typename T> __device__ __forceinline__ v3t<T> vsub(v3t<T> a, v3t<T> b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+template <typename T> __device__ __forceinline__ v3t<T> vcross(v3t<T> a, v3t<T> b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+template <typename T> __device__ __forceinline__ T vdot(v3t<T> a, v3t<T> b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+template <typename T> __device__ __forceinline__ v3t<T> vscale(v3t<T> a, T s) { return {a.x * s, a.y * s, a.z * s}; }
+template <typename T> __device__ __forceinline__ v3t<T> vpos(const float* p, int i) { return {(T)p[3 * i], (T)p[3 * i + 1], (T)p[3 * i + 2]}; }
+__device__ __forceinline__ float trint(float x) { return rintf(x); }
+__device__ __forceinline__ double trint(double x) { return rint(x); }
+// 1 / x, 1 / sqrt(x): double for the energy path, the hardware approximations with one Newton step where the
+// value is raised to a power in float (the force path, like the on-chip kernels: ~1 ulp, a tenth of the instructions of the
+// IEEE sequences nvcc emits without fast-math)
+__device__ __forceinline__ double trcp(double x) { return 1.0 / x; }
+__device__ __forceinline__ double trsqrt(double x) { return drsqrt(x); }  // hardware seed + one third-order step: < 1 ulp of FP64
+__device__ __forceinline__ float trcp(float x) { const float y = fast_rcp(x); return y * (2.0f - x * y); }
+__device__ __forceinline__ float trsqrt(float x) { return rsqrt_nr(x); }
 // wrap_dist (forces.py:358-363): every component, unless the whole box diagonal is zero
-__device__ __forceinline__ d3 lwrap(d3 d, const double* b, bool vac) {
+template <typename T> __device__ __forceinline__ v3t<T> vwrap(v3t<T> d, const T* b, bool vac) {
   if (vac) return d;
-  d.x -= b[0] * rint(d.x / b[0]); d.y -= b[1] * rint(d.y / b[1]); d.z -= b[2] * rint(d.z / b[2]);
+  d.x -= b[0] * trint(d.x / b[0]); d.y -= b[1] * trint(d.y / b[1]); d.z -= b[2] * trint(d.z / b[2]);
   return d;
 }
-__device__ __forceinline__ void ladd(long long* f, int i, d3 a, double s) {
-  atomicAdd((unsigned long long*)(f + 3 * i), (unsigned long long)__double2ll_rn(s * a.x * kLFixScale));
-  atomicAdd((unsigned long long*)(f + 3 * i + 1), (unsigned long long)__double2ll_rn(s * a.y * kLFixScale));
-  atomicAdd((unsigned long long*)(f + 3 * i + 2), (unsigned long long)__double2ll_rn(s * a.z * kLFixScale));
+// Where the force vectors of an item go.  Round 1 added each to a per-atom int64 fixed-point accumulator with three 64-bit
+// GLOBAL atomics (~18 M per step of 256 x 1 040 atoms: the kernel sat at ~95 us whatever its arithmetic cost).  Measured
+// alternatives: private slots in global memory + a gather kernel (5.8 M scattered 12-byte stores and their re-read:
+// 63 + 41 us); an atom-centric kernel that re-evaluates an item for every atom it touches (lanes of a warp sit at different
+// kinds: 304 us).  Kept: slots in SHARED memory, one CTA per window of kLWin atoms -- the CTA evaluates every item that
+// touches the window (items across a window edge are evaluated by both windows), writes the vectors of ITS atoms to their
+// private slots, and sums each atom's slots in a fixed order: no atomic, no global scratch, exact fp32, any magnitude.
+struct WindowSink {
+  float* slots;  // shared memory, float3 per slot
+  ushort4 sl;    // slot of each role, 0xffff = not in this window
+};
+struct NoSink {};
+template <typename T> __device__ __forceinline__ void lput(WindowSink& f, int role, v3t<T> a, T s) {
+  const unsigned sidx = role == 0 ? f.sl.x : (role == 1 ? f.sl.y : (role == 2 ? f.sl.z : f.sl.w));
+  if (sidx != 0xffffu) { f.slots[3 * sidx] = (float)(s * a.x); f.slots[3 * sidx + 1] = (float)(s * a.y); f.slots[3 * sidx + 2] = (float)(s * a.z); }
 }
+template <typename T> __device__ __forceinline__ void lput(NoSink&, int, v3t<T>, T) {}
 
-// evaluate_torsion (forces.py:540-602) for one quadruple with its terms; returns the energy.
+// evaluate_torsion (forces.py:540-602) for one quadruple with its terms; returns the energy, adds the forces when FORCE.
 // Terms of the AMBER branch with an integer periodicity 1..6 (marker 2) never form phi: cos / sin(n phi) come from
-// (cos phi + i sin phi)^n and cos / sin(phi0) from the host (FP64), which takes atan2, sin and cos out of the common case
-// (the FP64 transcendentals were most of this kernel's instructions).  Other terms use phi = -atan2(sin, cos) as written.
-__device__ __forceinline__ double ltorsion(const float* p, const double* bx, bool vac, int4 q, const float4* term,
-                                           const double2* term_cs, int t0, int t1, long long* f) {
-  const d3 r12 = lwrap(dsub(lpos(p, q.x), lpos(p, q.y)), bx, vac);
-  const d3 r23 = lwrap(dsub(lpos(p, q.y), lpos(p, q.z)), bx, vac);
-  const d3 r34 = lwrap(dsub(lpos(p, q.z), lpos(p, q.w)), bx, vac);
-  const d3 cA = dcross(r12, r23), cB = dcross(r23, r34), cC = dcross(r23, cA);
-  const double nA = sqrt(ddot(cA, cA)), nB = sqrt(ddot(cB, cB)), nC = sqrt(ddot(cC, cC));
-  const d3 ncB = dscale(cB, 1.0 / nB);
-  const double cosPhi = ddot(cA, ncB) / nA, sinPhi = ddot(cC, ncB) / nC;  // forces.py:548-551; phi = -atan2(sinPhi, cosPhi)
-  const double hinv = 1.0 / sqrt(cosPhi * cosPhi + sinPhi * sinPhi);
-  const double c1 = cosPhi * hinv, s1 = -sinPhi * hinv;  // cos phi, sin phi
-  double phi = 0.0;
+// (cos phi + i sin phi)^n and cos / sin(phi0) from the host (FP64).  Other terms use phi = -atan2(sin, cos) as written.
+template <typename T, bool FORCE, typename SINK>
+__device__ __forceinline__ T ltorsion(const float* p, const T* bx, bool vac, int4 q, const float4* term,
+                                      const double2* term_cs, int t0, int t1, SINK& f) {
+  typedef v3t<T> V;
+  const V r12 = vwrap(vsub(vpos<T>(p, q.x), vpos<T>(p, q.y)), bx, vac);
+  const V r23 = vwrap(vsub(vpos<T>(p, q.y), vpos<T>(p, q.z)), bx, vac);
+  const V r34 = vwrap(vsub(vpos<T>(p, q.z), vpos<T>(p, q.w)), bx, vac);
+  const V cA = vcross(r12, r23), cB = vcross(r23, r34), cC = vcross(r23, cA);
+  const T inA = trsqrt(vdot(cA, cA)), inB = trsqrt(vdot(cB, cB)), inC = trsqrt(vdot(cC, cC));
+  const V ncB = vscale(cB, inB);
+  const T cosPhi = vdot(cA, ncB) * inA, sinPhi = vdot(cC, ncB) * inC;  // forces.py:548-551; phi = -atan2(sinPhi, cosPhi)
+  const T hinv = trsqrt(cosPhi * cosPhi + sinPhi * sinPhi);
+  const T c1 = cosPhi * hinv, s1 = -sinPhi * hinv;  // cos phi, sin phi
+  T phi = 0;
   bool have_phi = false;
-  double pot = 0.0, coeff = 0.0;
+  T pot = 0, coeff = 0;
   for (int t = t0; t < t1; ++t) {
     const float4 tp = __ldg(term + t);
-    const double k0 = tp.x, phi0 = tp.y, per = tp.z;
+    const T k0 = tp.x, phi0 = tp.y, per = tp.z;
     if (tp.w == 2.0f) {  // AMBER branch, integer periodicity: k (1 + cos(n phi - phi0)), forces.py:565-569
       const double2 cs0 = term_cs[t];
       const int n = (int)tp.z;
-      double cn = c1, sn = s1;
+      T cn = c1, sn = s1;
       for (int k = 1; k < n; ++k) {
-        const double cc = cn * c1 - sn * s1;
+        const T cc = cn * c1 - sn * s1;
         sn = sn * c1 + cn * s1;
         cn = cc;
       }
-      pot += k0 * (1.0 + (cn * cs0.x + sn * cs0.y));
-      coeff += -per * k0 * (sn * cs0.x - cn * cs0.y);
+      pot += k0 * ((T)1 + (cn * (T)cs0.x + sn * (T)cs0.y));
+      coeff += -per * k0 * (sn * (T)cs0.x - cn * (T)cs0.y);
       continue;
     }
     if (!have_phi) { phi = -atan2(sinPhi, cosPhi); have_phi = true; }
     if (tp.w == 0.0f) {  // AMBER branch, any periodicity
-      const double ad = per * phi - phi0;
-      pot += k0 * (1.0 + cos(ad));
+      const T ad = per * phi - phi0;
+      pot += k0 * ((T)1 + cos(ad));
       coeff += -per * k0 * sin(ad);
     } else {  // CHARMM harmonic branch, forces.py:570-576
-      double ad = phi - phi0;
-      if (ad < -M_PI) ad += 2.0 * M_PI; else if (ad > M_PI) ad -= 2.0 * M_PI;
+      T ad = phi - phi0;
+      if (ad < (T)-M_PI) ad += (T)(2.0 * M_PI); else if (ad > (T)M_PI) ad -= (T)(2.0 * M_PI);
       pot += k0 * ad * ad;
-      coeff += 2.0 * k0 * ad;
+      coeff += (T)2 * k0 * ad;
     }
   }
-  const double nd2 = sqrt(ddot(r23, r23)), n2d2 = nd2 * nd2;  // OpenMM projection, forces.py:582-600
-  const double ff0 = (-coeff * nd2) / (nA * nA), ff1 = ddot(r12, r23) / n2d2, ff2 = ddot(r34, r23) / n2d2;
-  const double ff3 = (coeff * nd2) / (nB * nB);
-  const d3 f0 = dscale(cA, ff0), f3 = dscale(cB, ff3);
-  const d3 s = dsub(dscale(f0, ff1), dscale(f3, ff2));
-  ladd(f, q.x, f0, -1.0);
-  ladd(f, q.y, {f0.x + s.x, f0.y + s.y, f0.z + s.z}, 1.0);
-  ladd(f, q.z, {f3.x - s.x, f3.y - s.y, f3.z - s.z}, 1.0);
-  ladd(f, q.w, f3, -1.0);
+  if (FORCE) {
+    const T n23sq = vdot(r23, r23), in23 = trsqrt(n23sq), nd2 = n23sq * in23, in2d2 = in23 * in23;  // OpenMM projection, forces.py:582-600
+    const T ff0 = (-coeff * nd2) * (inA * inA), ff1 = vdot(r12, r23) * in2d2, ff2 = vdot(r34, r23) * in2d2;
+    const T ff3 = (coeff * nd2) * (inB * inB);
+    const V f0 = vscale(cA, ff0), f3 = vscale(cB, ff3);
+    const V s = vsub(vscale(f0, ff1), vscale(f3, ff2));
+    lput<T>(f, 0, f0, (T)-1);
+    lput<T>(f, 1, {f0.x + s.x, f0.y + s.y, f0.z + s.z}, (T)1);
+    lput<T>(f, 2, {f3.x - s.x, f3.y - s.y, f3.z - s.z}, (T)1);
+    lput<T>(f, 3, f3, (T)-1);
+  }
   return pot;
+}
+
+// One bonded item g of the concatenated list [bonds | angles | dihedrals | 1-4 pairs | impropers] (EVERY kind present: the
+// callers skip the kinds a call has switched off): adds its energy to the slot it is booked under, hands its force vectors
+// to the sink when FORCE.
+struct LItemRanges { int e1, e2, e3, e4, e5; bool lj14, el14; uint32_t on; /* bit k: kind k is evaluated */ };
+__device__ __forceinline__ LItemRanges litem_ranges(const LargeTopo& T, uint32_t terms) {
+  LItemRanges G;
+  G.e1 = T.nbonds; G.e2 = G.e1 + T.nangles; G.e3 = G.e2 + T.ndih; G.e4 = G.e3 + T.n14; G.e5 = G.e4 + T.nimp;
+  G.lj14 = terms & B200MD_T_LJ; G.el14 = terms & B200MD_T_ELECTROSTATICS;
+  G.on = ((terms & B200MD_T_BONDS) ? 1u : 0u) | ((terms & B200MD_T_ANGLES) ? 2u : 0u) | ((terms & B200MD_T_DIHEDRALS) ? 4u : 0u) |
+         (((terms & B200MD_T_14) && (G.lj14 || G.el14)) ? 8u : 0u) | ((terms & B200MD_T_IMPROPERS) ? 16u : 0u);
+  return G;
+}
+__device__ __forceinline__ int litem_kind(const LItemRanges& G, int g) { return (g >= G.e1) + (g >= G.e2) + (g >= G.e3) + (g >= G.e4); }
+template <typename T, bool FORCE, typename SINK>
+__device__ __forceinline__ void litem(const LargeTopo& T_, const ForceParams& P, const LItemRanges& G, int g, const float* p,
+                                      const T* bx, bool vac, SINK& f, T* e /* [8] */) {
+  typedef v3t<T> V;
+  if (g < G.e1) {  // forces.py:111-132, 492-501
+    const int2 ij = __ldg(T_.bond_idx + g);
+    const float2 kp = __ldg(T_.bond_prm + g);
+    const V d = vwrap(vsub(vpos<T>(p, ij.x), vpos<T>(p, ij.y)), bx, vac);
+    const T r2b = vdot(d, d), idist = trsqrt(r2b), dist = r2b * idist;
+    if (P.has_cutoff && !(dist <= (T)P.rc)) {  // forces.py:117-125: dropped (its slots must still read as zero)
+      if (FORCE) { const V zero = {(T)0, (T)0, (T)0}; lput<T>(f, 0, zero, (T)0); lput<T>(f, 1, zero, (T)0); }
+      return;
+    }
+    const T x = dist - (T)kp.y;
+    e[B200MD_E_BONDS] += (T)kp.x * x * x;
+    if (FORCE) {
+      const T c = (T)2 * (T)kp.x * x * idist;
+      lput<T>(f, 0, d, -c);
+      lput<T>(f, 1, d, c);
+    }
+  } else if (g < G.e2) {  // forces.py:134-145, 504-537
+    const int a = g - G.e1;
+    const int q0 = __ldg(T_.angle_idx + 3 * a), q1 = __ldg(T_.angle_idx + 3 * a + 1), q2 = __ldg(T_.angle_idx + 3 * a + 2);
+    const float2 kp = __ldg(T_.angle_prm + a);
+    const V r21 = vwrap(vsub(vpos<T>(p, q0), vpos<T>(p, q1)), bx, vac);
+    const V r23 = vwrap(vsub(vpos<T>(p, q2), vpos<T>(p, q1)), bx, vac);
+    const T n23i = trsqrt(vdot(r23, r23)), n21i = trsqrt(vdot(r21, r21));
+    T ct = vdot(r23, r21) * n21i * n23i;
+    ct = ct < (T)-1 ? (T)-1 : (ct > (T)1 ? (T)1 : ct);
+    const T dth = acos(ct) - (T)kp.y;
+    e[B200MD_E_ANGLES] += (T)kp.x * dth * dth;
+    if (FORCE) {
+      const T st2 = (T)1 - ct * ct;
+      const T coef = st2 > (T)0 ? (T)-2 * (T)kp.x * dth * trsqrt(st2) : (T)0;  // 0 where sin(theta) == 0 (forces.py:521-523)
+      const V f0 = vscale(vsub(vscale(r21, ct * n21i), vscale(r23, n23i)), coef * n21i);
+      const V f2 = vscale(vsub(vscale(r23, ct * n23i), vscale(r21, n21i)), coef * n23i);
+      lput<T>(f, 0, f0, (T)1);
+      lput<T>(f, 2, f2, (T)1);
+      lput<T>(f, 1, {f0.x + f2.x, f0.y + f2.y, f0.z + f2.z}, (T)-1);
+    }
+  } else if (g < G.e3) {  // forces.py:147-174
+    const int d = g - G.e2;
+    e[B200MD_E_DIHEDRALS] += ltorsion<T, FORCE, SINK>(p, bx, vac, __ldg(T_.dih_idx + d), T_.dih_term, T_.dih_cs, __ldg(T_.dih_start + d), __ldg(T_.dih_start + d + 1), f);
+  } else if (g < G.e4) {  // forces.py:176-226: never cut, switched or reaction-field corrected
+    const int k = g - G.e3;
+    const int2 ij = __ldg(T_.idx14 + k);
+    const float4 q = __ldg(T_.prm14 + k);
+    const V d = vwrap(vsub(vpos<T>(p, ij.x), vpos<T>(p, ij.y)), bx, vac);
+    const T r2 = vdot(d, d), rinv1 = trsqrt(r2), rinv2 = rinv1 * rinv1, rinv6 = rinv2 * rinv2 * rinv2;
+    T c = 0;  // -(dE/dr) / r
+    if (G.lj14) {
+      const T iscnb = trcp((T)q.z);
+      e[B200MD_E_LJ] += ((T)q.x * rinv6 * rinv6 - (T)q.y * rinv6) * iscnb;
+      c += ((T)12 * (T)q.x * rinv6 * rinv6 - (T)6 * (T)q.y * rinv6) * rinv2 * iscnb;
+    }
+    if (G.el14) {
+      const T pot = (T)kLElec * (T)__ldg(T_.charge + ij.x) * (T)__ldg(T_.charge + ij.y) * rinv1 * trcp((T)q.w);
+      e[B200MD_E_ELECTROSTATICS] += pot;
+      c += pot * rinv2;
+    }
+    if (FORCE) {
+      lput<T>(f, 0, d, c);
+      lput<T>(f, 1, d, -c);
+    }
+  } else {  // forces.py:228-255
+    const int d = g - G.e4;
+    e[B200MD_E_IMPROPERS] += ltorsion<T, FORCE, SINK>(p, bx, vac, __ldg(T_.imp_idx + d), T_.imp_term, T_.imp_cs, __ldg(T_.imp_start + d), __ldg(T_.imp_start + d + 1), f);
+  }
 }
 
 // FP64 block reduction of `n` values per thread in a fixed order; result valid in thread 0
@@ -152,99 +274,32 @@ __device__ __forceinline__ void lreduce(double (&e)[NV], double* sred /* [THREAD
   __syncthreads();
 }
 
+// Bonded ENERGIES (report steps / Forces.compute with energies), FP64, item-centric: one thread per item, no forces.
 // grid (nblk, min(R, 65535)); partial[(r * npart + blockIdx.x) * 8 + slot]
 __global__ void __launch_bounds__(kLBondedThreads)
-large_bonded_kernel(const LargeTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
-                    const float* __restrict__ box, long long* __restrict__ fbond, double* __restrict__ partial,
-                    const int npart, const float* __restrict__ smd_centers, const double smd_center, double* __restrict__ smd_rec) {
+large_bonded_energy_kernel(const LargeTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
+                           const float* __restrict__ box, double* __restrict__ partial, const int npart,
+                           const float* __restrict__ smd_centers, const double smd_center) {
   __shared__ double sred[(kLBondedThreads / 32) * B200MD_NUM_ENERGIES];
   const int tid = threadIdx.x;
   const int N = T.natoms;
-  const uint32_t terms = P.terms;
-  const int nb = (terms & B200MD_T_BONDS) ? T.nbonds : 0;
-  const int na = (terms & B200MD_T_ANGLES) ? T.nangles : 0;
-  const int nd = (terms & B200MD_T_DIHEDRALS) ? T.ndih : 0;
-  const bool lj14 = terms & B200MD_T_LJ, el14 = terms & B200MD_T_ELECTROSTATICS;
-  const int n4 = ((terms & B200MD_T_14) && (lj14 || el14)) ? T.n14 : 0;
-  const int ni = (terms & B200MD_T_IMPROPERS) ? T.nimp : 0;
-  const int e1 = nb, e2 = e1 + na, e3 = e2 + nd, e4 = e3 + n4, e5 = e4 + ni;
+  const LItemRanges G = litem_ranges(T, P.terms);
+  NoSink none;
   for (long long r = blockIdx.y; r < R; r += gridDim.y) {
     const float* p = pos + r * N * 3;
-    long long* f = fbond + r * N * 3;
-    double bx[3] = {0.0, 0.0, 0.0};
-    if (box) { bx[0] = __ldg(box + r * 9); bx[1] = __ldg(box + r * 9 + 4); bx[2] = __ldg(box + r * 9 + 8); }
-    const bool vac = bx[0] == 0.0 && bx[1] == 0.0 && bx[2] == 0.0;
+    double bxd[3] = {0.0, 0.0, 0.0};
+    if (box) { bxd[0] = __ldg(box + r * 9); bxd[1] = __ldg(box + r * 9 + 4); bxd[2] = __ldg(box + r * 9 + 8); }
+    const bool vac = bxd[0] == 0.0 && bxd[1] == 0.0 && bxd[2] == 0.0;
     double e[B200MD_NUM_ENERGIES];
 #pragma unroll
     for (int k = 0; k < B200MD_NUM_ENERGIES; ++k) e[k] = 0.0;
-    for (int g = blockIdx.x * kLBondedThreads + tid; g < e5; g += gridDim.x * kLBondedThreads) {
-      if (g < e1) {  // forces.py:111-132, 492-501
-        const int2 ij = __ldg(T.bond_idx + g);
-        const float2 kp = __ldg(T.bond_prm + g);
-        const d3 d = lwrap(dsub(lpos(p, ij.x), lpos(p, ij.y)), bx, vac);
-        const double dist = sqrt(ddot(d, d));
-        if (P.has_cutoff && !(dist <= (double)P.rc)) continue;
-        const double x = dist - (double)kp.y;
-        e[B200MD_E_BONDS] += (double)kp.x * x * x;
-        const double c = 2.0 * (double)kp.x * x / dist;
-        ladd(f, ij.x, d, -c);
-        ladd(f, ij.y, d, c);
-      } else if (g < e2) {  // forces.py:134-145, 504-537
-        const int a = g - e1;
-        const int q0 = __ldg(T.angle_idx + 3 * a), q1 = __ldg(T.angle_idx + 3 * a + 1), q2 = __ldg(T.angle_idx + 3 * a + 2);
-        const float2 kp = __ldg(T.angle_prm + a);
-        const d3 r21 = lwrap(dsub(lpos(p, q0), lpos(p, q1)), bx, vac);
-        const d3 r23 = lwrap(dsub(lpos(p, q2), lpos(p, q1)), bx, vac);
-        const double n23i = 1.0 / sqrt(ddot(r23, r23)), n21i = 1.0 / sqrt(ddot(r21, r21));
-        double ct = ddot(r23, r21) * n21i * n23i;
-        ct = ct < -1.0 ? -1.0 : (ct > 1.0 ? 1.0 : ct);
-        const double dth = acos(ct) - (double)kp.y;
-        e[B200MD_E_ANGLES] += (double)kp.x * dth * dth;
-        const double st = sqrt(1.0 - ct * ct);
-        const double coef = st != 0.0 ? -2.0 * (double)kp.x * dth / st : 0.0;
-        const d3 f0 = dscale(dsub(dscale(r21, ct * n21i), dscale(r23, n23i)), coef * n21i);
-        const d3 f2 = dscale(dsub(dscale(r23, ct * n23i), dscale(r21, n21i)), coef * n23i);
-        ladd(f, q0, f0, 1.0);
-        ladd(f, q2, f2, 1.0);
-        ladd(f, q1, {f0.x + f2.x, f0.y + f2.y, f0.z + f2.z}, -1.0);
-      } else if (g < e3) {  // forces.py:147-174
-        const int d = g - e2;
-        e[B200MD_E_DIHEDRALS] += ltorsion(p, bx, vac, __ldg(T.dih_idx + d), T.dih_term, T.dih_cs, __ldg(T.dih_start + d), __ldg(T.dih_start + d + 1), f);
-      } else if (g < e4) {  // forces.py:176-226: never cut, switched or reaction-field corrected
-        const int k = g - e3;
-        const int2 ij = __ldg(T.idx14 + k);
-        const float4 q = __ldg(T.prm14 + k);
-        const d3 d = lwrap(dsub(lpos(p, ij.x), lpos(p, ij.y)), bx, vac);
-        const double r2 = ddot(d, d), rinv2 = 1.0 / r2, rinv6 = rinv2 * rinv2 * rinv2, rinv1 = sqrt(rinv2);
-        double c = 0.0;  // -(dE/dr) / r
-        if (lj14) {
-          e[B200MD_E_LJ] += ((double)q.x * rinv6 * rinv6 - (double)q.y * rinv6) / (double)q.z;
-          c += (12.0 * (double)q.x * rinv6 * rinv6 - 6.0 * (double)q.y * rinv6) * rinv2 / (double)q.z;
-        }
-        if (el14) {
-          const double pot = kLElec * (double)__ldg(T.charge + ij.x) * (double)__ldg(T.charge + ij.y) * rinv1 / (double)q.w;
-          e[B200MD_E_ELECTROSTATICS] += pot;
-          c += pot * rinv2;
-        }
-        ladd(f, ij.x, d, c);
-        ladd(f, ij.y, d, -c);
-      } else {  // forces.py:228-255
-        const int d = g - e4;
-        e[B200MD_E_IMPROPERS] += ltorsion(p, bx, vac, __ldg(T.imp_idx + d), T.imp_term, T.imp_cs, __ldg(T.imp_start + d), __ldg(T.imp_start + d + 1), f);
-      }
-    }
-    if (P.smd_on && blockIdx.x == 0 && tid == 0) {  // potcalc.py:75-89, not wrapped
+    for (int g = blockIdx.x * kLBondedThreads + tid; g < G.e5; g += gridDim.x * kLBondedThreads)
+      if (((G.on >> litem_kind(G, g)) & 1u)) litem<double, false, NoSink>(T, P, G, g, p, bxd, vac, none, e);
+    if (P.smd_on && blockIdx.x == 0 && tid == 0) {
       const double center = smd_centers ? (double)__ldg(smd_centers + r) : smd_center;
-      const d3 d = dsub(lpos(p, P.smd_a2), lpos(p, P.smd_a1));
-      const double dist = sqrt(ddot(d, d)), dev = center - dist;
+      const v3t<double> d = vsub(vpos<double>(p, P.smd_a2), vpos<double>(p, P.smd_a1));
+      const double dev = center - sqrt(vdot(d, d));
       e[B200MD_E_EXTERNAL] += 0.5 * (double)P.smd_fk * dev * dev;
-      const double c = (double)P.smd_fk * dev / dist;
-      ladd(f, P.smd_a2, d, c);
-      ladd(f, P.smd_a1, d, -c);
-      if (smd_rec) {  // [R][2]: end-to-end distance of this step, work since the first step of the call
-        smd_rec[2 * r] = dist;
-        smd_rec[2 * r + 1] += (double)P.smd_fk * dev * (double)P.smd_rate;
-      }
     }
     lreduce<B200MD_NUM_ENERGIES, kLBondedThreads>(e, sred, tid);
     if (tid == 0) {
@@ -291,6 +346,10 @@ __device__ __forceinline__ float lds_f32(uint32_t addr) {
 // Row stride of the shared-memory type-pair table in entries: odd, so that the (12 A, -6 B) entries of one column sit
 // in distinct banks for up to 16 row types (lanes differ in their row = type of i, the column = type of j is uniform)
 __host__ __device__ inline int large_tab_stride(int ntypes) { return ntypes | 1; }
+// dynamic shared memory of large_forces_kernel: tables | bonded slots | staged positions
+inline int large_dyn_bytes(const LargeTopo& T) {
+  return (int)sizeof(float) * (2 * T.ntypes * large_tab_stride(T.ntypes) + 3 * T.win_slots_max + 3 * T.halo_max);
+}
 
 // grid (nwords, min(R, 65535)).  Shared memory: the two type-pair tables (2 ntypes^2 floats, dynamic) + statics.
 // The j tile of a warp is staged structure-of-arrays (x[32], y[32], z[32], q[32], type[32]) so that one broadcast LDS.64
@@ -299,7 +358,7 @@ __host__ __device__ inline int large_tab_stride(int ntypes) { return ntypes | 1;
 template <int MODE, bool ENERGY, bool PBC>
 __device__ __forceinline__ void large_pairs_body(const LargeTopo& T, const ForceParams& P, const float* __restrict__ p,
                                                  const uint32_t tbase, float* sj /* [4][32] */, int* stj, double* sjd /* [4][32] */,
-                                                 const float3 nbox, const float3 ibox, int ib, int warp, int lane, float xi,
+                                                 const float3 nbox, const float3 ibox, int ib, int warp /* 0, 1: the two warps on this i-block */, int lane, float xi,
                                                  float yi, float zi, float kqi, const float* __restrict__ bb, float& fx,
                                                  float& fy, float& fz, double& eel, double& elj) {
   const int N = T.natoms;
@@ -307,16 +366,23 @@ __device__ __forceinline__ void large_pairs_body(const LargeTopo& T, const Force
   const PairConst C = make_pair_const<MODE>(P);
   const u64 xi2 = dup2(xi), yi2 = dup2(yi), zi2 = dup2(zi), kq2 = dup2(kqi);
   u64 ax = 0ull, ay = 0ull, az = 0ull;
-  // the j atoms, their table offsets and the mask word of the NEXT tile are fetched while the current one is evaluated
+  // Cutoff mode, vacuum: which j tiles can hold a pair within the cutoff is decided BEFORE anything of a tile is loaded
+  // (round 1 staged every tile into shared memory and only then tested it: 100 us per step of 256 x 1 040 atoms for the ~5
+  // of 33 tiles per i-block that survive).  Lane l of warp w looks at tile 2 l + w of a window of 64: the tile's bounding box
+  // against the i-block's own box (both from large_bbox_kernel); a ballot gives the warp's to-do list.  A tile on the list is
+  // then tested against this lane's i atom (tighter), and only tiles some lane can reach are evaluated.  Component-wise the
+  // box distance is a lower bound of |xi - xj| for every pair, and fp32 subtraction / fma are monotonic, so a skipped tile
+  // holds only pairs the cutoff test of pair_eval2 would zero: results are bit-identical with and without the skip.
+  const bool boxtest = MODE == 1 && !PBC && bb != nullptr;
+  const bool live_i = 32 * ib + lane < N;
+  float4 ilo = make_float4(0.f, 0.f, 0.f, 0.f), ihi = ilo;
+  if (boxtest) { ilo = __ldg((const float4*)(bb + 8 * ib)); ihi = __ldg((const float4*)(bb + 8 * ib + 4)); }
+  // the j atoms, their table offsets, the mask word and the box of the NEXT tile on the list are fetched while the current
+  // one is evaluated
   float jx = 0.f, jy = 0.f, jz = 0.f, jq = 0.f;
   int jtype = 0;
   uint32_t mn = 0xffffffffu;
-  // cutoff mode, vacuum: the tile's bounding box against this lane's i atom.  Component-wise |xi - box| <= |xi - xj| for
-  // every atom of the tile and fp32 subtraction / fma are monotonic, so d2 <= r2 of every pair of the lane: a tile that all
-  // lanes place beyond the cutoff holds only pairs the cutoff test of pair_eval2 would zero -- results are bit-identical
-  const bool boxtest = MODE == 1 && !PBC && bb != nullptr;
   float4 blo = make_float4(0.f, 0.f, 0.f, 0.f), bhi = blo;
-  const bool live_i = 32 * ib + lane < N;
   auto fetch = [&](int jt) {
     if (boxtest) { blo = __ldg((const float4*)(bb + 8 * jt)); bhi = __ldg((const float4*)(bb + 8 * jt + 4)); }
     const int j = 32 * jt + lane;
@@ -325,32 +391,69 @@ __device__ __forceinline__ void large_pairs_body(const LargeTopo& T, const Force
     jtype = __ldg(T.atom_type + j) * 8;  // byte offset of the (12 A, -6 B) entry in this lane's table row
     mn = __ldg(mrow + jt);
   };
-  if (warp < T.nwords) fetch(warp);
-  for (int jt = warp; jt < T.nwords; jt += kLThreads / 32) {
-    const uint32_t m = mn;
-    bool far = false;
-    if (boxtest) {
-      const float ex = fmaxf(fmaxf(__fsub_rn(blo.x, xi), __fsub_rn(xi, bhi.x)), 0.0f), ey = fmaxf(fmaxf(__fsub_rn(blo.y, yi), __fsub_rn(yi, bhi.y)), 0.0f);
-      const float ez = fmaxf(fmaxf(__fsub_rn(blo.z, zi), __fsub_rn(zi, bhi.z)), 0.0f);
-      far = !live_i || !(__fmaf_rn(ez, ez, __fmaf_rn(ey, ey, __fmul_rn(ex, ex))) <= P.rc2);
+  // to-do list of a window of 64 tiles: lane l of warp w (0, 1: the two warps on this i-block) tests tile 2 l + w.  (Measured
+  // and dropped: handing the k-th tile ON the list to warp k & 1 so that both carry equal counts -- no gain; a 64-thread
+  // named barrier per warp pair instead of the CTA barrier before the force rows -- 10 us slower.)
+  for (int base = 0; base < T.nwords; base += 64) {
+    const int mine = base + 2 * lane + warp;
+    bool need = mine < T.nwords;
+    if (boxtest && need) {
+      const float4 tlo = __ldg((const float4*)(bb + 8 * mine)), thi = __ldg((const float4*)(bb + 8 * mine + 4));
+      const float gx = fmaxf(fmaxf(__fsub_rn(tlo.x, ihi.x), __fsub_rn(ilo.x, thi.x)), 0.0f);
+      const float gy = fmaxf(fmaxf(__fsub_rn(tlo.y, ihi.y), __fsub_rn(ilo.y, thi.y)), 0.0f);
+      const float gz = fmaxf(fmaxf(__fsub_rn(tlo.z, ihi.z), __fsub_rn(ilo.z, thi.z)), 0.0f);
+      need = __fmaf_rn(gz, gz, __fmaf_rn(gy, gy, __fmul_rn(gx, gx))) <= P.rc2;
     }
-    __syncwarp();
-    sj[lane] = jx; sj[32 + lane] = jy; sj[64 + lane] = jz; sj[96 + lane] = jq;
-    stj[lane] = jtype;
-    if (ENERGY && jt >= ib) { sjd[lane] = (double)jx; sjd[32 + lane] = (double)jy; sjd[64 + lane] = (double)jz; sjd[96 + lane] = (double)jq; }
-    __syncwarp();
-    if (jt + kLThreads / 32 < T.nwords) fetch(jt + kLThreads / 32);
-    if (__all_sync(0xffffffffu, far || m == 0xffffffffu)) continue;
-#pragma unroll 4
-    for (int jj = 0; jj < 32; jj += 2) {
-      const u64 xj = *(const u64*)(sj + jj), yj = *(const u64*)(sj + 32 + jj), zj = *(const u64*)(sj + 64 + jj);
-      const u64 qj = *(const u64*)(sj + 96 + jj);
-      const int2 tj = *(const int2*)(stj + jj);
-      const u64 a12 = pk(lds_f32<0>(tbase + tj.x), lds_f32<0>(tbase + tj.y)), nb6 = pk(lds_f32<4>(tbase + tj.x), lds_f32<4>(tbase + tj.y));
-      u64 dx = sub2(xi2, xj), dy = sub2(yi2, yj), dz = sub2(zi2, zj);
-      if (PBC) { dx = wrap2(dx, nbox.x, ibox.x); dy = wrap2(dy, nbox.y, ibox.y); dz = wrap2(dz, nbox.z, ibox.z); }
-      const u64 sc = pair_eval2<MODE>(dx, dy, dz, kqi, kq2, qj, a12, nb6, (m >> jj) & 1u, (m >> (jj + 1)) & 1u, P, C);
-      ax = fma2(sc, dx, ax); ay = fma2(sc, dy, ay); az = fma2(sc, dz, az);
+    uint32_t todo = __ballot_sync(0xffffffffu, need);
+    if (todo) fetch(base + 2 * (__ffs(todo) - 1) + warp);
+    while (todo) {
+      const int jt = base + 2 * (__ffs(todo) - 1) + warp;
+      todo &= todo - 1;
+      const uint32_t m = mn;
+      bool far = false;
+      if (boxtest) {
+        const float ex = fmaxf(fmaxf(__fsub_rn(blo.x, xi), __fsub_rn(xi, bhi.x)), 0.0f), ey = fmaxf(fmaxf(__fsub_rn(blo.y, yi), __fsub_rn(yi, bhi.y)), 0.0f);
+        const float ez = fmaxf(fmaxf(__fsub_rn(blo.z, zi), __fsub_rn(zi, bhi.z)), 0.0f);
+        far = !live_i || !(__fmaf_rn(ez, ez, __fmaf_rn(ey, ey, __fmul_rn(ex, ex))) <= P.rc2);
+      }
+      const bool skip = __all_sync(0xffffffffu, far || m == 0xffffffffu);
+      if (!skip) {
+        __syncwarp();
+        sj[lane] = jx; sj[32 + lane] = jy; sj[64 + lane] = jz; sj[96 + lane] = jq;
+        stj[lane] = jtype;
+        if (ENERGY && jt >= ib) { sjd[lane] = (double)jx; sjd[32 + lane] = (double)jy; sjd[64 + lane] = (double)jz; sjd[96 + lane] = (double)jq; }
+        __syncwarp();
+      }
+      if (todo) fetch(base + 2 * (__ffs(todo) - 1) + warp);
+      if (skip) continue;
+#pragma unroll 1
+    for (int j8 = 0; j8 < 32; j8 += 8) {
+      // Cutoff mode: 8 j atoms none of the 32 i atoms reaches contribute exactly zero (pair_eval2 zeroes every term of a
+      // pair beyond the cutoff) and are dropped on a warp vote, like the passes of the on-chip tiles.  The r^2 are the
+      // expressions pair_eval2 evaluates (same operands, same order): bit-identical results, the test costs the compares.
+      if (MODE == 1) {
+        bool in = false;
+#pragma unroll
+        for (int jj = j8; jj < j8 + 8; jj += 2) {
+          u64 dx = sub2(xi2, *(const u64*)(sj + jj)), dy = sub2(yi2, *(const u64*)(sj + 32 + jj)), dz = sub2(zi2, *(const u64*)(sj + 64 + jj));
+          if (PBC) { dx = wrap2(dx, nbox.x, ibox.x); dy = wrap2(dy, nbox.y, ibox.y); dz = wrap2(dz, nbox.z, ibox.z); }
+          float ra, rb;
+          upk(fma2(dz, dz, fma2(dy, dy, mul2(dx, dx))), ra, rb);
+          in = in || ra <= P.rc2 || rb <= P.rc2;
+        }
+        if (!__any_sync(0xffffffffu, in)) continue;
+      }
+#pragma unroll
+      for (int jj = j8; jj < j8 + 8; jj += 2) {
+        const u64 xj = *(const u64*)(sj + jj), yj = *(const u64*)(sj + 32 + jj), zj = *(const u64*)(sj + 64 + jj);
+        const u64 qj = *(const u64*)(sj + 96 + jj);
+        const int2 tj = *(const int2*)(stj + jj);
+        const u64 a12 = pk(lds_f32<0>(tbase + tj.x), lds_f32<0>(tbase + tj.y)), nb6 = pk(lds_f32<4>(tbase + tj.x), lds_f32<4>(tbase + tj.y));
+        u64 dx = sub2(xi2, xj), dy = sub2(yi2, yj), dz = sub2(zi2, zj);
+        if (PBC) { dx = wrap2(dx, nbox.x, ibox.x); dy = wrap2(dy, nbox.y, ibox.y); dz = wrap2(dz, nbox.z, ibox.z); }
+        const u64 sc = pair_eval2<MODE>(dx, dy, dz, kqi, kq2, qj, a12, nb6, (m >> jj) & 1u, (m >> (jj + 1)) & 1u, P, C);
+        ax = fma2(sc, dx, ax); ay = fma2(sc, dy, ay); az = fma2(sc, dz, az);
+      }
     }
     if (ENERGY && jt >= ib) {  // FP64 energies of the unordered pairs this tile owns (forces.py:379-413, 451-489 in double)
       const double xd = (double)xi, yd = (double)yi, zd = (double)zi;
@@ -369,7 +472,7 @@ __device__ __forceinline__ void large_pairs_body(const LargeTopo& T, const Force
         }
         const double r2 = dx * dx + dy * dy + dz * dz;
         if (MODE == 1 && !(r2 <= rc2)) continue;
-        const double rinv = rsqrt(r2), r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
+        const double rinv = drsqrt(r2), r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
         const double2 ab = __ldg(trow + (stj[jj] >> 3));
         const double qq = kq * sjd[96 + jj];
         double lj = (ta * ab.x * r6 + tb * ab.y) * r6;
@@ -386,83 +489,146 @@ __device__ __forceinline__ void large_pairs_body(const LargeTopo& T, const Force
         elj += lj;
       }
     }
+    }
   }
   fx = hsum2(ax); fy = hsum2(ay); fz = hsum2(az);
 }
 
+// Every force of one Forces.compute in ONE launch: grid (nwin, min(R, 65535)), CTA = one window of kLWin = 64 atoms of one
+// replica.  Phase A, bonded (fp32): the CTA evaluates every item that touches the window into private shared-memory slots
+// (positions of the atoms those items reference are staged in shared memory first when they span at most kLHalo atoms --
+// true of any chain-ordered topology), then thread a < 64 sums atom a's slots in their fixed order and adds the SMD
+// restraint.  Phase B, pairs: warps (0, 1) take the window's first 32-atom i-block, warps (2, 3) the second, each pair of
+// warps splitting the j tiles (large_pairs_body).  Epilogue: force row = bonded + (warp 0 + warp 1), written once, coalesced.
+// Separate bonded and pair kernels (54 + 76 us per step of 256 x 1 040 atoms in cutoff mode, each issuing on ~half of the
+// cycles: the bonded one waits on gathered loads, the pair one on its short tile lists) ran back to back; here CTAs in
+// different phases share an SM and fill each other's stalls, and the force rows are written once instead of written,
+// re-read and re-written.
+// Shared memory (dynamic): type-pair tables | bonded slots [win_slots_max][3] | staged positions [halo_max][3].
+#ifndef LV_OCC
+#define LV_OCC 5
+#endif
 template <int MODE, bool ENERGY>
-__global__ void __launch_bounds__(kLThreads)
-large_pairs_kernel(const LargeTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
-                   const float* __restrict__ box, const long long* __restrict__ fbond, float* __restrict__ forces,
-                   double* __restrict__ partial, const int npart, const int part0, uint32_t* __restrict__ status,
-                   const float* __restrict__ bbox) {
+__global__ void __launch_bounds__(kLThreads, ENERGY ? 4 : LV_OCC)
+large_forces_kernel(const LargeTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
+                    const float* __restrict__ box, float* __restrict__ forces, double* __restrict__ partial, const int npart,
+                    const int part0, uint32_t* __restrict__ status, const float* __restrict__ bbox,
+                    const float* __restrict__ smd_centers, const double smd_center, double* __restrict__ smd_rec) {
   extern __shared__ __align__(16) char lsmem[];
-  float* sAB = (float*)lsmem;  // [ntypes][stride] entries (12 A tab_a, 6 B tab_b)
   const int tstride = large_tab_stride(T.ntypes);
+  float* sAB = (float*)lsmem;  // [ntypes][stride] entries (12 A tab_a, 6 B tab_b)
+  float* lslots = sAB + 2 * T.ntypes * tstride;
+  float* shalo = lslots + 3 * T.win_slots_max;
   __shared__ __align__(16) float sj[kLThreads / 32][4 * 32];
   __shared__ __align__(16) int stj[kLThreads / 32][32];
   __shared__ double sjd[ENERGY ? kLThreads / 32 : 1][ENERGY ? 4 * 32 : 1];
   __shared__ float sf[kLThreads / 32][3][32];
+  __shared__ float sbond[3 * kLWin];
   __shared__ double sred[(kLThreads / 32) * 2];
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int N = T.natoms, ib = blockIdx.x;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, w = blockIdx.x;
+  const int N = T.natoms;
   for (int k = tid; k < T.ntypes * T.ntypes; k += kLThreads) {
     const int t = k / T.ntypes, u = k - t * T.ntypes;
     sAB[2 * (t * tstride + u)] = __ldg(T.tab12a + k) * P.tab_a;
     sAB[2 * (t * tstride + u) + 1] = __ldg(T.tab6b + k) * P.tab_b;
   }
-  const int i = 32 * ib + lane;
-  const bool live = i < N;
+  // phase A constants
+  const LItemRanges G = litem_ranges(T, P.terms);
+  const int k0 = __ldg(T.win_start + w), k1 = __ldg(T.win_start + w + 1);
+  const int hlo = __ldg(T.win_lo + w), hn = __ldg(T.win_n + w);
+  // warps (0, 1) own the window's first i-block, warps (2, 3) the second: the even warp of each pair gathers the bonded slots
+  // of its 32 atoms while the odd warp already starts on its pair tiles
+  const int aw = 32 * (warp >> 1) + lane;  // atom of the window this thread gathers (even warps)
+  const int a = kLWin * w + aw;
+  const bool gatherer = (warp & 1) == 0;
+  const bool mine = gatherer && a < N;
+  const int g0 = __ldg(T.gstart + kLWin * w);
+  const int s0 = mine ? __ldg(T.gstart + a) - g0 : 0, s1 = mine ? __ldg(T.gstart + a + 1) - g0 : 0;
+  // phase B constants
+  const int ib = 2 * w + (warp >> 1), sub = warp & 1;
+  const bool ib_ok = ib < T.nwords;
+  const int i = ib_ok ? 32 * ib + lane : 0;
+  const bool live = ib_ok && i < N;
   const uint32_t tbase = (uint32_t)__cvta_generic_to_shared(sAB) + (uint32_t)(__ldg(T.atom_type + i) * tstride * 8);
   const float kqi = __fmul_rn(__ldg(T.charge + i) * P.el_on, kElecFactor);
   const bool nonbonded = (P.terms & (B200MD_T_ELECTROSTATICS | B200MD_T_LJ | B200MD_T_REPULSION | B200MD_T_REPULSIONCG)) != 0;
-  __syncthreads();
   for (long long r = blockIdx.y; r < R; r += gridDim.y) {
     const float* p = pos + r * N * 3;
-    float xi = 0.f, yi = 0.f, zi = 0.f;
-    if (live) { xi = __ldg(p + 3 * i); yi = __ldg(p + 3 * i + 1); zi = __ldg(p + 3 * i + 2); }
-    if (warp == 0 && live && status != nullptr && (xi != xi || yi != yi || zi != zi)) atomicOr(status + r, B200MD_FLAG_NAN_POS);
     const float b0 = box ? __ldg(box + r * 9) : 0.0f, b1 = box ? __ldg(box + r * 9 + 4) : 0.0f, b2 = box ? __ldg(box + r * 9 + 8) : 0.0f;
     const bool pbc = b0 != 0.0f || b1 != 0.0f || b2 != 0.0f;  // forces.py:359
+    // ---- phase A: bonded items of the window ----
+    __syncthreads();  // the tables (first pass); the slots and staged positions of the previous replica are no longer read
+    for (int k = tid; k < 3 * hn; k += kLThreads) shalo[k] = __ldg(p + 3 * hlo + k);
+    __syncthreads();
+    {
+      const float* pe = hn > 0 ? shalo - 3 * hlo : p;
+      const float bxf[3] = {b0, b1, b2};
+      WindowSink sink;
+      sink.slots = lslots;
+      float ef[B200MD_NUM_ENERGIES] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};  // by-product of the float path, not read
+      for (int k = k0 + tid; k < k1; k += kLThreads) {
+        const int g = (int)__ldg(T.win_item + k);
+        sink.sl = __ldg(T.win_slot + k);
+        if (((G.on >> litem_kind(G, g)) & 1u)) {
+          litem<float, true, WindowSink>(T, P, G, g, pe, bxf, !pbc, sink, ef);
+        } else {  // a kind the call has switched off: its slots read as zero
+          const v3t<float> zero = {0.0f, 0.0f, 0.0f};
+#pragma unroll
+          for (int c = 0; c < 4; ++c) lput<float>(sink, c, zero, 0.0f);
+        }
+      }
+    }
+    __syncthreads();
+    if (gatherer) {
+      float bx = 0.0f, by = 0.0f, bz = 0.0f;
+      for (int sidx = s0; sidx < s1; ++sidx) { bx += lslots[3 * sidx]; by += lslots[3 * sidx + 1]; bz += lslots[3 * sidx + 2]; }
+      if (mine && P.smd_on && (a == P.smd_a1 || a == P.smd_a2)) {  // potcalc.py:75-89, not wrapped; FP64: (c - d) cancels near the centre
+        const double center = smd_centers ? (double)__ldg(smd_centers + r) : smd_center;
+        const v3t<double> d = vsub(vpos<double>(p, P.smd_a2), vpos<double>(p, P.smd_a1));
+        const double dist = sqrt(vdot(d, d)), dev = center - dist;
+        const double c = (double)P.smd_fk * dev / dist;  // force on atom2 = +fk (c - d) unit(r2 - r1)
+        const float sg = a == P.smd_a2 ? 1.0f : -1.0f;
+        bx += sg * (float)(c * d.x); by += sg * (float)(c * d.y); bz += sg * (float)(c * d.z);
+        if (smd_rec && a == P.smd_a2) {  // [R][2]: end-to-end distance of this step, work since the first step of the call
+          smd_rec[2 * r] = dist;
+          smd_rec[2 * r + 1] += (double)P.smd_fk * dev * (double)P.smd_rate;
+        }
+      }
+      sbond[3 * aw] = bx; sbond[3 * aw + 1] = by; sbond[3 * aw + 2] = bz;
+    }
+    // ---- phase B: pair tiles of the window's two i-blocks ----
+    float xi = 0.f, yi = 0.f, zi = 0.f;
+    if (live) { xi = __ldg(p + 3 * i); yi = __ldg(p + 3 * i + 1); zi = __ldg(p + 3 * i + 2); }
+    if (sub == 0 && live && status != nullptr && (xi != xi || yi != yi || zi != zi)) atomicOr(status + r, B200MD_FLAG_NAN_POS);
     const float3 nbox = make_float3(-b0, -b1, -b2);
     const float3 ibox = make_float3(b0 != 0.0f ? 1.0f / b0 : 0.0f, b1 != 0.0f ? 1.0f / b1 : 0.0f, b2 != 0.0f ? 1.0f / b2 : 0.0f);
     float fx = 0.f, fy = 0.f, fz = 0.f;
     double e[2] = {0.0, 0.0};
-    if (nonbonded) {
+    if (nonbonded && ib_ok) {
       double* sd = sjd[ENERGY ? warp : 0];
-      if (pbc) large_pairs_body<MODE, ENERGY, true>(T, P, p, tbase, sj[warp], stj[warp], sd, nbox, ibox, ib, warp, lane, xi, yi, zi, kqi, nullptr, fx, fy, fz, e[0], e[1]);
-      else large_pairs_body<MODE, ENERGY, false>(T, P, p, tbase, sj[warp], stj[warp], sd, nbox, ibox, ib, warp, lane, xi, yi, zi, kqi,
-                                                 bbox ? bbox + r * T.nwords * 8 : nullptr, fx, fy, fz, e[0], e[1]);
+      if (pbc) large_pairs_body<MODE, ENERGY, true>(T, P, p, tbase, sj[warp], stj[warp], sd, nbox, ibox, ib, sub, lane, xi, yi, zi, kqi, nullptr, fx, fy, fz, e[0], e[1]);
+      else large_pairs_body<MODE, ENERGY, false>(T, P, p, tbase, sj[warp], stj[warp], sd, nbox, ibox, ib, sub, lane, xi, yi, zi, kqi,
+                                                    bbox ? bbox + r * T.nwords * 8 : nullptr, fx, fy, fz, e[0], e[1]);
     }
     sf[warp][0][lane] = fx; sf[warp][1][lane] = fy; sf[warp][2][lane] = fz;
     __syncthreads();
-    if (tid < 96) {  // thread (c, lane): fixed-order sum over the warps + the bonded accumulator, one coalesced row
-      const int a = tid / 3, c = tid - 3 * a, ia = 32 * ib + a;
-      if (ia < N) {
-        const float s = __fadd_rn(__fadd_rn(sf[0][c][a], sf[1][c][a]), __fadd_rn(sf[2][c][a], sf[3][c][a]));
-        // fbond == nullptr: the bonded kernel runs concurrently on a second stream, large_combine_kernel adds it afterwards
-        const double fb = fbond != nullptr ? (double)fbond[(r * N + ia) * 3 + c] * kLFixInv : 0.0;
-        forces[(r * N + ia) * 3 + c] = fbond != nullptr ? (float)((double)s + fb) : s;
+    for (int k = tid & 63; k < 96; k += 64) {  // thread (atom, c): bonded + (even warp + odd warp), 32 coalesced rows
+      const int l = k / 3, c = k - 3 * l, ia = 32 * ib + l;
+      if (ib_ok && ia < N) {
+        const int wb = warp & ~1;
+        forces[(r * N + ia) * 3 + c] = __fadd_rn(sbond[96 * (warp >> 1) + k], __fadd_rn(sf[wb][c][l], sf[wb + 1][c][l]));
       }
     }
     if (ENERGY) {
       lreduce<2, kLThreads>(e, sred, tid);
       if (tid == 0) {
-        double* o = partial + (r * npart + part0 + ib) * B200MD_NUM_ENERGIES;
+        double* o = partial + (r * npart + part0 + w) * B200MD_NUM_ENERGIES;
         o[B200MD_E_ELECTROSTATICS] = e[0]; o[B200MD_E_LJ] = e[1];
 #pragma unroll
         for (int k = 2; k < B200MD_NUM_ENERGIES; ++k) o[k] = 0.0;
       }
-    } else {
-      __syncthreads();
     }
   }
-}
-
-// forces = pair row (fp32) + bonded accumulator: the same expression, hence the same bits, as the fused epilogue above
-__global__ void large_combine_kernel(const long long n, const long long* __restrict__ fbond, float* __restrict__ forces) {
-  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (g < n) forces[g] = (float)((double)forces[g] + (double)fbond[g] * kLFixInv);
 }
 
 // energies[r][k] = sum over the npart per-CTA partials, in index order
@@ -494,14 +660,19 @@ __global__ void large_vv1_kernel(const LargeTopo T, const float dt, const long l
 
 // Langevin kick (vel += -gamma vel dt + vcoeff N(0,1)) and _second_VV; with `ekin` the per-block kinetic-energy
 // partials of a report step.  grid (ceil(N / 256), R): blocks do not straddle replicas.
+// fuse_next: also the _first_VV of the NEXT step (same atom, same thread: vel += 0.5 dt f / m ; pos += dt vel) and, with
+// `bbox`, the bounding boxes of the moved 32-atom tiles (a warp is a tile: blocks start at multiples of 256 atoms) -- one
+// launch instead of three between two force evaluations.  The host does not fuse on snapshot steps and on the last step
+// of a call, where pos must stay x(t + dt).
 __global__ void __launch_bounds__(256)
 large_vv2_kernel(const LargeTopo T, const StepParams I, const unsigned long long gstep, const long long R,
                  float* __restrict__ vel, const float* __restrict__ forces, float* __restrict__ pos,
-                 double* __restrict__ ekin, uint32_t* __restrict__ status) {
+                 double* __restrict__ ekin, uint32_t* __restrict__ status, const int fuse_next, float* __restrict__ bbox) {
   __shared__ double sred[8];
   const int tid = threadIdx.x, a = blockIdx.x * 256 + tid;
   for (long long r = blockIdx.y; r < R; r += gridDim.y) {
     double e[1] = {0.0};
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
     if (a < T.natoms) {
       const long long g = r * T.natoms + a;
       const float mass = __ldg(T.mass + a), invm = 1.0f / mass, hdt_m = 0.5f * I.dt * invm;
@@ -519,8 +690,32 @@ large_vv2_kernel(const LargeTopo T, const StepParams I, const unsigned long long
         vel[3 * g + c] = v[c];
       }
       e[0] = 0.5 * (double)mass * ((double)v[0] * v[0] + (double)v[1] * v[1] + (double)v[2] * v[2]);
-      const float x = pos[3 * g], y = pos[3 * g + 1], z = pos[3 * g + 2];
+      float x = pos[3 * g], y = pos[3 * g + 1], z = pos[3 * g + 2];
       if (status != nullptr && (x != x || y != y || z != z)) atomicOr(status + r, B200MD_FLAG_NAN_POS);
+      if (fuse_next) {  // large_vv1_kernel's arithmetic, expression by expression (bit-identical trajectories)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          v[c] = fmaf(hdt_m, forces[3 * g + c], v[c]);
+          vel[3 * g + c] = v[c];
+        }
+        x = fmaf(I.dt, v[0], x); y = fmaf(I.dt, v[1], y); z = fmaf(I.dt, v[2], z);
+        pos[3 * g] = x; pos[3 * g + 1] = y; pos[3 * g + 2] = z;
+      }
+      lo[0] = hi[0] = x; lo[1] = hi[1] = y; lo[2] = hi[2] = z;
+    }
+    if (fuse_next && bbox != nullptr) {  // as large_bbox_kernel
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          lo[c] = fminf(lo[c], __shfl_xor_sync(0xffffffffu, lo[c], o));
+          hi[c] = fmaxf(hi[c], __shfl_xor_sync(0xffffffffu, hi[c], o));
+        }
+      const int lane = tid & 31, tile = a >> 5;
+      if (lane < 3 && tile < T.nwords) {
+        bbox[(r * T.nwords + tile) * 8 + lane] = lane == 0 ? lo[0] : (lane == 1 ? lo[1] : lo[2]);
+        bbox[(r * T.nwords + tile) * 8 + 4 + lane] = lane == 0 ? hi[0] : (lane == 1 ? hi[1] : hi[2]);
+      }
     }
     if (ekin != nullptr) {
       lreduce<1, 256>(e, sred, tid);
