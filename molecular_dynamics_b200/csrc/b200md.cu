@@ -598,7 +598,7 @@ struct b200md_topology {
   // second stream of the large-solute calls: the latency-bound FP64 bonded kernel runs beside the throughput-bound pair
   // kernel (fork / join by events, so the caller's stream still orders the call as a whole)
   mutable cudaStream_t aux = nullptr;
-  mutable cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  mutable cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_bonded = nullptr;
 };
 
 namespace {
@@ -1329,7 +1329,7 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
         for (int c = 0; c < K.arity; ++c) ++gstart[K.idx[K.arity * it + c] + 1];
     for (int a = 0; a < N; ++a) gstart[a + 1] += gstart[a];
     for (int w = 0; w < nwin; ++w) win_slots_max = std::max(win_slots_max, gstart[std::min(N, kLWin * (w + 1))] - gstart[kLWin * w]);
-    if (win_slots_max >= 0xffff || (size_t)win_slots_max * 12 > 200 * 1024) {
+    if (win_slots_max >= 0xffff || (size_t)win_slots_max * 16 > 190 * 1024) {
       delete topo; fail(B200MD_ERR_UNSUPPORTED, "a window of 64 atoms carries more bonded contributions than fit in shared memory"); return nullptr;
     }
     std::vector<int> cur(gstart.begin(), gstart.end() - 1);
@@ -1389,6 +1389,8 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   L.win_start = (const int*)(base + o_wst); L.win_item = (const uint32_t*)(base + o_wit); L.win_slot = (const ushort4*)(base + o_wsl);
   L.gstart = (const int*)(base + o_gst); L.nwin = nwin; L.win_slots_max = win_slots_max; L.halo_max = halo_max;
   L.win_lo = (const int*)(base + o_wlo); L.win_n = (const int*)(base + o_wn);
+  L.nblk = (W + kLBT - 1) / kLBT;  // pair rectangles over nblk blocks of bt <= kLBT tiles, as even as the tile count allows
+  L.bt = (W + L.nblk - 1) / L.nblk;
   L.nbonds = d->nbonds; L.nangles = d->nangles; L.ndih = d->ndihedrals; L.n14 = d->n14; L.nimp = d->nimpropers;
   L.bond_idx = (const int2*)(base + o_bi); L.bond_prm = (const float2*)(base + o_bp);
   L.angle_idx = (const int*)(base + o_ai); L.angle_prm = (const float2*)(base + o_ap);
@@ -1396,17 +1398,16 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   L.idx14 = (const int2*)(base + o_i14); L.prm14 = (const float4*)(base + o_p14);
   L.dih_cs = (const double2*)(base + o_dcs); L.imp_cs = (const double2*)(base + o_ics);
   L.imp_idx = (const int4*)(base + o_iq); L.imp_start = (const int*)(base + o_is); L.imp_term = (const float4*)(base + o_it);
-  const int dyn_bytes = large_dyn_bytes(L);
-  if (dyn_bytes > 200 * 1024) {
+  const int pair_bytes = large_pairs_dyn_bytes(L), bonded_bytes = large_bonded_dyn_bytes(L);
+  if (pair_bytes > 200 * 1024 || bonded_bytes > 200 * 1024) {
     cudaFree(topo->blob); delete topo;
-    fail(B200MD_ERR_UNSUPPORTED, "type tables + the bonded slots of a 64-atom window exceed shared memory"); return nullptr;
+    fail(B200MD_ERR_UNSUPPORTED, "the type tables or the bonded slots of a 64-atom window exceed shared memory"); return nullptr;
   }
-  if (dyn_bytes > 32 * 1024) {
-    cudaFuncSetAttribute(large_forces_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_bytes);
-    cudaFuncSetAttribute(large_forces_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_bytes);
-    cudaFuncSetAttribute(large_forces_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_bytes);
-    cudaFuncSetAttribute(large_forces_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_bytes);
+  if (pair_bytes > 32 * 1024) {
+    cudaFuncSetAttribute(large_pairs_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, pair_bytes);
+    cudaFuncSetAttribute(large_pairs_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, pair_bytes);
   }
+  if (bonded_bytes > 32 * 1024) cudaFuncSetAttribute(large_bonded_forces_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bonded_bytes);
   g_last_error.clear();
   return topo;
 }
@@ -1417,6 +1418,7 @@ struct LargeWork {
   cudaStream_t st;
   double* partial = nullptr; double* energies = nullptr; double* ekin = nullptr; double* smd = nullptr;
   float* bbox = nullptr;
+  float* fpart = nullptr;  // [R][nblk + 1][natoms][3] partial force rows of large_forces_kernel
   int nbonded_blocks = 0, npart = 0, nek = 0;
 };
 
@@ -1427,10 +1429,10 @@ static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, 
   // FP64 energy partials -- and with it every bit of a replica's result -- does not depend on the replica count of the call
   (void)R;
   w.nbonded_blocks = (int)std::max<long long>(1, std::min<long long>(64, (items + 4 * kLBondedThreads - 1) / (4 * kLBondedThreads)));
-  w.npart = w.nbonded_blocks + L.nwin;
+  w.npart = w.nbonded_blocks + L.nwords;
   w.nek = (L.natoms + 255) / 256;
   auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
-  const size_t b_f = 0;
+  const size_t b_f = up(sizeof(float) * 3 * (size_t)R * (L.nblk + 1) * L.natoms);
   const size_t b_p = up(sizeof(double) * (size_t)R * w.npart * B200MD_NUM_ENERGIES);
   const size_t b_e = integrator ? up(sizeof(double) * (size_t)R * B200MD_NUM_ENERGIES) : 0, b_k = integrator ? up(sizeof(double) * (size_t)R * w.nek) : 0;
   const size_t b_s = (integrator && smd) ? up(sizeof(double) * 2 * (size_t)R) : 0;
@@ -1444,6 +1446,7 @@ static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, 
   }
   topo->ws_stream = w.st;
   char* base = (char*)topo->ws;
+  w.fpart = (float*)base; base += b_f;
   w.partial = (double*)base; base += b_p;
   w.bbox = (float*)base; base += b_b;
   if (integrator) {
@@ -1457,10 +1460,11 @@ static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, 
   return B200MD_OK;
 }
 
-// One Forces.compute over R replicas: zero the accumulator, bonded items, pair tiles (+ the force row), energies.
+// One Forces.compute over R replicas: tile boxes (cutoff mode), the force launch (partial rows), their sum into `forces`
+// unless the caller takes it itself (the integrator), and on a report step the FP64 energies beside them on a second stream.
 static int large_forces(const b200md_topology* topo, const ForceParams& P, int64_t R, const float* pos, const float* box,
                         float* forces, double* energies, uint32_t* status, double smd_center, bool with_energy, LargeWork& w,
-                        bool bbox_ready = false) {
+                        bool bbox_ready = false, bool sum_rows = true) {
   const LargeTopo& L = topo->ldev;
   cudaStream_t st = w.st;
   const int gy = (int)std::min<int64_t>(R, 65535);
@@ -1469,42 +1473,63 @@ static int large_forces(const b200md_topology* topo, const ForceParams& P, int64
     CUDA_TRY(cudaStreamCreateWithFlags(&topo->aux, cudaStreamNonBlocking));
     CUDA_TRY(cudaEventCreateWithFlags(&topo->ev_fork, cudaEventDisableTiming));
     CUDA_TRY(cudaEventCreateWithFlags(&topo->ev_join, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventCreateWithFlags(&topo->ev_bonded, cudaEventDisableTiming));
   }
-  // Forces: one launch (large_forces_kernel: bonded windows + pair tiles).  Bonded energies (FP64, item-centric) only read
-  // the positions: on a report step they run beside it on a second stream.
-  cudaStream_t sb = overlap_on ? topo->aux : st;
-  if (with_energy) {
-    if (overlap_on) {
-      CUDA_TRY(cudaEventRecord(topo->ev_fork, st));
-      CUDA_TRY(cudaStreamWaitEvent(sb, topo->ev_fork, 0));
-    }
-    large_bonded_energy_kernel<<<dim3(w.nbonded_blocks, gy), kLBondedThreads, 0, sb>>>(L, P, R, pos, box, w.partial, w.npart,
-                                                                                      P.smd_centers, smd_center);
-    if (overlap_on) CUDA_TRY(cudaEventRecord(topo->ev_join, sb));
-    g_launches.fetch_add(1);
-  }
-  const int dyn_bytes = large_dyn_bytes(L);
-  const dim3 grid(L.nwin, gy);
   const bool pairs_on = (P.terms & (B200MD_T_ELECTROSTATICS | B200MD_T_LJ | B200MD_T_REPULSION | B200MD_T_REPULSIONCG)) != 0;
   const float* bbox = nullptr;
-  if (P.has_cutoff && pairs_on && L.nwords > 4) {  // tile bounding boxes for the cutoff skip (vacuum replicas use them)
+  if (P.has_cutoff && pairs_on && L.nwords > 4) {  // tile bounding boxes for the cutoff skips (vacuum replicas use them)
     if (!bbox_ready) {  // (the integrator's fused half-kick kernel has written them already)
       large_bbox_kernel<<<dim3((L.nwords + 3) / 4, gy), 128, 0, st>>>(L, R, pos, w.bbox);
       g_launches.fetch_add(1);
     }
     bbox = w.bbox;
   }
-#define B200MD_LAUNCH_LPAIRS(M, E)                                                                                                         \
-  large_forces_kernel<M, E><<<grid, kLThreads, dyn_bytes, st>>>(L, P, R, pos, box, forces, w.partial, w.npart, w.nbonded_blocks, status, bbox, \
-                                                                P.smd_centers, smd_center, w.smd)
-  if (P.has_cutoff) { if (with_energy) B200MD_LAUNCH_LPAIRS(1, true); else B200MD_LAUNCH_LPAIRS(1, false); }
-  else { if (with_energy) B200MD_LAUNCH_LPAIRS(0, true); else B200MD_LAUNCH_LPAIRS(0, false); }
-#undef B200MD_LAUNCH_LPAIRS
+  // The bonded windows and the pair rectangles write different slots of the partial rows and only read the positions: the
+  // bonded launch (latency-bound, 64 registers) runs on a second stream beside the pair launch (packed-FP32-bound, 96
+  // registers), and on a report step the FP64 energy kernels follow it there.  Fork / join by events, so the caller's
+  // stream still orders the call as a whole.
+  static const bool split_on = overlap_on && !(getenv("B200MD_LARGE_SPLIT") && atoi(getenv("B200MD_LARGE_SPLIT")) == 0);
+  cudaStream_t sb = overlap_on ? topo->aux : st;
+  cudaStream_t sf = split_on ? topo->aux : st;  // stream of the bonded force launch
+  const int npart = pairs_on ? w.npart : w.nbonded_blocks;
+  if (overlap_on && (with_energy || (split_on && pairs_on))) {
+    CUDA_TRY(cudaEventRecord(topo->ev_fork, st));
+    CUDA_TRY(cudaStreamWaitEvent(sb, topo->ev_fork, 0));
+  } else {
+    sf = st;
+  }
+  large_bonded_forces_kernel<<<dim3(L.nwin, gy), kLBondedThreads, large_bonded_dyn_bytes(L), sf>>>(L, P, R, pos, box, w.fpart, status, P.smd_centers,
+                                                                                                   smd_center, w.smd);
   g_launches.fetch_add(1);
+  if (sf != st) CUDA_TRY(cudaEventRecord(topo->ev_bonded, sf));
   if (with_energy) {
-    if (overlap_on) CUDA_TRY(cudaStreamWaitEvent(st, topo->ev_join, 0));  // join: the bonded energy partials are complete
+    large_bonded_energy_kernel<<<dim3(w.nbonded_blocks, gy), kLBondedThreads, 0, sb>>>(L, P, R, pos, box, w.partial, npart,
+                                                                                      P.smd_centers, smd_center);
+    g_launches.fetch_add(1);
+    if (pairs_on) {
+      if (P.has_cutoff) large_pair_energy_kernel<1><<<dim3(L.nwords, gy), kLThreads, 0, sb>>>(L, P, R, pos, box, w.partial, npart, w.nbonded_blocks, bbox);
+      else large_pair_energy_kernel<0><<<dim3(L.nwords, gy), kLThreads, 0, sb>>>(L, P, R, pos, box, w.partial, npart, w.nbonded_blocks, bbox);
+      g_launches.fetch_add(1);
+    }
+    if (overlap_on) CUDA_TRY(cudaEventRecord(topo->ev_join, sb));
+  }
+  if (pairs_on) {
+    const dim3 grid(L.nblk * (L.nblk + 1) / 2, gy);
+    const int dyn_bytes = large_pairs_dyn_bytes(L);
+    if (P.has_cutoff) large_pairs_kernel<1><<<grid, kLThreads, dyn_bytes, st>>>(L, P, R, pos, box, w.fpart, bbox);
+    else large_pairs_kernel<0><<<grid, kLThreads, dyn_bytes, st>>>(L, P, R, pos, box, w.fpart, bbox);
+    g_launches.fetch_add(1);
+  }
+  if (sf != st) CUDA_TRY(cudaStreamWaitEvent(st, topo->ev_bonded, 0));
+  if (sum_rows) {
+    const long long n = (long long)R * L.natoms * 3;
+    large_sum_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(L, R, w.fpart, pairs_on ? 0 : L.nblk, forces);
+    g_launches.fetch_add(1);
+  }
+  if (with_energy) {
+    if (overlap_on) CUDA_TRY(cudaStreamWaitEvent(st, topo->ev_join, 0));  // join: the energy partials are complete
     const long long n = (long long)R * B200MD_NUM_ENERGIES;
-    large_finish_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(R, w.partial, w.npart, energies);
+    large_finish_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(R, w.partial, npart, energies);
     g_launches.fetch_add(1);
   }
   CUDA_TRY(cudaGetLastError());
@@ -1537,8 +1562,8 @@ static int large_integrate(const b200md_topology* topo, const ForceParams& P, co
   // Between two force evaluations the second half-kick of step s, the first half-kick of step s + 1 and the tile bounding
   // boxes are ONE launch (large_vv2_kernel with fuse_next) -- except where pos must stay x(t + dt): snapshot steps and the
   // last step of the call.
-  const bool want_bbox = P.has_cutoff && L.nwords > 4 &&
-                         (P.terms & (B200MD_T_ELECTROSTATICS | B200MD_T_LJ | B200MD_T_REPULSION | B200MD_T_REPULSIONCG)) != 0;
+  const bool pairs_on = (P.terms & (B200MD_T_ELECTROSTATICS | B200MD_T_LJ | B200MD_T_REPULSION | B200MD_T_REPULSIONCG)) != 0;
+  const bool want_bbox = P.has_cutoff && L.nwords > 4 && pairs_on;
   bool fused_prev = false;
   for (int s = 0; s < I.nsteps; ++s) {
     const unsigned long long gstep = I.step0 + (unsigned long long)s;
@@ -1548,12 +1573,12 @@ static int large_integrate(const b200md_topology* topo, const ForceParams& P, co
       g_launches.fetch_add(1);
     }
     const double center = (double)P.smd_c0 + (double)P.smd_rate * (double)(gstep + 1);
-    rc = large_forces(topo, P, R, pos, box, forces, w.energies, status, center, report, w, fused_prev && want_bbox);
+    rc = large_forces(topo, P, R, pos, box, forces, w.energies, status, center, report, w, fused_prev && want_bbox, false);
     if (rc) return rc;
     const bool snap = I.snapshot_every > 0 && snapshots != nullptr && (s + 1) % I.snapshot_every == 0;
     const bool fuse = s + 1 < I.nsteps && !snap;
     large_vv2_kernel<<<dim3(w.nek, (unsigned)std::min<int64_t>(R, 65535)), 256, 0, st>>>(L, I, gstep, R, vel, forces, pos, report ? w.ekin : nullptr,
-                                                                                       status, fuse ? 1 : 0, (fuse && want_bbox) ? w.bbox : nullptr);
+                                                                                       status, fuse ? 1 : 0, (fuse && want_bbox) ? w.bbox : nullptr, w.fpart, pairs_on ? 0 : L.nblk);
     fused_prev = fuse;
     g_launches.fetch_add(1);
     if (report && observables != nullptr) {
@@ -1579,6 +1604,7 @@ extern "C" void b200md_topology_destroy(b200md_topology* topo) {
   if (topo->aux) cudaStreamDestroy(topo->aux);
   if (topo->ev_fork) cudaEventDestroy(topo->ev_fork);
   if (topo->ev_join) cudaEventDestroy(topo->ev_join);
+  if (topo->ev_bonded) cudaEventDestroy(topo->ev_bonded);
   delete topo;
 }
 

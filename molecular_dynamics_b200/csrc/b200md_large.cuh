@@ -58,6 +58,7 @@ struct LargeTopo {
   const int* win_lo;         // [nwin] first atom the window's items reference
   const int* win_n;          // [nwin] how many atoms from win_lo they span, 0 when more than kLHalo (then read from HBM)
   int nwin, win_slots_max, halo_max;  // windows; largest slot count / staged span of a window (shared memory = 12 bytes x each)
+  int bt, nblk;                       // pair rectangles: tiles per atom block (<= kLBT), number of blocks
 };
 constexpr int kLWin = 64, kLHalo = 320;
 
@@ -94,13 +95,13 @@ template <typename T> __device__ __forceinline__ v3t<T> vwrap(v3t<T> d, const T*
 // touches the window (items across a window edge are evaluated by both windows), writes the vectors of ITS atoms to their
 // private slots, and sums each atom's slots in a fixed order: no atomic, no global scratch, exact fp32, any magnitude.
 struct WindowSink {
-  float* slots;  // shared memory, float3 per slot
+  float4* slots;  // shared memory, one 16-byte slot per contribution (one STS.128 / LDS.128 each)
   ushort4 sl;    // slot of each role, 0xffff = not in this window
 };
 struct NoSink {};
 template <typename T> __device__ __forceinline__ void lput(WindowSink& f, int role, v3t<T> a, T s) {
   const unsigned sidx = role == 0 ? f.sl.x : (role == 1 ? f.sl.y : (role == 2 ? f.sl.z : f.sl.w));
-  if (sidx != 0xffffu) { f.slots[3 * sidx] = (float)(s * a.x); f.slots[3 * sidx + 1] = (float)(s * a.y); f.slots[3 * sidx + 2] = (float)(s * a.z); }
+  if (sidx != 0xffffu) f.slots[sidx] = make_float4((float)(s * a.x), (float)(s * a.y), (float)(s * a.z), 0.0f);
 }
 template <typename T> __device__ __forceinline__ void lput(NoSink&, int, v3t<T>, T) {}
 
@@ -346,218 +347,334 @@ __device__ __forceinline__ float lds_f32(uint32_t addr) {
 // Row stride of the shared-memory type-pair table in entries: odd, so that the (12 A, -6 B) entries of one column sit
 // in distinct banks for up to 16 row types (lanes differ in their row = type of i, the column = type of j is uniform)
 __host__ __device__ inline int large_tab_stride(int ntypes) { return ntypes | 1; }
-// dynamic shared memory of large_forces_kernel: tables | bonded slots | staged positions
-inline int large_dyn_bytes(const LargeTopo& T) {
-  return (int)sizeof(float) * (2 * T.ntypes * large_tab_stride(T.ntypes) + 3 * T.win_slots_max + 3 * T.halo_max);
-}
 
-// grid (nwords, min(R, 65535)).  Shared memory: the two type-pair tables (2 ntypes^2 floats, dynamic) + statics.
-// The j tile of a warp is staged structure-of-arrays (x[32], y[32], z[32], q[32], type[32]) so that one broadcast LDS.64
-// delivers the operands of TWO j atoms as a packed f32x2: the pair arithmetic is pair_eval2 (FFMA2 / FMUL2 / FADD2, one
-// issue slot per two pairs), like the on-chip tiles.
-template <int MODE, bool ENERGY, bool PBC>
-__device__ __forceinline__ void large_pairs_body(const LargeTopo& T, const ForceParams& P, const float* __restrict__ p,
-                                                 const uint32_t tbase, float* sj /* [4][32] */, int* stj, double* sjd /* [4][32] */,
-                                                 const float3 nbox, const float3 ibox, int ib, int warp /* 0, 1: the two warps on this i-block */, int lane, float xi,
-                                                 float yi, float zi, float kqi, const float* __restrict__ bb, float& fx,
-                                                 float& fy, float& fz, double& eel, double& elj) {
-  const int N = T.natoms;
-  const uint32_t* mrow = T.mask + (size_t)(32 * ib + lane) * T.nwords;
-  const PairConst C = make_pair_const<MODE>(P);
-  const u64 xi2 = dup2(xi), yi2 = dup2(yi), zi2 = dup2(zi), kq2 = dup2(kqi);
-  u64 ax = 0ull, ay = 0ull, az = 0ull;
-  // Cutoff mode, vacuum: which j tiles can hold a pair within the cutoff is decided BEFORE anything of a tile is loaded
-  // (round 1 staged every tile into shared memory and only then tested it: 100 us per step of 256 x 1 040 atoms for the ~5
-  // of 33 tiles per i-block that survive).  Lane l of warp w looks at tile 2 l + w of a window of 64: the tile's bounding box
-  // against the i-block's own box (both from large_bbox_kernel); a ballot gives the warp's to-do list.  A tile on the list is
-  // then tested against this lane's i atom (tighter), and only tiles some lane can reach are evaluated.  Component-wise the
-  // box distance is a lower bound of |xi - xj| for every pair, and fp32 subtraction / fma are monotonic, so a skipped tile
-  // holds only pairs the cutoff test of pair_eval2 would zero: results are bit-identical with and without the skip.
+// ---- pair forces: HALF shell over rectangles of atom blocks ------------------------------------------------------------
+// The 32-atom tiles are grouped into nblk blocks of bt <= kLBT tiles.  One CTA takes one rectangle (BI >= BJ) of one
+// replica: both blocks are staged in shared memory (the i block as float4 rows, the j block structure-of-arrays); warp w
+// holds, for every j tile of BJ in turn, the tile's w-th chunk of 8 atoms in broadcast operands and meets it with the
+// 32-atom i tiles of BI ("passes", lane = i atom) exactly like the on-chip tile task of b200md_forces.cuh: packed
+// pair_eval2, the i-side force of a pass added to the warp's private shared-memory row, the j-side force kept in 24
+// registers over the passes and transposed once per chunk by a shuffle butterfly.  In a diagonal rectangle a chunk only
+// meets i tiles ABOVE its own tile, and the 32 x 32 pairs inside a tile are evaluated full-shell by its lanes (no j side).
+// Every unordered pair is evaluated once -- round 1 evaluated each from both atoms.
+// Cutoff mode, vacuum: lane l < bt tests tile box (BI, l) against the j tile's box (large_bbox_kernel), a ballot is the
+// chunk's pass list; a listed pass still drops out on a warp vote when none of its 32 x 8 pairs is within the cutoff
+// (the r^2 of the vote are the expressions pair_eval2 evaluates: bit-identical with and without the skips).
+// The CTA writes the block's partial force rows fpart[r][slot][atom][3]: atoms of BI -> slot BJ, atoms of BJ -> slot BI
+// (diagonal: both sides summed into slot BI), so atom a of block B finds slot k written by rectangle (max(B, k), min(B, k)):
+// every slot of every atom is written exactly once per launch, no atomics, no zeroing, a fixed summation order.
+constexpr int kLBT = 9;          // tiles per block at most
+constexpr int kLB = 32 * kLBT;   // atoms per block at most
+struct RectSmem {
+  float4 ipos[kLB];  // x, y, z, charge * el_on * kElecFactor
+  float jx[kLB], jy[kLB], jz[kLB], jq[kLB];  // jq: charge * el_on
+  int irow[kLB];     // byte offset of the i atom's row in the type-pair table
+  int jcol[kLB];     // byte offset of the j atom's column
+  float fi[kLThreads / 32][3][kLB];
+  float fj[3][kLB];
+};
+
+template <int MODE, bool PBC>
+__device__ __forceinline__ void large_rect(const LargeTopo& T, const ForceParams& P, const float* __restrict__ p,
+                                           const float* __restrict__ bb, RectSmem& S, const uint32_t tab, const int BI,
+                                           const int BJ, const float3 nbox, const float3 ibox, float* __restrict__ out_i,
+                                           float* __restrict__ out_j, const int tid) {
+  const int N = T.natoms, bt = T.bt, nw = T.nwords;
+  const int warp = tid >> 5, lane = tid & 31;
+  const bool diag = BI == BJ;
+  const int tstride = large_tab_stride(T.ntypes);
+  const int nia = min(32 * bt, max(0, 32 * nw - 32 * bt * BI)), nja = min(32 * bt, max(0, 32 * nw - 32 * bt * BJ));  // padded atoms of the blocks
   const bool boxtest = MODE == 1 && !PBC && bb != nullptr;
-  const bool live_i = 32 * ib + lane < N;
-  float4 ilo = make_float4(0.f, 0.f, 0.f, 0.f), ihi = ilo;
-  if (boxtest) { ilo = __ldg((const float4*)(bb + 8 * ib)); ihi = __ldg((const float4*)(bb + 8 * ib + 4)); }
-  // the j atoms, their table offsets, the mask word and the box of the NEXT tile on the list are fetched while the current
-  // one is evaluated
-  float jx = 0.f, jy = 0.f, jz = 0.f, jq = 0.f;
-  int jtype = 0;
-  uint32_t mn = 0xffffffffu;
-  float4 blo = make_float4(0.f, 0.f, 0.f, 0.f), bhi = blo;
-  auto fetch = [&](int jt) {
-    if (boxtest) { blo = __ldg((const float4*)(bb + 8 * jt)); bhi = __ldg((const float4*)(bb + 8 * jt + 4)); }
-    const int j = 32 * jt + lane;
-    jx = jy = jz = jq = 0.f;
-    if (j < N) { jx = __ldg(p + 3 * j); jy = __ldg(p + 3 * j + 1); jz = __ldg(p + 3 * j + 2); jq = __ldg(T.charge + j) * P.el_on; }
-    jtype = __ldg(T.atom_type + j) * 8;  // byte offset of the (12 A, -6 B) entry in this lane's table row
-    mn = __ldg(mrow + jt);
-  };
-  // to-do list of a window of 64 tiles: lane l of warp w (0, 1: the two warps on this i-block) tests tile 2 l + w.  (Measured
-  // and dropped: handing the k-th tile ON the list to warp k & 1 so that both carry equal counts -- no gain; a 64-thread
-  // named barrier per warp pair instead of the CTA barrier before the force rows -- 10 us slower.)
-  for (int base = 0; base < T.nwords; base += 64) {
-    const int mine = base + 2 * lane + warp;
-    bool need = mine < T.nwords;
+  if (boxtest) {  // the whole rectangle beyond the cutoff (chains far apart): its rows are zero
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    const int blk = lane < 16 ? BI : BJ, tl = lane & 15, tile = blk * bt + tl;
+    if (tl < bt && tile < nw) {
+      const float4 a = __ldg((const float4*)(bb + 8 * tile)), b = __ldg((const float4*)(bb + 8 * tile + 4));
+      lo[0] = a.x; lo[1] = a.y; lo[2] = a.z; hi[0] = b.x; hi[1] = b.y; hi[2] = b.z;
+    }
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        lo[c] = fminf(lo[c], __shfl_xor_sync(0xffffffffu, lo[c], o));
+        hi[c] = fmaxf(hi[c], __shfl_xor_sync(0xffffffffu, hi[c], o));
+      }
+    float g2 = 0.0f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {  // lanes 0..15 hold BI's box, 16..31 BJ's
+      const float olo = __shfl_xor_sync(0xffffffffu, lo[c], 16), ohi = __shfl_xor_sync(0xffffffffu, hi[c], 16);
+      const float g = fmaxf(fmaxf(__fsub_rn(olo, hi[c]), __fsub_rn(lo[c], ohi)), 0.0f);
+      g2 = __fmaf_rn(g, g, g2);
+    }
+    if (!(g2 <= P.rc2)) {  // (uniform over the CTA: every warp computes the same boxes)
+      for (int k = tid; k < 3 * nia; k += kLThreads) if (32 * bt * BI + k / 3 < N) out_i[k] = 0.0f;
+      if (!diag) for (int k = tid; k < 3 * nja; k += kLThreads) if (32 * bt * BJ + k / 3 < N) out_j[k] = 0.0f;
+      return;
+    }
+  }
+  // stage the two blocks, zero the accumulators
+  for (int t = tid; t < 32 * bt; t += kLThreads) {
+    const int ai = 32 * bt * BI + t, aj = 32 * bt * BJ + t;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    int row = 0;
+    if (ai < N) {
+      v = make_float4(__ldg(p + 3 * ai), __ldg(p + 3 * ai + 1), __ldg(p + 3 * ai + 2), __fmul_rn(__ldg(T.charge + ai) * P.el_on, kElecFactor));
+      row = __ldg(T.atom_type + ai) * tstride * 8;
+    }
+    S.ipos[t] = v; S.irow[t] = row;
+    float x = 0.f, y = 0.f, z = 0.f, q = 0.f;
+    int col = 0;
+    if (aj < N) { x = __ldg(p + 3 * aj); y = __ldg(p + 3 * aj + 1); z = __ldg(p + 3 * aj + 2); q = __ldg(T.charge + aj) * P.el_on; col = __ldg(T.atom_type + aj) * 8; }
+    S.jx[t] = x; S.jy[t] = y; S.jz[t] = z; S.jq[t] = q; S.jcol[t] = col;
+  }
+  for (int k = tid; k < (kLThreads / 32) * 3 * kLB; k += kLThreads) (&S.fi[0][0][0])[k] = 0.0f;
+  for (int k = tid; k < 3 * kLB; k += kLThreads) (&S.fj[0][0])[k] = 0.0f;
+  __syncthreads();
+  const PairConst C = make_pair_const<MODE>(P);
+  // ---- chunks of 8 j atoms against the i tiles ----
+  for (int jtl = 0; jtl < bt; ++jtl) {
+    const int jt = BJ * bt + jtl;
+    if (jt >= nw) break;
+    const int j0 = 32 * jtl + 8 * warp;  // this warp's chunk of the tile
+    // pass list: i tiles of BI (above the j tile in a diagonal rectangle) that exist and, in cutoff mode, can reach the j tile
+    bool need = lane < bt && BI * bt + lane < nw && (!diag || lane > jtl);
     if (boxtest && need) {
-      const float4 tlo = __ldg((const float4*)(bb + 8 * mine)), thi = __ldg((const float4*)(bb + 8 * mine + 4));
+      const int it = BI * bt + lane;
+      const float4 ilo = __ldg((const float4*)(bb + 8 * it)), ihi = __ldg((const float4*)(bb + 8 * it + 4));
+      const float4 tlo = __ldg((const float4*)(bb + 8 * jt)), thi = __ldg((const float4*)(bb + 8 * jt + 4));
       const float gx = fmaxf(fmaxf(__fsub_rn(tlo.x, ihi.x), __fsub_rn(ilo.x, thi.x)), 0.0f);
       const float gy = fmaxf(fmaxf(__fsub_rn(tlo.y, ihi.y), __fsub_rn(ilo.y, thi.y)), 0.0f);
       const float gz = fmaxf(fmaxf(__fsub_rn(tlo.z, ihi.z), __fsub_rn(ilo.z, thi.z)), 0.0f);
       need = __fmaf_rn(gz, gz, __fmaf_rn(gy, gy, __fmul_rn(gx, gx))) <= P.rc2;
     }
     uint32_t todo = __ballot_sync(0xffffffffu, need);
-    if (todo) fetch(base + 2 * (__ffs(todo) - 1) + warp);
-    while (todo) {
-      const int jt = base + 2 * (__ffs(todo) - 1) + warp;
-      todo &= todo - 1;
-      const uint32_t m = mn;
-      bool far = false;
-      if (boxtest) {
-        const float ex = fmaxf(fmaxf(__fsub_rn(blo.x, xi), __fsub_rn(xi, bhi.x)), 0.0f), ey = fmaxf(fmaxf(__fsub_rn(blo.y, yi), __fsub_rn(yi, bhi.y)), 0.0f);
-        const float ez = fmaxf(fmaxf(__fsub_rn(blo.z, zi), __fsub_rn(zi, bhi.z)), 0.0f);
-        far = !live_i || !(__fmaf_rn(ez, ez, __fmaf_rn(ey, ey, __fmul_rn(ex, ex))) <= P.rc2);
-      }
-      const bool skip = __all_sync(0xffffffffu, far || m == 0xffffffffu);
-      if (!skip) {
-        __syncwarp();
-        sj[lane] = jx; sj[32 + lane] = jy; sj[64 + lane] = jz; sj[96 + lane] = jq;
-        stj[lane] = jtype;
-        if (ENERGY && jt >= ib) { sjd[lane] = (double)jx; sjd[32 + lane] = (double)jy; sjd[64 + lane] = (double)jz; sjd[96 + lane] = (double)jq; }
-        __syncwarp();
-      }
-      if (todo) fetch(base + 2 * (__ffs(todo) - 1) + warp);
-      if (skip) continue;
+    if (todo == 0u) continue;  // fj of the chunk stays zero
+    int jc[8];
+    {
+      const int4 c0 = *(const int4*)(S.jcol + j0), c1 = *(const int4*)(S.jcol + j0 + 4);
+      jc[0] = c0.x; jc[1] = c0.y; jc[2] = c0.z; jc[3] = c0.w; jc[4] = c1.x; jc[5] = c1.y; jc[6] = c1.z; jc[7] = c1.w;
+    }
+    u64 fjx[4], fjy[4], fjz[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) fjx[q] = fjy[q] = fjz[q] = 0ull;
+    bool any = MODE == 0;  // cutoff mode: did any listed pass survive its vote?
+    // the i atom, its table row and its mask word of the NEXT pass are fetched while the current one computes
+    int ibl_n = __ffs(todo) - 1;
+    float4 pi_n = S.ipos[32 * ibl_n + lane];
+    int roff_n = S.irow[32 * ibl_n + lane];
+    uint32_t mw_n = __ldg(T.mask + (size_t)(32 * (BI * bt + ibl_n) + lane) * nw + jt);
 #pragma unroll 1
-    for (int j8 = 0; j8 < 32; j8 += 8) {
-      // Cutoff mode: 8 j atoms none of the 32 i atoms reaches contribute exactly zero (pair_eval2 zeroes every term of a
-      // pair beyond the cutoff) and are dropped on a warp vote, like the passes of the on-chip tiles.  The r^2 are the
-      // expressions pair_eval2 evaluates (same operands, same order): bit-identical results, the test costs the compares.
+    while (todo) {
+      asm volatile("" ::: "memory");  // re-read the 8 broadcast j atoms every pass instead of pinning 32 registers
+      const int ibl = ibl_n;
+      todo &= todo - 1;
+      const float4 pi = pi_n;
+      const uint32_t taddr = tab + (uint32_t)roff_n;
+      const uint32_t m8 = (mw_n >> (8 * warp)) & 0xffu;
+      if (todo) {
+        ibl_n = __ffs(todo) - 1;
+        pi_n = S.ipos[32 * ibl_n + lane];
+        roff_n = S.irow[32 * ibl_n + lane];
+        mw_n = __ldg(T.mask + (size_t)(32 * (BI * bt + ibl_n) + lane) * nw + jt);
+      }
+      const float kqi = pi.w;
+      const u64 xi = dup2(pi.x), yi = dup2(pi.y), zi = dup2(pi.z), kq2 = dup2(kqi);
       if (MODE == 1) {
         bool in = false;
 #pragma unroll
-        for (int jj = j8; jj < j8 + 8; jj += 2) {
-          u64 dx = sub2(xi2, *(const u64*)(sj + jj)), dy = sub2(yi2, *(const u64*)(sj + 32 + jj)), dz = sub2(zi2, *(const u64*)(sj + 64 + jj));
-          if (PBC) { dx = wrap2(dx, nbox.x, ibox.x); dy = wrap2(dy, nbox.y, ibox.y); dz = wrap2(dz, nbox.z, ibox.z); }
-          float ra, rb;
-          upk(fma2(dz, dz, fma2(dy, dy, mul2(dx, dx))), ra, rb);
-          in = in || ra <= P.rc2 || rb <= P.rc2;
+        for (int h = 0; h < 2; ++h) {
+          const ulonglong2 xj = *(const ulonglong2*)(S.jx + j0 + 4 * h), yj = *(const ulonglong2*)(S.jy + j0 + 4 * h), zj = *(const ulonglong2*)(S.jz + j0 + 4 * h);
+#pragma unroll
+          for (int k = 0; k < 2; ++k) {
+            u64 dx = sub2(xi, k ? xj.y : xj.x), dy = sub2(yi, k ? yj.y : yj.x), dz = sub2(zi, k ? zj.y : zj.x);
+            if (PBC) { dx = wrap2(dx, nbox.x, ibox.x); dy = wrap2(dy, nbox.y, ibox.y); dz = wrap2(dz, nbox.z, ibox.z); }
+            float ra, rb;
+            upk(fma2(dz, dz, fma2(dy, dy, mul2(dx, dx))), ra, rb);
+            in = in || ra <= P.rc2 || rb <= P.rc2;
+          }
         }
         if (!__any_sync(0xffffffffu, in)) continue;
+        any = true;
+      }
+      u64 ax = 0ull, ay = 0ull, az = 0ull;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const ulonglong2 xj = *(const ulonglong2*)(S.jx + j0 + 4 * h), yj = *(const ulonglong2*)(S.jy + j0 + 4 * h), zj = *(const ulonglong2*)(S.jz + j0 + 4 * h);
+        const ulonglong2 qj = *(const ulonglong2*)(S.jq + j0 + 4 * h);
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          const int q = 2 * h + k;
+          const u64 a12 = pk(lds_f32<0>(taddr + jc[2 * q]), lds_f32<0>(taddr + jc[2 * q + 1]));
+          const u64 nb6 = pk(lds_f32<4>(taddr + jc[2 * q]), lds_f32<4>(taddr + jc[2 * q + 1]));
+          u64 dx = sub2(xi, k ? xj.y : xj.x), dy = sub2(yi, k ? yj.y : yj.x), dz = sub2(zi, k ? zj.y : zj.x);
+          if (PBC) { dx = wrap2(dx, nbox.x, ibox.x); dy = wrap2(dy, nbox.y, ibox.y); dz = wrap2(dz, nbox.z, ibox.z); }
+          const u64 sc = pair_eval2<MODE>(dx, dy, dz, kqi, kq2, k ? qj.y : qj.x, a12, nb6, (m8 >> (2 * q)) & 1u, (m8 >> (2 * q + 1)) & 1u, P, C);
+          ax = fma2(sc, dx, ax); ay = fma2(sc, dy, ay); az = fma2(sc, dz, az);
+          fjx[q] = fma2(sc, dx, fjx[q]); fjy[q] = fma2(sc, dy, fjy[q]); fjz[q] = fma2(sc, dz, fjz[q]);
+        }
+      }
+      float* f = &S.fi[warp][0][32 * ibl + lane];
+      f[0] = __fadd_rn(f[0], hsum2(ax)); f[kLB] = __fadd_rn(f[kLB], hsum2(ay)); f[2 * kLB] = __fadd_rn(f[2 * kLB], hsum2(az));
+    }
+    if (!any) continue;  // every pass dropped out: fj of the chunk stays zero
+    // transposing butterfly (as tile_task): 24 per-lane partials -> per-atom sums; after the xor-16/8/4 stages lane l holds
+    // atom (l >> 2) & 7 of the chunk, xor-2/1 finish the sum.  Fixed order => deterministic.
+    float fj[8][3];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      upk(fjx[q], fj[2 * q][0], fj[2 * q + 1][0]);
+      upk(fjy[q], fj[2 * q][1], fj[2 * q + 1][1]);
+      upk(fjz[q], fj[2 * q][2], fj[2 * q + 1][2]);
+    }
+    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4;
+    float v4[4][3], v2[2][3], v1[3];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float send = b4 ? fj[k][c] : fj[k + 4][c], keep = b4 ? fj[k + 4][c] : fj[k][c];
+        v4[k][c] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 16));
       }
 #pragma unroll
-      for (int jj = j8; jj < j8 + 8; jj += 2) {
-        const u64 xj = *(const u64*)(sj + jj), yj = *(const u64*)(sj + 32 + jj), zj = *(const u64*)(sj + 64 + jj);
-        const u64 qj = *(const u64*)(sj + 96 + jj);
-        const int2 tj = *(const int2*)(stj + jj);
-        const u64 a12 = pk(lds_f32<0>(tbase + tj.x), lds_f32<0>(tbase + tj.y)), nb6 = pk(lds_f32<4>(tbase + tj.x), lds_f32<4>(tbase + tj.y));
-        u64 dx = sub2(xi2, xj), dy = sub2(yi2, yj), dz = sub2(zi2, zj);
+    for (int k = 0; k < 2; ++k)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float send = b3 ? v4[k][c] : v4[k + 2][c], keep = b3 ? v4[k + 2][c] : v4[k][c];
+        v2[k][c] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 8));
+      }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float send = b2 ? v2[0][c] : v2[1][c], keep = b2 ? v2[1][c] : v2[0][c];
+      float v = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 4));
+      v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, 2));
+      v1[c] = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, 1));
+    }
+    if ((lane & 3) == 0) {
+      const int j = j0 + (lane >> 2);
+      S.fj[0][j] = -v1[0]; S.fj[1][j] = -v1[1]; S.fj[2][j] = -v1[2];
+    }
+  }
+  // ---- pairs inside a tile (diagonal rectangles): lane = i atom meets the 32 atoms of its own tile, no j side ----
+  if (diag) {
+    for (int tl = warp; tl < bt; tl += kLThreads / 32) {
+      const int tile = BI * bt + tl;
+      if (tile >= nw) break;
+      const float4 pi = S.ipos[32 * tl + lane];
+      const uint32_t taddr = tab + (uint32_t)S.irow[32 * tl + lane];
+      const uint32_t m = __ldg(T.mask + (size_t)(32 * tile + lane) * nw + tile);
+      const float kqi = pi.w;
+      const u64 xi = dup2(pi.x), yi = dup2(pi.y), zi = dup2(pi.z), kq2 = dup2(kqi);
+      u64 ax = 0ull, ay = 0ull, az = 0ull;
+#pragma unroll 4
+      for (int jj = 0; jj < 32; jj += 2) {
+        const float* sj = S.jx + 32 * tl + jj;
+        const u64 xj = *(const u64*)sj, yj = *(const u64*)(sj + kLB), zj = *(const u64*)(sj + 2 * kLB), qj = *(const u64*)(sj + 3 * kLB);
+        const int2 tj = *(const int2*)(S.jcol + 32 * tl + jj);
+        const u64 a12 = pk(lds_f32<0>(taddr + tj.x), lds_f32<0>(taddr + tj.y)), nb6 = pk(lds_f32<4>(taddr + tj.x), lds_f32<4>(taddr + tj.y));
+        u64 dx = sub2(xi, xj), dy = sub2(yi, yj), dz = sub2(zi, zj);
         if (PBC) { dx = wrap2(dx, nbox.x, ibox.x); dy = wrap2(dy, nbox.y, ibox.y); dz = wrap2(dz, nbox.z, ibox.z); }
         const u64 sc = pair_eval2<MODE>(dx, dy, dz, kqi, kq2, qj, a12, nb6, (m >> jj) & 1u, (m >> (jj + 1)) & 1u, P, C);
         ax = fma2(sc, dx, ax); ay = fma2(sc, dy, ay); az = fma2(sc, dz, az);
       }
-    }
-    if (ENERGY && jt >= ib) {  // FP64 energies of the unordered pairs this tile owns (forces.py:379-413, 451-489 in double)
-      const double xd = (double)xi, yd = (double)yi, zd = (double)zi;
-      const double kq = kLElec * (double)(__ldg(T.charge + 32 * ib + lane) * P.el_on);
-      const double rc2 = P.rc_d * P.rc_d, ta = (double)P.tab_a, tb = (double)P.tab_b;
-      const double2* trow = T.tab64 + (size_t)__ldg(T.atom_type + 32 * ib + lane) * T.ntypes;
-      const int jfirst = jt == ib ? lane + 1 : 0;  // diagonal tile: j > i
-      for (int jj = 0; jj < 32; ++jj) {
-        if (jj < jfirst || ((m >> jj) & 1u)) continue;
-        double dx = xd - sjd[jj], dy = yd - sjd[32 + jj], dz = zd - sjd[64 + jj];
-        if (PBC) {
-          const double bx = -(double)nbox.x, by = -(double)nbox.y, bz = -(double)nbox.z;
-          if (bx != 0.0) dx -= bx * rint(dx / bx);
-          if (by != 0.0) dy -= by * rint(dy / by);
-          if (bz != 0.0) dz -= bz * rint(dz / bz);
-        }
-        const double r2 = dx * dx + dy * dy + dz * dz;
-        if (MODE == 1 && !(r2 <= rc2)) continue;
-        const double rinv = drsqrt(r2), r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
-        const double2 ab = __ldg(trow + (stj[jj] >> 3));
-        const double qq = kq * sjd[96 + jj];
-        double lj = (ta * ab.x * r6 + tb * ab.y) * r6;
-        if (MODE == 1) {
-          const double r = r2 * rinv;
-          if (r > P.rs_d) {
-            const double t = (r - P.rs_d) * P.inv_sw_d;
-            lj *= 1.0 + t * t * t * (-10.0 + t * (15.0 - t * 6.0));
-          }
-          eel += qq * (rinv + P.krf_d * r2 - P.crf_d);
-        } else {
-          eel += qq * rinv;
-        }
-        elj += lj;
-      }
-    }
+      float* f = &S.fi[warp][0][32 * tl + lane];
+      f[0] = __fadd_rn(f[0], hsum2(ax)); f[kLB] = __fadd_rn(f[kLB], hsum2(ay)); f[2 * kLB] = __fadd_rn(f[2 * kLB], hsum2(az));
     }
   }
-  fx = hsum2(ax); fy = hsum2(ay); fz = hsum2(az);
+  __syncthreads();
+  for (int k = tid; k < 3 * nia; k += kLThreads) {
+    const int t = k / 3, c = k - 3 * t;
+    if (32 * bt * BI + t < N) {
+      float v = __fadd_rn(__fadd_rn(S.fi[0][c][t], S.fi[1][c][t]), __fadd_rn(S.fi[2][c][t], S.fi[3][c][t]));
+      if (diag) v = __fadd_rn(v, S.fj[c][t]);
+      out_i[k] = v;
+    }
+  }
+  if (!diag)
+    for (int k = tid; k < 3 * nja; k += kLThreads) {
+      const int t = k / 3, c = k - 3 * t;
+      if (32 * bt * BJ + t < N) out_j[k] = S.fj[c][t];
+    }
 }
 
-// Every force of one Forces.compute in ONE launch: grid (nwin, min(R, 65535)), CTA = one window of kLWin = 64 atoms of one
-// replica.  Phase A, bonded (fp32): the CTA evaluates every item that touches the window into private shared-memory slots
-// (positions of the atoms those items reference are staged in shared memory first when they span at most kLHalo atoms --
-// true of any chain-ordered topology), then thread a < 64 sums atom a's slots in their fixed order and adds the SMD
-// restraint.  Phase B, pairs: warps (0, 1) take the window's first 32-atom i-block, warps (2, 3) the second, each pair of
-// warps splitting the j tiles (large_pairs_body).  Epilogue: force row = bonded + (warp 0 + warp 1), written once, coalesced.
-// Separate bonded and pair kernels (54 + 76 us per step of 256 x 1 040 atoms in cutoff mode, each issuing on ~half of the
-// cycles: the bonded one waits on gathered loads, the pair one on its short tile lists) ran back to back; here CTAs in
-// different phases share an SM and fill each other's stalls, and the force rows are written once instead of written,
-// re-read and re-written.
-// Shared memory (dynamic): type-pair tables | bonded slots [win_slots_max][3] | staged positions [halo_max][3].
-#ifndef LV_OCC
-#define LV_OCC 5
-#endif
-template <int MODE, bool ENERGY>
-__global__ void __launch_bounds__(kLThreads, ENERGY ? 4 : LV_OCC)
-large_forces_kernel(const LargeTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
-                    const float* __restrict__ box, float* __restrict__ forces, double* __restrict__ partial, const int npart,
-                    const int part0, uint32_t* __restrict__ status, const float* __restrict__ bbox,
-                    const float* __restrict__ smd_centers, const double smd_center, double* __restrict__ smd_rec) {
+// Every force of one Forces.compute in ONE launch, as partial rows: grid (nrect + nwin, min(R, 65535)).
+//   CTA x < nrect : pair rectangle x = BI (BI + 1) / 2 + BJ of one replica (large_rect above) -> slots 0 .. nblk - 1;
+//   CTA x >= nrect: bonded window w = x - nrect of kLWin = 64 atoms (fp32): every item that touches the window is evaluated
+//                   into private shared-memory slots (positions of the atoms those items reference are staged in shared
+//                   memory first when they span at most kLHalo atoms -- true of any chain-ordered topology), then thread
+//                   a < 64 sums atom a's slots in their fixed order, adds the SMD restraint and writes slot nblk.
+// The two kinds of CTA share the SMs (the bonded ones wait on gathered loads, the pair ones issue packed FP32), and the
+// force row of an atom is the fixed-order sum of its nblk + 1 slots, taken by the consumer (large_sum_kernel, or the
+// integrator's half-kick kernel, which reads the rows anyway).
+// Shared memory (dynamic): type-pair tables + RectSmem  or  bonded slots [win_slots_max][3] + staged positions [halo_max][3].
+__device__ __forceinline__ float large_row_sum(const float* __restrict__ fpart, const long long r, const int nslot, const int slot0,
+                                               const int N, const int a, const int c) {
+  const float* q = fpart + ((size_t)r * nslot * N + a) * 3 + c;
+  float f = q[(size_t)(nslot - 1) * N * 3];  // bonded
+  for (int k = slot0; k < nslot - 1; ++k) f = __fadd_rn(f, q[(size_t)k * N * 3]);
+  return f;
+}
+inline int large_tab_bytes(const LargeTopo& T) { return (2 * T.ntypes * large_tab_stride(T.ntypes) * (int)sizeof(float) + 15) & ~15; }
+inline int large_pairs_dyn_bytes(const LargeTopo& T) { return large_tab_bytes(T) + (int)sizeof(RectSmem); }
+inline int large_bonded_dyn_bytes(const LargeTopo& T) { return (int)sizeof(float) * (4 * T.win_slots_max + 3 * T.halo_max); }
+
+template <int MODE>
+__global__ void __launch_bounds__(kLThreads, 5)
+large_pairs_kernel(const LargeTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
+                   const float* __restrict__ box, float* __restrict__ fpart, const float* __restrict__ bbox) {
   extern __shared__ __align__(16) char lsmem[];
   const int tstride = large_tab_stride(T.ntypes);
-  float* sAB = (float*)lsmem;  // [ntypes][stride] entries (12 A tab_a, 6 B tab_b)
-  float* lslots = sAB + 2 * T.ntypes * tstride;
-  float* shalo = lslots + 3 * T.win_slots_max;
-  __shared__ __align__(16) float sj[kLThreads / 32][4 * 32];
-  __shared__ __align__(16) int stj[kLThreads / 32][32];
-  __shared__ double sjd[ENERGY ? kLThreads / 32 : 1][ENERGY ? 4 * 32 : 1];
-  __shared__ float sf[kLThreads / 32][3][32];
-  __shared__ float sbond[3 * kLWin];
-  __shared__ double sred[(kLThreads / 32) * 2];
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, w = blockIdx.x;
-  const int N = T.natoms;
-  for (int k = tid; k < T.ntypes * T.ntypes; k += kLThreads) {
-    const int t = k / T.ntypes, u = k - t * T.ntypes;
-    sAB[2 * (t * tstride + u)] = __ldg(T.tab12a + k) * P.tab_a;
-    sAB[2 * (t * tstride + u) + 1] = __ldg(T.tab6b + k) * P.tab_b;
+  const int tab_bytes = (2 * T.ntypes * tstride * (int)sizeof(float) + 15) & ~15;
+  const int tid = threadIdx.x;
+  const int N = T.natoms, nslot = T.nblk + 1;
+  {
+    float* sAB = (float*)lsmem;  // [ntypes][stride] entries (12 A tab_a, 6 B tab_b)
+    RectSmem& S = *(RectSmem*)(lsmem + tab_bytes);
+    for (int k = tid; k < T.ntypes * T.ntypes; k += kLThreads) {
+      const int t = k / T.ntypes, u = k - t * T.ntypes;
+      sAB[2 * (t * tstride + u)] = __ldg(T.tab12a + k) * P.tab_a;
+      sAB[2 * (t * tstride + u) + 1] = __ldg(T.tab6b + k) * P.tab_b;
+    }
+    int BI = 0;
+    while ((BI + 1) * (BI + 2) / 2 <= (int)blockIdx.x) ++BI;
+    const int BJ = (int)blockIdx.x - BI * (BI + 1) / 2;
+    const uint32_t tab = (uint32_t)__cvta_generic_to_shared(sAB);
+    for (long long r = blockIdx.y; r < R; r += gridDim.y) {
+      const float* p = pos + r * N * 3;
+      const float b0 = box ? __ldg(box + r * 9) : 0.0f, b1 = box ? __ldg(box + r * 9 + 4) : 0.0f, b2 = box ? __ldg(box + r * 9 + 8) : 0.0f;
+      const bool pbc = b0 != 0.0f || b1 != 0.0f || b2 != 0.0f;  // forces.py:359
+      const float3 nbox = make_float3(-b0, -b1, -b2);
+      const float3 ibox = make_float3(b0 != 0.0f ? 1.0f / b0 : 0.0f, b1 != 0.0f ? 1.0f / b1 : 0.0f, b2 != 0.0f ? 1.0f / b2 : 0.0f);
+      float* out_i = fpart + (((size_t)r * nslot + BJ) * N + 32 * T.bt * BI) * 3;
+      float* out_j = fpart + (((size_t)r * nslot + BI) * N + 32 * T.bt * BJ) * 3;
+      __syncthreads();  // the tables (first pass); the previous replica's rows have been read
+      if (pbc) large_rect<MODE, true>(T, P, p, nullptr, S, tab, BI, BJ, nbox, ibox, out_i, out_j, tid);
+      else large_rect<MODE, false>(T, P, p, bbox ? bbox + r * T.nwords * 8 : nullptr, S, tab, BI, BJ, nbox, ibox, out_i, out_j, tid);
+    }
   }
-  // phase A constants
+}
+
+__global__ void __launch_bounds__(kLBondedThreads, 8)
+large_bonded_forces_kernel(const LargeTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
+                           const float* __restrict__ box, float* __restrict__ fpart, uint32_t* __restrict__ status,
+                           const float* __restrict__ smd_centers, const double smd_center, double* __restrict__ smd_rec) {
+  extern __shared__ __align__(16) char lsmem[];
+  const int tid = threadIdx.x;
+  const int N = T.natoms, nslot = T.nblk + 1;
+  float4* lslots = (float4*)lsmem;
+  float* shalo = (float*)(lslots + T.win_slots_max);
+  const int w = (int)blockIdx.x;
   const LItemRanges G = litem_ranges(T, P.terms);
   const int k0 = __ldg(T.win_start + w), k1 = __ldg(T.win_start + w + 1);
   const int hlo = __ldg(T.win_lo + w), hn = __ldg(T.win_n + w);
-  // warps (0, 1) own the window's first i-block, warps (2, 3) the second: the even warp of each pair gathers the bonded slots
-  // of its 32 atoms while the odd warp already starts on its pair tiles
-  const int aw = 32 * (warp >> 1) + lane;  // atom of the window this thread gathers (even warps)
-  const int a = kLWin * w + aw;
-  const bool gatherer = (warp & 1) == 0;
-  const bool mine = gatherer && a < N;
+  const int a = kLWin * w + tid;  // the atom this thread gathers (tid < kLWin)
+  const bool mine = tid < kLWin && a < N;
   const int g0 = __ldg(T.gstart + kLWin * w);
   const int s0 = mine ? __ldg(T.gstart + a) - g0 : 0, s1 = mine ? __ldg(T.gstart + a + 1) - g0 : 0;
-  // phase B constants
-  const int ib = 2 * w + (warp >> 1), sub = warp & 1;
-  const bool ib_ok = ib < T.nwords;
-  const int i = ib_ok ? 32 * ib + lane : 0;
-  const bool live = ib_ok && i < N;
-  const uint32_t tbase = (uint32_t)__cvta_generic_to_shared(sAB) + (uint32_t)(__ldg(T.atom_type + i) * tstride * 8);
-  const float kqi = __fmul_rn(__ldg(T.charge + i) * P.el_on, kElecFactor);
-  const bool nonbonded = (P.terms & (B200MD_T_ELECTROSTATICS | B200MD_T_LJ | B200MD_T_REPULSION | B200MD_T_REPULSIONCG)) != 0;
   for (long long r = blockIdx.y; r < R; r += gridDim.y) {
     const float* p = pos + r * N * 3;
     const float b0 = box ? __ldg(box + r * 9) : 0.0f, b1 = box ? __ldg(box + r * 9 + 4) : 0.0f, b2 = box ? __ldg(box + r * 9 + 8) : 0.0f;
-    const bool pbc = b0 != 0.0f || b1 != 0.0f || b2 != 0.0f;  // forces.py:359
-    // ---- phase A: bonded items of the window ----
-    __syncthreads();  // the tables (first pass); the slots and staged positions of the previous replica are no longer read
+    const bool pbc = b0 != 0.0f || b1 != 0.0f || b2 != 0.0f;
+    __syncthreads();  // the slots and staged positions of the previous replica are no longer read
     for (int k = tid; k < 3 * hn; k += kLThreads) shalo[k] = __ldg(p + 3 * hlo + k);
     __syncthreads();
     {
@@ -579,10 +696,12 @@ large_forces_kernel(const LargeTopo T, const ForceParams P, const long long R, c
       }
     }
     __syncthreads();
-    if (gatherer) {
+    if (mine) {
       float bx = 0.0f, by = 0.0f, bz = 0.0f;
-      for (int sidx = s0; sidx < s1; ++sidx) { bx += lslots[3 * sidx]; by += lslots[3 * sidx + 1]; bz += lslots[3 * sidx + 2]; }
-      if (mine && P.smd_on && (a == P.smd_a1 || a == P.smd_a2)) {  // potcalc.py:75-89, not wrapped; FP64: (c - d) cancels near the centre
+      for (int sidx = s0; sidx < s1; ++sidx) { const float4 v = lslots[sidx]; bx += v.x; by += v.y; bz += v.z; }
+      const float x = __ldg(p + 3 * a), y = __ldg(p + 3 * a + 1), z = __ldg(p + 3 * a + 2);
+      if (status != nullptr && (x != x || y != y || z != z)) atomicOr(status + r, B200MD_FLAG_NAN_POS);
+      if (P.smd_on && (a == P.smd_a1 || a == P.smd_a2)) {  // potcalc.py:75-89, not wrapped; FP64: (c - d) cancels near the centre
         const double center = smd_centers ? (double)__ldg(smd_centers + r) : smd_center;
         const v3t<double> d = vsub(vpos<double>(p, P.smd_a2), vpos<double>(p, P.smd_a1));
         const double dist = sqrt(vdot(d, d)), dev = center - dist;
@@ -594,39 +713,106 @@ large_forces_kernel(const LargeTopo T, const ForceParams P, const long long R, c
           smd_rec[2 * r + 1] += (double)P.smd_fk * dev * (double)P.smd_rate;
         }
       }
-      sbond[3 * aw] = bx; sbond[3 * aw + 1] = by; sbond[3 * aw + 2] = bz;
+      float* o = fpart + (((size_t)r * nslot + T.nblk) * N + a) * 3;
+      o[0] = bx; o[1] = by; o[2] = bz;
     }
-    // ---- phase B: pair tiles of the window's two i-blocks ----
-    float xi = 0.f, yi = 0.f, zi = 0.f;
-    if (live) { xi = __ldg(p + 3 * i); yi = __ldg(p + 3 * i + 1); zi = __ldg(p + 3 * i + 2); }
-    if (sub == 0 && live && status != nullptr && (xi != xi || yi != yi || zi != zi)) atomicOr(status + r, B200MD_FLAG_NAN_POS);
-    const float3 nbox = make_float3(-b0, -b1, -b2);
-    const float3 ibox = make_float3(b0 != 0.0f ? 1.0f / b0 : 0.0f, b1 != 0.0f ? 1.0f / b1 : 0.0f, b2 != 0.0f ? 1.0f / b2 : 0.0f);
-    float fx = 0.f, fy = 0.f, fz = 0.f;
+  }
+}
+
+// forces[r][a][c] = bonded slot + pair slots slot0 .. nblk - 1 in index order (Forces.compute; the integrator's half-kick
+// kernel takes the same sum itself)
+__global__ void large_sum_kernel(const LargeTopo T, const long long R, const float* __restrict__ fpart, const int slot0,
+                                 float* __restrict__ forces) {
+  const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= R * T.natoms * 3) return;
+  const long long r = g / (T.natoms * 3);
+  const int k = (int)(g - r * T.natoms * 3), a = k / 3, c = k - 3 * a;
+  forces[g] = large_row_sum(fpart, r, T.nblk + 1, slot0, T.natoms, a, c);
+}
+
+// FP64 energies of the nonbonded pairs (report steps / Forces.compute with energies; forces.py:379-413, 451-489 in double
+// from the fp32 positions), half shell: CTA = 32-atom i tile, lane = i atom, the 4 warps split the j tiles jt >= ib
+// (j > i inside the diagonal tile).  grid (nwords, min(R, 65535)); partial[(r * npart + part0 + ib) * 8 + {el, lj}].
+// Only reads the positions: the host runs it beside the force launch on the second stream.
+template <int MODE>
+__global__ void __launch_bounds__(kLThreads)
+large_pair_energy_kernel(const LargeTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
+                         const float* __restrict__ box, double* __restrict__ partial, const int npart, const int part0,
+                         const float* __restrict__ bbox) {
+  __shared__ double sjd[kLThreads / 32][4 * 32];
+  __shared__ int stj[kLThreads / 32][32];
+  __shared__ double sred[(kLThreads / 32) * 2];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, ib = blockIdx.x;
+  const int N = T.natoms, i = 32 * ib + lane;
+  const bool live = i < N;
+  const double kq = kLElec * (double)(__ldg(T.charge + i) * P.el_on);
+  const double2* trow = T.tab64 + (size_t)__ldg(T.atom_type + i) * T.ntypes;
+  const uint32_t* mrow = T.mask + (size_t)i * T.nwords;
+  const double rc2 = P.rc_d * P.rc_d, ta = (double)P.tab_a, tb = (double)P.tab_b;
+  for (long long r = blockIdx.y; r < R; r += gridDim.y) {
+    const float* p = pos + r * N * 3;
+    const double bx = box ? (double)__ldg(box + r * 9) : 0.0, by = box ? (double)__ldg(box + r * 9 + 4) : 0.0, bz = box ? (double)__ldg(box + r * 9 + 8) : 0.0;
+    const bool pbc = bx != 0.0 || by != 0.0 || bz != 0.0;
+    const float* bb = (MODE == 1 && !pbc && bbox != nullptr) ? bbox + r * T.nwords * 8 : nullptr;
+    double xd = 0.0, yd = 0.0, zd = 0.0;
+    if (live) { xd = (double)__ldg(p + 3 * i); yd = (double)__ldg(p + 3 * i + 1); zd = (double)__ldg(p + 3 * i + 2); }
     double e[2] = {0.0, 0.0};
-    if (nonbonded && ib_ok) {
-      double* sd = sjd[ENERGY ? warp : 0];
-      if (pbc) large_pairs_body<MODE, ENERGY, true>(T, P, p, tbase, sj[warp], stj[warp], sd, nbox, ibox, ib, sub, lane, xi, yi, zi, kqi, nullptr, fx, fy, fz, e[0], e[1]);
-      else large_pairs_body<MODE, ENERGY, false>(T, P, p, tbase, sj[warp], stj[warp], sd, nbox, ibox, ib, sub, lane, xi, yi, zi, kqi,
-                                                    bbox ? bbox + r * T.nwords * 8 : nullptr, fx, fy, fz, e[0], e[1]);
-    }
-    sf[warp][0][lane] = fx; sf[warp][1][lane] = fy; sf[warp][2][lane] = fz;
-    __syncthreads();
-    for (int k = tid & 63; k < 96; k += 64) {  // thread (atom, c): bonded + (even warp + odd warp), 32 coalesced rows
-      const int l = k / 3, c = k - 3 * l, ia = 32 * ib + l;
-      if (ib_ok && ia < N) {
-        const int wb = warp & ~1;
-        forces[(r * N + ia) * 3 + c] = __fadd_rn(sbond[96 * (warp >> 1) + k], __fadd_rn(sf[wb][c][l], sf[wb + 1][c][l]));
+    for (int jt = ib + warp; jt < T.nwords; jt += kLThreads / 32) {
+      if (bb != nullptr) {  // warp-uniform: the two tile boxes are further apart than the cutoff
+        const float4 ilo = __ldg((const float4*)(bb + 8 * ib)), ihi = __ldg((const float4*)(bb + 8 * ib + 4));
+        const float4 tlo = __ldg((const float4*)(bb + 8 * jt)), thi = __ldg((const float4*)(bb + 8 * jt + 4));
+        const float gx = fmaxf(fmaxf(__fsub_rn(tlo.x, ihi.x), __fsub_rn(ilo.x, thi.x)), 0.0f);
+        const float gy = fmaxf(fmaxf(__fsub_rn(tlo.y, ihi.y), __fsub_rn(ilo.y, thi.y)), 0.0f);
+        const float gz = fmaxf(fmaxf(__fsub_rn(tlo.z, ihi.z), __fsub_rn(ilo.z, thi.z)), 0.0f);
+        // (the gap components are fp32 lower bounds of the FP64 |d| below: 1 ulp of margin per component covers the rounding)
+        if (__fmaf_rn(gz, gz, __fmaf_rn(gy, gy, __fmul_rn(gx, gx))) > 1.00001f * P.rc2) continue;
+      }
+      const int j = 32 * jt + lane;
+      double* sd = sjd[warp];
+      __syncwarp();
+      if (j < N) {
+        sd[lane] = (double)__ldg(p + 3 * j); sd[32 + lane] = (double)__ldg(p + 3 * j + 1); sd[64 + lane] = (double)__ldg(p + 3 * j + 2);
+        sd[96 + lane] = (double)(__ldg(T.charge + j) * P.el_on);
+      } else {
+        sd[lane] = 0.0; sd[32 + lane] = 0.0; sd[64 + lane] = 0.0; sd[96 + lane] = 0.0;
+      }
+      stj[warp][lane] = __ldg(T.atom_type + j);
+      __syncwarp();
+      const uint32_t m = __ldg(mrow + jt);
+      const int jfirst = jt == ib ? lane + 1 : 0;  // diagonal tile: j > i
+      for (int jj = 0; jj < 32; ++jj) {
+        if (jj < jfirst || ((m >> jj) & 1u)) continue;
+        double dx = xd - sd[jj], dy = yd - sd[32 + jj], dz = zd - sd[64 + jj];
+        if (pbc) {
+          if (bx != 0.0) dx -= bx * rint(dx / bx);
+          if (by != 0.0) dy -= by * rint(dy / by);
+          if (bz != 0.0) dz -= bz * rint(dz / bz);
+        }
+        const double r2 = dx * dx + dy * dy + dz * dz;
+        if (MODE == 1 && !(r2 <= rc2)) continue;
+        const double rinv = drsqrt(r2), r2inv = rinv * rinv, r6 = r2inv * r2inv * r2inv;
+        const double2 ab = __ldg(trow + stj[warp][jj]);
+        const double qq = kq * sd[96 + jj];
+        double lj = (ta * ab.x * r6 + tb * ab.y) * r6;
+        if (MODE == 1) {
+          const double rr = r2 * rinv;
+          if (rr > P.rs_d) {
+            const double t = (rr - P.rs_d) * P.inv_sw_d;
+            lj *= 1.0 + t * t * t * (-10.0 + t * (15.0 - t * 6.0));
+          }
+          e[0] += qq * (rinv + P.krf_d * r2 - P.crf_d);
+        } else {
+          e[0] += qq * rinv;
+        }
+        e[1] += lj;
       }
     }
-    if (ENERGY) {
-      lreduce<2, kLThreads>(e, sred, tid);
-      if (tid == 0) {
-        double* o = partial + (r * npart + part0 + w) * B200MD_NUM_ENERGIES;
-        o[B200MD_E_ELECTROSTATICS] = e[0]; o[B200MD_E_LJ] = e[1];
+    lreduce<2, kLThreads>(e, sred, tid);
+    if (tid == 0) {
+      double* o = partial + (r * npart + part0 + ib) * B200MD_NUM_ENERGIES;
+      o[B200MD_E_ELECTROSTATICS] = e[0]; o[B200MD_E_LJ] = e[1];
 #pragma unroll
-        for (int k = 2; k < B200MD_NUM_ENERGIES; ++k) o[k] = 0.0;
-      }
+      for (int k = 2; k < B200MD_NUM_ENERGIES; ++k) o[k] = 0.0;
     }
   }
 }
@@ -666,8 +852,9 @@ __global__ void large_vv1_kernel(const LargeTopo T, const float dt, const long l
 // of a call, where pos must stay x(t + dt).
 __global__ void __launch_bounds__(256)
 large_vv2_kernel(const LargeTopo T, const StepParams I, const unsigned long long gstep, const long long R,
-                 float* __restrict__ vel, const float* __restrict__ forces, float* __restrict__ pos,
-                 double* __restrict__ ekin, uint32_t* __restrict__ status, const int fuse_next, float* __restrict__ bbox) {
+                 float* __restrict__ vel, float* __restrict__ forces, float* __restrict__ pos,
+                 double* __restrict__ ekin, uint32_t* __restrict__ status, const int fuse_next, float* __restrict__ bbox,
+                 const float* __restrict__ fpart, const int slot0) {
   __shared__ double sred[8];
   const int tid = threadIdx.x, a = blockIdx.x * 256 + tid;
   for (long long r = blockIdx.y; r < R; r += gridDim.y) {
@@ -677,6 +864,12 @@ large_vv2_kernel(const LargeTopo T, const StepParams I, const unsigned long long
       const long long g = r * T.natoms + a;
       const float mass = __ldg(T.mass + a), invm = 1.0f / mass, hdt_m = 0.5f * I.dt * invm;
       float v[3] = {vel[3 * g], vel[3 * g + 1], vel[3 * g + 2]};
+      float f[3];  // the force row: fixed-order sum of the partial rows of large_forces_kernel, stored for the caller
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        f[c] = large_row_sum(fpart, r, T.nblk + 1, slot0, T.natoms, a, c);
+        forces[3 * g + c] = f[c];
+      }
       if (I.temperature > 0.0f) {
         const float vcoef = sqrtf(2.0f * I.gamma * invm * kBoltzman * I.temperature * I.dt), vdamp = I.gamma * I.dt;
         float n[3];
@@ -686,7 +879,7 @@ large_vv2_kernel(const LargeTopo T, const StepParams I, const unsigned long long
       }
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        v[c] = fmaf(hdt_m, forces[3 * g + c], v[c]);
+        v[c] = fmaf(hdt_m, f[c], v[c]);
         vel[3 * g + c] = v[c];
       }
       e[0] = 0.5 * (double)mass * ((double)v[0] * v[0] + (double)v[1] * v[1] + (double)v[2] * v[2]);
@@ -695,7 +888,7 @@ large_vv2_kernel(const LargeTopo T, const StepParams I, const unsigned long long
       if (fuse_next) {  // large_vv1_kernel's arithmetic, expression by expression (bit-identical trajectories)
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-          v[c] = fmaf(hdt_m, forces[3 * g + c], v[c]);
+          v[c] = fmaf(hdt_m, f[c], v[c]);
           vel[3 * g + c] = v[c];
         }
         x = fmaf(I.dt, v[0], x); y = fmaf(I.dt, v[1], y); z = fmaf(I.dt, v[2], z);
