@@ -624,14 +624,31 @@ def run_ours(args):
         flopL = 36 * npairL + copies * (FLOP_PER_REPLICA_EVAL - 36 * 4820)
         extra["large_solute_1040_atoms_forces_compute"] = {
             "value": RL / tL, "unit": "replica-evaluations/s", "replicas": RL, "natoms": NL, "unique_pairs": npairL,
-            "ms_per_call": 1e3 * tL, "tflops": RL / tL * flopL / 1e12, "launches_per_call": 4,
-            "note": "full-shell pair tiles: every pair is evaluated from both of its atoms, the flop count credits it once"}
+            "ms_per_call": 1e3 * tL, "tflops": RL / tL * flopL / 1e12,
+            "note": "half-shell pair rectangles + bonded windows (fp32 forces) and all 8 energy terms in FP64 (two more kernels on a second stream)"}
+        tLf = timed(lambda: fL.compute_batch(sysL.pos, sysL.box, sysL.forces, energies=False), 3)
+        extra["large_solute_1040_atoms_forces_compute"]["force_only"] = {"value": RL / tLf, "ms_per_call": 1e3 * tLf,
+                                                                       "tflops": RL / tLf * flopL / 1e12}
         integL = Integrator(sysL, fL, timestep=1.0, device=dev, gamma=1.0, T=300.0, seed=44)
         integL.energy_every, integL.check_nan = 10, False
         tL2 = timed(lambda: integL.step(niter=20), 2)
         extra["large_solute_1040_atoms_langevin"] = {"value": RL * 20 / tL2, "unit": "replica-steps/s", "replicas": RL,
-                                                    "natoms": NL, "md_steps_per_call": 20,
+                                                    "natoms": NL, "md_steps_per_call": 20, "energy_every": 10,
                                                     "tflops": RL * 20 / tL2 * (flopL + 60 * NL) / 1e12}
+        integL.energy_every = 100
+        tL3 = timed(lambda: integL.step(niter=100), 2)
+        extra["large_solute_1040_atoms_langevin"]["energy_every_100"] = {"value": RL * 100 / tL3, "md_steps_per_call": 100,
+                                                                        "us_per_step": 1e6 * tL3 / 100}
+        # the same bundle with the 9 A cutoff / reaction field / 7.5 A switch (the mode the tile-box skips exist for)
+        fLc = Forces(parL, cutoff=9.0, rfa=True, switch_dist=7.5)
+        fLc.check_nan = False
+        integLc = Integrator(sysL, fLc, timestep=1.0, device=dev, gamma=1.0, T=300.0, seed=45)
+        integLc.energy_every, integLc.check_nan = 100, False
+        integLc.step(niter=20)
+        tL4 = timed(lambda: integLc.step(niter=100), 2)
+        extra["large_solute_1040_atoms_langevin_cutoff9_rfa_switch7.5"] = {
+            "value": RL * 100 / tL4, "unit": "replica-steps/s", "replicas": RL, "natoms": NL, "md_steps_per_call": 100,
+            "energy_every": 100, "us_per_step": 1e6 * tL4 / 100}
         del sysL, posL
 
     if rank == 0:

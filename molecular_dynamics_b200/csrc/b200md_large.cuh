@@ -2,31 +2,40 @@
 // V_Calculations/Test-10_diALA/potcalc.py:114).  Same reference semantics as the one-CTA-per-replica kernels
 // (TorchMD_Fix/forces.py Forces.compute :82-344, upstream Integrator.step), but a replica no longer fits on chip:
 //
-//   large_bonded_kernel  one thread per bonded item (bonds, angles, proper torsions with all their terms, 1-4 pairs,
-//                        impropers, the SMD restraint) in FP64; force vectors go to a per-atom 2^-30 fixed-point
-//                        int64 accumulator in HBM by integer atomics (associative: the sum does not depend on the
-//                        order the atomics land in, so results stay bit-reproducible);
-//   large_pairs_kernel   all-pairs LJ + Coulomb, FULL shell: CTA = one 32-atom i-block of one replica, lane = i atom,
-//                        the 4 warps split the j tiles of 32 atoms (staged per warp in shared memory, read as
-//                        broadcasts), exclusions are one 32-bit mask word per (i atom, j tile); no j-side force, no
-//                        atomics; the warps' partial sums meet in shared memory in a fixed order and the force row is
-//                        written once, coalesced (with the bonded accumulator added when the bonded kernel ran before it
-//                        on the same stream; by default that kernel runs beside this one on a second stream and
-//                        large_combine_kernel adds the accumulator afterwards: same expression, same bits);
-//   large_bbox_kernel    cutoff mode: bounding box of every 32-atom tile, so a warp can drop j tiles beyond the cutoff;
-//   large_finish_kernel  per-replica energies = fixed-order sum of the per-CTA FP64 partials;
-//   large_vv1 / large_vv2 / large_observe   the velocity-Verlet halves, the Langevin kick (same Philox stream as the
-//                        fused kernel: keyed by seed, global replica, atom, global step) and the observable record.
-// Pair FORCES are the packed pair_eval2<MODE> of b200md_forces.cuh (two j atoms per FFMA2 issue slot, FP32).  Pair
-// ENERGIES (ENERGY instantiation) are evaluated in FP64 from the fp32 positions, half shell (tiles above the diagonal
-// and j > i inside the diagonal tile): the lj / electrostatics sums cancel too far for fp32 pair terms to meet the
-// 1e-6-per-term contract.
+//   large_pairs_kernel          LJ + Coulomb forces, HALF shell: CTA = one rectangle (BI >= BJ) of two blocks of <= 288
+//                               atoms of one replica, both staged in shared memory; a warp holds a chunk of 8 j atoms as
+//                               broadcast operands and meets it with 32-atom i tiles (lane = i atom) in packed FP32
+//                               (pair_eval2 of b200md_forces.cuh); i-side force -> the warp's shared-memory row, j-side
+//                               force -> 24 registers over the passes, transposed once per chunk by a shuffle butterfly.
+//                               Cutoff mode: tile bounding boxes give each chunk its pass list by one ballot, a listed
+//                               pass still drops out on a warp vote (bit-identical with and without the skips);
+//   large_bonded_forces_kernel  bonds, angles, torsions with all their terms, 1-4 pairs, impropers, the SMD restraint in
+//                               fp32: CTA = one window of 64 atoms, every item that touches the window is evaluated into
+//                               private shared-memory slots (no atomics), thread a sums atom a's slots in a fixed order;
+//   -> both write PARTIAL force rows fpart[replica][slot][atom][3] (pairs: slot = the partner block, bonded: the last
+//      slot; every slot of every atom is written exactly once per call), so the two launches are independent and run
+//      beside each other on two streams; the force row is the fixed-order sum of the slots, taken by the consumer:
+//   large_sum_kernel            Forces.compute;
+//   large_vv2_kernel            the integrator: Langevin kick + second half-kick of step s, first half-kick + drift of step
+//                               s + 1 and the tile bounding boxes of the moved atoms in ONE launch between two force
+//                               evaluations (large_vv1_kernel only opens a call and follows snapshot steps);
+//   large_bonded_energy_kernel, large_pair_energy_kernel   report steps / Forces.compute with energies: every term in FP64
+//                               from the fp32 positions, item- / tile-centric, no forces; they only read the positions
+//                               and run on the second stream; large_finish_kernel sums the per-CTA partials in index order;
+//   large_bbox_kernel, large_observe_kernel   tile boxes of a Forces.compute call; the observable record.
+// The Langevin noise is the same Philox stream as the fused kernel (keyed by seed, global replica, atom, global step).
+// Energies are FP64 because the lj / electrostatics sums cancel too far for fp32 pair terms to meet the 1e-6-per-term
+// contract; forces are fp32 like the on-chip kernels.  Results are bit-reproducible and do not depend on
+// the replica count of a call or on how often energies are recorded (every summation order is fixed by the topology).
+// Round 1 for comparison: full-shell 32 x 32 tiles (every pair evaluated from both atoms), one FP64 thread per bonded item
+// with int64 global atomics, 4-6 launches per step: 397 / 246 us per Langevin step of 256 x 1 040 atoms (plain / cutoff
+// 9 A); now 270 / 128 us (profiles/r02_large_solute.md).
 #pragma once
 #include "b200md_forces.cuh"
 
 namespace b200md {
 
-constexpr int kLThreads = 128;  // pair kernel: 4 warps on one i-block
+constexpr int kLThreads = 128;  // pair kernels: 4 warps per CTA
 constexpr int kLBondedThreads = 128;
 constexpr double kLElec = 332.06371307417066;
 
@@ -618,7 +627,7 @@ inline int large_pairs_dyn_bytes(const LargeTopo& T) { return large_tab_bytes(T)
 inline int large_bonded_dyn_bytes(const LargeTopo& T) { return (int)sizeof(float) * (4 * T.win_slots_max + 3 * T.halo_max); }
 
 template <int MODE>
-__global__ void __launch_bounds__(kLThreads, 5)
+__global__ void __launch_bounds__(kLThreads, 5)  // (4 and 6 CTAs per SM measured within 2 % of 5)
 large_pairs_kernel(const LargeTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
                    const float* __restrict__ box, float* __restrict__ fpart, const float* __restrict__ bbox) {
   extern __shared__ __align__(16) char lsmem[];
