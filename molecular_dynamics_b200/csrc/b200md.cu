@@ -1316,7 +1316,8 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   if (nitems >= (1ll << 31)) { delete topo; fail(B200MD_ERR_UNSUPPORTED, "more than 2^31 bonded items"); return nullptr; }
   const int nwin = (N + kLWin - 1) / kLWin;
   std::vector<int> gstart(N + 1, 0), win_start(nwin + 1, 0);
-  std::vector<uint32_t> win_item;
+  std::vector<int4> win_atoms, win_kend(nwin, make_int4(0, 0, 0, 0));
+  std::vector<float4> win_prm;
   std::vector<ushort4> win_slot;
   int win_slots_max = 1, halo_max = 0;
   std::vector<int> win_lo(nwin, 0), win_n(nwin, 0);
@@ -1361,13 +1362,41 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
       }
     for (int w = 0; w < nwin; ++w) {
       win_start[w + 1] = win_start[w] + (int)per[w].size();
-      for (const auto& e : per[w]) { win_item.push_back(e.first); win_slot.push_back(e.second); }
+      int kend[4] = {win_start[w + 1], win_start[w + 1], win_start[w + 1], win_start[w + 1]};  // first entry of kinds 1 .. 4 (entries are in kind order)
+      for (const auto& e : per[w]) {
+        const int gi = (int)e.first, at = (int)win_slot.size();
+        const int e1 = d->nbonds, e2 = e1 + d->nangles, e3 = e2 + d->ndihedrals, e4 = e3 + d->n14;
+        const int kind = (gi >= e1) + (gi >= e2) + (gi >= e3) + (gi >= e4);
+        for (int q = kind; q >= 1; --q) kend[q - 1] = std::min(kend[q - 1], at);
+        int4 qa = make_int4(0, 0, 0, 0);
+        float4 pr = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (kind == 0) {
+          qa.x = bidx[gi].x; qa.y = bidx[gi].y; pr.x = bprm[gi].x; pr.y = bprm[gi].y;
+        } else if (kind == 1) {
+          const int a = gi - e1;
+          qa.x = aidx[3 * a]; qa.y = aidx[3 * a + 1]; qa.z = aidx[3 * a + 2]; pr.x = aprm[a].x; pr.y = aprm[a].y;
+        } else if (kind == 2) {
+          const int k = gi - e2;
+          qa = dq[k];
+          memcpy(&pr.x, &ds[k], 4); memcpy(&pr.y, &ds[k + 1], 4);
+        } else if (kind == 3) {
+          const int k = gi - e3;
+          qa.x = i14[k].x; qa.y = i14[k].y;
+          pr.x = p14[k].x / p14[k].z; pr.y = p14[k].y / p14[k].z; pr.z = charge[qa.x] * charge[qa.y] / p14[k].w;
+        } else {
+          const int k = gi - e4;
+          qa = iq[k];
+          memcpy(&pr.x, &is[k], 4); memcpy(&pr.y, &is[k + 1], 4);
+        }
+        win_atoms.push_back(qa); win_prm.push_back(pr); win_slot.push_back(e.second);
+      }
+      win_kend[w] = make_int4(kend[0], kend[1], kend[2], kend[3]);
       if (hi[w] >= lo[w] && hi[w] - lo[w] + 1 <= kLHalo) { win_lo[w] = lo[w]; win_n[w] = hi[w] - lo[w] + 1; halo_max = std::max(halo_max, win_n[w]); }
     }
-    if (win_item.empty()) { win_item.push_back(0); win_slot.push_back(make_ushort4(0xffff, 0xffff, 0xffff, 0xffff)); }
+    if (win_slot.empty()) { win_atoms.push_back(make_int4(0, 0, 0, 0)); win_prm.push_back(make_float4(0.f, 0.f, 0.f, 0.f)); win_slot.push_back(make_ushort4(0xffff, 0xffff, 0xffff, 0xffff)); }
   }
   BlobBuilder B;
-  const size_t o_wst = B.add(win_start), o_wit = B.add(win_item), o_wsl = B.add(win_slot), o_gst = B.add(gstart), o_wlo = B.add(win_lo), o_wn = B.add(win_n);
+  const size_t o_wst = B.add(win_start), o_wat = B.add(win_atoms), o_wpr = B.add(win_prm), o_wke = B.add(win_kend), o_wsl = B.add(win_slot), o_gst = B.add(gstart), o_wlo = B.add(win_lo), o_wn = B.add(win_n);
   const size_t o_type = B.add(atype), o_q = B.add(charge), o_m = B.add(mass), o_a = B.add(t12a), o_b = B.add(t6b), o_mask = B.add(mask),
                o_bi = B.add(bidx), o_bp = B.add(bprm), o_ai = B.add(aidx), o_ap = B.add(aprm), o_dq = B.add(dq), o_ds = B.add(ds),
                o_dt = B.add(dt), o_i14 = B.add(i14), o_p14 = B.add(p14), o_iq = B.add(iq), o_is = B.add(is), o_it = B.add(it), o_dcs = B.add(dcs), o_ics = B.add(ics), o_t64 = B.add(tab64);
@@ -1386,7 +1415,7 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   L.atom_type = (const int*)(base + o_type); L.charge = (const float*)(base + o_q); L.mass = (const float*)(base + o_m);
   L.tab12a = (const float*)(base + o_a); L.tab6b = (const float*)(base + o_b); L.mask = (const uint32_t*)(base + o_mask);
   L.tab64 = (const double2*)(base + o_t64);
-  L.win_start = (const int*)(base + o_wst); L.win_item = (const uint32_t*)(base + o_wit); L.win_slot = (const ushort4*)(base + o_wsl);
+  L.win_start = (const int*)(base + o_wst); L.win_atoms = (const int4*)(base + o_wat); L.win_prm = (const float4*)(base + o_wpr); L.win_kend = (const int4*)(base + o_wke); L.win_slot = (const ushort4*)(base + o_wsl);
   L.gstart = (const int*)(base + o_gst); L.nwin = nwin; L.win_slots_max = win_slots_max; L.halo_max = halo_max;
   L.win_lo = (const int*)(base + o_wlo); L.win_n = (const int*)(base + o_wn);
   L.nblk = (W + kLBT - 1) / kLBT;  // pair rectangles over nblk blocks of bt <= kLBT tiles, as even as the tile count allows

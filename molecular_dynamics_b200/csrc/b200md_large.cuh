@@ -61,7 +61,9 @@ struct LargeTopo {
   // contribution (0xffff: the atom belongs to another window).  Slots are atom-major: atom a of the window owns
   // [gstart[a], gstart[a + 1]) - gstart[first atom of the window], in the fixed order bonds, angles, dihedrals, 1-4, impropers.
   const int* win_start;      // [nwin + 1]
-  const uint32_t* win_item;  // [entries]
+  const int4* win_kend;      // [nwin] first entry of the window's angles, dihedrals, 1-4 pairs, impropers (entries are kind-sorted)
+  const int4* win_atoms;     // [entries] atom indices of the item
+  const float4* win_prm;     // [entries] bond / angle: (k, x0); torsions: (first term, end term) as int bits; 1-4: (A / scnb, B / scnb, q_i q_j / scee, -)
   const ushort4* win_slot;   // [entries]
   const int* gstart;         // [natoms + 1]
   const int* win_lo;         // [nwin] first atom the window's items reference
@@ -81,6 +83,20 @@ template <typename T> __device__ __forceinline__ v3t<T> vcross(v3t<T> a, v3t<T> 
 template <typename T> __device__ __forceinline__ T vdot(v3t<T> a, v3t<T> b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 template <typename T> __device__ __forceinline__ v3t<T> vscale(v3t<T> a, T s) { return {a.x * s, a.y * s, a.z * s}; }
 template <typename T> __device__ __forceinline__ v3t<T> vpos(const float* p, int i) { return {(T)p[3 * i], (T)p[3 * i + 1], (T)p[3 * i + 2]}; }
+// Where an item reads its atoms: the replica's rows in HBM, or (bonded force windows) 16-byte rows staged in shared memory,
+// addressed as shared so that one LDS.128 delivers an atom (a generic pointer that is sometimes shared costs an LD each).
+struct GlobalPos {
+  const float* p;
+  template <typename T> __device__ __forceinline__ v3t<T> get(int i) const { return {(T)p[3 * i], (T)p[3 * i + 1], (T)p[3 * i + 2]}; }
+};
+struct SharedPos {
+  uint32_t base;  // shared byte address of atom 0's row (the staged span starts at atom lo: base = rows - 16 lo)
+  template <typename T> __device__ __forceinline__ v3t<T> get(int i) const {
+    float x, y, z, w;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x), "=f"(y), "=f"(z), "=f"(w) : "r"(base + 16u * (uint32_t)i));
+    return {(T)x, (T)y, (T)z};
+  }
+};
 __device__ __forceinline__ float trint(float x) { return rintf(x); }
 __device__ __forceinline__ double trint(double x) { return rint(x); }
 // 1 / x, 1 / sqrt(x): double for the energy path, the hardware approximations with one Newton step where the
@@ -117,13 +133,13 @@ template <typename T> __device__ __forceinline__ void lput(NoSink&, int, v3t<T>,
 // evaluate_torsion (forces.py:540-602) for one quadruple with its terms; returns the energy, adds the forces when FORCE.
 // Terms of the AMBER branch with an integer periodicity 1..6 (marker 2) never form phi: cos / sin(n phi) come from
 // (cos phi + i sin phi)^n and cos / sin(phi0) from the host (FP64).  Other terms use phi = -atan2(sin, cos) as written.
-template <typename T, bool FORCE, typename SINK>
-__device__ __forceinline__ T ltorsion(const float* p, const T* bx, bool vac, int4 q, const float4* term,
+template <typename T, bool FORCE, typename SINK, typename POS>
+__device__ __forceinline__ T ltorsion(const POS& p, const T* bx, bool vac, int4 q, const float4* term,
                                       const double2* term_cs, int t0, int t1, SINK& f) {
   typedef v3t<T> V;
-  const V r12 = vwrap(vsub(vpos<T>(p, q.x), vpos<T>(p, q.y)), bx, vac);
-  const V r23 = vwrap(vsub(vpos<T>(p, q.y), vpos<T>(p, q.z)), bx, vac);
-  const V r34 = vwrap(vsub(vpos<T>(p, q.z), vpos<T>(p, q.w)), bx, vac);
+  const V r12 = vwrap(vsub(p.template get<T>(q.x), p.template get<T>(q.y)), bx, vac);
+  const V r23 = vwrap(vsub(p.template get<T>(q.y), p.template get<T>(q.z)), bx, vac);
+  const V r34 = vwrap(vsub(p.template get<T>(q.z), p.template get<T>(q.w)), bx, vac);
   const V cA = vcross(r12, r23), cB = vcross(r23, r34), cC = vcross(r23, cA);
   const T inA = trsqrt(vdot(cA, cA)), inB = trsqrt(vdot(cB, cB)), inC = trsqrt(vdot(cC, cC));
   const V ncB = vscale(cB, inB);
@@ -188,63 +204,57 @@ __device__ __forceinline__ LItemRanges litem_ranges(const LargeTopo& T, uint32_t
   return G;
 }
 __device__ __forceinline__ int litem_kind(const LItemRanges& G, int g) { return (g >= G.e1) + (g >= G.e2) + (g >= G.e3) + (g >= G.e4); }
-template <typename T, bool FORCE, typename SINK>
-__device__ __forceinline__ void litem(const LargeTopo& T_, const ForceParams& P, const LItemRanges& G, int g, const float* p,
-                                      const T* bx, bool vac, SINK& f, T* e /* [8] */) {
+// The arithmetic of one item of kind `kind` on atoms q with parameters prm (bond / angle: (k, x0); 1-4: (A, B, scnb, scee)
+// and qq14 = q_i q_j; torsions: terms [t0, t1) of the kind's term list).
+template <typename T, bool FORCE, typename SINK, typename POS>
+__device__ __forceinline__ void litem_eval(const LargeTopo& T_, const ForceParams& P, const LItemRanges& G, const int kind,
+                                           const int4 q, const float4 prm, const T qq14, const int t0, const int t1,
+                                           const POS& p, const T* bx, bool vac, SINK& f, T* e /* [8] */) {
   typedef v3t<T> V;
-  if (g < G.e1) {  // forces.py:111-132, 492-501
-    const int2 ij = __ldg(T_.bond_idx + g);
-    const float2 kp = __ldg(T_.bond_prm + g);
-    const V d = vwrap(vsub(vpos<T>(p, ij.x), vpos<T>(p, ij.y)), bx, vac);
+  if (kind == 0) {  // forces.py:111-132, 492-501
+    const V d = vwrap(vsub(p.template get<T>(q.x), p.template get<T>(q.y)), bx, vac);
     const T r2b = vdot(d, d), idist = trsqrt(r2b), dist = r2b * idist;
     if (P.has_cutoff && !(dist <= (T)P.rc)) {  // forces.py:117-125: dropped (its slots must still read as zero)
       if (FORCE) { const V zero = {(T)0, (T)0, (T)0}; lput<T>(f, 0, zero, (T)0); lput<T>(f, 1, zero, (T)0); }
       return;
     }
-    const T x = dist - (T)kp.y;
-    e[B200MD_E_BONDS] += (T)kp.x * x * x;
+    const T x = dist - (T)prm.y;
+    e[B200MD_E_BONDS] += (T)prm.x * x * x;
     if (FORCE) {
-      const T c = (T)2 * (T)kp.x * x * idist;
+      const T c = (T)2 * (T)prm.x * x * idist;
       lput<T>(f, 0, d, -c);
       lput<T>(f, 1, d, c);
     }
-  } else if (g < G.e2) {  // forces.py:134-145, 504-537
-    const int a = g - G.e1;
-    const int q0 = __ldg(T_.angle_idx + 3 * a), q1 = __ldg(T_.angle_idx + 3 * a + 1), q2 = __ldg(T_.angle_idx + 3 * a + 2);
-    const float2 kp = __ldg(T_.angle_prm + a);
-    const V r21 = vwrap(vsub(vpos<T>(p, q0), vpos<T>(p, q1)), bx, vac);
-    const V r23 = vwrap(vsub(vpos<T>(p, q2), vpos<T>(p, q1)), bx, vac);
+  } else if (kind == 1) {  // forces.py:134-145, 504-537
+    const V r21 = vwrap(vsub(p.template get<T>(q.x), p.template get<T>(q.y)), bx, vac);
+    const V r23 = vwrap(vsub(p.template get<T>(q.z), p.template get<T>(q.y)), bx, vac);
     const T n23i = trsqrt(vdot(r23, r23)), n21i = trsqrt(vdot(r21, r21));
     T ct = vdot(r23, r21) * n21i * n23i;
     ct = ct < (T)-1 ? (T)-1 : (ct > (T)1 ? (T)1 : ct);
-    const T dth = acos(ct) - (T)kp.y;
-    e[B200MD_E_ANGLES] += (T)kp.x * dth * dth;
+    const T dth = acos(ct) - (T)prm.y;
+    e[B200MD_E_ANGLES] += (T)prm.x * dth * dth;
     if (FORCE) {
       const T st2 = (T)1 - ct * ct;
-      const T coef = st2 > (T)0 ? (T)-2 * (T)kp.x * dth * trsqrt(st2) : (T)0;  // 0 where sin(theta) == 0 (forces.py:521-523)
+      const T coef = st2 > (T)0 ? (T)-2 * (T)prm.x * dth * trsqrt(st2) : (T)0;  // 0 where sin(theta) == 0 (forces.py:521-523)
       const V f0 = vscale(vsub(vscale(r21, ct * n21i), vscale(r23, n23i)), coef * n21i);
       const V f2 = vscale(vsub(vscale(r23, ct * n23i), vscale(r21, n21i)), coef * n23i);
       lput<T>(f, 0, f0, (T)1);
       lput<T>(f, 2, f2, (T)1);
       lput<T>(f, 1, {f0.x + f2.x, f0.y + f2.y, f0.z + f2.z}, (T)-1);
     }
-  } else if (g < G.e3) {  // forces.py:147-174
-    const int d = g - G.e2;
-    e[B200MD_E_DIHEDRALS] += ltorsion<T, FORCE, SINK>(p, bx, vac, __ldg(T_.dih_idx + d), T_.dih_term, T_.dih_cs, __ldg(T_.dih_start + d), __ldg(T_.dih_start + d + 1), f);
-  } else if (g < G.e4) {  // forces.py:176-226: never cut, switched or reaction-field corrected
-    const int k = g - G.e3;
-    const int2 ij = __ldg(T_.idx14 + k);
-    const float4 q = __ldg(T_.prm14 + k);
-    const V d = vwrap(vsub(vpos<T>(p, ij.x), vpos<T>(p, ij.y)), bx, vac);
+  } else if (kind == 2) {  // forces.py:147-174
+    e[B200MD_E_DIHEDRALS] += ltorsion<T, FORCE, SINK, POS>(p, bx, vac, q, T_.dih_term, T_.dih_cs, t0, t1, f);
+  } else if (kind == 3) {  // forces.py:176-226: never cut, switched or reaction-field corrected
+    const V d = vwrap(vsub(p.template get<T>(q.x), p.template get<T>(q.y)), bx, vac);
     const T r2 = vdot(d, d), rinv1 = trsqrt(r2), rinv2 = rinv1 * rinv1, rinv6 = rinv2 * rinv2 * rinv2;
     T c = 0;  // -(dE/dr) / r
     if (G.lj14) {
-      const T iscnb = trcp((T)q.z);
-      e[B200MD_E_LJ] += ((T)q.x * rinv6 * rinv6 - (T)q.y * rinv6) * iscnb;
-      c += ((T)12 * (T)q.x * rinv6 * rinv6 - (T)6 * (T)q.y * rinv6) * rinv2 * iscnb;
+      const T iscnb = trcp((T)prm.z);
+      e[B200MD_E_LJ] += ((T)prm.x * rinv6 * rinv6 - (T)prm.y * rinv6) * iscnb;
+      c += ((T)12 * (T)prm.x * rinv6 * rinv6 - (T)6 * (T)prm.y * rinv6) * rinv2 * iscnb;
     }
     if (G.el14) {
-      const T pot = (T)kLElec * (T)__ldg(T_.charge + ij.x) * (T)__ldg(T_.charge + ij.y) * rinv1 * trcp((T)q.w);
+      const T pot = (T)kLElec * qq14 * rinv1 * trcp((T)prm.w);
       e[B200MD_E_ELECTROSTATICS] += pot;
       c += pot * rinv2;
     }
@@ -253,9 +263,43 @@ __device__ __forceinline__ void litem(const LargeTopo& T_, const ForceParams& P,
       lput<T>(f, 1, d, -c);
     }
   } else {  // forces.py:228-255
-    const int d = g - G.e4;
-    e[B200MD_E_IMPROPERS] += ltorsion<T, FORCE, SINK>(p, bx, vac, __ldg(T_.imp_idx + d), T_.imp_term, T_.imp_cs, __ldg(T_.imp_start + d), __ldg(T_.imp_start + d + 1), f);
+    e[B200MD_E_IMPROPERS] += ltorsion<T, FORCE, SINK, POS>(p, bx, vac, q, T_.imp_term, T_.imp_cs, t0, t1, f);
   }
+}
+
+// Item g of the concatenated list [bonds | angles | dihedrals | 1-4 pairs | impropers]: its indices and parameters from the
+// per-kind arrays (the FP64 energy kernel; the force kernel reads the same data inline from its window lists).
+template <typename T, bool FORCE, typename SINK>
+__device__ __forceinline__ void litem(const LargeTopo& T_, const ForceParams& P, const LItemRanges& G, int g, const float* pg,
+                                      const T* bx, bool vac, SINK& f, T* e /* [8] */) {
+  const GlobalPos p = {pg};
+  int4 q = make_int4(0, 0, 0, 0);
+  float4 prm = make_float4(0.f, 0.f, 0.f, 0.f);
+  T qq14 = 0;
+  int t0 = 0, t1 = 0;
+  const int kind = litem_kind(G, g);
+  if (kind == 0) {
+    const int2 ij = __ldg(T_.bond_idx + g);
+    const float2 kp = __ldg(T_.bond_prm + g);
+    q.x = ij.x; q.y = ij.y; prm.x = kp.x; prm.y = kp.y;
+  } else if (kind == 1) {
+    const int a = g - G.e1;
+    q.x = __ldg(T_.angle_idx + 3 * a); q.y = __ldg(T_.angle_idx + 3 * a + 1); q.z = __ldg(T_.angle_idx + 3 * a + 2);
+    const float2 kp = __ldg(T_.angle_prm + a);
+    prm.x = kp.x; prm.y = kp.y;
+  } else if (kind == 2) {
+    const int d = g - G.e2;
+    q = __ldg(T_.dih_idx + d); t0 = __ldg(T_.dih_start + d); t1 = __ldg(T_.dih_start + d + 1);
+  } else if (kind == 3) {
+    const int k = g - G.e3;
+    const int2 ij = __ldg(T_.idx14 + k);
+    q.x = ij.x; q.y = ij.y; prm = __ldg(T_.prm14 + k);
+    qq14 = (T)__ldg(T_.charge + ij.x) * (T)__ldg(T_.charge + ij.y);
+  } else {
+    const int d = g - G.e4;
+    q = __ldg(T_.imp_idx + d); t0 = __ldg(T_.imp_start + d); t1 = __ldg(T_.imp_start + d + 1);
+  }
+  litem_eval<T, FORCE, SINK, GlobalPos>(T_, P, G, kind, q, prm, qq14, t0, t1, p, bx, vac, f, e);
 }
 
 // FP64 block reduction of `n` values per thread in a fixed order; result valid in thread 0
@@ -624,7 +668,7 @@ __device__ __forceinline__ float large_row_sum(const float* __restrict__ fpart, 
 }
 inline int large_tab_bytes(const LargeTopo& T) { return (2 * T.ntypes * large_tab_stride(T.ntypes) * (int)sizeof(float) + 15) & ~15; }
 inline int large_pairs_dyn_bytes(const LargeTopo& T) { return large_tab_bytes(T) + (int)sizeof(RectSmem); }
-inline int large_bonded_dyn_bytes(const LargeTopo& T) { return (int)sizeof(float) * (4 * T.win_slots_max + 3 * T.halo_max); }
+inline int large_bonded_dyn_bytes(const LargeTopo& T) { return (int)sizeof(float4) * (T.win_slots_max + T.halo_max); }
 
 template <int MODE>
 __global__ void __launch_bounds__(kLThreads, 5)  // (4 and 6 CTAs per SM measured within 2 % of 5)
@@ -670,10 +714,11 @@ large_bonded_forces_kernel(const LargeTopo T, const ForceParams P, const long lo
   const int tid = threadIdx.x;
   const int N = T.natoms, nslot = T.nblk + 1;
   float4* lslots = (float4*)lsmem;
-  float* shalo = (float*)(lslots + T.win_slots_max);
+  float4* shalo = lslots + T.win_slots_max;
   const int w = (int)blockIdx.x;
   const LItemRanges G = litem_ranges(T, P.terms);
   const int k0 = __ldg(T.win_start + w), k1 = __ldg(T.win_start + w + 1);
+  const int4 ke = __ldg(T.win_kend + w);  // first entry of the angles, dihedrals, 1-4 pairs, impropers of the window
   const int hlo = __ldg(T.win_lo + w), hn = __ldg(T.win_n + w);
   const int a = kLWin * w + tid;  // the atom this thread gathers (tid < kLWin)
   const bool mine = tid < kLWin && a < N;
@@ -684,26 +729,36 @@ large_bonded_forces_kernel(const LargeTopo T, const ForceParams P, const long lo
     const float b0 = box ? __ldg(box + r * 9) : 0.0f, b1 = box ? __ldg(box + r * 9 + 4) : 0.0f, b2 = box ? __ldg(box + r * 9 + 8) : 0.0f;
     const bool pbc = b0 != 0.0f || b1 != 0.0f || b2 != 0.0f;
     __syncthreads();  // the slots and staged positions of the previous replica are no longer read
-    for (int k = tid; k < 3 * hn; k += kLThreads) shalo[k] = __ldg(p + 3 * hlo + k);
+    for (int k = tid; k < hn; k += kLThreads) shalo[k] = make_float4(__ldg(p + 3 * (hlo + k)), __ldg(p + 3 * (hlo + k) + 1), __ldg(p + 3 * (hlo + k) + 2), 0.0f);
     __syncthreads();
-    {
-      const float* pe = hn > 0 ? shalo - 3 * hlo : p;
-      const float bxf[3] = {b0, b1, b2};
+    const float bxf[3] = {b0, b1, b2};
+    auto items = [&](const auto& pe) {
       WindowSink sink;
       sink.slots = lslots;
       float ef[B200MD_NUM_ENERGIES] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};  // by-product of the float path, not read
       for (int k = k0 + tid; k < k1; k += kLThreads) {
-        const int g = (int)__ldg(T.win_item + k);
+        // everything the item needs arrives in three coalesced loads of the window's own lists (round 2 first read the item
+        // number, then gathered its indices and its parameters from the per-kind arrays: three dependent loads deep)
+        const int4 q = __ldg(T.win_atoms + k);
+        const float4 prm = __ldg(T.win_prm + k);
         sink.sl = __ldg(T.win_slot + k);
-        if (((G.on >> litem_kind(G, g)) & 1u)) {
-          litem<float, true, WindowSink>(T, P, G, g, pe, bxf, !pbc, sink, ef);
+        const int kind = (k >= ke.x) + (k >= ke.y) + (k >= ke.z) + (k >= ke.w);
+        if (((G.on >> kind) & 1u)) {
+          float4 pk4 = prm;
+          float qq = 0.0f;
+          int t0 = 0, t1 = 0;
+          if (kind == 3) { qq = prm.z; pk4.z = 1.0f; pk4.w = 1.0f; }  // scnb, scee are folded into A, B, q_i q_j on the host
+          else if (kind == 2 || kind == 4) { t0 = __float_as_int(prm.x); t1 = __float_as_int(prm.y); }
+          litem_eval<float, true, WindowSink>(T, P, G, kind, q, pk4, qq, t0, t1, pe, bxf, !pbc, sink, ef);
         } else {  // a kind the call has switched off: its slots read as zero
           const v3t<float> zero = {0.0f, 0.0f, 0.0f};
 #pragma unroll
           for (int c = 0; c < 4; ++c) lput<float>(sink, c, zero, 0.0f);
         }
       }
-    }
+    };
+    if (hn > 0) items(SharedPos{(uint32_t)__cvta_generic_to_shared(shalo) - 16u * (uint32_t)hlo});
+    else items(GlobalPos{p});  // the window's items span more than kLHalo atoms: from HBM
     __syncthreads();
     if (mine) {
       float bx = 0.0f, by = 0.0f, bz = 0.0f;
@@ -779,12 +834,10 @@ large_pair_energy_kernel(const LargeTopo T, const ForceParams P, const long long
       const int j = 32 * jt + lane;
       double* sd = sjd[warp];
       __syncwarp();
-      if (j < N) {
-        sd[lane] = (double)__ldg(p + 3 * j); sd[32 + lane] = (double)__ldg(p + 3 * j + 1); sd[64 + lane] = (double)__ldg(p + 3 * j + 2);
-        sd[96 + lane] = (double)(__ldg(T.charge + j) * P.el_on);
-      } else {
-        sd[lane] = 0.0; sd[32 + lane] = 0.0; sd[64 + lane] = 0.0; sd[96 + lane] = 0.0;
-      }
+      float jx = 0.f, jy = 0.f, jz = 0.f, jq = 0.f;
+      if (j < N) { jx = __ldg(p + 3 * j); jy = __ldg(p + 3 * j + 1); jz = __ldg(p + 3 * j + 2); jq = __ldg(T.charge + j) * P.el_on; }
+      sd[lane] = (double)jx; sd[32 + lane] = (double)jy; sd[64 + lane] = (double)jz; sd[96 + lane] = (double)jq;
+
       stj[warp][lane] = __ldg(T.atom_type + j);
       __syncwarp();
       const uint32_t m = __ldg(mrow + jt);
