@@ -590,12 +590,12 @@ struct b200md_topology {
   bool large = false;
   LargeTopo ldev{};
   int mask_words = 4;  // uint32 words per row of mask_rows
-  // grow-only device workspace of the large-solute calls (bonded-force accumulator, energy partials ...), reused from
+  // grow-only device workspace of the large-solute calls (partial force rows, energy partials, tile boxes ...), reused from
   // call to call: stream-ordered on `ws_stream`; a call on another stream first waits for that one
   mutable void* ws = nullptr;
   mutable size_t ws_bytes = 0;
   mutable cudaStream_t ws_stream = nullptr;
-  // second stream of the large-solute calls: the latency-bound FP64 bonded kernel runs beside the throughput-bound pair
+  // second stream of the large-solute calls: the latency-bound bonded kernel (and the FP64 energy kernels) run beside the throughput-bound pair
   // kernel (fork / join by events, so the caller's stream still orders the call as a whole)
   mutable cudaStream_t aux = nullptr;
   mutable cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_bonded = nullptr;
@@ -1441,8 +1441,8 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   return topo;
 }
 
-// Workspace of one large-solute call, carved from the topology's grow-only device buffer: the int64 bonded-force
-// accumulator, the per-CTA energy partials, the per-replica energies / kinetic-energy partials / SMD record of the integrator.
+// Workspace of one large-solute call, carved from the topology's grow-only device buffer: the partial force rows, the tile
+// boxes, the per-CTA energy partials, the per-replica energies / kinetic-energy partials / SMD record of the integrator.
 struct LargeWork {
   cudaStream_t st;
   double* partial = nullptr; double* energies = nullptr; double* ekin = nullptr; double* smd = nullptr;

@@ -771,7 +771,7 @@ class _RandomMolecule:
     to their 1-4 pair, random LJ tables.  The oracle restates forces.py for arbitrary parameter objects, so it is the
     reference here."""
 
-    def __init__(self, natoms, seed, R=3):
+    def __init__(self, natoms, seed, R=3, long_bonds=()):
         rng = np.random.default_rng(seed)
         N = natoms
         # start structure: a helix (no collinear triples, which make torsion gradients singular), jittered
@@ -791,10 +791,12 @@ class _RandomMolecule:
             j = int(min(N - 1, i + rng.integers(2, 6)))
             if (i, j) not in bonds:
                 bonds.append((i, j))
-        bonds = np.array(sorted(set(bonds)))
+        bonds = np.array(sorted(set(bonds) | set(long_bonds)))  # long_bonds: cross-links far along the chain (disulfide-like)
         dist0 = np.linalg.norm(base[bonds[:, 0]] - base[bonds[:, 1]], axis=1)
         arrs["bonds"] = bonds
         arrs["bond_params"] = np.stack([rng.uniform(100, 450, len(bonds)), dist0 + rng.uniform(-0.1, 0.1, len(bonds))], 1)
+        for lb in long_bonds:  # hundreds of A long on this helix: a soft spring, so that fp32 rounding of the length (3e-5 A)
+            arrs["bond_params"][(bonds == np.array(lb)).all(1), 0] = 2.0  # stays far below the force tolerance
         if N >= 3:
             ang = np.array([(i, i + 1, i + 2) for i in range(N - 2)])
             arrs["angles"] = ang
@@ -945,7 +947,7 @@ def test_chamber_energies_on_gpu_against_namd_at_the_restart_frame():
 
 
 # ---- solutes above 128 atoms: the large-solute kernels (csrc/b200md_large.cuh) --------------------------------------
-@pytest.mark.parametrize("natoms,seed", [(129, 30), (160, 31), (257, 32), (300, 33), (1000, 34)])
+@pytest.mark.parametrize("natoms,seed", [(129, 30), (160, 31), (257, 32), (300, 33), (700, 35), (1000, 34)])
 def test_large_solute_forces_vs_oracle(natoms, seed):
     """SURVEY 8f N4 (larger solutes, e.g. the adk system named at V_Calculations/Test-10_diALA/potcalc.py:114): above 128
     atoms the same Forces.compute runs as bonded-item + 32 x 32 pair-tile kernels; same tolerances as the on-chip path."""
@@ -967,6 +969,21 @@ def test_large_solute_forces_vs_oracle(natoms, seed):
     allowed = np.zeros((natoms, natoms), bool)
     allowed[g.ava_idx[:, 0], g.ava_idx[:, 1]] = allowed[g.ava_idx[:, 1], g.ava_idx[:, 0]] = True
     np.testing.assert_array_equal(~bits, allowed)
+
+
+def test_large_solute_cross_links_far_along_the_chain_vs_oracle():
+    """Bonded windows stage the positions their items reference in shared memory when those span at most 320 atoms; a
+    cross-link far along the chain (here atoms 5-650 and 100-400 of 700) widens the span of its windows beyond that, and they
+    read positions from HBM instead (GlobalPos in large_bonded_forces_kernel).  Same results either way; in cutoff mode the
+    cross-link bonds are longer than the cutoff and drop out (forces.py:117-125)."""
+    g = _RandomMolecule(700, 36, R=2, long_bonds=((5, 650), (100, 400)))
+    for mode in ("plain", "rf"):
+        f_ref, e_ref = oracle.forces(g.packed, g.pos, **MODES[mode])
+        f, e, _ = run_gpu(g, g.pos, **MODES[mode])
+        ferr = np.abs(f - f_ref).reshape(len(f), -1).max(1) / np.abs(f_ref).reshape(len(f), -1).max(1)
+        assert ferr.max() < 1e-5, (mode, ferr.max())
+        check_energies(e, e_ref, f"large solute with cross-links, {mode}")
+    assert np.abs(f_ref[:, 5]).max() > 0 and np.abs(f[:, 650] - f_ref[:, 650]).max() < 1e-5 * np.abs(f_ref).max()
 
 
 def test_large_solute_term_subsets_box_and_smd_vs_oracle():
@@ -1077,6 +1094,51 @@ def test_large_solute_bundle_of_ala10_chains_vs_oracle():
     F.compute_batch(torch.tensor(posb, device=DEV), s.box, s.forces)
     f_ref, _ = oracle.forces(packed, posb, box=box.reshape(R, 9), **MODES["rf"])
     assert np.abs(s.forces.cpu().numpy() - f_ref).max() / np.abs(f_ref).max() < 1e-5
+
+
+def test_large_solute_benchmark_bundle_far_apart_chains_vs_oracle():
+    """The topology bench.py and tools/profile_large.py time: 10 deca-alanine chains 40 A apart as one 1 040-atom topology
+    (33 tiles -> 4 atom blocks of 9, 9, 9, 6 tiles, 10 pair rectangles), here on a 4 x 3 grid around the origin (on the
+    bench's line the coordinates reach 390 A, where the fp32 state alone costs 1.5e-5 A per step).  In cutoff mode some
+    rectangles lie wholly beyond the cutoff and write zero rows without staging anything; tiles that straddle two chains
+    have 40 A boxes.  Forces, energies, and a few NVE steps of the integrator (fused half-kicks, partial rows summed in the
+    half-kick kernel) against the oracle."""
+    g = load_golden("ala10")
+    copies, R = 10, 2
+    parL = g.par.tiled(copies)
+    N = 104 * copies
+    k = np.repeat(np.arange(copies), 104)
+    shift = np.stack([40.0 * (k % 4) - 60.0, 40.0 * (k // 4) - 40.0, np.zeros(N)], 1)[None]
+    pos = g["base_frames"][:R * copies].reshape(R, N, 3) + shift
+    pos = (pos - pos.mean(1, keepdims=True) + shift.mean(1, keepdims=True)).astype(np.float32)
+    packed = _cabi.PackedTopology(parL, _cabi.make_pair_index(N, parL.get_exclusions()))
+    parG = Parameters.from_arrays(parL.to_arrays(), device=DEV)
+    for mode in ("plain", "rf"):
+        F = Forces(parG, **MODES[mode])
+        s = System(N, R, torch.float, DEV)
+        s.pos[:] = torch.tensor(pos, device=DEV)
+        e = F.compute_batch(s.pos, s.box, s.forces).cpu().numpy()
+        f_ref, e_ref = oracle.forces(packed, pos, **MODES[mode])
+        assert np.abs(s.forces.cpu().numpy() - f_ref).max() / np.abs(f_ref).max() < 1e-5, mode
+        np.testing.assert_allclose(e, e_ref, rtol=1e-9, atol=1e-9)
+        f_only = torch.zeros_like(s.forces)
+        F.compute_batch(s.pos, s.box, f_only, energies=False)
+        assert torch.equal(f_only, s.forces)  # forces do not depend on whether energies are recorded
+        # 12 NVE steps, energies every 5 (report steps run the FP64 kernels beside the force launches)
+        vel0 = (0.01 * np.random.default_rng(3).standard_normal(pos.shape)).astype(np.float32)
+        s.vel[:] = torch.tensor(vel0, device=DEV)
+        integ = Integrator(s, F, timestep=1.0, device=DEV)
+        integ.energy_every = 5
+        integ.step(niter=12)
+        o = oracle.integrate(packed, pos, vel0, f_ref, nsteps=12, dt=np.float32(integ.dt), energy_every=5, **MODES[mode])
+        # fp32 state at coordinates up to ~80 A (half an ulp = 4e-6 A per step, times bond constants of ~1e3 in the forces)
+        assert np.abs(s.pos.cpu().numpy() - o["pos"]).max() < 1e-4, mode
+        assert np.abs(s.vel.cpu().numpy() - o["vel"]).max() < 1e-3 * max(1.0, np.abs(o["vel"]).max()), mode
+        obs, ref = integ.observables.cpu().numpy(), o["observables"]
+        assert obs.shape[0] == 3  # steps 5, 10 and the last one
+        sc = np.abs(ref[:, :, :8]).sum(-1) + 1.0
+        assert (np.abs(obs[:, :, :8].sum(-1) - ref[:, :, :8].sum(-1)) <= 1e-5 * sc).all(), mode
+        np.testing.assert_allclose(obs[:, :, _cabi.OBS_EKIN], ref[:, :, _cabi.OBS_EKIN], rtol=1e-4)
 
 
 def test_large_solute_results_do_not_depend_on_the_batch():
