@@ -31,10 +31,16 @@
 // with int64 global atomics, 4-6 launches per step: 397 / 246 us per Langevin step of 256 x 1 040 atoms (plain / cutoff
 // 9 A); now 270 / 128 us (profiles/r02_large_solute.md).
 #pragma once
+#include <cooperative_groups.h>
+
 #include "b200md_forces.cuh"
 
 namespace b200md {
 
+// Loads of data another CTA may have written earlier in the SAME launch (positions, tile boxes, partial rows in the
+// persistent multi-step kernel): COH = true reads through L2 (ld.global.cg); the per-launch kernels keep the read-only path.
+template <bool COH> __device__ __forceinline__ float ldm(const float* a) { return COH ? __ldcg(a) : __ldg(a); }
+template <bool COH> __device__ __forceinline__ float4 ldm4(const float4* a) { return COH ? __ldcg(a) : __ldg(a); }
 constexpr int kLThreads = 128;  // pair kernels: 4 warps per CTA
 constexpr int kLBondedThreads = 128;
 constexpr double kLElec = 332.06371307417066;
@@ -427,7 +433,7 @@ struct RectSmem {
   float fj[3][kLB];
 };
 
-template <int MODE, bool PBC>
+template <int MODE, bool PBC, bool COH>
 __device__ __forceinline__ void large_rect(const LargeTopo& T, const ForceParams& P, const float* __restrict__ p,
                                            const float* __restrict__ bb, RectSmem& S, const uint32_t tab, const int BI,
                                            const int BJ, const float3 nbox, const float3 ibox, float* __restrict__ out_i,
@@ -442,7 +448,7 @@ __device__ __forceinline__ void large_rect(const LargeTopo& T, const ForceParams
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
     const int blk = lane < 16 ? BI : BJ, tl = lane & 15, tile = blk * bt + tl;
     if (tl < bt && tile < nw) {
-      const float4 a = __ldg((const float4*)(bb + 8 * tile)), b = __ldg((const float4*)(bb + 8 * tile + 4));
+      const float4 a = ldm4<COH>((const float4*)(bb + 8 * tile)), b = ldm4<COH>((const float4*)(bb + 8 * tile + 4));
       lo[0] = a.x; lo[1] = a.y; lo[2] = a.z; hi[0] = b.x; hi[1] = b.y; hi[2] = b.z;
     }
 #pragma unroll
@@ -471,13 +477,13 @@ __device__ __forceinline__ void large_rect(const LargeTopo& T, const ForceParams
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     int row = 0;
     if (ai < N) {
-      v = make_float4(__ldg(p + 3 * ai), __ldg(p + 3 * ai + 1), __ldg(p + 3 * ai + 2), __fmul_rn(__ldg(T.charge + ai) * P.el_on, kElecFactor));
+      v = make_float4(ldm<COH>(p + 3 * ai), ldm<COH>(p + 3 * ai + 1), ldm<COH>(p + 3 * ai + 2), __fmul_rn(__ldg(T.charge + ai) * P.el_on, kElecFactor));
       row = __ldg(T.atom_type + ai) * tstride * 8;
     }
     S.ipos[t] = v; S.irow[t] = row;
     float x = 0.f, y = 0.f, z = 0.f, q = 0.f;
     int col = 0;
-    if (aj < N) { x = __ldg(p + 3 * aj); y = __ldg(p + 3 * aj + 1); z = __ldg(p + 3 * aj + 2); q = __ldg(T.charge + aj) * P.el_on; col = __ldg(T.atom_type + aj) * 8; }
+    if (aj < N) { x = ldm<COH>(p + 3 * aj); y = ldm<COH>(p + 3 * aj + 1); z = ldm<COH>(p + 3 * aj + 2); q = __ldg(T.charge + aj) * P.el_on; col = __ldg(T.atom_type + aj) * 8; }
     S.jx[t] = x; S.jy[t] = y; S.jz[t] = z; S.jq[t] = q; S.jcol[t] = col;
   }
   for (int k = tid; k < (kLThreads / 32) * 3 * kLB; k += kLThreads) (&S.fi[0][0][0])[k] = 0.0f;
@@ -493,8 +499,8 @@ __device__ __forceinline__ void large_rect(const LargeTopo& T, const ForceParams
     bool need = lane < bt && BI * bt + lane < nw && (!diag || lane > jtl);
     if (boxtest && need) {
       const int it = BI * bt + lane;
-      const float4 ilo = __ldg((const float4*)(bb + 8 * it)), ihi = __ldg((const float4*)(bb + 8 * it + 4));
-      const float4 tlo = __ldg((const float4*)(bb + 8 * jt)), thi = __ldg((const float4*)(bb + 8 * jt + 4));
+      const float4 ilo = ldm4<COH>((const float4*)(bb + 8 * it)), ihi = ldm4<COH>((const float4*)(bb + 8 * it + 4));
+      const float4 tlo = ldm4<COH>((const float4*)(bb + 8 * jt)), thi = ldm4<COH>((const float4*)(bb + 8 * jt + 4));
       const float gx = fmaxf(fmaxf(__fsub_rn(tlo.x, ihi.x), __fsub_rn(ilo.x, thi.x)), 0.0f);
       const float gy = fmaxf(fmaxf(__fsub_rn(tlo.y, ihi.y), __fsub_rn(ilo.y, thi.y)), 0.0f);
       const float gz = fmaxf(fmaxf(__fsub_rn(tlo.z, ihi.z), __fsub_rn(ilo.z, thi.z)), 0.0f);
@@ -659,63 +665,72 @@ __device__ __forceinline__ void large_rect(const LargeTopo& T, const ForceParams
 // force row of an atom is the fixed-order sum of its nblk + 1 slots, taken by the consumer (large_sum_kernel, or the
 // integrator's half-kick kernel, which reads the rows anyway).
 // Shared memory (dynamic): type-pair tables + RectSmem  or  bonded slots [win_slots_max][3] + staged positions [halo_max][3].
-__device__ __forceinline__ float large_row_sum(const float* __restrict__ fpart, const long long r, const int nslot, const int slot0,
+template <bool COH>
+__device__ __forceinline__ float large_row_sum(const float* fpart, const long long r, const int nslot, const int slot0,
                                                const int N, const int a, const int c) {
   const float* q = fpart + ((size_t)r * nslot * N + a) * 3 + c;
-  float f = q[(size_t)(nslot - 1) * N * 3];  // bonded
-  for (int k = slot0; k < nslot - 1; ++k) f = __fadd_rn(f, q[(size_t)k * N * 3]);
+  float f = COH ? __ldcg(q + (size_t)(nslot - 1) * N * 3) : q[(size_t)(nslot - 1) * N * 3];  // bonded
+  for (int k = slot0; k < nslot - 1; ++k) f = __fadd_rn(f, COH ? __ldcg(q + (size_t)k * N * 3) : q[(size_t)k * N * 3]);
   return f;
 }
-inline int large_tab_bytes(const LargeTopo& T) { return (2 * T.ntypes * large_tab_stride(T.ntypes) * (int)sizeof(float) + 15) & ~15; }
+__host__ __device__ inline int large_tab_bytes(const LargeTopo& T) { return (2 * T.ntypes * large_tab_stride(T.ntypes) * (int)sizeof(float) + 15) & ~15; }
 inline int large_pairs_dyn_bytes(const LargeTopo& T) { return large_tab_bytes(T) + (int)sizeof(RectSmem); }
 inline int large_bonded_dyn_bytes(const LargeTopo& T) { return (int)sizeof(float4) * (T.win_slots_max + T.halo_max); }
+inline int large_steps_dyn_bytes(const LargeTopo& T) { return large_tab_bytes(T) + std::max((int)sizeof(RectSmem), large_bonded_dyn_bytes(T)); }
 
+// The type-pair tables of a CTA, staged once per launch: [ntypes][stride] entries (12 A tab_a, 6 B tab_b)
+__device__ __forceinline__ void large_stage_tables(const LargeTopo& T, const ForceParams& P, float* sAB, const int tid) {
+  const int tstride = large_tab_stride(T.ntypes);
+  for (int k = tid; k < T.ntypes * T.ntypes; k += kLThreads) {
+    const int t = k / T.ntypes, u = k - t * T.ntypes;
+    sAB[2 * (t * tstride + u)] = __ldg(T.tab12a + k) * P.tab_a;
+    sAB[2 * (t * tstride + u) + 1] = __ldg(T.tab6b + k) * P.tab_b;
+  }
+}
+
+// One pair rectangle (index x = BI (BI + 1) / 2 + BJ) of replica r.  lsmem: tables | RectSmem.
+template <int MODE, bool COH>
+__device__ __forceinline__ void large_pairs_unit(const LargeTopo& T, const ForceParams& P, const float* pos, const float* box,
+                                                 float* fpart, const float* bbox, const long long r, const int x, char* lsmem,
+                                                 const int tid) {
+  const int N = T.natoms, nslot = T.nblk + 1;
+  RectSmem& S = *(RectSmem*)(lsmem + large_tab_bytes(T));
+  const uint32_t tab = (uint32_t)__cvta_generic_to_shared(lsmem);
+  int BI = 0;
+  while ((BI + 1) * (BI + 2) / 2 <= x) ++BI;
+  const int BJ = x - BI * (BI + 1) / 2;
+  const float* p = pos + r * N * 3;
+  const float b0 = box ? __ldg(box + r * 9) : 0.0f, b1 = box ? __ldg(box + r * 9 + 4) : 0.0f, b2 = box ? __ldg(box + r * 9 + 8) : 0.0f;
+  const bool pbc = b0 != 0.0f || b1 != 0.0f || b2 != 0.0f;  // forces.py:359
+  const float3 nbox = make_float3(-b0, -b1, -b2);
+  const float3 ibox = make_float3(b0 != 0.0f ? 1.0f / b0 : 0.0f, b1 != 0.0f ? 1.0f / b1 : 0.0f, b2 != 0.0f ? 1.0f / b2 : 0.0f);
+  float* out_i = fpart + (((size_t)r * nslot + BJ) * N + 32 * T.bt * BI) * 3;
+  float* out_j = fpart + (((size_t)r * nslot + BI) * N + 32 * T.bt * BJ) * 3;
+  __syncthreads();  // the tables (first unit); the previous unit's rows have been read
+  if (pbc) large_rect<MODE, true, COH>(T, P, p, nullptr, S, tab, BI, BJ, nbox, ibox, out_i, out_j, tid);
+  else large_rect<MODE, false, COH>(T, P, p, bbox ? bbox + r * T.nwords * 8 : nullptr, S, tab, BI, BJ, nbox, ibox, out_i, out_j, tid);
+}
+
+// grid (nrect, min(R, 65535))
 template <int MODE>
 __global__ void __launch_bounds__(kLThreads, 5)  // (4 and 6 CTAs per SM measured within 2 % of 5)
 large_pairs_kernel(const LargeTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
                    const float* __restrict__ box, float* __restrict__ fpart, const float* __restrict__ bbox) {
   extern __shared__ __align__(16) char lsmem[];
-  const int tstride = large_tab_stride(T.ntypes);
-  const int tab_bytes = (2 * T.ntypes * tstride * (int)sizeof(float) + 15) & ~15;
-  const int tid = threadIdx.x;
-  const int N = T.natoms, nslot = T.nblk + 1;
-  {
-    float* sAB = (float*)lsmem;  // [ntypes][stride] entries (12 A tab_a, 6 B tab_b)
-    RectSmem& S = *(RectSmem*)(lsmem + tab_bytes);
-    for (int k = tid; k < T.ntypes * T.ntypes; k += kLThreads) {
-      const int t = k / T.ntypes, u = k - t * T.ntypes;
-      sAB[2 * (t * tstride + u)] = __ldg(T.tab12a + k) * P.tab_a;
-      sAB[2 * (t * tstride + u) + 1] = __ldg(T.tab6b + k) * P.tab_b;
-    }
-    int BI = 0;
-    while ((BI + 1) * (BI + 2) / 2 <= (int)blockIdx.x) ++BI;
-    const int BJ = (int)blockIdx.x - BI * (BI + 1) / 2;
-    const uint32_t tab = (uint32_t)__cvta_generic_to_shared(sAB);
-    for (long long r = blockIdx.y; r < R; r += gridDim.y) {
-      const float* p = pos + r * N * 3;
-      const float b0 = box ? __ldg(box + r * 9) : 0.0f, b1 = box ? __ldg(box + r * 9 + 4) : 0.0f, b2 = box ? __ldg(box + r * 9 + 8) : 0.0f;
-      const bool pbc = b0 != 0.0f || b1 != 0.0f || b2 != 0.0f;  // forces.py:359
-      const float3 nbox = make_float3(-b0, -b1, -b2);
-      const float3 ibox = make_float3(b0 != 0.0f ? 1.0f / b0 : 0.0f, b1 != 0.0f ? 1.0f / b1 : 0.0f, b2 != 0.0f ? 1.0f / b2 : 0.0f);
-      float* out_i = fpart + (((size_t)r * nslot + BJ) * N + 32 * T.bt * BI) * 3;
-      float* out_j = fpart + (((size_t)r * nslot + BI) * N + 32 * T.bt * BJ) * 3;
-      __syncthreads();  // the tables (first pass); the previous replica's rows have been read
-      if (pbc) large_rect<MODE, true>(T, P, p, nullptr, S, tab, BI, BJ, nbox, ibox, out_i, out_j, tid);
-      else large_rect<MODE, false>(T, P, p, bbox ? bbox + r * T.nwords * 8 : nullptr, S, tab, BI, BJ, nbox, ibox, out_i, out_j, tid);
-    }
-  }
+  large_stage_tables(T, P, (float*)lsmem, threadIdx.x);
+  for (long long r = blockIdx.y; r < R; r += gridDim.y)
+    large_pairs_unit<MODE, false>(T, P, pos, box, fpart, bbox, r, (int)blockIdx.x, lsmem, threadIdx.x);
 }
 
-__global__ void __launch_bounds__(kLBondedThreads, 8)
-large_bonded_forces_kernel(const LargeTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
-                           const float* __restrict__ box, float* __restrict__ fpart, uint32_t* __restrict__ status,
-                           const float* __restrict__ smd_centers, const double smd_center, double* __restrict__ smd_rec) {
-  extern __shared__ __align__(16) char lsmem[];
-  const int tid = threadIdx.x;
+// The bonded window w of replica r (+ the SMD restraint, the NaN flag of its atoms) -> the last slot of the partial rows.
+// wsmem: slots [win_slots_max] float4 | staged positions [halo_max] float4.
+template <bool COH>
+__device__ __forceinline__ void large_bonded_unit(const LargeTopo& T, const ForceParams& P, const float* pos, const float* box,
+                                                  float* fpart, uint32_t* status, const float* smd_centers, const double smd_center,
+                                                  double* smd_rec, const long long r, const int w, char* wsmem, const int tid) {
   const int N = T.natoms, nslot = T.nblk + 1;
-  float4* lslots = (float4*)lsmem;
+  float4* lslots = (float4*)wsmem;
   float4* shalo = lslots + T.win_slots_max;
-  const int w = (int)blockIdx.x;
   const LItemRanges G = litem_ranges(T, P.terms);
   const int k0 = __ldg(T.win_start + w), k1 = __ldg(T.win_start + w + 1);
   const int4 ke = __ldg(T.win_kend + w);  // first entry of the angles, dihedrals, 1-4 pairs, impropers of the window
@@ -724,63 +739,73 @@ large_bonded_forces_kernel(const LargeTopo T, const ForceParams P, const long lo
   const bool mine = tid < kLWin && a < N;
   const int g0 = __ldg(T.gstart + kLWin * w);
   const int s0 = mine ? __ldg(T.gstart + a) - g0 : 0, s1 = mine ? __ldg(T.gstart + a + 1) - g0 : 0;
-  for (long long r = blockIdx.y; r < R; r += gridDim.y) {
-    const float* p = pos + r * N * 3;
-    const float b0 = box ? __ldg(box + r * 9) : 0.0f, b1 = box ? __ldg(box + r * 9 + 4) : 0.0f, b2 = box ? __ldg(box + r * 9 + 8) : 0.0f;
-    const bool pbc = b0 != 0.0f || b1 != 0.0f || b2 != 0.0f;
-    __syncthreads();  // the slots and staged positions of the previous replica are no longer read
-    for (int k = tid; k < hn; k += kLThreads) shalo[k] = make_float4(__ldg(p + 3 * (hlo + k)), __ldg(p + 3 * (hlo + k) + 1), __ldg(p + 3 * (hlo + k) + 2), 0.0f);
-    __syncthreads();
-    const float bxf[3] = {b0, b1, b2};
-    auto items = [&](const auto& pe) {
-      WindowSink sink;
-      sink.slots = lslots;
-      float ef[B200MD_NUM_ENERGIES] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};  // by-product of the float path, not read
-      for (int k = k0 + tid; k < k1; k += kLThreads) {
-        // everything the item needs arrives in three coalesced loads of the window's own lists (round 2 first read the item
-        // number, then gathered its indices and its parameters from the per-kind arrays: three dependent loads deep)
-        const int4 q = __ldg(T.win_atoms + k);
-        const float4 prm = __ldg(T.win_prm + k);
-        sink.sl = __ldg(T.win_slot + k);
-        const int kind = (k >= ke.x) + (k >= ke.y) + (k >= ke.z) + (k >= ke.w);
-        if (((G.on >> kind) & 1u)) {
-          float4 pk4 = prm;
-          float qq = 0.0f;
-          int t0 = 0, t1 = 0;
-          if (kind == 3) { qq = prm.z; pk4.z = 1.0f; pk4.w = 1.0f; }  // scnb, scee are folded into A, B, q_i q_j on the host
-          else if (kind == 2 || kind == 4) { t0 = __float_as_int(prm.x); t1 = __float_as_int(prm.y); }
-          litem_eval<float, true, WindowSink>(T, P, G, kind, q, pk4, qq, t0, t1, pe, bxf, !pbc, sink, ef);
-        } else {  // a kind the call has switched off: its slots read as zero
-          const v3t<float> zero = {0.0f, 0.0f, 0.0f};
+  const float* p = pos + r * N * 3;
+  const float b0 = box ? __ldg(box + r * 9) : 0.0f, b1 = box ? __ldg(box + r * 9 + 4) : 0.0f, b2 = box ? __ldg(box + r * 9 + 8) : 0.0f;
+  const bool pbc = b0 != 0.0f || b1 != 0.0f || b2 != 0.0f;
+  __syncthreads();  // the slots and staged positions of the previous unit are no longer read
+  for (int k = tid; k < hn; k += kLThreads) shalo[k] = make_float4(ldm<COH>(p + 3 * (hlo + k)), ldm<COH>(p + 3 * (hlo + k) + 1), ldm<COH>(p + 3 * (hlo + k) + 2), 0.0f);
+  __syncthreads();
+  const float bxf[3] = {b0, b1, b2};
+  auto items = [&](const auto& pe) {
+    WindowSink sink;
+    sink.slots = lslots;
+    float ef[B200MD_NUM_ENERGIES] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};  // by-product of the float path, not read
+    for (int k = k0 + tid; k < k1; k += kLThreads) {
+      // everything the item needs arrives in three coalesced loads of the window's own lists (round 2 first read the item
+      // number, then gathered its indices and its parameters from the per-kind arrays: three dependent loads deep)
+      const int4 q = __ldg(T.win_atoms + k);
+      const float4 prm = __ldg(T.win_prm + k);
+      sink.sl = __ldg(T.win_slot + k);
+      const int kind = (k >= ke.x) + (k >= ke.y) + (k >= ke.z) + (k >= ke.w);
+      if (((G.on >> kind) & 1u)) {
+        float4 pk4 = prm;
+        float qq = 0.0f;
+        int t0 = 0, t1 = 0;
+        if (kind == 3) { qq = prm.z; pk4.z = 1.0f; pk4.w = 1.0f; }  // scnb, scee are folded into A, B, q_i q_j on the host
+        else if (kind == 2 || kind == 4) { t0 = __float_as_int(prm.x); t1 = __float_as_int(prm.y); }
+        litem_eval<float, true, WindowSink>(T, P, G, kind, q, pk4, qq, t0, t1, pe, bxf, !pbc, sink, ef);
+      } else {  // a kind the call has switched off: its slots read as zero
+        const v3t<float> zero = {0.0f, 0.0f, 0.0f};
 #pragma unroll
-          for (int c = 0; c < 4; ++c) lput<float>(sink, c, zero, 0.0f);
-        }
+        for (int c = 0; c < 4; ++c) lput<float>(sink, c, zero, 0.0f);
       }
-    };
-    if (hn > 0) items(SharedPos{(uint32_t)__cvta_generic_to_shared(shalo) - 16u * (uint32_t)hlo});
-    else items(GlobalPos{p});  // the window's items span more than kLHalo atoms: from HBM
-    __syncthreads();
-    if (mine) {
-      float bx = 0.0f, by = 0.0f, bz = 0.0f;
-      for (int sidx = s0; sidx < s1; ++sidx) { const float4 v = lslots[sidx]; bx += v.x; by += v.y; bz += v.z; }
-      const float x = __ldg(p + 3 * a), y = __ldg(p + 3 * a + 1), z = __ldg(p + 3 * a + 2);
-      if (status != nullptr && (x != x || y != y || z != z)) atomicOr(status + r, B200MD_FLAG_NAN_POS);
-      if (P.smd_on && (a == P.smd_a1 || a == P.smd_a2)) {  // potcalc.py:75-89, not wrapped; FP64: (c - d) cancels near the centre
-        const double center = smd_centers ? (double)__ldg(smd_centers + r) : smd_center;
-        const v3t<double> d = vsub(vpos<double>(p, P.smd_a2), vpos<double>(p, P.smd_a1));
-        const double dist = sqrt(vdot(d, d)), dev = center - dist;
-        const double c = (double)P.smd_fk * dev / dist;  // force on atom2 = +fk (c - d) unit(r2 - r1)
-        const float sg = a == P.smd_a2 ? 1.0f : -1.0f;
-        bx += sg * (float)(c * d.x); by += sg * (float)(c * d.y); bz += sg * (float)(c * d.z);
-        if (smd_rec && a == P.smd_a2) {  // [R][2]: end-to-end distance of this step, work since the first step of the call
-          smd_rec[2 * r] = dist;
-          smd_rec[2 * r + 1] += (double)P.smd_fk * dev * (double)P.smd_rate;
-        }
-      }
-      float* o = fpart + (((size_t)r * nslot + T.nblk) * N + a) * 3;
-      o[0] = bx; o[1] = by; o[2] = bz;
     }
+  };
+  if (hn > 0) items(SharedPos{(uint32_t)__cvta_generic_to_shared(shalo) - 16u * (uint32_t)hlo});
+  else items(GlobalPos{p});  // the window's items span more than kLHalo atoms: from HBM
+  __syncthreads();
+  if (mine) {
+    float bx = 0.0f, by = 0.0f, bz = 0.0f;
+    for (int sidx = s0; sidx < s1; ++sidx) { const float4 v = lslots[sidx]; bx += v.x; by += v.y; bz += v.z; }
+    const float x = ldm<COH>(p + 3 * a), y = ldm<COH>(p + 3 * a + 1), z = ldm<COH>(p + 3 * a + 2);
+    if (status != nullptr && (x != x || y != y || z != z)) atomicOr(status + r, B200MD_FLAG_NAN_POS);
+    if (P.smd_on && (a == P.smd_a1 || a == P.smd_a2)) {  // potcalc.py:75-89, not wrapped; FP64: (c - d) cancels near the centre
+      const double center = smd_centers ? (double)__ldg(smd_centers + r) : smd_center;
+      const v3t<double> p1 = {(double)ldm<COH>(p + 3 * P.smd_a1), (double)ldm<COH>(p + 3 * P.smd_a1 + 1), (double)ldm<COH>(p + 3 * P.smd_a1 + 2)};
+      const v3t<double> p2 = {(double)ldm<COH>(p + 3 * P.smd_a2), (double)ldm<COH>(p + 3 * P.smd_a2 + 1), (double)ldm<COH>(p + 3 * P.smd_a2 + 2)};
+      const v3t<double> d = vsub(p2, p1);
+      const double dist = sqrt(vdot(d, d)), dev = center - dist;
+      const double c = (double)P.smd_fk * dev / dist;  // force on atom2 = +fk (c - d) unit(r2 - r1)
+      const float sg = a == P.smd_a2 ? 1.0f : -1.0f;
+      bx += sg * (float)(c * d.x); by += sg * (float)(c * d.y); bz += sg * (float)(c * d.z);
+      if (smd_rec && a == P.smd_a2) {  // [R][2]: end-to-end distance of this step, work since the first step of the call
+        smd_rec[2 * r] = dist;
+        smd_rec[2 * r + 1] += (double)P.smd_fk * dev * (double)P.smd_rate;
+      }
+    }
+    float* o = fpart + (((size_t)r * nslot + T.nblk) * N + a) * 3;
+    o[0] = bx; o[1] = by; o[2] = bz;
   }
+}
+
+// grid (nwin, min(R, 65535))
+__global__ void __launch_bounds__(kLBondedThreads, 8)
+large_bonded_forces_kernel(const LargeTopo T, const ForceParams P, const long long R, const float* __restrict__ pos,
+                           const float* __restrict__ box, float* __restrict__ fpart, uint32_t* __restrict__ status,
+                           const float* __restrict__ smd_centers, const double smd_center, double* __restrict__ smd_rec) {
+  extern __shared__ __align__(16) char lsmem[];
+  for (long long r = blockIdx.y; r < R; r += gridDim.y)
+    large_bonded_unit<false>(T, P, pos, box, fpart, status, smd_centers, smd_center, smd_rec, r, (int)blockIdx.x, lsmem, threadIdx.x);
 }
 
 // forces[r][a][c] = bonded slot + pair slots slot0 .. nblk - 1 in index order (Forces.compute; the integrator's half-kick
@@ -791,7 +816,7 @@ __global__ void large_sum_kernel(const LargeTopo T, const long long R, const flo
   if (g >= R * T.natoms * 3) return;
   const long long r = g / (T.natoms * 3);
   const int k = (int)(g - r * T.natoms * 3), a = k / 3, c = k - 3 * a;
-  forces[g] = large_row_sum(fpart, r, T.nblk + 1, slot0, T.natoms, a, c);
+  forces[g] = large_row_sum<false>(fpart, r, T.nblk + 1, slot0, T.natoms, a, c);
 }
 
 // FP64 energies of the nonbonded pairs (report steps / Forces.compute with energies; forces.py:379-413, 451-489 in double
@@ -906,12 +931,72 @@ __global__ void large_vv1_kernel(const LargeTopo T, const float dt, const long l
   }
 }
 
-// Langevin kick (vel += -gamma vel dt + vcoeff N(0,1)) and _second_VV; with `ekin` the per-block kinetic-energy
-// partials of a report step.  grid (ceil(N / 256), R): blocks do not straddle replicas.
-// fuse_next: also the _first_VV of the NEXT step (same atom, same thread: vel += 0.5 dt f / m ; pos += dt vel) and, with
-// `bbox`, the bounding boxes of the moved 32-atom tiles (a warp is a tile: blocks start at multiples of 256 atoms) -- one
-// launch instead of three between two force evaluations.  The host does not fuse on snapshot steps and on the last step
-// of a call, where pos must stay x(t + dt).
+// Atom a of replica r between two force evaluations: the force row (fixed-order sum of the partial rows, stored for the
+// caller), the Langevin kick (vel += -gamma vel dt + vcoeff N(0,1)), _second_VV of step `gstep` and -- fuse_next -- the
+// _first_VV of the next step (same atom, same thread: vel += 0.5 dt f / m ; pos += dt vel, large_vv1_kernel's arithmetic
+// expression by expression).  Returns the kinetic energy after _second_VV; lo = hi = the atom's (moved) position.
+template <bool COH>
+__device__ __forceinline__ double large_vv2_atom(const LargeTopo& T, const StepParams& I, const unsigned long long gstep,
+                                                 const long long r, const int a, float* vel, float* forces, float* pos,
+                                                 uint32_t* status, const int fuse_next, const float* fpart, const int slot0,
+                                                 float (&lo)[3], float (&hi)[3]) {
+  const long long g = r * T.natoms + a;
+  const float mass = __ldg(T.mass + a), invm = 1.0f / mass, hdt_m = 0.5f * I.dt * invm;
+  float v[3] = {vel[3 * g], vel[3 * g + 1], vel[3 * g + 2]};
+  float f[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    f[c] = large_row_sum<COH>(fpart, r, T.nblk + 1, slot0, T.natoms, a, c);
+    forces[3 * g + c] = f[c];
+  }
+  if (I.temperature > 0.0f) {
+    const float vcoef = sqrtf(2.0f * I.gamma * invm * kBoltzman * I.temperature * I.dt), vdamp = I.gamma * I.dt;
+    float n[3];
+    normal3(I.seed, (unsigned long long)(I.replica0 + r), (uint32_t)a, gstep, n);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) v[c] += fmaf(vcoef, n[c], -vdamp * v[c]);
+  }
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    v[c] = fmaf(hdt_m, f[c], v[c]);
+    vel[3 * g + c] = v[c];
+  }
+  const double ek = 0.5 * (double)mass * ((double)v[0] * v[0] + (double)v[1] * v[1] + (double)v[2] * v[2]);
+  float x = pos[3 * g], y = pos[3 * g + 1], z = pos[3 * g + 2];
+  if (status != nullptr && (x != x || y != y || z != z)) atomicOr(status + r, B200MD_FLAG_NAN_POS);
+  if (fuse_next) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      v[c] = fmaf(hdt_m, f[c], v[c]);
+      vel[3 * g + c] = v[c];
+    }
+    x = fmaf(I.dt, v[0], x); y = fmaf(I.dt, v[1], y); z = fmaf(I.dt, v[2], z);
+    pos[3 * g] = x; pos[3 * g + 1] = y; pos[3 * g + 2] = z;
+  }
+  lo[0] = hi[0] = x; lo[1] = hi[1] = y; lo[2] = hi[2] = z;
+  return ek;
+}
+// bounding box of the 32-atom tile held by this warp (lane = atom a, a warp-aligned), as large_bbox_kernel writes it
+__device__ __forceinline__ void large_tile_box_store(const LargeTopo& T, float* bbox, const long long r, const int a, const int lane,
+                                                     float (&lo)[3], float (&hi)[3]) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      lo[c] = fminf(lo[c], __shfl_xor_sync(0xffffffffu, lo[c], o));
+      hi[c] = fmaxf(hi[c], __shfl_xor_sync(0xffffffffu, hi[c], o));
+    }
+  const int tile = a >> 5;
+  if (lane < 3 && tile < T.nwords) {
+    bbox[(r * T.nwords + tile) * 8 + lane] = lane == 0 ? lo[0] : (lane == 1 ? lo[1] : lo[2]);
+    bbox[(r * T.nwords + tile) * 8 + 4 + lane] = lane == 0 ? hi[0] : (lane == 1 ? hi[1] : hi[2]);
+  }
+}
+
+// The integrator's launch between two force evaluations.  grid (ceil(N / 256), R): blocks do not straddle replicas.  With
+// `ekin` the per-block kinetic-energy partials of a report step; with fuse_next and `bbox` the bounding boxes of the moved
+// tiles (a warp is a tile: blocks start at multiples of 256 atoms) -- one launch instead of three.  The host does not fuse
+// on snapshot steps and on the last step of a call, where pos must stay x(t + dt).
 __global__ void __launch_bounds__(256)
 large_vv2_kernel(const LargeTopo T, const StepParams I, const unsigned long long gstep, const long long R,
                  float* __restrict__ vel, float* __restrict__ forces, float* __restrict__ pos,
@@ -922,60 +1007,59 @@ large_vv2_kernel(const LargeTopo T, const StepParams I, const unsigned long long
   for (long long r = blockIdx.y; r < R; r += gridDim.y) {
     double e[1] = {0.0};
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
-    if (a < T.natoms) {
-      const long long g = r * T.natoms + a;
-      const float mass = __ldg(T.mass + a), invm = 1.0f / mass, hdt_m = 0.5f * I.dt * invm;
-      float v[3] = {vel[3 * g], vel[3 * g + 1], vel[3 * g + 2]};
-      float f[3];  // the force row: fixed-order sum of the partial rows of large_forces_kernel, stored for the caller
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        f[c] = large_row_sum(fpart, r, T.nblk + 1, slot0, T.natoms, a, c);
-        forces[3 * g + c] = f[c];
-      }
-      if (I.temperature > 0.0f) {
-        const float vcoef = sqrtf(2.0f * I.gamma * invm * kBoltzman * I.temperature * I.dt), vdamp = I.gamma * I.dt;
-        float n[3];
-        normal3(I.seed, (unsigned long long)(I.replica0 + r), (uint32_t)a, gstep, n);
-#pragma unroll
-        for (int c = 0; c < 3; ++c) v[c] += fmaf(vcoef, n[c], -vdamp * v[c]);
-      }
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        v[c] = fmaf(hdt_m, f[c], v[c]);
-        vel[3 * g + c] = v[c];
-      }
-      e[0] = 0.5 * (double)mass * ((double)v[0] * v[0] + (double)v[1] * v[1] + (double)v[2] * v[2]);
-      float x = pos[3 * g], y = pos[3 * g + 1], z = pos[3 * g + 2];
-      if (status != nullptr && (x != x || y != y || z != z)) atomicOr(status + r, B200MD_FLAG_NAN_POS);
-      if (fuse_next) {  // large_vv1_kernel's arithmetic, expression by expression (bit-identical trajectories)
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          v[c] = fmaf(hdt_m, f[c], v[c]);
-          vel[3 * g + c] = v[c];
-        }
-        x = fmaf(I.dt, v[0], x); y = fmaf(I.dt, v[1], y); z = fmaf(I.dt, v[2], z);
-        pos[3 * g] = x; pos[3 * g + 1] = y; pos[3 * g + 2] = z;
-      }
-      lo[0] = hi[0] = x; lo[1] = hi[1] = y; lo[2] = hi[2] = z;
-    }
-    if (fuse_next && bbox != nullptr) {  // as large_bbox_kernel
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1)
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          lo[c] = fminf(lo[c], __shfl_xor_sync(0xffffffffu, lo[c], o));
-          hi[c] = fmaxf(hi[c], __shfl_xor_sync(0xffffffffu, hi[c], o));
-        }
-      const int lane = tid & 31, tile = a >> 5;
-      if (lane < 3 && tile < T.nwords) {
-        bbox[(r * T.nwords + tile) * 8 + lane] = lane == 0 ? lo[0] : (lane == 1 ? lo[1] : lo[2]);
-        bbox[(r * T.nwords + tile) * 8 + 4 + lane] = lane == 0 ? hi[0] : (lane == 1 ? hi[1] : hi[2]);
-      }
-    }
+    if (a < T.natoms) e[0] = large_vv2_atom<false>(T, I, gstep, r, a, vel, forces, pos, status, fuse_next, fpart, slot0, lo, hi);
+    if (fuse_next && bbox != nullptr) large_tile_box_store(T, bbox, r, a, tid & 31, lo, hi);
     if (ekin != nullptr) {
       lreduce<1, 256>(e, sred, tid);
       if (tid == 0) ekin[r * gridDim.x + blockIdx.x] = e[0];
     }
+  }
+}
+
+// Steps [s_begin, s_end) of one Integrator.step call in ONE cooperative launch (none of them a report step): per step
+//   phase F  the pair rectangles and bonded windows of all replicas, handed out CTA by CTA (the units of
+//            large_pairs_kernel / large_bonded_forces_kernel, same code, same partial rows);
+//   -- grid barrier --
+//   phase V  large_vv2_kernel's atoms (second half-kick of the step, first half-kick + drift of the next, tile boxes);
+//   -- grid barrier --
+// For calls with few replicas of a large solute the per-step launches of the other path are latency, not work; here the
+// state stays in L2 between the phases and a step costs its two grid barriers plus its longest unit (a Langevin step of
+// ONE 3 328-atom replica, cutoff mode: 30.5 us as 3 launches + 2 stream joins, 27.9 us here -- the longest rectangle is
+// most of it).  Results are bit-identical to the per-step launches (same unit code; positions, boxes and rows another
+// CTA wrote are read through L2, ldm<true>).  With more replicas the per-step launches are faster (the two kinds of CTA
+// in one kernel share one register allocation: 16 x 3 328 atoms 60 us against 49 us), so the host takes this path only
+// while the units of a step fill at most half of the resident grid.
+template <int MODE>
+__global__ void __launch_bounds__(kLThreads, 4)
+large_steps_kernel(const LargeTopo T, const ForceParams P, const StepParams I, const long long R, float* pos, float* vel,
+                   float* forces, const float* __restrict__ box, float* fpart, float* bbox, uint32_t* status,
+                   double* smd_rec, const int s_begin, const int s_end, const int snapshots_on, const int pairs_on) {
+  extern __shared__ __align__(16) char lsmem[];
+  cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  const int tid = threadIdx.x;
+  large_stage_tables(T, P, (float*)lsmem, tid);
+  char* wsmem = lsmem + large_tab_bytes(T);  // the bonded windows use the RectSmem region
+  const int nrect = pairs_on ? T.nblk * (T.nblk + 1) / 2 : 0, slot0 = pairs_on ? 0 : T.nblk;
+  const long long npair = (long long)nrect * R, nunits = npair + (long long)T.nwin * R;
+  const int chunks = (T.natoms + kLThreads - 1) / kLThreads;
+  for (int s = s_begin; s < s_end; ++s) {
+    const unsigned long long gstep = I.step0 + (unsigned long long)s;
+    const double center = (double)P.smd_c0 + (double)P.smd_rate * (double)(gstep + 1);
+    for (long long u = blockIdx.x; u < nunits; u += gridDim.x) {
+      if (u < npair) large_pairs_unit<MODE, true>(T, P, pos, box, fpart, bbox, u / nrect, (int)(u % nrect), lsmem, tid);
+      else large_bonded_unit<true>(T, P, pos, box, fpart, status, P.smd_centers, center, smd_rec, (u - npair) / T.nwin, (int)((u - npair) % T.nwin), wsmem, tid);
+    }
+    grid.sync();
+    const bool snap = snapshots_on && I.snapshot_every > 0 && (s + 1) % I.snapshot_every == 0;
+    const int fuse = (s + 1 < I.nsteps && !snap) ? 1 : 0;
+    for (long long c = blockIdx.x; c < (long long)chunks * R; c += gridDim.x) {
+      const long long r = c / chunks;
+      const int a = (int)(c % chunks) * kLThreads + tid;
+      float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+      if (a < T.natoms) large_vv2_atom<true>(T, I, gstep, r, a, vel, forces, pos, status, fuse, fpart, slot0, lo, hi);
+      if (fuse && bbox != nullptr) large_tile_box_store(T, bbox, r, a, tid & 31, lo, hi);
+    }
+    grid.sync();
   }
 }
 

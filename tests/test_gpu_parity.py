@@ -1050,6 +1050,33 @@ def test_large_solute_integrator_vs_oracle_and_bitwise_determinism():
     assert torch.equal(s.pos[2:3], s3.pos) and torch.equal(integ.observables[:, 2:3], integ3.observables)
 
 
+@pytest.mark.parametrize("mode", ["plain", "rf"])
+def test_large_solute_persistent_steps_kernel_is_bitwise_the_per_step_launches(mode, monkeypatch):
+    """Few replicas of a large solute: runs of steps between report steps are ONE cooperative launch (large_steps_kernel:
+    forces, grid barrier, half-kicks, grid barrier per step); with many replicas every step is 3 launches.  Same unit code,
+    same summation orders: every bit of the trajectory, the records and the snapshots agrees -- Langevin noise, a moving
+    SMD restraint, snapshot steps (which end a run) and a periodic replica included."""
+    g = _RandomMolecule(400, 43, R=4)
+    vel0 = (0.02 * np.random.default_rng(43).standard_normal(g.pos.shape)).astype(np.float32)
+    out = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("B200MD_LARGE_PERSISTENT", flag)
+        par, s = make_system(g, g.pos, vel0)
+        s.box[1, 0, 0], s.box[1, 1, 1], s.box[1, 2, 2] = 60.0, 60.0, 900.0
+        F = Forces(par, external=SMDBias([3], [390], fk=1.0, cent_0=300.0, rate_per_step=1e-3), **MODES[mode])
+        F.compute_batch(s.pos, s.box, s.forces)
+        integ = Integrator(s, F, timestep=0.5, device=DEV, gamma=1.0, T=300.0, seed=5)
+        integ.energy_every, integ.snapshot_every = 6, 7
+        lib = _cabi.load_library()
+        n0 = lib.b200md_launch_count()
+        integ.step(niter=23)
+        out[flag] = (s.pos.clone(), s.vel.clone(), s.forces.clone(), integ.observables.clone(), integ.snapshots.clone(),
+                     lib.b200md_launch_count() - n0)
+    for a, b in zip(out["0"][:5], out["1"][:5]):
+        assert torch.isfinite(b).all() and torch.equal(a, b)
+    assert out["1"][5] < out["0"][5] / 2  # 23 steps: 4 report steps + 7 runs (+ first half-kicks) against 3 launches a step
+
+
 def test_large_solute_unsupported_options_raise():
     g = _RandomMolecule(140, 42, R=1)
     par, s = make_system(g, g.pos, np.zeros_like(g.pos))
