@@ -1623,16 +1623,18 @@ static int large_integrate(const b200md_topology* topo, const ForceParams& P, co
   for (int s = 0; s < I.nsteps; ++s) {
     const unsigned long long gstep = I.step0 + (unsigned long long)s;
     const bool report = is_report(s);
+    if (!fused_prev) {
+      large_vv1_kernel<<<(unsigned)((natom + 255) / 256), 256, 0, st>>>(L, I.dt, R, pos, vel, forces);
+      g_launches.fetch_add(1);
+    }
+    bool boxes_ready = fused_prev && want_bbox;
     if (persist && !report) {
       int e = s;
       while (e < I.nsteps && !is_report(e)) { ++e; if (is_snap(e - 1)) break; }  // steps [s, e): no report, a snapshot only after the last
-      if (!fused_prev) {
-        large_vv1_kernel<<<(unsigned)((natom + 255) / 256), 256, 0, st>>>(L, I.dt, R, pos, vel, forces);
+      if (want_bbox && !boxes_ready) {
+        large_bbox_kernel<<<dim3((L.nwords + 3) / 4, (unsigned)std::min<int64_t>(R, 65535)), 128, 0, st>>>(L, R, pos, w.bbox);
         g_launches.fetch_add(1);
-        if (want_bbox) {
-          large_bbox_kernel<<<dim3((L.nwords + 3) / 4, (unsigned)std::min<int64_t>(R, 65535)), 128, 0, st>>>(L, R, pos, w.bbox);
-          g_launches.fetch_add(1);
-        }
+        boxes_ready = true;
       }
       const long long chunks = (long long)((L.natoms + kLThreads - 1) / kLThreads) * R;
       const unsigned grid = (unsigned)std::max<long long>(1, std::min<long long>(resident, std::max<long long>(units, chunks)));
@@ -1642,22 +1644,21 @@ static int large_integrate(const b200md_topology* topo, const ForceParams& P, co
       LargeTopo Lc = L; ForceParams Pc = P; StepParams Ic = I;
       void* args[] = {&Lc, &Pc, &Ic, &Rl, &pos, &vel, &forces, &box, &w.fpart, &bb, &status, &w.smd, &s_begin, &s_end, &snaps_on, &pon};
       const void* fn = mode ? (const void*)large_steps_kernel<1> : (const void*)large_steps_kernel<0>;
-      CUDA_TRY(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kLThreads), args, (size_t)large_steps_dyn_bytes(L), st));
-      g_launches.fetch_add(1);
-      fused_prev = e < I.nsteps && !is_snap(e - 1);
-      if (is_snap(e - 1)) {
-        const long long slot = e / I.snapshot_every - 1;
-        CUDA_TRY(cudaMemcpyAsync((char*)snapshots + slot * frame, pos, frame, cudaMemcpyDeviceToDevice, st));
+      if (cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kLThreads), args, (size_t)large_steps_dyn_bytes(L), st) == cudaSuccess) {
+        g_launches.fetch_add(1);
+        fused_prev = e < I.nsteps && !is_snap(e - 1);
+        if (is_snap(e - 1)) {
+          const long long slot = e / I.snapshot_every - 1;
+          CUDA_TRY(cudaMemcpyAsync((char*)snapshots + slot * frame, pos, frame, cudaMemcpyDeviceToDevice, st));
+        }
+        s = e - 1;
+        continue;
       }
-      s = e - 1;
-      continue;
-    }
-    if (!fused_prev) {
-      large_vv1_kernel<<<(unsigned)((natom + 255) / 256), 256, 0, st>>>(L, I.dt, R, pos, vel, forces);
-      g_launches.fetch_add(1);
+      cudaGetLastError();  // the grid does not fit this context (MPS share, a capture ...): the per-step launches do the same work
+      persist = false;
     }
     const double center = (double)P.smd_c0 + (double)P.smd_rate * (double)(gstep + 1);
-    rc = large_forces(topo, P, R, pos, box, forces, w.energies, status, center, report, w, fused_prev && want_bbox, false);
+    rc = large_forces(topo, P, R, pos, box, forces, w.energies, status, center, report, w, boxes_ready, false);
     if (rc) return rc;
     const bool snap = I.snapshot_every > 0 && snapshots != nullptr && (s + 1) % I.snapshot_every == 0;
     const bool fuse = s + 1 < I.nsteps && !snap;
