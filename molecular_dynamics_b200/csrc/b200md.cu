@@ -1462,7 +1462,7 @@ struct LargeWork {
   cudaStream_t st;
   double* partial = nullptr; double* energies = nullptr; double* ekin = nullptr; double* smd = nullptr;
   float* bbox = nullptr;
-  float* fpart = nullptr;  // [R][nblk + 1][natoms][3] partial force rows of large_forces_kernel
+  float* fpart = nullptr;  // [R][nblk + 1][natoms][3] partial force rows (large_pairs_kernel, large_bonded_forces_kernel)
   int nbonded_blocks = 0, npart = 0, nek = 0;
 };
 

@@ -950,7 +950,7 @@ def test_chamber_energies_on_gpu_against_namd_at_the_restart_frame():
 @pytest.mark.parametrize("natoms,seed", [(129, 30), (160, 31), (257, 32), (300, 33), (700, 35), (1000, 34)])
 def test_large_solute_forces_vs_oracle(natoms, seed):
     """SURVEY 8f N4 (larger solutes, e.g. the adk system named at V_Calculations/Test-10_diALA/potcalc.py:114): above 128
-    atoms the same Forces.compute runs as bonded-item + 32 x 32 pair-tile kernels; same tolerances as the on-chip path."""
+    atoms the same Forces.compute runs as bonded-window + half-shell pair-rectangle kernels; same tolerances as the on-chip path."""
     g = _RandomMolecule(natoms, seed, R=2)
     for mode in ("plain", "rf"):
         f_ref, e_ref = oracle.forces(g.packed, g.pos, **MODES[mode])
@@ -1042,7 +1042,7 @@ def test_large_solute_integrator_vs_oracle_and_bitwise_determinism():
     np.testing.assert_allclose(obs[:, :, _cabi.OBS_E2E_DIST], ref[:, :, _cabi.OBS_E2E_DIST], rtol=1e-5)
     np.testing.assert_allclose(obs[:, :, _cabi.OBS_SMD_WORK], ref[:, :, _cabi.OBS_SMD_WORK], rtol=1e-4, atol=1e-7)
     assert np.abs(integ.snapshots.cpu().numpy() - out["snapshots"]).max() < 3e-4
-    # same run again, and replica 2 alone as its own shard: bit-identical (integer force accumulation, fixed-order
+    # same run again, and replica 2 alone as its own shard: bit-identical (private force slots and partial rows, fixed-order
     # reductions, RNG keyed by the global replica index)
     s2, integ2, _ = run()
     assert torch.equal(s.pos, s2.pos) and torch.equal(s.vel, s2.vel) and torch.equal(integ.observables, integ2.observables)
@@ -1075,6 +1075,32 @@ def test_large_solute_persistent_steps_kernel_is_bitwise_the_per_step_launches(m
     for a, b in zip(out["0"][:5], out["1"][:5]):
         assert torch.isfinite(b).all() and torch.equal(a, b)
     assert out["1"][5] < out["0"][5] / 2  # 23 steps: 4 report steps + 7 runs (+ first half-kicks) against 3 launches a step
+
+
+def test_large_solute_more_replicas_than_grid_rows():
+    """The large-solute grids carry the replica in blockIdx.y (at most 65 535 rows): beyond that a CTA loops over replicas.
+    66 000 replicas of a 129-atom molecule, copies of two conformers: every copy must carry the bits of its original,
+    through Forces.compute and a few NVE steps (per-step launches: the units of a step exceed the resident grid)."""
+    g = _RandomMolecule(129, 44, R=2)
+    R = 66000
+    par = gpu_par(g)
+    idx = torch.arange(R, device=DEV) % 2
+    s = System(129, R, torch.float, DEV)
+    s.pos[:] = torch.tensor(g.pos, device=DEV)[idx]
+    s.vel[:] = torch.tensor((0.01 * np.random.default_rng(44).standard_normal(g.pos.shape)).astype(np.float32), device=DEV)[idx]
+    F = Forces(par, **MODES["rf"])
+    e = F.compute_batch(s.pos, s.box, s.forces)
+    f_ref, e_ref = oracle.forces(g.packed, g.pos, **MODES["rf"])
+    assert np.abs(s.forces[:2].cpu().numpy() - f_ref).max() / np.abs(f_ref).max() < 1e-5
+    check_energies(e[:2].cpu().numpy(), e_ref, "large solute, 66 000 replicas")
+    for t in (s.forces, e):
+        assert torch.equal(t, t[:2][idx])
+    integ = Integrator(s, F, timestep=1.0, device=DEV)
+    integ.energy_every = 2
+    integ.step(niter=3)
+    for t in (s.pos, s.vel, s.forces):
+        assert torch.isfinite(t).all() and torch.equal(t, t[:2][idx])
+    assert torch.equal(integ.observables, integ.observables[:, :2][:, idx])
 
 
 def test_large_solute_unsupported_options_raise():
