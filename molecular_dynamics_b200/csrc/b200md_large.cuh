@@ -29,7 +29,7 @@
 // the replica count of a call or on how often energies are recorded (every summation order is fixed by the topology).
 // Round 1 for comparison: full-shell 32 x 32 tiles (every pair evaluated from both atoms), one FP64 thread per bonded item
 // with int64 global atomics, 4-6 launches per step: 397 / 246 us per Langevin step of 256 x 1 040 atoms (plain / cutoff
-// 9 A); now 270 / 128 us (profiles/r02_large_solute.md).
+// 9 A); now 256 / 124 us (profiles/r02_large_solute.md).
 #pragma once
 #include <cooperative_groups.h>
 
@@ -735,8 +735,8 @@ __device__ __forceinline__ void large_bonded_unit(const LargeTopo& T, const Forc
   const int k0 = __ldg(T.win_start + w), k1 = __ldg(T.win_start + w + 1);
   const int4 ke = __ldg(T.win_kend + w);  // first entry of the angles, dihedrals, 1-4 pairs, impropers of the window
   const int hlo = __ldg(T.win_lo + w), hn = __ldg(T.win_n + w);
-  const int a = kLWin * w + tid;  // the atom this thread gathers (tid < kLWin)
-  const bool mine = tid < kLWin && a < N;
+  const int a = kLWin * w + (tid >> 1), half = tid & 1;  // two threads gather an atom: its even / its odd slots
+  const bool mine = a < N;
   const int g0 = __ldg(T.gstart + kLWin * w);
   const int s0 = mine ? __ldg(T.gstart + a) - g0 : 0, s1 = mine ? __ldg(T.gstart + a + 1) - g0 : 0;
   const float* p = pos + r * N * 3;
@@ -774,9 +774,12 @@ __device__ __forceinline__ void large_bonded_unit(const LargeTopo& T, const Forc
   if (hn > 0) items(SharedPos{(uint32_t)__cvta_generic_to_shared(shalo) - 16u * (uint32_t)hlo});
   else items(GlobalPos{p});  // the window's items span more than kLHalo atoms: from HBM
   __syncthreads();
-  if (mine) {
-    float bx = 0.0f, by = 0.0f, bz = 0.0f;
-    for (int sidx = s0; sidx < s1; ++sidx) { const float4 v = lslots[sidx]; bx += v.x; by += v.y; bz += v.z; }
+  float bx = 0.0f, by = 0.0f, bz = 0.0f;
+  for (int sidx = s0 + half; sidx < s1; sidx += 2) { const float4 v = lslots[sidx]; bx += v.x; by += v.y; bz += v.z; }
+  bx = __fadd_rn(bx, __shfl_xor_sync(0xffffffffu, bx, 1));  // (even slots in order) + (odd slots in order): a fixed order
+  by = __fadd_rn(by, __shfl_xor_sync(0xffffffffu, by, 1));
+  bz = __fadd_rn(bz, __shfl_xor_sync(0xffffffffu, bz, 1));
+  if (mine && half == 0) {
     const float x = ldm<COH>(p + 3 * a), y = ldm<COH>(p + 3 * a + 1), z = ldm<COH>(p + 3 * a + 2);
     if (status != nullptr && (x != x || y != y || z != z)) atomicOr(status + r, B200MD_FLAG_NAN_POS);
     if (P.smd_on && (a == P.smd_a1 || a == P.smd_a2)) {  // potcalc.py:75-89, not wrapped; FP64: (c - d) cancels near the centre
