@@ -7,8 +7,9 @@ the energies come from a kernel, so the graph edge is provided by an autograd.Fu
     d(sum_k g_k E_k)/d pos = - sum_k g_k F_k
 
 When every enabled term of a replica receives the same upstream weight the total force of the forward
-launch is reused; otherwise the per-term forces F_k are recomputed with one force-only launch per group of
-columns that share a weight (``energies=False``: the FP64 energy pass is skipped).
+launch is reused; otherwise columns that share a weight form a group, the most expensive group is taken from the
+forward's total force, and each further group costs one force-only launch (``energies=False``: no FP64 energy pass):
+``sum_g w_g F_g = w_0 F_tot + sum_{g > 0} (w_g - w_0) F_g``.
 """
 from __future__ import annotations
 
@@ -72,33 +73,53 @@ class _EnergyFunction(torch.autograd.Function):
         allcols = cols + [_cabi.NUM_ENERGIES + k for k in range(len(extra))]
         if not allcols:
             return torch.zeros_like(pos).to(ctx.in_dtype), None, None, None
+        # which columns carry the same weight on every replica: ONE small comparison and one device -> host read (each
+        # torch.equal / bool() here was a stream synchronisation of its own; a loss like cgan.py:351-353 paid ten per step)
         gsel = g[:, allcols]
-        if bool((gsel == gsel[:, :1]).all()):  # uniform weight per replica: reuse the forward launch
+        eq = (gsel.unsqueeze(2) == gsel.unsqueeze(1)).all(0).cpu()
+        if bool(eq[0].all()):  # uniform weight per replica: reuse the forward launch
             grad = -gsel[:, :1, None].to(ftot.dtype) * ftot
             return grad.to(ctx.in_dtype), None, None, None
         b = box.to(device=pos.device, dtype=torch.float32).contiguous()
-        grad = torch.zeros_like(pos)
         tmp = torch.empty_like(pos)
         # columns that carry the same weight on every replica share a launch: the ML callers' loss
         # sum(terms) + 200 * E2End (cgan.py:351-353) needs two, not one per column
         groups = []
-        for c in cols:
+        for i, c in enumerate(cols):
             for grp in groups:
-                if torch.equal(g[:, c], g[:, grp[0]]):
+                if bool(eq[i, cols.index(grp[0])]):
                     grp.append(c)
                     break
             else:
                 groups.append([c])
-        for grp in groups:
-            tmask = 0
+        # The forward launch already holds the sum of ALL per-column forces (ftot), so the most expensive group needs no
+        # launch of its own: with weights w_g,  sum_g w_g F_g = w_0 F_tot + sum_{g > 0} (w_g - w_0) F_g.  The ML callers'
+        # loss (all terms at one weight, the restraint at another) costs ONE extra launch -- of the restraint alone.
+        def cost(grp):
+            tm = 0
             for c in grp:
                 if c != 7:
-                    tmask |= _term_mask(mask, c)
-            fobj._launch(pos, b, tmp, terms_mask=tmask, with_smd=7 in grp, energies=False, smd_center=ctx.smd_center)
-            grad -= g[:, grp[0]:grp[0] + 1, None].to(tmp.dtype) * tmp
-        for k, term in enumerate(extra):
-            fobj._launch(pos, b, tmp, terms_mask=_B[term], with_smd=False, energies=False)
-            grad -= g[:, _cabi.NUM_ENERGIES + k:_cabi.NUM_ENERGIES + k + 1, None].to(tmp.dtype) * tmp
+                    tm |= _term_mask(mask, c)
+            return bin(tm).count("1") + (8 if tm & (_B["lj"] | _B["electrostatics"] | _B["repulsion"] | _B["repulsioncg"]) else 0)
+
+        launches = [("cols", grp) for grp in groups] + [("extra", k) for k in range(len(extra))]
+        base = max(range(len(groups)), key=lambda i: cost(groups[i]))
+        w0 = g[:, groups[base][0]:groups[base][0] + 1, None].to(ftot.dtype)
+        grad = -w0 * ftot
+        for kind, item in launches:
+            if kind == "cols":
+                if item is groups[base]:
+                    continue
+                tmask = 0
+                for c in item:
+                    if c != 7:
+                        tmask |= _term_mask(mask, c)
+                fobj._launch(pos, b, tmp, terms_mask=tmask, with_smd=7 in item, energies=False, smd_center=ctx.smd_center)
+                wg = g[:, item[0]:item[0] + 1, None].to(tmp.dtype)
+            else:
+                fobj._launch(pos, b, tmp, terms_mask=_B[extra[item]], with_smd=False, energies=False)
+                wg = g[:, _cabi.NUM_ENERGIES + item:_cabi.NUM_ENERGIES + item + 1, None].to(tmp.dtype)
+            grad -= (wg - w0) * tmp
         return grad.to(ctx.in_dtype), None, None, None
 
 

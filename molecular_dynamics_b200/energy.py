@@ -105,7 +105,8 @@ class Energy:
             ene = self.forces.compute_batch(pos, box, frc).to(pos.dtype)
         self.last_forces = frc
         keys = list(self.forces.energies) + ["external"]
-        out = {k: ene[:, _cabi.energy_slot(k)] for k in keys}
+        cols = ene.unbind(1)  # ONE autograd node for all columns (a select per term costs a zero-fill + copy each in backward)
+        out = {k: cols[_cabi.energy_slot(k)] for k in keys}
         if self.colvar_name is not None:  # the adapter books the restraint under the colvar's name
             out[self.colvar_name] = out.pop("external")
         phis = self.forces.dihedral_angles(pos, None)
