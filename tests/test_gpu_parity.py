@@ -137,6 +137,23 @@ def test_term_subsets():
         check(g, g["pos"], f, e, f_ref, e_ref, str(terms))
 
 
+def test_custom_op_registration_matches_the_direct_ctypes_call():
+    """Forces calls the ctypes function directly in eager mode; the same call is registered as the custom op
+    b200md::forces_compute for traced graphs.  Both must fill the same bits."""
+    g = load_golden("ala10")
+    par = Parameters.from_arrays(g.par.to_arrays(), device=DEV)
+    F = Forces(par, cutoff=9.0, rfa=True, switch_dist=7.5, external=SMDBias([3], [98], fk=1.0, cent_0=14.0))
+    p = torch.tensor(g["pos"][:7].astype(np.float32), device=DEV)
+    b = torch.zeros((7, 3, 3), device=DEV)
+    f1 = torch.zeros_like(p)
+    e1 = F.compute_batch(p, b, f1)
+    f2, e2 = torch.zeros_like(p), torch.zeros((7, _cabi.NUM_ENERGIES), dtype=torch.float64, device=DEV)
+    status = torch.zeros(7, dtype=torch.int32, device=DEV)
+    (smd_on, a1, a2, fk, c0), cen = F._smd_args(7, torch.device(DEV), None)
+    torch.ops.b200md.forces_compute(p, b, f2, e2, status, F._handle(torch.device(DEV)), *F._opts(), smd_on, a1, a2, fk, c0, cen)
+    assert torch.equal(f1, f2) and torch.equal(e1, e2) and int(status.max()) == 0
+
+
 def test_reference_shaped_compute_api():
     g = load_golden("bb40")
     par = gpu_par(g)
