@@ -29,7 +29,7 @@
 // the replica count of a call or on how often energies are recorded (every summation order is fixed by the topology).
 // Round 1 for comparison: full-shell 32 x 32 tiles (every pair evaluated from both atoms), one FP64 thread per bonded item
 // with int64 global atomics, 4-6 launches per step: 397 / 246 us per Langevin step of 256 x 1 040 atoms (plain / cutoff
-// 9 A); now 256 / 124 us (profiles/r02_large_solute.md).
+// 9 A); now 255 / 120 us (profiles/r02_large_solute.md).
 #pragma once
 #include <cooperative_groups.h>
 

@@ -66,13 +66,13 @@ def _forces_compute_op(pos: torch.Tensor, box: torch.Tensor, forces: torch.Tenso
                     smd_a2, smd_fk, smd_c0, smd_centers)
 
 
-@torch.library.custom_op("b200md::integrate", mutates_args=("pos", "vel", "forces", "observables", "snapshots", "status"))
-def _integrate_op(pos: torch.Tensor, vel: torch.Tensor, forces: torch.Tensor, box: torch.Tensor,
-                  observables: torch.Tensor, snapshots: torch.Tensor, status: torch.Tensor, handle: int, terms: int,
-                  cutoff: float, rfa: bool, eps: float, switch_dist: float, smd_on: bool, smd_a1: int, smd_a2: int,
-                  smd_fk: float, smd_c0: float, smd_rate: float, dt: float, gamma: float, temperature: float,
-                  seed: int, step0: int, replica0: int, nsteps: int, energy_every: int, snapshot_every: int,
-                  rigid_bonds: bool = False) -> None:
+def _integrate(pos: torch.Tensor, vel: torch.Tensor, forces: torch.Tensor, box: torch.Tensor,
+               observables: torch.Tensor, snapshots: torch.Tensor, status: torch.Tensor, handle: int, terms: int,
+               cutoff: float, rfa: bool, eps: float, switch_dist: float, smd_on: bool, smd_a1: int, smd_a2: int,
+               smd_fk: float, smd_c0: float, smd_rate: float, dt: float, gamma: float, temperature: float,
+               seed: int, step0: int, replica0: int, nsteps: int, energy_every: int, snapshot_every: int,
+               rigid_bonds: bool = False) -> None:
+    """ctypes call of b200md_integrate on the current stream (eager path; ``b200md::integrate`` below for traced graphs)."""
     lib = _cabi.load_library()
     fo = _cabi.ForceOpts(terms, cutoff, int(rfa), eps, switch_dist)
     so = _cabi.SmdOpts(int(smd_on), smd_a1, smd_a2, smd_fk, smd_c0, smd_rate, None)
@@ -83,6 +83,18 @@ def _integrate_op(pos: torch.Tensor, vel: torch.Tensor, forces: torch.Tensor, bo
         _check(lib.b200md_integrate(C.c_void_p(handle), C.byref(fo), C.byref(so), C.byref(io), pos.shape[0], _ptr(pos),
                                     _ptr(vel), _ptr(forces), _ptr(box), _ptr(observables), snaps, _ptr(status),
                                     _stream_ptr(pos.device)))
+
+
+@torch.library.custom_op("b200md::integrate", mutates_args=("pos", "vel", "forces", "observables", "snapshots", "status"))
+def _integrate_op(pos: torch.Tensor, vel: torch.Tensor, forces: torch.Tensor, box: torch.Tensor,
+                  observables: torch.Tensor, snapshots: torch.Tensor, status: torch.Tensor, handle: int, terms: int,
+                  cutoff: float, rfa: bool, eps: float, switch_dist: float, smd_on: bool, smd_a1: int, smd_a2: int,
+                  smd_fk: float, smd_c0: float, smd_rate: float, dt: float, gamma: float, temperature: float,
+                  seed: int, step0: int, replica0: int, nsteps: int, energy_every: int, snapshot_every: int,
+                  rigid_bonds: bool = False) -> None:
+    _integrate(pos, vel, forces, box, observables, snapshots, status, handle, terms, cutoff, rfa, eps, switch_dist, smd_on,
+               smd_a1, smd_a2, smd_fk, smd_c0, smd_rate, dt, gamma, temperature, seed, step0, replica0, nsteps, energy_every,
+               snapshot_every, rigid_bonds)
 
 
 class SMDBias:

@@ -21,7 +21,7 @@ import numpy as np
 import torch
 
 from . import _cabi
-from .forces import SMDBias
+from .forces import SMDBias, _integrate
 
 TIMEFACTOR = 48.88821  # fs per internal time unit
 BOLTZMAN = 0.001987191  # kcal/mol/K
@@ -170,10 +170,10 @@ class Integrator:
         else:
             smd = (False, 0, 0, 0.0, 0.0, 0.0)
         smd_c0 = smd[4]
-        torch.ops.b200md.integrate(pos, vel, frc, box, obs, snaps, status, f._handle(dev), *f._opts(), smd[0], smd[1],
-                                   smd[2], smd[3], smd_c0, smd[5], float(self.dt), float(self.gamma),
-                                   float(self.T) if self.T else 0.0, self.seed, self.step_count, self.replica0,
-                                   int(niter), int(energy_every), int(self.snapshot_every), self.rigid_bonds)
+        call = torch.ops.b200md.integrate if torch.compiler.is_compiling() else _integrate
+        call(pos, vel, frc, box, obs, snaps, status, f._handle(dev), *f._opts(), smd[0], smd[1], smd[2], smd[3], smd_c0,
+             smd[5], float(self.dt), float(self.gamma), float(self.T) if self.T else 0.0, self.seed, self.step_count,
+             self.replica0, int(niter), int(energy_every), int(self.snapshot_every), self.rigid_bonds)
         self.step_count += int(niter)
         if self.rigid_bonds:
             import ctypes

@@ -137,7 +137,7 @@ def test_term_subsets():
         check(g, g["pos"], f, e, f_ref, e_ref, str(terms))
 
 
-def test_custom_op_registration_matches_the_direct_ctypes_call():
+def test_custom_op_registration_matches_the_direct_ctypes_call(monkeypatch):
     """Forces calls the ctypes function directly in eager mode; the same call is registered as the custom op
     b200md::forces_compute for traced graphs.  Both must fill the same bits."""
     g = load_golden("ala10")
@@ -152,6 +152,22 @@ def test_custom_op_registration_matches_the_direct_ctypes_call():
     (smd_on, a1, a2, fk, c0), cen = F._smd_args(7, torch.device(DEV), None)
     torch.ops.b200md.forces_compute(p, b, f2, e2, status, F._handle(torch.device(DEV)), *F._opts(), smd_on, a1, a2, fk, c0, cen)
     assert torch.equal(f1, f2) and torch.equal(e1, e2) and int(status.max()) == 0
+
+    # the classes pick the custom ops when a graph is being compiled: same bits from Integrator.step either way
+    def run():
+        s = System(104, 7, torch.float, DEV)
+        s.pos[:] = p
+        F.compute_batch(s.pos, s.box, s.forces)
+        integ = Integrator(s, F, timestep=1.0, device=DEV, gamma=1.0, T=300.0, seed=3)
+        integ.energy_every = 5
+        integ.step(niter=12)
+        return s.pos.clone(), s.vel.clone(), integ.observables.clone()
+
+    direct = run()
+    monkeypatch.setattr(torch.compiler, "is_compiling", lambda: True)
+    via_op = run()
+    for a, c in zip(direct, via_op):
+        assert torch.equal(a, c)
 
 
 def test_reference_shaped_compute_api():
