@@ -1,3 +1,5 @@
+"""Per-kernel totals of an ncu launch list (`ncu --metrics gpu__time_duration.sum --csv --log-file x.csv ...`):
+average duration x launches = total, share of the listed time.  usage: python tools/launch_summary.py x.csv"""
 import csv,sys,collections
 rows=[r for r in csv.reader(open(sys.argv[1])) if len(r)>10]
 hdr=rows[0]; ki=hdr.index('Kernel Name'); vi=hdr.index('Metric Value'); ui=hdr.index('Metric Unit')
