@@ -1136,6 +1136,37 @@ def test_large_solute_more_replicas_than_grid_rows():
     assert torch.equal(integ.observables, integ.observables[:, :2][:, idx])
 
 
+def test_large_solute_minimise_then_equilibrate():
+    """The reference's own use of a large solute (potcalc.py / tutorial.ipynb on a prmtop): minimise, draw
+    Maxwell-Boltzmann velocities, run Langevin dynamics -- on a 3-chain deca-alanine bundle (312 atoms) behind the same
+    classes: FIRE lowers the energy of perturbed conformers, the thermostat then holds ~300 K."""
+    from molecular_dynamics_b200 import maxwell_boltzmann, minimize_fire
+
+    g = load_golden("ala10")
+    copies, R = 3, 8
+    parL = Parameters.from_arrays(g.par.tiled(copies).to_arrays(), device=DEV)
+    shift = np.repeat(np.arange(copies), 104)[None, :, None] * np.array([0.0, 12.0, 12.0])
+    rng = np.random.default_rng(8)
+    pos = (g["base_frames"][:R * copies].reshape(R, copies * 104, 3) + shift + 0.05 * rng.standard_normal((R, copies * 104, 3))).astype(np.float32)
+    s = System(copies * 104, R, torch.float, DEV)
+    s.pos[:] = torch.tensor(pos, device=DEV)
+    F = Forces(parL, cutoff=9.0, rfa=True, switch_dist=7.5)
+    e0 = F.compute_batch(s.pos, s.box, s.forces).sum(1).cpu().numpy()
+    out = minimize_fire(s, F, steps=300, fmax=5.0)
+    e1 = out["epot"].cpu().numpy()
+    assert (e1 < e0 - 150.0).all(), (e0, e1)
+    assert not torch.isnan(s.pos).any()
+    s.set_velocities(maxwell_boltzmann(parL.masses, T=300.0, replicas=R))
+    F.compute_batch(s.pos, s.box, s.forces)
+    integ = Integrator(s, F, timestep=1.0, device=DEV, gamma=10.0, T=300.0, seed=12)  # 0.1 ps coupling: from a minimum, half
+    integ.energy_every = 50                                                            # of the drawn kinetic energy goes into
+    integ.step(niter=1000)                                                             # the potential within a few periods
+    ek = integ.observables[-8:, :, _cabi.OBS_EKIN].mean().item()
+    temp = 2.0 * ek / (3 * copies * 104 * 0.001987191)  # Ekin = 3/2 N kB T, kB in kcal/mol/K
+    assert 240.0 < temp < 360.0, temp
+    assert torch.isfinite(s.pos).all()
+
+
 def test_large_solute_unsupported_options_raise():
     g = _RandomMolecule(140, 42, R=1)
     par, s = make_system(g, g.pos, np.zeros_like(g.pos))
