@@ -416,8 +416,8 @@ __host__ __device__ inline int large_tab_stride(int ntypes) { return ntypes | 1;
 // registers over the passes and transposed once per chunk by a shuffle butterfly.  In a diagonal rectangle a chunk only
 // meets i tiles ABOVE its own tile, and the 32 x 32 pairs inside a tile are evaluated full-shell by its lanes (no j side).
 // Every unordered pair is evaluated once -- round 1 evaluated each from both atoms.
-// Cutoff mode, vacuum: lane l < bt tests tile box (BI, l) against the j tile's box (large_bbox_kernel), a ballot is the
-// chunk's pass list; a listed pass still drops out on a warp vote when none of its 32 x 8 pairs is within the cutoff
+// Cutoff mode: lane l < bt tests tile box (BI, l) against the j tile's box (large_bbox_kernel; under periodic boundaries
+// by the minimum image of the box centres, lgap), a ballot is the chunk's pass list; a listed pass still drops out on a warp vote when none of its 32 x 8 pairs is within the cutoff
 // (the r^2 of the vote are the expressions pair_eval2 evaluates: bit-identical with and without the skips).
 // The CTA writes the block's partial force rows fpart[r][slot][atom][3]: atoms of BI -> slot BJ, atoms of BJ -> slot BI
 // (diagonal: both sides summed into slot BI), so atom a of block B finds slot k written by rectangle (max(B, k), min(B, k)):
@@ -433,6 +433,20 @@ struct RectSmem {
   float fj[3][kLB];
 };
 
+// Lower bound of |x_a - x_b| in one component for atoms a, b inside the intervals [alo, ahi], [blo, bhi].  Vacuum: the gap
+// of the intervals, in the monotonic fp32 arithmetic of the pair loop (an exact bound).  Periodic (box length -nb, 1 / L =
+// ib; 0, 0 for an open direction): the minimum-image distance of the interval centres less the two half widths -- any pair
+// is x_a - x_b = (c_a - c_b) + (d_a - d_b) with |d| <= the half widths, so no image brings it closer; the callers leave a
+// 0.1 % margin on the squared distance for the rounding of this expression (3e-6 A at 100 A against 4.5e-3 A of margin).
+template <bool PBC>
+__device__ __forceinline__ float lgap(const float alo, const float ahi, const float blo, const float bhi, const float nb,
+                                      const float ib) {
+  if (!PBC) return fmaxf(fmaxf(__fsub_rn(blo, ahi), __fsub_rn(alo, bhi)), 0.0f);
+  float c = 0.5f * ((alo + ahi) - (blo + bhi));
+  c = fmaf(nb, rintf(c * ib), c);
+  return fmaxf(fabsf(c) - 0.5f * ((ahi - alo) + (bhi - blo)), 0.0f);
+}
+
 template <int MODE, bool PBC, bool COH>
 __device__ __forceinline__ void large_rect(const LargeTopo& T, const ForceParams& P, const float* __restrict__ p,
                                            const float* __restrict__ bb, RectSmem& S, const uint32_t tab, const int BI,
@@ -443,7 +457,8 @@ __device__ __forceinline__ void large_rect(const LargeTopo& T, const ForceParams
   const bool diag = BI == BJ;
   const int tstride = large_tab_stride(T.ntypes);
   const int nia = min(32 * bt, max(0, 32 * nw - 32 * bt * BI)), nja = min(32 * bt, max(0, 32 * nw - 32 * bt * BJ));  // padded atoms of the blocks
-  const bool boxtest = MODE == 1 && !PBC && bb != nullptr;
+  const bool boxtest = MODE == 1 && bb != nullptr;
+  const float rc2_box = PBC ? 1.001f * P.rc2 : P.rc2;
   if (boxtest) {  // the whole rectangle beyond the cutoff (chains far apart): its rows are zero
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
     const int blk = lane < 16 ? BI : BJ, tl = lane & 15, tile = blk * bt + tl;
@@ -462,10 +477,10 @@ __device__ __forceinline__ void large_rect(const LargeTopo& T, const ForceParams
 #pragma unroll
     for (int c = 0; c < 3; ++c) {  // lanes 0..15 hold BI's box, 16..31 BJ's
       const float olo = __shfl_xor_sync(0xffffffffu, lo[c], 16), ohi = __shfl_xor_sync(0xffffffffu, hi[c], 16);
-      const float g = fmaxf(fmaxf(__fsub_rn(olo, hi[c]), __fsub_rn(lo[c], ohi)), 0.0f);
+      const float g = lgap<PBC>(lo[c], hi[c], olo, ohi, c == 0 ? nbox.x : (c == 1 ? nbox.y : nbox.z), c == 0 ? ibox.x : (c == 1 ? ibox.y : ibox.z));
       g2 = __fmaf_rn(g, g, g2);
     }
-    if (!(g2 <= P.rc2)) {  // (uniform over the CTA: every warp computes the same boxes)
+    if (!(g2 <= rc2_box)) {  // (uniform over the CTA: every warp computes the same boxes)
       for (int k = tid; k < 3 * nia; k += kLThreads) if (32 * bt * BI + k / 3 < N) out_i[k] = 0.0f;
       if (!diag) for (int k = tid; k < 3 * nja; k += kLThreads) if (32 * bt * BJ + k / 3 < N) out_j[k] = 0.0f;
       return;
@@ -501,10 +516,9 @@ __device__ __forceinline__ void large_rect(const LargeTopo& T, const ForceParams
       const int it = BI * bt + lane;
       const float4 ilo = ldm4<COH>((const float4*)(bb + 8 * it)), ihi = ldm4<COH>((const float4*)(bb + 8 * it + 4));
       const float4 tlo = ldm4<COH>((const float4*)(bb + 8 * jt)), thi = ldm4<COH>((const float4*)(bb + 8 * jt + 4));
-      const float gx = fmaxf(fmaxf(__fsub_rn(tlo.x, ihi.x), __fsub_rn(ilo.x, thi.x)), 0.0f);
-      const float gy = fmaxf(fmaxf(__fsub_rn(tlo.y, ihi.y), __fsub_rn(ilo.y, thi.y)), 0.0f);
-      const float gz = fmaxf(fmaxf(__fsub_rn(tlo.z, ihi.z), __fsub_rn(ilo.z, thi.z)), 0.0f);
-      need = __fmaf_rn(gz, gz, __fmaf_rn(gy, gy, __fmul_rn(gx, gx))) <= P.rc2;
+      const float gx = lgap<PBC>(ilo.x, ihi.x, tlo.x, thi.x, nbox.x, ibox.x), gy = lgap<PBC>(ilo.y, ihi.y, tlo.y, thi.y, nbox.y, ibox.y);
+      const float gz = lgap<PBC>(ilo.z, ihi.z, tlo.z, thi.z, nbox.z, ibox.z);
+      need = __fmaf_rn(gz, gz, __fmaf_rn(gy, gy, __fmul_rn(gx, gx))) <= rc2_box;
     }
     uint32_t todo = __ballot_sync(0xffffffffu, need);
     if (todo == 0u) continue;  // fj of the chunk stays zero
@@ -707,8 +721,9 @@ __device__ __forceinline__ void large_pairs_unit(const LargeTopo& T, const Force
   float* out_i = fpart + (((size_t)r * nslot + BJ) * N + 32 * T.bt * BI) * 3;
   float* out_j = fpart + (((size_t)r * nslot + BI) * N + 32 * T.bt * BJ) * 3;
   __syncthreads();  // the tables (first unit); the previous unit's rows have been read
-  if (pbc) large_rect<MODE, true, COH>(T, P, p, nullptr, S, tab, BI, BJ, nbox, ibox, out_i, out_j, tid);
-  else large_rect<MODE, false, COH>(T, P, p, bbox ? bbox + r * T.nwords * 8 : nullptr, S, tab, BI, BJ, nbox, ibox, out_i, out_j, tid);
+  const float* bb = bbox ? bbox + r * T.nwords * 8 : nullptr;
+  if (pbc) large_rect<MODE, true, COH>(T, P, p, bb, S, tab, BI, BJ, nbox, ibox, out_i, out_j, tid);
+  else large_rect<MODE, false, COH>(T, P, p, bb, S, tab, BI, BJ, nbox, ibox, out_i, out_j, tid);
 }
 
 // grid (nrect, min(R, 65535))

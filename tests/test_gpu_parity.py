@@ -1211,6 +1211,18 @@ def test_large_solute_bundle_of_ala10_chains_vs_oracle():
     F.compute_batch(torch.tensor(posb, device=DEV), s.box, s.forces)
     f_ref, _ = oracle.forces(packed, posb, box=box.reshape(R, 9), **MODES["rf"])
     assert np.abs(s.forces.cpu().numpy() - f_ref).max() / np.abs(f_ref).max() < 1e-5
+    # a box that makes the first and the last chain neighbours THROUGH the boundary (60 A in y, z: chain 5 at (50, 50) is
+    # 10 A from chain 0's image), long in x: the periodic tile-box test (minimum image of the box centres) keeps those
+    # tile pairs and drops the far ones; one replica stays in vacuum
+    box[:, 0, 0], box[:, 1, 1], box[:, 2, 2] = 200.0, 60.0, 60.0
+    box[1] = 0.0
+    s.box[:] = torch.tensor(box, device=DEV)
+    e = F.compute_batch(torch.tensor(pos, device=DEV), s.box, s.forces).cpu().numpy()
+    f_ref, e_ref = oracle.forces(packed, pos, box=box.reshape(R, 9), **MODES["rf"])
+    assert np.abs(s.forces.cpu().numpy() - f_ref).max() / np.abs(f_ref).max() < 1e-5
+    np.testing.assert_allclose(e, e_ref, rtol=1e-9, atol=1e-9)
+    f_vac, _ = oracle.forces(packed, pos[:1], **MODES["rf"])
+    assert np.abs(f_ref[0] - f_vac[0]).max() > 1e-3  # the boundary neighbours do interact
 
 
 def test_large_solute_benchmark_bundle_far_apart_chains_vs_oracle():
