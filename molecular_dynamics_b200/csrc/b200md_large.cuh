@@ -860,7 +860,7 @@ large_pair_energy_kernel(const LargeTopo T, const ForceParams P, const long long
     const float* p = pos + r * N * 3;
     const double bx = box ? (double)__ldg(box + r * 9) : 0.0, by = box ? (double)__ldg(box + r * 9 + 4) : 0.0, bz = box ? (double)__ldg(box + r * 9 + 8) : 0.0;
     const bool pbc = bx != 0.0 || by != 0.0 || bz != 0.0;
-    const float* bb = (MODE == 1 && !pbc && bbox != nullptr) ? bbox + r * T.nwords * 8 : nullptr;
+    const float* bb = (MODE == 1 && bbox != nullptr) ? bbox + r * T.nwords * 8 : nullptr;
     double xd = 0.0, yd = 0.0, zd = 0.0;
     if (live) { xd = (double)__ldg(p + 3 * i); yd = (double)__ldg(p + 3 * i + 1); zd = (double)__ldg(p + 3 * i + 2); }
     double e[2] = {0.0, 0.0};
@@ -868,11 +868,17 @@ large_pair_energy_kernel(const LargeTopo T, const ForceParams P, const long long
       if (bb != nullptr) {  // warp-uniform: the two tile boxes are further apart than the cutoff
         const float4 ilo = __ldg((const float4*)(bb + 8 * ib)), ihi = __ldg((const float4*)(bb + 8 * ib + 4));
         const float4 tlo = __ldg((const float4*)(bb + 8 * jt)), thi = __ldg((const float4*)(bb + 8 * jt + 4));
-        const float gx = fmaxf(fmaxf(__fsub_rn(tlo.x, ihi.x), __fsub_rn(ilo.x, thi.x)), 0.0f);
-        const float gy = fmaxf(fmaxf(__fsub_rn(tlo.y, ihi.y), __fsub_rn(ilo.y, thi.y)), 0.0f);
-        const float gz = fmaxf(fmaxf(__fsub_rn(tlo.z, ihi.z), __fsub_rn(ilo.z, thi.z)), 0.0f);
-        // (the gap components are fp32 lower bounds of the FP64 |d| below: 1 ulp of margin per component covers the rounding)
-        if (__fmaf_rn(gz, gz, __fmaf_rn(gy, gy, __fmul_rn(gx, gx))) > 1.00001f * P.rc2) continue;
+        float gx, gy, gz;
+        if (pbc) {  // minimum image of the box centres (lgap); its own rounding is covered by the 0.1 % margin below
+          gx = lgap<true>(ilo.x, ihi.x, tlo.x, thi.x, -(float)bx, bx != 0.0 ? (float)(1.0 / bx) : 0.0f);
+          gy = lgap<true>(ilo.y, ihi.y, tlo.y, thi.y, -(float)by, by != 0.0 ? (float)(1.0 / by) : 0.0f);
+          gz = lgap<true>(ilo.z, ihi.z, tlo.z, thi.z, -(float)bz, bz != 0.0 ? (float)(1.0 / bz) : 0.0f);
+        } else {
+          gx = lgap<false>(ilo.x, ihi.x, tlo.x, thi.x, 0.0f, 0.0f); gy = lgap<false>(ilo.y, ihi.y, tlo.y, thi.y, 0.0f, 0.0f);
+          gz = lgap<false>(ilo.z, ihi.z, tlo.z, thi.z, 0.0f, 0.0f);
+        }
+        // (the gap components are fp32 lower bounds of the FP64 |d| below: the margin covers their rounding)
+        if (__fmaf_rn(gz, gz, __fmaf_rn(gy, gy, __fmul_rn(gx, gx))) > (pbc ? 1.001f : 1.00001f) * P.rc2) continue;
       }
       const int j = 32 * jt + lane;
       double* sd = sjd[warp];
