@@ -1382,6 +1382,19 @@ def test_compute_batch_host_pipelines_copies_and_matches_compute_batch():
     bad[500, 3, 1] = float("nan")
     with pytest.raises(RuntimeError, match="NaN"):
         F.compute_batch_host(bad, device=DEV)
+    # a solute above 128 atoms through the same call (large-solute kernels, their second stream and workspace under the
+    # chunk stream): 3 deca-alanine chains as one 312-atom topology
+    copies, RL = 3, 40
+    parL = Parameters.from_arrays(g.par.tiled(copies).to_arrays(), device=DEV)
+    shift = np.repeat(np.arange(copies), 104)[None, :, None] * np.array([0.0, 11.0, 11.0])
+    posL = (pos[:RL * copies].reshape(RL, copies * 104, 3) + shift).astype(np.float32)
+    FL = Forces(parL, **MODES["rf"])
+    dpL = torch.tensor(posL, device=DEV)
+    fL_ref = torch.empty_like(dpL)
+    eL_ref = FL.compute_batch(dpL, torch.zeros((RL, 3, 3), device=DEV), fL_ref)
+    for chunks in (1, 3):
+        fL, eL = FL.compute_batch_host(torch.tensor(posL).pin_memory(), chunks=chunks, device=DEV)
+        assert torch.equal(fL, fL_ref.cpu()) and torch.equal(eL, eL_ref.cpu()), chunks
 
 
 def test_report_after_the_last_step_when_niter_is_not_a_multiple():
