@@ -234,6 +234,23 @@ def test_autograd_matches_forces():
     want = -(2.0 * fb + 0.5 * (fl - fd) + (fe - fd))
     got = pos2.grad.cpu().numpy()
     assert np.abs(got - want).max() <= 2e-5 * np.abs(want).max()
+    # the same graph edge above 128 atoms (three chains as one 312-atom topology: the large-solute kernels, term subsets
+    # without pair terms included)
+    gl = load_golden("ala10x3")
+    FL = Forces(gpu_par(gl), cutoff=9.0, rfa=True, switch_dist=7.5)
+    p3 = torch.tensor(gl["pos"][:2], device=DEV, requires_grad=True)
+    s3 = System(312, 2, torch.float, DEV)
+    pot = FL.compute(p3, s3.box, s3.forces, returnDetails=True)
+    loss = sum(3.0 * p["angles"] + 0.25 * p["lj"] + p["electrostatics"] + p["bonds"] for p in pot).sum()
+    loss.backward()
+    m = dict(cutoff=9.0, rfa=True, switch_dist=7.5)
+    fa, _ = oracle.forces(gl.packed, gl["pos"][:2], terms=("angles",), **m)
+    fb, _ = oracle.forces(gl.packed, gl["pos"][:2], terms=("bonds",), **m)
+    fl, _ = oracle.forces(gl.packed, gl["pos"][:2], terms=("lj", "dihedrals", "1-4"), **m)
+    fd, _ = oracle.forces(gl.packed, gl["pos"][:2], terms=("dihedrals",), **m)
+    fe, _ = oracle.forces(gl.packed, gl["pos"][:2], terms=("electrostatics", "dihedrals", "1-4"), **m)
+    want = -(3.0 * fa + fb + 0.25 * (fl - fd) + (fe - fd))
+    assert np.abs(p3.grad.cpu().numpy() - want).max() <= 2e-5 * np.abs(want).max()
 
 
 # ---------------------------------------------------------------------------------------------------
