@@ -394,6 +394,29 @@ __device__ __forceinline__ PhiGeom phi_geometry(const float4* pos, uchar4 q, con
   return g;
 }
 
+// crossC = r23 x crossA;  cos = A.B / (|A||B|),  sin = C.B / (|C||B|),  phi = -atan2(sin, cos)
+__device__ __forceinline__ float phi_angle(const PhiGeom& g) {
+  const float cx = g.r23y * g.az - g.r23z * g.ay, cy = g.r23z * g.ax - g.r23x * g.az, cz = g.r23x * g.ay - g.r23y * g.ax;
+  const float na = sqrtf(g.ax * g.ax + g.ay * g.ay + g.az * g.az), nb = sqrtf(g.bx * g.bx + g.by * g.by + g.bz * g.bz);
+  const float nc = sqrtf(cx * cx + cy * cy + cz * cz);
+  const float cosp = (g.ax * g.bx + g.ay * g.by + g.az * g.bz) / nb / na;
+  const float sinp = (cx * g.bx + cy * g.by + cz * g.bz) / nb / nc;
+  return -atan2f(sinp, cosp);
+}
+// d phi / d x of the atom at position `role` of the quadruple (see dihedral_angles_backward_kernel)
+__device__ __forceinline__ void phi_gradient(const PhiGeom& g, const int role, float& dx, float& dy, float& dz) {
+  const float n23sq = g.r23x * g.r23x + g.r23y * g.r23y + g.r23z * g.r23z, n23 = sqrtf(n23sq);
+  const float f0 = -n23 / (g.ax * g.ax + g.ay * g.ay + g.az * g.az), f3 = n23 / (g.bx * g.bx + g.by * g.by + g.bz * g.bz);
+  const float g0x = f0 * g.ax, g0y = f0 * g.ay, g0z = f0 * g.az, g3x = f3 * g.bx, g3y = f3 * g.by, g3z = f3 * g.bz;
+  const float ff1 = (g.r12x * g.r23x + g.r12y * g.r23y + g.r12z * g.r23z) / n23sq;
+  const float ff2 = (g.r34x * g.r23x + g.r34y * g.r23y + g.r34z * g.r23z) / n23sq;
+  const float sx = ff1 * g0x - ff2 * g3x, sy = ff1 * g0y - ff2 * g3y, sz = ff1 * g0z - ff2 * g3z;
+  if (role == 0) { dx = g0x; dy = g0y; dz = g0z; }
+  else if (role == 1) { dx = -g0x - sx; dy = -g0y - sy; dz = -g0z - sz; }
+  else if (role == 2) { dx = -g3x + sx; dy = -g3y + sy; dz = -g3z + sz; }
+  else { dx = g3x; dy = g3y; dz = g3z; }
+}
+
 __device__ __forceinline__ void stage_replica(float4* spos, float* sbox, const float* pos, const float* box, long long r,
                                               int N, int tid) {
   if (tid < N) {
@@ -415,14 +438,7 @@ __global__ void __launch_bounds__(kThreads) dihedral_angles_kernel(const DevTopo
     stage_replica(spos, sbox, pos, box, r, T.natoms, tid);
     __syncthreads();
     for (int d = tid; d < T.nphi; d += kThreads) {
-      const PhiGeom g = phi_geometry(spos, T.phi_idx[d], sbox);
-      // crossC = r23 x crossA;  cos = A.B / (|A||B|),  sin = C.B / (|C||B|),  phi = -atan2(sin, cos)
-      const float cx = g.r23y * g.az - g.r23z * g.ay, cy = g.r23z * g.ax - g.r23x * g.az, cz = g.r23x * g.ay - g.r23y * g.ax;
-      const float na = sqrtf(g.ax * g.ax + g.ay * g.ay + g.az * g.az), nb = sqrtf(g.bx * g.bx + g.by * g.by + g.bz * g.bz);
-      const float nc = sqrtf(cx * cx + cy * cy + cz * cz);
-      const float cosp = (g.ax * g.bx + g.ay * g.by + g.az * g.bz) / nb / na;
-      const float sinp = (cx * g.bx + cy * g.by + cz * g.bz) / nb / nc;
-      phi[r * T.nphi + d] = -atan2f(sinp, cosp);
+      phi[r * T.nphi + d] = phi_angle(phi_geometry(spos, T.phi_idx[d], sbox));
     }
   }
 }
@@ -451,24 +467,52 @@ __global__ void __launch_bounds__(kThreads) dihedral_angles_backward_kernel(cons
       const int i1 = T.phi_start[tid + 1];
       for (int i = T.phi_start[tid]; i < i1; ++i) {
         const int item = T.phi_items[i], d = item & 0x3fff, role = item >> 14;
-        const PhiGeom g = phi_geometry(spos, T.phi_idx[d], sbox);
-        const float n23sq = g.r23x * g.r23x + g.r23y * g.r23y + g.r23z * g.r23z, n23 = sqrtf(n23sq);
-        const float f0 = -n23 / (g.ax * g.ax + g.ay * g.ay + g.az * g.az), f3 = n23 / (g.bx * g.bx + g.by * g.by + g.bz * g.bz);
-        const float g0x = f0 * g.ax, g0y = f0 * g.ay, g0z = f0 * g.az, g3x = f3 * g.bx, g3y = f3 * g.by, g3z = f3 * g.bz;
-        const float ff1 = (g.r12x * g.r23x + g.r12y * g.r23y + g.r12z * g.r23z) / n23sq;
-        const float ff2 = (g.r34x * g.r23x + g.r34y * g.r23y + g.r34z * g.r23z) / n23sq;
-        const float sx = ff1 * g0x - ff2 * g3x, sy = ff1 * g0y - ff2 * g3y, sz = ff1 * g0z - ff2 * g3z;
         float dx, dy, dz;
-        if (role == 0) { dx = g0x; dy = g0y; dz = g0z; }
-        else if (role == 1) { dx = -g0x - sx; dy = -g0y - sy; dz = -g0z - sz; }
-        else if (role == 2) { dx = -g3x + sx; dy = -g3y + sy; dz = -g3z + sz; }
-        else { dx = g3x; dy = g3y; dz = g3z; }
+        phi_gradient(phi_geometry(spos, T.phi_idx[d], sbox), role, dx, dy, dz);
         const float w = sg[d];
         gx = fmaf(w, dx, gx); gy = fmaf(w, dy, gy); gz = fmaf(w, dz, gz);
       }
       const long long base = (r * T.natoms + tid) * 3;
       grad_pos[base] = gx; grad_pos[base + 1] = gy; grad_pos[base + 2] = gz;
     }
+  }
+}
+
+// The same two kernels for solutes above 128 atoms: the replica does not fit shared memory, every thread reads the four
+// atoms of its dihedral from HBM (one thread per (replica, dihedral) forward, per (replica, atom) backward; same arithmetic).
+__device__ __forceinline__ PhiGeom large_phi_geometry(const float* __restrict__ p, const int4 q, const float* bx) {
+  float4 lp[4];
+  const int a[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int k = 0; k < 4; ++k) lp[k] = make_float4(p[3 * a[k]], p[3 * a[k] + 1], p[3 * a[k] + 2], 0.0f);
+  return phi_geometry(lp, make_uchar4(0, 1, 2, 3), bx);
+}
+__global__ void large_dihedral_angles_kernel(const LargeTopo T, const long long R, const float* __restrict__ pos,
+                                             const float* __restrict__ box, float* __restrict__ phi) {
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < R * T.ndih; g += (long long)gridDim.x * blockDim.x) {
+    const long long r = g / T.ndih;
+    const int d = (int)(g - r * T.ndih);
+    const float bx[3] = {box ? __ldg(box + r * 9) : 0.0f, box ? __ldg(box + r * 9 + 4) : 0.0f, box ? __ldg(box + r * 9 + 8) : 0.0f};
+    phi[g] = phi_angle(large_phi_geometry(pos + r * T.natoms * 3, __ldg(T.dih_idx + d), bx));
+  }
+}
+__global__ void large_dihedral_angles_backward_kernel(const LargeTopo T, const long long R, const float* __restrict__ pos,
+                                                      const float* __restrict__ box, const float* __restrict__ grad_phi,
+                                                      float* __restrict__ grad_pos) {
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < R * T.natoms; g += (long long)gridDim.x * blockDim.x) {
+    const long long r = g / T.natoms;
+    const int a = (int)(g - r * T.natoms);
+    const float bx[3] = {box ? __ldg(box + r * 9) : 0.0f, box ? __ldg(box + r * 9 + 4) : 0.0f, box ? __ldg(box + r * 9 + 8) : 0.0f};
+    float gx = 0.0f, gy = 0.0f, gz = 0.0f;
+    const int i1 = __ldg(T.phi_start + a + 1);
+    for (int i = __ldg(T.phi_start + a); i < i1; ++i) {
+      const int item = __ldg(T.phi_items + i), d = item >> 2, role = item & 3;
+      float dx, dy, dz;
+      phi_gradient(large_phi_geometry(pos + r * T.natoms * 3, __ldg(T.dih_idx + d), bx), role, dx, dy, dz);
+      const float w = grad_phi[r * T.ndih + d];
+      gx = fmaf(w, dx, gx); gy = fmaf(w, dy, gy); gz = fmaf(w, dz, gz);
+    }
+    grad_pos[3 * g] = gx; grad_pos[3 * g + 1] = gy; grad_pos[3 * g + 2] = gz;
   }
 }
 
@@ -1396,7 +1440,20 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
     }
     if (win_slot.empty()) { win_atoms.push_back(make_int4(0, 0, 0, 0)); win_prm.push_back(make_float4(0.f, 0.f, 0.f, 0.f)); win_slot.push_back(make_ushort4(0xffff, 0xffff, 0xffff, 0xffff)); }
   }
+  // atom-major lists of the dihedrals an atom sits in (dihedral << 2 | role): the dihedral-angle backward gathers by atom
+  std::vector<int> phi_start(N + 1, 0), phi_items;
+  {
+    std::vector<int> cnt(N + 1, 0);
+    for (int q = 0; q < d->ndihedrals; ++q)
+      for (int role = 0; role < 4; ++role) ++cnt[d->dihedral_idx[4 * q + role] + 1];
+    for (int a = 0; a < N; ++a) phi_start[a + 1] = phi_start[a] + cnt[a + 1];
+    phi_items.assign(std::max(1, phi_start[N]), 0);
+    std::vector<int> cur(phi_start.begin(), phi_start.end() - 1);
+    for (int q = 0; q < d->ndihedrals; ++q)
+      for (int role = 0; role < 4; ++role) phi_items[cur[d->dihedral_idx[4 * q + role]]++] = (q << 2) | role;
+  }
   BlobBuilder B;
+  const size_t o_phs = B.add(phi_start), o_phit = B.add(phi_items);
   const size_t o_wst = B.add(win_start), o_wat = B.add(win_atoms), o_wpr = B.add(win_prm), o_wke = B.add(win_kend), o_wsl = B.add(win_slot), o_gst = B.add(gstart), o_wlo = B.add(win_lo), o_wn = B.add(win_n);
   const size_t o_type = B.add(atype), o_q = B.add(charge), o_m = B.add(mass), o_a = B.add(t12a), o_b = B.add(t6b), o_mask = B.add(mask),
                o_bi = B.add(bidx), o_bp = B.add(bprm), o_ai = B.add(aidx), o_ap = B.add(aprm), o_dq = B.add(dq), o_ds = B.add(ds),
@@ -1419,6 +1476,7 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   L.win_start = (const int*)(base + o_wst); L.win_atoms = (const int4*)(base + o_wat); L.win_prm = (const float4*)(base + o_wpr); L.win_kend = (const int4*)(base + o_wke); L.win_slot = (const ushort4*)(base + o_wsl);
   L.gstart = (const int*)(base + o_gst); L.nwin = nwin; L.win_slots_max = win_slots_max; L.halo_max = halo_max;
   L.win_lo = (const int*)(base + o_wlo); L.win_n = (const int*)(base + o_wn);
+  L.phi_start = (const int*)(base + o_phs); L.phi_items = (const int*)(base + o_phit);
   L.nblk = (W + kLBT - 1) / kLBT;  // pair rectangles over nblk blocks of bt <= kLBT tiles, as even as the tile count allows
   L.bt = (W + L.nblk - 1) / L.nblk;
   L.nbonds = d->nbonds; L.nangles = d->nangles; L.ndih = d->ndihedrals; L.n14 = d->n14; L.nimp = d->nimpropers;
@@ -1709,13 +1767,21 @@ extern "C" int b200md_constrain(const b200md_topology* topo, int64_t R, float* p
   return B200MD_OK;
 }
 
-extern "C" int b200md_topology_ndihedrals(const b200md_topology* topo) { return topo ? topo->dev.nphi : -1; }
+extern "C" int b200md_topology_ndihedrals(const b200md_topology* topo) { return topo ? (topo->large ? topo->ldev.ndih : topo->dev.nphi) : -1; }
 
 extern "C" int b200md_dihedral_angles(const b200md_topology* topo, int64_t R, const float* pos, const float* box,
                                       float* phi, void* stream) {
   if (!topo || !pos || !phi) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
   if (R < 0) return fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica count");
-  if (topo->large) return fail(B200MD_ERR_UNSUPPORTED, "the dihedral-angle kernels need natoms <= 128");
+  if (topo->large) {
+    if (R == 0 || topo->ldev.ndih == 0) return B200MD_OK;
+    B200MD_ON_DEVICE(topo->device);
+    const long long n = (long long)R * topo->ldev.ndih;
+    large_dihedral_angles_kernel<<<(unsigned)std::min<long long>((n + 255) / 256, (long long)topo->num_sms * 32), 256, 0, (cudaStream_t)stream>>>(topo->ldev, R, pos, box, phi);
+    g_launches.fetch_add(1);
+    CUDA_TRY(cudaGetLastError());
+    return B200MD_OK;
+  }
   if (R == 0 || topo->dev.nphi == 0) return B200MD_OK;
   B200MD_ON_DEVICE(topo->device);
   const int grid = (int)std::min<long long>(R, (long long)topo->num_sms * 16);
@@ -1729,7 +1795,16 @@ extern "C" int b200md_dihedral_angles_backward(const b200md_topology* topo, int6
                                                const float* grad_phi, float* grad_pos, void* stream) {
   if (!topo || !pos || !grad_phi || !grad_pos) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
   if (R < 0) return fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica count");
-  if (topo->large) return fail(B200MD_ERR_UNSUPPORTED, "the dihedral-angle kernels need natoms <= 128");
+  if (topo->large) {
+    if (R == 0) return B200MD_OK;
+    B200MD_ON_DEVICE(topo->device);
+    const long long n = (long long)R * topo->ldev.natoms;
+    large_dihedral_angles_backward_kernel<<<(unsigned)std::min<long long>((n + 255) / 256, (long long)topo->num_sms * 32), 256, 0, (cudaStream_t)stream>>>(
+        topo->ldev, R, pos, box, grad_phi, grad_pos);
+    g_launches.fetch_add(1);
+    CUDA_TRY(cudaGetLastError());
+    return B200MD_OK;
+  }
   if (topo->dev.nphi > 512) return fail(B200MD_ERR_UNSUPPORTED, "dihedral-angle backward holds at most 512 dihedrals per replica");
   if (R == 0) return B200MD_OK;
   B200MD_ON_DEVICE(topo->device);

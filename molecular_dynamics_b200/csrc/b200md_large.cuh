@@ -76,6 +76,8 @@ struct LargeTopo {
   const int* win_n;          // [nwin] how many atoms from win_lo they span, 0 when more than kLHalo (then read from HBM)
   int nwin, win_slots_max, halo_max;  // windows; largest slot count / staged span of a window (shared memory = 12 bytes x each)
   int bt, nblk;                       // pair rectangles: tiles per atom block (<= kLBT), number of blocks
+  const int* phi_start;               // [natoms + 1] dihedral-angle backward: items of atom a are [phi_start[a], phi_start[a + 1])
+  const int* phi_items;               // dihedral << 2 | role
 };
 constexpr int kLWin = 64, kLHalo = 320;
 
