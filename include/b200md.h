@@ -24,8 +24,9 @@ extern "C" {
 #define B200MD_MAX_ATOMS 128   /* one CTA per replica; atoms live in 4 x 32-lane blocks          */
 /* Above B200MD_MAX_ATOMS a topology takes the large-solute kernels (the adk-1.0.prmtop system named at
  * V_Calculations/Test-10_diALA/potcalc.py:114 is the reference's example): same entry points and semantics; the replica
- * state lives in HBM, pairs run as 32 x 32 tiles with a dense exclusion bit matrix, one launch sequence per MD step.
- * Not available there: rigid_bonds, b200md_constrain, b200md_dihedral_angles* (B200MD_ERR_UNSUPPORTED). */
+ * state lives in HBM, pairs run half-shell over rectangles of 32-atom tiles with a dense exclusion bit matrix, bonded
+ * terms by windows of 64 atoms, three launches per MD step (one cooperative launch per run of steps for few replicas).
+ * Every entry point works there except b200md_integrate_noalloc (B200MD_ERR_UNSUPPORTED). */
 #define B200MD_MAX_ATOMS_LARGE 32768
 #define B200MD_NUM_ENERGIES 8  /* order of Forces.energies + "external" (forces.py:40-50,100)     */
 

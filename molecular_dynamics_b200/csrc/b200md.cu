@@ -1303,7 +1303,6 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   topo->natoms = N;
   topo->large = true;
   topo->dev.natoms = N; topo->dev.ntypes = NT;
-  topo->dev.ncons = -1;  // rigid bonds are a feature of the fused one-CTA-per-replica integrator
   topo->dev.nphi = d->ndihedrals;
   const int W = (N + 31) / 32, NP = 32 * W;
   topo->mask_words = W;
@@ -1452,7 +1451,46 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
     for (int q = 0; q < d->ndihedrals; ++q)
       for (int role = 0; role < 4; ++role) phi_items[cur[d->dihedral_idx[4 * q + role]]++] = (q << 2) | role;
   }
+  // rigid X-H bonds: groups of a heavy atom and its 1 .. 3 hydrogens (the rule of the on-chip path: a hydrogen is tied
+  // through its shortest bond row)
+  std::vector<int4> cgroup;
+  std::vector<float4> cdist2, cweight;
+  int ncons = 0, cmax = 0;
+  {
+    auto is_h = [&](int a) { return d->mass && d->mass[a] > 0.5f && d->mass[a] < 3.5f; };
+    std::vector<int> partner(N, -1);
+    std::vector<float> req(N, 0.0f);
+    for (int b = 0; b < d->nbonds; ++b) {
+      const int i = d->bond_idx[2 * b], j = d->bond_idx[2 * b + 1];
+      const float r0 = d->bond_prm[2 * b + 1];
+      for (int side = 0; side < 2; ++side) {
+        const int hh = side ? j : i, other = side ? i : j;
+        if (is_h(hh) && (partner[hh] < 0 || r0 < req[hh])) { partner[hh] = other; req[hh] = r0; }
+      }
+    }
+    std::vector<std::vector<int>> kids(N);
+    for (int a = 0; a < N && ncons >= 0; ++a) {
+      if (partner[a] < 0) continue;
+      const int pa = partner[a];
+      if (is_h(pa) || kids[pa].size() >= 3 || !(req[a] > 0.0f)) { ncons = -1; break; }
+      kids[pa].push_back(a);
+      ncons += 1;
+    }
+    if (ncons > 0)
+      for (int pa = 0; pa < N; ++pa) {
+        const int n = (int)kids[pa].size();
+        if (n == 0) continue;
+        int hh[3] = {pa, pa, pa};
+        float dd[3] = {1.0f, 1.0f, 1.0f}, ww[3] = {1.0f, 1.0f, 1.0f};
+        for (int k = 0; k < n; ++k) { hh[k] = kids[pa][k]; dd[k] = req[hh[k]] * req[hh[k]]; ww[k] = 1.0f / d->mass[hh[k]]; }
+        cgroup.push_back(make_int4(pa | (n << 24), hh[0], hh[1], hh[2]));
+        cdist2.push_back(make_float4(dd[0], dd[1], dd[2], 0.0f));
+        cweight.push_back(make_float4(1.0f / d->mass[pa], ww[0], ww[1], ww[2]));
+        cmax = std::max(cmax, n);
+      }
+  }
   BlobBuilder B;
+  const size_t o_cg = B.add(cgroup), o_cd = B.add(cdist2), o_cw = B.add(cweight);
   const size_t o_phs = B.add(phi_start), o_phit = B.add(phi_items);
   const size_t o_wst = B.add(win_start), o_wat = B.add(win_atoms), o_wpr = B.add(win_prm), o_wke = B.add(win_kend), o_wsl = B.add(win_slot), o_gst = B.add(gstart), o_wlo = B.add(win_lo), o_wn = B.add(win_n);
   const size_t o_type = B.add(atype), o_q = B.add(charge), o_m = B.add(mass), o_a = B.add(t12a), o_b = B.add(t6b), o_mask = B.add(mask),
@@ -1477,6 +1515,9 @@ static b200md_topology* create_large(const b200md_topology_desc* d, int device) 
   L.gstart = (const int*)(base + o_gst); L.nwin = nwin; L.win_slots_max = win_slots_max; L.halo_max = halo_max;
   L.win_lo = (const int*)(base + o_wlo); L.win_n = (const int*)(base + o_wn);
   L.phi_start = (const int*)(base + o_phs); L.phi_items = (const int*)(base + o_phit);
+  L.ngroups = (int)cgroup.size(); L.ncons = ncons; L.cmax = cmax;
+  topo->dev.ncons = ncons;  // (b200md_topology_num_constraints, the entry checks; the large-solute kernels read LargeTopo)
+  L.cgroup = (const int4*)(base + o_cg); L.cdist2 = (const float4*)(base + o_cd); L.cweight = (const float4*)(base + o_cw);
   L.nblk = (W + kLBT - 1) / kLBT;  // pair rectangles over nblk blocks of bt <= kLBT tiles, as even as the tile count allows
   L.bt = (W + L.nblk - 1) / L.nblk;
   L.nbonds = d->nbonds; L.nangles = d->nangles; L.ndih = d->ndihedrals; L.n14 = d->n14; L.nimp = d->nimpropers;
@@ -1521,10 +1562,11 @@ struct LargeWork {
   double* partial = nullptr; double* energies = nullptr; double* ekin = nullptr; double* smd = nullptr;
   float* bbox = nullptr;
   float* fpart = nullptr;  // [R][nblk + 1][natoms][3] partial force rows (large_pairs_kernel, large_bonded_forces_kernel)
+  float* pos_old = nullptr;  // rigid bonds: x(t), the bond vectors SHAKE works along
   int nbonded_blocks = 0, npart = 0, nek = 0;
 };
 
-static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, bool smd, LargeWork& w) {
+static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, bool smd, LargeWork& w, bool rigid = false) {
   const LargeTopo& L = topo->ldev;
   const long long items = (long long)L.nbonds + L.nangles + L.ndih + L.n14 + L.nimp;
   // bonded CTAs per replica: a function of the topology only (4 items per thread, at most 64 CTAs), so that the order of the
@@ -1539,7 +1581,8 @@ static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, 
   const size_t b_e = integrator ? up(sizeof(double) * (size_t)R * B200MD_NUM_ENERGIES) : 0, b_k = integrator ? up(sizeof(double) * (size_t)R * w.nek) : 0;
   const size_t b_s = (integrator && smd) ? up(sizeof(double) * 2 * (size_t)R) : 0;
   const size_t b_b = up(sizeof(float) * 8 * (size_t)R * L.nwords);
-  const size_t total = b_f + b_p + b_e + b_k + b_s + b_b;
+  const size_t b_o = rigid ? up(sizeof(float) * 3 * (size_t)R * L.natoms) : 0;  // x(t) for SHAKE
+  const size_t total = b_f + b_p + b_e + b_k + b_s + b_b + b_o;
   if (topo->ws != nullptr && topo->ws_stream != w.st) CUDA_TRY(cudaStreamSynchronize(topo->ws_stream));
   if (total > topo->ws_bytes) {
     if (topo->ws != nullptr) { CUDA_TRY(cudaStreamSynchronize(topo->ws_stream)); cudaFree(topo->ws); topo->ws = nullptr; topo->ws_bytes = 0; }
@@ -1551,6 +1594,7 @@ static int large_alloc(const b200md_topology* topo, int64_t R, bool integrator, 
   w.fpart = (float*)base; base += b_f;
   w.partial = (double*)base; base += b_p;
   w.bbox = (float*)base; base += b_b;
+  w.pos_old = rigid ? (float*)base : nullptr; base += b_o;
   if (integrator) {
     w.energies = (double*)base; base += b_e;
     w.ekin = (double*)base; base += b_k;
@@ -1651,11 +1695,11 @@ static int large_forces_compute(const b200md_topology* topo, const ForceParams& 
 // Integrator.step(niter) for large solutes: the upstream sequence as separate launches per step (the state lives in HBM)
 static int large_integrate(const b200md_topology* topo, const ForceParams& P, const StepParams& I, int64_t R, float* pos,
                            float* vel, float* forces, const float* box, double* observables, float* snapshots,
-                           uint32_t* status, void* stream) {
+                           uint32_t* status, void* stream, bool rigid) {
   const LargeTopo& L = topo->ldev;
   LargeWork w;
   w.st = (cudaStream_t)stream;
-  int rc = large_alloc(topo, R, true, P.smd_on != 0, w);
+  int rc = large_alloc(topo, R, true, P.smd_on != 0, w, rigid);
   if (rc) return rc;
   cudaStream_t st = w.st;
   if (status) CUDA_TRY(cudaMemsetAsync(status, 0, sizeof(uint32_t) * (size_t)R, st));
@@ -1678,12 +1722,22 @@ static int large_integrate(const b200md_topology* topo, const ForceParams& P, co
   const long long resident = (long long)topo->num_sms * topo->occ_steps[mode];
   bool persist = resident > 0 && 2 * units <= resident;
   if (const char* e = getenv("B200MD_LARGE_PERSISTENT")) persist = atoi(e) != 0 && resident > 0;  // (read per call: tests toggle it)
+  // Rigid X-H bonds: SHAKE sits between the drift and the force evaluation, RATTLE behind the second half-kick, so the
+  // half-kicks of neighbouring steps are not fused and every step is its own launches (first half-kick, SHAKE, forces,
+  // second half-kick, RATTLE).
+  if (rigid) persist = false;
+  const unsigned gcons = rigid ? (unsigned)std::min<long long>(((long long)R * L.ngroups + 127) / 128, (long long)topo->num_sms * 32) : 0;
   for (int s = 0; s < I.nsteps; ++s) {
     const unsigned long long gstep = I.step0 + (unsigned long long)s;
     const bool report = is_report(s);
     if (!fused_prev) {
+      if (rigid) CUDA_TRY(cudaMemcpyAsync(w.pos_old, pos, frame, cudaMemcpyDeviceToDevice, st));
       large_vv1_kernel<<<(unsigned)((natom + 255) / 256), 256, 0, st>>>(L, I.dt, R, pos, vel, forces);
       g_launches.fetch_add(1);
+      if (rigid) {
+        large_shake_kernel<<<gcons, 128, 0, st>>>(L, R, w.pos_old, pos, vel, 1.0f / I.dt, 1, status);
+        g_launches.fetch_add(1);
+      }
     }
     bool boxes_ready = fused_prev && want_bbox;
     if (persist && !report) {
@@ -1719,11 +1773,19 @@ static int large_integrate(const b200md_topology* topo, const ForceParams& P, co
     rc = large_forces(topo, P, R, pos, box, forces, w.energies, status, center, report, w, boxes_ready, false);
     if (rc) return rc;
     const bool snap = I.snapshot_every > 0 && snapshots != nullptr && (s + 1) % I.snapshot_every == 0;
-    const bool fuse = s + 1 < I.nsteps && !snap;
-    large_vv2_kernel<<<dim3(w.nek, (unsigned)std::min<int64_t>(R, 65535)), 256, 0, st>>>(L, I, gstep, R, vel, forces, pos, report ? w.ekin : nullptr,
+    const bool fuse = s + 1 < I.nsteps && !snap && !rigid;
+    large_vv2_kernel<<<dim3(w.nek, (unsigned)std::min<int64_t>(R, 65535)), 256, 0, st>>>(L, I, gstep, R, vel, forces, pos, (report && !rigid) ? w.ekin : nullptr,
                                                                                        status, fuse ? 1 : 0, (fuse && want_bbox) ? w.bbox : nullptr, w.fpart, pairs_on ? 0 : L.nblk);
     fused_prev = fuse;
     g_launches.fetch_add(1);
+    if (rigid) {
+      large_rattle_kernel<<<gcons, 128, 0, st>>>(L, R, pos, vel);
+      g_launches.fetch_add(1);
+      if (report) {  // the kinetic energy of the record is that of the constrained velocities
+        large_ekin_kernel<<<dim3(w.nek, (unsigned)std::min<int64_t>(R, 65535)), 256, 0, st>>>(L, R, vel, w.ekin);
+        g_launches.fetch_add(1);
+      }
+    }
     if (report && observables != nullptr) {
       const long long slot = I.energy_every > 0 ? s / I.energy_every : 0;
       large_observe_kernel<<<(unsigned)((R + 127) / 128), 128, 0, st>>>(R, w.energies, w.ekin, w.nek, w.smd,
@@ -1755,11 +1817,20 @@ extern "C" int b200md_constrain(const b200md_topology* topo, int64_t R, float* p
                                 void* stream) {
   if (!topo || !pos) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
   if (R < 0) return fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica count");
-  if (topo->large) return fail(B200MD_ERR_UNSUPPORTED, "rigid bonds need natoms <= 128");
   if (topo->dev.ncons < 0)
     return fail(B200MD_ERR_UNSUPPORTED, "rigid_bonds: a hydrogen is bonded to a hydrogen, or a heavy atom carries more than 3");
   if (R == 0 || topo->dev.ncons == 0) return B200MD_OK;
   B200MD_ON_DEVICE(topo->device);
+  if (topo->large) {  // one thread per (replica, group): four SHAKE sweeps about the present bond vectors, then RATTLE
+    const LargeTopo& L = topo->ldev;
+    if (status) CUDA_TRY(cudaMemsetAsync(status, 0, sizeof(uint32_t) * (size_t)R, (cudaStream_t)stream));
+    const unsigned gb = (unsigned)std::min<long long>(((long long)R * L.ngroups + 127) / 128, (long long)topo->num_sms * 32);
+    large_shake_kernel<<<gb, 128, 0, (cudaStream_t)stream>>>(L, R, pos, pos, nullptr, 0.0f, 4, status);
+    if (vel) large_rattle_kernel<<<gb, 128, 0, (cudaStream_t)stream>>>(L, R, pos, vel);
+    g_launches.fetch_add(vel ? 2 : 1);
+    CUDA_TRY(cudaGetLastError());
+    return B200MD_OK;
+  }
   const int grid = (int)std::min<long long>(R, (long long)topo->num_sms * 8);
   constrain_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(topo->dev, R, pos, vel, status);
   g_launches.fetch_add(1);
@@ -1928,8 +1999,6 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
   if (!topo || !io || !pos || !vel || !forces) return fail(B200MD_ERR_INVALID_ARGUMENT, "null argument");
   if (R < 0 || io->nsteps < 0) return fail(B200MD_ERR_INVALID_ARGUMENT, "negative replica or step count");
   if (R == 0 || io->nsteps == 0) return B200MD_OK;
-  if (io->rigid_bonds != 0 && topo->large)
-    return fail(B200MD_ERR_UNSUPPORTED, "rigid_bonds needs natoms <= 128 (the constraint solve lives in the fused one-CTA-per-replica kernel)");
   if (io->rigid_bonds != 0 && topo->dev.ncons < 0)
     return fail(B200MD_ERR_UNSUPPORTED, "rigid_bonds: a hydrogen is bonded to a hydrogen, or a heavy atom carries more than 3");
   ForceParams P;
@@ -1941,7 +2010,9 @@ extern "C" int b200md_integrate(const b200md_topology* topo, const b200md_force_
   I.seed = io->seed; I.step0 = io->step0; I.replica0 = io->replica0;
   I.nsteps = io->nsteps; I.energy_every = io->energy_every; I.snapshot_every = io->snapshot_every;
   B200MD_ON_DEVICE(topo->device);
-  if (topo->large) return large_integrate(topo, P, I, R, pos, vel, forces, box, observables, snapshots, status, stream);
+  if (topo->large)
+    return large_integrate(topo, P, I, R, pos, vel, forces, box, observables, snapshots, status, stream,
+                           io->rigid_bonds != 0 && topo->ldev.ncons > 0);
   const int mode = P.has_cutoff ? 1 : 0;
   cudaStream_t st = (cudaStream_t)stream;
   const bool rigid = io->rigid_bonds != 0 && T.ncons > 0;

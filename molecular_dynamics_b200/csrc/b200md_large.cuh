@@ -23,6 +23,9 @@
 //                               from the fp32 positions, item- / tile-centric, no forces; they only read the positions
 //                               and run on the second stream; large_finish_kernel sums the per-CTA partials in index order;
 //   large_bbox_kernel, large_observe_kernel   tile boxes of a Forces.compute call; the observable record.
+//   large_shake_kernel, large_rattle_kernel, large_ekin_kernel   rigid X-H bonds: one thread per hydrogen group (the group
+//                               solvers of the on-chip path on registers), the kinetic energy of the constrained velocities;
+//   large_steps_kernel          few replicas: runs of steps between two report steps as ONE cooperative launch.
 // The Langevin noise is the same Philox stream as the fused kernel (keyed by seed, global replica, atom, global step).
 // Energies are FP64 because the lj / electrostatics sums cancel too far for fp32 pair terms to meet the 1e-6-per-term
 // contract; forces are fp32 like the on-chip kernels.  Results are bit-reproducible and do not depend on
@@ -78,6 +81,11 @@ struct LargeTopo {
   int bt, nblk;                       // pair rectangles: tiles per atom block (<= kLBT), number of blocks
   const int* phi_start;               // [natoms + 1] dihedral-angle backward: items of atom a are [phi_start[a], phi_start[a + 1])
   const int* phi_items;               // dihedral << 2 | role
+  // rigid X-H bonds (SHAKE / RATTLE): groups of a heavy atom and its 1 .. 3 hydrogens
+  int ngroups, ncons, cmax;           // groups, constraints (-1: a group the solvers cannot hold), largest group
+  const int4* cgroup;                 // (parent | n << 24, h0, h1, h2)
+  const float4* cdist2;               // squared bond lengths
+  const float4* cweight;              // 1 / mass of (parent, h0, h1, h2)
 };
 constexpr int kLWin = 64, kLHalo = 320;
 
@@ -1086,6 +1094,194 @@ large_steps_kernel(const LargeTopo T, const ForceParams P, const StepParams I, c
       if (fuse && bbox != nullptr) large_tile_box_store(T, bbox, r, a, tid & 31, lo, hi);
     }
     grid.sync();
+  }
+}
+
+// ---- rigid X-H bonds for solutes above 128 atoms --------------------------------------------------------------------------
+// The group solvers of b200md_forces.cuh (Newton iterations on the multipliers of a heavy atom's 1 .. 3 X-H bonds, see
+// shake_group / rattle_group there) on registers: a group's atoms belong to no other group, so ONE thread loads the
+// group from HBM, solves, and writes its atoms back -- no barrier, no shared memory.  K = 1 or 3 as on chip.
+struct LGroup { int p, n, h[3]; float d2[3], wp, wh[3]; };
+__device__ __forceinline__ LGroup lgroup_load(const LargeTopo& T, const int gi) {
+  const int4 g = __ldg(T.cgroup + gi);
+  const float4 d2v = __ldg(T.cdist2 + gi), wv = __ldg(T.cweight + gi);
+  LGroup G;
+  G.p = g.x & 0xffffff; G.n = g.x >> 24;
+  G.h[0] = g.y; G.h[1] = g.z; G.h[2] = g.w;
+  G.d2[0] = d2v.x; G.d2[1] = d2v.y; G.d2[2] = d2v.z;
+  G.wp = wv.x; G.wh[0] = wv.y; G.wh[1] = wv.z; G.wh[2] = wv.w;
+  return G;
+}
+// s_k = x_p(t) - x_hk(t), u_k = x'_p - x'_hk (unconstrained).  Out: displacements dp of the parent, dh_k of hydrogen k that
+// restore |u_k + dp - dh_k|^2 = d_k^2 along the old bond vectors.  Returns false beyond kShakeTol.
+template <int K>
+__device__ __forceinline__ bool lshake_solve(const LGroup& G, const float (&sx)[K], const float (&sy)[K], const float (&sz)[K],
+                                             const float (&ux)[K], const float (&uy)[K], const float (&uz)[K], float (&dp)[3],
+                                             float (&dhx)[K], float (&dhy)[K], float (&dhz)[K]) {
+  const int n = G.n;
+  const float wp = G.wp;
+  float lam[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) lam[k] = 0.0f;
+  float dpx = 0.0f, dpy = 0.0f, dpz = 0.0f;
+#pragma unroll
+  for (int it = 0; it < kShakeNewtonIters; ++it) {
+    float A[K][K], b[K], rx[K], ry[K], rz[K], dl[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      rx[k] = fmaf(G.wh[k] * lam[k], sx[k], ux[k] + dpx);
+      ry[k] = fmaf(G.wh[k] * lam[k], sy[k], uy[k] + dpy);
+      rz[k] = fmaf(G.wh[k] * lam[k], sz[k], uz[k] + dpz);
+      b[k] = k < n ? G.d2[k] - (rx[k] * rx[k] + ry[k] * ry[k] + rz[k] * rz[k]) : 0.0f;
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k)
+#pragma unroll
+      for (int l = 0; l < K; ++l) {
+        const float sr = rx[k] * sx[l] + ry[k] * sy[l] + rz[k] * sz[l];
+        A[k][l] = 2.0f * sr * (k == l ? wp + G.wh[k] : wp);
+        if (k >= n || l >= n) A[k][l] = k == l ? 1.0f : 0.0f;
+      }
+    solve_k<K>(A, b, dl);
+    dpx = 0.0f; dpy = 0.0f; dpz = 0.0f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      lam[k] += dl[k];
+      dpx = fmaf(wp * lam[k], sx[k], dpx); dpy = fmaf(wp * lam[k], sy[k], dpy); dpz = fmaf(wp * lam[k], sz[k], dpz);
+    }
+  }
+  bool ok = true;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    dhx[k] = -G.wh[k] * lam[k] * sx[k]; dhy[k] = -G.wh[k] * lam[k] * sy[k]; dhz[k] = -G.wh[k] * lam[k] * sz[k];
+    if (k < n) {
+      const float rx = ux[k] + (dpx - dhx[k]), ry = uy[k] + (dpy - dhy[k]), rz = uz[k] + (dpz - dhz[k]);
+      ok = ok && fabsf(G.d2[k] - (rx * rx + ry * ry + rz * rz)) <= kShakeTol * G.d2[k];
+    }
+  }
+  dp[0] = dpx; dp[1] = dpy; dp[2] = dpz;
+  return ok;
+}
+// SHAKE after the first half-kick + drift: pold = x(t), pos = unconstrained x(t + dt) -> constrained, vel += d / dt.
+// `sweeps` > 1 (b200md_constrain): pold == pos, the linearisation point follows the projection.
+template <int K>
+__device__ __forceinline__ bool lshake_group(const LargeTopo& T, const int gi, const float* pold, float* pos, float* vel,
+                                             const float inv_dt, const int sweeps) {
+  const LGroup G = lgroup_load(T, gi);
+  float xo[K + 1][3], xn[K + 1][3];  // row 0: the parent, 1 ..: the hydrogens (an unused row repeats the parent)
+#pragma unroll
+  for (int k = 0; k <= K; ++k) {
+    const int a = k == 0 ? G.p : (k - 1 < G.n ? G.h[k - 1] : G.p);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) { xo[k][c] = pold[3 * a + c]; xn[k][c] = pos[3 * a + c]; }
+  }
+  bool ok = true;
+  float tot[K + 1][3];
+#pragma unroll
+  for (int k = 0; k <= K; ++k) tot[k][0] = tot[k][1] = tot[k][2] = 0.0f;
+  for (int sweep = 0; sweep < sweeps; ++sweep) {
+    float sx[K], sy[K], sz[K], ux[K], uy[K], uz[K], dp[3], dhx[K], dhy[K], dhz[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      sx[k] = xo[0][0] - xo[k + 1][0]; sy[k] = xo[0][1] - xo[k + 1][1]; sz[k] = xo[0][2] - xo[k + 1][2];
+      ux[k] = xn[0][0] - xn[k + 1][0]; uy[k] = xn[0][1] - xn[k + 1][1]; uz[k] = xn[0][2] - xn[k + 1][2];
+    }
+    ok = lshake_solve<K>(G, sx, sy, sz, ux, uy, uz, dp, dhx, dhy, dhz);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) { xn[0][c] += dp[c]; tot[0][c] += dp[c]; }
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      xn[k + 1][0] += dhx[k]; xn[k + 1][1] += dhy[k]; xn[k + 1][2] += dhz[k];
+      tot[k + 1][0] += dhx[k]; tot[k + 1][1] += dhy[k]; tot[k + 1][2] += dhz[k];
+    }
+    if (sweeps > 1) {
+#pragma unroll
+      for (int k = 0; k <= K; ++k)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) xo[k][c] = xn[k][c];
+    }
+  }
+#pragma unroll
+  for (int k = 0; k <= K; ++k) {
+    if (k == 0 || k - 1 < G.n) {
+      const int a = k == 0 ? G.p : G.h[k - 1];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        pos[3 * a + c] = xn[k][c];
+        if (vel != nullptr && inv_dt != 0.0f) vel[3 * a + c] = fmaf(tot[k][c], inv_dt, vel[3 * a + c]);
+      }
+    }
+  }
+  return ok;
+}
+// RATTLE: takes the components along the rigid bonds out of the group's velocities (positions hold the constraints)
+template <int K>
+__device__ __forceinline__ void lrattle_group(const LargeTopo& T, const int gi, const float* pos, float* vel) {
+  const LGroup G = lgroup_load(T, gi);
+  const int n = G.n;
+  const float wp = G.wp;
+  float vp[3] = {vel[3 * G.p], vel[3 * G.p + 1], vel[3 * G.p + 2]};
+  float rx[K], ry[K], rz[K], vx[K], vy[K], vz[K], A[K][K], b[K], mu[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const int a = k < n ? G.h[k] : G.p;
+    rx[k] = pos[3 * G.p] - pos[3 * a]; ry[k] = pos[3 * G.p + 1] - pos[3 * a + 1]; rz[k] = pos[3 * G.p + 2] - pos[3 * a + 2];
+    vx[k] = vel[3 * a]; vy[k] = vel[3 * a + 1]; vz[k] = vel[3 * a + 2];
+    b[k] = rx[k] * (vp[0] - vx[k]) + ry[k] * (vp[1] - vy[k]) + rz[k] * (vp[2] - vz[k]);
+  }
+#pragma unroll
+  for (int k = 0; k < K; ++k)
+#pragma unroll
+    for (int l = 0; l < K; ++l) {
+      const float rr = rx[k] * rx[l] + ry[k] * ry[l] + rz[k] * rz[l];
+      A[k][l] = rr * (k == l ? wp + G.wh[k] : wp);
+      if (k >= n || l >= n) A[k][l] = k == l ? 1.0f : 0.0f;
+    }
+  solve_k<K>(A, b, mu);
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    if (k < n) {
+      vp[0] = fmaf(-wp * mu[k], rx[k], vp[0]); vp[1] = fmaf(-wp * mu[k], ry[k], vp[1]); vp[2] = fmaf(-wp * mu[k], rz[k], vp[2]);
+      vel[3 * G.h[k]] = fmaf(G.wh[k] * mu[k], rx[k], vx[k]);
+      vel[3 * G.h[k] + 1] = fmaf(G.wh[k] * mu[k], ry[k], vy[k]);
+      vel[3 * G.h[k] + 2] = fmaf(G.wh[k] * mu[k], rz[k], vz[k]);
+    }
+  }
+  vel[3 * G.p] = vp[0]; vel[3 * G.p + 1] = vp[1]; vel[3 * G.p + 2] = vp[2];
+}
+// one thread per (replica, group)
+__global__ void large_shake_kernel(const LargeTopo T, const long long R, const float* pold, float* pos, float* vel,
+                                   const float inv_dt, const int sweeps, uint32_t* __restrict__ status) {
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < R * T.ngroups; g += (long long)gridDim.x * blockDim.x) {
+    const long long r = g / T.ngroups;
+    const int gi = (int)(g - r * T.ngroups);
+    const size_t off = (size_t)r * T.natoms * 3;
+    const bool ok = T.cmax > 1 ? lshake_group<3>(T, gi, pold + off, pos + off, vel ? vel + off : nullptr, inv_dt, sweeps)
+                               : lshake_group<1>(T, gi, pold + off, pos + off, vel ? vel + off : nullptr, inv_dt, sweeps);
+    if (!ok && status != nullptr) atomicOr(status + r, B200MD_FLAG_CONSTRAINT);
+  }
+}
+__global__ void large_rattle_kernel(const LargeTopo T, const long long R, const float* __restrict__ pos, float* vel) {
+  for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < R * T.ngroups; g += (long long)gridDim.x * blockDim.x) {
+    const long long r = g / T.ngroups;
+    const int gi = (int)(g - r * T.ngroups);
+    const size_t off = (size_t)r * T.natoms * 3;
+    if (T.cmax > 1) lrattle_group<3>(T, gi, pos + off, vel + off); else lrattle_group<1>(T, gi, pos + off, vel + off);
+  }
+}
+// kinetic energy after RATTLE (report steps of a rigid-bond run): the per-block partials large_vv2_kernel writes otherwise
+__global__ void __launch_bounds__(256)
+large_ekin_kernel(const LargeTopo T, const long long R, const float* __restrict__ vel, double* __restrict__ ekin) {
+  __shared__ double sred[8];
+  const int tid = threadIdx.x, a = blockIdx.x * 256 + tid;
+  for (long long r = blockIdx.y; r < R; r += gridDim.y) {
+    double e[1] = {0.0};
+    if (a < T.natoms) {
+      const float* v = vel + ((size_t)r * T.natoms + a) * 3;
+      e[0] = 0.5 * (double)__ldg(T.mass + a) * ((double)v[0] * v[0] + (double)v[1] * v[1] + (double)v[2] * v[2]);
+    }
+    lreduce<1, 256>(e, sred, tid);
+    if (tid == 0) ekin[r * gridDim.x + blockIdx.x] = e[0];
   }
 }
 
