@@ -1731,8 +1731,7 @@ static int large_integrate(const b200md_topology* topo, const ForceParams& P, co
     const unsigned long long gstep = I.step0 + (unsigned long long)s;
     const bool report = is_report(s);
     if (!fused_prev) {
-      if (rigid) CUDA_TRY(cudaMemcpyAsync(w.pos_old, pos, frame, cudaMemcpyDeviceToDevice, st));
-      large_vv1_kernel<<<(unsigned)((natom + 255) / 256), 256, 0, st>>>(L, I.dt, R, pos, vel, forces);
+      large_vv1_kernel<<<(unsigned)((natom + 255) / 256), 256, 0, st>>>(L, I.dt, R, pos, vel, forces, rigid ? w.pos_old : nullptr);
       g_launches.fetch_add(1);
       if (rigid) {
         large_shake_kernel<<<gcons, 128, 0, st>>>(L, R, w.pos_old, pos, vel, 1.0f / I.dt, 1, status);

@@ -951,8 +951,9 @@ __global__ void large_finish_kernel(const long long R, const double* __restrict_
 }
 
 // _first_VV of upstream torchmd.integrator: vel += 0.5 dt f / m ; pos += dt vel (one thread per atom)
+// (pos_old: rigid bonds -- x(t) is kept for SHAKE, which works along the old bond vectors)
 __global__ void large_vv1_kernel(const LargeTopo T, const float dt, const long long R, float* __restrict__ pos,
-                                 float* __restrict__ vel, const float* __restrict__ forces) {
+                                 float* __restrict__ vel, const float* __restrict__ forces, float* __restrict__ pos_old) {
   const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= R * T.natoms) return;
   const int a = (int)(g % T.natoms);
@@ -961,7 +962,9 @@ __global__ void large_vv1_kernel(const LargeTopo T, const float dt, const long l
   for (int c = 0; c < 3; ++c) {
     const float v = fmaf(hdt_m, forces[3 * g + c], vel[3 * g + c]);
     vel[3 * g + c] = v;
-    pos[3 * g + c] = fmaf(dt, v, pos[3 * g + c]);
+    const float x = pos[3 * g + c];
+    if (pos_old != nullptr) pos_old[3 * g + c] = x;
+    pos[3 * g + c] = fmaf(dt, v, x);
   }
 }
 
