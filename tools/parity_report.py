@@ -59,6 +59,25 @@ def main():
         f, e = gpu(g, pos, **kw)
         fr, er = oracle.forces(g.packed, pos, **kw)
         out.append(row("ala10 perturbed (vs C oracle)", mode, f, e, fr, er))
+    # solutes above 128 atoms (csrc/b200md_large.cuh): 312 atoms against the reference itself, the 1 040-atom benchmark
+    # bundle (ten chains 40 A apart) against the oracle
+    gl = load_golden("ala10x3")
+    for mode, kw in MODES.items():
+        f, e = gpu(gl, gl["pos"], **kw)
+        out.append(row("ala10x3, 312 atoms (large-solute kernels)", mode, f, e, gl[f"ref_{mode}_f64_forces"], gl[f"ref_{mode}_f64_energies"]))
+    copies, R = 10, 8
+    parL = g.par.tiled(copies)
+    shift = np.repeat(np.arange(copies), 104)[None, :, None] * np.array([40.0, 0.0, 0.0])
+    posL = (base[:R * copies].reshape(R, copies * 104, 3) + shift).astype(np.float32)
+    packedL = _cabi.PackedTopology(parL, _cabi.make_pair_index(104 * copies, parL.get_exclusions()))
+
+    class _G:
+        par = parL
+
+    for mode, kw in MODES.items():
+        f, e = gpu(_G, posL, **kw)
+        fr, er = oracle.forces(packedL, posL, **kw)
+        out.append(row("10 x ala10, 1 040 atoms (vs C oracle)", mode, f, e, fr, er))
     print("\n".join(out))
 
 
