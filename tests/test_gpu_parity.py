@@ -1681,6 +1681,22 @@ def test_library_calls_leave_the_current_device_alone():
     assert torch.cuda.current_device() == 0
     f_ref, e_ref = oracle.forces(g.packed, g["pos"])
     check_energies(e.cpu().numpy(), e_ref, "cuda:1")
+    # a solute above 128 atoms on the other device: the handle's second stream, workspace and cooperative launch live there
+    gl = load_golden("ala10x3")
+    res = []
+    for dev in ("cuda:1", "cuda:0"):
+        FL = Forces(Parameters.from_arrays(gl.par.to_arrays(), device=dev), **MODES["rf"])
+        sl = System(312, len(gl["pos"]), torch.float, dev)
+        sl.pos[:] = torch.tensor(gl["pos"], device=dev)
+        torch.cuda.set_device(0)
+        el = FL.compute_batch(sl.pos, sl.box, sl.forces)
+        integ = Integrator(sl, FL, timestep=1.0, device=dev, gamma=1.0, T=300.0, seed=2)
+        integ.energy_every = 4
+        integ.step(niter=9)
+        assert torch.cuda.current_device() == 0
+        res.append((el.cpu(), sl.pos.cpu(), integ.observables.cpu()))
+    for a, b in zip(*res):
+        assert torch.equal(a, b)
 
 
 def test_fire_update_kernel_vs_restatement():
