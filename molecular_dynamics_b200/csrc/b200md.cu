@@ -1636,7 +1636,9 @@ static int large_forces(const b200md_topology* topo, const ForceParams& P, int64
   // stream still orders the call as a whole.
   static const bool split_on = overlap_on && !(getenv("B200MD_LARGE_SPLIT") && atoi(getenv("B200MD_LARGE_SPLIT")) == 0);
   cudaStream_t sb = overlap_on ? topo->aux : st;
-  cudaStream_t sf = split_on ? topo->aux : st;  // stream of the bonded force launch
+  // stream of the bonded force launch: the second one, except on a report step, where that stream carries the FP64 energy
+  // kernels (the longer chain: 400 us against 233 us of force kernels for 256 x 1 040 atoms, plain) and the caller's stream both force kernels
+  cudaStream_t sf = (split_on && !with_energy) ? topo->aux : st;
   const int npart = pairs_on ? w.npart : w.nbonded_blocks;
   if (overlap_on && (with_energy || (split_on && pairs_on))) {
     CUDA_TRY(cudaEventRecord(topo->ev_fork, st));
