@@ -1181,7 +1181,7 @@ def test_large_solute_minimise_then_equilibrate():
     integ.step(niter=1000)                                                             # the potential within a few periods
     ek = integ.observables[-8:, :, _cabi.OBS_EKIN].mean().item()
     temp = 2.0 * ek / (3 * copies * 104 * 0.001987191)  # Ekin = 3/2 N kB T, kB in kcal/mol/K
-    assert 240.0 < temp < 360.0, temp
+    assert 270.0 < temp < 330.0, temp  # (300.5 K measured: deterministic seeds)
     assert torch.isfinite(s.pos).all()
 
 
