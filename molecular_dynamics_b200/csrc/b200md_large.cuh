@@ -91,8 +91,8 @@ constexpr int kLWin = 64, kLHalo = 320;
 
 // Bonded items are written once, on a scalar type T: T = float evaluates the FORCES (what every step needs; the
 // one-thread-per-item kernel was FP64 throughout in round 1 and, at 109 us per step of 256 x 1 040 atoms, the largest
-// kernel of a cutoff-mode step), T = double evaluates the ENERGIES of report steps (FORCE = false: no atomics).  An
-// ENERGY launch runs both, so the forces -- and with them the trajectory -- do not depend on how often energies are recorded.
+// kernel of a cutoff-mode step), T = double evaluates the ENERGIES of report steps (FORCE = false, NoSink).  A report
+// step runs both, so the forces -- and with them the trajectory -- do not depend on how often energies are recorded.
 template <typename T> struct v3t { T x, y, z; };
 template <typename T> __device__ __forceinline__ v3t<T> vsub(v3t<T> a, v3t<T> b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
 template <typename T> __device__ __forceinline__ v3t<T> vcross(v3t<T> a, v3t<T> b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
