@@ -15,8 +15,12 @@ def run(costs):
     """one schedule (the force tasks carry no energy arithmetic any more: the fused integrator and the single-shot
     forces_kernel share it), timed on the bench workload"""
     env = dict(os.environ, B200MD_COSTS=",".join(str(int(c)) for c in costs))
-    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--no-cpu", "--no-extra", "--strong-total", "0", "--steps", "5",
-                          "--warmup", "3", "--inner", "500", "--energy-every", "0"], env=env, capture_output=True, text=True).stdout
+    if "--forces" in sys.argv:  # the single-shot forces_kernel on BASELINE configs[1] instead of the fused integrator
+        cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--workload", "forces", "--no-cpu", "--no-energies", "--steps", "20", "--warmup", "3"]
+    else:
+        cmd = [sys.executable, os.path.join(ROOT, "bench.py"), "--no-cpu", "--no-extra", "--strong-total", "0", "--steps", "5",
+               "--warmup", "3", "--inner", "500", "--energy-every", "0"]
+    out = subprocess.run(cmd, env=env, capture_output=True, text=True).stdout
     try:
         return json.loads(out.strip().splitlines()[-1])["value"]
     except Exception:
@@ -25,11 +29,11 @@ def run(costs):
 
 def main():
     args = [x for x in sys.argv[1:] if not x.startswith("--")]
-    default = "105,120,52,30,77,230,380,400,100"
+    default = "126,144,52,30,77,230,380,400,100"
     costs = [int(x) for x in (args[0] if args else default).split(",")]
     best = run(costs)
     print("start", costs, f"{best:.4e}", flush=True)
-    for rnd in range(2):
+    for rnd in range(1 if "--forces" in sys.argv else 2):
         for k in range(len(costs)):
             if k == 7:
                 continue  # no general torsions in ALA10
